@@ -1,0 +1,57 @@
+/* oracle/mbg_oracle.h -- TEST INFRASTRUCTURE ONLY (see mbg_oracle.c header). */
+#ifndef MBG_ORACLE_H
+#define MBG_ORACLE_H
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* error-masking modes, numbered like the reference enum (MBG/ReadHelper.h:20-29) */
+enum { ORC_NO = 0, ORC_HPC = 1, ORC_COLLAPSE = 2, ORC_DINUC = 3, ORC_MSAT = 4, ORC_COLLAPSE_DINUC = 5, ORC_COLLAPSE_MSAT = 6 };
+
+/* one read part = one callback of the reference's iterateParts / iterateHashes (48 bytes, no padding) */
+typedef struct {
+	uint32_t read_idx;    /* index of the read in the order it was added */
+	uint32_t part_offset; /* ReadInfo.readName.second */
+	uint32_t raw_len;     /* ReadInfo.readLength */
+	uint32_t n_codes;     /* ReadInfo.readLengthHpc == number of codes of the part */
+	uint64_t code_begin;  /* first code in codes[] */
+	uint64_t pose_begin;  /* first of the n_codes+1 entries in poses[] */
+	uint64_t sel_begin;   /* first selected k-mer in positions[] / hashes[] */
+	uint32_t n_sel;       /* selected k-mers of the part */
+	uint32_t hashed;      /* 1 when n_codes >= k (the reference calls the hash callback for it) */
+} orc_part;
+
+typedef struct orc orc;
+
+orc* orc_create(int mode, uint32_t k, uint32_t w);
+void orc_free(orc* o);
+/* returns 0, or -1 palindromic k-mer that cannot be dropped / -2 unhashable k-mer (the reference aborts) */
+int orc_add_read(orc* o, const char* seq, uint64_t len);
+int orc_add_reads(orc* o, const char* bases, const uint64_t* offsets, uint64_t n_reads);
+void orc_build_table(orc* o);
+/* what: 0 parts 1 codes 2 poses 3 selected 4 nodes 5 edges 6 total selected k-mer instances in the table */
+uint64_t orc_count(const orc* o, int what);
+/* what: 0 parts 1 codes(u16) 2 poses(u32) 3 positions(u32) 4 hashes(u64 lo,hi) 5 node hashes(u64 lo,hi)
+ *       6 node coverage(u32) 7 node tip(u8) 8 edges(u32 x6: from,from_fw,to,to_fw,coverage,overlap) */
+const void* orc_data(const orc* o, int what);
+
+/* primitives, exported for the known-answer tests */
+uint64_t orc_char_hash(uint64_t code);
+uint16_t orc_complement(uint16_t code);
+uint32_t orc_code_motif_length(uint16_t code);
+uint32_t orc_max_code(void);
+uint64_t orc_murmur64a(const void* bytes, uint64_t len);
+void orc_kmer_hash(const uint16_t* codes, uint32_t k, uint64_t* lo, uint64_t* hi);
+void orc_rolling_hash(uint32_t s, const uint16_t* codes, uint64_t n, uint64_t* fw, uint64_t* bw);
+uint64_t orc_msat(const uint16_t* sym, const uint64_t* poses, uint64_t n, uint32_t max_motif, uint16_t* out_codes, uint64_t* out_poses);
+/* the scan-parallel formulation the CUDA kernels implement (DESIGN.md "K2"), restated sequentially so that its
+ * equivalence with orc_msat can be fuzzed on the CPU */
+uint64_t orc_msat_scanform(const uint16_t* sym, const uint64_t* poses, uint64_t n, uint32_t max_motif, uint16_t* out_codes, uint64_t* out_poses);
+uint64_t orc_syncmers_bruteforce(const uint16_t* codes, uint64_t n, uint32_t k, uint32_t w, uint32_t* out_positions);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

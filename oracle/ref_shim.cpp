@@ -1,0 +1,214 @@
+// oracle/ref_shim.cpp -- TEST INFRASTRUCTURE, not product code.
+//
+// A thin extern "C" shim (written for this repo) over the UNMODIFIED reference MBG objects compiled by
+// oracle/Makefile from /root/reference/src/hifioverlapper/MBG/src (commit 7bef84dd). It drives the reference's own
+// front end one read at a time and flattens what its callbacks receive, so that tests can compare the CUDA path,
+// the plain-C restatement (mbg_oracle.c) and the reference on identical inputs.
+//
+// Reference entry points used (all public in the reference):
+//   ReadpartIterator::iteratePartsOfRead / iterateHashesOfRead   ReadHelper.h:215-235
+//   ReadpartIterator::setMemoryReads                              ReadHelper.cpp:96-113
+//   loadReadsAsHashesMultithread                                  MBG.cpp:44-76   (external linkage)
+//   HashList::sortByHash / getEdgeCoverages / getSequenceOverlaps HashList.cpp:245-353,42-45,62-65
+//   FastHasher, getHash-derived tables, complement(), maxCode()   FastHasher.h, ErrorMaskHelper.cpp
+#include <cstdint>
+#include <cstring>
+#include <sstream>
+#include <string>
+#include <vector>
+#include "ReadHelper.h"
+#include "HashList.h"
+#include "FastHasher.h"
+#include "ErrorMaskHelper.h"
+#include "MBGCommon.h"
+
+uint64_t getHash(uint64_t key); // FastHasher.cpp:33
+void loadReadsAsHashesMultithread(HashList& result, const size_t kmerSize, const ReadpartIterator& partIterator, const size_t numThreads, std::ostream& log);
+
+namespace {
+
+struct Part {
+	uint32_t read_idx, part_offset, raw_len, n_codes;
+	uint64_t code_begin, pose_begin, sel_begin;
+	uint32_t n_sel, hashed;
+};
+
+struct Run {
+	std::vector<Part> parts;
+	std::vector<uint16_t> codes;
+	std::vector<uint32_t> poses;
+	std::vector<uint32_t> positions;
+	std::vector<uint64_t> hashes; // lo, hi interleaved
+	// table
+	std::vector<uint64_t> node_hash; // lo, hi interleaved, ascending canonical hash
+	std::vector<uint32_t> node_cov;
+	std::vector<uint8_t> node_tip;
+	std::vector<uint32_t> edges; // from_id, from_fw, to_id, to_fw, coverage, overlap
+	uint64_t total_selected = 0;
+};
+
+}
+
+extern "C" {
+
+// mode numbering = reference enum ErrorMasking (ReadHelper.h:20-29): 0 no, 1 hpc, 2 collapse, 3 dinuc, 4 msat,
+// 5 collapse-dinuc, 6 collapse-msat.
+void* refshim_run(int mode, uint64_t k, uint64_t w, const char* bases, const uint64_t* offsets, uint64_t n_reads, int build_table)
+{
+	Run* run = new Run;
+	std::vector<std::string> nofiles;
+	ReadpartIterator iterator { (size_t)k, (size_t)w, (ErrorMasking)mode, 1, nofiles, false, "" };
+	std::vector<std::pair<std::string, std::string>> memoryReads;
+	for (uint64_t r = 0; r < n_reads; r++)
+	{
+		std::string seq { bases + offsets[r], bases + offsets[r+1] };
+		if (seq.size() < 32) continue; // ReadHelper.h:838 (file path drops short reads before masking)
+		std::string name = std::to_string(r);
+		size_t firstPart = run->parts.size();
+		iterator.iteratePartsOfRead(name, seq, [run, r](const ReadInfo& read, const SequenceCharType& codes, const SequenceLengthType& poses, const std::string& raw)
+		{
+			Part p;
+			p.read_idx = (uint32_t)r;
+			p.part_offset = (uint32_t)read.readName.second;
+			p.raw_len = (uint32_t)read.readLength;
+			p.n_codes = (uint32_t)codes.size();
+			p.code_begin = run->codes.size();
+			p.pose_begin = run->poses.size();
+			p.sel_begin = 0;
+			p.n_sel = 0;
+			p.hashed = 0;
+			run->codes.insert(run->codes.end(), codes.begin(), codes.end());
+			for (size_t v : poses) run->poses.push_back((uint32_t)v);
+			run->parts.push_back(p);
+		});
+		iterator.iterateHashesOfRead(name, seq, [run, firstPart](const ReadInfo& read, const SequenceCharType& codes, const SequenceLengthType& poses, const std::string& raw, const std::vector<size_t>& positions, const std::vector<HashType>& hashes)
+		{
+			for (size_t i = firstPart; i < run->parts.size(); i++)
+			{
+				Part& p = run->parts[i];
+				if (p.part_offset != read.readName.second) continue;
+				p.hashed = 1;
+				p.sel_begin = run->positions.size();
+				p.n_sel = (uint32_t)positions.size();
+				for (size_t j = 0; j < positions.size(); j++)
+				{
+					run->positions.push_back((uint32_t)positions[j]);
+					run->hashes.push_back((uint64_t)hashes[j]);
+					run->hashes.push_back((uint64_t)(hashes[j] >> 64));
+				}
+				return;
+			}
+		});
+		if (build_table) memoryReads.emplace_back(name, seq);
+	}
+	if (build_table)
+	{
+		ReadpartIterator tableIterator { (size_t)k, (size_t)w, (ErrorMasking)mode, 1, nofiles, false, "" };
+		tableIterator.setMemoryReads(memoryReads);
+		HashList list { (size_t)k };
+		std::ostringstream log;
+		if (memoryReads.size() > 0) loadReadsAsHashesMultithread(list, k, tableIterator, 1, log);
+		list.sortByHash();
+		size_t n = list.size();
+		run->node_hash.resize(2*n);
+		run->node_cov.resize(n);
+		run->node_tip.resize(n);
+		for (auto pair : list.hashToNode)
+		{
+			run->node_hash[2*pair.second] = (uint64_t)pair.first;
+			run->node_hash[2*pair.second+1] = (uint64_t)(pair.first >> 64);
+		}
+		for (size_t i = 0; i < n; i++)
+		{
+			run->node_cov[i] = (uint32_t)list.coverage.get(i);
+			run->node_tip[i] = list.isTipKmer(i) ? 1 : 0;
+			run->total_selected += list.coverage.get(i);
+			for (int fw = 1; fw >= 0; fw--)
+			{
+				std::pair<size_t, bool> from { i, fw == 1 };
+				for (auto edge : list.getEdgeCoverages(from))
+				{
+					run->edges.push_back((uint32_t)i);
+					run->edges.push_back((uint32_t)fw);
+					run->edges.push_back((uint32_t)edge.first.first);
+					run->edges.push_back(edge.first.second ? 1 : 0);
+					run->edges.push_back((uint32_t)edge.second);
+					run->edges.push_back((uint32_t)list.getOverlap(from, edge.first));
+				}
+			}
+		}
+	}
+	return run;
+}
+
+void refshim_free(void* h) { delete (Run*)h; }
+
+uint64_t refshim_count(void* h, int what)
+{
+	Run* r = (Run*)h;
+	switch (what)
+	{
+		case 0: return r->parts.size();
+		case 1: return r->codes.size();
+		case 2: return r->poses.size();
+		case 3: return r->positions.size();
+		case 4: return r->node_cov.size();
+		case 5: return r->edges.size() / 6;
+		case 6: return r->total_selected;
+	}
+	return 0;
+}
+
+const void* refshim_data(void* h, int what)
+{
+	Run* r = (Run*)h;
+	switch (what)
+	{
+		case 0: return r->parts.data();
+		case 1: return r->codes.data();
+		case 2: return r->poses.data();
+		case 3: return r->positions.data();
+		case 4: return r->hashes.data();
+		case 5: return r->node_hash.data();
+		case 6: return r->node_cov.data();
+		case 7: return r->node_tip.data();
+		case 8: return r->edges.data();
+	}
+	return nullptr;
+}
+
+// Known-answer helpers (SURVEY.md 8c "tables", "FastHasher", "hash(vector)", "msat" rows).
+uint64_t refshim_max_code() { return maxCode(); }
+uint16_t refshim_complement(uint16_t c) { return complement(c); }
+uint64_t refshim_code_motif_length(uint16_t c) { return codeMotifLength(c); }
+uint64_t refshim_char_hash(uint64_t c) { return getHash(c); }
+void refshim_fasthasher(uint64_t s, const uint16_t* codes, uint64_t n, uint64_t* fw, uint64_t* bw)
+{
+	FastHasher hasher { (size_t)s };
+	for (uint64_t i = 0; i < n; i++)
+	{
+		hasher.addChar(codes[i]);
+		if (i >= s) hasher.removeChar(codes[i-s]);
+	}
+	*fw = hasher.getFwHash();
+	*bw = hasher.getBwHash();
+}
+void refshim_kmer_hash(const uint16_t* codes, uint64_t n, uint64_t* lo, uint64_t* hi)
+{
+	std::vector<uint16_t> v { codes, codes + n };
+	HashType h = hash(v);
+	*lo = (uint64_t)h;
+	*hi = (uint64_t)(h >> 64);
+}
+// multiRLECompress on an arbitrary symbol string (values 0..3), poses supplied by the caller (n+1 entries).
+uint64_t refshim_msat(const uint16_t* sym, const uint64_t* poses, uint64_t n, uint64_t max_motif, uint16_t* out_codes, uint64_t* out_poses)
+{
+	SequenceCharType s { sym, sym + n };
+	SequenceLengthType p { poses, poses + n + 1 };
+	auto result = multiRLECompress(s, p, max_motif);
+	for (size_t i = 0; i < result.first.size(); i++) out_codes[i] = result.first[i];
+	for (size_t i = 0; i < result.second.size(); i++) out_poses[i] = result.second[i];
+	return result.first.size();
+}
+
+}

@@ -1,0 +1,250 @@
+"""ctypes access to the CPU checkers (TEST INFRASTRUCTURE; product code never imports this).
+
+* ``Oracle``    -- oracle/libmbg_oracle.so, our plain-C restatement of the reference front end.
+* ``Reference`` -- oracle/_ref/libmbgref.so, the real reference objects (compiled from /root/reference by
+  oracle/Makefile) behind oracle/ref_shim.cpp.  Present only where it was built; it travels to the GPU box as a
+  prebuilt file.
+Both return the same flat numpy arrays so results can be compared with ``compare_runs``.
+"""
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+ORACLE_SO = os.path.join(ROOT, "oracle", "libmbg_oracle.so")
+REF_SO = os.path.join(ROOT, "oracle", "_ref", "libmbgref.so")
+
+MODES = {"no": 0, "hpc": 1, "collapse": 2, "dinuc": 3, "msat": 4, "collapse-dinuc": 5, "collapse-msat": 6}
+
+PART_DTYPE = np.dtype([
+    ("read_idx", "<u4"), ("part_offset", "<u4"), ("raw_len", "<u4"), ("n_codes", "<u4"),
+    ("code_begin", "<u8"), ("pose_begin", "<u8"), ("sel_begin", "<u8"), ("n_sel", "<u4"), ("hashed", "<u4")])
+assert PART_DTYPE.itemsize == 48
+
+
+def build_oracle():
+    if not os.path.exists(ORACLE_SO) or os.path.getmtime(ORACLE_SO) < os.path.getmtime(os.path.join(ROOT, "oracle", "mbg_oracle.c")):
+        subprocess.check_call(["make", "-C", os.path.join(ROOT, "oracle"), "libmbg_oracle.so"], stdout=subprocess.DEVNULL)
+    return ORACLE_SO
+
+
+def pack_reads(reads):
+    """list of bytes/str -> (uint8 array of concatenated bases, uint64 offsets[n+1])"""
+    bs = [r.encode() if isinstance(r, str) else bytes(r) for r in reads]
+    offsets = np.zeros(len(bs) + 1, dtype=np.uint64)
+    if bs:
+        offsets[1:] = np.cumsum([len(b) for b in bs], dtype=np.uint64)
+    bases = np.frombuffer(b"".join(bs), dtype=np.uint8).copy() if bs else np.zeros(0, dtype=np.uint8)
+    return bases, offsets
+
+
+def _arr(ptr, count, dtype):
+    dtype = np.dtype(dtype)
+    if count == 0 or not ptr:
+        return np.zeros(0, dtype=dtype)
+    buf = (C.c_char * (count * dtype.itemsize)).from_address(ptr)
+    return np.frombuffer(buf, dtype=dtype).copy()
+
+
+class RunResult(dict):
+    """parts, codes, poses, positions, hashes[n,2](lo,hi), node_hash[n,2], node_cov, node_tip, edges[n,6]"""
+    __getattr__ = dict.__getitem__
+
+
+def _collect(count, data, with_table):
+    res = RunResult()
+    res["parts"] = _arr(data(0), count(0), PART_DTYPE)
+    res["codes"] = _arr(data(1), count(1), "<u2")
+    res["poses"] = _arr(data(2), count(2), "<u4")
+    res["positions"] = _arr(data(3), count(3), "<u4")
+    res["hashes"] = _arr(data(4), count(3) * 2, "<u8").reshape(-1, 2)
+    if with_table:
+        res["node_hash"] = _arr(data(5), count(4) * 2, "<u8").reshape(-1, 2)
+        res["node_cov"] = _arr(data(6), count(4), "<u4")
+        res["node_tip"] = _arr(data(7), count(4), "u1")
+        res["edges"] = _arr(data(8), count(5) * 6, "<u4").reshape(-1, 6)
+        res["total_selected"] = int(count(6))
+    return res
+
+
+class Oracle:
+    def __init__(self):
+        self.lib = C.CDLL(build_oracle())
+        L = self.lib
+        L.orc_create.restype = C.c_void_p
+        L.orc_create.argtypes = [C.c_int, C.c_uint32, C.c_uint32]
+        L.orc_free.argtypes = [C.c_void_p]
+        L.orc_add_reads.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint64]
+        L.orc_add_reads.restype = C.c_int
+        L.orc_build_table.argtypes = [C.c_void_p]
+        L.orc_count.argtypes = [C.c_void_p, C.c_int]
+        L.orc_count.restype = C.c_uint64
+        L.orc_data.argtypes = [C.c_void_p, C.c_int]
+        L.orc_data.restype = C.c_void_p
+        L.orc_char_hash.argtypes = [C.c_uint64]
+        L.orc_char_hash.restype = C.c_uint64
+        L.orc_complement.argtypes = [C.c_uint16]
+        L.orc_complement.restype = C.c_uint16
+        L.orc_code_motif_length.argtypes = [C.c_uint16]
+        L.orc_code_motif_length.restype = C.c_uint32
+        L.orc_max_code.restype = C.c_uint32
+        L.orc_murmur64a.argtypes = [C.c_void_p, C.c_uint64]
+        L.orc_murmur64a.restype = C.c_uint64
+        L.orc_kmer_hash.argtypes = [C.c_void_p, C.c_uint32, C.c_void_p, C.c_void_p]
+        L.orc_rolling_hash.argtypes = [C.c_uint32, C.c_void_p, C.c_uint64, C.c_void_p, C.c_void_p]
+        for f in (L.orc_msat, L.orc_msat_scanform):
+            f.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64, C.c_uint32, C.c_void_p, C.c_void_p]
+            f.restype = C.c_uint64
+        L.orc_syncmers_bruteforce.argtypes = [C.c_void_p, C.c_uint64, C.c_uint32, C.c_uint32, C.c_void_p]
+        L.orc_syncmers_bruteforce.restype = C.c_uint64
+
+    def run(self, mode, k, w, reads, table=True):
+        bases, offsets = reads if isinstance(reads, tuple) else pack_reads(reads)
+        L = self.lib
+        h = L.orc_create(MODES[mode] if isinstance(mode, str) else mode, k, w)
+        try:
+            rc = L.orc_add_reads(h, bases.ctypes.data, offsets.ctypes.data, len(offsets) - 1)
+            if rc != 0:
+                raise RuntimeError("oracle: palindromic k-mer" if rc == -1 else "oracle: unhashable k-mer")
+            if table:
+                L.orc_build_table(h)
+            return _collect(lambda w_: L.orc_count(h, w_), lambda w_: L.orc_data(h, w_), table)
+        finally:
+            L.orc_free(h)
+
+    def char_hash(self, c):
+        return int(self.lib.orc_char_hash(c))
+
+    def complement(self, c):
+        return int(self.lib.orc_complement(c))
+
+    def kmer_hash(self, codes):
+        codes = np.ascontiguousarray(codes, dtype=np.uint16)
+        lo, hi = C.c_uint64(), C.c_uint64()
+        self.lib.orc_kmer_hash(codes.ctypes.data, len(codes), C.byref(lo), C.byref(hi))
+        return lo.value, hi.value
+
+    def rolling_hash(self, s, codes):
+        codes = np.ascontiguousarray(codes, dtype=np.uint16)
+        fw, bw = C.c_uint64(), C.c_uint64()
+        self.lib.orc_rolling_hash(s, codes.ctypes.data, len(codes), C.byref(fw), C.byref(bw))
+        return fw.value, bw.value
+
+    def _msat(self, fn, sym, poses, max_motif):
+        sym = np.ascontiguousarray(sym, dtype=np.uint16)
+        poses = np.ascontiguousarray(poses, dtype=np.uint64)
+        oc = np.zeros(len(sym) + 1, dtype=np.uint16)
+        op = np.zeros(len(sym) + 2, dtype=np.uint64)
+        n = fn(sym.ctypes.data, poses.ctypes.data, len(sym), max_motif, oc.ctypes.data, op.ctypes.data)
+        return oc[:n].copy(), op[:n + 1].copy()
+
+    def msat(self, sym, poses=None, max_motif=6):
+        poses = np.arange(len(sym) + 1, dtype=np.uint64) if poses is None else poses
+        return self._msat(self.lib.orc_msat, sym, poses, max_motif)
+
+    def msat_scanform(self, sym, poses=None, max_motif=6):
+        poses = np.arange(len(sym) + 1, dtype=np.uint64) if poses is None else poses
+        return self._msat(self.lib.orc_msat_scanform, sym, poses, max_motif)
+
+    def syncmers_bruteforce(self, codes, k, w):
+        codes = np.ascontiguousarray(codes, dtype=np.uint16)
+        out = np.zeros(max(len(codes), 1), dtype=np.uint32)
+        n = self.lib.orc_syncmers_bruteforce(codes.ctypes.data, len(codes), k, w, out.ctypes.data)
+        return out[:n].copy()
+
+
+def have_reference():
+    return os.path.exists(REF_SO)
+
+
+class Reference:
+    def __init__(self):
+        self.lib = C.CDLL(REF_SO)
+        L = self.lib
+        L.refshim_run.restype = C.c_void_p
+        L.refshim_run.argtypes = [C.c_int, C.c_uint64, C.c_uint64, C.c_void_p, C.c_void_p, C.c_uint64, C.c_int]
+        L.refshim_free.argtypes = [C.c_void_p]
+        L.refshim_count.argtypes = [C.c_void_p, C.c_int]
+        L.refshim_count.restype = C.c_uint64
+        L.refshim_data.argtypes = [C.c_void_p, C.c_int]
+        L.refshim_data.restype = C.c_void_p
+        L.refshim_max_code.restype = C.c_uint64
+        L.refshim_complement.argtypes = [C.c_uint16]
+        L.refshim_complement.restype = C.c_uint16
+        L.refshim_code_motif_length.argtypes = [C.c_uint16]
+        L.refshim_code_motif_length.restype = C.c_uint64
+        L.refshim_char_hash.argtypes = [C.c_uint64]
+        L.refshim_char_hash.restype = C.c_uint64
+        L.refshim_fasthasher.argtypes = [C.c_uint64, C.c_void_p, C.c_uint64, C.c_void_p, C.c_void_p]
+        L.refshim_kmer_hash.argtypes = [C.c_void_p, C.c_uint64, C.c_void_p, C.c_void_p]
+        L.refshim_msat.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64, C.c_uint64, C.c_void_p, C.c_void_p]
+        L.refshim_msat.restype = C.c_uint64
+
+    def run(self, mode, k, w, reads, table=True):
+        bases, offsets = reads if isinstance(reads, tuple) else pack_reads(reads)
+        L = self.lib
+        h = L.refshim_run(MODES[mode] if isinstance(mode, str) else mode, k, w, bases.ctypes.data, offsets.ctypes.data, len(offsets) - 1, 1 if table else 0)
+        try:
+            return _collect(lambda w_: L.refshim_count(h, w_), lambda w_: L.refshim_data(h, w_), table)
+        finally:
+            L.refshim_free(h)
+
+    def char_hash(self, c):
+        return int(self.lib.refshim_char_hash(c))
+
+    def complement(self, c):
+        return int(self.lib.refshim_complement(c))
+
+    def kmer_hash(self, codes):
+        codes = np.ascontiguousarray(codes, dtype=np.uint16)
+        lo, hi = C.c_uint64(), C.c_uint64()
+        self.lib.refshim_kmer_hash(codes.ctypes.data, len(codes), C.byref(lo), C.byref(hi))
+        return lo.value, hi.value
+
+    def rolling_hash(self, s, codes):
+        codes = np.ascontiguousarray(codes, dtype=np.uint16)
+        fw, bw = C.c_uint64(), C.c_uint64()
+        self.lib.refshim_fasthasher(s, codes.ctypes.data, len(codes), C.byref(fw), C.byref(bw))
+        return fw.value, bw.value
+
+    def msat(self, sym, poses=None, max_motif=6):
+        sym = np.ascontiguousarray(sym, dtype=np.uint16)
+        poses = np.arange(len(sym) + 1, dtype=np.uint64) if poses is None else np.ascontiguousarray(poses, dtype=np.uint64)
+        oc = np.zeros(len(sym) + 1, dtype=np.uint16)
+        op = np.zeros(len(sym) + 2, dtype=np.uint64)
+        n = self.lib.refshim_msat(sym.ctypes.data, poses.ctypes.data, len(sym), max_motif, oc.ctypes.data, op.ctypes.data)
+        return oc[:n].copy(), op[:n + 1].copy()
+
+
+def sorted_edges(edges):
+    if len(edges) == 0:
+        return edges
+    order = np.lexsort((edges[:, 3], edges[:, 2], edges[:, 1], edges[:, 0]))
+    return edges[order]
+
+
+def compare_runs(a, b, table=True, what=""):
+    """assert that two RunResults are identical (parts in the same (read, part) order)."""
+    assert len(a.parts) == len(b.parts), f"{what}: part count {len(a.parts)} != {len(b.parts)}"
+    for f in ("read_idx", "part_offset", "raw_len", "n_codes", "n_sel", "hashed"):
+        assert np.array_equal(a.parts[f], b.parts[f]), f"{what}: parts.{f} differ"
+    for f in ("codes", "poses", "positions", "hashes"):
+        assert a[f].shape == b[f].shape, f"{what}: {f} shape {a[f].shape} != {b[f].shape}"
+        assert np.array_equal(a[f], b[f]), f"{what}: {f} differ"
+    if table:
+        assert np.array_equal(a.node_hash, b.node_hash), f"{what}: node hashes differ"
+        assert np.array_equal(a.node_cov, b.node_cov), f"{what}: node coverage differs"
+        assert np.array_equal(a.node_tip, b.node_tip), f"{what}: tip flags differ"
+        assert np.array_equal(sorted_edges(a.edges), sorted_edges(b.edges)), f"{what}: edges differ"
+
+
+def lcg_bases(seed, n):
+    """SURVEY.md 8(c) generator: x <- x*6364136223846793005 + 1442695040888963407, base = ACGT[(x>>33)&3]."""
+    out = bytearray(n)
+    x = seed
+    for i in range(n):
+        x = (x * 6364136223846793005 + 1442695040888963407) & 0xFFFFFFFFFFFFFFFF
+        out[i] = b"ACGT"[(x >> 33) & 3]
+    return bytes(out)
