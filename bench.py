@@ -1,0 +1,375 @@
+#!/usr/bin/env python
+"""bench.py -- throughput of the MBG graph-build front end (BASELINE.json metric) on N B200s.
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload chr20|ecoli|herro] [--scale F]
+
+A "step" is one pass of the hot path (collapse -> microsatellite coding -> syncmer selection -> k-mer hashing ->
+k-mer table: nodes + edges) over one batch of synthetic HiFi-shaped reads.  One process per GPU (torchrun for N > 1);
+reads are sharded across ranks (weak scaling: genome and read count grow with N), selected k-mers are exchanged to
+their owner rank with an NCCL all-to-all, and each rank counts its partition of the k-mer space.
+
+`value`      raw bases/s with the 2-bit packed reads already resident in HBM (device time, CUDA events, max over ranks)
+`e2e`        the same metric through the C ABI from pinned HOST buffers: ASCII reads -> H2D -> pack -> ... -> table
+             -> D2H of the ordered node/edge table, every step
+`roofline`   dominant kernel against the measured HBM copy peak (MEASURED_PEAKS.json)
+`cpu_baseline` the reference's own hot path (oracle/_ref, all host cores) on a bounded sample of the same reads
+
+--impl reference times ONLY the reference's CPU implementation (rank 0), same metric/unit/config.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import tempfile
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+WORKLOADS = {
+    # name: genome bp per GPU, coverage, read length range, error ppm, k, w
+    "chr20": dict(genome=64_000_000, coverage=30, len_min=15000, len_max=20000, error_ppm=1000, k=1001, w=100,
+                  desc="human chr20-shaped synthetic HiFi 30x (64 Mbp per GPU, 15-20 kb reads, 0.1% errors), MBG k=1001 w=100 collapse-msat"),
+    "ecoli": dict(genome=5_000_000, coverage=24, len_min=11000, len_max=19000, error_ppm=1000, k=1001, w=100,
+                  desc="E. coli-shaped synthetic HiFi 24x (5 Mbp, ~15 kb reads), MBG k=1001 w=100 collapse-msat"),
+    "herro": dict(genome=64_000_000, coverage=30, len_min=30000, len_max=50000, error_ppm=7500, k=1001, w=100,
+                  desc="HERRO/ONT-duplex-shaped synthetic reads 30x (64 Mbp per GPU, 30-50 kb reads, 0.75% errors), MBG k=1001 w=100 collapse-msat"),
+}
+METRIC = "raw HiFi bases/s through the MBG graph-build front end (HPC+microsatellite compression, syncmer selection k=1001 w=100, 128-bit k-mer hashing, k-mer counting)"
+SEED_GENOME, SEED_READS = 7, 11
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled during the timed region"""
+
+    def __init__(self, device):
+        self.device, self.rows, self.proc = device, [], None
+
+    def start(self):
+        q = "clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.device), f"--query-gpu={q}", "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.thread = threading.Thread(target=self._read, daemon=True)
+            self.thread.start()
+        except OSError:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([x.strip() for x in line.split(",")])
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], None, set()
+        for r in self.rows:
+            if len(r) < 7:
+                continue
+            try:
+                sm.append(float(r[0]))
+                mx = float(r[1])
+            except ValueError:
+                continue
+            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), r[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": mx, "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def measured_peak():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        return float(json.load(open(p))["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
+
+
+def make_reads(wl, world, rank, scale, pinned_alloc=None, max_reads=None):
+    """this rank's shard: the genome grows with the world size (weak scaling), reads are dealt in contiguous blocks"""
+    from verkko_b200 import synth
+    genome_len = int(wl["genome"] * scale) * world
+    g = synth.genome(SEED_GENOME, genome_len)
+    mean_len = (wl["len_min"] + wl["len_max"]) / 2
+    per_rank = int(wl["genome"] * scale * wl["coverage"] / mean_len)
+    if max_reads:
+        per_rank = min(per_rank, max_reads)
+    first = rank * per_rank
+    offsets = synth.read_offsets(SEED_READS, g, per_rank, wl["len_min"], wl["len_max"], wl["error_ppm"], first_read=first)
+    nbytes = int(offsets[-1])
+    if pinned_alloc:
+        buf = pinned_alloc(nbytes + 64)
+        bases = buf.array[:nbytes]
+    else:
+        buf, bases = None, np.empty(nbytes, dtype=np.uint8)
+    synth.fill_reads(SEED_READS, g, per_rank, wl["len_min"], wl["len_max"], offsets, bases, wl["error_ppm"], first_read=first)
+    return bases, offsets, buf
+
+
+def reference_arm(args, wl):
+    """the reference's own CPU implementation of the path on all host cores, on a bounded sample of the workload"""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import ctypes as C
+    from oracle_lib import REF_SO, Oracle, have_reference
+    cores = os.cpu_count() or 1
+    budget_s = 25.0
+    # sample size: ~25 s of work at ~25 Mbase/s per core, capped by the producer-bound scaling of the reference
+    est_rate = 25e6 * min(cores, 8)
+    sample_reads = max(64, int(min(est_rate * budget_s / ((wl["len_min"] + wl["len_max"]) / 2), 20000)))
+    bases, offsets, _ = make_reads(wl, 1, 0, args.scale, max_reads=sample_reads)
+    n_reads = len(offsets) - 1
+    n_bases = int(offsets[-1])
+    times = []
+    if have_reference():
+        kind = "reference"
+        lib = C.CDLL(REF_SO)
+        lib.refshim_time_file.restype = C.c_double
+        lib.refshim_time_file.argtypes = [C.c_int, C.c_uint64, C.c_uint64, C.c_char_p, C.c_uint64, C.c_void_p, C.c_void_p]
+        with tempfile.TemporaryDirectory() as d:
+            fa = os.path.join(d, "sample.fa")
+            with open(fa, "wb") as f:
+                for i in range(n_reads):
+                    f.write(b">r%d\n" % i)
+                    f.write(bases[int(offsets[i]):int(offsets[i + 1])].tobytes())
+                    f.write(b"\n")
+            sel, dist = C.c_uint64(), C.c_uint64()
+            for it in range(args.warmup + args.steps):
+                devnull = os.open(os.devnull, os.O_WRONLY)
+                saved = os.dup(2)
+                os.dup2(devnull, 2)
+                try:
+                    t = lib.refshim_time_file(6, wl["k"], wl["w"], fa.encode(), cores, C.byref(sel), C.byref(dist))
+                finally:
+                    os.dup2(saved, 2)
+                    os.close(devnull)
+                    os.close(saved)
+                if it >= args.warmup:
+                    times.append(t)
+            selected = sel.value
+    else:
+        kind, cores = "port", 1
+        orc = Oracle()
+        for it in range(args.warmup + args.steps):
+            t0 = time.time()
+            r = orc.run("collapse-msat", wl["k"], wl["w"], (bases, offsets))
+            if it >= args.warmup:
+                times.append(time.time() - t0)
+        selected = len(r.positions)
+    sec = float(np.mean(times))
+    value = n_bases / sec
+    sample = f"{n_reads} reads / {n_bases} bases of the workload (FASTA file, page cache warm), {cores} worker threads + reader, loadReadsAsHashesMultithread"
+    line = {
+        "impl": "reference", "metric": METRIC, "value": value, "unit": "bases/s", "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": sec * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u16/u64 integer", "data": "synthetic",
+        "config": {"workload": wl["desc"] + f" [bounded sample: {n_reads} reads]", "k": wl["k"], "w": wl["w"], "error_masking": "collapse-msat"},
+        "kmers_per_s": selected / sec,
+        "cpu_baseline": {"value": value, "unit": "bases/s", "cores": cores, "kind": kind, "sample": sample},
+        "e2e": {"value": value, "unit": "bases/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line))
+
+
+def cpu_baseline(wl, scale):
+    """bounded sample (about 10-30 s of CPU work) of the same workload through the reference's own code"""
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import ctypes as C
+    from oracle_lib import REF_SO, Oracle, have_reference
+    cores = os.cpu_count() or 1
+    sample_reads = 3000 if have_reference() else 300
+    bases, offsets, _ = make_reads(wl, 1, 0, scale, max_reads=sample_reads)
+    n_reads, n_bases = len(offsets) - 1, int(offsets[-1])
+    if have_reference():
+        lib = C.CDLL(REF_SO)
+        lib.refshim_time_file.restype = C.c_double
+        lib.refshim_time_file.argtypes = [C.c_int, C.c_uint64, C.c_uint64, C.c_char_p, C.c_uint64, C.c_void_p, C.c_void_p]
+        with tempfile.TemporaryDirectory() as d:
+            fa = os.path.join(d, "sample.fa")
+            with open(fa, "wb") as f:
+                for i in range(n_reads):
+                    f.write(b">r%d\n" % i + bases[int(offsets[i]):int(offsets[i + 1])].tobytes() + b"\n")
+            devnull = os.open(os.devnull, os.O_WRONLY)
+            saved = os.dup(2)
+            os.dup2(devnull, 2)
+            try:
+                lib.refshim_time_file(6, wl["k"], wl["w"], fa.encode(), cores, None, None)       # warm
+                t = lib.refshim_time_file(6, wl["k"], wl["w"], fa.encode(), cores, None, None)
+            finally:
+                os.dup2(saved, 2)
+                os.close(devnull)
+                os.close(saved)
+        return {"value": n_bases / t, "unit": "bases/s", "cores": cores, "kind": "reference",
+                "sample": f"{n_reads} reads / {n_bases} bases of the workload, MBG's loadReadsAsHashesMultithread with {cores} worker threads (oracle/_ref)"}
+    orc = Oracle()
+    t0 = time.time()
+    orc.run("collapse-msat", wl["k"], wl["w"], (bases, offsets))
+    t = time.time() - t0
+    return {"value": n_bases / t, "unit": "bases/s", "cores": 1, "kind": "port",
+            "sample": f"{n_reads} reads / {n_bases} bases of the workload, oracle/mbg_oracle.c single thread"}
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default="chr20", choices=list(WORKLOADS))
+    ap.add_argument("--scale", type=float, default=1.0, help="shrink the genome (and read count) for quick runs")
+    ap.add_argument("--e2e-steps", type=int, default=2)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    wl = WORKLOADS[args.workload]
+    if args.impl == "reference":
+        reference_arm(args, wl)
+        return
+
+    import torch
+    import torch.distributed as dist
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a GPU: libmbgfe has no CPU path")
+    torch.cuda.set_device(local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    from verkko_b200 import MbgFrontEnd
+    from verkko_b200.distributed import DistributedCounter
+    from verkko_b200.frontend import NO_TABLE
+
+    fe = MbgFrontEnd(wl["k"], wl["w"], "collapse-msat", device=local_rank, rank=rank, world=world, flags=NO_TABLE if world > 1 else 0)
+    bases, offsets, pinned = make_reads(wl, world, rank, args.scale, pinned_alloc=fe.pinned)
+    n_bases = int(offsets[-1])
+    counter = DistributedCounter(fe, world, rank) if world > 1 else None
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+            torch.cuda.synchronize()
+
+    def step():
+        fe.process()
+        if counter:
+            counter.exchange_and_count()
+
+    # ---- resident throughput
+    fe.add_reads(bases, offsets)
+    fe.upload()
+    for _ in range(args.warmup):
+        step()
+    sampler = ClockSampler(local_rank)
+    barrier()
+    sampler.start()
+    stage_ms = {}
+    fe.timer_start()
+    t0 = time.time()
+    for _ in range(args.steps):
+        step()
+        st = fe.stats()
+        for kname in ("ms_collapse", "ms_msat", "ms_select", "ms_hash", "ms_nodes", "ms_edges", "ms_process"):
+            stage_ms[kname] = stage_ms.get(kname, 0.0) + st[kname]
+        if counter:
+            stage_ms["ms_exchange"] = stage_ms.get("ms_exchange", 0.0) + counter.last_exchange_ms
+    device_ms = fe.timer_stop()
+    barrier()
+    wall_ms = (time.time() - t0) * 1e3
+    clocks = sampler.stop()
+    st = fe.stats()
+    launches = st["launches"] * args.steps + (counter.launches * args.steps if counter else 0)
+    t = torch.tensor([device_ms, wall_ms, float(n_bases), float(st["selected"])], dtype=torch.float64, device="cuda")
+    if world > 1:
+        mx = t.clone()
+        dist.all_reduce(mx, op=dist.ReduceOp.MAX)
+        sm = t.clone()
+        dist.all_reduce(sm, op=dist.ReduceOp.SUM)
+        device_ms, wall_ms, total_bases, total_sel = float(mx[0]), float(mx[1]), float(sm[2]), float(sm[3])
+    else:
+        total_bases, total_sel = float(n_bases), float(st["selected"])
+    ms_per_step = device_ms / args.steps
+    value = total_bases / (ms_per_step * 1e-3)
+    parts_stats = dict(st)
+    fe.parts()
+    st = fe.stats()
+
+    # ---- end to end through the C ABI from pinned host buffers
+    e2e_ms, h2d, d2h = [], 0, 0
+    for it in range(1 + args.e2e_steps):
+        barrier()
+        t0 = time.time()
+        fe.add_reads(bases, offsets)
+        fe.upload()
+        st_up = fe.stats()
+        step()
+        if world == 1:
+            cov = fe.node_coverage()
+            fe.node_hashes()
+            fe.edges()
+            checksum = int(cov.sum())
+        else:
+            checksum = counter.download_counts()
+        barrier()
+        if it > 0:
+            e2e_ms.append((time.time() - t0) * 1e3)
+        st_e = fe.stats()
+        h2d, d2h = st_up["h2d_bytes"], st_e["d2h_bytes"]
+    e2e_t = torch.tensor([float(np.mean(e2e_ms))], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(e2e_t, op=dist.ReduceOp.MAX)
+    e2e_value = total_bases / (float(e2e_t[0]) * 1e-3)
+
+    if rank == 0:
+        peak, peak_src = measured_peak()
+        R, C1, C2, S = st["raw_bases"], st["collapsed_symbols"], st["codes"], st["selected"]
+        per_step = {k_: v / args.steps for k_, v in stage_ms.items()}
+        # algorithmic bytes per launch, from this run's exact counts
+        alg = {
+            "k_collapse": (R / 4 + C1 / 4, per_step["ms_collapse"]),
+            "k_msat": (C1 / 4 + 2 * C2, per_step["ms_msat"]),
+            "k_select": (2 * C2 + C2 / 8, per_step["ms_select"]),
+            "k_kmer_hash": (2 * C2 + 20 * S, per_step["ms_hash"]),
+            "k_insert_nodes": (64 * S + 16 * S, per_step["ms_nodes"]),
+            "k_insert_edges": (64 * S + 20 * S, per_step["ms_edges"]),
+        }
+        dominant = max(alg, key=lambda n: alg[n][1])
+        byts, ms = alg[dominant]
+        achieved = byts / (ms * 1e-3) / 1e9 if ms > 0 else 0.0
+        line = {
+            "metric": METRIC, "value": value, "unit": "bases/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "u16 codes / u64 hashes (integer)", "data": "synthetic",
+            "config": {"workload": wl["desc"] + (f" x{args.scale}" if args.scale != 1.0 else ""), "k": wl["k"], "w": wl["w"], "error_masking": "collapse-msat",
+                       "reads_per_gpu": len(offsets) - 1, "bases_per_gpu": n_bases, "parallelism": f"reads sharded over {world} GPU(s), k-mers owned by hash range",
+                       "l2": "inputs and intermediates (>= 0.48 GB packed reads per pass) are larger than the 126 MB L2; no flush needed"},
+            "kmers_per_s": total_sel / (ms_per_step * 1e-3),
+            "counts": {"raw_bases": R, "collapsed_symbols": C1, "codes": C2, "selected_kmers": S, "distinct_kmers": parts_stats["distinct"], "distinct_edges": parts_stats["distinct_edges"]},
+            "stage_ms_per_step": per_step, "wall_ms_per_step": wall_ms / args.steps,
+            "clocks": clocks,
+            "e2e": {"value": e2e_value, "unit": "bases/s", "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h), "ms_per_step": float(e2e_t[0]), "checksum": checksum},
+            "gpu_launches": int(launches),
+            "roofline": {"bound": "hbm", "kernel": dominant, "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": None,
+                         "peak_source": peak_src,
+                         "all_kernels_GBps": {n: (b / (m * 1e-3) / 1e9 if m > 0 else None) for n, (b, m) in alg.items()}},
+        }
+        if world == 1 and not args.no_cpu_baseline:
+            line["cpu_baseline"] = cpu_baseline(wl, args.scale)
+        print(json.dumps(line))
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

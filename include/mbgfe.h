@@ -1,0 +1,179 @@
+/* mbgfe.h -- C ABI of libmbgfe: the B200 (sm_100a) front end of MBG's graph build.
+ *
+ * This is the drop-in boundary for ONE path of marbl/verkko: what MBG does between "a read arrives" and "the k-mer
+ * table is built" in Verkko's buildGraph rule.  Reference = the MBG tree vendored at
+ * /root/reference/src/hifioverlapper/MBG/src (commit 7bef84dd), cited below as MBG/.  Each entry point names the
+ * reference interface it replaces.  Plain C types only; every array handed out is owned by the library and stays
+ * valid until the next mbgfe_process()/mbgfe_run()/mbgfe_reset() on the handle or mbgfe_destroy().
+ *
+ * Errors: functions return 0 on success, a negative MBGFE_E_* otherwise; mbgfe_last_error() describes the failure.
+ * The reference reports the same conditions with exit(1)/abort() (MBG/main.cpp:158-198, MBG/ReadHelper.h:775-783);
+ * the MBG-compatible command line maps the codes back to those behaviours.  There is NO CPU fallback: without a
+ * usable sm_100 device mbgfe_create() fails with MBGFE_E_CUDA.
+ */
+#ifndef MBGFE_H
+#define MBGFE_H
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define MBGFE_ABI_VERSION 1
+
+/* --error-masking, numbered like the reference enum ErrorMasking (MBG/ReadHelper.h:20-29) */
+enum {
+	MBGFE_MASK_NO = 0, MBGFE_MASK_HPC = 1, MBGFE_MASK_COLLAPSE = 2, MBGFE_MASK_DINUC = 3, MBGFE_MASK_MSAT = 4,
+	MBGFE_MASK_COLLAPSE_DINUC = 5, MBGFE_MASK_COLLAPSE_MSAT = 6
+};
+
+enum {
+	MBGFE_OK = 0,
+	MBGFE_E_PARAM = -1,      /* MBG/main.cpp:158-198 validation: k odd >= 31, 1 <= w <= k-30, ... */
+	MBGFE_E_CUDA = -2,       /* no device / CUDA runtime failure */
+	MBGFE_E_IO = -3,         /* unreadable input (MBG/MBG.cpp:1542-1549) */
+	MBGFE_E_PALINDROME = -4, /* palindromic k-mer that cannot be dropped (MBG/ReadHelper.h:775-777) */
+	MBGFE_E_UNHASHABLE = -5, /* fwHash == bwHash on a non-palindrome (MBG/ReadHelper.h:782-783) */
+	MBGFE_E_STATE = -6,      /* call order (results requested before a run, ...) */
+	MBGFE_E_LIMIT = -7       /* input exceeds a documented limit (read longer than 2^32-1 bases, k too large, ...) */
+};
+
+/* flags */
+enum {
+	MBGFE_KEEP_CODES = 1,   /* keep the per-part code arrays for mbgfe_data(MBGFE_CODES)         (iterateParts)  */
+	MBGFE_KEEP_POSES = 2,   /* also compute/keep the per-code positions (poses)                   (iterateParts)  */
+	MBGFE_NO_TABLE   = 4,   /* stop after k-mer hashing: no node/edge table                       (iterateHashes) */
+	MBGFE_NO_EDGES   = 8    /* count k-mers (nodes, tips) but skip the adjacency pass                              */
+};
+
+typedef struct {
+	uint32_t abi_version;     /* MBGFE_ABI_VERSION */
+	uint32_t k;               /* -k  (MBG/main.cpp:14) */
+	uint32_t w;               /* -w  (MBG/main.cpp:15); s-mer size is k-w+1 (MBG/ReadHelper.h:1085) */
+	uint32_t error_masking;   /* --error-masking (MBG/main.cpp:18) */
+	uint32_t kmer_abundance;  /* -a  (MBG/main.cpp:16): minimum coverage of nodes and edges in the filtered tables */
+	uint32_t flags;
+	int32_t  device;          /* CUDA device ordinal */
+	uint32_t rank;            /* this process's shard of the k-mer space, 0 <= rank < world (single GPU: 0 of 1) */
+	uint32_t world;
+	uint32_t reserved;
+	uint64_t table_slots;     /* initial node-table capacity in slots (0 = sized from the input); it grows on demand */
+} mbgfe_params;
+
+/* One read part == one callback of ReadpartIterator::iterateParts / iterateHashes (MBG/ReadHelper.h:167-235);
+ * fields follow ReadInfo (MBG/ReadHelper.h:81-88).  Parts are listed in (read, offset) order. 48 bytes. */
+typedef struct {
+	uint32_t read_idx;     /* index of the read in the order the reads were added */
+	uint32_t part_offset;  /* ReadInfo.readName.second */
+	uint32_t raw_len;      /* ReadInfo.readLength */
+	uint32_t n_codes;      /* ReadInfo.readLengthHpc == number of codes in the part */
+	uint64_t code_begin;   /* index of the part's first code in MBGFE_CODES */
+	uint64_t pose_begin;   /* index of the first of its n_codes+1 entries in MBGFE_POSES */
+	uint64_t sel_begin;    /* index of its first selected k-mer in MBGFE_POSITIONS / MBGFE_HASHES */
+	uint32_t n_sel;        /* number of selected k-mers (positions.size() in the reference callback) */
+	uint32_t hashed;       /* 1 when n_codes >= k, i.e. the reference would call the iterateHashes callback */
+} mbgfe_part;
+
+typedef struct { uint64_t lo, hi; } mbgfe_hash128;     /* HashType == unsigned __int128 (MBG/MBGCommon.h:10) */
+
+/* HashList after loadReadsAsHashesMultithread + sortByHash (MBG/MBG.cpp:44-76, MBG/HashList.cpp:245-353) */
+typedef struct {
+	uint32_t from, from_fw, to, to_fw; /* canonical form, MBG/MBGCommon.cpp:78-89; ids = rank of the canonical hash */
+	uint32_t coverage;                 /* HashList::getEdgeCoverage */
+	uint32_t overlap;                  /* HashList::getOverlap, in codes */
+} mbgfe_edge;
+
+/* result arrays for mbgfe_count()/mbgfe_data() */
+enum {
+	MBGFE_PARTS = 0,      /* mbgfe_part[]                                                                    */
+	MBGFE_CODES = 1,      /* uint16_t[]  (needs MBGFE_KEEP_CODES)  SequenceCharType of each part             */
+	MBGFE_POSES = 2,      /* uint32_t[]  (needs MBGFE_KEEP_POSES)  SequenceLengthType of each part           */
+	MBGFE_POSITIONS = 3,  /* uint32_t[]  selected k-mer start positions, part-local, in codes                */
+	MBGFE_HASHES = 4,     /* mbgfe_hash128[] forward hashes of the selected k-mers                           */
+	MBGFE_NODE_HASHES = 5,/* mbgfe_hash128[] canonical hashes, ascending == node id order after sortByHash   */
+	MBGFE_NODE_COVERAGE = 6, /* uint32_t[] HashList::coverage                                                */
+	MBGFE_NODE_TIP = 7,   /* uint8_t[]   HashList::isTipKmer                                                 */
+	MBGFE_EDGES = 8       /* mbgfe_edge[] sorted by (from, from_fw descending, to, to_fw)                     */
+};
+
+typedef struct {
+	uint64_t reads, raw_bases;           /* R */
+	uint64_t segments;                   /* maximal ACGT stretches of reads with >= 32 bases */
+	uint64_t collapsed_symbols;          /* C1: run-length / collapsed symbols */
+	uint64_t codes;                      /* C2: final codes of all parts */
+	uint64_t parts, hashed_parts;
+	uint64_t selected;                   /* S: selected k-mer instances ("total selected k-mers in reads") */
+	uint64_t distinct;                   /* D: table entries ("distinct selected k-mers in reads") */
+	uint64_t distinct_edges;
+	uint64_t table_slots, table_grows;
+	uint64_t nonacgt;                    /* characters outside ACGTacgt */
+	uint64_t h2d_bytes, d2h_bytes;       /* copied by the last upload / process / result download */
+	/* device time of the last run, milliseconds, CUDA events on the library's stream */
+	float ms_upload, ms_pack, ms_collapse, ms_msat, ms_select, ms_hash, ms_nodes, ms_edges, ms_process, ms_export;
+	uint32_t launches;                   /* kernels launched by the last mbgfe_process() */
+	uint32_t reserved;
+} mbgfe_stats;
+
+typedef struct mbgfe mbgfe;
+
+/* ReadpartIterator{k, w, errorMasking, ...} + HashList{k}  (MBG/ReadHelper.cpp:8-31, MBG/HashList.cpp:6-10) */
+int mbgfe_create(const mbgfe_params* params, mbgfe** out);
+void mbgfe_destroy(mbgfe* h);
+/* last error text of the handle (h == NULL: of the last failed mbgfe_create in this thread) */
+const char* mbgfe_last_error(const mbgfe* h);
+
+/* Pinned host memory for input buffers (so the H2D copies inside mbgfe_upload run at full PCIe rate). */
+void* mbgfe_alloc_pinned(uint64_t bytes);
+void mbgfe_free_pinned(void* p);
+
+/* Input.  Reads are ASCII (any case; everything outside ACGTacgt splits parts like the reference does):
+ * read r is bases[offsets[r] .. offsets[r+1]).  The buffers are NOT copied and must stay valid until the next
+ * mbgfe_upload()/mbgfe_run() returns.   Replaces iterateReadsMultithreaded + FastQ (MBG/ReadHelper.h:102-160). */
+int mbgfe_add_reads(mbgfe* h, const char* bases, const uint64_t* offsets, uint64_t n_reads);
+/* FASTA/FASTQ, optionally .gz, type chosen by suffix exactly like MBG/fastqloader.h:106-147 (unknown suffix == no
+ * reads); sequences are upper-cased, names kept for mbgfe_read_name().  Unreadable file -> MBGFE_E_IO. */
+int mbgfe_add_file(mbgfe* h, const char* path);
+const char* mbgfe_read_name(const mbgfe* h, uint64_t read_idx);
+
+/* Forget reads and results, keep parameters and device buffers. */
+int mbgfe_reset(mbgfe* h);
+
+/* mbgfe_upload: host -> HBM copy of the pending reads and 2-bit packing on the device (reads become resident).
+ * mbgfe_process: the whole front end on the resident reads: collapse / run-length -> microsatellite coding ->
+ *   rolling s-mer hash + closed-syncmer selection -> 128-bit k-mer hashes -> node table (coverage, tips) -> edge
+ *   table (coverage, overlaps).  May be called repeatedly; each call starts from an empty table.
+ *   == one pass of loadReadsAsHashesMultithread (MBG/MBG.cpp:44-76) over ReadpartIterator::iterateHashes.
+ * mbgfe_run = upload + process. */
+int mbgfe_upload(mbgfe* h);
+int mbgfe_process(mbgfe* h);
+int mbgfe_run(mbgfe* h);
+
+/* Results (downloaded and, for the tables, ordered on first request). */
+uint64_t mbgfe_count(mbgfe* h, int what);
+const void* mbgfe_data(mbgfe* h, int what);
+int mbgfe_get_stats(const mbgfe* h, mbgfe_stats* out);
+
+/* Device-side stopwatch on the library's stream (CUDA events): start, any number of calls, stop -> milliseconds. */
+int mbgfe_timer_start(mbgfe* h);
+int mbgfe_timer_stop(mbgfe* h, float* ms);
+
+/* Multi-GPU sharding by k-mer owner.  After mbgfe_process() with MBGFE_NO_TABLE on every rank:
+ *   mbgfe_exchange_counts  fills send_counts[world] = records this rank holds for each owner;
+ *   mbgfe_exchange_pack    writes the records, grouped by owner, into a device buffer and returns its address;
+ *   (the caller moves them with an NCCL all-to-all-v between device buffers)
+ *   mbgfe_exchange_insert  counts n_records received records (device pointer) into this rank's table partition.
+ * A record is 32 bytes: canonical hash lo, hi, flags (bit 0 tip), reserved. */
+int mbgfe_exchange_counts(mbgfe* h, uint64_t* send_counts);
+int mbgfe_exchange_pack(mbgfe* h, void** device_records);
+int mbgfe_exchange_reserve(mbgfe* h, uint64_t n_records, void** device_recv);
+int mbgfe_exchange_insert(mbgfe* h, const void* device_records, uint64_t n_records);
+
+/* Known-answer access to the device primitives (each runs a tiny kernel): per-code hash of the rolling hasher
+ * (MBG/FastHasher.cpp:33-43), code complement (MBG/ErrorMaskHelper.cpp:43-100), k-mer hash (MBG/MBGCommon.cpp:25-35). */
+int mbgfe_kat_tables(mbgfe* h, uint64_t* char_hash_30948, uint16_t* complement_30948);
+int mbgfe_kat_kmer_hash(mbgfe* h, const uint16_t* codes, uint32_t k, mbgfe_hash128* out);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

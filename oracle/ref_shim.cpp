@@ -12,6 +12,7 @@
 //   HashList::sortByHash / getEdgeCoverages / getSequenceOverlaps HashList.cpp:245-353,42-45,62-65
 //   FastHasher, getHash-derived tables, complement(), maxCode()   FastHasher.h, ErrorMaskHelper.cpp
 #include <cstdint>
+#include <chrono>
 #include <cstring>
 #include <sstream>
 #include <string>
@@ -175,6 +176,25 @@ const void* refshim_data(void* h, int what)
 		case 8: return r->edges.data();
 	}
 	return nullptr;
+}
+
+// The reference's own hot path, timed: ReadpartIterator over a FASTA/FASTQ file with `threads` worker threads feeding
+// loadReadsAsHashesMultithread (exactly what `MBG -t threads` runs in its "selecting k-mers and building graph
+// topology" phase before unitig construction, MBG/MBG.cpp:1570).  Returns seconds; fills selected / distinct counts.
+double refshim_time_file(int mode, uint64_t k, uint64_t w, const char* path, uint64_t threads, uint64_t* total_selected, uint64_t* distinct)
+{
+	std::vector<std::string> files { std::string(path) };
+	ReadpartIterator iterator { (size_t)k, (size_t)w, (ErrorMasking)mode, (size_t)threads, files, false, "" };
+	HashList list { (size_t)k };
+	std::ostringstream log;
+	auto t0 = std::chrono::steady_clock::now();
+	loadReadsAsHashesMultithread(list, k, iterator, threads, log);
+	auto t1 = std::chrono::steady_clock::now();
+	uint64_t total = 0;
+	for (size_t i = 0; i < list.size(); i++) total += list.coverage.get(i);
+	if (total_selected) *total_selected = total;
+	if (distinct) *distinct = list.size();
+	return std::chrono::duration<double>(t1 - t0).count();
 }
 
 // Known-answer helpers (SURVEY.md 8c "tables", "FastHasher", "hash(vector)", "msat" rows).

@@ -1,0 +1,196 @@
+// tests/emu/cuda_emu.h -- TEST INFRASTRUCTURE ONLY.
+//
+// A minimal emulation of the CUDA execution model, so that the kernels in verkko_b200/csrc/kernels.cuh and the
+// host orchestration in mbgfe.cu can be compiled with g++ and DEBUGGED in this GPU-less container (thread-block
+// barriers, warp shuffles, shared memory, atomics).  It exists only to find logic errors before spending GPU time;
+// it is built into tests/emu/libmbgfe_emu.so by tests/emu/Makefile, is never installed next to the product
+// library, and nothing in verkko_b200/ loads it.  The product library has no CPU path.
+//
+// Model: one CTA at a time; every CUDA thread of the CTA is an OS thread; __syncthreads() is a barrier; warp
+// collectives (__shfl_up_sync / __ballot_sync with the full mask) are implemented with CTA-wide barriers, so every
+// thread of the CTA must reach each collective -- which the kernels guarantee.  `__shared__` variables become
+// function-level statics (valid because CTAs run one after another).
+#pragma once
+#include <algorithm>
+#include <atomic>
+#include <condition_variable>
+#include <cstdint>
+#include <cstdlib>
+#include <cstring>
+#include <functional>
+#include <mutex>
+#include <thread>
+#include <vector>
+
+#define MBGFE_EMU 1
+#define __global__
+#define __device__
+#define __host__
+#define __forceinline__ inline
+#define __restrict__
+#define __launch_bounds__(...)
+#define __shared__ static
+#define __constant__ static const
+#define __align__(n) alignas(n)
+
+struct uint3 { unsigned x, y, z; };
+struct uint4 { unsigned x, y, z, w; };
+struct dim3 { unsigned x, y, z; dim3(unsigned a = 1, unsigned b = 1, unsigned c = 1) : x(a), y(b), z(c) {} };
+
+namespace emu {
+
+struct Barrier
+{
+	std::mutex m; std::condition_variable cv; unsigned n = 0, waiting = 0; unsigned long gen = 0;
+	void reset(unsigned count) { n = count; waiting = 0; }
+	void wait()
+	{
+		std::unique_lock<std::mutex> lk(m);
+		unsigned long g = gen;
+		if (++waiting == n) { waiting = 0; gen++; cv.notify_all(); return; }
+		cv.wait(lk, [&] { return gen != g; });
+	}
+};
+
+inline Barrier& barrier() { static Barrier b; return b; }
+inline uint64_t* xchg() { static uint64_t buf[2048]; return buf; }
+inline unsigned char*& dyn_smem() { static unsigned char* p = nullptr; return p; }
+inline std::mutex& big_lock() { static std::mutex m; return m; }
+
+}
+
+extern thread_local uint3 threadIdx;
+extern thread_local uint3 blockIdx;
+extern thread_local dim3 blockDim;
+extern thread_local dim3 gridDim;
+
+inline void __syncthreads() { emu::barrier().wait(); }
+
+template <typename T>
+inline T __shfl_up_sync(unsigned, T v, unsigned d)
+{
+	static_assert(sizeof(T) <= 8, "shuffle of <= 8 bytes");
+	uint64_t raw = 0; memcpy(&raw, &v, sizeof(T));
+	emu::xchg()[threadIdx.x] = raw;
+	emu::barrier().wait();
+	unsigned lane = threadIdx.x & 31;
+	uint64_t got = lane >= d ? emu::xchg()[threadIdx.x - d] : raw;
+	emu::barrier().wait();
+	T out; memcpy(&out, &got, sizeof(T));
+	return out;
+}
+
+template <typename T>
+inline T __shfl_sync(unsigned, T v, unsigned src)
+{
+	static_assert(sizeof(T) <= 8, "shuffle of <= 8 bytes");
+	uint64_t raw = 0; memcpy(&raw, &v, sizeof(T));
+	emu::xchg()[threadIdx.x] = raw;
+	emu::barrier().wait();
+	uint64_t got = emu::xchg()[(threadIdx.x & ~31u) + (src & 31)];
+	emu::barrier().wait();
+	T out; memcpy(&out, &got, sizeof(T));
+	return out;
+}
+
+inline unsigned long long __umul64hi(unsigned long long a, unsigned long long b) { return (unsigned long long)(((unsigned __int128)a * b) >> 64); }
+
+inline unsigned __ballot_sync(unsigned, int pred)
+{
+	emu::xchg()[threadIdx.x] = pred ? 1 : 0;
+	emu::barrier().wait();
+	unsigned base = threadIdx.x & ~31u, r = 0;
+	for (unsigned i = 0; i < 32 && base + i < blockDim.x; i++) if (emu::xchg()[base + i]) r |= 1u << i;
+	emu::barrier().wait();
+	return r;
+}
+
+inline int __ffs(unsigned v) { return __builtin_ffs((int)v); }
+inline int __ffsll(long long v) { return __builtin_ffsll(v); }
+inline int __popc(unsigned v) { return __builtin_popcount(v); }
+inline int __popcll(unsigned long long v) { return __builtin_popcountll(v); }
+template <typename T> inline T __ldg(const T* p) { return *p; }
+template <typename T> inline T __ldcs(const T* p) { return *p; }
+inline unsigned __vcmpeq4(unsigned a, unsigned b)
+{
+	unsigned r = 0;
+	for (int i = 0; i < 4; i++) if (((a >> (8 * i)) & 0xff) == ((b >> (8 * i)) & 0xff)) r |= 0xffu << (8 * i);
+	return r;
+}
+using std::max;
+using std::min;
+
+template <typename T> inline T atomicAdd(T* p, T v) { return __atomic_fetch_add(p, v, __ATOMIC_RELAXED); }
+template <typename T> inline T atomicOr(T* p, T v) { return __atomic_fetch_or(p, v, __ATOMIC_RELAXED); }
+template <typename T> inline T atomicMax(T* p, T v)
+{
+	T old = __atomic_load_n(p, __ATOMIC_RELAXED);
+	while (old < v && !__atomic_compare_exchange_n(p, &old, v, false, __ATOMIC_RELAXED, __ATOMIC_RELAXED)) {}
+	return old;
+}
+template <typename T> inline T atomicCAS(T* p, T expected, T desired)
+{
+	__atomic_compare_exchange_n(p, &expected, desired, false, __ATOMIC_RELAXED, __ATOMIC_RELAXED);
+	return expected;
+}
+
+// ------------------------------------------------------------------------------------------- runtime API
+typedef int cudaError_t;
+typedef void* cudaStream_t;
+typedef struct emuEvent { double t; }* cudaEvent_t;
+enum { cudaSuccess = 0 };
+enum cudaMemcpyKind { cudaMemcpyHostToDevice, cudaMemcpyDeviceToHost, cudaMemcpyDeviceToDevice };
+struct cudaDeviceProp { char name[64]; int major, minor, multiProcessorCount; size_t sharedMemPerBlockOptin; };
+inline const char* cudaGetErrorString(cudaError_t) { return "emulator"; }
+inline cudaError_t cudaGetLastError() { return 0; }
+inline cudaError_t cudaGetDeviceCount(int* n) { *n = 1; return 0; }
+inline cudaError_t cudaSetDevice(int) { return 0; }
+inline cudaError_t cudaGetDeviceProperties(cudaDeviceProp* p, int) { memset(p, 0, sizeof(*p)); strcpy(p->name, "emulated"); p->major = 10; p->minor = 0; p->multiProcessorCount = 4; p->sharedMemPerBlockOptin = 227 * 1024; return 0; }
+inline cudaError_t cudaStreamCreate(cudaStream_t* s) { *s = nullptr; return 0; }
+inline cudaError_t cudaStreamDestroy(cudaStream_t) { return 0; }
+inline cudaError_t cudaStreamSynchronize(cudaStream_t) { return 0; }
+inline cudaError_t cudaDeviceSynchronize() { return 0; }
+inline cudaError_t cudaMalloc(void** p, size_t n) { *p = calloc(1, n ? n : 1); return *p ? 0 : 2; }
+inline cudaError_t cudaFree(void* p) { free(p); return 0; }
+inline cudaError_t cudaMallocHost(void** p, size_t n) { *p = malloc(n ? n : 1); return *p ? 0 : 2; }
+inline cudaError_t cudaFreeHost(void* p) { free(p); return 0; }
+inline cudaError_t cudaMemcpyAsync(void* d, const void* s, size_t n, cudaMemcpyKind, cudaStream_t) { memcpy(d, s, n); return 0; }
+inline cudaError_t cudaMemcpy(void* d, const void* s, size_t n, cudaMemcpyKind) { memcpy(d, s, n); return 0; }
+inline cudaError_t cudaMemsetAsync(void* d, int v, size_t n, cudaStream_t) { memset(d, v, n); return 0; }
+inline cudaError_t cudaEventCreate(cudaEvent_t* e) { *e = new emuEvent{0}; return 0; }
+inline cudaError_t cudaEventDestroy(cudaEvent_t e) { delete e; return 0; }
+inline cudaError_t cudaEventRecord(cudaEvent_t, cudaStream_t) { return 0; }
+inline cudaError_t cudaEventSynchronize(cudaEvent_t) { return 0; }
+inline cudaError_t cudaEventElapsedTime(float* ms, cudaEvent_t, cudaEvent_t) { *ms = 0; return 0; }
+enum cudaFuncAttribute { cudaFuncAttributeMaxDynamicSharedMemorySize };
+template <typename F> inline cudaError_t cudaFuncSetAttribute(F, cudaFuncAttribute, int) { return 0; }
+
+namespace emu {
+
+template <typename K, typename... Args>
+void launch(K kernel, dim3 grid, dim3 block, size_t smem_bytes, Args... args)
+{
+	std::vector<unsigned char> smem(smem_bytes + 64);
+	dyn_smem() = smem.data();
+	barrier().reset(block.x);
+	std::vector<std::thread> pool;
+	for (unsigned t = 0; t < block.x; t++)
+	{
+		pool.emplace_back([=]()
+		{
+			blockDim = block; gridDim = grid; threadIdx = { t, 0, 0 };
+			for (unsigned b = 0; b < grid.x; b++)
+			{
+				blockIdx = { b, 0, 0 };
+				kernel(args...);
+				barrier().wait(); // CTAs run one after another: statics standing in for __shared__ are reused
+			}
+		});
+	}
+	for (auto& th : pool) th.join();
+}
+
+}
+
+#define MBGFE_LAUNCH(kernel, grid, block, smem, stream, ...) emu::launch(kernel, dim3(grid), dim3(block), (size_t)(smem), __VA_ARGS__)
+#define MBGFE_DYN_SMEM(name) unsigned char* name = emu::dyn_smem()

@@ -1,0 +1,20 @@
+"""run the C-ABI front end (real CUDA library, or the GPU-less emulator build) and collect its arrays"""
+from oracle_lib import RunResult
+from verkko_b200.frontend import KEEP_CODES, KEEP_POSES, MbgFrontEnd
+
+
+def run_frontend(mode, k, w, reads, library=None, flags=KEEP_CODES | KEEP_POSES, table=True, **kw):
+    fe = MbgFrontEnd(k, w, mode, flags=flags, library=library, **kw)
+    try:
+        if isinstance(reads, tuple):
+            fe.add_reads(*reads)
+        else:
+            fe.add_read_list(reads)
+        fe.run()
+        res = RunResult(parts=fe.parts(), codes=fe.codes(), poses=fe.poses(), positions=fe.positions(), hashes=fe.hashes())
+        if table:
+            res.update(node_hash=fe.node_hashes(), node_cov=fe.node_coverage(), node_tip=fe.node_tip(), edges=fe.edges())
+        res["stats"] = fe.stats()
+        return res
+    finally:
+        fe.close()

@@ -1,0 +1,19 @@
+"""Kernel logic checked WITHOUT a GPU: the CUDA sources compiled against tests/emu/cuda_emu.h (an execution-model
+emulator used for debugging; see that header) and driven through the same C ABI, compared with the oracle.
+These are not the parity tests proper -- those are tests/test_gpu_parity.py on a real B200."""
+import pytest
+
+import workloads
+from fe_helpers import run_frontend
+from oracle_lib import compare_runs
+
+
+@pytest.mark.parametrize("mode,k,w", [("collapse-msat", 1001, 100), ("hpc", 501, 50), ("no", 63, 33), ("msat", 255, 7), ("collapse-dinuc", 301, 30)])
+def test_emulated_kernels_match_oracle(oracle, emu_library, mode, k, w):
+    reads = [workloads.read_a()[:9000]] + workloads.edge_case_reads()
+    compare_runs(run_frontend(mode, k, w, reads, library=emu_library), oracle.run(mode, k, w, reads), what=f"{mode} k={k} w={w}")
+
+
+def test_emulated_kernels_table_with_coverage(oracle, emu_library):
+    reads = workloads.coverage_reads(n_reads=6)
+    compare_runs(run_frontend("collapse-msat", 501, 50, reads, library=emu_library), oracle.run("collapse-msat", 501, 50, reads), what="coverage")

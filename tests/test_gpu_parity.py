@@ -1,0 +1,131 @@
+"""Parity tests proper: the CUDA path, called through the C ABI, against the oracle and the committed golden
+fixtures, plus size-independent properties at larger sizes.  Bit-exact: everything on this path is integer work."""
+import glob
+import os
+
+import numpy as np
+import pytest
+
+import workloads
+from fe_helpers import run_frontend
+from oracle_lib import MODES, RunResult, compare_runs
+
+pytestmark = pytest.mark.gpu
+GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+
+
+def test_device_tables_known_answers(oracle):
+    from verkko_b200 import MbgFrontEnd
+    fe = MbgFrontEnd(1001, 100)
+    h, c = fe.kat_tables()
+    assert [int(x) for x in h[:4]] == [0x77cfa1eef01bca90, 0x5bca7c69b794f8ce, 0xb795033f6f2a0674, 0x135fddf6a6bfbbdd]
+    assert all(int(c[i]) == oracle.complement(i) for i in range(30948))
+    assert all(int(h[i]) == oracle.char_hash(i) for i in range(0, 30948, 13))
+    codes = np.array([(i * 7) % 4 for i in range(31)], dtype=np.uint16)
+    assert fe.kat_kmer_hash(codes) == (0xc8ec520a381594d1, 0x6515f3d84acb3010)
+    rng = np.random.default_rng(3)
+    for k in (31, 33, 35, 37, 1001, 2001):
+        codes = rng.integers(0, 30948, k).astype(np.uint16)
+        assert fe.kat_kmer_hash(codes) == oracle.kmer_hash(codes), k
+    fe.close()
+
+
+@pytest.mark.parametrize("path", sorted(glob.glob(os.path.join(GOLDEN, "*.npz"))))
+def test_golden_fixtures(path):
+    z = np.load(path)
+    mode, k, w = str(z["mode"]), int(z["k"]), int(z["w"])
+    got = run_frontend(mode, k, w, (z["bases"], z["offsets"]))
+    want = RunResult({f: z[f] for f in ("parts", "codes", "poses", "positions", "hashes", "node_hash", "node_cov", "node_tip", "edges")})
+    compare_runs(got, want, what=os.path.basename(path))
+
+
+@pytest.mark.parametrize("mode", list(MODES))
+def test_all_modes_against_oracle(oracle, mode):
+    reads = [workloads.read_a()] + workloads.edge_case_reads() + [workloads.repeat_rich(9, 30000)]
+    for k, w in ((1001, 100), (63, 33)):
+        compare_runs(run_frontend(mode, k, w, reads), oracle.run(mode, k, w, reads), what=f"{mode} k={k} w={w}")
+
+
+@pytest.mark.parametrize("k,w", [(31, 1), (501, 50), (1001, 17), (2001, 200), (3001, 100), (5001, 50), (255, 225)])
+def test_k_w_sweep_against_oracle(oracle, k, w):
+    reads = workloads.coverage_reads(seed=5, genome_len=60000, n_reads=10, len_min=15000, len_max=20000)
+    compare_runs(run_frontend("collapse-msat", k, w, reads), oracle.run("collapse-msat", k, w, reads), what=f"k={k} w={w}")
+
+
+def test_repeat_rich_reads(oracle):
+    reads = [workloads.repeat_rich(s, n) for s, n in ((1, 50000), (2, 20000), (3, 4097), (4, 4096), (5, 8191), (6, 131)) ]
+    for mode in ("collapse-msat", "msat", "dinuc"):
+        compare_runs(run_frontend(mode, 101, 10, reads), oracle.run(mode, 101, 10, reads), what=mode)
+
+
+def test_long_and_ragged_reads(oracle):
+    from verkko_b200 import synth
+    g = synth.genome(21, 400000)
+    reads = synth.reads(3, g, 40, 30, 120000, 5000)   # 30 bases .. 120 kb, 0.5 % errors (HERRO/duplex-shaped)
+    compare_runs(run_frontend("collapse-msat", 1001, 100, reads), oracle.run("collapse-msat", 1001, 100, reads), what="ragged")
+
+
+def test_ecoli_shaped_coverage(oracle):
+    """config #1 shape at reduced genome size: 24x coverage, 15 kb reads, full table parity"""
+    from verkko_b200 import synth
+    g = synth.genome(7, 400000)
+    reads = synth.reads(11, g, 640, 11000, 19000, 1000)
+    got = run_frontend("collapse-msat", 1001, 100, reads)
+    want = oracle.run("collapse-msat", 1001, 100, reads)
+    compare_runs(got, want, what="ecoli-shaped")
+    assert got["stats"]["selected"] == int(want.node_cov.sum())
+
+
+def test_empty_and_tiny_inputs():
+    r = run_frontend("collapse-msat", 1001, 100, [])
+    assert len(r.parts) == 0 and len(r.node_cov) == 0
+    r = run_frontend("collapse-msat", 1001, 100, [b"ACGT" * 5, b"", b"N" * 100])
+    assert len(r.parts) == 0 and len(r.positions) == 0
+
+
+def test_properties_at_bench_scale():
+    """size-independent properties on a chr20-shaped shard too large for the oracle: repeatability, coverage sums,
+    tips, ordering"""
+    from verkko_b200 import MbgFrontEnd, synth
+    g = synth.genome(7, 8_000_000)
+    bases, offsets = synth.reads(11, g, 13000, 15000, 20000, 1000)     # ~0.23 Gbp, 30x
+    fe = MbgFrontEnd(1001, 100, "collapse-msat")
+    fe.add_reads(bases, offsets)
+    fe.run()
+    st = fe.stats()
+    cov, tip, nh, edges = fe.node_coverage(), fe.node_tip(), fe.node_hashes(), fe.edges()
+    parts = fe.parts()
+    assert int(cov.sum()) == st["selected"] == int(parts["n_sel"].sum())
+    assert len(cov) == st["distinct"]
+    order = np.lexsort((nh[:, 0], nh[:, 1]))
+    assert np.array_equal(order, np.arange(len(nh))), "node table must be sorted by canonical hash"
+    assert int(edges[:, 4].sum()) == st["selected"] - int((parts["n_sel"] > 0).sum())
+    assert (edges[:, 5] >= 1).all() and (edges[:, 5] < 1001).all()
+    assert tip.sum() <= 2 * (parts["n_sel"] > 0).sum()
+    fe.process()                                                        # a second pass over the resident reads
+    assert np.array_equal(cov, fe.node_coverage()) and np.array_equal(nh, fe.node_hashes()) and np.array_equal(edges, fe.edges())
+    fe.close()
+
+
+def test_file_input(tmp_path, oracle):
+    import gzip
+    reads = [workloads.read_a(), workloads.read_with_other_characters().lower(), workloads.read_a()[3000:9000]]
+    fa = tmp_path / "reads.fa"
+    with open(fa, "wb") as f:
+        for i, r in enumerate(reads):
+            f.write(b">read%d some description\r\n" % i)
+            for j in range(0, len(r), 70):
+                f.write(r[j:j + 70] + b"\n")
+    fq = tmp_path / "reads.fastq.gz"
+    with gzip.open(fq, "wb") as f:
+        for i, r in enumerate(reads):
+            f.write(b"@q%d\n" % i + r + b"\n+\n" + b"I" * len(r) + b"\n")
+    from verkko_b200 import MbgFrontEnd
+    want = oracle.run("collapse-msat", 1001, 100, [r.upper() for r in reads] * 2)
+    fe = MbgFrontEnd(1001, 100, "collapse-msat")
+    fe.add_file(str(fa))
+    fe.add_file(str(fq))
+    fe.run()
+    assert fe.read_name(0) == "read0 some description" and fe.read_name(3) == "q0"
+    assert np.array_equal(fe.hashes(), want.hashes) and np.array_equal(fe.node_coverage(), want.node_cov)
+    fe.close()

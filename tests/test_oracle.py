@@ -1,0 +1,112 @@
+"""CPU tests of the checker itself: known answers, the reference compiled here, committed golden fixtures."""
+import glob
+import os
+
+import numpy as np
+import pytest
+
+import workloads
+from oracle_lib import MODES, RunResult, compare_runs, lcg_bases
+
+GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+
+
+def test_tables_known_answers(oracle):
+    # SURVEY.md 8(c) "tables" row, minted from the reference
+    assert oracle.lib.orc_max_code() == 30948
+    assert [oracle.char_hash(c) for c in range(4)] == [0x77cfa1eef01bca90, 0x5bca7c69b794f8ce, 0xb795033f6f2a0674, 0x135fddf6a6bfbbdd]
+    for a, b in ((0, 3), (1, 2), (4, 34), (5, 35), (6, 26), (36, 225), (228, 1248), (1252, 6367), (6372, 30942), (30947, 6377)):
+        assert oracle.complement(a) == b
+    for c in range(0, 30948, 7):
+        assert oracle.complement(oracle.complement(c)) == c
+    assert [oracle.lib.orc_code_motif_length(c) for c in (4, 36, 228, 1252, 6372)] == [2, 3, 4, 5, 6]
+
+
+def test_hash_known_answers(oracle):
+    b = lcg_bases(7, 902)
+    codes = np.array([b"ACGT".index(x) for x in b], dtype=np.uint16)
+    assert oracle.rolling_hash(902, codes) == (0x7868dd6946eb7eeb, 0xac082fb93b68b8f2)
+    codes = np.array([(i * 7) % 4 for i in range(31)], dtype=np.uint16)
+    assert oracle.kmer_hash(codes) == (0xc8ec520a381594d1, 0x6515f3d84acb3010)
+
+
+def test_msat_known_answer(oracle):
+    s = "ACGTACGATCAGCTAGCTAGCATCGATCGACTACACACACACACACACAGTCAGTCATGATGATGATGATGATCAGCTAGCATCGAGCATCGATCGACTAGC"
+    sym = np.array(["ACGT".index(ch) for ch in s], dtype=np.uint16)
+    want = [0, 1, 2, 3, 0, 1, 2, 0, 3, 1, 387, 445, 1, 3, 7, 1, 0, 951, 0, 205, 1, 0, 2, 1, 3, 0, 2, 1, 0, 3, 1, 2, 0, 2, 1, 445, 1, 3, 0, 2, 1]
+    codes, poses = oracle.msat(sym)
+    assert codes.tolist() == want
+    assert poses.tolist()[:21] == [0, 1, 2, 3, 4, 5, 6, 7, 8, 9, 10, 21, 30, 31, 32, 47, 48, 49, 56, 57, 73]
+    assert poses.tolist()[-6:] == [97, 98, 99, 100, 101, 102]
+    c2, p2 = oracle.msat_scanform(sym)
+    assert c2.tolist() == want and p2.tolist() == poses.tolist()
+
+
+KAT = {  # (codes, selected, first positions, last position, h[0] hi:lo, xor hi:lo)
+    ("collapse-msat", 1001, 100): (9861, 180, [3, 69, 137], 8784, (0x37b28bbafe4ca20e, 0xb05b9c088ddff306), (0x62db18cc977053eb, 0x646835421a56e8fb)),
+    ("hpc", 1001, 100): (14906, 283, [16, 115, 129], 13899, (0xa44ec27ba0fa75e8, 0xeb8e6c3091dc1055), (0xcb6fa6b01ee5b63c, 0x7e4a10eae7660319)),
+    ("no", 1001, 100): (20000, 381, [67, 71, 170], 18934, (0x7675d69525c130df, 0xc8805d6414fdc0cc), (0x19cfb4d85d721e61, 0x09086f49deabb55d)),
+    ("collapse-msat", 501, 50): (9861, 363, [22, 27, 76], 9335, (0x0dd66565f7f7a450, 0x78de3737236c25db), (0xe4266bf336b7323d, 0x9308f9cdd482ffe1)),
+}
+
+
+@pytest.mark.parametrize("key", list(KAT))
+def test_read_known_answers(oracle, key):
+    mode, k, w = key
+    n_codes, n_sel, first, last, h0, hx = KAT[key]
+    r = oracle.run(mode, k, w, [workloads.read_a()])
+    assert len(r.codes) == n_codes and len(r.positions) == n_sel
+    assert r.positions[:3].tolist() == first and int(r.positions[-1]) == last
+    assert (int(r.hashes[0, 1]), int(r.hashes[0, 0])) == h0
+    x = np.bitwise_xor.reduce(r.hashes, axis=0)
+    assert (int(x[1]), int(x[0])) == hx
+
+
+def test_split_at_n_known_answer(oracle):
+    rb = bytearray(workloads.read_a())
+    rb[5000:5002] = b"NN"
+    r = oracle.run("collapse-msat", 1001, 100, [bytes(rb)])
+    assert r.parts["part_offset"].tolist() == [0, 3761]
+    assert r.parts["n_codes"].tolist() == [2512, 7349]
+    assert r.parts["n_sel"].tolist() == [36, 122]
+    assert int(r.poses[2512]) == 3760 and int(r.poses[-1]) == 14907
+
+
+@pytest.mark.parametrize("mode", list(MODES))
+def test_oracle_equals_reference(oracle, reference, mode):
+    for k, w, reads in ((1001, 100, [workloads.read_a()] + workloads.edge_case_reads()), (301, 30, workloads.coverage_reads()),
+                        (63, 33, [workloads.repeat_rich(3, 5000), workloads.repeat_rich(4, 700)])):
+        compare_runs(oracle.run(mode, k, w, reads), reference.run(mode, k, w, reads), what=f"{mode} k={k} w={w}")
+
+
+def test_msat_scanform_equals_reference_algorithm(oracle):
+    """the scan-parallel formulation the CUDA kernel uses == the sequential reference algorithm (on run-length input)"""
+    rng = np.random.default_rng(5)
+    for it in range(400):
+        s = np.frombuffer(workloads.repeat_rich(100 + it, int(rng.integers(40, 600))), dtype=np.uint8)
+        sym = np.searchsorted(np.frombuffer(b"ACGT", dtype=np.uint8), s).astype(np.uint16)
+        keep = np.ones(len(sym), bool)
+        keep[1:] = sym[1:] != sym[:-1]
+        sym = sym[keep]
+        if len(sym) < 32:
+            continue
+        for mm in (2, 6):
+            a, b = oracle.msat(sym, max_motif=mm), oracle.msat_scanform(sym, max_motif=mm)
+            assert np.array_equal(a[0], b[0]) and np.array_equal(a[1], b[1]), (it, mm)
+
+
+def test_syncmer_rule_bruteforce(oracle):
+    r = oracle.run("collapse-msat", 201, 20, [workloads.read_a()[:6000]], table=False)
+    p = r.parts[0]
+    codes = r.codes[int(p["code_begin"]):int(p["code_begin"]) + int(p["n_codes"])]
+    assert np.array_equal(oracle.syncmers_bruteforce(codes, 201, 20), r.positions)
+
+
+@pytest.mark.parametrize("path", sorted(glob.glob(os.path.join(GOLDEN, "*.npz"))))
+def test_golden_fixtures(oracle, path):
+    """fixtures written by tools/make_golden.py from the reference compiled in the build container"""
+    z = np.load(path)
+    mode, k, w = str(z["mode"]), int(z["k"]), int(z["w"])
+    got = oracle.run(mode, k, w, (z["bases"], z["offsets"]))
+    want = RunResult({f: z[f] for f in ("parts", "codes", "poses", "positions", "hashes", "node_hash", "node_cov", "node_tip", "edges")})
+    compare_runs(got, want, what=os.path.basename(path))

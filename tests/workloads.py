@@ -1,0 +1,54 @@
+"""Seeded inputs shared by the CPU and GPU tests."""
+import numpy as np
+
+from oracle_lib import lcg_bases, pack_reads
+
+
+def read_a():
+    """SURVEY.md 8(c) KAT read: LCG(1), 20 000 bases."""
+    return lcg_bases(1, 20000)
+
+
+def read_with_other_characters():
+    rb = bytearray(read_a())
+    rb[5000:5002] = b"NN"
+    rb[9000:9003] = b"NRN"
+    rb[0:1] = b"N"
+    rb[-1:] = b"n"
+    rb[12000:12040] = b"N" * 40
+    rb[15000:15010] = b"ACGTNACGTN"
+    return bytes(rb)
+
+
+def edge_case_reads():
+    a = read_a()
+    return [read_with_other_characters(), a[:31], a[:32], b"ACGT" * 10, b"N" * 50, b"", a[100:163], b"acgtacgtac" * 8 + a[:3000].lower()]
+
+
+def repeat_rich(seed, n):
+    """microsatellite / homopolymer rich sequence"""
+    rng = np.random.default_rng(seed)
+    out = []
+    total = 0
+    while total < n:
+        t = rng.integers(0, 3)
+        if t == 0:
+            piece = rng.integers(0, 4, rng.integers(1, 40))
+        else:
+            m = int(rng.integers(1, 8))
+            motif = rng.integers(0, 4, m)
+            c = int(rng.integers(2, 30))
+            piece = np.tile(motif, c)[: m * c - int(rng.integers(0, m))]
+        out.append(piece)
+        total += len(piece)
+    return bytes(np.frombuffer(b"ACGT", dtype=np.uint8)[np.concatenate(out)[:n]])
+
+
+def coverage_reads(seed=11, genome_len=30000, n_reads=12, len_min=8000, len_max=12000, error_ppm=1000):
+    from verkko_b200 import synth
+    g = synth.genome(7, genome_len)
+    return synth.reads(seed, g, n_reads, len_min, len_max, error_ppm)
+
+
+def as_pair(reads):
+    return reads if isinstance(reads, tuple) else pack_reads(reads)

@@ -1,0 +1,1200 @@
+// kernels.cuh -- sm_100a device code of libmbgfe (hand-written CUDA; no library kernels).
+//
+// Data layout in HBM (all indices are in bases / symbols / codes, never bytes, unless stated):
+//   packed   2-bit bases of the whole batch, base i at bits [2*(i%32), +2) of 64-bit word i/32 (A0 C1 G2 T3);
+//            reads are NOT padded: read r occupies [offsets[r], offsets[r+1]) exactly as in the ASCII buffer.
+//   segment  maximal ACGT stretch of a read (the whole read when it has no other characters).  Segment g owns the
+//            output range [out_base[g], out_base[g] + len[g] + 1) in every per-symbol array; out_base is a multiple
+//            of 64, so each segment starts on a 128-bit boundary in the 2-bit symbol array and on a 128-byte boundary
+//            in the 16-bit code array.
+//   sym      2-bit run-length / collapsed symbols (output of K1), same packing as `packed`, indexed by out_base.
+//   codes    uint16 final codes (output of K2), indexed by out_base.
+//   selmask  1 bit per code position: k-mer starting there is selected (output of K3a), indexed by out_base.
+//   inst_*   one entry per selected k-mer instance, in (segment, position) order (output of K3b).
+//
+// Reference citations: MBG/ = /root/reference/src/hifioverlapper/MBG/src (commit 7bef84dd).
+#pragma once
+#include <cstdint>
+#ifdef MBGFE_EMU_BUILD
+#include "cuda_emu.h"   // tests/emu: GPU-less debugging build, never shipped (see that header)
+#else
+#include <cuda_runtime.h>
+#define MBGFE_LAUNCH(kernel, grid, block, smem, stream, ...) kernel<<<(grid), (block), (smem), (stream)>>>(__VA_ARGS__)
+#define MBGFE_DYN_SMEM(name) extern __shared__ __align__(16) unsigned char name[]
+#endif
+
+namespace mbgfe_dev {
+
+constexpr uint32_t FULL = 0xffffffffu;
+
+__host__ __device__ __forceinline__ uint64_t rotl64(uint64_t v, uint32_t r) { r &= 63; return (v << r) | (v >> ((64 - r) & 63)); }
+__host__ __device__ __forceinline__ uint64_t rotr64(uint64_t v, uint32_t r) { r &= 63; return (v >> r) | (v << ((64 - r) & 63)); }
+
+// 64 bits of a 2-bit packed array starting at symbol index `sym` (the array is padded by two words)
+__device__ __forceinline__ uint64_t window64(const uint64_t* __restrict__ p, uint64_t sym)
+{
+	uint64_t q = sym >> 5;
+	uint32_t sh = (uint32_t)(sym & 31) * 2;
+	uint64_t lo = __ldg(p + q);
+	if (sh == 0) return lo;
+	uint64_t hi = __ldg(p + q + 1);
+	return (lo >> sh) | (hi << (64 - sh));
+}
+
+__device__ __forceinline__ uint32_t symbol_at(const uint64_t* __restrict__ p, uint64_t sym)
+{
+	return (uint32_t)(__ldg(p + (sym >> 5)) >> ((sym & 31) * 2)) & 3;
+}
+
+// mask with the low 2*n bits set (n in 0..32)
+__device__ __forceinline__ uint64_t low_pairs(uint32_t n) { return n >= 32 ? ~0ull : ((1ull << (2 * n)) - 1); }
+
+// ---------------------------------------------------------------------------------------------- block scans
+
+template <int NT>
+__device__ __forceinline__ uint32_t block_exclusive_sum(uint32_t v, uint32_t* warp_tmp, uint32_t& total)
+{
+	const uint32_t lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+	uint32_t inc = v;
+#pragma unroll
+	for (int d = 1; d < 32; d <<= 1) { uint32_t t = __shfl_up_sync(FULL, inc, d); if (lane >= d) inc += t; }
+	if (lane == 31) warp_tmp[wid] = inc;
+	__syncthreads();
+	uint32_t base = 0, tot = 0;
+#pragma unroll
+	for (int i = 0; i < NT / 32; i++) { uint32_t t = warp_tmp[i]; if (i < (int)wid) base += t; tot += t; }
+	__syncthreads();
+	total = tot;
+	return base + inc - v;
+}
+
+template <int NT>
+__device__ __forceinline__ uint32_t block_exclusive_max(uint32_t v, uint32_t* warp_tmp, uint32_t& total)
+{
+	const uint32_t lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+	uint32_t inc = v;
+#pragma unroll
+	for (int d = 1; d < 32; d <<= 1) { uint32_t t = __shfl_up_sync(FULL, inc, d); if (lane >= d) inc = max(inc, t); }
+	uint32_t prev = __shfl_up_sync(FULL, inc, 1);
+	if (lane == 0) prev = 0;
+	if (lane == 31) warp_tmp[wid] = inc;
+	__syncthreads();
+	uint32_t base = 0, tot = 0;
+#pragma unroll
+	for (int i = 0; i < NT / 32; i++) { uint32_t t = warp_tmp[i]; if (i < (int)wid) base = max(base, t); tot = max(tot, t); }
+	__syncthreads();
+	total = tot;
+	return max(base, prev);
+}
+
+// exclusive "last valid value" scan: result = the value of the closest preceding thread with valid != 0
+struct LastRun { uint32_t start, prev_end, m; }; // m == 0 -> empty
+template <int NT>
+__device__ __forceinline__ LastRun block_exclusive_last(LastRun v, LastRun* warp_tmp, LastRun& total)
+{
+	const uint32_t lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+	LastRun inc = v;
+#pragma unroll
+	for (int d = 1; d < 32; d <<= 1)
+	{
+		LastRun t;
+		t.start = __shfl_up_sync(FULL, inc.start, d);
+		t.prev_end = __shfl_up_sync(FULL, inc.prev_end, d);
+		t.m = __shfl_up_sync(FULL, inc.m, d);
+		if (lane >= d && inc.m == 0) inc = t;
+	}
+	LastRun prev;
+	prev.start = __shfl_up_sync(FULL, inc.start, 1);
+	prev.prev_end = __shfl_up_sync(FULL, inc.prev_end, 1);
+	prev.m = __shfl_up_sync(FULL, inc.m, 1);
+	if (lane == 0) prev.m = 0;
+	if (lane == 31) warp_tmp[wid] = inc;
+	__syncthreads();
+	LastRun base; base.m = 0; base.start = 0; base.prev_end = 0;
+	LastRun tot = base;
+#pragma unroll
+	for (int i = 0; i < NT / 32; i++) { LastRun t = warp_tmp[i]; if (t.m) { if (i < (int)wid) base = t; tot = t; } }
+	__syncthreads();
+	total = tot;
+	return prev.m ? prev : base;
+}
+
+struct Xor2 { uint64_t a, b; };
+template <int NT>
+__device__ __forceinline__ Xor2 block_exclusive_xor(Xor2 v, Xor2* warp_tmp, Xor2& total)
+{
+	const uint32_t lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+	Xor2 inc = v;
+#pragma unroll
+	for (int d = 1; d < 32; d <<= 1)
+	{
+		uint64_t ta = __shfl_up_sync(FULL, inc.a, d), tb = __shfl_up_sync(FULL, inc.b, d);
+		if (lane >= d) { inc.a ^= ta; inc.b ^= tb; }
+	}
+	if (lane == 31) warp_tmp[wid] = inc;
+	__syncthreads();
+	Xor2 base = { 0, 0 }, tot = { 0, 0 };
+#pragma unroll
+	for (int i = 0; i < NT / 32; i++) { Xor2 t = warp_tmp[i]; if (i < (int)wid) { base.a ^= t.a; base.b ^= t.b; } tot.a ^= t.a; tot.b ^= t.b; }
+	__syncthreads();
+	total = tot;
+	Xor2 r = { base.a ^ inc.a ^ v.a, base.b ^ inc.b ^ v.b };
+	return r;
+}
+
+// ------------------------------------------------------------------------------------------------ tables
+
+// Alphabet of MBG's microsatellite coding (MBG/ErrorMaskHelper.cpp:9-25): codes below CODES_BEFORE[m+1] have motif
+// length <= m.
+__constant__ uint32_t CODES_BEFORE[8] = { 0, 0, 4, 36, 228, 1252, 6372, 30948 };
+constexpr uint32_t MAX_CODE = 30948;
+
+// per-code mix of the rolling hasher (MBG/FastHasher.cpp:33-43)
+__host__ __device__ __forceinline__ uint64_t char_hash(uint64_t key)
+{
+	key = (~key) + (key << 21);
+	key ^= key >> 24;
+	key *= 265;
+	key ^= key >> 14;
+	key *= 21;
+	key ^= key >> 28;
+	key += key << 31;
+	return key;
+}
+
+// reverse complement of one code (MBG/ErrorMaskHelper.cpp:43-73): rotate the motif left by `overhang` symbols,
+// complement every symbol, reverse the symbol order; motif length and overhang are kept
+__device__ __forceinline__ uint32_t complement_code(uint32_t code)
+{
+	uint32_t m = 1;
+	while (m < 6 && CODES_BEFORE[m + 1] <= code) m++;
+	uint32_t v = code - CODES_BEFORE[m];
+	uint32_t motif = v / m, overhang = v - motif * m;
+	uint32_t out = 0;
+	for (uint32_t i = 0; i < m; i++)
+	{
+		uint32_t src_digit = (overhang + (m - 1 - i)) % m;                 // digit index, 0 = most significant
+		uint32_t d = (motif >> (2 * (m - 1 - src_digit))) & 3;
+		out = (out << 2) | (3 - d);
+	}
+	return CODES_BEFORE[m] + out * m + overhang;
+}
+
+// tab_hash[c] = char_hash(c), tab_hash_rc[c] = char_hash(complement(c)), tab_comp[c] = complement(c)
+__global__ void k_build_tables(uint64_t* __restrict__ tab_hash, uint64_t* __restrict__ tab_hash_rc, uint16_t* __restrict__ tab_comp)
+{
+	uint32_t c = blockIdx.x * blockDim.x + threadIdx.x;
+	if (c >= MAX_CODE) return;
+	uint32_t rc = complement_code(c);
+	tab_hash[c] = char_hash(c);
+	tab_hash_rc[c] = char_hash(rc);
+	tab_comp[c] = (uint16_t)rc;
+}
+
+// ---------------------------------------------------------------------------------------------- K0: pack
+
+// ASCII -> 2-bit.  One thread converts 16 characters (one 128-bit load) into one 32-bit word; characters outside
+// ACGTacgt are packed as A and their batch positions appended to `nonacgt` (rare; the host splits segments there).
+// Algorithmic bytes: 1 read + 1/4 written per base.
+__global__ void __launch_bounds__(256) k_pack_ascii(const uint4* __restrict__ ascii, uint64_t n_bases, uint32_t* __restrict__ packed,
+	uint64_t* __restrict__ nonacgt, unsigned long long* __restrict__ nonacgt_count, uint64_t nonacgt_cap)
+{
+	const uint64_t n_chunks = (n_bases + 15) / 16;
+	for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n_chunks; i += (uint64_t)gridDim.x * blockDim.x)
+	{
+		uint4 v = __ldcs(ascii + i);
+		uint32_t in[4] = { v.x, v.y, v.z, v.w };
+		uint32_t out = 0;
+#pragma unroll
+		for (int j = 0; j < 4; j++)
+		{
+			uint32_t x = in[j];
+			uint32_t u = x & 0xdfdfdfdfu;
+			uint32_t ok = __vcmpeq4(u, 0x41414141u) | __vcmpeq4(u, 0x43434343u) | __vcmpeq4(u, 0x47474747u) | __vcmpeq4(u, 0x54545454u);
+			if (ok != 0xffffffffu)
+			{
+				for (int b = 0; b < 4; b++)
+				{
+					uint64_t pos = i * 16 + j * 4 + b;
+					if (((ok >> (8 * b)) & 0xff) == 0 && pos < n_bases)
+					{
+						unsigned long long slot = atomicAdd(nonacgt_count, 1ull);
+						if (slot < nonacgt_cap) nonacgt[slot] = pos;
+					}
+				}
+				x &= ok; // non-ACGT -> 0 -> packs as A
+			}
+			uint32_t t = ((x >> 1) ^ (x >> 2)) & 0x03030303u; // A0 C1 G2 T3
+			t |= t >> 6;
+			t = (t | (t >> 12)) & 0xff;
+			out |= t << (8 * j);
+		}
+		packed[i] = out;
+	}
+}
+
+// ------------------------------------------------------------------------------------------ K1: collapse
+
+// bit-compress: gathers the 2-bit groups of x selected by `keep` (one flag per group, at the even bit) into the low
+// bits, preserving order.  Parallel-suffix method (Hacker's Delight 7-4) on pair masks.
+__device__ __forceinline__ uint64_t compress_pairs(uint64_t x, uint64_t keep)
+{
+	uint64_t m = keep | (keep << 1);
+	x &= m;
+	uint64_t mk = ~m << 1;
+#pragma unroll
+	for (int i = 0; i < 6; i++)
+	{
+		uint64_t mp = mk ^ (mk << 1);
+		mp ^= mp << 2; mp ^= mp << 4; mp ^= mp << 8; mp ^= mp << 16; mp ^= mp << 32;
+		uint64_t mv = mp & m;
+		m = (m ^ mv) | (mv >> (1 << i));
+		uint64_t t = x & mv;
+		x = (x ^ t) | (t >> (1 << i));
+		mk &= ~mp;
+	}
+	return x;
+}
+
+struct SegTable
+{
+	const uint64_t* in_start;  // first base of the segment in `packed`
+	const uint32_t* len;       // bases
+	const uint64_t* out_base;  // first symbol / code slot owned by the segment
+	uint32_t n;
+};
+
+// K1: homopolymer collapse (MBG/ReadHelper.h:864-876 collapse, :899-1018 run-length symbols).  One CTA per segment;
+// each thread owns one 64-bit word = 32 bases per tile: neighbour compare -> keep mask -> popcount -> block prefix sum
+// -> bit-compress -> merged into a shared-memory staging tile -> coalesced 64-bit stores.
+// keep_all != 0 (--error-masking=no): every base is a symbol (the kernel only re-aligns the segment).
+// pos1 != nullptr: also writes the segment-relative raw position of every kept base (the run starts, i.e. poses).
+// Algorithmic bytes: 1/4 read per base + 1/4 written per symbol (+ 4 per symbol when pos1 is requested).
+template <int NT>
+__global__ void __launch_bounds__(NT) k_collapse(SegTable seg, const uint64_t* __restrict__ packed, uint64_t* __restrict__ sym,
+	uint32_t* __restrict__ seg_c1, uint32_t* __restrict__ pos1, int keep_all)
+{
+	__shared__ unsigned long long stage[NT + 2];
+	__shared__ uint32_t warp_tmp[NT / 32];
+	const uint32_t g = blockIdx.x;
+	if (g >= seg.n) return;
+	const uint64_t in0 = seg.in_start[g];
+	const uint32_t len = seg.len[g];
+	const uint64_t out0 = seg.out_base[g];
+	uint64_t* __restrict__ out = sym + (out0 >> 5);
+	uint32_t carry = 0; // symbols written so far
+	if (threadIdx.x == 0) stage[0] = 0;
+	for (uint32_t tile = 0; tile < len; tile += NT * 32)
+	{
+		const uint32_t base0 = tile + threadIdx.x * 32;
+		uint64_t x = 0, keep = 0;
+		if (base0 < len)
+		{
+			const uint32_t nvalid = min(32u, len - base0);
+			x = window64(packed, in0 + base0);
+			if (keep_all) keep = 0x5555555555555555ull;
+			else
+			{
+				uint64_t y = base0 == 0 ? (x << 2) : window64(packed, in0 + base0 - 1);
+				uint64_t d = x ^ y;
+				keep = (d | (d >> 1)) & 0x5555555555555555ull;
+				if (base0 == 0) keep |= 1;
+			}
+			keep &= low_pairs(nvalid);
+		}
+		const uint32_t cnt = __popcll(keep);
+		uint32_t tile_total;
+		const uint32_t excl = block_exclusive_sum<NT>(cnt, warp_tmp, tile_total);
+		// the staging tile holds symbols [carry & ~31, ...): word 0 keeps the partial word of the previous tile
+		for (uint32_t i = 1 + threadIdx.x; i < NT + 2; i += NT) stage[i] = 0;
+		__syncthreads();
+		if (cnt)
+		{
+			const uint64_t c = compress_pairs(x, keep);
+			const uint32_t o = (carry & 31) + excl;
+			const uint32_t sh = (o & 31) * 2;
+			atomicOr(&stage[o >> 5], (unsigned long long)(c << sh));
+			if (sh && (cnt * 2 + sh > 64)) atomicOr(&stage[(o >> 5) + 1], (unsigned long long)(c >> (64 - sh)));
+			if (pos1)
+			{
+				uint32_t idx = carry + excl;
+				uint64_t kk = keep;
+				while (kk) { uint32_t b = __ffsll((long long)kk) - 1; kk &= kk - 1; pos1[out0 + idx++] = base0 + (b >> 1); }
+			}
+		}
+		__syncthreads();
+		const uint32_t filled = (carry & 31) + tile_total;       // symbols now in the staging tile
+		const bool last = tile + NT * 32 >= len;
+		const uint32_t n_words = last ? (filled + 31) / 32 : filled / 32;
+		const uint32_t w0 = carry >> 5;
+		for (uint32_t i = threadIdx.x; i < n_words; i += NT) out[w0 + i] = stage[i];
+		const unsigned long long partial = (filled & 31) ? stage[filled >> 5] : 0ull;
+		__syncthreads();
+		if (threadIdx.x == 0) stage[0] = partial;
+		carry += tile_total;
+	}
+	if (threadIdx.x == 0)
+	{
+		seg_c1[g] = carry;
+		if (pos1) pos1[out0 + carry] = len;
+	}
+}
+
+// ------------------------------------------------------------------------------- K2: microsatellite coding
+
+// 1 bit per symbol (at the even bit) where sym[p] == sym[p+m], from 32 symbols x and the 32 that follow (nx)
+__device__ __forceinline__ uint64_t eq_shift(uint64_t x, uint64_t nx, uint32_t m)
+{
+	uint64_t y = (x >> (2 * m)) | (nx << (64 - 2 * m));
+	uint64_t d = x ^ y;
+	return ~(d | (d >> 1)) & 0x5555555555555555ull;
+}
+
+// K2: multiRLECompress (MBG/ErrorMaskHelper.cpp:169-342) in scan-parallel form (DESIGN.md "K2"; the sequential
+// statement of exactly this algorithm is oracle/mbg_oracle.c:orc_msat_scanform, fuzzed against the reference).
+//   candidates : starts a of maximal stretches of eq_m (sym[p]==sym[p+m]) of length L >= m; run = [a, a+L+m)
+//   emitted    : candidate end > exclusive prefix maximum of candidate ends           (block max-scan + carry)
+//   cover      : 1 = inside exactly one emitted run, else single-symbol codes        (from the two carried ends)
+//   code start : p == 0 | cover(p) != 1 | cover(p-1) != 1 | a run is emitted at p     (popcount + block sum-scan)
+// One CTA per segment, one 64-bit word (32 symbols) per thread and tile; three block scans per tile.
+// Segments with fewer than 32 symbols produce no part (MBG/ReadHelper.h:847,858,882,893): seg_c2 = 0.
+// Algorithmic bytes: 1/4 read per symbol + 2 written per code (+ 4 per code when poses are requested).
+template <int NT>
+__global__ void __launch_bounds__(NT) k_msat(SegTable seg, const uint64_t* __restrict__ sym, const uint32_t* __restrict__ seg_c1,
+	uint16_t* __restrict__ codes, uint32_t* __restrict__ seg_c2, const uint32_t* __restrict__ pos1, uint32_t* __restrict__ pos2,
+	uint32_t max_motif)
+{
+	__shared__ uint32_t cand[NT * 33];      // per symbol of the tile: (run end << 3) | (7 - motif length), 0 = none (row stride 33: no bank conflicts)
+	__shared__ uint32_t warp_tmp[NT / 32];
+	__shared__ LastRun warp_last[NT / 32];
+	const uint32_t g = blockIdx.x;
+	if (g >= seg.n) return;
+	const uint32_t n = seg_c1[g];
+	if (n < 32) { if (threadIdx.x == 0) seg_c2[g] = 0; return; }
+	const uint64_t out0 = seg.out_base[g];
+	const uint64_t* __restrict__ s = sym + (out0 >> 5);   // segment-local words
+	const uint32_t n_words = (n + 31) / 32;
+	uint32_t* my_cand = cand + threadIdx.x * 33;
+	uint32_t carry_max = 0;            // maximum run end over all candidates of earlier tiles
+	LastRun carry_last; carry_last.m = 0; carry_last.start = 0; carry_last.prev_end = 0;
+	uint32_t carry_codes = 0;
+	for (uint32_t tile = 0; tile < n; tile += NT * 32)
+	{
+		const uint32_t p0 = tile + threadIdx.x * 32;
+		const uint32_t j = p0 >> 5;
+		const bool active = p0 < n;
+		uint64_t w0 = 0, w1 = 0;
+		if (active) { w0 = __ldg(s + j); if (j + 1 < n_words) w1 = __ldg(s + j + 1); }
+		// ---- candidates: starts of stretches of eq_m of length >= m, with the end of the run they open
+		uint32_t local_max = 0;
+		uint32_t cand_bits = 0;
+		if (active)
+		{
+			for (uint32_t m = 2; m <= max_motif; m++)
+			{
+				if (n < 2 * m) break;
+				const uint32_t lim = n - m;            // eq_m(p) is defined for p < lim
+				uint64_t e0 = eq_shift(w0, w1, m);
+				uint64_t e1 = eq_shift(w1, 0, m) & low_pairs(32 - m); // what w1 alone determines
+				e0 &= lim > p0 ? low_pairs(min(32u, lim - p0)) : 0ull;
+				e1 &= lim > p0 + 32 ? low_pairs(min(32u, lim - p0 - 32)) : 0ull;
+				uint64_t prev = 0;
+				if (p0 > 0 && p0 - 1 < lim) prev = symbol_at(s, p0 - 1) == symbol_at(s, p0 - 1 + m) ? 1ull : 0ull;
+				uint64_t run = e0 & ~((e0 << 2) | prev);
+				for (uint32_t t = 1; t < m; t++) run &= (e0 >> (2 * t)) | (e1 << (64 - 2 * t));
+				while (run)
+				{
+					const uint32_t b = (uint32_t)(__ffsll((long long)run) - 1) >> 1;
+					run &= run - 1;
+					// eq_m holds on [a, a+m); walk on, 32 symbols per step, to the first p with sym[p] != sym[p+m]
+					uint32_t q = p0 + b + m;
+					while (q < lim)
+					{
+						const uint64_t d = window64(s, q) ^ window64(s, q + m);
+						uint64_t ne = (d | (d >> 1)) & 0x5555555555555555ull;
+						const uint32_t room = lim - q;
+						if (room < 32) ne |= ~low_pairs(room) & 0x5555555555555555ull;
+						if (ne) { q += (uint32_t)(__ffsll((long long)ne) - 1) >> 1; break; }
+						q += 32;
+					}
+					if (q > lim) q = lim;
+					const uint32_t end = q + m;
+					const uint32_t val = (end << 3) | (7 - m);   // larger end wins, then smaller motif
+					if (!((cand_bits >> b) & 1) || val > my_cand[b]) my_cand[b] = val;
+					cand_bits |= 1u << b;
+					local_max = max(local_max, end);
+				}
+			}
+		}
+		// ---- scan 1: exclusive prefix maximum of candidate ends
+		uint32_t tile_max;
+		const uint32_t pm_in = max(block_exclusive_max<NT>(local_max, warp_tmp, tile_max), carry_max);
+		// ---- emitted runs of this word: end beyond everything seen before
+		uint32_t emit_bits = 0;
+		LastRun my_last; my_last.m = 0; my_last.start = 0; my_last.prev_end = 0;
+		{
+			uint32_t running = pm_in;
+			uint32_t cb = cand_bits;
+			while (cb)
+			{
+				const uint32_t b = __ffs(cb) - 1; cb &= cb - 1;
+				const uint32_t val = my_cand[b];
+				const uint32_t end = val >> 3;
+				if (end > running)
+				{
+					emit_bits |= 1u << b;
+					my_last.start = p0 + b; my_last.prev_end = running; my_last.m = 7 - (val & 7);
+					running = end;
+				}
+			}
+		}
+		// ---- scan 2: latest emitted run that starts before this word
+		LastRun tile_last;
+		LastRun last_in = block_exclusive_last<NT>(my_last, warp_last, tile_last);
+		if (last_in.m == 0) last_in = carry_last;
+		// ---- coverage of the 32 symbols of this word
+		//   ge1(p): some run covers p      <=> (maximum run end over candidates at or before p) > p
+		//   ge2(p): two runs cover p       <=> (prev_end of the latest emitted run at or before p) > p
+		uint32_t flags = 0, cover1 = 0;
+		bool prev_cover1 = false;
+		if (active)
+		{
+			const uint32_t nvalid = min(32u, n - p0);
+			const uint32_t valid = nvalid >= 32 ? FULL : ((1u << nvalid) - 1);
+			const uint32_t pe_in = last_in.m ? last_in.prev_end : 0;
+			uint32_t ge1 = pm_in > p0 ? (pm_in - p0 >= 32 ? FULL : ((1u << (pm_in - p0)) - 1)) : 0;
+			uint32_t ge2 = pe_in > p0 ? (pe_in - p0 >= 32 ? FULL : ((1u << (pe_in - p0)) - 1)) : 0;
+			uint32_t running = pm_in;
+			uint32_t eb = emit_bits;
+			while (eb)
+			{
+				const uint32_t b = __ffs(eb) - 1; eb &= eb - 1;
+				const uint32_t end = my_cand[b] >> 3;
+				const uint32_t from = ~((1u << b) - 1);
+				ge1 |= from & (end - p0 >= 32 ? FULL : ((1u << (end - p0)) - 1));
+				ge2 &= ~from;
+				if (running > p0 + b) ge2 |= from & (running - p0 >= 32 ? FULL : ((1u << (running - p0)) - 1));
+				running = end;
+			}
+			cover1 = ge1 & ~ge2 & valid;
+			if (p0 > 0) prev_cover1 = (pm_in > p0 - 1) && !(pe_in > p0 - 1);
+			const uint32_t not1 = ~cover1;
+			const uint32_t prev_not1 = (not1 << 1) | (prev_cover1 ? 0u : 1u);
+			flags = (not1 | prev_not1 | emit_bits) & valid;
+		}
+		// ---- scan 3: index of the first code that starts in this word
+		uint32_t tile_codes;
+		uint32_t idx = block_exclusive_sum<NT>(__popc(flags), warp_tmp, tile_codes) + carry_codes;
+		// ---- codes: a single-symbol code at every flag outside cover == 1; a stretch of cover == 1 is written when
+		//      it ends (at the next flag, or at n), by the thread that owns the symbol after it
+		if (active)
+		{
+			LastRun cur = last_in;          // latest emitted run starting before the cursor
+			uint32_t run_end = pm_in;       // end of that run (== prefix maximum)
+			uint32_t eb = emit_bits;
+			uint32_t fb = flags;
+			const bool owns_end = p0 + 32 >= n;
+			while (true)
+			{
+				uint32_t b;
+				bool at_end = false;
+				if (fb) { b = __ffs(fb) - 1; fb &= fb - 1; }
+				else if (owns_end) { b = n - p0; at_end = true; }
+				else break;
+				// runs emitted at symbols before b now precede the cursor
+				while (eb && (uint32_t)(__ffs(eb) - 1) < b)
+				{
+					const uint32_t bb = __ffs(eb) - 1; eb &= eb - 1;
+					cur.start = p0 + bb; cur.prev_end = run_end; cur.m = 7 - (my_cand[bb] & 7);
+					run_end = my_cand[bb] >> 3;
+				}
+				const uint32_t q = p0 + b;
+				const bool before_cover1 = b == 0 ? prev_cover1 : ((cover1 >> (b - 1)) & 1) != 0;
+				if (before_cover1)
+				{
+					// symbols [ps, q) are covered by `cur` alone: one code with its motif length (clamped to the stretch)
+					const uint32_t ps = max(cur.start, cur.prev_end);
+					const uint32_t slen = q - ps;
+					const uint32_t m = min(cur.m, slen);
+					uint32_t motif = 0;
+					for (uint32_t i = 0; i < m; i++) motif = (motif << 2) | symbol_at(s, ps + i);
+					const uint32_t oi = idx - 1;
+					codes[out0 + oi] = (uint16_t)(CODES_BEFORE[m] + motif * m + (slen % m));
+					if (pos2) pos2[out0 + oi] = pos1 ? pos1[out0 + ps] : ps;
+				}
+				if (at_end) break;
+				if (!((cover1 >> b) & 1))
+				{
+					codes[out0 + idx] = (uint16_t)((w0 >> (2 * b)) & 3);
+					if (pos2) pos2[out0 + idx] = pos1 ? pos1[out0 + q] : q;
+				}
+				idx++;
+			}
+		}
+		carry_max = max(carry_max, tile_max);
+		if (tile_last.m) carry_last = tile_last;
+		carry_codes += tile_codes;
+	}
+	if (threadIdx.x == 0)
+	{
+		seg_c2[g] = carry_codes;
+		if (pos2) pos2[out0 + carry_codes] = pos1 ? pos1[out0 + n] : n;
+	}
+}
+
+// modes without microsatellite coding: codes are the symbols themselves (2-bit -> uint16), poses are pos1
+template <int NT>
+__global__ void __launch_bounds__(NT) k_unpack_symbols(SegTable seg, const uint64_t* __restrict__ sym, const uint32_t* __restrict__ seg_c1,
+	uint16_t* __restrict__ codes, uint32_t* __restrict__ seg_c2, const uint32_t* __restrict__ pos1, uint32_t* __restrict__ pos2)
+{
+	const uint32_t g = blockIdx.x;
+	if (g >= seg.n) return;
+	const uint32_t n = seg_c1[g];
+	const uint64_t out0 = seg.out_base[g];
+	const uint64_t* __restrict__ s = sym + (out0 >> 5);
+	for (uint32_t p = threadIdx.x; p < n; p += NT)
+	{
+		codes[out0 + p] = (uint16_t)((__ldg(s + (p >> 5)) >> ((p & 31) * 2)) & 3);
+		if (pos2) pos2[out0 + p] = pos1 ? pos1[out0 + p] : p;
+	}
+	if (threadIdx.x == 0)
+	{
+		seg_c2[g] = n;
+		if (pos2) pos2[out0 + n] = pos1 ? pos1[out0 + n] : n;
+	}
+}
+
+// ----------------------------------------------------------------- K3a: rolling s-mer hash + syncmer selection
+
+// Shared-memory plan of k_select for history H (multiple of 64, >= k-1) and tile T (multiple of 64):
+//   P,Q   pad(H + T + 1) x 8 B each : XOR prefix of rotr(hash[c_j], j) / rotl(hash_rc[c_j], j), j = buffer-local index
+//   hv    (T + W8) x 8 B            : canonical s-mer hash at buffer-local s-mer index, W8 = roundup8(w) + 8
+//   bmin, bmin2                     : minima over aligned blocks of 8 hashes, and one sparse-table level over those
+// pad(l) = l + l/8 spreads the per-thread runs of 8 consecutive prefix values over the banks.
+struct SelectPlan { uint32_t H, T, W8, smem_bytes; };
+__host__ __device__ __forceinline__ uint32_t pad8(uint32_t l) { return l + (l >> 3); }
+
+// K3a: FastHasher + findSyncmerPositions (MBG/FastHasher.h:16-32, MBG/ReadHelper.h:31-79) without the sequential
+// dependence: with P[n] = XOR_{j<n} rotr(h[c_j], j) and Q[n] = XOR_{j<n} rotl(hrc[c_j], j) the rolling hash of the
+// s-mer at i is min(rotl(P[i+s]^P[i], i+s-1), rotr(Q[i+s]^Q[i], i)), so a tile needs two XOR block
+// scans and then every s-mer is independent.  k-mer p is selected iff hash[p] or hash[p+w-1] equals the minimum of
+// hash[p..p+w-1] (ties kept).  The window minimum is assembled from minima of aligned blocks of 8
+// hashes plus one sparse-table level over those, so each thread decides 8 consecutive k-mers with O(1) reads.
+// One CTA per segment walks the segment in tiles of T new codes; the prefix values of the last H codes stay in
+// shared memory, so no code is hashed twice.  Output: 1 bit per code position + selected count per segment.
+// Algorithmic bytes: 2 read per code + 1/8 written per code.
+template <int NT>
+__global__ void __launch_bounds__(NT) k_select(SegTable seg, const uint16_t* __restrict__ codes, const uint32_t* __restrict__ seg_c2,
+	const uint64_t* __restrict__ tab_hash, const uint64_t* __restrict__ tab_hash_rc, uint8_t* __restrict__ selmask, uint32_t* __restrict__ seg_nsel,
+	uint32_t k, uint32_t w, SelectPlan plan)
+{
+	MBGFE_DYN_SMEM(smem_raw);
+	__shared__ Xor2 warp_x[NT / 32];
+	__shared__ uint32_t warp_tmp[NT / 32];
+	const uint32_t g = blockIdx.x;
+	if (g >= seg.n) return;
+	const uint32_t n = seg_c2[g];
+	if (n < k) { if (threadIdx.x == 0) seg_nsel[g] = 0; return; }
+	const uint32_t H = plan.H, T = plan.T;
+	const uint32_t n_pref = pad8(H + T + 1) + 1;
+	uint64_t* P = (uint64_t*)smem_raw;
+	uint64_t* Q = P + n_pref;
+	uint64_t* hv = Q + n_pref;
+	const uint32_t n_h = T + plan.W8;
+	uint64_t* bmin = hv + n_h;
+	const uint32_t n_blocks = n_h / 8;
+	uint64_t* bmin2 = bmin + n_blocks;
+	const uint64_t out0 = seg.out_base[g];
+	const uint16_t* __restrict__ c = codes + out0;
+	uint8_t* __restrict__ mask_out = selmask + (out0 >> 3);
+	const uint32_t s = k - w + 1;
+	const uint32_t n_kmers = n - k + 1;
+	const uint32_t n_smers = n - s + 1;
+	// window [p, p+w-1] with w-1 = 8a + r
+	const uint32_t a = (w - 1) >> 3, r = (w - 1) & 7;
+	uint32_t lvl = 0;
+	if (a >= 2) { while ((2u << lvl) <= a - 1) lvl++; }
+	const uint32_t span = 1u << lvl;
+	uint32_t total_sel = 0;
+	// buffer-local index l  <->  global code / s-mer / k-mer index (tile0 - H + l)
+	for (uint32_t i = threadIdx.x; i <= H; i += NT) { P[pad8(i)] = 0; Q[pad8(i)] = 0; }
+	Xor2 carry = { 0, 0 };
+	__syncthreads();
+	for (uint32_t tile0 = 0; ; tile0 += T)
+	{
+		// ---- XOR prefix over the new codes [tile0, tile0 + n_new): buffer-local (H, H + n_new]
+		const uint32_t n_new = min(T, n - tile0);
+		const uint32_t per = (T + NT - 1) / NT;
+		const uint32_t lo = min(n_new, threadIdx.x * per), hi = min(n_new, lo + per);
+		Xor2 acc = { 0, 0 };
+		for (uint32_t i = lo; i < hi; i++)
+		{
+			const uint32_t code = c[tile0 + i];
+			const uint32_t l = H + i;          // only l mod 64 matters; H and T are multiples of 64
+			acc.a ^= rotr64(__ldg(tab_hash + code), l);
+			acc.b ^= rotl64(__ldg(tab_hash_rc + code), l);
+			P[pad8(l + 1)] = acc.a; Q[pad8(l + 1)] = acc.b;
+		}
+		Xor2 tile_x;
+		Xor2 off = block_exclusive_xor<NT>(acc, warp_x, tile_x);
+		off.a ^= carry.a; off.b ^= carry.b;
+		for (uint32_t i = lo; i < hi; i++) { P[pad8(H + i + 1)] ^= off.a; Q[pad8(H + i + 1)] ^= off.b; }
+		carry.a ^= tile_x.a; carry.b ^= tile_x.b;
+		__syncthreads();
+		// ---- k-mers decided by this tile: buffer-local [0, T) == global [tile0 - H, tile0 - H + T).  The last tile
+		//      (all codes loaded) decides everything that is left, in rounds of T positions.
+		const bool all_loaded = tile0 + T >= n;
+		const int64_t first_kmer = (int64_t)tile0 - (int64_t)H;
+		for (uint32_t round = 0; ; round += T)
+		{
+			// canonical hashes of the s-mers at buffer-local [round, round + n_h)
+			for (uint32_t i = threadIdx.x; i < n_h; i += NT)
+			{
+				const uint32_t l = round + i;
+				const int64_t gi = first_kmer + l;
+				uint64_t v = ~0ull;
+				if (gi >= 0 && gi < (int64_t)n_smers && l + s <= H + n_new)
+				{
+					const uint64_t fw = rotl64(P[pad8(l + s)] ^ P[pad8(l)], l + s - 1);
+					const uint64_t bw = rotr64(Q[pad8(l + s)] ^ Q[pad8(l)], l);
+					v = fw < bw ? fw : bw;
+				}
+				hv[i] = v;
+			}
+			__syncthreads();
+			for (uint32_t b = threadIdx.x; b < n_blocks; b += NT)
+			{
+				uint64_t m = hv[8 * b];
+#pragma unroll
+				for (int t = 1; t < 8; t++) m = min(m, hv[8 * b + t]);
+				bmin[b] = m;
+			}
+			__syncthreads();
+			for (uint32_t b = threadIdx.x; b < n_blocks; b += NT)
+			{
+				uint64_t m = bmin[b];
+				for (uint32_t t = 1; t < span && b + t < n_blocks; t++) m = min(m, bmin[b + t]);
+				bmin2[b] = m;
+			}
+			__syncthreads();
+			uint32_t my_count = 0;
+			for (uint32_t b = threadIdx.x; b < T / 8; b += NT)
+			{
+				const int64_t gp0 = first_kmer + round + 8 * b;
+				if (gp0 < 0 || gp0 >= (int64_t)n_kmers) continue;
+				// 8 k-mers at buffer-local positions round + 8b + j  (hv index 8b + j)
+				uint64_t own[8], suf[8];
+#pragma unroll
+				for (int t = 0; t < 8; t++) own[t] = hv[8 * b + t];
+				suf[7] = own[7];
+#pragma unroll
+				for (int t = 6; t >= 0; t--) suf[t] = min(own[t], suf[t + 1]);
+				uint64_t core = ~0ull;                                   // blocks b+1 .. b+a-1
+				if (a >= 2) core = min(bmin2[b + 1], bmin2[b + a - span]);
+				const uint64_t core_plus = a >= 1 ? min(core, bmin[b + a]) : ~0ull; // blocks b+1 .. b+a
+				uint32_t bits = 0;
+#pragma unroll
+				for (int jj = 0; jj < 8; jj++)
+				{
+					uint64_t wmin, last;
+					if (a == 0)
+					{
+						wmin = own[jj]; last = own[jj];
+						for (uint32_t t = 1; t <= r; t++) { last = hv[8 * b + jj + t]; wmin = min(wmin, last); }
+					}
+					else
+					{
+						const uint32_t e = jj + r;                       // window end = block b+a, offset e
+						const uint32_t eb = e < 8 ? b + a : b + a + 1;
+						const uint32_t eo = e < 8 ? e : e - 8;
+						uint64_t pre = hv[8 * eb];
+						for (uint32_t t = 1; t <= eo; t++) pre = min(pre, hv[8 * eb + t]);
+						last = hv[8 * eb + eo];
+						wmin = min(suf[jj], min(pre, e < 8 ? core : core_plus));
+					}
+					if (gp0 + jj < (int64_t)n_kmers && (own[jj] == wmin || last == wmin)) bits |= 1u << jj;
+				}
+				mask_out[gp0 >> 3] = (uint8_t)bits;
+				my_count += __popc(bits);
+			}
+			uint32_t round_sel;
+			block_exclusive_sum<NT>(my_count, warp_tmp, round_sel);
+			total_sel += round_sel;
+			if (!all_loaded) break;
+			if (first_kmer + (int64_t)round + (int64_t)T >= (int64_t)n_kmers) break;
+		}
+		if (all_loaded) break;
+		// ---- slide the history: buffer-local [T, T+H] -> [0, H] (ranges may overlap: read a chunk, barrier, write it)
+		for (uint32_t base = 0; base <= H; base += NT)
+		{
+			const uint32_t i = base + threadIdx.x;
+			uint64_t pv = 0, qv = 0;
+			if (i <= H) { pv = P[pad8(T + i)]; qv = Q[pad8(T + i)]; }
+			__syncthreads();
+			if (i <= H) { P[pad8(i)] = pv; Q[pad8(i)] = qv; }
+			__syncthreads();
+		}
+	}
+	if (threadIdx.x == 0) seg_nsel[g] = total_sel;
+}
+
+// --------------------------------------------------------------------------- K3b: positions and k-mer hashes
+
+// exclusive prefix sum of a small uint32 array into uint64 (one CTA; segment tables are small)
+template <int NT>
+__global__ void __launch_bounds__(NT) k_scan_u32(const uint32_t* __restrict__ in, uint64_t* __restrict__ out, uint32_t n)
+{
+	__shared__ uint32_t warp_tmp[NT / 32];
+	uint64_t carry = 0;
+	for (uint32_t base = 0; base < n; base += NT)
+	{
+		uint32_t i = base + threadIdx.x;
+		uint32_t v = i < n ? in[i] : 0;
+		uint32_t tot;
+		uint32_t ex = block_exclusive_sum<NT>(v, warp_tmp, tot);
+		if (i < n) out[i] = carry + ex;
+		carry += tot;
+	}
+	if (threadIdx.x == 0) out[n] = carry;
+}
+
+// K3b1: selection bitmask -> instance list.  One CTA per segment; inst_pos = part-local k-mer position,
+// inst_seg = segment, inst_flag bit0 = first selected k-mer of its part, bit1 = last (the tips, MBG/MBG.cpp:58).
+template <int NT>
+__global__ void __launch_bounds__(NT) k_list_selected(SegTable seg, const uint32_t* __restrict__ selmask32, const uint32_t* __restrict__ seg_c2,
+	const uint32_t* __restrict__ seg_nsel, const uint64_t* __restrict__ sel_begin, uint32_t* __restrict__ inst_pos, uint32_t* __restrict__ inst_seg,
+	uint8_t* __restrict__ inst_flag, uint32_t k)
+{
+	__shared__ uint32_t warp_tmp[NT / 32];
+	const uint32_t g = blockIdx.x;
+	if (g >= seg.n) return;
+	const uint32_t nsel = seg_nsel[g];
+	if (nsel == 0) return;
+	const uint32_t n_kmers = seg_c2[g] - k + 1;
+	const uint64_t out0 = seg.out_base[g];
+	const uint32_t* __restrict__ mw = selmask32 + (out0 >> 5);
+	const uint64_t begin = sel_begin[g];
+	uint32_t carry = 0;
+	for (uint32_t base = 0; base < n_kmers; base += NT * 32)
+	{
+		uint32_t p0 = base + threadIdx.x * 32;
+		uint32_t bits = 0;
+		if (p0 < n_kmers)
+		{
+			bits = mw[p0 >> 5];
+			uint32_t nv = n_kmers - p0;
+			if (nv < 32) bits &= (1u << nv) - 1;
+		}
+		uint32_t tot;
+		uint32_t idx = block_exclusive_sum<NT>(__popc(bits), warp_tmp, tot) + carry;
+		while (bits)
+		{
+			uint32_t b = __ffs(bits) - 1; bits &= bits - 1;
+			inst_pos[begin + idx] = p0 + b;
+			inst_seg[begin + idx] = g;
+			inst_flag[begin + idx] = (uint8_t)((idx == 0 ? 1 : 0) | (idx == nsel - 1 ? 2 : 0));
+			idx++;
+		}
+		carry += tot;
+	}
+}
+
+// libstdc++ std::hash<std::string_view> == _Hash_bytes (MurmurHash64A variant, seed 0xc70f6907) as called by
+// MBG/MBGCommon.cpp:25-35 on the raw little-endian bytes of `half` uint16 codes.
+struct Murmur
+{
+	static constexpr uint64_t MUL = 0xc6a4a7935bd1e995ull;
+	uint64_t h;
+	__device__ __forceinline__ void init(uint64_t len_bytes) { h = 0xc70f6907ull ^ (len_bytes * MUL); }
+	__device__ __forceinline__ void block(uint64_t wd) { wd *= MUL; wd ^= wd >> 47; wd *= MUL; h ^= wd; h *= MUL; }
+	__device__ __forceinline__ void tail(uint64_t wd) { h ^= wd; h *= MUL; }
+	__device__ __forceinline__ uint64_t finish() { h ^= h >> 47; h *= MUL; h ^= h >> 47; return h; }
+};
+
+// K3b2: 128-bit k-mer hash (MBG/MBGCommon.cpp:25-35).  One thread per (instance, half): half 0 hashes the first
+// (k+1)/2 codes, half 1 the first (k+1)/2 codes of the reverse complement (complemented codes read backwards from
+// the k-mer's end).  Codes of a read stay L1/L2 resident across the ~k/50 k-mers that cover them.
+__global__ void __launch_bounds__(256) k_kmer_hash(const uint64_t* __restrict__ seg_out_base, const uint16_t* __restrict__ codes,
+	const uint16_t* __restrict__ tab_comp, const uint32_t* __restrict__ inst_pos, const uint32_t* __restrict__ inst_seg, uint64_t n_inst,
+	uint64_t* __restrict__ inst_hash, uint32_t k)
+{
+	const uint64_t t = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+	if (t >= 2 * n_inst) return;
+	const uint64_t i = t >> 1;
+	const uint32_t dir = (uint32_t)(t & 1);
+	const uint16_t* __restrict__ c = codes + seg_out_base[inst_seg[i]] + inst_pos[i];
+	const uint32_t half = (k + 1) / 2;
+	Murmur mm;
+	mm.init((uint64_t)half * 2);
+	const uint32_t n_blocks = half / 4;
+	if (dir == 0)
+	{
+		for (uint32_t b = 0; b < n_blocks; b++)
+		{
+			const uint16_t* p = c + 4 * b;
+			uint64_t wd = (uint64_t)p[0] | ((uint64_t)p[1] << 16) | ((uint64_t)p[2] << 32) | ((uint64_t)p[3] << 48);
+			mm.block(wd);
+		}
+		uint32_t rem = half & 3;
+		if (rem)
+		{
+			uint64_t wd = 0;
+			for (uint32_t j = 0; j < rem; j++) wd |= (uint64_t)c[4 * n_blocks + j] << (16 * j);
+			mm.tail(wd);
+		}
+	}
+	else
+	{
+		const uint16_t* e = c + (k - 1);
+		for (uint32_t b = 0; b < n_blocks; b++)
+		{
+			const uint16_t* p = e - 4 * b;
+			uint32_t c0 = p[0], c1 = *(p - 1), c2 = *(p - 2), c3 = *(p - 3);
+			c0 = c0 < 4 ? 3 - c0 : __ldg(tab_comp + c0);
+			c1 = c1 < 4 ? 3 - c1 : __ldg(tab_comp + c1);
+			c2 = c2 < 4 ? 3 - c2 : __ldg(tab_comp + c2);
+			c3 = c3 < 4 ? 3 - c3 : __ldg(tab_comp + c3);
+			uint64_t wd = (uint64_t)c0 | ((uint64_t)c1 << 16) | ((uint64_t)c2 << 32) | ((uint64_t)c3 << 48);
+			mm.block(wd);
+		}
+		uint32_t rem = half & 3;
+		if (rem)
+		{
+			uint64_t wd = 0;
+			for (uint32_t j = 0; j < rem; j++)
+			{
+				uint32_t cc = *(e - 4 * n_blocks - j);
+				cc = cc < 4 ? 3 - cc : __ldg(tab_comp + cc);
+				wd |= (uint64_t)cc << (16 * j);
+			}
+			mm.tail(wd);
+		}
+	}
+	inst_hash[2 * i + dir] = mm.finish();
+}
+
+// instances whose two halves hash alike: palindromes or (practically impossible) collisions -> host decides
+__global__ void __launch_bounds__(256) k_find_palindromes(const uint64_t* __restrict__ inst_hash, uint64_t n_inst, unsigned long long* __restrict__ count,
+	uint64_t* __restrict__ list, uint64_t cap)
+{
+	const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+	if (i >= n_inst) return;
+	if (inst_hash[2 * i] == inst_hash[2 * i + 1])
+	{
+		unsigned long long slot = atomicAdd(count, 1ull);
+		if (slot < cap) list[slot] = i;
+	}
+}
+
+// ---------------------------------------------------------------------------------------- K4: k-mer table
+
+// Node table: open addressing, linear probing, 32-byte slots (one DRAM sector):
+//   key_lo, key_hi : canonical hash (min of forward and swapped hash); all-ones = empty (cannot occur: it would need
+//                    fw == bw, which is a palindrome and never reaches the table)
+//   count          : coverage (HashList::coverage, MBG/HashList.cpp:120-149)
+//   flags          : bit 0 tip (HashList::setTipKmer)
+//   rank           : node id after the export sort (HashList::sortByHash)
+struct __align__(32) NodeSlot { uint64_t key_lo, key_hi; uint32_t count, flags; uint64_t rank; };
+
+__device__ __forceinline__ uint64_t slot_hash(uint64_t lo, uint64_t hi)
+{
+	uint64_t x = lo ^ (hi * 0x9e3779b97f4a7c15ull);
+	x ^= x >> 32;
+	return x;
+}
+
+// 128-bit compare-and-swap (sm_90+): returns true when the slot held {exp_lo, exp_hi} and now holds {lo, hi};
+// old_* always receive what the slot held.  load128 is one 16-byte access (never a torn pair of halves).
+#ifdef MBGFE_EMU_BUILD
+__device__ __forceinline__ bool cas128(NodeSlot* slot, uint64_t exp_lo, uint64_t exp_hi, uint64_t lo, uint64_t hi, uint64_t& old_lo, uint64_t& old_hi)
+{
+	std::lock_guard<std::mutex> guard(emu::big_lock());
+	old_lo = slot->key_lo; old_hi = slot->key_hi;
+	if (old_lo == exp_lo && old_hi == exp_hi) { slot->key_lo = lo; slot->key_hi = hi; return true; }
+	return false;
+}
+__device__ __forceinline__ void load128(const NodeSlot* slot, uint64_t& lo, uint64_t& hi)
+{
+	std::lock_guard<std::mutex> guard(emu::big_lock());
+	lo = slot->key_lo; hi = slot->key_hi;
+}
+#else
+__device__ __forceinline__ bool cas128(NodeSlot* slot, uint64_t exp_lo, uint64_t exp_hi, uint64_t lo, uint64_t hi, uint64_t& old_lo, uint64_t& old_hi)
+{
+	asm volatile(
+		"{\n\t"
+		".reg .b128 cmp, val, old;\n\t"
+		"mov.b128 cmp, {%2, %3};\n\t"
+		"mov.b128 val, {%4, %5};\n\t"
+		"atom.global.relaxed.gpu.cas.b128 old, [%6], cmp, val;\n\t"
+		"mov.b128 {%0, %1}, old;\n\t"
+		"}"
+		: "=l"(old_lo), "=l"(old_hi)
+		: "l"(exp_lo), "l"(exp_hi), "l"(lo), "l"(hi), "l"(slot)
+		: "memory");
+	return old_lo == exp_lo && old_hi == exp_hi;
+}
+__device__ __forceinline__ void load128(const NodeSlot* slot, uint64_t& lo, uint64_t& hi)
+{
+	asm volatile("ld.volatile.global.v2.u64 {%0, %1}, [%2];" : "=l"(lo), "=l"(hi) : "l"(slot) : "memory");
+}
+#endif
+
+__device__ __forceinline__ void canonical_key(uint64_t lo, uint64_t hi, uint64_t& key_lo, uint64_t& key_hi, uint32_t& fw)
+{
+	// forward hash = hi:lo, backward hash = lo:hi (halves swapped, MBG/HashList.cpp:122-127); fw == forward is smaller
+	fw = hi < lo ? 1u : 0u;
+	key_hi = fw ? hi : lo;
+	key_lo = fw ? lo : hi;
+}
+
+// Lock-free insert-or-update.  Slots only ever go from empty to one key, so a loaded value with no all-ones half is a
+// complete key; a value with an all-ones half may be empty or half-visible and is settled by the CAS, whose return
+// value is authoritative.  Returns the slot; is_new reports whether this call created the entry.
+__device__ __forceinline__ uint64_t node_insert(NodeSlot* __restrict__ table, uint64_t mask, uint64_t key_lo, uint64_t key_hi, uint32_t add, uint32_t flags, bool& is_new)
+{
+	uint64_t slot = slot_hash(key_lo, key_hi) & mask;
+	is_new = false;
+	while (true)
+	{
+		NodeSlot* sp = table + slot;
+		uint64_t cur_lo, cur_hi;
+		load128(sp, cur_lo, cur_hi);
+		if (cur_lo == ~0ull || cur_hi == ~0ull)
+		{
+			uint64_t old_lo, old_hi;
+			if (cas128(sp, ~0ull, ~0ull, key_lo, key_hi, old_lo, old_hi)) { is_new = true; cur_lo = key_lo; cur_hi = key_hi; }
+			else { cur_lo = old_lo; cur_hi = old_hi; }
+		}
+		if (cur_lo == key_lo && cur_hi == key_hi)
+		{
+			if (add) atomicAdd(&sp->count, add);
+			if (flags) atomicOr(&sp->flags, flags);
+			return slot;
+		}
+		slot = (slot + 1) & mask;
+	}
+}
+
+// one atomicAdd per warp for a per-thread 0/1 contribution; every thread of the warp must call it
+__device__ __forceinline__ void warp_count(unsigned long long* counter, bool pred)
+{
+	const uint32_t m = __ballot_sync(FULL, pred);
+	if ((threadIdx.x & 31) == 0 && m) atomicAdd(counter, (unsigned long long)__popc(m));
+}
+
+// warp-aggregated slot allocation: returns the output index for threads with pred; every thread must call it
+__device__ __forceinline__ unsigned long long warp_alloc(unsigned long long* cursor, bool pred)
+{
+	const uint32_t m = __ballot_sync(FULL, pred);
+	unsigned long long base = 0;
+	if ((threadIdx.x & 31) == 0 && m) base = atomicAdd(cursor, (unsigned long long)__popc(m));
+	base = __shfl_sync(FULL, base, 0);
+	return base + __popc(m & ((1u << (threadIdx.x & 31)) - 1));
+}
+
+__global__ void __launch_bounds__(256) k_table_clear(NodeSlot* __restrict__ table, uint64_t n_slots)
+{
+	for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n_slots; i += (uint64_t)gridDim.x * blockDim.x)
+	{
+		NodeSlot s; s.key_lo = ~0ull; s.key_hi = ~0ull; s.count = 0; s.flags = 0; s.rank = 0;
+		table[i] = s;
+	}
+}
+
+// K4a: count k-mers.  One thread per instance: canonical key, probe, 128-bit CAS claim, atomic add / or
+// (HashList::addNode + setTipKmer, MBG/HashList.cpp:120-149,23-26).
+// Algorithmic bytes: 16 read per instance + one 32-byte slot read and written (random access: sector-bound).
+__global__ void __launch_bounds__(256) k_insert_nodes(const uint64_t* __restrict__ inst_hash, const uint8_t* __restrict__ inst_flag, uint64_t n_inst,
+	NodeSlot* __restrict__ table, uint64_t mask, uint32_t* __restrict__ inst_slot, unsigned long long* __restrict__ distinct)
+{
+	const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+	bool is_new = false;
+	if (i < n_inst)
+	{
+		const uint64_t lo = inst_hash[2 * i], hi = inst_hash[2 * i + 1];
+		if (lo == hi) inst_slot[i] = 0xffffffffu; // palindrome (rare; the host resolves these before the table pass)
+		else
+		{
+			uint64_t key_lo, key_hi; uint32_t fw;
+			canonical_key(lo, hi, key_lo, key_hi, fw);
+			inst_slot[i] = (uint32_t)node_insert(table, mask, key_lo, key_hi, 1, inst_flag[i] ? 1u : 0u, is_new);
+		}
+	}
+	warp_count(distinct, is_new);
+}
+
+// records received from other ranks: {key_lo, key_hi, flags, reserved}
+__global__ void __launch_bounds__(256) k_insert_records(const uint64_t* __restrict__ rec, uint64_t n_rec, NodeSlot* __restrict__ table, uint64_t mask,
+	unsigned long long* __restrict__ distinct)
+{
+	const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+	bool is_new = false;
+	if (i < n_rec) node_insert(table, mask, rec[4 * i], rec[4 * i + 1], 1, (uint32_t)rec[4 * i + 2] & 1u, is_new);
+	warp_count(distinct, is_new);
+}
+
+// re-insert every entry of an old table into a larger one (growth)
+__global__ void __launch_bounds__(256) k_table_rehash(const NodeSlot* __restrict__ old_table, uint64_t old_slots, NodeSlot* __restrict__ table, uint64_t mask)
+{
+	for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < old_slots; i += (uint64_t)gridDim.x * blockDim.x)
+	{
+		NodeSlot s = old_table[i];
+		if (s.key_lo == ~0ull && s.key_hi == ~0ull) continue;
+		bool is_new;
+		node_insert(table, mask, s.key_lo, s.key_hi, s.count, s.flags, is_new);
+	}
+}
+
+__global__ void __launch_bounds__(256) k_lookup_nodes(const uint64_t* __restrict__ inst_hash, uint64_t n_inst, const NodeSlot* __restrict__ table, uint64_t mask,
+	uint32_t* __restrict__ inst_slot)
+{
+	const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+	if (i >= n_inst) return;
+	uint64_t lo = inst_hash[2 * i], hi = inst_hash[2 * i + 1];
+	uint64_t key_lo, key_hi; uint32_t fw;
+	canonical_key(lo, hi, key_lo, key_hi, fw);
+	uint64_t slot = slot_hash(key_lo, key_hi) & mask;
+	while (true)
+	{
+		const NodeSlot* sp = table + slot;
+		uint64_t cl = sp->key_lo, ch = sp->key_hi;
+		if (cl == key_lo && ch == key_hi) { inst_slot[i] = (uint32_t)slot; return; }
+		if (cl == ~0ull && ch == ~0ull) { inst_slot[i] = 0xffffffffu; return; }
+		slot = (slot + 1) & mask;
+	}
+}
+
+// Edge table: 32-byte slots keyed by the canonical (from, to) pair of (node slot << 1 | fw).
+//   key      : from << 32 | to ; all-ones = empty
+//   ordered  : (global instance index of the later k-mer << 24) | overlap ; atomicMax keeps the LAST observation
+//              in input order == what a single reference worker thread leaves (MBG/HashList.cpp:67-72)
+//   count    : HashList::addEdgeCoverage (MBG/HashList.cpp:103-112)
+struct __align__(32) EdgeSlot { unsigned long long key; unsigned long long ordered; uint32_t count, pad0; uint64_t pad1; };
+
+__global__ void __launch_bounds__(256) k_edge_clear(EdgeSlot* __restrict__ table, uint64_t n_slots)
+{
+	for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n_slots; i += (uint64_t)gridDim.x * blockDim.x)
+	{
+		EdgeSlot s; s.key = ~0ull; s.ordered = 0; s.count = 0; s.pad0 = 0; s.pad1 = 0;
+		table[i] = s;
+	}
+}
+
+// K4b: adjacency.  One thread per instance that has a predecessor in its part: canonical edge
+// (MBG/MBGCommon.cpp:78-89, decided by comparing canonical hashes, which is the id order after sortByHash),
+// coverage += 1, overlap = prev_pos + k - pos (MBG/MBG.cpp:59-67).
+__global__ void __launch_bounds__(256) k_insert_edges(const uint64_t* __restrict__ inst_hash, const uint32_t* __restrict__ inst_pos, const uint8_t* __restrict__ inst_flag,
+	const uint32_t* __restrict__ inst_slot, uint64_t n_inst, EdgeSlot* __restrict__ table, uint64_t mask, unsigned long long* __restrict__ distinct, uint32_t k)
+{
+	const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+	bool is_new = false;
+	if (i < n_inst && i > 0 && !(inst_flag[i] & 1) && inst_slot[i] != 0xffffffffu && inst_slot[i - 1] != 0xffffffffu)
+	{
+		uint64_t ak_lo, ak_hi, bk_lo, bk_hi; uint32_t afw, bfw;
+		canonical_key(inst_hash[2 * (i - 1)], inst_hash[2 * (i - 1) + 1], ak_lo, ak_hi, afw);
+		canonical_key(inst_hash[2 * i], inst_hash[2 * i + 1], bk_lo, bk_hi, bfw);
+		uint32_t from = inst_slot[i - 1], to = inst_slot[i];
+		uint32_t from_fw = afw, to_fw = bfw;
+		const bool to_smaller = bk_hi < ak_hi || (bk_hi == ak_hi && bk_lo < ak_lo);
+		const bool same = bk_hi == ak_hi && bk_lo == ak_lo;
+		if (to_smaller || (same && !to_fw && !from_fw))
+		{
+			const uint32_t t = from; from = to; to = t;
+			const uint32_t f = from_fw; from_fw = !to_fw; to_fw = !f;
+		}
+		const unsigned long long key = ((unsigned long long)(((uint64_t)from << 1) | from_fw) << 32) | (((uint64_t)to << 1) | to_fw);
+		const uint32_t overlap = inst_pos[i - 1] + k - inst_pos[i];
+		const unsigned long long ordered = ((unsigned long long)i << 24) | overlap;
+		uint64_t slot = slot_hash(key, key >> 17) & mask;
+		while (true)
+		{
+			EdgeSlot* sp = table + slot;
+			unsigned long long cur = *(volatile unsigned long long*)&sp->key;
+			if (cur == ~0ull)
+			{
+				const unsigned long long old = atomicCAS(&sp->key, ~0ull, key);
+				if (old == ~0ull) { is_new = true; cur = key; } else cur = old;
+			}
+			if (cur == key)
+			{
+				atomicAdd(&sp->count, 1u);
+				atomicMax(&sp->ordered, ordered);
+				break;
+			}
+			slot = (slot + 1) & mask;
+		}
+	}
+	warp_count(distinct, is_new);
+}
+
+// ------------------------------------------------------------------------------------------------ export
+
+// occupied node slots -> dense arrays (order arbitrary; sorted by key afterwards)
+struct NodeOut { uint64_t key_lo, key_hi; uint32_t count, flags; uint64_t slot; };
+__global__ void __launch_bounds__(256) k_export_nodes(const NodeSlot* __restrict__ table, uint64_t n_slots, NodeOut* __restrict__ out, unsigned long long* __restrict__ cursor)
+{
+	const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
+	const uint64_t rounds = (n_slots + stride - 1) / stride;
+	for (uint64_t rd = 0; rd < rounds; rd++)
+	{
+		const uint64_t i = rd * stride + (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+		NodeSlot s; s.key_lo = ~0ull; s.key_hi = ~0ull; s.count = 0; s.flags = 0; s.rank = 0;
+		if (i < n_slots) s = table[i];
+		const bool used = !(s.key_lo == ~0ull && s.key_hi == ~0ull);
+		const unsigned long long o = warp_alloc(cursor, used);
+		if (used) { NodeOut r; r.key_lo = s.key_lo; r.key_hi = s.key_hi; r.count = s.count; r.flags = s.flags; r.slot = i; out[o] = r; }
+	}
+}
+
+struct EdgeOut { unsigned long long key; unsigned long long ordered; uint32_t count, pad; };
+__global__ void __launch_bounds__(256) k_export_edges(const EdgeSlot* __restrict__ table, uint64_t n_slots, EdgeOut* __restrict__ out, unsigned long long* __restrict__ cursor)
+{
+	const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
+	const uint64_t rounds = (n_slots + stride - 1) / stride;
+	for (uint64_t rd = 0; rd < rounds; rd++)
+	{
+		const uint64_t i = rd * stride + (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+		EdgeSlot s; s.key = ~0ull; s.ordered = 0; s.count = 0;
+		if (i < n_slots) s = table[i];
+		const bool used = s.key != ~0ull;
+		const unsigned long long o = warp_alloc(cursor, used);
+		if (used) { EdgeOut r; r.key = s.key; r.ordered = s.ordered; r.count = s.count; r.pad = 0; out[o] = r; }
+	}
+}
+
+// ------------------------------------------------------------------------------------- multi-GPU exchange
+
+__device__ __forceinline__ uint32_t owner_of(uint64_t key_hi, uint32_t world)
+{
+	return (uint32_t)__umul64hi(key_hi, (uint64_t)world); // range partition of the canonical hash space
+}
+
+__global__ void __launch_bounds__(256) k_owner_count(const uint64_t* __restrict__ inst_hash, uint64_t n_inst, uint32_t world, unsigned long long* __restrict__ counts)
+{
+	const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+	if (i >= n_inst) return;
+	uint64_t lo = inst_hash[2 * i], hi = inst_hash[2 * i + 1];
+	if (lo == hi) return;
+	uint64_t key_lo, key_hi; uint32_t fw;
+	canonical_key(lo, hi, key_lo, key_hi, fw);
+	atomicAdd(counts + owner_of(key_hi, world), 1ull);
+}
+
+__global__ void __launch_bounds__(256) k_owner_pack(const uint64_t* __restrict__ inst_hash, const uint8_t* __restrict__ inst_flag, uint64_t n_inst, uint32_t world,
+	unsigned long long* __restrict__ cursors, uint64_t* __restrict__ records)
+{
+	const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+	if (i >= n_inst) return;
+	uint64_t lo = inst_hash[2 * i], hi = inst_hash[2 * i + 1];
+	if (lo == hi) return;
+	uint64_t key_lo, key_hi; uint32_t fw;
+	canonical_key(lo, hi, key_lo, key_hi, fw);
+	unsigned long long o = atomicAdd(cursors + owner_of(key_hi, world), 1ull);
+	records[4 * o] = key_lo; records[4 * o + 1] = key_hi; records[4 * o + 2] = inst_flag[i] ? 1 : 0; records[4 * o + 3] = 0;
+}
+
+// KAT helper: complement table and per-code hash are read back directly; the k-mer hash runs k_kmer_hash on one
+// synthetic instance.
+
+} // namespace mbgfe_dev

@@ -1,0 +1,985 @@
+// mbgfe.cu -- host side of libmbgfe: C ABI (include/mbgfe.h), batch upload, kernel sequencing, result export.
+//
+// Reference being replaced (MBG/ = /root/reference/src/hifioverlapper/MBG/src, commit 7bef84dd):
+//   ReadpartIterator::iterateHashes / iterateParts (MBG/ReadHelper.h:167-235, 792-841) and the loop body of
+//   loadReadsAsHashesMultithread (MBG/MBG.cpp:44-76) with its HashList (MBG/HashList.cpp).
+// The compute path is CUDA only (kernels.cuh).  There is no host implementation of any stage in this file: the host
+// parses files, builds the (tiny) segment table, sequences kernels and orders the exported table.
+#include <algorithm>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+#include <zlib.h>
+
+#include "kernels.cuh"
+#include "../../include/mbgfe.h"
+
+#ifdef MBGFE_EMU_BUILD
+thread_local uint3 threadIdx;
+thread_local uint3 blockIdx;
+thread_local dim3 blockDim;
+thread_local dim3 gridDim;
+#endif
+
+using namespace mbgfe_dev;
+
+namespace {
+
+thread_local std::string g_create_error;
+
+struct DevBuf
+{
+	void* p = nullptr;
+	size_t cap = 0;
+	template <typename T> T* as() const { return (T*)p; }
+};
+
+struct HostChunk { const char* bases; const uint64_t* offsets; uint64_t n_reads; };
+
+struct Timer
+{
+	cudaEvent_t a = nullptr, b = nullptr;
+};
+
+}
+
+struct mbgfe
+{
+	mbgfe_params prm;
+	std::string err;
+	bool collapse = false, msat = false;
+	uint32_t max_motif = 6;
+	cudaStream_t stream = nullptr;
+	int sm_count = 148;
+	size_t max_smem = 0;
+	SelectPlan plan;
+
+	// code tables
+	DevBuf tab_hash, tab_hash_rc, tab_comp;
+
+	// pending input
+	std::vector<HostChunk> pending;
+	std::vector<std::string> names;
+	std::vector<std::vector<char>*> owned_bases;       // file-loaded reads
+	std::vector<std::vector<uint64_t>*> owned_offsets;
+
+	// resident batch (host metadata)
+	bool resident = false, processed = false, exported_parts = false, exported_table = false, exported_codes = false, have_table = false;
+	uint64_t n_reads = 0, n_bases = 0;
+	std::vector<uint64_t> read_off;                   // n_reads + 1
+	std::vector<uint64_t> seg_in, seg_out;            // per segment
+	std::vector<uint32_t> seg_len, seg_read, seg_rawoff, seg_nonacgt_before;
+	uint64_t total_out = 0;
+	uint64_t nonacgt_count = 0;
+
+	// device buffers
+	DevBuf d_ascii, d_packed, d_nonacgt, d_counters;
+	DevBuf d_seg_in, d_seg_out, d_seg_len, d_seg_c1, d_seg_c2, d_seg_nsel, d_sel_begin;
+	DevBuf d_sym, d_codes, d_selmask, d_pos1, d_pos2;
+	DevBuf d_inst_pos, d_inst_seg, d_inst_flag, d_inst_hash, d_inst_slot, d_pal_list;
+	DevBuf d_nodes, d_edges, d_node_out, d_edge_out, d_records, d_recv;
+	uint64_t node_slots = 0, edge_slots = 0;
+	uint64_t n_inst = 0;
+
+	// host results
+	std::vector<mbgfe_part> parts;
+	std::vector<uint16_t> h_codes;
+	std::vector<uint32_t> h_poses, h_positions;
+	std::vector<mbgfe_hash128> h_hashes, h_node_hashes;
+	std::vector<uint32_t> h_node_cov;
+	std::vector<uint8_t> h_node_tip;
+	std::vector<mbgfe_edge> h_edges;
+	std::vector<uint32_t> h_seg_c1, h_seg_c2, h_seg_nsel;
+	std::vector<uint64_t> h_sel_begin;
+
+	mbgfe_stats stats;
+	cudaEvent_t ev[16];
+};
+
+namespace {
+
+int fail(mbgfe* h, int code, const char* fmt, ...)
+{
+	char buf[512];
+	va_list ap; va_start(ap, fmt); vsnprintf(buf, sizeof(buf), fmt, ap); va_end(ap);
+	if (h) h->err = buf; else g_create_error = buf;
+	return code;
+}
+
+#define CU(h, call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) return fail(h, MBGFE_E_CUDA, "%s failed: %s (%s:%d)", #call, cudaGetErrorString(e_), __FILE__, __LINE__); } while (0)
+
+int ensure(mbgfe* h, DevBuf& b, size_t bytes)
+{
+	bytes = (bytes + 255) & ~(size_t)255;
+	if (b.cap >= bytes) return 0;
+	if (b.p) CU(h, cudaFree(b.p));
+	b.p = nullptr; b.cap = 0;
+	CU(h, cudaMalloc(&b.p, bytes));
+	b.cap = bytes;
+	return 0;
+}
+
+void release(DevBuf& b) { if (b.p) cudaFree(b.p); b.p = nullptr; b.cap = 0; }
+
+uint64_t next_pow2(uint64_t v) { uint64_t p = 1; while (p < v) p <<= 1; return p; }
+
+bool is_acgt(char c) { c &= (char)0xdf; return c == 'A' || c == 'C' || c == 'G' || c == 'T'; }
+
+enum { CTR_NONACGT = 0, CTR_PALINDROME = 1, CTR_DISTINCT = 2, CTR_EDGES = 3, CTR_CURSOR = 4, CTR_OWNER = 8 /* .. 8+world */ };
+
+constexpr int NT_COLLAPSE = 128, NT_MSAT = 128, NT_SELECT = 256, NT_LIST = 128;
+
+SegTable seg_table(const mbgfe* h)
+{
+	SegTable t;
+	t.in_start = h->d_seg_in.as<uint64_t>();
+	t.len = h->d_seg_len.as<uint32_t>();
+	t.out_base = h->d_seg_out.as<uint64_t>();
+	t.n = (uint32_t)h->seg_len.size();
+	return t;
+}
+
+// Segments of the resident reads: reads shorter than 32 bases are ignored (MBG/ReadHelper.h:838); the others are cut
+// at every character outside ACGTacgt (positions found by k_pack_ascii, sorted ascending in `bad`).
+void build_segments(mbgfe* h, const std::vector<uint64_t>& bad, const std::vector<const char*>& read_ptr)
+{
+	h->seg_in.clear(); h->seg_out.clear(); h->seg_len.clear(); h->seg_read.clear(); h->seg_rawoff.clear(); h->seg_nonacgt_before.clear();
+	uint64_t out = 0;
+	size_t bi = 0;
+	auto add = [&](uint64_t r, uint64_t start, uint64_t len, uint32_t nonacgt_before)
+	{
+		h->seg_in.push_back(start);
+		h->seg_len.push_back((uint32_t)len);
+		h->seg_read.push_back((uint32_t)r);
+		h->seg_rawoff.push_back((uint32_t)(start - h->read_off[r]));
+		h->seg_nonacgt_before.push_back(nonacgt_before);
+		h->seg_out.push_back(out);
+		out += (len + 1 + 63) & ~(uint64_t)63;
+	};
+	for (uint64_t r = 0; r < h->n_reads; r++)
+	{
+		const uint64_t a = h->read_off[r], b = h->read_off[r + 1];
+		while (bi < bad.size() && bad[bi] < a) bi++;
+		if (b - a < 32) { while (bi < bad.size() && bad[bi] < b) bi++; continue; }
+		if (bi >= bad.size() || bad[bi] >= b) { add(r, a, b - a, 0); continue; }
+		// read with other characters: walk its non-ACGT positions
+		const char* raw = read_ptr[r];
+		uint64_t cur = a;
+		uint32_t collapsed_other = 0; // characters outside ACGT that survive the collapse step, so far
+		while (cur < b)
+		{
+			uint64_t stop = (bi < bad.size() && bad[bi] < b) ? bad[bi] : b;
+			if (stop > cur) add(r, cur, stop - cur, collapsed_other);
+			if (stop >= b) break;
+			// run of non-ACGT characters starting at stop
+			uint64_t e = stop;
+			while (bi < bad.size() && bad[bi] == e && e < b)
+			{
+				const uint64_t i = e - a;
+				// the reference compares the (already upper-cased) characters exactly (MBG/ReadHelper.h:873)
+				char c = raw[i], p = i > 0 ? raw[i - 1] : 0;
+				if (c >= 'a' && c <= 'z') c = (char)(c - 32);
+				if (p >= 'a' && p <= 'z') p = (char)(p - 32);
+				if (i == 0 || c != p) collapsed_other++;
+				e++; bi++;
+			}
+			cur = e;
+		}
+	}
+	h->total_out = out;
+}
+
+int upload_segments(mbgfe* h)
+{
+	const size_t n = h->seg_len.size();
+	if (int rc = ensure(h, h->d_seg_in, (n + 1) * 8)) return rc;
+	if (int rc = ensure(h, h->d_seg_out, (n + 1) * 8)) return rc;
+	if (int rc = ensure(h, h->d_seg_len, (n + 1) * 4)) return rc;
+	if (int rc = ensure(h, h->d_seg_c1, (n + 1) * 4)) return rc;
+	if (int rc = ensure(h, h->d_seg_c2, (n + 1) * 4)) return rc;
+	if (int rc = ensure(h, h->d_seg_nsel, (n + 1) * 4)) return rc;
+	if (int rc = ensure(h, h->d_sel_begin, (n + 2) * 8)) return rc;
+	if (n)
+	{
+		CU(h, cudaMemcpyAsync(h->d_seg_in.p, h->seg_in.data(), n * 8, cudaMemcpyHostToDevice, h->stream));
+		CU(h, cudaMemcpyAsync(h->d_seg_out.p, h->seg_out.data(), n * 8, cudaMemcpyHostToDevice, h->stream));
+		CU(h, cudaMemcpyAsync(h->d_seg_len.p, h->seg_len.data(), n * 4, cudaMemcpyHostToDevice, h->stream));
+		h->stats.h2d_bytes += n * 20;
+	}
+	return 0;
+}
+
+SelectPlan make_plan(uint32_t k, uint32_t w, size_t max_smem, bool& ok)
+{
+	SelectPlan p;
+	p.H = (k - 1 + 63) & ~63u;
+	p.W8 = ((w + 7) & ~7u) + 8;
+	ok = false;
+	for (uint32_t T : { 4096u, 2048u, 1024u, 512u })
+	{
+		p.T = T;
+		size_t n_pref = pad8(p.H + T + 1) + 1;
+		size_t n_h = T + p.W8;
+		size_t bytes = 2 * n_pref * 8 + n_h * 8 + 2 * (n_h / 8) * 8 + 64;
+		p.smem_bytes = (uint32_t)bytes;
+		// keep at least two CTAs per SM for the default parameters
+		size_t budget = T == 4096 ? max_smem / 2 - 2048 : max_smem - 4096;
+		if (bytes <= budget) { ok = true; break; }
+	}
+	return p;
+}
+
+void tick(mbgfe* h, int i) { cudaEventRecord(h->ev[i], h->stream); }
+float elapsed(mbgfe* h, int a, int b) { float ms = 0; cudaEventElapsedTime(&ms, h->ev[a], h->ev[b]); return ms; }
+
+int read_counter(mbgfe* h, int idx, uint64_t* out)
+{
+	unsigned long long v = 0;
+	CU(h, cudaMemcpyAsync(&v, h->d_counters.as<unsigned long long>() + idx, 8, cudaMemcpyDeviceToHost, h->stream));
+	CU(h, cudaStreamSynchronize(h->stream));
+	h->stats.d2h_bytes += 8;
+	*out = v;
+	return 0;
+}
+
+template <typename T>
+int download(mbgfe* h, std::vector<T>& dst, const DevBuf& src, size_t count, size_t first = 0)
+{
+	dst.resize(count);
+	if (count == 0) return 0;
+	CU(h, cudaMemcpyAsync(dst.data(), src.as<T>() + first, count * sizeof(T), cudaMemcpyDeviceToHost, h->stream));
+	CU(h, cudaStreamSynchronize(h->stream));
+	h->stats.d2h_bytes += count * sizeof(T);
+	return 0;
+}
+
+void clear_results(mbgfe* h)
+{
+	h->processed = false; h->exported_parts = false; h->exported_table = false; h->exported_codes = false; h->have_table = false;
+	h->parts.clear(); h->h_codes.clear(); h->h_poses.clear(); h->h_positions.clear(); h->h_hashes.clear();
+	h->h_node_hashes.clear(); h->h_node_cov.clear(); h->h_node_tip.clear(); h->h_edges.clear();
+	h->n_inst = 0;
+}
+
+// ---------------------------------------------------------------------------------------------- file input
+
+// FASTA / FASTQ reader with the reference's conventions (MBG/fastqloader.h): type by suffix after stripping ".gz",
+// unknown suffix reads nothing; name = header line without its first character and trailing '\r'; FASTA sequence =
+// concatenation of the following non-empty lines; a-z upper-cased.
+int load_file(mbgfe* h, const char* path)
+{
+	std::string name = path;
+	std::string base = name;
+	if (base.size() >= 3 && base.compare(base.size() - 3, 3, ".gz") == 0) base.resize(base.size() - 3);
+	auto ends = [&](const char* suf) { size_t n = strlen(suf); return base.size() >= n && base.compare(base.size() - n, n, suf) == 0; };
+	const bool fastq = ends(".fastq") || ends(".fq");
+	const bool fasta = ends(".fasta") || ends(".fa");
+	gzFile f = gzopen(path, "rb");
+	if (!f) return fail(h, MBGFE_E_IO, "cannot read %s", path);
+	if (!fastq && !fasta) { gzclose(f); return 0; }
+	gzbuffer(f, 1 << 20);
+	auto* bases = new std::vector<char>();
+	auto* offsets = new std::vector<uint64_t>();
+	offsets->push_back(0);
+	std::vector<char> buf(1 << 22);
+	std::string line;
+	bool in_record = false;
+	int fastq_state = 0; // 0 header, 1 sequence, 2 plus, 3 quality
+	auto finish_line = [&]()
+	{
+		if (!line.empty() && line.back() == '\r') line.pop_back();
+		if (fasta)
+		{
+			if (line.empty()) return;
+			if (line[0] == '>')
+			{
+				if (in_record) offsets->push_back(bases->size());
+				h->names.push_back(line.substr(1));
+				in_record = true;
+				return;
+			}
+			if (!in_record) return;
+			for (char c : line) bases->push_back((c >= 'a' && c <= 'z') ? (char)(c - 32) : c);
+		}
+		else
+		{
+			switch (fastq_state)
+			{
+				case 0:
+					if (line.empty() || line[0] != '@') return;
+					h->names.push_back(line.substr(1));
+					fastq_state = 1;
+					return;
+				case 1:
+					for (char c : line) bases->push_back((c >= 'a' && c <= 'z') ? (char)(c - 32) : c);
+					offsets->push_back(bases->size());
+					fastq_state = 2;
+					return;
+				case 2: fastq_state = 3; return;
+				case 3: fastq_state = 0; return;
+			}
+		}
+	};
+	while (true)
+	{
+		int got = gzread(f, buf.data(), (unsigned)buf.size());
+		if (got < 0) { gzclose(f); delete bases; delete offsets; return fail(h, MBGFE_E_IO, "read error in %s", path); }
+		if (got == 0) break;
+		const char* p = buf.data();
+		const char* end = p + got;
+		while (p < end)
+		{
+			const char* nl = (const char*)memchr(p, '\n', end - p);
+			if (!nl) { line.append(p, end - p); break; }
+			line.append(p, nl - p);
+			finish_line();
+			line.clear();
+			p = nl + 1;
+		}
+	}
+	if (!line.empty()) finish_line();
+	if (fasta && in_record) offsets->push_back(bases->size());
+	if (fastq && fastq_state == 1) { h->names.pop_back(); }
+	gzclose(f);
+	h->owned_bases.push_back(bases);
+	h->owned_offsets.push_back(offsets);
+	HostChunk c = { bases->data(), offsets->data(), offsets->size() - 1 };
+	if (c.n_reads) h->pending.push_back(c);
+	return 0;
+}
+
+}
+
+// ====================================================================================================== C ABI
+
+extern "C" {
+
+const char* mbgfe_last_error(const mbgfe* h) { return h ? h->err.c_str() : g_create_error.c_str(); }
+
+int mbgfe_create(const mbgfe_params* prm, mbgfe** out)
+{
+	if (!prm || !out) return fail(nullptr, MBGFE_E_PARAM, "null argument");
+	*out = nullptr;
+	if (prm->abi_version != MBGFE_ABI_VERSION) return fail(nullptr, MBGFE_E_PARAM, "ABI version %u, library has %u", prm->abi_version, MBGFE_ABI_VERSION);
+	// MBG/main.cpp:158-198
+	if (prm->k % 2 == 0) return fail(nullptr, MBGFE_E_PARAM, "k must be odd");
+	if (prm->k < 31) return fail(nullptr, MBGFE_E_PARAM, "k must be at least 31");
+	if (prm->w == 0) return fail(nullptr, MBGFE_E_PARAM, "w must be at least 1");
+	if (prm->w > prm->k - 30) return fail(nullptr, MBGFE_E_PARAM, "w must be at most k-30");
+	if (prm->error_masking > MBGFE_MASK_COLLAPSE_MSAT) return fail(nullptr, MBGFE_E_PARAM, "unknown error masking mode %u", prm->error_masking);
+	if (prm->world == 0 || prm->rank >= prm->world) return fail(nullptr, MBGFE_E_PARAM, "rank %u outside world %u", prm->rank, prm->world);
+	int n_dev = 0;
+	cudaError_t e = cudaGetDeviceCount(&n_dev);
+	if (e != cudaSuccess || n_dev == 0) return fail(nullptr, MBGFE_E_CUDA, "no CUDA device: libmbgfe has no CPU path (%s)", e != cudaSuccess ? cudaGetErrorString(e) : "0 devices");
+	if (prm->device < 0 || prm->device >= n_dev) return fail(nullptr, MBGFE_E_CUDA, "device %d of %d", prm->device, n_dev);
+	mbgfe* h = new mbgfe();
+	h->prm = *prm;
+	memset(&h->stats, 0, sizeof(h->stats));
+	const uint32_t em = prm->error_masking;
+	h->collapse = em == MBGFE_MASK_COLLAPSE || em == MBGFE_MASK_COLLAPSE_DINUC || em == MBGFE_MASK_COLLAPSE_MSAT;
+	h->msat = em == MBGFE_MASK_DINUC || em == MBGFE_MASK_MSAT || em == MBGFE_MASK_COLLAPSE_DINUC || em == MBGFE_MASK_COLLAPSE_MSAT;
+	h->max_motif = (em == MBGFE_MASK_DINUC || em == MBGFE_MASK_COLLAPSE_DINUC) ? 2 : 6;
+	auto bail = [&](int rc) { g_create_error = h->err; mbgfe_destroy(h); return rc; };
+	if (cudaSetDevice(prm->device) != cudaSuccess) return bail(fail(h, MBGFE_E_CUDA, "cudaSetDevice(%d) failed", prm->device));
+	cudaDeviceProp prop;
+	if (cudaGetDeviceProperties(&prop, prm->device) != cudaSuccess) return bail(fail(h, MBGFE_E_CUDA, "cudaGetDeviceProperties failed"));
+	if (prop.major < 10) return bail(fail(h, MBGFE_E_CUDA, "device %s is sm_%d%d; libmbgfe is built for sm_100a only", prop.name, prop.major, prop.minor));
+	h->sm_count = prop.multiProcessorCount;
+	h->max_smem = prop.sharedMemPerBlockOptin;
+	bool ok = false;
+	h->plan = make_plan(prm->k, prm->w, h->max_smem, ok);
+	if (!ok) return bail(fail(h, MBGFE_E_LIMIT, "k=%u needs more shared memory than one SM has (limit about k=9000)", prm->k));
+	if (cudaStreamCreate(&h->stream) != cudaSuccess) return bail(fail(h, MBGFE_E_CUDA, "cudaStreamCreate failed"));
+	for (auto& e2 : h->ev) if (cudaEventCreate(&e2) != cudaSuccess) return bail(fail(h, MBGFE_E_CUDA, "cudaEventCreate failed"));
+	if (ensure(h, h->tab_hash, MAX_CODE * 8) || ensure(h, h->tab_hash_rc, MAX_CODE * 8) || ensure(h, h->tab_comp, MAX_CODE * 2) ||
+		ensure(h, h->d_counters, (CTR_OWNER + prm->world + 8) * 8)) return bail(MBGFE_E_CUDA);
+	MBGFE_LAUNCH(k_build_tables, (MAX_CODE + 255) / 256, 256, 0, h->stream, h->tab_hash.as<uint64_t>(), h->tab_hash_rc.as<uint64_t>(), h->tab_comp.as<uint16_t>());
+	cudaFuncSetAttribute(k_select<NT_SELECT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->plan.smem_bytes);
+	if (cudaStreamSynchronize(h->stream) != cudaSuccess || cudaGetLastError() != cudaSuccess)
+		return bail(fail(h, MBGFE_E_CUDA, "table kernel failed: is this an sm_100 device?"));
+	*out = h;
+	return 0;
+}
+
+void mbgfe_destroy(mbgfe* h)
+{
+	if (!h) return;
+	for (DevBuf* b : { &h->tab_hash, &h->tab_hash_rc, &h->tab_comp, &h->d_ascii, &h->d_packed, &h->d_nonacgt, &h->d_counters, &h->d_seg_in, &h->d_seg_out,
+		&h->d_seg_len, &h->d_seg_c1, &h->d_seg_c2, &h->d_seg_nsel, &h->d_sel_begin, &h->d_sym, &h->d_codes, &h->d_selmask, &h->d_pos1, &h->d_pos2,
+		&h->d_inst_pos, &h->d_inst_seg, &h->d_inst_flag, &h->d_inst_hash, &h->d_inst_slot, &h->d_pal_list, &h->d_nodes, &h->d_edges, &h->d_node_out,
+		&h->d_edge_out, &h->d_records, &h->d_recv }) release(*b);
+	for (auto& e : h->ev) if (e) cudaEventDestroy(e);
+	if (h->stream) cudaStreamDestroy(h->stream);
+	for (auto* v : h->owned_bases) delete v;
+	for (auto* v : h->owned_offsets) delete v;
+	delete h;
+}
+
+void* mbgfe_alloc_pinned(uint64_t bytes)
+{
+	void* p = nullptr;
+	if (cudaMallocHost(&p, bytes) != cudaSuccess) return nullptr;
+	return p;
+}
+
+void mbgfe_free_pinned(void* p) { if (p) cudaFreeHost(p); }
+
+int mbgfe_add_reads(mbgfe* h, const char* bases, const uint64_t* offsets, uint64_t n_reads)
+{
+	if (!h) return MBGFE_E_PARAM;
+	if (n_reads == 0) return 0;
+	if (!bases || !offsets) return fail(h, MBGFE_E_PARAM, "null read buffer");
+	for (uint64_t r = 0; r < n_reads; r++)
+	{
+		if (offsets[r + 1] < offsets[r]) return fail(h, MBGFE_E_PARAM, "offsets must be non-decreasing (read %llu)", (unsigned long long)r);
+		if (offsets[r + 1] - offsets[r] >= (1ull << 29)) return fail(h, MBGFE_E_LIMIT, "read %llu is longer than 2^29-1 bases", (unsigned long long)r);
+	}
+	HostChunk c = { bases, offsets, n_reads };
+	h->pending.push_back(c);
+	return 0;
+}
+
+int mbgfe_add_file(mbgfe* h, const char* path)
+{
+	if (!h || !path) return MBGFE_E_PARAM;
+	// names are indexed by read; reads added without names before this file get empty names
+	uint64_t have = 0;
+	for (auto& c : h->pending) have += c.n_reads;
+	if (h->names.size() < have) h->names.resize(have);
+	return load_file(h, path);
+}
+
+const char* mbgfe_read_name(const mbgfe* h, uint64_t read_idx)
+{
+	if (!h || read_idx >= h->names.size()) return "";
+	return h->names[read_idx].c_str();
+}
+
+int mbgfe_reset(mbgfe* h)
+{
+	if (!h) return MBGFE_E_PARAM;
+	h->pending.clear();
+	h->names.clear();
+	for (auto* v : h->owned_bases) delete v;
+	for (auto* v : h->owned_offsets) delete v;
+	h->owned_bases.clear(); h->owned_offsets.clear();
+	h->resident = false;
+	h->n_reads = 0; h->n_bases = 0;
+	clear_results(h);
+	return 0;
+}
+
+int mbgfe_upload(mbgfe* h)
+{
+	if (!h) return MBGFE_E_PARAM;
+	clear_results(h);
+	h->resident = false;
+	h->stats.h2d_bytes = 0; h->stats.d2h_bytes = 0;
+	uint64_t n_reads = 0, n_bases = 0;
+	for (auto& c : h->pending) { n_reads += c.n_reads; n_bases += c.offsets[c.n_reads] - c.offsets[0]; }
+	if (n_reads >= (1ull << 32)) return fail(h, MBGFE_E_LIMIT, "more than 2^32-1 reads in one batch");
+	h->n_reads = n_reads; h->n_bases = n_bases;
+	h->read_off.resize(n_reads + 1);
+	std::vector<const char*> read_ptr(n_reads);
+	if (int rc = ensure(h, h->d_ascii, n_bases + 64)) return rc;
+	if (int rc = ensure(h, h->d_packed, n_bases / 4 + 64)) return rc;
+	const uint64_t bad_cap = std::max<uint64_t>(1 << 20, n_bases / 16);
+	if (int rc = ensure(h, h->d_nonacgt, bad_cap * 8)) return rc;
+	tick(h, 0);
+	CU(h, cudaMemsetAsync(h->d_counters.p, 0, h->d_counters.cap, h->stream));
+	uint64_t pos = 0, r = 0;
+	for (auto& c : h->pending)
+	{
+		const uint64_t first = c.offsets[0], bytes = c.offsets[c.n_reads] - first;
+		if (bytes) CU(h, cudaMemcpyAsync(h->d_ascii.as<char>() + pos, c.bases + first, bytes, cudaMemcpyHostToDevice, h->stream));
+		for (uint64_t i = 0; i < c.n_reads; i++, r++) { h->read_off[r] = pos + (c.offsets[i] - first); read_ptr[r] = c.bases + c.offsets[i]; }
+		pos += bytes;
+	}
+	h->read_off[n_reads] = pos;
+	h->stats.h2d_bytes += n_bases;
+	tick(h, 1);
+	if (n_bases)
+	{
+		const uint64_t chunks = (n_bases + 15) / 16;
+		const unsigned grid = (unsigned)std::min<uint64_t>((chunks + 255) / 256, (uint64_t)h->sm_count * 16);
+		MBGFE_LAUNCH(k_pack_ascii, grid, 256, 0, h->stream, (const uint4*)h->d_ascii.p, n_bases, h->d_packed.as<uint32_t>(), h->d_nonacgt.as<uint64_t>(),
+			h->d_counters.as<unsigned long long>() + CTR_NONACGT, bad_cap);
+	}
+	tick(h, 2);
+	uint64_t n_bad = 0;
+	if (int rc = read_counter(h, CTR_NONACGT, &n_bad)) return rc;
+	CU(h, cudaGetLastError());
+	if (n_bad > bad_cap) return fail(h, MBGFE_E_LIMIT, "%llu characters outside ACGT in %llu bases: more than 1 in 16", (unsigned long long)n_bad, (unsigned long long)n_bases);
+	std::vector<uint64_t> bad;
+	if (n_bad) { if (int rc = download(h, bad, h->d_nonacgt, n_bad)) return rc; std::sort(bad.begin(), bad.end()); }
+	h->nonacgt_count = n_bad;
+	build_segments(h, bad, read_ptr);
+	if (int rc = upload_segments(h)) return rc;
+	CU(h, cudaStreamSynchronize(h->stream));
+	h->stats.ms_upload = elapsed(h, 0, 1);
+	h->stats.ms_pack = elapsed(h, 1, 2);
+	h->stats.reads = n_reads; h->stats.raw_bases = n_bases; h->stats.segments = h->seg_len.size(); h->stats.nonacgt = n_bad;
+	h->pending.clear();
+	h->resident = true;
+	return 0;
+}
+
+int mbgfe_process(mbgfe* h)
+{
+	if (!h) return MBGFE_E_PARAM;
+	if (!h->resident) return fail(h, MBGFE_E_STATE, "mbgfe_process before mbgfe_upload");
+	clear_results(h);
+	const uint32_t k = h->prm.k, w = h->prm.w;
+	const uint32_t n_seg = (uint32_t)h->seg_len.size();
+	const bool want_poses = (h->prm.flags & MBGFE_KEEP_POSES) != 0;
+	const bool need_pos1 = want_poses && !h->collapse;
+	uint32_t launches = 0;
+	const uint64_t tot = h->total_out;
+	if (int rc = ensure(h, h->d_sym, tot / 4 + 64)) return rc;
+	if (int rc = ensure(h, h->d_codes, tot * 2 + 64)) return rc;
+	if (int rc = ensure(h, h->d_selmask, tot / 8 + 64)) return rc;
+	if (need_pos1) if (int rc = ensure(h, h->d_pos1, tot * 4 + 64)) return rc;
+	if (want_poses) if (int rc = ensure(h, h->d_pos2, tot * 4 + 64)) return rc;
+	unsigned long long* ctr = h->d_counters.as<unsigned long long>();
+	CU(h, cudaMemsetAsync(ctr + CTR_PALINDROME, 0, (CTR_OWNER + h->prm.world - CTR_PALINDROME) * 8, h->stream));
+	const SegTable st = seg_table(h);
+	uint32_t* pos1 = need_pos1 ? h->d_pos1.as<uint32_t>() : nullptr;
+	uint32_t* pos2 = want_poses ? h->d_pos2.as<uint32_t>() : nullptr;
+	tick(h, 3);
+	if (n_seg)
+	{
+		MBGFE_LAUNCH(k_collapse<NT_COLLAPSE>, n_seg, NT_COLLAPSE, 0, h->stream, st, h->d_packed.as<uint64_t>(), h->d_sym.as<uint64_t>(), h->d_seg_c1.as<uint32_t>(), pos1,
+			h->prm.error_masking == MBGFE_MASK_NO ? 1 : 0);
+		launches++;
+	}
+	tick(h, 4);
+	if (n_seg)
+	{
+		if (h->msat)
+			MBGFE_LAUNCH(k_msat<NT_MSAT>, n_seg, NT_MSAT, 0, h->stream, st, h->d_sym.as<uint64_t>(), h->d_seg_c1.as<uint32_t>(), h->d_codes.as<uint16_t>(), h->d_seg_c2.as<uint32_t>(),
+				(const uint32_t*)pos1, pos2, h->max_motif);
+		else
+			MBGFE_LAUNCH(k_unpack_symbols<NT_MSAT>, n_seg, NT_MSAT, 0, h->stream, st, h->d_sym.as<uint64_t>(), h->d_seg_c1.as<uint32_t>(), h->d_codes.as<uint16_t>(),
+				h->d_seg_c2.as<uint32_t>(), (const uint32_t*)pos1, pos2);
+		launches++;
+	}
+	tick(h, 5);
+	if (n_seg)
+	{
+		MBGFE_LAUNCH(k_select<NT_SELECT>, n_seg, NT_SELECT, h->plan.smem_bytes, h->stream, st, h->d_codes.as<uint16_t>(), h->d_seg_c2.as<uint32_t>(), h->tab_hash.as<uint64_t>(),
+			h->tab_hash_rc.as<uint64_t>(), h->d_selmask.as<uint8_t>(), h->d_seg_nsel.as<uint32_t>(), k, w, h->plan);
+		launches++;
+	}
+	MBGFE_LAUNCH(k_scan_u32<1024>, 1, 1024, 0, h->stream, h->d_seg_nsel.as<uint32_t>(), h->d_sel_begin.as<uint64_t>(), n_seg);
+	launches++;
+	tick(h, 6);
+	uint64_t n_inst = 0;
+	CU(h, cudaMemcpyAsync(&n_inst, h->d_sel_begin.as<uint64_t>() + n_seg, 8, cudaMemcpyDeviceToHost, h->stream));
+	CU(h, cudaStreamSynchronize(h->stream));
+	CU(h, cudaGetLastError());
+	h->stats.d2h_bytes += 8;
+	h->n_inst = n_inst;
+	if (int rc = ensure(h, h->d_inst_pos, n_inst * 4 + 64)) return rc;
+	if (int rc = ensure(h, h->d_inst_seg, n_inst * 4 + 64)) return rc;
+	if (int rc = ensure(h, h->d_inst_flag, n_inst + 64)) return rc;
+	if (int rc = ensure(h, h->d_inst_hash, n_inst * 16 + 64)) return rc;
+	if (int rc = ensure(h, h->d_inst_slot, n_inst * 4 + 64)) return rc;
+	const uint64_t pal_cap = 1 << 16;
+	if (int rc = ensure(h, h->d_pal_list, pal_cap * 8)) return rc;
+	if (n_inst)
+	{
+		MBGFE_LAUNCH(k_list_selected<NT_LIST>, n_seg, NT_LIST, 0, h->stream, st, h->d_selmask.as<uint32_t>(), h->d_seg_c2.as<uint32_t>(), h->d_seg_nsel.as<uint32_t>(),
+			h->d_sel_begin.as<uint64_t>(), h->d_inst_pos.as<uint32_t>(), h->d_inst_seg.as<uint32_t>(), h->d_inst_flag.as<uint8_t>(), k);
+		MBGFE_LAUNCH(k_kmer_hash, (unsigned)((2 * n_inst + 255) / 256), 256, 0, h->stream, h->d_seg_out.as<uint64_t>(), h->d_codes.as<uint16_t>(), h->tab_comp.as<uint16_t>(),
+			h->d_inst_pos.as<uint32_t>(), h->d_inst_seg.as<uint32_t>(), n_inst, h->d_inst_hash.as<uint64_t>(), k);
+		MBGFE_LAUNCH(k_find_palindromes, (unsigned)((n_inst + 255) / 256), 256, 0, h->stream, h->d_inst_hash.as<uint64_t>(), n_inst, ctr + CTR_PALINDROME,
+			h->d_pal_list.as<uint64_t>(), pal_cap);
+		launches += 3;
+	}
+	tick(h, 7);
+	uint64_t n_pal = 0;
+	if (int rc = read_counter(h, CTR_PALINDROME, &n_pal)) return rc;
+	if (n_pal)
+	{
+		// MBG/ReadHelper.h:755-785.  Not implemented yet on the device side: report instead of producing a wrong table.
+		return fail(h, MBGFE_E_PALINDROME, "%llu selected k-mers hash identically in both directions (palindromic k-mer); try a different -w", (unsigned long long)n_pal);
+	}
+	h->stats.distinct = 0; h->stats.distinct_edges = 0;
+	if (!(h->prm.flags & MBGFE_NO_TABLE))
+	{
+		const uint64_t slots = std::max<uint64_t>(next_pow2(std::max<uint64_t>(2 * n_inst, 1024)), h->prm.table_slots ? next_pow2(h->prm.table_slots) : 0);
+		if (slots >= (1ull << 31)) return fail(h, MBGFE_E_LIMIT, "node table would need %llu slots (limit 2^31 per GPU)", (unsigned long long)slots);
+		if (int rc = ensure(h, h->d_nodes, slots * sizeof(NodeSlot))) return rc;
+		h->node_slots = slots;
+		const unsigned clear_grid = (unsigned)std::min<uint64_t>((slots + 255) / 256, (uint64_t)h->sm_count * 8);
+		MBGFE_LAUNCH(k_table_clear, clear_grid, 256, 0, h->stream, h->d_nodes.as<NodeSlot>(), slots);
+		launches++;
+		if (n_inst)
+		{
+			MBGFE_LAUNCH(k_insert_nodes, (unsigned)((n_inst + 255) / 256), 256, 0, h->stream, h->d_inst_hash.as<uint64_t>(), h->d_inst_flag.as<uint8_t>(), n_inst,
+				h->d_nodes.as<NodeSlot>(), slots - 1, h->d_inst_slot.as<uint32_t>(), ctr + CTR_DISTINCT);
+			launches++;
+		}
+		tick(h, 8);
+		if (!(h->prm.flags & MBGFE_NO_EDGES))
+		{
+			if (int rc = ensure(h, h->d_edges, slots * sizeof(EdgeSlot))) return rc;
+			h->edge_slots = slots;
+			MBGFE_LAUNCH(k_edge_clear, clear_grid, 256, 0, h->stream, h->d_edges.as<EdgeSlot>(), slots);
+			launches++;
+			if (n_inst)
+			{
+				MBGFE_LAUNCH(k_insert_edges, (unsigned)((n_inst + 255) / 256), 256, 0, h->stream, h->d_inst_hash.as<uint64_t>(), h->d_inst_pos.as<uint32_t>(),
+					h->d_inst_flag.as<uint8_t>(), h->d_inst_slot.as<uint32_t>(), n_inst, h->d_edges.as<EdgeSlot>(), slots - 1, ctr + CTR_EDGES, k);
+				launches++;
+			}
+		}
+		else h->edge_slots = 0;
+		tick(h, 9);
+		unsigned long long two[2] = { 0, 0 };
+		CU(h, cudaMemcpyAsync(two, ctr + CTR_DISTINCT, 16, cudaMemcpyDeviceToHost, h->stream));
+		CU(h, cudaStreamSynchronize(h->stream));
+		h->stats.d2h_bytes += 16;
+		h->stats.distinct = two[0]; h->stats.distinct_edges = two[1];
+		h->stats.table_slots = slots;
+		h->have_table = true;
+	}
+	else { tick(h, 8); tick(h, 9); CU(h, cudaStreamSynchronize(h->stream)); }
+	CU(h, cudaGetLastError());
+	h->stats.ms_collapse = elapsed(h, 3, 4);
+	h->stats.ms_msat = elapsed(h, 4, 5);
+	h->stats.ms_select = elapsed(h, 5, 6);
+	h->stats.ms_hash = elapsed(h, 6, 7);
+	h->stats.ms_nodes = elapsed(h, 7, 8);
+	h->stats.ms_edges = elapsed(h, 8, 9);
+	h->stats.ms_process = elapsed(h, 3, 9);
+	h->stats.selected = n_inst;
+	h->stats.launches = launches;
+	h->processed = true;
+	return 0;
+}
+
+int mbgfe_run(mbgfe* h)
+{
+	if (int rc = mbgfe_upload(h)) return rc;
+	return mbgfe_process(h);
+}
+
+}
+
+namespace {
+
+// part table: per-segment results -> reference-shaped parts (MBG/ReadHelper.h:81-88, 838-862, 976-977, 1058-1059)
+int export_parts(mbgfe* h)
+{
+	if (h->exported_parts) return 0;
+	const size_t n_seg = h->seg_len.size();
+	if (int rc = download(h, h->h_seg_c1, h->d_seg_c1, n_seg)) return rc;
+	if (int rc = download(h, h->h_seg_c2, h->d_seg_c2, n_seg)) return rc;
+	if (int rc = download(h, h->h_seg_nsel, h->d_seg_nsel, n_seg)) return rc;
+	if (int rc = download(h, h->h_sel_begin, h->d_sel_begin, n_seg + 1)) return rc;
+	h->parts.clear();
+	uint64_t code_cursor = 0, pose_cursor = 0, c1_total = 0, hashed = 0;
+	uint32_t cur_read = 0xffffffffu, collapsed_before = 0;
+	const uint32_t em = h->prm.error_masking;
+	for (size_t g = 0; g < n_seg; g++)
+	{
+		if (h->seg_read[g] != cur_read) { cur_read = h->seg_read[g]; collapsed_before = 0; }
+		const uint32_t c1 = h->h_seg_c1[g], c2 = h->h_seg_c2[g];
+		c1_total += c1;
+		uint32_t offset;
+		if (h->collapse) offset = collapsed_before + h->seg_nonacgt_before[g];
+		else if (em == MBGFE_MASK_NO) offset = h->seg_rawoff[g] == 0 ? 0 : h->seg_rawoff[g] - 1; // index of the last non-ACGT character in front (MBG/ReadHelper.h:1064)
+		else offset = h->seg_rawoff[g];
+		collapsed_before += c1;
+		if (c2 == 0) continue; // microsatellite modes drop stretches with fewer than 32 symbols
+		mbgfe_part p;
+		p.read_idx = h->seg_read[g];
+		p.part_offset = offset;
+		p.raw_len = (uint32_t)(h->read_off[p.read_idx + 1] - h->read_off[p.read_idx]);
+		p.n_codes = c2;
+		p.code_begin = code_cursor;
+		p.pose_begin = pose_cursor;
+		p.sel_begin = h->h_sel_begin[g];
+		p.n_sel = h->h_seg_nsel[g];
+		p.hashed = c2 >= h->prm.k ? 1 : 0;
+		hashed += p.hashed;
+		code_cursor += c2;
+		pose_cursor += c2 + 1;
+		h->parts.push_back(p);
+	}
+	h->stats.collapsed_symbols = c1_total;
+	h->stats.codes = code_cursor;
+	h->stats.parts = h->parts.size();
+	h->stats.hashed_parts = hashed;
+	h->exported_parts = true;
+	return 0;
+}
+
+int export_codes(mbgfe* h)
+{
+	if (h->exported_codes) return 0;
+	if (int rc = export_parts(h)) return rc;
+	const bool want_poses = (h->prm.flags & MBGFE_KEEP_POSES) != 0;
+	std::vector<uint16_t> all;
+	std::vector<uint32_t> allp;
+	if (int rc = download(h, all, h->d_codes, h->total_out)) return rc;
+	if (want_poses) if (int rc = download(h, allp, h->d_pos2, h->total_out)) return rc;
+	h->h_codes.resize(h->stats.codes);
+	h->h_poses.resize(want_poses ? h->stats.codes + h->parts.size() : 0);
+	size_t pi = 0;
+	for (size_t g = 0; g < h->seg_len.size(); g++)
+	{
+		const uint32_t c2 = h->h_seg_c2[g];
+		if (c2 == 0) continue;
+		const mbgfe_part& p = h->parts[pi++];
+		memcpy(h->h_codes.data() + p.code_begin, all.data() + h->seg_out[g], (size_t)c2 * 2);
+		if (want_poses)
+		{
+			// device poses are relative to the stretch; the reference reports positions in the (collapsed) read
+			const uint32_t base = h->collapse ? p.part_offset : h->seg_rawoff[g];
+			for (uint32_t i = 0; i <= c2; i++) h->h_poses[p.pose_begin + i] = allp[h->seg_out[g] + i] + base;
+		}
+	}
+	h->exported_codes = true;
+	return 0;
+}
+
+int export_instances(mbgfe* h)
+{
+	if (h->h_positions.size() == h->n_inst && h->h_hashes.size() == h->n_inst) return 0;
+	if (int rc = download(h, h->h_positions, h->d_inst_pos, h->n_inst)) return rc;
+	std::vector<uint64_t> raw;
+	if (int rc = download(h, raw, h->d_inst_hash, 2 * h->n_inst)) return rc;
+	h->h_hashes.resize(h->n_inst);
+	if (h->n_inst) memcpy(h->h_hashes.data(), raw.data(), h->n_inst * 16);
+	return 0;
+}
+
+// HashList::sortByHash (MBG/HashList.cpp:245-353): ids = ranks of the canonical hashes; edges re-canonicalised with
+// those ids (already canonical: the device compared the hashes themselves), listed per node forward side first.
+int export_table(mbgfe* h)
+{
+	if (h->exported_table) return 0;
+	if (!h->have_table) return fail(h, MBGFE_E_STATE, "table requested but none was built (MBGFE_NO_TABLE without mbgfe_exchange_insert)");
+	tick(h, 10);
+	unsigned long long* ctr = h->d_counters.as<unsigned long long>();
+	const uint64_t n_nodes = h->stats.distinct, n_edges = h->stats.distinct_edges;
+	if (int rc = ensure(h, h->d_node_out, (n_nodes + 1) * sizeof(NodeOut))) return rc;
+	if (int rc = ensure(h, h->d_edge_out, (n_edges + 1) * sizeof(EdgeOut))) return rc;
+	CU(h, cudaMemsetAsync(ctr + CTR_CURSOR, 0, 16, h->stream));
+	const unsigned grid = (unsigned)std::min<uint64_t>((h->node_slots + 255) / 256, (uint64_t)h->sm_count * 8);
+	MBGFE_LAUNCH(k_export_nodes, grid, 256, 0, h->stream, h->d_nodes.as<NodeSlot>(), h->node_slots, h->d_node_out.as<NodeOut>(), ctr + CTR_CURSOR);
+	if (h->edge_slots) MBGFE_LAUNCH(k_export_edges, grid, 256, 0, h->stream, h->d_edges.as<EdgeSlot>(), h->edge_slots, h->d_edge_out.as<EdgeOut>(), ctr + CTR_CURSOR + 1);
+	std::vector<NodeOut> nodes;
+	std::vector<EdgeOut> edges;
+	if (int rc = download(h, nodes, h->d_node_out, n_nodes)) return rc;
+	if (h->edge_slots) if (int rc = download(h, edges, h->d_edge_out, n_edges)) return rc;
+	CU(h, cudaGetLastError());
+	std::sort(nodes.begin(), nodes.end(), [](const NodeOut& x, const NodeOut& y) { return x.key_hi != y.key_hi ? x.key_hi < y.key_hi : x.key_lo < y.key_lo; });
+	const uint32_t min_cov = 0; // the raw table; -a filtering is applied by the consumers (getCoveredEdges etc.)
+	(void)min_cov;
+	h->h_node_hashes.resize(n_nodes); h->h_node_cov.resize(n_nodes); h->h_node_tip.resize(n_nodes);
+	std::vector<uint32_t> rank_of_slot;
+	rank_of_slot.assign(h->node_slots, 0xffffffffu);
+	for (size_t i = 0; i < n_nodes; i++)
+	{
+		h->h_node_hashes[i].lo = nodes[i].key_lo; h->h_node_hashes[i].hi = nodes[i].key_hi;
+		h->h_node_cov[i] = nodes[i].count;
+		h->h_node_tip[i] = (uint8_t)(nodes[i].flags & 1);
+		rank_of_slot[nodes[i].slot] = (uint32_t)i;
+	}
+	h->h_edges.resize(edges.size());
+	for (size_t i = 0; i < edges.size(); i++)
+	{
+		const uint32_t a = (uint32_t)(edges[i].key >> 32), b = (uint32_t)edges[i].key;
+		mbgfe_edge e;
+		e.from = rank_of_slot[a >> 1]; e.from_fw = a & 1;
+		e.to = rank_of_slot[b >> 1]; e.to_fw = b & 1;
+		e.coverage = edges[i].count;
+		e.overlap = (uint32_t)(edges[i].ordered & 0xffffff);
+		h->h_edges[i] = e;
+	}
+	std::sort(h->h_edges.begin(), h->h_edges.end(), [](const mbgfe_edge& x, const mbgfe_edge& y)
+	{
+		if (x.from != y.from) return x.from < y.from;
+		if (x.from_fw != y.from_fw) return x.from_fw > y.from_fw;
+		if (x.to != y.to) return x.to < y.to;
+		return x.to_fw < y.to_fw;
+	});
+	tick(h, 11);
+	CU(h, cudaStreamSynchronize(h->stream));
+	h->stats.ms_export = elapsed(h, 10, 11);
+	h->exported_table = true;
+	return 0;
+}
+
+}
+
+extern "C" {
+
+uint64_t mbgfe_count(mbgfe* h, int what)
+{
+	if (!h || !h->processed) return 0;
+	switch (what)
+	{
+		case MBGFE_PARTS: if (export_parts(h)) return 0; return h->parts.size();
+		case MBGFE_CODES: if (export_parts(h)) return 0; return (h->prm.flags & MBGFE_KEEP_CODES) ? h->stats.codes : 0;
+		case MBGFE_POSES: if (export_parts(h)) return 0; return (h->prm.flags & MBGFE_KEEP_POSES) ? h->stats.codes + h->parts.size() : 0;
+		case MBGFE_POSITIONS: case MBGFE_HASHES: return h->n_inst;
+		case MBGFE_NODE_HASHES: case MBGFE_NODE_COVERAGE: case MBGFE_NODE_TIP: return h->have_table ? h->stats.distinct : 0;
+		case MBGFE_EDGES: return h->have_table ? h->stats.distinct_edges : 0;
+	}
+	return 0;
+}
+
+const void* mbgfe_data(mbgfe* h, int what)
+{
+	if (!h) return nullptr;
+	if (!h->processed) { fail(h, MBGFE_E_STATE, "results requested before mbgfe_process"); return nullptr; }
+	switch (what)
+	{
+		case MBGFE_PARTS: if (export_parts(h)) return nullptr; return h->parts.data();
+		case MBGFE_CODES:
+			if (!(h->prm.flags & MBGFE_KEEP_CODES)) { fail(h, MBGFE_E_STATE, "codes requested without MBGFE_KEEP_CODES"); return nullptr; }
+			if (export_codes(h)) return nullptr; return h->h_codes.data();
+		case MBGFE_POSES:
+			if (!(h->prm.flags & MBGFE_KEEP_POSES)) { fail(h, MBGFE_E_STATE, "poses requested without MBGFE_KEEP_POSES"); return nullptr; }
+			if (export_codes(h)) return nullptr; return h->h_poses.data();
+		case MBGFE_POSITIONS: if (export_instances(h)) return nullptr; return h->h_positions.data();
+		case MBGFE_HASHES: if (export_instances(h)) return nullptr; return h->h_hashes.data();
+		case MBGFE_NODE_HASHES: if (export_table(h)) return nullptr; return h->h_node_hashes.data();
+		case MBGFE_NODE_COVERAGE: if (export_table(h)) return nullptr; return h->h_node_cov.data();
+		case MBGFE_NODE_TIP: if (export_table(h)) return nullptr; return h->h_node_tip.data();
+		case MBGFE_EDGES: if (export_table(h)) return nullptr; return h->h_edges.data();
+	}
+	fail(h, MBGFE_E_PARAM, "unknown result array %d", what);
+	return nullptr;
+}
+
+int mbgfe_get_stats(const mbgfe* h, mbgfe_stats* out)
+{
+	if (!h || !out) return MBGFE_E_PARAM;
+	*out = h->stats;
+	return 0;
+}
+
+int mbgfe_timer_start(mbgfe* h)
+{
+	if (!h) return MBGFE_E_PARAM;
+	CU(h, cudaEventRecord(h->ev[14], h->stream));
+	return 0;
+}
+
+int mbgfe_timer_stop(mbgfe* h, float* ms)
+{
+	if (!h || !ms) return MBGFE_E_PARAM;
+	CU(h, cudaEventRecord(h->ev[15], h->stream));
+	CU(h, cudaEventSynchronize(h->ev[15]));
+	CU(h, cudaEventElapsedTime(ms, h->ev[14], h->ev[15]));
+	return 0;
+}
+
+int mbgfe_exchange_counts(mbgfe* h, uint64_t* send_counts)
+{
+	if (!h || !send_counts) return MBGFE_E_PARAM;
+	if (!h->processed) return fail(h, MBGFE_E_STATE, "exchange before mbgfe_process");
+	unsigned long long* ctr = h->d_counters.as<unsigned long long>();
+	const uint32_t world = h->prm.world;
+	CU(h, cudaMemsetAsync(ctr + CTR_OWNER, 0, world * 8, h->stream));
+	if (h->n_inst) MBGFE_LAUNCH(k_owner_count, (unsigned)((h->n_inst + 255) / 256), 256, 0, h->stream, h->d_inst_hash.as<uint64_t>(), h->n_inst, world, ctr + CTR_OWNER);
+	std::vector<unsigned long long> c(world);
+	CU(h, cudaMemcpyAsync(c.data(), ctr + CTR_OWNER, world * 8, cudaMemcpyDeviceToHost, h->stream));
+	CU(h, cudaStreamSynchronize(h->stream));
+	for (uint32_t i = 0; i < world; i++) send_counts[i] = c[i];
+	return 0;
+}
+
+int mbgfe_exchange_pack(mbgfe* h, void** device_records)
+{
+	if (!h || !device_records) return MBGFE_E_PARAM;
+	if (!h->processed) return fail(h, MBGFE_E_STATE, "exchange before mbgfe_process");
+	const uint32_t world = h->prm.world;
+	std::vector<uint64_t> counts(world);
+	if (int rc = mbgfe_exchange_counts(h, counts.data())) return rc;
+	std::vector<unsigned long long> cursors(world);
+	uint64_t total = 0;
+	for (uint32_t i = 0; i < world; i++) { cursors[i] = total; total += counts[i]; }
+	if (int rc = ensure(h, h->d_records, (total + 1) * 32)) return rc;
+	unsigned long long* ctr = h->d_counters.as<unsigned long long>();
+	CU(h, cudaMemcpyAsync(ctr + CTR_OWNER, cursors.data(), world * 8, cudaMemcpyHostToDevice, h->stream));
+	if (h->n_inst) MBGFE_LAUNCH(k_owner_pack, (unsigned)((h->n_inst + 255) / 256), 256, 0, h->stream, h->d_inst_hash.as<uint64_t>(), h->d_inst_flag.as<uint8_t>(), h->n_inst, world,
+		ctr + CTR_OWNER, h->d_records.as<uint64_t>());
+	CU(h, cudaStreamSynchronize(h->stream));
+	CU(h, cudaGetLastError());
+	*device_records = h->d_records.p;
+	return 0;
+}
+
+int mbgfe_exchange_reserve(mbgfe* h, uint64_t n_records, void** device_recv)
+{
+	if (!h || !device_recv) return MBGFE_E_PARAM;
+	if (int rc = ensure(h, h->d_recv, (n_records + 1) * 32)) return rc;
+	*device_recv = h->d_recv.p;
+	return 0;
+}
+
+int mbgfe_exchange_insert(mbgfe* h, const void* device_records, uint64_t n_records)
+{
+	if (!h) return MBGFE_E_PARAM;
+	unsigned long long* ctr = h->d_counters.as<unsigned long long>();
+	const uint64_t slots = next_pow2(std::max<uint64_t>(2 * n_records, 1024));
+	if (slots >= (1ull << 31)) return fail(h, MBGFE_E_LIMIT, "node table would need %llu slots (limit 2^31 per GPU)", (unsigned long long)slots);
+	if (int rc = ensure(h, h->d_nodes, slots * sizeof(NodeSlot))) return rc;
+	h->node_slots = slots; h->edge_slots = 0;
+	CU(h, cudaMemsetAsync(ctr + CTR_DISTINCT, 0, 16, h->stream));
+	tick(h, 12);
+	const unsigned clear_grid = (unsigned)std::min<uint64_t>((slots + 255) / 256, (uint64_t)h->sm_count * 8);
+	MBGFE_LAUNCH(k_table_clear, clear_grid, 256, 0, h->stream, h->d_nodes.as<NodeSlot>(), slots);
+	if (n_records) MBGFE_LAUNCH(k_insert_records, (unsigned)((n_records + 255) / 256), 256, 0, h->stream, (const uint64_t*)device_records, n_records, h->d_nodes.as<NodeSlot>(), slots - 1,
+		ctr + CTR_DISTINCT);
+	tick(h, 13);
+	uint64_t d = 0;
+	if (int rc = read_counter(h, CTR_DISTINCT, &d)) return rc;
+	CU(h, cudaGetLastError());
+	h->stats.distinct = d; h->stats.distinct_edges = 0; h->stats.table_slots = slots;
+	h->stats.ms_nodes = elapsed(h, 12, 13);
+	h->exported_table = false;
+	h->have_table = true;
+	return 0;
+}
+
+int mbgfe_kat_tables(mbgfe* h, uint64_t* char_hash_30948, uint16_t* complement_30948)
+{
+	if (!h) return MBGFE_E_PARAM;
+	if (char_hash_30948) CU(h, cudaMemcpy(char_hash_30948, h->tab_hash.p, MAX_CODE * 8, cudaMemcpyDeviceToHost));
+	if (complement_30948) CU(h, cudaMemcpy(complement_30948, h->tab_comp.p, MAX_CODE * 2, cudaMemcpyDeviceToHost));
+	return 0;
+}
+
+int mbgfe_kat_kmer_hash(mbgfe* h, const uint16_t* codes, uint32_t k, mbgfe_hash128* out)
+{
+	if (!h || !codes || !out) return MBGFE_E_PARAM;
+	DevBuf d_codes, d_misc;
+	if (int rc = ensure(h, d_codes, (size_t)k * 2 + 64)) return rc;
+	if (int rc = ensure(h, d_misc, 64)) { release(d_codes); return rc; }
+	// one synthetic instance: segment 0 at out_base 0, position 0
+	uint64_t zero64 = 0; uint32_t zero32 = 0;
+	cudaMemcpy(d_codes.p, codes, (size_t)k * 2, cudaMemcpyHostToDevice);
+	cudaMemcpy(d_misc.as<char>() + 0, &zero64, 8, cudaMemcpyHostToDevice);   // seg_out_base[0]
+	cudaMemcpy(d_misc.as<char>() + 8, &zero32, 4, cudaMemcpyHostToDevice);   // inst_pos[0]
+	cudaMemcpy(d_misc.as<char>() + 12, &zero32, 4, cudaMemcpyHostToDevice);  // inst_seg[0]
+	MBGFE_LAUNCH(k_kmer_hash, 1, 256, 0, h->stream, (const uint64_t*)d_misc.p, d_codes.as<uint16_t>(), h->tab_comp.as<uint16_t>(), (const uint32_t*)(d_misc.as<char>() + 8),
+		(const uint32_t*)(d_misc.as<char>() + 12), (uint64_t)1, (uint64_t*)(d_misc.as<char>() + 16), k);
+	cudaStreamSynchronize(h->stream);
+	uint64_t res[2] = { 0, 0 };
+	cudaError_t e = cudaMemcpy(res, d_misc.as<char>() + 16, 16, cudaMemcpyDeviceToHost);
+	release(d_codes); release(d_misc);
+	if (e != cudaSuccess) return fail(h, MBGFE_E_CUDA, "kat kernel failed: %s", cudaGetErrorString(e));
+	out->lo = res[0]; out->hi = res[1];
+	return 0;
+}
+
+}

@@ -1,0 +1,267 @@
+"""ctypes mirror of include/mbgfe.h.
+
+Mirrors the reference seam ``ReadpartIterator`` + ``loadReadsAsHashesMultithread`` (MBG/ReadHelper.h:162-241,
+MBG/MBG.cpp:44-76): construct with (k, w, error masking), add reads, run, read the per-part arrays and the table.
+The library is CUDA only; loading or creating a handle fails loudly when the extension or the GPU is missing.
+"""
+import ctypes as C
+import os
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+MODES = {"no": 0, "hpc": 1, "collapse": 2, "dinuc": 3, "msat": 4, "collapse-dinuc": 5, "collapse-msat": 6}
+
+KEEP_CODES, KEEP_POSES, NO_TABLE, NO_EDGES = 1, 2, 4, 8
+PARTS, CODES, POSES, POSITIONS, HASHES, NODE_HASHES, NODE_COVERAGE, NODE_TIP, EDGES = range(9)
+
+PART_DTYPE = np.dtype([
+    ("read_idx", "<u4"), ("part_offset", "<u4"), ("raw_len", "<u4"), ("n_codes", "<u4"),
+    ("code_begin", "<u8"), ("pose_begin", "<u8"), ("sel_begin", "<u8"), ("n_sel", "<u4"), ("hashed", "<u4")])
+
+
+class Params(C.Structure):
+    _fields_ = [("abi_version", C.c_uint32), ("k", C.c_uint32), ("w", C.c_uint32), ("error_masking", C.c_uint32),
+                ("kmer_abundance", C.c_uint32), ("flags", C.c_uint32), ("device", C.c_int32), ("rank", C.c_uint32),
+                ("world", C.c_uint32), ("reserved", C.c_uint32), ("table_slots", C.c_uint64)]
+
+
+class Stats(C.Structure):
+    _fields_ = [(n, C.c_uint64) for n in (
+        "reads", "raw_bases", "segments", "collapsed_symbols", "codes", "parts", "hashed_parts", "selected", "distinct",
+        "distinct_edges", "table_slots", "table_grows", "nonacgt", "h2d_bytes", "d2h_bytes")] + [(n, C.c_float) for n in (
+        "ms_upload", "ms_pack", "ms_collapse", "ms_msat", "ms_select", "ms_hash", "ms_nodes", "ms_edges", "ms_process",
+        "ms_export")] + [("launches", C.c_uint32), ("reserved", C.c_uint32)]
+
+
+class MbgfeError(RuntimeError):
+    def __init__(self, code, text):
+        super().__init__(f"mbgfe error {code}: {text}")
+        self.code = code
+
+
+def library_path():
+    """The in-tree CUDA library.  MBGFE_LIBRARY overrides it (used by the GPU-less emulator tests only)."""
+    return os.environ.get("MBGFE_LIBRARY", os.path.join(HERE, "libmbgfe.so"))
+
+
+_lib = None
+
+
+def load_library(path=None):
+    global _lib
+    if _lib is not None and path is None:
+        return _lib
+    path = path or library_path()
+    if not os.path.exists(path):
+        raise MbgfeError(-2, f"{path} is missing: build it with `python -c 'import __graft_entry__ as g; g.build()'` "
+                             "(there is no CPU fallback)")
+    L = C.CDLL(path)
+    L.mbgfe_create.argtypes = [C.POINTER(Params), C.POINTER(C.c_void_p)]
+    L.mbgfe_destroy.argtypes = [C.c_void_p]
+    L.mbgfe_last_error.argtypes = [C.c_void_p]
+    L.mbgfe_last_error.restype = C.c_char_p
+    L.mbgfe_alloc_pinned.argtypes = [C.c_uint64]
+    L.mbgfe_alloc_pinned.restype = C.c_void_p
+    L.mbgfe_free_pinned.argtypes = [C.c_void_p]
+    L.mbgfe_add_reads.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint64]
+    L.mbgfe_add_file.argtypes = [C.c_void_p, C.c_char_p]
+    L.mbgfe_read_name.argtypes = [C.c_void_p, C.c_uint64]
+    L.mbgfe_read_name.restype = C.c_char_p
+    for f in (L.mbgfe_reset, L.mbgfe_upload, L.mbgfe_process, L.mbgfe_run):
+        f.argtypes = [C.c_void_p]
+    L.mbgfe_count.argtypes = [C.c_void_p, C.c_int]
+    L.mbgfe_count.restype = C.c_uint64
+    L.mbgfe_data.argtypes = [C.c_void_p, C.c_int]
+    L.mbgfe_data.restype = C.c_void_p
+    L.mbgfe_get_stats.argtypes = [C.c_void_p, C.POINTER(Stats)]
+    L.mbgfe_timer_start.argtypes = [C.c_void_p]
+    L.mbgfe_timer_stop.argtypes = [C.c_void_p, C.POINTER(C.c_float)]
+    L.mbgfe_exchange_counts.argtypes = [C.c_void_p, C.c_void_p]
+    L.mbgfe_exchange_pack.argtypes = [C.c_void_p, C.POINTER(C.c_void_p)]
+    L.mbgfe_exchange_reserve.argtypes = [C.c_void_p, C.c_uint64, C.POINTER(C.c_void_p)]
+    L.mbgfe_exchange_insert.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64]
+    L.mbgfe_kat_tables.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
+    L.mbgfe_kat_kmer_hash.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p]
+    if path == library_path():
+        _lib = L
+    return L
+
+
+def _array(ptr, count, dtype):
+    dtype = np.dtype(dtype)
+    if count == 0 or not ptr:
+        return np.zeros(0, dtype=dtype)
+    buf = (C.c_char * (count * dtype.itemsize)).from_address(ptr)
+    return np.frombuffer(buf, dtype=dtype).copy()
+
+
+class PinnedBuffer:
+    """numpy view of page-locked host memory from mbgfe_alloc_pinned."""
+
+    def __init__(self, lib, nbytes):
+        self.lib, self.nbytes = lib, int(nbytes)
+        self.ptr = lib.mbgfe_alloc_pinned(max(self.nbytes, 1))
+        if not self.ptr:
+            raise MbgfeError(-2, f"cannot allocate {nbytes} bytes of pinned memory")
+        self.array = np.frombuffer((C.c_char * max(self.nbytes, 1)).from_address(self.ptr), dtype=np.uint8)[:self.nbytes]
+
+    def free(self):
+        if self.ptr:
+            self.array = None
+            self.lib.mbgfe_free_pinned(self.ptr)
+            self.ptr = None
+
+
+class MbgFrontEnd:
+    """ReadpartIterator{k, w, errorMasking} + HashList{k} on one B200."""
+
+    def __init__(self, k, w, error_masking="collapse-msat", kmer_abundance=1, flags=0, device=0, rank=0, world=1,
+                 table_slots=0, library=None):
+        self.lib = load_library(library)
+        mode = MODES[error_masking] if isinstance(error_masking, str) else int(error_masking)
+        self.params = Params(1, k, w, mode, kmer_abundance, flags, device, rank, world, 0, table_slots)
+        self.handle = C.c_void_p()
+        rc = self.lib.mbgfe_create(C.byref(self.params), C.byref(self.handle))
+        if rc != 0:
+            raise MbgfeError(rc, self.lib.mbgfe_last_error(None).decode())
+        self._keep = []
+
+    def close(self):
+        if self.handle:
+            self.lib.mbgfe_destroy(self.handle)
+            self.handle = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def _check(self, rc):
+        if rc != 0:
+            raise MbgfeError(rc, self.lib.mbgfe_last_error(self.handle).decode())
+
+    # ---- input
+    def add_reads(self, bases, offsets):
+        """bases: uint8 array (ASCII), offsets: uint64 array of n+1 entries.  Buffers are referenced, not copied."""
+        bases = np.ascontiguousarray(bases, dtype=np.uint8)
+        offsets = np.ascontiguousarray(offsets, dtype=np.uint64)
+        self._keep.append((bases, offsets))
+        self._check(self.lib.mbgfe_add_reads(self.handle, bases.ctypes.data, offsets.ctypes.data, len(offsets) - 1))
+
+    def add_read_list(self, reads):
+        bs = [r.encode() if isinstance(r, str) else bytes(r) for r in reads]
+        offsets = np.zeros(len(bs) + 1, dtype=np.uint64)
+        if bs:
+            offsets[1:] = np.cumsum([len(b) for b in bs], dtype=np.uint64)
+        bases = np.frombuffer(b"".join(bs), dtype=np.uint8).copy() if bs else np.zeros(0, dtype=np.uint8)
+        self.add_reads(bases, offsets)
+
+    def add_file(self, path):
+        self._check(self.lib.mbgfe_add_file(self.handle, os.fsencode(path)))
+
+    def read_name(self, idx):
+        return self.lib.mbgfe_read_name(self.handle, idx).decode()
+
+    def reset(self):
+        self._check(self.lib.mbgfe_reset(self.handle))
+        self._keep = []
+
+    # ---- run
+    def upload(self):
+        self._check(self.lib.mbgfe_upload(self.handle))
+        self._keep = []
+
+    def process(self):
+        self._check(self.lib.mbgfe_process(self.handle))
+
+    def run(self):
+        self._check(self.lib.mbgfe_run(self.handle))
+        self._keep = []
+
+    # ---- results
+    def count(self, what):
+        return int(self.lib.mbgfe_count(self.handle, what))
+
+    def _data(self, what, dtype, per=1):
+        n = self.count(what)
+        ptr = self.lib.mbgfe_data(self.handle, what)
+        if n and not ptr:
+            self._check(-6)
+        return _array(ptr, n * per, dtype)
+
+    def parts(self):
+        return self._data(PARTS, PART_DTYPE)
+
+    def codes(self):
+        return self._data(CODES, "<u2")
+
+    def poses(self):
+        return self._data(POSES, "<u4")
+
+    def positions(self):
+        return self._data(POSITIONS, "<u4")
+
+    def hashes(self):
+        return self._data(HASHES, "<u8", 2).reshape(-1, 2)
+
+    def node_hashes(self):
+        return self._data(NODE_HASHES, "<u8", 2).reshape(-1, 2)
+
+    def node_coverage(self):
+        return self._data(NODE_COVERAGE, "<u4")
+
+    def node_tip(self):
+        return self._data(NODE_TIP, "u1")
+
+    def edges(self):
+        return self._data(EDGES, "<u4", 6).reshape(-1, 6)
+
+    def stats(self):
+        s = Stats()
+        self._check(self.lib.mbgfe_get_stats(self.handle, C.byref(s)))
+        return {n: getattr(s, n) for n, _ in Stats._fields_ if n != "reserved"}
+
+    def timer_start(self):
+        self._check(self.lib.mbgfe_timer_start(self.handle))
+
+    def timer_stop(self):
+        ms = C.c_float()
+        self._check(self.lib.mbgfe_timer_stop(self.handle, C.byref(ms)))
+        return float(ms.value)
+
+    def pinned(self, nbytes):
+        return PinnedBuffer(self.lib, nbytes)
+
+    # ---- multi-GPU exchange (device pointers as integers)
+    def exchange_counts(self):
+        out = np.zeros(self.params.world, dtype=np.uint64)
+        self._check(self.lib.mbgfe_exchange_counts(self.handle, out.ctypes.data))
+        return out
+
+    def exchange_pack(self):
+        p = C.c_void_p()
+        self._check(self.lib.mbgfe_exchange_pack(self.handle, C.byref(p)))
+        return p.value or 0
+
+    def exchange_reserve(self, n_records):
+        p = C.c_void_p()
+        self._check(self.lib.mbgfe_exchange_reserve(self.handle, n_records, C.byref(p)))
+        return p.value or 0
+
+    def exchange_insert(self, device_ptr, n_records):
+        self._check(self.lib.mbgfe_exchange_insert(self.handle, device_ptr, n_records))
+
+    # ---- known-answer access
+    def kat_tables(self):
+        h = np.zeros(30948, dtype=np.uint64)
+        c = np.zeros(30948, dtype=np.uint16)
+        self._check(self.lib.mbgfe_kat_tables(self.handle, h.ctypes.data, c.ctypes.data))
+        return h, c
+
+    def kat_kmer_hash(self, codes):
+        codes = np.ascontiguousarray(codes, dtype=np.uint16)
+        out = np.zeros(2, dtype=np.uint64)
+        self._check(self.lib.mbgfe_kat_kmer_hash(self.handle, codes.ctypes.data, len(codes), out.ctypes.data))
+        return int(out[0]), int(out[1])
