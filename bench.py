@@ -56,6 +56,10 @@ class ClockSampler:
                                          stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
             self.thread = threading.Thread(target=self._read, daemon=True)
             self.thread.start()
+            t0 = time.time()
+            while not self.rows and time.time() - t0 < 3.0:   # nvidia-smi needs a moment before its first sample
+                time.sleep(0.02)
+            self.rows.clear()
         except OSError:
             self.proc = None
 

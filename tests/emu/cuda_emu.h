@@ -122,6 +122,7 @@ using std::min;
 
 template <typename T> inline T atomicAdd(T* p, T v) { return __atomic_fetch_add(p, v, __ATOMIC_RELAXED); }
 template <typename T> inline T atomicOr(T* p, T v) { return __atomic_fetch_or(p, v, __ATOMIC_RELAXED); }
+template <typename T> inline T atomicAnd(T* p, T v) { return __atomic_fetch_and(p, v, __ATOMIC_RELAXED); }
 template <typename T> inline T atomicMax(T* p, T v)
 {
 	T old = __atomic_load_n(p, __ATOMIC_RELAXED);

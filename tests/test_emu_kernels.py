@@ -17,3 +17,15 @@ def test_emulated_kernels_match_oracle(oracle, emu_library, mode, k, w):
 def test_emulated_kernels_table_with_coverage(oracle, emu_library):
     reads = workloads.coverage_reads(n_reads=6)
     compare_runs(run_frontend("collapse-msat", 501, 50, reads, library=emu_library), oracle.run("collapse-msat", 501, 50, reads), what="coverage")
+
+
+def test_emulated_palindrome_rule(oracle, emu_library):
+    """droppable palindromes vanish like in the reference; a non-droppable one is an error in both"""
+    from verkko_b200 import MbgfeError
+    reads = [workloads.repeat_rich(9, 12000), workloads.palindrome_read(1000)]
+    compare_runs(run_frontend("dinuc", 63, 33, reads, library=emu_library), oracle.run("dinuc", 63, 33, reads), what="droppable")
+    with pytest.raises(RuntimeError, match="palindromic"):
+        oracle.run("dinuc", 63, 33, [workloads.palindrome_read(1021)])
+    with pytest.raises(MbgfeError) as e:
+        run_frontend("dinuc", 63, 33, [workloads.palindrome_read(1021)], library=emu_library)
+    assert e.value.code == -4

@@ -58,6 +58,18 @@ def test_repeat_rich_reads(oracle):
         compare_runs(run_frontend(mode, 101, 10, reads), oracle.run(mode, 101, 10, reads), what=mode)
 
 
+def test_palindrome_rule(oracle):
+    """MBG/ReadHelper.h:755-785: droppable palindromic k-mers vanish, a non-droppable one is an error (reference: abort)"""
+    from verkko_b200 import MbgfeError
+    reads = [workloads.repeat_rich(9, 30000), workloads.palindrome_read(1000)]
+    compare_runs(run_frontend("dinuc", 63, 33, reads), oracle.run("dinuc", 63, 33, reads), what="droppable")
+    with pytest.raises(RuntimeError, match="palindromic"):
+        oracle.run("dinuc", 63, 33, [workloads.palindrome_read(1021)])
+    with pytest.raises(MbgfeError) as e:
+        run_frontend("dinuc", 63, 33, [workloads.palindrome_read(1021)])
+    assert e.value.code == -4
+
+
 def test_long_and_ragged_reads(oracle):
     from verkko_b200 import synth
     g = synth.genome(21, 400000)

@@ -52,3 +52,12 @@ def coverage_reads(seed=11, genome_len=30000, n_reads=12, len_min=8000, len_max=
 
 def as_pair(reads):
     return reads if isinstance(reads, tuple) else pack_reads(reads)
+
+
+def palindrome_read(seed):
+    """X + (AT)^6 + revcomp(X): in dinuc mode the AT run is one self-complementary code, so the k-mer centred on it is
+    a reverse-complement palindrome.  seed 1021 (k=63, w=33): the palindrome is selected with neighbours >= k apart,
+    where the reference aborts (MBG/ReadHelper.h:775-777); seed 1000: dropped silently / not selected."""
+    comp = {65: 84, 67: 71, 71: 67, 84: 65}
+    x = lcg_bases(seed, 400)
+    return x + b"AT" * 6 + bytes(comp[c] for c in reversed(x))

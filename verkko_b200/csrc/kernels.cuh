@@ -873,7 +873,7 @@ __global__ void __launch_bounds__(256) k_kmer_hash(const uint64_t* __restrict__ 
 	inst_hash[2 * i + dir] = mm.finish();
 }
 
-// instances whose two halves hash alike: palindromes or (practically impossible) collisions -> host decides
+// instances whose two halves hash alike: palindromes or (practically impossible) collisions
 __global__ void __launch_bounds__(256) k_find_palindromes(const uint64_t* __restrict__ inst_hash, uint64_t n_inst, unsigned long long* __restrict__ count,
 	uint64_t* __restrict__ list, uint64_t cap)
 {
@@ -884,6 +884,55 @@ __global__ void __launch_bounds__(256) k_find_palindromes(const uint64_t* __rest
 		unsigned long long slot = atomicAdd(count, 1ull);
 		if (slot < cap) list[slot] = i;
 	}
+}
+
+// The reference's palindrome rule (MBG/ReadHelper.h:755-785) for the instances found above: a k-mer whose two hashes
+// agree must be a true reverse-complement palindrome (else: "unhashable", errors[1]); it is dropped silently when it
+// is the first or last selected k-mer of its part or when its neighbours are less than k apart, otherwise the
+// reference aborts (errors[0]).  Dropping = clearing its bit in the selection mask; the instance list is then rebuilt.
+__global__ void __launch_bounds__(128) k_resolve_palindromes(const uint64_t* __restrict__ list, uint64_t n_list, const uint32_t* __restrict__ inst_pos,
+	const uint32_t* __restrict__ inst_seg, const uint8_t* __restrict__ inst_flag, const uint64_t* __restrict__ seg_out_base, const uint16_t* __restrict__ codes,
+	const uint16_t* __restrict__ tab_comp, uint32_t* __restrict__ selmask32, uint32_t k, unsigned long long* __restrict__ errors)
+{
+	const uint64_t t = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+	if (t >= n_list) return;
+	const uint64_t i = list[t];
+	const uint64_t out0 = seg_out_base[inst_seg[i]];
+	const uint32_t pos = inst_pos[i];
+	const uint16_t* __restrict__ c = codes + out0 + pos;
+	bool palindrome = true;
+	for (uint32_t j = 0; j < k / 2; j++)
+	{
+		if (c[j] != tab_comp[c[k - 1 - j]]) { palindrome = false; break; }
+	}
+	if (!palindrome) { atomicAdd(errors + 1, 1ull); return; }
+	const uint32_t fl = inst_flag[i];
+	const bool droppable = (fl & 3) != 0 || inst_pos[i + 1] - inst_pos[i - 1] < k;
+	if (!droppable) { atomicAdd(errors + 0, 1ull); return; }
+	atomicAnd(selmask32 + ((out0 + pos) >> 5), ~(1u << (pos & 31)));
+}
+
+// selected count per segment straight from the selection mask (after palindromes were dropped)
+template <int NT>
+__global__ void __launch_bounds__(NT) k_recount_selected(SegTable seg, const uint32_t* __restrict__ selmask32, const uint32_t* __restrict__ seg_c2, uint32_t* __restrict__ seg_nsel, uint32_t k)
+{
+	__shared__ uint32_t warp_tmp[NT / 32];
+	const uint32_t g = blockIdx.x;
+	if (g >= seg.n) return;
+	const uint32_t n = seg_c2[g];
+	if (n < k) { if (threadIdx.x == 0) seg_nsel[g] = 0; return; }
+	const uint32_t n_kmers = n - k + 1;
+	const uint32_t* __restrict__ mw = selmask32 + (seg.out_base[g] >> 5);
+	uint32_t cnt = 0;
+	for (uint32_t p0 = threadIdx.x * 32; p0 < n_kmers; p0 += NT * 32)
+	{
+		uint32_t bits = mw[p0 >> 5];
+		if (n_kmers - p0 < 32) bits &= (1u << (n_kmers - p0)) - 1;
+		cnt += __popc(bits);
+	}
+	uint32_t total;
+	block_exclusive_sum<NT>(cnt, warp_tmp, total);
+	if (threadIdx.x == 0) seg_nsel[g] = total;
 }
 
 // ---------------------------------------------------------------------------------------- K4: k-mer table

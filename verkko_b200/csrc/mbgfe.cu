@@ -586,25 +586,42 @@ int mbgfe_process(mbgfe* h)
 	if (int rc = ensure(h, h->d_inst_flag, n_inst + 64)) return rc;
 	if (int rc = ensure(h, h->d_inst_hash, n_inst * 16 + 64)) return rc;
 	if (int rc = ensure(h, h->d_inst_slot, n_inst * 4 + 64)) return rc;
-	const uint64_t pal_cap = 1 << 16;
+	const uint64_t pal_cap = 1 << 20;
 	if (int rc = ensure(h, h->d_pal_list, pal_cap * 8)) return rc;
-	if (n_inst)
+	for (int pass = 0; pass < 2; pass++)
 	{
-		MBGFE_LAUNCH(k_list_selected<NT_LIST>, n_seg, NT_LIST, 0, h->stream, st, h->d_selmask.as<uint32_t>(), h->d_seg_c2.as<uint32_t>(), h->d_seg_nsel.as<uint32_t>(),
-			h->d_sel_begin.as<uint64_t>(), h->d_inst_pos.as<uint32_t>(), h->d_inst_seg.as<uint32_t>(), h->d_inst_flag.as<uint8_t>(), k);
-		MBGFE_LAUNCH(k_kmer_hash, (unsigned)((2 * n_inst + 255) / 256), 256, 0, h->stream, h->d_seg_out.as<uint64_t>(), h->d_codes.as<uint16_t>(), h->tab_comp.as<uint16_t>(),
-			h->d_inst_pos.as<uint32_t>(), h->d_inst_seg.as<uint32_t>(), n_inst, h->d_inst_hash.as<uint64_t>(), k);
-		MBGFE_LAUNCH(k_find_palindromes, (unsigned)((n_inst + 255) / 256), 256, 0, h->stream, h->d_inst_hash.as<uint64_t>(), n_inst, ctr + CTR_PALINDROME,
-			h->d_pal_list.as<uint64_t>(), pal_cap);
+		if (n_inst)
+		{
+			MBGFE_LAUNCH(k_list_selected<NT_LIST>, n_seg, NT_LIST, 0, h->stream, st, h->d_selmask.as<uint32_t>(), h->d_seg_c2.as<uint32_t>(), h->d_seg_nsel.as<uint32_t>(),
+				h->d_sel_begin.as<uint64_t>(), h->d_inst_pos.as<uint32_t>(), h->d_inst_seg.as<uint32_t>(), h->d_inst_flag.as<uint8_t>(), k);
+			MBGFE_LAUNCH(k_kmer_hash, (unsigned)((2 * n_inst + 255) / 256), 256, 0, h->stream, h->d_seg_out.as<uint64_t>(), h->d_codes.as<uint16_t>(), h->tab_comp.as<uint16_t>(),
+				h->d_inst_pos.as<uint32_t>(), h->d_inst_seg.as<uint32_t>(), n_inst, h->d_inst_hash.as<uint64_t>(), k);
+			MBGFE_LAUNCH(k_find_palindromes, (unsigned)((n_inst + 255) / 256), 256, 0, h->stream, h->d_inst_hash.as<uint64_t>(), n_inst, ctr + CTR_PALINDROME,
+				h->d_pal_list.as<uint64_t>(), pal_cap);
+			launches += 3;
+		}
+		if (pass == 0) tick(h, 7);
+		uint64_t n_pal = 0;
+		if (int rc = read_counter(h, CTR_PALINDROME, &n_pal)) return rc;
+		if (n_pal == 0) break;
+		// rare path (MBG/ReadHelper.h:755-785): drop what the reference drops, fail where it aborts, rebuild the list
+		if (pass == 1) return fail(h, MBGFE_E_PALINDROME, "palindromic k-mers remain after dropping");
+		if (n_pal > pal_cap) return fail(h, MBGFE_E_LIMIT, "%llu palindromic k-mers (limit %llu)", (unsigned long long)n_pal, (unsigned long long)pal_cap);
+		MBGFE_LAUNCH(k_resolve_palindromes, (unsigned)((n_pal + 127) / 128), 128, 0, h->stream, h->d_pal_list.as<uint64_t>(), n_pal, h->d_inst_pos.as<uint32_t>(),
+			h->d_inst_seg.as<uint32_t>(), h->d_inst_flag.as<uint8_t>(), h->d_seg_out.as<uint64_t>(), h->d_codes.as<uint16_t>(), h->tab_comp.as<uint16_t>(),
+			h->d_selmask.as<uint32_t>(), k, ctr + CTR_CURSOR);
+		unsigned long long errs[2] = { 0, 0 };
+		CU(h, cudaMemcpyAsync(errs, ctr + CTR_CURSOR, 16, cudaMemcpyDeviceToHost, h->stream));
+		CU(h, cudaStreamSynchronize(h->stream));
+		if (errs[1]) return fail(h, MBGFE_E_UNHASHABLE, "unhashable k-mer: forward and reverse hashes agree on a non-palindrome (%llu)", errs[1]);
+		if (errs[0]) return fail(h, MBGFE_E_PALINDROME, "the genome has a palindromic k-mer (%llu); cannot build a graph, try a different -w", errs[0]);
+		MBGFE_LAUNCH(k_recount_selected<NT_LIST>, n_seg, NT_LIST, 0, h->stream, st, h->d_selmask.as<uint32_t>(), h->d_seg_c2.as<uint32_t>(), h->d_seg_nsel.as<uint32_t>(), k);
+		MBGFE_LAUNCH(k_scan_u32<1024>, 1, 1024, 0, h->stream, h->d_seg_nsel.as<uint32_t>(), h->d_sel_begin.as<uint64_t>(), n_seg);
+		CU(h, cudaMemsetAsync(ctr + CTR_PALINDROME, 0, 8, h->stream));
+		CU(h, cudaMemcpyAsync(&n_inst, h->d_sel_begin.as<uint64_t>() + n_seg, 8, cudaMemcpyDeviceToHost, h->stream));
+		CU(h, cudaStreamSynchronize(h->stream));
+		h->n_inst = n_inst;
 		launches += 3;
-	}
-	tick(h, 7);
-	uint64_t n_pal = 0;
-	if (int rc = read_counter(h, CTR_PALINDROME, &n_pal)) return rc;
-	if (n_pal)
-	{
-		// MBG/ReadHelper.h:755-785.  Not implemented yet on the device side: report instead of producing a wrong table.
-		return fail(h, MBGFE_E_PALINDROME, "%llu selected k-mers hash identically in both directions (palindromic k-mer); try a different -w", (unsigned long long)n_pal);
 	}
 	h->stats.distinct = 0; h->stats.distinct_edges = 0;
 	if (!(h->prm.flags & MBGFE_NO_TABLE))
