@@ -308,25 +308,30 @@ def main():
     fe.parts()
     st = fe.stats()
 
-    # ---- end to end through the C ABI from pinned host buffers
-    e2e_ms, h2d, d2h = [], 0, 0
+    # ---- end to end through the C ABI from pinned host buffers: ASCII reads in host memory -> ordered table in host memory
+    e2e_ms, h2d, d2h, e2e_parts = [], 0, 0, {}
     for it in range(1 + args.e2e_steps):
         barrier()
         t0 = time.time()
         fe.add_reads(bases, offsets)
         fe.upload()
+        t1 = time.time()
         st_up = fe.stats()
         step()
+        t2 = time.time()
         if world == 1:
-            cov = fe.node_coverage()
-            fe.node_hashes()
-            fe.edges()
-            checksum = int(cov.sum())
+            cov = fe.node_coverage(copy=False)       # views of the library's pinned result arrays (no extra host copy)
+            hashes = fe.node_hashes(copy=False)
+            edges = fe.edges(copy=False)
+            checksum = int(cov.sum(dtype=np.uint64)) + len(hashes) + len(edges)
         else:
             checksum = counter.download_counts()
         barrier()
+        t3 = time.time()
         if it > 0:
-            e2e_ms.append((time.time() - t0) * 1e3)
+            e2e_ms.append((t3 - t0) * 1e3)
+            for name, dt in (("upload_ms", t1 - t0), ("process_ms", t2 - t1), ("export_ms", t3 - t2)):
+                e2e_parts[name] = e2e_parts.get(name, 0.0) + dt * 1e3 / args.e2e_steps
         st_e = fe.stats()
         h2d, d2h = st_up["h2d_bytes"], st_e["d2h_bytes"]
     e2e_t = torch.tensor([float(np.mean(e2e_ms))], dtype=torch.float64, device="cuda")
@@ -361,7 +366,8 @@ def main():
             "counts": {"raw_bases": R, "collapsed_symbols": C1, "codes": C2, "selected_kmers": S, "distinct_kmers": parts_stats["distinct"], "distinct_edges": parts_stats["distinct_edges"]},
             "stage_ms_per_step": per_step, "wall_ms_per_step": wall_ms / args.steps,
             "clocks": clocks,
-            "e2e": {"value": e2e_value, "unit": "bases/s", "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h), "ms_per_step": float(e2e_t[0]), "checksum": checksum},
+            "e2e": {"value": e2e_value, "unit": "bases/s", "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h), "ms_per_step": float(e2e_t[0]), "checksum": checksum,
+                    "wall_ms": e2e_parts, "device_ms": {"h2d": st_up["ms_upload"], "pack": st_up["ms_pack"], "export_sort_d2h": st_e["ms_export"]}},
             "gpu_launches": int(launches),
             "roofline": {"bound": "hbm", "kernel": dominant, "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": None,
                          "peak_source": peak_src,

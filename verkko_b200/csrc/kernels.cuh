@@ -758,6 +758,35 @@ __global__ void __launch_bounds__(NT) k_scan_u32(const uint32_t* __restrict__ in
 	if (threadIdx.x == 0) out[n] = carry;
 }
 
+// two-level exclusive prefix sum for large arrays: tile totals, (k_scan_u32 over the totals), then tile rescans
+constexpr int SCAN_NT = 256, SCAN_IPT = 8;
+__global__ void __launch_bounds__(SCAN_NT) k_scan_tile_totals(const uint32_t* __restrict__ in, uint32_t* __restrict__ tile_total, uint32_t n)
+{
+	__shared__ uint32_t warp_tmp[SCAN_NT / 32];
+	const uint32_t base = blockIdx.x * (SCAN_NT * SCAN_IPT) + threadIdx.x * SCAN_IPT;
+	uint32_t v = 0;
+#pragma unroll
+	for (int j = 0; j < SCAN_IPT; j++) if (base + j < n) v += in[base + j];
+	uint32_t tot;
+	block_exclusive_sum<SCAN_NT>(v, warp_tmp, tot);
+	if (threadIdx.x == 0) tile_total[blockIdx.x] = tot;
+}
+
+__global__ void __launch_bounds__(SCAN_NT) k_scan_tiles(const uint32_t* __restrict__ in, const uint64_t* __restrict__ tile_offset, uint64_t* __restrict__ out, uint32_t n)
+{
+	__shared__ uint32_t warp_tmp[SCAN_NT / 32];
+	const uint32_t base = blockIdx.x * (SCAN_NT * SCAN_IPT) + threadIdx.x * SCAN_IPT;
+	uint32_t vals[SCAN_IPT];
+	uint32_t v = 0;
+#pragma unroll
+	for (int j = 0; j < SCAN_IPT; j++) { vals[j] = base + j < n ? in[base + j] : 0; v += vals[j]; }
+	uint32_t tot;
+	uint64_t run = tile_offset[blockIdx.x] + block_exclusive_sum<SCAN_NT>(v, warp_tmp, tot);
+#pragma unroll
+	for (int j = 0; j < SCAN_IPT; j++) { if (base + j < n) out[base + j] = run; run += vals[j]; }
+	if (blockIdx.x == gridDim.x - 1 && threadIdx.x == SCAN_NT - 1) out[n] = run;
+}
+
 // K3b1: selection bitmask -> instance list.  One CTA per segment; inst_pos = part-local k-mer position,
 // inst_seg = segment, inst_flag bit0 = first selected k-mer of its part, bit1 = last (the tips, MBG/MBG.cpp:58).
 template <int NT>
@@ -1179,36 +1208,128 @@ __global__ void __launch_bounds__(256) k_insert_edges(const uint64_t* __restrict
 
 // ------------------------------------------------------------------------------------------------ export
 
-// occupied node slots -> dense arrays (order arbitrary; sorted by key afterwards)
+// HashList::sortByHash (MBG/HashList.cpp:245-353) on the device: node ids are the ranks of the canonical hashes.
+// Canonical hashes are Murmur output, i.e. uniform, so one MSD bucket pass on the top bits of key_hi leaves buckets
+// of a few dozen entries; each bucket is then ordered by counting, for every entry, the entries of its bucket with a
+// smaller key (keys are distinct).  count -> scan -> scatter -> rank; the rank is also written back into the table
+// slot so that edges (keyed by slot) can be renumbered.
 struct NodeOut { uint64_t key_lo, key_hi; uint32_t count, flags; uint64_t slot; };
-__global__ void __launch_bounds__(256) k_export_nodes(const NodeSlot* __restrict__ table, uint64_t n_slots, NodeOut* __restrict__ out, unsigned long long* __restrict__ cursor)
+
+__global__ void __launch_bounds__(256) k_node_bucket_count(const NodeSlot* __restrict__ table, uint64_t n_slots, uint32_t shift, uint32_t* __restrict__ counts)
 {
-	const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
-	const uint64_t rounds = (n_slots + stride - 1) / stride;
-	for (uint64_t rd = 0; rd < rounds; rd++)
+	for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n_slots; i += (uint64_t)gridDim.x * blockDim.x)
 	{
-		const uint64_t i = rd * stride + (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
-		NodeSlot s; s.key_lo = ~0ull; s.key_hi = ~0ull; s.count = 0; s.flags = 0; s.rank = 0;
-		if (i < n_slots) s = table[i];
-		const bool used = !(s.key_lo == ~0ull && s.key_hi == ~0ull);
-		const unsigned long long o = warp_alloc(cursor, used);
-		if (used) { NodeOut r; r.key_lo = s.key_lo; r.key_hi = s.key_hi; r.count = s.count; r.flags = s.flags; r.slot = i; out[o] = r; }
+		const uint64_t hi = table[i].key_hi, lo = table[i].key_lo;
+		if (hi == ~0ull && lo == ~0ull) continue;
+		atomicAdd(counts + (shift >= 64 ? 0 : (hi >> shift)), 1u);
 	}
 }
 
-struct EdgeOut { unsigned long long key; unsigned long long ordered; uint32_t count, pad; };
-__global__ void __launch_bounds__(256) k_export_edges(const EdgeSlot* __restrict__ table, uint64_t n_slots, EdgeOut* __restrict__ out, unsigned long long* __restrict__ cursor)
+__global__ void __launch_bounds__(256) k_node_bucket_scatter(const NodeSlot* __restrict__ table, uint64_t n_slots, uint32_t shift, const uint64_t* __restrict__ bucket_begin,
+	uint32_t* __restrict__ fill, NodeOut* __restrict__ tmp)
 {
-	const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
-	const uint64_t rounds = (n_slots + stride - 1) / stride;
-	for (uint64_t rd = 0; rd < rounds; rd++)
+	for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n_slots; i += (uint64_t)gridDim.x * blockDim.x)
 	{
-		const uint64_t i = rd * stride + (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
-		EdgeSlot s; s.key = ~0ull; s.ordered = 0; s.count = 0;
-		if (i < n_slots) s = table[i];
-		const bool used = s.key != ~0ull;
-		const unsigned long long o = warp_alloc(cursor, used);
-		if (used) { EdgeOut r; r.key = s.key; r.ordered = s.ordered; r.count = s.count; r.pad = 0; out[o] = r; }
+		const NodeSlot s = table[i];
+		if (s.key_hi == ~0ull && s.key_lo == ~0ull) continue;
+		const uint64_t b = shift >= 64 ? 0 : (s.key_hi >> shift);
+		const uint64_t o = bucket_begin[b] + atomicAdd(fill + b, 1u);
+		NodeOut r; r.key_lo = s.key_lo; r.key_hi = s.key_hi; r.count = s.count; r.flags = s.flags; r.slot = i;
+		tmp[o] = r;
+	}
+}
+
+// one warp per bucket; lanes take entries round-robin and count smaller keys (uniform-address loads: L1 broadcasts)
+__global__ void __launch_bounds__(256) k_node_bucket_rank(const NodeOut* __restrict__ tmp, const uint64_t* __restrict__ bucket_begin, uint32_t n_buckets,
+	uint64_t* __restrict__ out_hash, uint32_t* __restrict__ out_cov, uint8_t* __restrict__ out_tip, NodeSlot* __restrict__ table)
+{
+	const uint32_t lane = threadIdx.x & 31;
+	const uint32_t warps = (gridDim.x * blockDim.x) >> 5;
+	for (uint32_t b = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; b < n_buckets; b += warps)
+	{
+		const uint64_t begin = bucket_begin[b];
+		const uint32_t n = (uint32_t)(bucket_begin[b + 1] - begin);
+		const NodeOut* __restrict__ e = tmp + begin;
+		for (uint32_t i = lane; i < n; i += 32)
+		{
+			const NodeOut mine = e[i];
+			uint32_t rank = 0;
+			for (uint32_t j = 0; j < n; j++)
+			{
+				const uint64_t hi = e[j].key_hi, lo = e[j].key_lo;
+				rank += (hi < mine.key_hi || (hi == mine.key_hi && lo < mine.key_lo)) ? 1u : 0u;
+			}
+			const uint64_t o = begin + rank;
+			out_hash[2 * o] = mine.key_lo; out_hash[2 * o + 1] = mine.key_hi;
+			out_cov[o] = mine.count;
+			out_tip[o] = (uint8_t)(mine.flags & 1);
+			table[mine.slot].rank = o;
+		}
+	}
+}
+
+// Edges: translated from slot pairs to node ids, then ordered by (from, from_fw descending, to, to_fw) with the same
+// bucket scheme on `from` (MBG writes a node's forward-side edges first, MBG/MBG.cpp:967-989).
+struct EdgeRec { uint32_t from, from_fw, to, to_fw, coverage, overlap; };   // == mbgfe_edge
+
+__device__ __forceinline__ EdgeRec edge_record(const EdgeSlot& s, const NodeSlot* __restrict__ nodes)
+{
+	const uint32_t a = (uint32_t)(s.key >> 32), b = (uint32_t)s.key;
+	EdgeRec r;
+	r.from = (uint32_t)nodes[a >> 1].rank; r.from_fw = a & 1;
+	r.to = (uint32_t)nodes[b >> 1].rank; r.to_fw = b & 1;
+	r.coverage = s.count;
+	r.overlap = (uint32_t)(s.ordered & 0xffffff);
+	return r;
+}
+
+__device__ __forceinline__ uint64_t edge_order_key(const EdgeRec& r)
+{
+	return ((uint64_t)((r.from << 1) | (1u - r.from_fw)) << 32) | (uint64_t)((r.to << 1) | r.to_fw);
+}
+
+__global__ void __launch_bounds__(256) k_edge_bucket_count(const EdgeSlot* __restrict__ table, uint64_t n_slots, const NodeSlot* __restrict__ nodes, uint32_t shift,
+	uint32_t* __restrict__ counts)
+{
+	for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n_slots; i += (uint64_t)gridDim.x * blockDim.x)
+	{
+		const unsigned long long key = table[i].key;
+		if (key == ~0ull) continue;
+		const uint32_t from = (uint32_t)nodes[key >> 33].rank;
+		atomicAdd(counts + (from >> shift), 1u);
+	}
+}
+
+__global__ void __launch_bounds__(256) k_edge_bucket_scatter(const EdgeSlot* __restrict__ table, uint64_t n_slots, const NodeSlot* __restrict__ nodes, uint32_t shift,
+	const uint64_t* __restrict__ bucket_begin, uint32_t* __restrict__ fill, EdgeRec* __restrict__ tmp)
+{
+	for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n_slots; i += (uint64_t)gridDim.x * blockDim.x)
+	{
+		const EdgeSlot s = table[i];
+		if (s.key == ~0ull) continue;
+		const EdgeRec r = edge_record(s, nodes);
+		const uint32_t b = r.from >> shift;
+		tmp[bucket_begin[b] + atomicAdd(fill + b, 1u)] = r;
+	}
+}
+
+__global__ void __launch_bounds__(256) k_edge_bucket_rank(const EdgeRec* __restrict__ tmp, const uint64_t* __restrict__ bucket_begin, uint32_t n_buckets, EdgeRec* __restrict__ out)
+{
+	const uint32_t lane = threadIdx.x & 31;
+	const uint32_t warps = (gridDim.x * blockDim.x) >> 5;
+	for (uint32_t b = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; b < n_buckets; b += warps)
+	{
+		const uint64_t begin = bucket_begin[b];
+		const uint32_t n = (uint32_t)(bucket_begin[b + 1] - begin);
+		const EdgeRec* __restrict__ e = tmp + begin;
+		for (uint32_t i = lane; i < n; i += 32)
+		{
+			const EdgeRec mine = e[i];
+			const uint64_t mk = edge_order_key(mine);
+			uint32_t rank = 0;
+			for (uint32_t j = 0; j < n; j++) rank += edge_order_key(e[j]) < mk ? 1u : 0u;
+			out[begin + rank] = mine;
+		}
 	}
 }
 

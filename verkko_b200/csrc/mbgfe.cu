@@ -16,6 +16,8 @@
 #include "kernels.cuh"
 #include "../../include/mbgfe.h"
 
+static_assert(sizeof(mbgfe_dev::EdgeRec) == sizeof(mbgfe_edge), "device edge record is the ABI edge record");
+
 #ifdef MBGFE_EMU_BUILD
 thread_local uint3 threadIdx;
 thread_local uint3 blockIdx;
@@ -30,6 +32,13 @@ namespace {
 thread_local std::string g_create_error;
 
 struct DevBuf
+{
+	void* p = nullptr;
+	size_t cap = 0;
+	template <typename T> T* as() const { return (T*)p; }
+};
+
+struct HostBuf
 {
 	void* p = nullptr;
 	size_t cap = 0;
@@ -80,6 +89,8 @@ struct mbgfe
 	DevBuf d_sym, d_codes, d_selmask, d_pos1, d_pos2;
 	DevBuf d_inst_pos, d_inst_seg, d_inst_flag, d_inst_hash, d_inst_slot, d_pal_list;
 	DevBuf d_nodes, d_edges, d_node_out, d_edge_out, d_records, d_recv;
+	DevBuf d_bucket_count, d_bucket_begin, d_scan_tot, d_scan_off;      // export: bucket tables and scan scratch
+	DevBuf d_node_hash_sorted, d_node_cov, d_node_tip, d_edges_sorted;    // export: final layout, device resident
 	uint64_t node_slots = 0, edge_slots = 0;
 	uint64_t n_inst = 0;
 
@@ -87,10 +98,9 @@ struct mbgfe
 	std::vector<mbgfe_part> parts;
 	std::vector<uint16_t> h_codes;
 	std::vector<uint32_t> h_poses, h_positions;
-	std::vector<mbgfe_hash128> h_hashes, h_node_hashes;
-	std::vector<uint32_t> h_node_cov;
-	std::vector<uint8_t> h_node_tip;
-	std::vector<mbgfe_edge> h_edges;
+	std::vector<mbgfe_hash128> h_hashes;
+	HostBuf p_node_hashes, p_node_cov, p_node_tip, p_edges;           // pinned: the table arrives by DMA at full rate
+	uint64_t n_nodes_out = 0, n_edges_out = 0;
 	std::vector<uint32_t> h_seg_c1, h_seg_c2, h_seg_nsel;
 	std::vector<uint64_t> h_sel_begin;
 
@@ -122,6 +132,19 @@ int ensure(mbgfe* h, DevBuf& b, size_t bytes)
 }
 
 void release(DevBuf& b) { if (b.p) cudaFree(b.p); b.p = nullptr; b.cap = 0; }
+
+int ensure_host(mbgfe* h, HostBuf& b, size_t bytes)
+{
+	bytes = (bytes + 4095) & ~(size_t)4095;
+	if (b.cap >= bytes) return 0;
+	if (b.p) CU(h, cudaFreeHost(b.p));
+	b.p = nullptr; b.cap = 0;
+	CU(h, cudaMallocHost(&b.p, bytes));
+	b.cap = bytes;
+	return 0;
+}
+
+void release_host(HostBuf& b) { if (b.p) cudaFreeHost(b.p); b.p = nullptr; b.cap = 0; }
 
 uint64_t next_pow2(uint64_t v) { uint64_t p = 1; while (p < v) p <<= 1; return p; }
 
@@ -259,7 +282,7 @@ void clear_results(mbgfe* h)
 {
 	h->processed = false; h->exported_parts = false; h->exported_table = false; h->exported_codes = false; h->have_table = false;
 	h->parts.clear(); h->h_codes.clear(); h->h_poses.clear(); h->h_positions.clear(); h->h_hashes.clear();
-	h->h_node_hashes.clear(); h->h_node_cov.clear(); h->h_node_tip.clear(); h->h_edges.clear();
+	h->n_nodes_out = 0; h->n_edges_out = 0;
 	h->n_inst = 0;
 }
 
@@ -409,7 +432,9 @@ void mbgfe_destroy(mbgfe* h)
 	for (DevBuf* b : { &h->tab_hash, &h->tab_hash_rc, &h->tab_comp, &h->d_ascii, &h->d_packed, &h->d_nonacgt, &h->d_counters, &h->d_seg_in, &h->d_seg_out,
 		&h->d_seg_len, &h->d_seg_c1, &h->d_seg_c2, &h->d_seg_nsel, &h->d_sel_begin, &h->d_sym, &h->d_codes, &h->d_selmask, &h->d_pos1, &h->d_pos2,
 		&h->d_inst_pos, &h->d_inst_seg, &h->d_inst_flag, &h->d_inst_hash, &h->d_inst_slot, &h->d_pal_list, &h->d_nodes, &h->d_edges, &h->d_node_out,
-		&h->d_edge_out, &h->d_records, &h->d_recv }) release(*b);
+		&h->d_edge_out, &h->d_records, &h->d_recv, &h->d_bucket_count, &h->d_bucket_begin, &h->d_scan_tot, &h->d_scan_off, &h->d_node_hash_sorted, &h->d_node_cov,
+		&h->d_node_tip, &h->d_edges_sorted }) release(*b);
+	for (HostBuf* b : { &h->p_node_hashes, &h->p_node_cov, &h->p_node_tip, &h->p_edges }) release_host(*b);
 	for (auto& e : h->ev) if (e) cudaEventDestroy(e);
 	if (h->stream) cudaStreamDestroy(h->stream);
 	for (auto* v : h->owned_bases) delete v;
@@ -775,59 +800,86 @@ int export_instances(mbgfe* h)
 	return 0;
 }
 
-// HashList::sortByHash (MBG/HashList.cpp:245-353): ids = ranks of the canonical hashes; edges re-canonicalised with
-// those ids (already canonical: the device compared the hashes themselves), listed per node forward side first.
+// exclusive prefix sum of n uint32 -> n+1 uint64 on the device (two-level)
+int device_scan(mbgfe* h, const uint32_t* in, uint64_t* out, uint32_t n)
+{
+	const uint32_t tile = SCAN_NT * SCAN_IPT;
+	const uint32_t n_tiles = std::max<uint32_t>(1, (n + tile - 1) / tile);
+	if (int rc = ensure(h, h->d_scan_tot, (size_t)(n_tiles + 1) * 4)) return rc;
+	if (int rc = ensure(h, h->d_scan_off, (size_t)(n_tiles + 2) * 8)) return rc;
+	MBGFE_LAUNCH(k_scan_tile_totals, n_tiles, SCAN_NT, 0, h->stream, in, h->d_scan_tot.as<uint32_t>(), n);
+	MBGFE_LAUNCH(k_scan_u32<1024>, 1, 1024, 0, h->stream, h->d_scan_tot.as<uint32_t>(), h->d_scan_off.as<uint64_t>(), n_tiles);
+	MBGFE_LAUNCH(k_scan_tiles, n_tiles, SCAN_NT, 0, h->stream, in, h->d_scan_off.as<uint64_t>(), out, n);
+	return 0;
+}
+
+// HashList::sortByHash (MBG/HashList.cpp:245-353): ids = ranks of the canonical hashes; edges renumbered with those
+// ids (already canonical: the device compared the hashes themselves), listed per node forward side first.
+// Everything is ordered on the device (kernels.cuh "export"); the host only receives the finished arrays by DMA.
 int export_table(mbgfe* h)
 {
 	if (h->exported_table) return 0;
 	if (!h->have_table) return fail(h, MBGFE_E_STATE, "table requested but none was built (MBGFE_NO_TABLE without mbgfe_exchange_insert)");
 	tick(h, 10);
-	unsigned long long* ctr = h->d_counters.as<unsigned long long>();
-	const uint64_t n_nodes = h->stats.distinct, n_edges = h->stats.distinct_edges;
+	const uint64_t n_nodes = h->stats.distinct, n_edges = h->edge_slots ? h->stats.distinct_edges : 0;
+	const unsigned grid = (unsigned)std::min<uint64_t>((h->node_slots + 255) / 256, (uint64_t)h->sm_count * 16);
+	// ---- nodes: buckets of ~32 entries on the top bits of the canonical hash
+	uint32_t bits = 0;
+	while (bits < 26 && (n_nodes >> bits) > 32) bits++;
+	const uint32_t n_buckets = 1u << bits;
+	const uint32_t shift = 64 - bits;
+	if (int rc = ensure(h, h->d_bucket_count, (size_t)n_buckets * 4 + 64)) return rc;
+	if (int rc = ensure(h, h->d_bucket_begin, (size_t)(n_buckets + 2) * 8)) return rc;
 	if (int rc = ensure(h, h->d_node_out, (n_nodes + 1) * sizeof(NodeOut))) return rc;
-	if (int rc = ensure(h, h->d_edge_out, (n_edges + 1) * sizeof(EdgeOut))) return rc;
-	CU(h, cudaMemsetAsync(ctr + CTR_CURSOR, 0, 16, h->stream));
-	const unsigned grid = (unsigned)std::min<uint64_t>((h->node_slots + 255) / 256, (uint64_t)h->sm_count * 8);
-	MBGFE_LAUNCH(k_export_nodes, grid, 256, 0, h->stream, h->d_nodes.as<NodeSlot>(), h->node_slots, h->d_node_out.as<NodeOut>(), ctr + CTR_CURSOR);
-	if (h->edge_slots) MBGFE_LAUNCH(k_export_edges, grid, 256, 0, h->stream, h->d_edges.as<EdgeSlot>(), h->edge_slots, h->d_edge_out.as<EdgeOut>(), ctr + CTR_CURSOR + 1);
-	std::vector<NodeOut> nodes;
-	std::vector<EdgeOut> edges;
-	if (int rc = download(h, nodes, h->d_node_out, n_nodes)) return rc;
-	if (h->edge_slots) if (int rc = download(h, edges, h->d_edge_out, n_edges)) return rc;
-	CU(h, cudaGetLastError());
-	std::sort(nodes.begin(), nodes.end(), [](const NodeOut& x, const NodeOut& y) { return x.key_hi != y.key_hi ? x.key_hi < y.key_hi : x.key_lo < y.key_lo; });
-	const uint32_t min_cov = 0; // the raw table; -a filtering is applied by the consumers (getCoveredEdges etc.)
-	(void)min_cov;
-	h->h_node_hashes.resize(n_nodes); h->h_node_cov.resize(n_nodes); h->h_node_tip.resize(n_nodes);
-	std::vector<uint32_t> rank_of_slot;
-	rank_of_slot.assign(h->node_slots, 0xffffffffu);
-	for (size_t i = 0; i < n_nodes; i++)
+	if (int rc = ensure(h, h->d_node_hash_sorted, (n_nodes + 1) * 16)) return rc;
+	if (int rc = ensure(h, h->d_node_cov, (n_nodes + 1) * 4)) return rc;
+	if (int rc = ensure(h, h->d_node_tip, n_nodes + 64)) return rc;
+	if (int rc = ensure_host(h, h->p_node_hashes, (n_nodes + 1) * 16)) return rc;
+	if (int rc = ensure_host(h, h->p_node_cov, (n_nodes + 1) * 4)) return rc;
+	if (int rc = ensure_host(h, h->p_node_tip, n_nodes + 64)) return rc;
+	const unsigned rank_grid = (unsigned)std::min<uint64_t>(((uint64_t)n_buckets * 32 + 255) / 256, (uint64_t)h->sm_count * 32);
+	CU(h, cudaMemsetAsync(h->d_bucket_count.p, 0, (size_t)n_buckets * 4, h->stream));
+	MBGFE_LAUNCH(k_node_bucket_count, grid, 256, 0, h->stream, h->d_nodes.as<NodeSlot>(), h->node_slots, shift, h->d_bucket_count.as<uint32_t>());
+	if (int rc = device_scan(h, h->d_bucket_count.as<uint32_t>(), h->d_bucket_begin.as<uint64_t>(), n_buckets)) return rc;
+	CU(h, cudaMemsetAsync(h->d_bucket_count.p, 0, (size_t)n_buckets * 4, h->stream));
+	MBGFE_LAUNCH(k_node_bucket_scatter, grid, 256, 0, h->stream, h->d_nodes.as<NodeSlot>(), h->node_slots, shift, h->d_bucket_begin.as<uint64_t>(),
+		h->d_bucket_count.as<uint32_t>(), h->d_node_out.as<NodeOut>());
+	MBGFE_LAUNCH(k_node_bucket_rank, rank_grid, 256, 0, h->stream, h->d_node_out.as<NodeOut>(), h->d_bucket_begin.as<uint64_t>(), n_buckets,
+		h->d_node_hash_sorted.as<uint64_t>(), h->d_node_cov.as<uint32_t>(), h->d_node_tip.as<uint8_t>(), h->d_nodes.as<NodeSlot>());
+	if (n_nodes)
 	{
-		h->h_node_hashes[i].lo = nodes[i].key_lo; h->h_node_hashes[i].hi = nodes[i].key_hi;
-		h->h_node_cov[i] = nodes[i].count;
-		h->h_node_tip[i] = (uint8_t)(nodes[i].flags & 1);
-		rank_of_slot[nodes[i].slot] = (uint32_t)i;
+		CU(h, cudaMemcpyAsync(h->p_node_hashes.p, h->d_node_hash_sorted.p, n_nodes * 16, cudaMemcpyDeviceToHost, h->stream));
+		CU(h, cudaMemcpyAsync(h->p_node_cov.p, h->d_node_cov.p, n_nodes * 4, cudaMemcpyDeviceToHost, h->stream));
+		CU(h, cudaMemcpyAsync(h->p_node_tip.p, h->d_node_tip.p, n_nodes, cudaMemcpyDeviceToHost, h->stream));
+		h->stats.d2h_bytes += n_nodes * 21;
 	}
-	h->h_edges.resize(edges.size());
-	for (size_t i = 0; i < edges.size(); i++)
+	// ---- edges: node slots -> node ids, buckets of ~32 edges on `from`
+	if (n_edges)
 	{
-		const uint32_t a = (uint32_t)(edges[i].key >> 32), b = (uint32_t)edges[i].key;
-		mbgfe_edge e;
-		e.from = rank_of_slot[a >> 1]; e.from_fw = a & 1;
-		e.to = rank_of_slot[b >> 1]; e.to_fw = b & 1;
-		e.coverage = edges[i].count;
-		e.overlap = (uint32_t)(edges[i].ordered & 0xffffff);
-		h->h_edges[i] = e;
+		uint32_t eshift = 0;
+		while (eshift < 31 && (n_nodes >> eshift) > std::max<uint64_t>(1, n_edges / 32)) eshift++;
+		const uint32_t n_eb = (uint32_t)(n_nodes >> eshift) + 1;
+		if (int rc = ensure(h, h->d_bucket_count, (size_t)n_eb * 4 + 64)) return rc;
+		if (int rc = ensure(h, h->d_bucket_begin, (size_t)(n_eb + 2) * 8)) return rc;
+		if (int rc = ensure(h, h->d_edge_out, (n_edges + 1) * sizeof(EdgeRec))) return rc;
+		if (int rc = ensure(h, h->d_edges_sorted, (n_edges + 1) * sizeof(EdgeRec))) return rc;
+		if (int rc = ensure_host(h, h->p_edges, (n_edges + 1) * sizeof(mbgfe_edge))) return rc;
+		const unsigned egrid = (unsigned)std::min<uint64_t>((h->edge_slots + 255) / 256, (uint64_t)h->sm_count * 16);
+		const unsigned erank_grid = (unsigned)std::min<uint64_t>(((uint64_t)n_eb * 32 + 255) / 256, (uint64_t)h->sm_count * 32);
+		CU(h, cudaMemsetAsync(h->d_bucket_count.p, 0, (size_t)n_eb * 4, h->stream));
+		MBGFE_LAUNCH(k_edge_bucket_count, egrid, 256, 0, h->stream, h->d_edges.as<EdgeSlot>(), h->edge_slots, h->d_nodes.as<NodeSlot>(), eshift, h->d_bucket_count.as<uint32_t>());
+		if (int rc = device_scan(h, h->d_bucket_count.as<uint32_t>(), h->d_bucket_begin.as<uint64_t>(), n_eb)) return rc;
+		CU(h, cudaMemsetAsync(h->d_bucket_count.p, 0, (size_t)n_eb * 4, h->stream));
+		MBGFE_LAUNCH(k_edge_bucket_scatter, egrid, 256, 0, h->stream, h->d_edges.as<EdgeSlot>(), h->edge_slots, h->d_nodes.as<NodeSlot>(), eshift,
+			h->d_bucket_begin.as<uint64_t>(), h->d_bucket_count.as<uint32_t>(), h->d_edge_out.as<EdgeRec>());
+		MBGFE_LAUNCH(k_edge_bucket_rank, erank_grid, 256, 0, h->stream, h->d_edge_out.as<EdgeRec>(), h->d_bucket_begin.as<uint64_t>(), n_eb, h->d_edges_sorted.as<EdgeRec>());
+		CU(h, cudaMemcpyAsync(h->p_edges.p, h->d_edges_sorted.p, n_edges * sizeof(mbgfe_edge), cudaMemcpyDeviceToHost, h->stream));
+		h->stats.d2h_bytes += n_edges * sizeof(mbgfe_edge);
 	}
-	std::sort(h->h_edges.begin(), h->h_edges.end(), [](const mbgfe_edge& x, const mbgfe_edge& y)
-	{
-		if (x.from != y.from) return x.from < y.from;
-		if (x.from_fw != y.from_fw) return x.from_fw > y.from_fw;
-		if (x.to != y.to) return x.to < y.to;
-		return x.to_fw < y.to_fw;
-	});
 	tick(h, 11);
 	CU(h, cudaStreamSynchronize(h->stream));
+	CU(h, cudaGetLastError());
+	h->n_nodes_out = n_nodes; h->n_edges_out = n_edges;
 	h->stats.ms_export = elapsed(h, 10, 11);
 	h->exported_table = true;
 	return 0;
@@ -847,7 +899,7 @@ uint64_t mbgfe_count(mbgfe* h, int what)
 		case MBGFE_POSES: if (export_parts(h)) return 0; return (h->prm.flags & MBGFE_KEEP_POSES) ? h->stats.codes + h->parts.size() : 0;
 		case MBGFE_POSITIONS: case MBGFE_HASHES: return h->n_inst;
 		case MBGFE_NODE_HASHES: case MBGFE_NODE_COVERAGE: case MBGFE_NODE_TIP: return h->have_table ? h->stats.distinct : 0;
-		case MBGFE_EDGES: return h->have_table ? h->stats.distinct_edges : 0;
+		case MBGFE_EDGES: return (h->have_table && h->edge_slots) ? h->stats.distinct_edges : 0;
 	}
 	return 0;
 }
@@ -867,10 +919,10 @@ const void* mbgfe_data(mbgfe* h, int what)
 			if (export_codes(h)) return nullptr; return h->h_poses.data();
 		case MBGFE_POSITIONS: if (export_instances(h)) return nullptr; return h->h_positions.data();
 		case MBGFE_HASHES: if (export_instances(h)) return nullptr; return h->h_hashes.data();
-		case MBGFE_NODE_HASHES: if (export_table(h)) return nullptr; return h->h_node_hashes.data();
-		case MBGFE_NODE_COVERAGE: if (export_table(h)) return nullptr; return h->h_node_cov.data();
-		case MBGFE_NODE_TIP: if (export_table(h)) return nullptr; return h->h_node_tip.data();
-		case MBGFE_EDGES: if (export_table(h)) return nullptr; return h->h_edges.data();
+		case MBGFE_NODE_HASHES: if (export_table(h)) return nullptr; return h->p_node_hashes.p;
+		case MBGFE_NODE_COVERAGE: if (export_table(h)) return nullptr; return h->p_node_cov.p;
+		case MBGFE_NODE_TIP: if (export_table(h)) return nullptr; return h->p_node_tip.p;
+		case MBGFE_EDGES: if (export_table(h)) return nullptr; return h->p_edges.p;
 	}
 	fail(h, MBGFE_E_PARAM, "unknown result array %d", what);
 	return nullptr;

@@ -68,6 +68,6 @@ class DistributedCounter:
         self.sent_bytes = n_send * 32
 
     def download_counts(self):
-        cov = self.fe.node_coverage()
-        self.fe.node_hashes()
-        return int(cov.sum())
+        cov = self.fe.node_coverage(copy=False)
+        self.fe.node_hashes(copy=False)
+        return int(cov.sum(dtype=np.uint64))

@@ -88,12 +88,14 @@ def load_library(path=None):
     return L
 
 
-def _array(ptr, count, dtype):
+def _array(ptr, count, dtype, copy=True):
+    """numpy array over library-owned memory; copy=False gives a view that is valid until the next run on the handle"""
     dtype = np.dtype(dtype)
     if count == 0 or not ptr:
         return np.zeros(0, dtype=dtype)
     buf = (C.c_char * (count * dtype.itemsize)).from_address(ptr)
-    return np.frombuffer(buf, dtype=dtype).copy()
+    a = np.frombuffer(buf, dtype=dtype)
+    return a.copy() if copy else a
 
 
 class PinnedBuffer:
@@ -184,12 +186,12 @@ class MbgFrontEnd:
     def count(self, what):
         return int(self.lib.mbgfe_count(self.handle, what))
 
-    def _data(self, what, dtype, per=1):
+    def _data(self, what, dtype, per=1, copy=True):
         n = self.count(what)
         ptr = self.lib.mbgfe_data(self.handle, what)
         if n and not ptr:
             self._check(-6)
-        return _array(ptr, n * per, dtype)
+        return _array(ptr, n * per, dtype, copy)
 
     def parts(self):
         return self._data(PARTS, PART_DTYPE)
@@ -206,17 +208,17 @@ class MbgFrontEnd:
     def hashes(self):
         return self._data(HASHES, "<u8", 2).reshape(-1, 2)
 
-    def node_hashes(self):
-        return self._data(NODE_HASHES, "<u8", 2).reshape(-1, 2)
+    def node_hashes(self, copy=True):
+        return self._data(NODE_HASHES, "<u8", 2, copy).reshape(-1, 2)
 
-    def node_coverage(self):
-        return self._data(NODE_COVERAGE, "<u4")
+    def node_coverage(self, copy=True):
+        return self._data(NODE_COVERAGE, "<u4", 1, copy)
 
-    def node_tip(self):
-        return self._data(NODE_TIP, "u1")
+    def node_tip(self, copy=True):
+        return self._data(NODE_TIP, "u1", 1, copy)
 
-    def edges(self):
-        return self._data(EDGES, "<u4", 6).reshape(-1, 6)
+    def edges(self, copy=True):
+        return self._data(EDGES, "<u4", 6, copy).reshape(-1, 6)
 
     def stats(self):
         s = Stats()
