@@ -180,14 +180,15 @@ __device__ __forceinline__ uint32_t complement_code(uint32_t code)
 	return CODES_BEFORE[m] + out * m + overhang;
 }
 
-// tab_hash[c] = char_hash(c), tab_hash_rc[c] = char_hash(complement(c)), tab_comp[c] = complement(c)
-__global__ void k_build_tables(uint64_t* __restrict__ tab_hash, uint64_t* __restrict__ tab_hash_rc, uint16_t* __restrict__ tab_comp)
+// tab_hash[c] = char_hash(c), tab_comp[c] = complement(c), tab_pair[c] = { char_hash(c), char_hash(complement(c)) }
+__global__ void k_build_tables(uint64_t* __restrict__ tab_hash, uint4* __restrict__ tab_pair, uint16_t* __restrict__ tab_comp)
 {
 	uint32_t c = blockIdx.x * blockDim.x + threadIdx.x;
 	if (c >= MAX_CODE) return;
-	uint32_t rc = complement_code(c);
-	tab_hash[c] = char_hash(c);
-	tab_hash_rc[c] = char_hash(rc);
+	const uint32_t rc = complement_code(c);
+	const uint64_t hf = char_hash(c), hb = char_hash(rc);
+	tab_hash[c] = hf;
+	tab_pair[c] = make_uint4((uint32_t)hf, (uint32_t)(hf >> 32), (uint32_t)hb, (uint32_t)(hb >> 32));
 	tab_comp[c] = (uint16_t)rc;
 }
 
@@ -566,175 +567,234 @@ __global__ void __launch_bounds__(NT) k_unpack_symbols(SegTable seg, const uint6
 
 // ----------------------------------------------------------------- K3a: rolling s-mer hash + syncmer selection
 
-// Shared-memory plan of k_select for history H (multiple of 64, >= k-1) and tile T (multiple of 64):
-//   P,Q   pad(H + T + 1) x 8 B each : XOR prefix of rotr(hash[c_j], j) / rotl(hash_rc[c_j], j), j = buffer-local index
-//   hv    (T + W8) x 8 B            : canonical s-mer hash at buffer-local s-mer index, W8 = roundup8(w) + 8
-//   bmin, bmin2                     : minima over aligned blocks of 8 hashes, and one sparse-table level over those
-// pad(l) = l + l/8 spreads the per-thread runs of 8 consecutive prefix values over the banks.
-struct SelectPlan { uint32_t H, T, W8, smem_bytes; };
-__host__ __device__ __forceinline__ uint32_t pad8(uint32_t l) { return l + (l >> 3); }
+// 64-bit rotations by a value known to be in 0..63
+__device__ __forceinline__ uint64_t rotl_c(uint64_t v, uint32_t r) { return r ? ((v << r) | (v >> (64 - r))) : v; }
+__device__ __forceinline__ uint64_t rotr_c(uint64_t v, uint32_t r) { return r ? ((v >> r) | (v << (64 - r))) : v; }
+__device__ __forceinline__ uint64_t u64_of(uint32_t lo, uint32_t hi) { return ((uint64_t)hi << 32) | lo; }
+
+// Shared-memory plan of k_select<NT>.  A tile is T = 8 NT codes: every thread owns 8 consecutive codes / s-mer hashes /
+// k-mer decisions per tile, kept in registers.  Three stages run per tile with fixed lags (all multiples of 8):
+//   A  prefix values for codes [t0, t0+T)          -> pq ring   (16 B per prefix index: P', Q')
+//   B  s-mer hashes for [t0-LH, t0-LH+T)           -> h ring    (8 B per s-mer) + per-block minimum + minimum of the
+//                                                                first r hashes of each block of 8
+//   C  k-mer decisions for [t0-LH-LW, t0-LH-LW+T)  -> 1 bit per position
+// Ring layouts are padded per block of 8 entries (pq: 9 x 16 B, h: 10 x 8 B) so that threads that own consecutive blocks
+// hit distinct banks with 128-bit accesses.
+struct SelectPlan { uint32_t LH, LW, NBP, NBH, smem_bytes; };
 
 // K3a: FastHasher + findSyncmerPositions (MBG/FastHasher.h:16-32, MBG/ReadHelper.h:31-79) without the sequential
-// dependence: with P[n] = XOR_{j<n} rotr(h[c_j], j) and Q[n] = XOR_{j<n} rotl(hrc[c_j], j) the rolling hash of the
-// s-mer at i is min(rotl(P[i+s]^P[i], i+s-1), rotr(Q[i+s]^Q[i], i)), so a tile needs two XOR block
-// scans and then every s-mer is independent.  k-mer p is selected iff hash[p] or hash[p+w-1] equals the minimum of
-// hash[p..p+w-1] (ties kept).  The window minimum is assembled from minima of aligned blocks of 8
-// hashes plus one sparse-table level over those, so each thread decides 8 consecutive k-mers with O(1) reads.
-// One CTA per segment walks the segment in tiles of T new codes; the prefix values of the last H codes stay in
-// shared memory, so no code is hashed twice.  Output: 1 bit per code position + selected count per segment.
+// dependence.  The reference rolls fw = rotl(fw,1)^H[c] with the outgoing character removed; with the "moving frame"
+// prefixes  P'[n+1] = rotl(P'[n] ^ H[c_n], 1)  and  Q'[n+1] = rotr(Q'[n] ^ H[comp c_n], 1)  (P'[0] = Q'[0] = 0) the hash
+// of the s-mer starting at i is
+//     fw(i) = rotr(P'[i+s], 1) ^ rotl(P'[i], s-1),   bw(i) = rotl(Q'[i+s], s) ^ Q'[i],   hash = min(fw, bw)
+// (SURVEY.md H3 rewritten so that no rotation depends on the position).  Prefixes are a scan with the operator
+// (a, b) -> rotl(a, len b) ^ b; a thread's 8 codes, a warp's 256 and a tile's 8 NT codes span multiples of 8 / 64
+// positions, so every rotation in the scan is by a compile-time constant and warp/tile carries are plain XORs.
+// k-mer p is selected iff hash[p] or hash[p+w-1] equals the minimum of hash[p..p+w-1] (ties kept).  With
+// w-1 = 8a + r the window of p = 8b+j is: the suffix of block b from j, blocks b+1..b+a-1 (block minima), and the
+// first r+j+1 hashes counted from the start of block b+a (a running minimum over the 8 "last" hashes, seeded with the
+// minimum of the first r hashes of that block).
+// One CTA per segment.  Output: 1 bit per code position + selected count per segment.
 // Algorithmic bytes: 2 read per code + 1/8 written per code.
 template <int NT>
 __global__ void __launch_bounds__(NT) k_select(SegTable seg, const uint16_t* __restrict__ codes, const uint32_t* __restrict__ seg_c2,
-	const uint64_t* __restrict__ tab_hash, const uint64_t* __restrict__ tab_hash_rc, uint8_t* __restrict__ selmask, uint32_t* __restrict__ seg_nsel,
-	uint32_t k, uint32_t w, SelectPlan plan)
+	const uint4* __restrict__ tab_pair, uint8_t* __restrict__ selmask, uint32_t* __restrict__ seg_nsel, uint32_t k, uint32_t w, SelectPlan plan)
 {
+	constexpr uint32_t T = NT * 8;
+	constexpr uint64_t INF = ~0ull;
 	MBGFE_DYN_SMEM(smem_raw);
-	__shared__ Xor2 warp_x[NT / 32];
+	__shared__ uint4 small_tab[4];
+	__shared__ Xor2 warp_tot[NT / 32];
 	__shared__ uint32_t warp_tmp[NT / 32];
 	const uint32_t g = blockIdx.x;
 	if (g >= seg.n) return;
 	const uint32_t n = seg_c2[g];
 	if (n < k) { if (threadIdx.x == 0) seg_nsel[g] = 0; return; }
-	const uint32_t H = plan.H, T = plan.T;
-	const uint32_t n_pref = pad8(H + T + 1) + 1;
-	uint64_t* P = (uint64_t*)smem_raw;
-	uint64_t* Q = P + n_pref;
-	uint64_t* hv = Q + n_pref;
-	const uint32_t n_h = T + plan.W8;
-	uint64_t* bmin = hv + n_h;
-	const uint32_t n_blocks = n_h / 8;
-	uint64_t* bmin2 = bmin + n_blocks;
+	const uint32_t NBP = plan.NBP, NBH = plan.NBH, LH = plan.LH, LW = plan.LW;
+	uint4* pq = (uint4*)smem_raw;                                  // NBP blocks x 9 entries
+	uint64_t* hr = (uint64_t*)(pq + (size_t)NBP * 9);              // NBH blocks x 10 entries
+	uint64_t* bm = hr + (size_t)NBH * 10;                          // NBH block minima
+	uint64_t* pre = bm + NBH;                                      // NBH minima of the first r hashes of a block
 	const uint64_t out0 = seg.out_base[g];
 	const uint16_t* __restrict__ c = codes + out0;
 	uint8_t* __restrict__ mask_out = selmask + (out0 >> 3);
 	const uint32_t s = k - w + 1;
-	const uint32_t n_kmers = n - k + 1;
-	const uint32_t n_smers = n - s + 1;
-	// window [p, p+w-1] with w-1 = 8a + r
+	const uint32_t n_kmers = n - k + 1, n_smers = n - s + 1;
 	const uint32_t a = (w - 1) >> 3, r = (w - 1) & 7;
-	uint32_t lvl = 0;
-	if (a >= 2) { while ((2u << lvl) <= a - 1) lvl++; }
-	const uint32_t span = 1u << lvl;
-	uint32_t total_sel = 0;
-	// buffer-local index l  <->  global code / s-mer / k-mer index (tile0 - H + l)
-	for (uint32_t i = threadIdx.x; i <= H; i += NT) { P[pad8(i)] = 0; Q[pad8(i)] = 0; }
+	const uint32_t sa = s >> 3, sr = s & 7;
+	const uint32_t rot_s1 = (s - 1) & 63, rot_s = s & 63;
+	const uint32_t lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+	if (threadIdx.x < 4) small_tab[threadIdx.x] = __ldg(tab_pair + threadIdx.x);
+	if (threadIdx.x == 0) pq[0] = make_uint4(0, 0, 0, 0);          // P'[0] = Q'[0] = 0
+	// ring cursors (in blocks) of the first block each stage touches in the current tile
+	uint32_t curA = 0;                                             // pq block of prefix index t0
+	uint32_t curBp = (NBP - (LH >> 3) % NBP) % NBP;                // pq block of prefix index t0 - LH
+	uint32_t curBh = (NBH - (LH >> 3) % NBH) % NBH;                // h block of s-mer t0 - LH
+	uint32_t curC = (NBH - ((LH + LW) >> 3) % NBH) % NBH;          // h block of k-mer t0 - LH - LW
 	Xor2 carry = { 0, 0 };
+	uint32_t my_sel = 0;
 	__syncthreads();
-	for (uint32_t tile0 = 0; ; tile0 += T)
+	for (uint32_t t0 = 0; t0 < n + LH + LW; t0 += T)
 	{
-		// ---- XOR prefix over the new codes [tile0, tile0 + n_new): buffer-local (H, H + n_new]
-		const uint32_t n_new = min(T, n - tile0);
-		const uint32_t per = (T + NT - 1) / NT;
-		const uint32_t lo = min(n_new, threadIdx.x * per), hi = min(n_new, lo + per);
-		Xor2 acc = { 0, 0 };
-		for (uint32_t i = lo; i < hi; i++)
+		// ------------------------------------------------------------------ stage A: prefixes of the new codes
+		if (t0 < n)
 		{
-			const uint32_t code = c[tile0 + i];
-			const uint32_t l = H + i;          // only l mod 64 matters; H and T are multiples of 64
-			acc.a ^= rotr64(__ldg(tab_hash + code), l);
-			acc.b ^= rotl64(__ldg(tab_hash_rc + code), l);
-			P[pad8(l + 1)] = acc.a; Q[pad8(l + 1)] = acc.b;
+			const uint32_t j0 = t0 + 8 * threadIdx.x;
+			uint4 cw = make_uint4(0, 0, 0, 0);
+			if (j0 < n) cw = __ldg((const uint4*)(c + j0));
+			const uint32_t cws[4] = { cw.x, cw.y, cw.z, cw.w };
+			uint64_t hf[8], hb[8];
+#pragma unroll
+			for (int e = 0; e < 8; e++)
+			{
+				uint32_t code = (cws[e >> 1] >> ((e & 1) * 16)) & 0xffff;
+				if (j0 + e >= n) code = 0;
+				uint4 v = small_tab[code & 3];
+				if (code >= 4) v = __ldg(tab_pair + code);
+				hf[e] = u64_of(v.x, v.y); hb[e] = u64_of(v.z, v.w);
+			}
+			uint64_t ip = 0, iq = 0;
+#pragma unroll
+			for (int e = 0; e < 8; e++) { ip = rotl_c(ip ^ hf[e], 1); iq = rotr_c(iq ^ hb[e], 1); }
+			// inclusive warp scan; the value coming from d lanes below is advanced over the 8d codes gathered so far
+#pragma unroll
+			for (int d = 1; d < 32; d <<= 1)
+			{
+				const uint64_t tp = __shfl_up_sync(FULL, ip, d), tq = __shfl_up_sync(FULL, iq, d);
+				if (lane >= (uint32_t)d) { ip ^= rotl_c(tp, (8 * d) & 63); iq ^= rotr_c(tq, (8 * d) & 63); }
+			}
+			if (lane == 31) { Xor2 t; t.a = ip; t.b = iq; warp_tot[wid] = t; }
+			uint64_t ep = __shfl_up_sync(FULL, ip, 1), eq = __shfl_up_sync(FULL, iq, 1);
+			if (lane == 0) { ep = 0; eq = 0; }
+			__syncthreads();
+			Xor2 wbase = carry;
+#pragma unroll
+			for (int i = 0; i < NT / 32; i++) { const Xor2 t = warp_tot[i]; if (i < (int)wid) { wbase.a ^= t.a; wbase.b ^= t.b; } carry.a ^= t.a; carry.b ^= t.b; }
+			uint64_t pv = rotl_c(wbase.a, (8 * lane) & 63) ^ ep, qv = rotr_c(wbase.b, (8 * lane) & 63) ^ eq;
+			// prefix index j0+e+1 lives in block curA + thread (offsets 1..7) and the next block (offset 0)
+			uint32_t blk = curA + threadIdx.x; if (blk >= NBP) blk -= NBP;
+			uint32_t blk2 = blk + 1; if (blk2 >= NBP) blk2 -= NBP;
+			uint4* dst = pq + (size_t)blk * 9;
+#pragma unroll
+			for (int e = 0; e < 8; e++)
+			{
+				pv = rotl_c(pv ^ hf[e], 1); qv = rotr_c(qv ^ hb[e], 1);
+				const uint4 v = make_uint4((uint32_t)pv, (uint32_t)(pv >> 32), (uint32_t)qv, (uint32_t)(qv >> 32));
+				if (e < 7) dst[e + 1] = v; else pq[(size_t)blk2 * 9] = v;
+			}
 		}
-		Xor2 tile_x;
-		Xor2 off = block_exclusive_xor<NT>(acc, warp_x, tile_x);
-		off.a ^= carry.a; off.b ^= carry.b;
-		for (uint32_t i = lo; i < hi; i++) { P[pad8(H + i + 1)] ^= off.a; Q[pad8(H + i + 1)] ^= off.b; }
-		carry.a ^= tile_x.a; carry.b ^= tile_x.b;
 		__syncthreads();
-		// ---- k-mers decided by this tile: buffer-local [0, T) == global [tile0 - H, tile0 - H + T).  The last tile
-		//      (all codes loaded) decides everything that is left, in rounds of T positions.
-		const bool all_loaded = tile0 + T >= n;
-		const int64_t first_kmer = (int64_t)tile0 - (int64_t)H;
-		for (uint32_t round = 0; ; round += T)
+		// ------------------------------------------------------------------ stage B: s-mer hashes
 		{
-			// canonical hashes of the s-mers at buffer-local [round, round + n_h)
-			for (uint32_t i = threadIdx.x; i < n_h; i += NT)
+			const int64_t i0 = (int64_t)t0 - (int64_t)LH + 8 * (int64_t)threadIdx.x;
+			if (i0 >= 0)
 			{
-				const uint32_t l = round + i;
-				const int64_t gi = first_kmer + l;
-				uint64_t v = ~0ull;
-				if (gi >= 0 && gi < (int64_t)n_smers && l + s <= H + n_new)
+				uint32_t b0 = curBp + threadIdx.x; if (b0 >= NBP) b0 -= NBP;
+				uint32_t b1 = b0 + sa; if (b1 >= NBP) b1 -= NBP;
+				uint32_t b2 = b1 + 1; if (b2 >= NBP) b2 -= NBP;
+				const uint4* x0 = pq + (size_t)b0 * 9;
+				const uint4* y1 = pq + (size_t)b1 * 9;
+				const uint4* y2 = pq + (size_t)b2 * 9;
+				uint64_t hv[8];
+				uint64_t m = INF, mpre = INF;
+#pragma unroll
+				for (int e = 0; e < 8; e++)
 				{
-					const uint64_t fw = rotl64(P[pad8(l + s)] ^ P[pad8(l)], l + s - 1);
-					const uint64_t bw = rotr64(Q[pad8(l + s)] ^ Q[pad8(l)], l);
-					v = fw < bw ? fw : bw;
+					uint64_t v = INF;
+					if ((uint64_t)i0 + e < n_smers)
+					{
+						const uint4 x = x0[e];
+						const uint4 y = (e + sr < 8) ? y1[e + sr] : y2[e + sr - 8];
+						const uint64_t fw = rotr_c(u64_of(y.x, y.y), 1) ^ rotl_c(u64_of(x.x, x.y), rot_s1);
+						const uint64_t bw = rotl_c(u64_of(y.z, y.w), rot_s) ^ u64_of(x.z, x.w);
+						v = fw < bw ? fw : bw;
+					}
+					hv[e] = v;
+					if ((uint32_t)e == r) mpre = m;      // minimum of the first r hashes of the block
+					m = v < m ? v : m;
 				}
-				hv[i] = v;
-			}
-			__syncthreads();
-			for (uint32_t b = threadIdx.x; b < n_blocks; b += NT)
-			{
-				uint64_t m = hv[8 * b];
+				uint32_t hbk = curBh + threadIdx.x; if (hbk >= NBH) hbk -= NBH;
+				uint4* dst = (uint4*)(hr + (size_t)hbk * 10);
 #pragma unroll
-				for (int t = 1; t < 8; t++) m = min(m, hv[8 * b + t]);
-				bmin[b] = m;
+				for (int e = 0; e < 4; e++)
+					dst[e] = make_uint4((uint32_t)hv[2 * e], (uint32_t)(hv[2 * e] >> 32), (uint32_t)hv[2 * e + 1], (uint32_t)(hv[2 * e + 1] >> 32));
+				bm[hbk] = m;
+				pre[hbk] = mpre;
 			}
-			__syncthreads();
-			for (uint32_t b = threadIdx.x; b < n_blocks; b += NT)
+		}
+		__syncthreads();
+		// ------------------------------------------------------------------ stage C: decisions
+		{
+			const int64_t p0 = (int64_t)t0 - (int64_t)LH - (int64_t)LW + 8 * (int64_t)threadIdx.x;
+			if (p0 >= 0 && p0 < (int64_t)n_kmers)
 			{
-				uint64_t m = bmin[b];
-				for (uint32_t t = 1; t < span && b + t < n_blocks; t++) m = min(m, bmin[b + t]);
-				bmin2[b] = m;
-			}
-			__syncthreads();
-			uint32_t my_count = 0;
-			for (uint32_t b = threadIdx.x; b < T / 8; b += NT)
-			{
-				const int64_t gp0 = first_kmer + round + 8 * b;
-				if (gp0 < 0 || gp0 >= (int64_t)n_kmers) continue;
-				// 8 k-mers at buffer-local positions round + 8b + j  (hv index 8b + j)
-				uint64_t own[8], suf[8];
+				uint32_t d0 = curC + threadIdx.x; if (d0 >= NBH) d0 -= NBH;
+				uint64_t own[8];
+				{
+					const uint4* src = (const uint4*)(hr + (size_t)d0 * 10);
 #pragma unroll
-				for (int t = 0; t < 8; t++) own[t] = hv[8 * b + t];
-				suf[7] = own[7];
-#pragma unroll
-				for (int t = 6; t >= 0; t--) suf[t] = min(own[t], suf[t + 1]);
-				uint64_t core = ~0ull;                                   // blocks b+1 .. b+a-1
-				if (a >= 2) core = min(bmin2[b + 1], bmin2[b + a - span]);
-				const uint64_t core_plus = a >= 1 ? min(core, bmin[b + a]) : ~0ull; // blocks b+1 .. b+a
+					for (int e = 0; e < 4; e++) { const uint4 v = src[e]; own[2 * e] = u64_of(v.x, v.y); own[2 * e + 1] = u64_of(v.z, v.w); }
+				}
 				uint32_t bits = 0;
-#pragma unroll
-				for (int jj = 0; jj < 8; jj++)
+				if (a == 0)
 				{
-					uint64_t wmin, last;
-					if (a == 0)
+					// window inside this block and the next one
+					uint32_t d1 = d0 + 1; if (d1 >= NBH) d1 -= NBH;
+					uint64_t ext[16];
+#pragma unroll
+					for (int e = 0; e < 8; e++) { ext[e] = own[e]; ext[8 + e] = hr[(size_t)d1 * 10 + e]; }
+#pragma unroll
+					for (int j = 0; j < 8; j++)
 					{
-						wmin = own[jj]; last = own[jj];
-						for (uint32_t t = 1; t <= r; t++) { last = hv[8 * b + jj + t]; wmin = min(wmin, last); }
+						uint64_t wmin = ext[j], last = ext[j];
+#pragma unroll
+						for (int t = 1; t < 8; t++) if ((uint32_t)t <= r) { last = ext[j + t]; wmin = last < wmin ? last : wmin; }
+						if (own[j] == wmin || last == wmin) bits |= 1u << j;
 					}
-					else
-					{
-						const uint32_t e = jj + r;                       // window end = block b+a, offset e
-						const uint32_t eb = e < 8 ? b + a : b + a + 1;
-						const uint32_t eo = e < 8 ? e : e - 8;
-						uint64_t pre = hv[8 * eb];
-						for (uint32_t t = 1; t <= eo; t++) pre = min(pre, hv[8 * eb + t]);
-						last = hv[8 * eb + eo];
-						wmin = min(suf[jj], min(pre, e < 8 ? core : core_plus));
-					}
-					if (gp0 + jj < (int64_t)n_kmers && (own[jj] == wmin || last == wmin)) bits |= 1u << jj;
 				}
-				mask_out[gp0 >> 3] = (uint8_t)bits;
-				my_count += __popc(bits);
+				else
+				{
+					uint64_t suf[8];
+					suf[7] = own[7];
+#pragma unroll
+					for (int t = 6; t >= 0; t--) suf[t] = own[t] < suf[t + 1] ? own[t] : suf[t + 1];
+					uint64_t core = INF;                                 // blocks b+1 .. b+a-1
+					uint32_t bi = d0;
+					for (uint32_t t = 1; t < a; t++)
+					{
+						bi++; if (bi >= NBH) bi -= NBH;
+						const uint64_t v = bm[bi];
+						core = v < core ? v : core;
+					}
+					uint32_t e0 = d0 + a; if (e0 >= NBH) e0 -= NBH;      // block that holds the window ends
+					uint32_t e1 = e0 + 1; if (e1 >= NBH) e1 -= NBH;
+					uint64_t run = pre[e0];
+					const uint64_t* l0 = hr + (size_t)e0 * 10;
+					const uint64_t* l1 = hr + (size_t)e1 * 10;
+#pragma unroll
+					for (int j = 0; j < 8; j++)
+					{
+						const uint64_t last = (j + r < 8) ? l0[j + r] : l1[j + r - 8];
+						run = last < run ? last : run;
+						uint64_t wmin = suf[j] < core ? suf[j] : core;
+						wmin = run < wmin ? run : wmin;
+						if (own[j] == wmin || last == wmin) bits |= 1u << j;
+					}
+				}
+				const uint32_t left = n_kmers - (uint32_t)p0;
+				if (left < 8) bits &= (1u << left) - 1;
+				mask_out[p0 >> 3] = (uint8_t)bits;
+				my_sel += __popc(bits);
 			}
-			uint32_t round_sel;
-			block_exclusive_sum<NT>(my_count, warp_tmp, round_sel);
-			total_sel += round_sel;
-			if (!all_loaded) break;
-			if (first_kmer + (int64_t)round + (int64_t)T >= (int64_t)n_kmers) break;
 		}
-		if (all_loaded) break;
-		// ---- slide the history: buffer-local [T, T+H] -> [0, H] (ranges may overlap: read a chunk, barrier, write it)
-		for (uint32_t base = 0; base <= H; base += NT)
-		{
-			const uint32_t i = base + threadIdx.x;
-			uint64_t pv = 0, qv = 0;
-			if (i <= H) { pv = P[pad8(T + i)]; qv = Q[pad8(T + i)]; }
-			__syncthreads();
-			if (i <= H) { P[pad8(i)] = pv; Q[pad8(i)] = qv; }
-			__syncthreads();
-		}
+		__syncthreads();
+		curA += NT; if (curA >= NBP) curA -= NBP;
+		curBp += NT; if (curBp >= NBP) curBp -= NBP;
+		curBh += NT; if (curBh >= NBH) curBh -= NBH;
+		curC += NT; if (curC >= NBH) curC -= NBH;
 	}
+	uint32_t total_sel;
+	block_exclusive_sum<NT>(my_sel, warp_tmp, total_sel);
 	if (threadIdx.x == 0) seg_nsel[g] = total_sel;
 }
 

@@ -66,7 +66,7 @@ struct mbgfe
 	SelectPlan plan;
 
 	// code tables
-	DevBuf tab_hash, tab_hash_rc, tab_comp;
+	DevBuf tab_hash, tab_pair, tab_comp;
 
 	// pending input
 	std::vector<HostChunk> pending;
@@ -237,20 +237,14 @@ int upload_segments(mbgfe* h)
 SelectPlan make_plan(uint32_t k, uint32_t w, size_t max_smem, bool& ok)
 {
 	SelectPlan p;
-	p.H = (k - 1 + 63) & ~63u;
-	p.W8 = ((w + 7) & ~7u) + 8;
-	ok = false;
-	for (uint32_t T : { 4096u, 2048u, 1024u, 512u })
-	{
-		p.T = T;
-		size_t n_pref = pad8(p.H + T + 1) + 1;
-		size_t n_h = T + p.W8;
-		size_t bytes = 2 * n_pref * 8 + n_h * 8 + 2 * (n_h / 8) * 8 + 64;
-		p.smem_bytes = (uint32_t)bytes;
-		// keep at least two CTAs per SM for the default parameters
-		size_t budget = T == 4096 ? max_smem / 2 - 2048 : max_smem - 4096;
-		if (bytes <= budget) { ok = true; break; }
-	}
+	const uint32_t s = k - w + 1, a = (w - 1) >> 3, T = NT_SELECT * 8;
+	p.LH = (s - 1 + 7) & ~7u;
+	p.LW = 8 * (a + 1);
+	p.NBP = (p.LH + T) / 8 + 2;
+	p.NBH = NT_SELECT + p.LW / 8 + 2;
+	const size_t bytes = (size_t)p.NBP * 9 * 16 + (size_t)p.NBH * 10 * 8 + (size_t)p.NBH * 16 + 64;
+	p.smem_bytes = (uint32_t)bytes;
+	ok = bytes + 2048 <= max_smem;
 	return p;
 }
 
@@ -413,12 +407,12 @@ int mbgfe_create(const mbgfe_params* prm, mbgfe** out)
 	h->max_smem = prop.sharedMemPerBlockOptin;
 	bool ok = false;
 	h->plan = make_plan(prm->k, prm->w, h->max_smem, ok);
-	if (!ok) return bail(fail(h, MBGFE_E_LIMIT, "k=%u needs more shared memory than one SM has (limit about k=9000)", prm->k));
+	if (!ok) return bail(fail(h, MBGFE_E_LIMIT, "k=%u needs more shared memory than one SM has (limit about k=11000)", prm->k));
 	if (cudaStreamCreate(&h->stream) != cudaSuccess) return bail(fail(h, MBGFE_E_CUDA, "cudaStreamCreate failed"));
 	for (auto& e2 : h->ev) if (cudaEventCreate(&e2) != cudaSuccess) return bail(fail(h, MBGFE_E_CUDA, "cudaEventCreate failed"));
-	if (ensure(h, h->tab_hash, MAX_CODE * 8) || ensure(h, h->tab_hash_rc, MAX_CODE * 8) || ensure(h, h->tab_comp, MAX_CODE * 2) ||
+	if (ensure(h, h->tab_hash, MAX_CODE * 8) || ensure(h, h->tab_pair, MAX_CODE * 16) || ensure(h, h->tab_comp, MAX_CODE * 2) ||
 		ensure(h, h->d_counters, (CTR_OWNER + prm->world + 8) * 8)) return bail(MBGFE_E_CUDA);
-	MBGFE_LAUNCH(k_build_tables, (MAX_CODE + 255) / 256, 256, 0, h->stream, h->tab_hash.as<uint64_t>(), h->tab_hash_rc.as<uint64_t>(), h->tab_comp.as<uint16_t>());
+	MBGFE_LAUNCH(k_build_tables, (MAX_CODE + 255) / 256, 256, 0, h->stream, h->tab_hash.as<uint64_t>(), h->tab_pair.as<uint4>(), h->tab_comp.as<uint16_t>());
 	cudaFuncSetAttribute(k_select<NT_SELECT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->plan.smem_bytes);
 	if (cudaStreamSynchronize(h->stream) != cudaSuccess || cudaGetLastError() != cudaSuccess)
 		return bail(fail(h, MBGFE_E_CUDA, "table kernel failed: is this an sm_100 device?"));
@@ -429,7 +423,7 @@ int mbgfe_create(const mbgfe_params* prm, mbgfe** out)
 void mbgfe_destroy(mbgfe* h)
 {
 	if (!h) return;
-	for (DevBuf* b : { &h->tab_hash, &h->tab_hash_rc, &h->tab_comp, &h->d_ascii, &h->d_packed, &h->d_nonacgt, &h->d_counters, &h->d_seg_in, &h->d_seg_out,
+	for (DevBuf* b : { &h->tab_hash, &h->tab_pair, &h->tab_comp, &h->d_ascii, &h->d_packed, &h->d_nonacgt, &h->d_counters, &h->d_seg_in, &h->d_seg_out,
 		&h->d_seg_len, &h->d_seg_c1, &h->d_seg_c2, &h->d_seg_nsel, &h->d_sel_begin, &h->d_sym, &h->d_codes, &h->d_selmask, &h->d_pos1, &h->d_pos2,
 		&h->d_inst_pos, &h->d_inst_seg, &h->d_inst_flag, &h->d_inst_hash, &h->d_inst_slot, &h->d_pal_list, &h->d_nodes, &h->d_edges, &h->d_node_out,
 		&h->d_edge_out, &h->d_records, &h->d_recv, &h->d_bucket_count, &h->d_bucket_begin, &h->d_scan_tot, &h->d_scan_off, &h->d_node_hash_sorted, &h->d_node_cov,
@@ -593,8 +587,8 @@ int mbgfe_process(mbgfe* h)
 	tick(h, 5);
 	if (n_seg)
 	{
-		MBGFE_LAUNCH(k_select<NT_SELECT>, n_seg, NT_SELECT, h->plan.smem_bytes, h->stream, st, h->d_codes.as<uint16_t>(), h->d_seg_c2.as<uint32_t>(), h->tab_hash.as<uint64_t>(),
-			h->tab_hash_rc.as<uint64_t>(), h->d_selmask.as<uint8_t>(), h->d_seg_nsel.as<uint32_t>(), k, w, h->plan);
+		MBGFE_LAUNCH(k_select<NT_SELECT>, n_seg, NT_SELECT, h->plan.smem_bytes, h->stream, st, h->d_codes.as<uint16_t>(), h->d_seg_c2.as<uint32_t>(), h->tab_pair.as<uint4>(),
+			h->d_selmask.as<uint8_t>(), h->d_seg_nsel.as<uint32_t>(), k, w, h->plan);
 		launches++;
 	}
 	MBGFE_LAUNCH(k_scan_u32<1024>, 1, 1024, 0, h->stream, h->d_seg_nsel.as<uint32_t>(), h->d_sel_begin.as<uint64_t>(), n_seg);
