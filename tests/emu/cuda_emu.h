@@ -94,6 +94,7 @@ inline T __shfl_sync(unsigned, T v, unsigned src)
 	return out;
 }
 
+inline void __syncwarp(unsigned = 0xffffffffu) { emu::barrier().wait(); }
 inline unsigned long long __umul64hi(unsigned long long a, unsigned long long b) { return (unsigned long long)(((unsigned __int128)a * b) >> 64); }
 
 inline unsigned __ballot_sync(unsigned, int pred)

@@ -362,8 +362,8 @@ __device__ __forceinline__ uint64_t eq_shift(uint64_t x, uint64_t nx, uint32_t m
 // Algorithmic bytes: 1/4 read per symbol + 2 written per code (+ 4 per code when poses are requested).
 template <int NT>
 __global__ void __launch_bounds__(NT) k_msat(SegTable seg, const uint64_t* __restrict__ sym, const uint32_t* __restrict__ seg_c1,
-	uint16_t* __restrict__ codes, uint32_t* __restrict__ seg_c2, const uint32_t* __restrict__ pos1, uint32_t* __restrict__ pos2,
-	uint32_t max_motif)
+	uint16_t* __restrict__ codes, uint16_t* __restrict__ rrc, const uint16_t* __restrict__ tab_comp, uint32_t* __restrict__ seg_c2, const uint32_t* __restrict__ pos1,
+	uint32_t* __restrict__ pos2, uint32_t max_motif)
 {
 	__shared__ uint32_t cand[NT * 33];      // per symbol of the tile: (run end << 3) | (7 - motif length), 0 = none (row stride 33: no bank conflicts)
 	__shared__ uint32_t warp_tmp[NT / 32];
@@ -373,6 +373,7 @@ __global__ void __launch_bounds__(NT) k_msat(SegTable seg, const uint64_t* __res
 	const uint32_t n = seg_c1[g];
 	if (n < 32) { if (threadIdx.x == 0) seg_c2[g] = 0; return; }
 	const uint64_t out0 = seg.out_base[g];
+	const uint64_t rr0 = seg.out_base[g + 1] - 1;          // rrc[rr0 - i] = complement(code i): the reverse complement reads forwards
 	const uint64_t* __restrict__ s = sym + (out0 >> 5);   // segment-local words
 	const uint32_t n_words = (n + 31) / 32;
 	uint32_t* my_cand = cand + threadIdx.x * 33;
@@ -520,13 +521,17 @@ __global__ void __launch_bounds__(NT) k_msat(SegTable seg, const uint64_t* __res
 					uint32_t motif = 0;
 					for (uint32_t i = 0; i < m; i++) motif = (motif << 2) | symbol_at(s, ps + i);
 					const uint32_t oi = idx - 1;
-					codes[out0 + oi] = (uint16_t)(CODES_BEFORE[m] + motif * m + (slen % m));
+					const uint32_t code = CODES_BEFORE[m] + motif * m + (slen % m);
+					codes[out0 + oi] = (uint16_t)code;
+					rrc[rr0 - oi] = code < 4 ? (uint16_t)(3 - code) : __ldg(tab_comp + code);
 					if (pos2) pos2[out0 + oi] = pos1 ? pos1[out0 + ps] : ps;
 				}
 				if (at_end) break;
 				if (!((cover1 >> b) & 1))
 				{
-					codes[out0 + idx] = (uint16_t)((w0 >> (2 * b)) & 3);
+					const uint32_t sc = (uint32_t)(w0 >> (2 * b)) & 3;
+					codes[out0 + idx] = (uint16_t)sc;
+					rrc[rr0 - idx] = (uint16_t)(3 - sc);
 					if (pos2) pos2[out0 + idx] = pos1 ? pos1[out0 + q] : q;
 				}
 				idx++;
@@ -546,16 +551,19 @@ __global__ void __launch_bounds__(NT) k_msat(SegTable seg, const uint64_t* __res
 // modes without microsatellite coding: codes are the symbols themselves (2-bit -> uint16), poses are pos1
 template <int NT>
 __global__ void __launch_bounds__(NT) k_unpack_symbols(SegTable seg, const uint64_t* __restrict__ sym, const uint32_t* __restrict__ seg_c1,
-	uint16_t* __restrict__ codes, uint32_t* __restrict__ seg_c2, const uint32_t* __restrict__ pos1, uint32_t* __restrict__ pos2)
+	uint16_t* __restrict__ codes, uint16_t* __restrict__ rrc, uint32_t* __restrict__ seg_c2, const uint32_t* __restrict__ pos1, uint32_t* __restrict__ pos2)
 {
 	const uint32_t g = blockIdx.x;
 	if (g >= seg.n) return;
 	const uint32_t n = seg_c1[g];
 	const uint64_t out0 = seg.out_base[g];
+	const uint64_t rr0 = seg.out_base[g + 1] - 1;
 	const uint64_t* __restrict__ s = sym + (out0 >> 5);
 	for (uint32_t p = threadIdx.x; p < n; p += NT)
 	{
-		codes[out0 + p] = (uint16_t)((__ldg(s + (p >> 5)) >> ((p & 31) * 2)) & 3);
+		const uint32_t sc = (uint32_t)(__ldg(s + (p >> 5)) >> ((p & 31) * 2)) & 3;
+		codes[out0 + p] = (uint16_t)sc;
+		rrc[rr0 - p] = (uint16_t)(3 - sc);
 		if (pos2) pos2[out0 + p] = pos1 ? pos1[out0 + p] : p;
 	}
 	if (threadIdx.x == 0)
@@ -571,6 +579,19 @@ __global__ void __launch_bounds__(NT) k_unpack_symbols(SegTable seg, const uint6
 __device__ __forceinline__ uint64_t rotl_c(uint64_t v, uint32_t r) { return r ? ((v << r) | (v >> (64 - r))) : v; }
 __device__ __forceinline__ uint64_t rotr_c(uint64_t v, uint32_t r) { return r ? ((v >> r) | (v << (64 - r))) : v; }
 __device__ __forceinline__ uint64_t u64_of(uint32_t lo, uint32_t hi) { return ((uint64_t)hi << 32) | lo; }
+// rotation by a run-time amount r in 0..63 as two funnel shifts (+ a word swap when r >= 32): 4 ALU instructions
+// instead of the ~10 a generic 64-bit shift pair costs
+__device__ __forceinline__ uint64_t rotl_v(uint64_t v, uint32_t r)
+{
+#ifdef MBGFE_EMU_BUILD
+	return rotl64(v, r);
+#else
+	uint32_t lo = (uint32_t)v, hi = (uint32_t)(v >> 32);
+	if (r & 32) { const uint32_t t = lo; lo = hi; hi = t; }
+	return u64_of(__funnelshift_l(hi, lo, r), __funnelshift_l(lo, hi, r));
+#endif
+}
+__device__ __forceinline__ uint64_t rotr_v(uint64_t v, uint32_t r) { return rotl_v(v, (64 - r) & 63); }
 
 // Shared-memory plan of k_select<NT>.  A tile is T = 8 NT codes: every thread owns 8 consecutive codes / s-mer hashes /
 // k-mer decisions per tile, kept in registers.  Three stages run per tile with fixed lags (all multiples of 8):
@@ -697,16 +718,18 @@ __global__ void __launch_bounds__(NT) k_select(SegTable seg, const uint16_t* __r
 				const uint4* y2 = pq + (size_t)b2 * 9;
 				uint64_t hv[8];
 				uint64_t m = INF, mpre = INF;
+				const uint32_t i0u = (uint32_t)i0;
+				const uint32_t n_ok = i0u < n_smers ? min(8u, n_smers - i0u) : 0u;    // valid s-mers of this block
 #pragma unroll
 				for (int e = 0; e < 8; e++)
 				{
 					uint64_t v = INF;
-					if ((uint64_t)i0 + e < n_smers)
+					if ((uint32_t)e < n_ok)
 					{
 						const uint4 x = x0[e];
 						const uint4 y = (e + sr < 8) ? y1[e + sr] : y2[e + sr - 8];
-						const uint64_t fw = rotr_c(u64_of(y.x, y.y), 1) ^ rotl_c(u64_of(x.x, x.y), rot_s1);
-						const uint64_t bw = rotl_c(u64_of(y.z, y.w), rot_s) ^ u64_of(x.z, x.w);
+						const uint64_t fw = rotr_c(u64_of(y.x, y.y), 1) ^ rotl_v(u64_of(x.x, x.y), rot_s1);
+						const uint64_t bw = rotl_v(u64_of(y.z, y.w), rot_s) ^ u64_of(x.z, x.w);
 						v = fw < bw ? fw : bw;
 					}
 					hv[e] = v;
@@ -759,12 +782,14 @@ __global__ void __launch_bounds__(NT) k_select(SegTable seg, const uint16_t* __r
 #pragma unroll
 					for (int t = 6; t >= 0; t--) suf[t] = own[t] < suf[t + 1] ? own[t] : suf[t + 1];
 					uint64_t core = INF;                                 // blocks b+1 .. b+a-1
-					uint32_t bi = d0;
-					for (uint32_t t = 1; t < a; t++)
 					{
-						bi++; if (bi >= NBH) bi -= NBH;
-						const uint64_t v = bm[bi];
-						core = v < core ? v : core;
+						// blocks d0+1 .. d0+a-1 of the ring: at most one wrap, so two plain runs
+						const uint32_t first = d0 + 1, cnt = a - 1;
+						const uint32_t run1 = first >= NBH ? 0 : min(cnt, NBH - first);
+						const uint64_t* q1 = bm + first;
+						for (uint32_t t = 0; t < run1; t++) { const uint64_t v = q1[t]; core = v < core ? v : core; }
+						const uint64_t* q2 = bm + (first >= NBH ? first - NBH : 0);
+						for (uint32_t t = 0; t < cnt - run1; t++) { const uint64_t v = q2[t]; core = v < core ? v : core; }
 					}
 					uint32_t e0 = d0 + a; if (e0 >= NBH) e0 -= NBH;      // block that holds the window ends
 					uint32_t e1 = e0 + 1; if (e1 >= NBH) e1 -= NBH;
@@ -900,66 +925,78 @@ struct Murmur
 	__device__ __forceinline__ uint64_t finish() { h ^= h >> 47; h *= MUL; h ^= h >> 47; return h; }
 };
 
-// K3b2: 128-bit k-mer hash (MBG/MBGCommon.cpp:25-35).  One thread per (instance, half): half 0 hashes the first
-// (k+1)/2 codes, half 1 the first (k+1)/2 codes of the reverse complement (complemented codes read backwards from
-// the k-mer's end).  Codes of a read stay L1/L2 resident across the ~k/50 k-mers that cover them.
-__global__ void __launch_bounds__(256) k_kmer_hash(const uint64_t* __restrict__ seg_out_base, const uint16_t* __restrict__ codes,
-	const uint16_t* __restrict__ tab_comp, const uint32_t* __restrict__ inst_pos, const uint32_t* __restrict__ inst_seg, uint64_t n_inst,
+// K3b2: 128-bit k-mer hash (MBG/MBGCommon.cpp:25-35): low 64 bits = Murmur over the first (k+1)/2 codes of the k-mer,
+// high 64 bits = Murmur over the first (k+1)/2 codes of its reverse complement.  `rrc` holds every segment's
+// complemented codes in reverse order (written by K2), so both halves are the same forward walk over a code array.
+// A warp owns 32 (instance, half) pairs and alternates two phases over chunks of 32 blocks of 8 bytes:
+//   mix    for each of its 32 pairs in turn, the 32 lanes load 32 consecutive blocks (coalesced) and apply the part
+//          of Murmur that does not depend on the running hash (two of its three multiplications); the results go
+//          to shared memory, transposed
+//   chain  lane j folds the 32 premixed blocks of pair j into its running hash (h = (h ^ f) * m), conflict-free
+// so that no global load is scattered and the serial part of the hash is 5 instructions per block.
+// Algorithmic bytes: 2 read per code (codes of a read stay cache resident across the ~k/50 k-mers that cover them,
+// both directions) + 16 written per instance.
+constexpr int HASH_WARPS = 4;
+__global__ void __launch_bounds__(HASH_WARPS * 32) k_kmer_hash(const uint64_t* __restrict__ seg_out_base, const uint16_t* __restrict__ codes,
+	const uint16_t* __restrict__ rrc, const uint32_t* __restrict__ inst_pos, const uint32_t* __restrict__ inst_seg, uint64_t n_inst,
 	uint64_t* __restrict__ inst_hash, uint32_t k)
 {
-	const uint64_t t = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
-	if (t >= 2 * n_inst) return;
-	const uint64_t i = t >> 1;
-	const uint32_t dir = (uint32_t)(t & 1);
-	const uint16_t* __restrict__ c = codes + seg_out_base[inst_seg[i]] + inst_pos[i];
+	__shared__ uint64_t premixed[HASH_WARPS][32][33];
+	const uint32_t lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+	const uint64_t t = ((uint64_t)blockIdx.x * HASH_WARPS + wid) * 32 + lane;
+	const bool valid = t < 2 * n_inst;
+	const uint16_t* my = codes;        // lanes past the end walk the start of the array and discard the result
+	if (valid)
+	{
+		const uint64_t i = t >> 1;
+		const uint32_t g = inst_seg[i], pos = inst_pos[i];
+		const uint64_t ob = seg_out_base[g];
+		my = (t & 1) ? rrc + (seg_out_base[g + 1] - k - pos) : codes + ob + pos;
+	}
+	const uint64_t my_addr = (uint64_t)my;
 	const uint32_t half = (k + 1) / 2;
+	const uint32_t n_blocks = half / 4, rem = half & 3;
 	Murmur mm;
 	mm.init((uint64_t)half * 2);
-	const uint32_t n_blocks = half / 4;
-	if (dir == 0)
+	for (uint32_t c0 = 0; c0 < n_blocks; c0 += 32)
 	{
-		for (uint32_t b = 0; b < n_blocks; b++)
+		const uint32_t nb = min(32u, n_blocks - c0);
+		for (uint32_t j = 0; j < 32; j++)
 		{
-			const uint16_t* p = c + 4 * b;
-			uint64_t wd = (uint64_t)p[0] | ((uint64_t)p[1] << 16) | ((uint64_t)p[2] << 32) | ((uint64_t)p[3] << 48);
-			mm.block(wd);
-		}
-		uint32_t rem = half & 3;
-		if (rem)
-		{
-			uint64_t wd = 0;
-			for (uint32_t j = 0; j < rem; j++) wd |= (uint64_t)c[4 * n_blocks + j] << (16 * j);
-			mm.tail(wd);
-		}
-	}
-	else
-	{
-		const uint16_t* e = c + (k - 1);
-		for (uint32_t b = 0; b < n_blocks; b++)
-		{
-			const uint16_t* p = e - 4 * b;
-			uint32_t c0 = p[0], c1 = *(p - 1), c2 = *(p - 2), c3 = *(p - 3);
-			c0 = c0 < 4 ? 3 - c0 : __ldg(tab_comp + c0);
-			c1 = c1 < 4 ? 3 - c1 : __ldg(tab_comp + c1);
-			c2 = c2 < 4 ? 3 - c2 : __ldg(tab_comp + c2);
-			c3 = c3 < 4 ? 3 - c3 : __ldg(tab_comp + c3);
-			uint64_t wd = (uint64_t)c0 | ((uint64_t)c1 << 16) | ((uint64_t)c2 << 32) | ((uint64_t)c3 << 48);
-			mm.block(wd);
-		}
-		uint32_t rem = half & 3;
-		if (rem)
-		{
-			uint64_t wd = 0;
-			for (uint32_t j = 0; j < rem; j++)
+			const uint64_t a = __shfl_sync(FULL, my_addr, j) + 8ull * (c0 + lane);
+			if (lane < nb)
 			{
-				uint32_t cc = *(e - 4 * n_blocks - j);
-				cc = cc < 4 ? 3 - cc : __ldg(tab_comp + cc);
-				wd |= (uint64_t)cc << (16 * j);
+				const uint32_t* __restrict__ p = (const uint32_t*)(a & ~3ull);
+				uint32_t w0 = __ldg(p), w1 = __ldg(p + 1);
+				if (a & 2)
+				{
+					const uint32_t w2 = __ldg(p + 2);
+					w0 = (w0 >> 16) | (w1 << 16);
+					w1 = (w1 >> 16) | (w2 << 16);
+				}
+				uint64_t wd = u64_of(w0, w1);
+				wd *= Murmur::MUL; wd ^= wd >> 47; wd *= Murmur::MUL;
+				premixed[wid][j][lane] = wd;
 			}
-			mm.tail(wd);
 		}
+		__syncwarp();
+		for (uint32_t b = 0; b < nb; b++) { mm.h ^= premixed[wid][lane][b]; mm.h *= Murmur::MUL; }
+		__syncwarp();
 	}
-	inst_hash[2 * i + dir] = mm.finish();
+	if (rem)
+	{
+		uint64_t wd = 0;
+		for (uint32_t j = 0; j < rem; j++) wd |= (uint64_t)my[4 * n_blocks + j] << (16 * j);
+		mm.tail(wd);
+	}
+	if (valid) inst_hash[t] = mm.finish();
+}
+
+// KAT helper: rrc for one stand-alone code array of n codes (cap == n)
+__global__ void k_revcomp_codes(const uint16_t* __restrict__ codes, uint32_t n, const uint16_t* __restrict__ tab_comp, uint16_t* __restrict__ rrc)
+{
+	const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+	if (i < n) rrc[n - 1 - i] = tab_comp[codes[i]];
 }
 
 // instances whose two halves hash alike: palindromes or (practically impossible) collisions

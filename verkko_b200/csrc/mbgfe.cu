@@ -86,7 +86,7 @@ struct mbgfe
 	// device buffers
 	DevBuf d_ascii, d_packed, d_nonacgt, d_counters;
 	DevBuf d_seg_in, d_seg_out, d_seg_len, d_seg_c1, d_seg_c2, d_seg_nsel, d_sel_begin;
-	DevBuf d_sym, d_codes, d_selmask, d_pos1, d_pos2;
+	DevBuf d_sym, d_codes, d_rrc, d_selmask, d_pos1, d_pos2;
 	DevBuf d_inst_pos, d_inst_seg, d_inst_flag, d_inst_hash, d_inst_slot, d_pal_list;
 	DevBuf d_nodes, d_edges, d_node_out, d_edge_out, d_records, d_recv;
 	DevBuf d_bucket_count, d_bucket_begin, d_scan_tot, d_scan_off;      // export: bucket tables and scan scratch
@@ -228,6 +228,7 @@ int upload_segments(mbgfe* h)
 	{
 		CU(h, cudaMemcpyAsync(h->d_seg_in.p, h->seg_in.data(), n * 8, cudaMemcpyHostToDevice, h->stream));
 		CU(h, cudaMemcpyAsync(h->d_seg_out.p, h->seg_out.data(), n * 8, cudaMemcpyHostToDevice, h->stream));
+		CU(h, cudaMemcpyAsync(h->d_seg_out.as<uint64_t>() + n, &h->total_out, 8, cudaMemcpyHostToDevice, h->stream));   // out_base[n]: end of the last slot
 		CU(h, cudaMemcpyAsync(h->d_seg_len.p, h->seg_len.data(), n * 4, cudaMemcpyHostToDevice, h->stream));
 		h->stats.h2d_bytes += n * 20;
 	}
@@ -424,7 +425,7 @@ void mbgfe_destroy(mbgfe* h)
 {
 	if (!h) return;
 	for (DevBuf* b : { &h->tab_hash, &h->tab_pair, &h->tab_comp, &h->d_ascii, &h->d_packed, &h->d_nonacgt, &h->d_counters, &h->d_seg_in, &h->d_seg_out,
-		&h->d_seg_len, &h->d_seg_c1, &h->d_seg_c2, &h->d_seg_nsel, &h->d_sel_begin, &h->d_sym, &h->d_codes, &h->d_selmask, &h->d_pos1, &h->d_pos2,
+		&h->d_seg_len, &h->d_seg_c1, &h->d_seg_c2, &h->d_seg_nsel, &h->d_sel_begin, &h->d_sym, &h->d_codes, &h->d_rrc, &h->d_selmask, &h->d_pos1, &h->d_pos2,
 		&h->d_inst_pos, &h->d_inst_seg, &h->d_inst_flag, &h->d_inst_hash, &h->d_inst_slot, &h->d_pal_list, &h->d_nodes, &h->d_edges, &h->d_node_out,
 		&h->d_edge_out, &h->d_records, &h->d_recv, &h->d_bucket_count, &h->d_bucket_begin, &h->d_scan_tot, &h->d_scan_off, &h->d_node_hash_sorted, &h->d_node_cov,
 		&h->d_node_tip, &h->d_edges_sorted }) release(*b);
@@ -558,6 +559,7 @@ int mbgfe_process(mbgfe* h)
 	const uint64_t tot = h->total_out;
 	if (int rc = ensure(h, h->d_sym, tot / 4 + 64)) return rc;
 	if (int rc = ensure(h, h->d_codes, tot * 2 + 64)) return rc;
+	if (int rc = ensure(h, h->d_rrc, tot * 2 + 64)) return rc;
 	if (int rc = ensure(h, h->d_selmask, tot / 8 + 64)) return rc;
 	if (need_pos1) if (int rc = ensure(h, h->d_pos1, tot * 4 + 64)) return rc;
 	if (want_poses) if (int rc = ensure(h, h->d_pos2, tot * 4 + 64)) return rc;
@@ -577,11 +579,11 @@ int mbgfe_process(mbgfe* h)
 	if (n_seg)
 	{
 		if (h->msat)
-			MBGFE_LAUNCH(k_msat<NT_MSAT>, n_seg, NT_MSAT, 0, h->stream, st, h->d_sym.as<uint64_t>(), h->d_seg_c1.as<uint32_t>(), h->d_codes.as<uint16_t>(), h->d_seg_c2.as<uint32_t>(),
-				(const uint32_t*)pos1, pos2, h->max_motif);
+			MBGFE_LAUNCH(k_msat<NT_MSAT>, n_seg, NT_MSAT, 0, h->stream, st, h->d_sym.as<uint64_t>(), h->d_seg_c1.as<uint32_t>(), h->d_codes.as<uint16_t>(), h->d_rrc.as<uint16_t>(),
+				h->tab_comp.as<uint16_t>(), h->d_seg_c2.as<uint32_t>(), (const uint32_t*)pos1, pos2, h->max_motif);
 		else
 			MBGFE_LAUNCH(k_unpack_symbols<NT_MSAT>, n_seg, NT_MSAT, 0, h->stream, st, h->d_sym.as<uint64_t>(), h->d_seg_c1.as<uint32_t>(), h->d_codes.as<uint16_t>(),
-				h->d_seg_c2.as<uint32_t>(), (const uint32_t*)pos1, pos2);
+				h->d_rrc.as<uint16_t>(), h->d_seg_c2.as<uint32_t>(), (const uint32_t*)pos1, pos2);
 		launches++;
 	}
 	tick(h, 5);
@@ -613,8 +615,8 @@ int mbgfe_process(mbgfe* h)
 		{
 			MBGFE_LAUNCH(k_list_selected<NT_LIST>, n_seg, NT_LIST, 0, h->stream, st, h->d_selmask.as<uint32_t>(), h->d_seg_c2.as<uint32_t>(), h->d_seg_nsel.as<uint32_t>(),
 				h->d_sel_begin.as<uint64_t>(), h->d_inst_pos.as<uint32_t>(), h->d_inst_seg.as<uint32_t>(), h->d_inst_flag.as<uint8_t>(), k);
-			MBGFE_LAUNCH(k_kmer_hash, (unsigned)((2 * n_inst + 255) / 256), 256, 0, h->stream, h->d_seg_out.as<uint64_t>(), h->d_codes.as<uint16_t>(), h->tab_comp.as<uint16_t>(),
-				h->d_inst_pos.as<uint32_t>(), h->d_inst_seg.as<uint32_t>(), n_inst, h->d_inst_hash.as<uint64_t>(), k);
+			MBGFE_LAUNCH(k_kmer_hash, (unsigned)((2 * n_inst + HASH_WARPS * 32 - 1) / (HASH_WARPS * 32)), HASH_WARPS * 32, 0, h->stream, h->d_seg_out.as<uint64_t>(),
+				h->d_codes.as<uint16_t>(), h->d_rrc.as<uint16_t>(), h->d_inst_pos.as<uint32_t>(), h->d_inst_seg.as<uint32_t>(), n_inst, h->d_inst_hash.as<uint64_t>(), k);
 			MBGFE_LAUNCH(k_find_palindromes, (unsigned)((n_inst + 255) / 256), 256, 0, h->stream, h->d_inst_hash.as<uint64_t>(), n_inst, ctr + CTR_PALINDROME,
 				h->d_pal_list.as<uint64_t>(), pal_cap);
 			launches += 3;
@@ -1025,21 +1027,28 @@ int mbgfe_kat_tables(mbgfe* h, uint64_t* char_hash_30948, uint16_t* complement_3
 int mbgfe_kat_kmer_hash(mbgfe* h, const uint16_t* codes, uint32_t k, mbgfe_hash128* out)
 {
 	if (!h || !codes || !out) return MBGFE_E_PARAM;
-	DevBuf d_codes, d_misc;
-	if (int rc = ensure(h, d_codes, (size_t)k * 2 + 64)) return rc;
-	if (int rc = ensure(h, d_misc, 64)) { release(d_codes); return rc; }
-	// one synthetic instance: segment 0 at out_base 0, position 0
-	uint64_t zero64 = 0; uint32_t zero32 = 0;
-	cudaMemcpy(d_codes.p, codes, (size_t)k * 2, cudaMemcpyHostToDevice);
-	cudaMemcpy(d_misc.as<char>() + 0, &zero64, 8, cudaMemcpyHostToDevice);   // seg_out_base[0]
-	cudaMemcpy(d_misc.as<char>() + 8, &zero32, 4, cudaMemcpyHostToDevice);   // inst_pos[0]
-	cudaMemcpy(d_misc.as<char>() + 12, &zero32, 4, cudaMemcpyHostToDevice);  // inst_seg[0]
-	MBGFE_LAUNCH(k_kmer_hash, 1, 256, 0, h->stream, (const uint64_t*)d_misc.p, d_codes.as<uint16_t>(), h->tab_comp.as<uint16_t>(), (const uint32_t*)(d_misc.as<char>() + 8),
-		(const uint32_t*)(d_misc.as<char>() + 12), (uint64_t)1, (uint64_t*)(d_misc.as<char>() + 16), k);
+	if (k == 0) return fail(h, MBGFE_E_PARAM, "k must be positive");
+	DevBuf d_codes, d_rrc, d_misc;
+	int rc = ensure(h, d_codes, (size_t)k * 2 + 64);
+	if (!rc) rc = ensure(h, d_rrc, (size_t)k * 2 + 64);
+	if (!rc) rc = ensure(h, d_misc, 64);
+	if (rc) { release(d_codes); release(d_rrc); release(d_misc); return rc; }
+	// one synthetic instance: a single segment whose slot is exactly the k codes, position 0
+	const uint64_t bases[2] = { 0, k };
+	const uint32_t zero32 = 0;
+	cudaMemsetAsync(d_codes.p, 0, d_codes.cap, h->stream);
+	cudaMemsetAsync(d_rrc.p, 0, d_rrc.cap, h->stream);
+	cudaMemcpyAsync(d_codes.p, codes, (size_t)k * 2, cudaMemcpyHostToDevice, h->stream);
+	cudaMemcpyAsync(d_misc.as<char>() + 0, bases, 16, cudaMemcpyHostToDevice, h->stream);   // seg_out_base[0..1]
+	cudaMemcpyAsync(d_misc.as<char>() + 16, &zero32, 4, cudaMemcpyHostToDevice, h->stream);  // inst_pos[0]
+	cudaMemcpyAsync(d_misc.as<char>() + 20, &zero32, 4, cudaMemcpyHostToDevice, h->stream);  // inst_seg[0]
+	MBGFE_LAUNCH(k_revcomp_codes, (k + 255) / 256, 256, 0, h->stream, d_codes.as<uint16_t>(), k, h->tab_comp.as<uint16_t>(), d_rrc.as<uint16_t>());
+	MBGFE_LAUNCH(k_kmer_hash, 1, HASH_WARPS * 32, 0, h->stream, (const uint64_t*)d_misc.p, d_codes.as<uint16_t>(), d_rrc.as<uint16_t>(), (const uint32_t*)(d_misc.as<char>() + 16),
+		(const uint32_t*)(d_misc.as<char>() + 20), (uint64_t)1, (uint64_t*)(d_misc.as<char>() + 32), k);
 	cudaStreamSynchronize(h->stream);
 	uint64_t res[2] = { 0, 0 };
-	cudaError_t e = cudaMemcpy(res, d_misc.as<char>() + 16, 16, cudaMemcpyDeviceToHost);
-	release(d_codes); release(d_misc);
+	cudaError_t e = cudaMemcpy(res, d_misc.as<char>() + 32, 16, cudaMemcpyDeviceToHost);
+	release(d_codes); release(d_rrc); release(d_misc);
 	if (e != cudaSuccess) return fail(h, MBGFE_E_CUDA, "kat kernel failed: %s", cudaGetErrorString(e));
 	out->lo = res[0]; out->hi = res[1];
 	return 0;
