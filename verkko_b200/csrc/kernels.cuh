@@ -961,22 +961,30 @@ __global__ void __launch_bounds__(HASH_WARPS * 32) k_kmer_hash(const uint64_t* _
 	for (uint32_t c0 = 0; c0 < n_blocks; c0 += 32)
 	{
 		const uint32_t nb = min(32u, n_blocks - c0);
-		for (uint32_t j = 0; j < 32; j++)
+		// four pairs per round: all twelve loads are issued before the first one is consumed
+		for (uint32_t j0 = 0; j0 < 32; j0 += 4)
 		{
-			const uint64_t a = __shfl_sync(FULL, my_addr, j) + 8ull * (c0 + lane);
-			if (lane < nb)
+			uint32_t w0[4], w1[4], w2[4], sh[4];
+#pragma unroll
+			for (int u = 0; u < 4; u++)
 			{
+				const uint64_t a = __shfl_sync(FULL, my_addr, j0 + u) + 8ull * (c0 + lane);
 				const uint32_t* __restrict__ p = (const uint32_t*)(a & ~3ull);
-				uint32_t w0 = __ldg(p), w1 = __ldg(p + 1);
-				if (a & 2)
-				{
-					const uint32_t w2 = __ldg(p + 2);
-					w0 = (w0 >> 16) | (w1 << 16);
-					w1 = (w1 >> 16) | (w2 << 16);
-				}
-				uint64_t wd = u64_of(w0, w1);
+				sh[u] = ((uint32_t)a & 2) * 8;          // 0 or 16: the block starts in the middle of a 32-bit word
+				w0[u] = 0; w1[u] = 0; w2[u] = 0;
+				if (lane < nb) { w0[u] = __ldg(p); w1[u] = __ldg(p + 1); w2[u] = __ldg(p + 2); }
+			}
+#pragma unroll
+			for (int u = 0; u < 4; u++)
+			{
+#ifdef MBGFE_EMU_BUILD
+				const uint32_t lo = sh[u] ? (w0[u] >> 16) | (w1[u] << 16) : w0[u], hi = sh[u] ? (w1[u] >> 16) | (w2[u] << 16) : w1[u];
+#else
+				const uint32_t lo = __funnelshift_r(w0[u], w1[u], sh[u]), hi = __funnelshift_r(w1[u], w2[u], sh[u]);
+#endif
+				uint64_t wd = u64_of(lo, hi);
 				wd *= Murmur::MUL; wd ^= wd >> 47; wd *= Murmur::MUL;
-				premixed[wid][j][lane] = wd;
+				if (lane < nb) premixed[wid][j0 + u][lane] = wd;
 			}
 		}
 		__syncwarp();
