@@ -197,11 +197,11 @@ __global__ void k_build_tables(uint64_t* __restrict__ tab_hash, uint4* __restric
 // ASCII -> 2-bit.  One thread converts 16 characters (one 128-bit load) into one 32-bit word; characters outside
 // ACGTacgt are packed as A and their batch positions appended to `nonacgt` (rare; the host splits segments there).
 // Algorithmic bytes: 1 read + 1/4 written per base.
-__global__ void __launch_bounds__(256) k_pack_ascii(const uint4* __restrict__ ascii, uint64_t n_bases, uint32_t* __restrict__ packed,
-	uint64_t* __restrict__ nonacgt, unsigned long long* __restrict__ nonacgt_count, uint64_t nonacgt_cap)
+__global__ void __launch_bounds__(256) k_pack_ascii(const uint4* __restrict__ ascii, uint64_t n_bases, uint64_t first_chunk, uint64_t end_chunk,
+	uint32_t* __restrict__ packed, uint64_t* __restrict__ nonacgt, unsigned long long* __restrict__ nonacgt_count, uint64_t nonacgt_cap)
 {
-	const uint64_t n_chunks = (n_bases + 15) / 16;
-	for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n_chunks; i += (uint64_t)gridDim.x * blockDim.x)
+	// chunks of 16 characters [first_chunk, end_chunk): the pipelined upload packs each piece as it arrives
+	for (uint64_t i = first_chunk + (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < end_chunk; i += (uint64_t)gridDim.x * blockDim.x)
 	{
 		uint4 v = __ldcs(ascii + i);
 		uint32_t in[4] = { v.x, v.y, v.z, v.w };

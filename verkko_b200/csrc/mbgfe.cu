@@ -60,7 +60,8 @@ struct mbgfe
 	std::string err;
 	bool collapse = false, msat = false;
 	uint32_t max_motif = 6;
-	cudaStream_t stream = nullptr;
+	cudaStream_t stream = nullptr, copy_stream = nullptr;
+	std::vector<cudaEvent_t> piece_events;            // one per H2D piece of the pipelined upload
 	int sm_count = 148;
 	size_t max_smem = 0;
 	SelectPlan plan;
@@ -370,6 +371,12 @@ int load_file(mbgfe* h, const char* path)
 
 }
 
+namespace {
+int prepare_process(mbgfe* h);
+uint32_t launch_front(mbgfe* h, uint32_t g0, uint32_t cnt, bool timed);
+int process_tail(mbgfe* h, uint32_t launches);
+}
+
 // ====================================================================================================== C ABI
 
 extern "C" {
@@ -409,7 +416,7 @@ int mbgfe_create(const mbgfe_params* prm, mbgfe** out)
 	bool ok = false;
 	h->plan = make_plan(prm->k, prm->w, h->max_smem, ok);
 	if (!ok) return bail(fail(h, MBGFE_E_LIMIT, "k=%u needs more shared memory than one SM has (limit about k=11000)", prm->k));
-	if (cudaStreamCreate(&h->stream) != cudaSuccess) return bail(fail(h, MBGFE_E_CUDA, "cudaStreamCreate failed"));
+	if (cudaStreamCreate(&h->stream) != cudaSuccess || cudaStreamCreate(&h->copy_stream) != cudaSuccess) return bail(fail(h, MBGFE_E_CUDA, "cudaStreamCreate failed"));
 	for (auto& e2 : h->ev) if (cudaEventCreate(&e2) != cudaSuccess) return bail(fail(h, MBGFE_E_CUDA, "cudaEventCreate failed"));
 	if (ensure(h, h->tab_hash, MAX_CODE * 8) || ensure(h, h->tab_pair, MAX_CODE * 16) || ensure(h, h->tab_comp, MAX_CODE * 2) ||
 		ensure(h, h->d_counters, (CTR_OWNER + prm->world + 8) * 8)) return bail(MBGFE_E_CUDA);
@@ -431,6 +438,8 @@ void mbgfe_destroy(mbgfe* h)
 		&h->d_node_tip, &h->d_edges_sorted }) release(*b);
 	for (HostBuf* b : { &h->p_node_hashes, &h->p_node_cov, &h->p_node_tip, &h->p_edges }) release_host(*b);
 	for (auto& e : h->ev) if (e) cudaEventDestroy(e);
+	for (auto& e : h->piece_events) cudaEventDestroy(e);
+	if (h->copy_stream) cudaStreamDestroy(h->copy_stream);
 	if (h->stream) cudaStreamDestroy(h->stream);
 	for (auto* v : h->owned_bases) delete v;
 	for (auto* v : h->owned_offsets) delete v;
@@ -524,7 +533,7 @@ int mbgfe_upload(mbgfe* h)
 	{
 		const uint64_t chunks = (n_bases + 15) / 16;
 		const unsigned grid = (unsigned)std::min<uint64_t>((chunks + 255) / 256, (uint64_t)h->sm_count * 16);
-		MBGFE_LAUNCH(k_pack_ascii, grid, 256, 0, h->stream, (const uint4*)h->d_ascii.p, n_bases, h->d_packed.as<uint32_t>(), h->d_nonacgt.as<uint64_t>(),
+		MBGFE_LAUNCH(k_pack_ascii, grid, 256, 0, h->stream, (const uint4*)h->d_ascii.p, n_bases, (uint64_t)0, chunks, h->d_packed.as<uint32_t>(), h->d_nonacgt.as<uint64_t>(),
 			h->d_counters.as<unsigned long long>() + CTR_NONACGT, bad_cap);
 	}
 	tick(h, 2);
@@ -551,11 +560,21 @@ int mbgfe_process(mbgfe* h)
 	if (!h) return MBGFE_E_PARAM;
 	if (!h->resident) return fail(h, MBGFE_E_STATE, "mbgfe_process before mbgfe_upload");
 	clear_results(h);
-	const uint32_t k = h->prm.k, w = h->prm.w;
-	const uint32_t n_seg = (uint32_t)h->seg_len.size();
+	if (int rc = prepare_process(h)) return rc;
+	tick(h, 3);
+	const uint32_t launches = launch_front(h, 0, (uint32_t)h->seg_len.size(), true);
+	return process_tail(h, launches);
+}
+
+}
+
+namespace {
+
+// device buffers of one pass over the resident batch + counter reset
+int prepare_process(mbgfe* h)
+{
 	const bool want_poses = (h->prm.flags & MBGFE_KEEP_POSES) != 0;
 	const bool need_pos1 = want_poses && !h->collapse;
-	uint32_t launches = 0;
 	const uint64_t tot = h->total_out;
 	if (int rc = ensure(h, h->d_sym, tot / 4 + 64)) return rc;
 	if (int rc = ensure(h, h->d_codes, tot * 2 + 64)) return rc;
@@ -565,34 +584,48 @@ int mbgfe_process(mbgfe* h)
 	if (want_poses) if (int rc = ensure(h, h->d_pos2, tot * 4 + 64)) return rc;
 	unsigned long long* ctr = h->d_counters.as<unsigned long long>();
 	CU(h, cudaMemsetAsync(ctr + CTR_PALINDROME, 0, (CTR_OWNER + h->prm.world - CTR_PALINDROME) * 8, h->stream));
-	const SegTable st = seg_table(h);
+	return 0;
+}
+
+// K1 -> K2 -> K3a on segments [g0, g0 + cnt).  Segments are independent, so the pipelined upload can run each piece's
+// segments while later pieces are still crossing PCIe.  timed: record the per-stage events (whole-batch launches only).
+uint32_t launch_front(mbgfe* h, uint32_t g0, uint32_t cnt, bool timed)
+{
+	if (cnt == 0) { if (timed) { tick(h, 4); tick(h, 5); } return 0; }
+	const uint32_t k = h->prm.k, w = h->prm.w;
+	const bool want_poses = (h->prm.flags & MBGFE_KEEP_POSES) != 0;
+	const bool need_pos1 = want_poses && !h->collapse;
+	SegTable st;
+	st.in_start = h->d_seg_in.as<uint64_t>() + g0;
+	st.len = h->d_seg_len.as<uint32_t>() + g0;
+	st.out_base = h->d_seg_out.as<uint64_t>() + g0;
+	st.n = cnt;
 	uint32_t* pos1 = need_pos1 ? h->d_pos1.as<uint32_t>() : nullptr;
 	uint32_t* pos2 = want_poses ? h->d_pos2.as<uint32_t>() : nullptr;
-	tick(h, 3);
-	if (n_seg)
-	{
-		MBGFE_LAUNCH(k_collapse<NT_COLLAPSE>, n_seg, NT_COLLAPSE, 0, h->stream, st, h->d_packed.as<uint64_t>(), h->d_sym.as<uint64_t>(), h->d_seg_c1.as<uint32_t>(), pos1,
-			h->prm.error_masking == MBGFE_MASK_NO ? 1 : 0);
-		launches++;
-	}
-	tick(h, 4);
-	if (n_seg)
-	{
-		if (h->msat)
-			MBGFE_LAUNCH(k_msat<NT_MSAT>, n_seg, NT_MSAT, 0, h->stream, st, h->d_sym.as<uint64_t>(), h->d_seg_c1.as<uint32_t>(), h->d_codes.as<uint16_t>(), h->d_rrc.as<uint16_t>(),
-				h->tab_comp.as<uint16_t>(), h->d_seg_c2.as<uint32_t>(), (const uint32_t*)pos1, pos2, h->max_motif);
-		else
-			MBGFE_LAUNCH(k_unpack_symbols<NT_MSAT>, n_seg, NT_MSAT, 0, h->stream, st, h->d_sym.as<uint64_t>(), h->d_seg_c1.as<uint32_t>(), h->d_codes.as<uint16_t>(),
-				h->d_rrc.as<uint16_t>(), h->d_seg_c2.as<uint32_t>(), (const uint32_t*)pos1, pos2);
-		launches++;
-	}
-	tick(h, 5);
-	if (n_seg)
-	{
-		MBGFE_LAUNCH(k_select<NT_SELECT>, n_seg, NT_SELECT, h->plan.smem_bytes, h->stream, st, h->d_codes.as<uint16_t>(), h->d_seg_c2.as<uint32_t>(), h->tab_pair.as<uint4>(),
-			h->d_selmask.as<uint8_t>(), h->d_seg_nsel.as<uint32_t>(), k, w, h->plan);
-		launches++;
-	}
+	uint32_t* c1 = h->d_seg_c1.as<uint32_t>() + g0;
+	uint32_t* c2 = h->d_seg_c2.as<uint32_t>() + g0;
+	MBGFE_LAUNCH(k_collapse<NT_COLLAPSE>, cnt, NT_COLLAPSE, 0, h->stream, st, h->d_packed.as<uint64_t>(), h->d_sym.as<uint64_t>(), c1, pos1,
+		h->prm.error_masking == MBGFE_MASK_NO ? 1 : 0);
+	if (timed) tick(h, 4);
+	if (h->msat)
+		MBGFE_LAUNCH(k_msat<NT_MSAT>, cnt, NT_MSAT, 0, h->stream, st, h->d_sym.as<uint64_t>(), c1, h->d_codes.as<uint16_t>(), h->d_rrc.as<uint16_t>(),
+			h->tab_comp.as<uint16_t>(), c2, (const uint32_t*)pos1, pos2, h->max_motif);
+	else
+		MBGFE_LAUNCH(k_unpack_symbols<NT_MSAT>, cnt, NT_MSAT, 0, h->stream, st, h->d_sym.as<uint64_t>(), c1, h->d_codes.as<uint16_t>(),
+			h->d_rrc.as<uint16_t>(), c2, (const uint32_t*)pos1, pos2);
+	if (timed) tick(h, 5);
+	MBGFE_LAUNCH(k_select<NT_SELECT>, cnt, NT_SELECT, h->plan.smem_bytes, h->stream, st, h->d_codes.as<uint16_t>(), c2, h->tab_pair.as<uint4>(),
+		h->d_selmask.as<uint8_t>(), h->d_seg_nsel.as<uint32_t>() + g0, k, w, h->plan);
+	return 3;
+}
+
+// everything after selection: instance list, k-mer hashes, palindrome rule, node and edge tables
+int process_tail(mbgfe* h, uint32_t launches)
+{
+	const uint32_t k = h->prm.k;
+	const uint32_t n_seg = (uint32_t)h->seg_len.size();
+	unsigned long long* ctr = h->d_counters.as<unsigned long long>();
+	const SegTable st = seg_table(h);
 	MBGFE_LAUNCH(k_scan_u32<1024>, 1, 1024, 0, h->stream, h->d_seg_nsel.as<uint32_t>(), h->d_sel_begin.as<uint64_t>(), n_seg);
 	launches++;
 	tick(h, 6);
@@ -699,10 +732,112 @@ int mbgfe_process(mbgfe* h)
 	return 0;
 }
 
+}
+
+extern "C" {
+
+// mbgfe_run: upload and front end pipelined.  The ASCII reads cross PCIe in pieces on a copy stream; as soon as a piece
+// has landed it is packed and the segments that are complete run K1 -> K2 -> K3a on the compute stream, so the front
+// end hides behind the transfer.  The segment table is built before anything is copied, from the read lengths alone,
+// assuming no characters outside ACGT (true for corrected HiFi reads); K0 counts such characters, and if it finds any
+// the batch -- resident by then -- is cut at them and reprocessed the ordinary way.
 int mbgfe_run(mbgfe* h)
 {
-	if (int rc = mbgfe_upload(h)) return rc;
-	return mbgfe_process(h);
+	if (!h) return MBGFE_E_PARAM;
+	clear_results(h);
+	h->resident = false;
+	h->stats.h2d_bytes = 0; h->stats.d2h_bytes = 0;
+	uint64_t n_reads = 0, n_bases = 0;
+	for (auto& c : h->pending) { n_reads += c.n_reads; n_bases += c.offsets[c.n_reads] - c.offsets[0]; }
+	if (n_reads >= (1ull << 32)) return fail(h, MBGFE_E_LIMIT, "more than 2^32-1 reads in one batch");
+	h->n_reads = n_reads; h->n_bases = n_bases;
+	h->read_off.resize(n_reads + 1);
+	std::vector<const char*> read_ptr(n_reads);
+	{
+		uint64_t pos = 0, r = 0;
+		for (auto& c : h->pending)
+		{
+			const uint64_t first = c.offsets[0];
+			for (uint64_t i = 0; i < c.n_reads; i++, r++) { h->read_off[r] = pos + (c.offsets[i] - first); read_ptr[r] = c.bases + c.offsets[i]; }
+			pos += c.offsets[c.n_reads] - first;
+		}
+		h->read_off[n_reads] = pos;
+	}
+	if (int rc = ensure(h, h->d_ascii, n_bases + 64)) return rc;
+	if (int rc = ensure(h, h->d_packed, n_bases / 4 + 64)) return rc;
+	const uint64_t bad_cap = std::max<uint64_t>(1 << 20, n_bases / 16);
+	if (int rc = ensure(h, h->d_nonacgt, bad_cap * 8)) return rc;
+	const std::vector<uint64_t> none;
+	build_segments(h, none, read_ptr);
+	const uint32_t n_seg = (uint32_t)h->seg_len.size();
+	CU(h, cudaMemsetAsync(h->d_counters.p, 0, h->d_counters.cap, h->stream));
+	if (int rc = upload_segments(h)) return rc;
+	if (int rc = prepare_process(h)) return rc;
+	tick(h, 0);
+	tick(h, 3); tick(h, 4); tick(h, 5);     // pipelined: the whole front end is reported under ms_select
+	CU(h, cudaStreamWaitEvent(h->copy_stream, h->ev[0], 0));
+	const uint64_t PIECE = 48ull << 20;
+	uint64_t pos = 0, packed_upto = 0;
+	uint32_t g_done = 0, launches = 0;
+	size_t piece = 0;
+	for (size_t ci = 0; ci < h->pending.size(); ci++)
+	{
+		const HostChunk& c = h->pending[ci];
+		const uint64_t first = c.offsets[0], bytes = c.offsets[c.n_reads] - first;
+		for (uint64_t off = 0; off < bytes; off += PIECE)
+		{
+			const uint64_t len = std::min(PIECE, bytes - off);
+			if (piece >= h->piece_events.size()) { cudaEvent_t e; CU(h, cudaEventCreate(&e)); h->piece_events.push_back(e); }
+			CU(h, cudaMemcpyAsync(h->d_ascii.as<char>() + pos, c.bases + first + off, len, cudaMemcpyHostToDevice, h->copy_stream));
+			CU(h, cudaEventRecord(h->piece_events[piece], h->copy_stream));
+			CU(h, cudaStreamWaitEvent(h->stream, h->piece_events[piece], 0));
+			piece++;
+			pos += len;
+			const bool last = pos == n_bases;
+			const uint64_t pack_to = last ? n_bases : (pos & ~(uint64_t)15);
+			if (pack_to > packed_upto)
+			{
+				const uint64_t c0 = packed_upto / 16, c1 = (pack_to + 15) / 16;
+				const unsigned grid = (unsigned)std::min<uint64_t>((c1 - c0 + 255) / 256, (uint64_t)h->sm_count * 16);
+				MBGFE_LAUNCH(k_pack_ascii, grid, 256, 0, h->stream, (const uint4*)h->d_ascii.p, n_bases, c0, c1, h->d_packed.as<uint32_t>(), h->d_nonacgt.as<uint64_t>(),
+					h->d_counters.as<unsigned long long>() + CTR_NONACGT, bad_cap);
+				launches++;
+				packed_upto = pack_to;
+			}
+			uint32_t g_end = g_done;
+			while (g_end < n_seg && h->read_off[h->seg_read[g_end] + 1] <= packed_upto) g_end++;
+			launches += launch_front(h, g_done, g_end - g_done, false);
+			g_done = g_end;
+		}
+	}
+	CU(h, cudaEventRecord(h->ev[1], h->copy_stream));
+	launches += launch_front(h, g_done, n_seg - g_done, false);
+	h->stats.h2d_bytes += n_bases;
+	uint64_t n_bad = 0;
+	if (int rc = read_counter(h, CTR_NONACGT, &n_bad)) return rc;
+	CU(h, cudaGetLastError());
+	h->stats.ms_upload = elapsed(h, 0, 1);
+	h->stats.ms_pack = 0;
+	h->stats.reads = n_reads; h->stats.raw_bases = n_bases; h->stats.nonacgt = n_bad;
+	h->nonacgt_count = n_bad;
+	h->pending.clear();
+	if (n_bad)
+	{
+		// rare: cut the reads at the characters outside ACGT and run the resident batch again
+		if (n_bad > bad_cap) return fail(h, MBGFE_E_LIMIT, "%llu characters outside ACGT in %llu bases: more than 1 in 16", (unsigned long long)n_bad, (unsigned long long)n_bases);
+		std::vector<uint64_t> bad;
+		if (int rc = download(h, bad, h->d_nonacgt, n_bad)) return rc;
+		std::sort(bad.begin(), bad.end());
+		build_segments(h, bad, read_ptr);
+		if (int rc = upload_segments(h)) return rc;
+		CU(h, cudaStreamSynchronize(h->stream));
+		h->stats.segments = h->seg_len.size();
+		h->resident = true;
+		return mbgfe_process(h);
+	}
+	h->stats.segments = n_seg;
+	h->resident = true;
+	return process_tail(h, launches);
 }
 
 }
