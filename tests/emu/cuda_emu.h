@@ -107,6 +107,7 @@ inline unsigned __ballot_sync(unsigned, int pred)
 	return r;
 }
 
+inline int __clz(unsigned v) { return v ? __builtin_clz(v) : 32; }
 inline int __ffs(unsigned v) { return __builtin_ffs((int)v); }
 inline int __ffsll(long long v) { return __builtin_ffsll(v); }
 inline int __popc(unsigned v) { return __builtin_popcount(v); }

@@ -1,13 +1,15 @@
 // kernels.cuh -- sm_100a device code of libmbgfe (hand-written CUDA; no library kernels).
 //
 // Data layout in HBM (all indices are in bases / symbols / codes, never bytes, unless stated):
-//   packed   2-bit bases of the whole batch, base i at bits [2*(i%32), +2) of 64-bit word i/32 (A0 C1 G2 T3);
-//            reads are NOT padded: read r occupies [offsets[r], offsets[r+1]) exactly as in the ASCII buffer.
+//   packed   2-bit bases of the whole batch in PLANAR 64-bit words: word i/32 holds bases 32(i/32)..+31, the low bit of
+//            base i at bit i%32 and its high bit at bit 32 + i%32 (A0 C1 G2 T3).  One bit per position in each 32-bit
+//            plane keeps every later mask operation (neighbour compares, period tests, compaction) 32 bits wide.
+//            Reads are NOT padded: read r occupies [offsets[r], offsets[r+1]) exactly as in the ASCII buffer.
 //   segment  maximal ACGT stretch of a read (the whole read when it has no other characters).  Segment g owns the
 //            output range [out_base[g], out_base[g] + len[g] + 1) in every per-symbol array; out_base is a multiple
 //            of 64, so each segment starts on a 128-bit boundary in the 2-bit symbol array and on a 128-byte boundary
 //            in the 16-bit code array.
-//   sym      2-bit run-length / collapsed symbols (output of K1), same packing as `packed`, indexed by out_base.
+//   sym      2-bit run-length / collapsed symbols (output of K1), same planar packing as `packed`, indexed by out_base.
 //   codes    uint16 final codes (output of K2), indexed by out_base.
 //   selmask  1 bit per code position: k-mer starting there is selected (output of K3a), indexed by out_base.
 //   inst_*   one entry per selected k-mer instance, in (segment, position) order (output of K3b).
@@ -30,24 +32,37 @@ constexpr uint32_t FULL = 0xffffffffu;
 __host__ __device__ __forceinline__ uint64_t rotl64(uint64_t v, uint32_t r) { r &= 63; return (v << r) | (v >> ((64 - r) & 63)); }
 __host__ __device__ __forceinline__ uint64_t rotr64(uint64_t v, uint32_t r) { r &= 63; return (v >> r) | (v << ((64 - r) & 63)); }
 
-// 64 bits of a 2-bit packed array starting at symbol index `sym` (the array is padded by two words)
-__device__ __forceinline__ uint64_t window64(const uint64_t* __restrict__ p, uint64_t sym)
+struct Planes { uint32_t lo, hi; };    // 32 symbols: bit i of lo / hi = low / high bit of symbol i
+__device__ __forceinline__ Planes planes_of(uint64_t w) { Planes p; p.lo = (uint32_t)w; p.hi = (uint32_t)(w >> 32); return p; }
+__device__ __forceinline__ uint64_t word_of(uint32_t lo, uint32_t hi) { return ((uint64_t)hi << 32) | lo; }
+// low n bits set (n in 0..32)
+__device__ __forceinline__ uint32_t low_bits(uint32_t n) { return n >= 32 ? 0xffffffffu : ((1u << n) - 1); }
+// (hi:lo) >> sh, low 32 bits (sh in 0..31)
+__device__ __forceinline__ uint32_t funnel_r(uint32_t lo, uint32_t hi, uint32_t sh)
 {
-	uint64_t q = sym >> 5;
-	uint32_t sh = (uint32_t)(sym & 31) * 2;
-	uint64_t lo = __ldg(p + q);
-	if (sh == 0) return lo;
-	uint64_t hi = __ldg(p + q + 1);
-	return (lo >> sh) | (hi << (64 - sh));
+#ifdef MBGFE_EMU_BUILD
+	return sh ? ((lo >> sh) | (hi << (32 - sh))) : lo;
+#else
+	return __funnelshift_r(lo, hi, sh);
+#endif
 }
-
+// planes of 32 symbols a[sh..] ++ b[..sh)
+__device__ __forceinline__ Planes shift_in(Planes a, Planes b, uint32_t sh) { Planes r; r.lo = funnel_r(a.lo, b.lo, sh); r.hi = funnel_r(a.hi, b.hi, sh); return r; }
+// 32 symbols of a planar array starting at symbol index `sym` (the array is padded by two words)
+__device__ __forceinline__ Planes window32(const uint64_t* __restrict__ p, uint64_t sym)
+{
+	const uint64_t q = sym >> 5;
+	const uint32_t sh = (uint32_t)(sym & 31);
+	const Planes a = planes_of(__ldg(p + q));
+	if (sh == 0) return a;
+	return shift_in(a, planes_of(__ldg(p + q + 1)), sh);
+}
 __device__ __forceinline__ uint32_t symbol_at(const uint64_t* __restrict__ p, uint64_t sym)
 {
-	return (uint32_t)(__ldg(p + (sym >> 5)) >> ((sym & 31) * 2)) & 3;
+	const uint64_t w = __ldg(p + (sym >> 5));
+	const uint32_t b = (uint32_t)(sym & 31);
+	return ((uint32_t)(w >> b) & 1) | (((uint32_t)(w >> (32 + b)) & 1) << 1);
 }
-
-// mask with the low 2*n bits set (n in 0..32)
-__device__ __forceinline__ uint64_t low_pairs(uint32_t n) { return n >= 32 ? ~0ull : ((1ull << (2 * n)) - 1); }
 
 // ---------------------------------------------------------------------------------------------- block scans
 
@@ -194,79 +209,79 @@ __global__ void k_build_tables(uint64_t* __restrict__ tab_hash, uint4* __restric
 
 // ---------------------------------------------------------------------------------------------- K0: pack
 
-// ASCII -> 2-bit.  One thread converts 16 characters (one 128-bit load) into one 32-bit word; characters outside
-// ACGTacgt are packed as A and their batch positions appended to `nonacgt` (rare; the host splits segments there).
-// Algorithmic bytes: 1 read + 1/4 written per base.
+// ASCII -> planar 2-bit.  One thread converts 32 characters (two 128-bit loads) into one 64-bit planar word; characters
+// outside ACGTacgt are packed as A and their batch positions appended to `nonacgt` (rare; the host splits segments
+// there).  Per 4 characters: byte-SIMD test, (x>>1 ^ x>>2) & 3 per byte, and one multiplication per plane that gathers
+// the four bits (bit 8i -> bit 28+i).   Algorithmic bytes: 1 read + 1/4 written per base.
 __global__ void __launch_bounds__(256) k_pack_ascii(const uint4* __restrict__ ascii, uint64_t n_bases, uint64_t first_chunk, uint64_t end_chunk,
-	uint32_t* __restrict__ packed, uint64_t* __restrict__ nonacgt, unsigned long long* __restrict__ nonacgt_count, uint64_t nonacgt_cap)
+	uint64_t* __restrict__ packed, uint64_t* __restrict__ nonacgt, unsigned long long* __restrict__ nonacgt_count, uint64_t nonacgt_cap)
 {
-	// chunks of 16 characters [first_chunk, end_chunk): the pipelined upload packs each piece as it arrives
+	// chunks of 32 characters [first_chunk, end_chunk): the pipelined upload packs each piece as it arrives
 	for (uint64_t i = first_chunk + (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < end_chunk; i += (uint64_t)gridDim.x * blockDim.x)
 	{
-		uint4 v = __ldcs(ascii + i);
-		uint32_t in[4] = { v.x, v.y, v.z, v.w };
-		uint32_t out = 0;
+		const uint4 v0 = __ldcs(ascii + 2 * i), v1 = __ldcs(ascii + 2 * i + 1);
+		const uint32_t in[8] = { v0.x, v0.y, v0.z, v0.w, v1.x, v1.y, v1.z, v1.w };
+		uint32_t lo = 0, hi = 0;
 #pragma unroll
-		for (int j = 0; j < 4; j++)
+		for (int j = 0; j < 8; j++)
 		{
 			uint32_t x = in[j];
-			uint32_t u = x & 0xdfdfdfdfu;
-			uint32_t ok = __vcmpeq4(u, 0x41414141u) | __vcmpeq4(u, 0x43434343u) | __vcmpeq4(u, 0x47474747u) | __vcmpeq4(u, 0x54545454u);
+			const uint32_t u = x & 0xdfdfdfdfu;
+			const uint32_t ok = __vcmpeq4(u, 0x41414141u) | __vcmpeq4(u, 0x43434343u) | __vcmpeq4(u, 0x47474747u) | __vcmpeq4(u, 0x54545454u);
 			if (ok != 0xffffffffu)
 			{
 				for (int b = 0; b < 4; b++)
 				{
-					uint64_t pos = i * 16 + j * 4 + b;
+					const uint64_t pos = i * 32 + j * 4 + b;
 					if (((ok >> (8 * b)) & 0xff) == 0 && pos < n_bases)
 					{
-						unsigned long long slot = atomicAdd(nonacgt_count, 1ull);
+						const unsigned long long slot = atomicAdd(nonacgt_count, 1ull);
 						if (slot < nonacgt_cap) nonacgt[slot] = pos;
 					}
 				}
 				x &= ok; // non-ACGT -> 0 -> packs as A
 			}
-			uint32_t t = ((x >> 1) ^ (x >> 2)) & 0x03030303u; // A0 C1 G2 T3
-			t |= t >> 6;
-			t = (t | (t >> 12)) & 0xff;
-			out |= t << (8 * j);
+			const uint32_t t = ((x >> 1) ^ (x >> 2)) & 0x03030303u; // A0 C1 G2 T3
+			lo |= (((t & 0x01010101u) * 0x10204080u) >> 28) << (4 * j);
+			hi |= ((((t >> 1) & 0x01010101u) * 0x10204080u) >> 28) << (4 * j);
 		}
-		packed[i] = out;
+		packed[i] = word_of(lo, hi);
 	}
 }
 
 // ------------------------------------------------------------------------------------------ K1: collapse
 
-// bit-compress: gathers the 2-bit groups of x selected by `keep` (one flag per group, at the even bit) into the low
-// bits, preserving order.  Parallel-suffix method (Hacker's Delight 7-4) on pair masks.
-__device__ __forceinline__ uint64_t compress_pairs(uint64_t x, uint64_t keep)
+// bit-compress of both planes: gathers the bits selected by `m` into the low bits, preserving order.
+// Parallel-suffix method (Hacker's Delight 7-4); the move masks are computed once and applied to both planes.
+__device__ __forceinline__ void compress_planes(uint32_t& lo, uint32_t& hi, uint32_t m)
 {
-	uint64_t m = keep | (keep << 1);
-	x &= m;
-	uint64_t mk = ~m << 1;
+	lo &= m; hi &= m;
+	uint32_t mk = ~m << 1;
 #pragma unroll
-	for (int i = 0; i < 6; i++)
+	for (int i = 0; i < 5; i++)
 	{
-		uint64_t mp = mk ^ (mk << 1);
-		mp ^= mp << 2; mp ^= mp << 4; mp ^= mp << 8; mp ^= mp << 16; mp ^= mp << 32;
-		uint64_t mv = mp & m;
+		uint32_t mp = mk ^ (mk << 1);
+		mp ^= mp << 2; mp ^= mp << 4; mp ^= mp << 8; mp ^= mp << 16;
+		const uint32_t mv = mp & m;
 		m = (m ^ mv) | (mv >> (1 << i));
-		uint64_t t = x & mv;
-		x = (x ^ t) | (t >> (1 << i));
+		uint32_t t = lo & mv;
+		lo = (lo ^ t) | (t >> (1 << i));
+		t = hi & mv;
+		hi = (hi ^ t) | (t >> (1 << i));
 		mk &= ~mp;
 	}
-	return x;
 }
 
 struct SegTable
 {
 	const uint64_t* in_start;  // first base of the segment in `packed`
 	const uint32_t* len;       // bases
-	const uint64_t* out_base;  // first symbol / code slot owned by the segment
+	const uint64_t* out_base;  // first symbol / code slot owned by the segment (n + 1 entries)
 	uint32_t n;
 };
 
 // K1: homopolymer collapse (MBG/ReadHelper.h:864-876 collapse, :899-1018 run-length symbols).  One CTA per segment;
-// each thread owns one 64-bit word = 32 bases per tile: neighbour compare -> keep mask -> popcount -> block prefix sum
+// each thread owns 32 bases per tile: neighbour compare on both planes -> keep mask -> popcount -> block prefix sum
 // -> bit-compress -> merged into a shared-memory staging tile -> coalesced 64-bit stores.
 // keep_all != 0 (--error-masking=no): every base is a symbol (the kernel only re-aligns the segment).
 // pos1 != nullptr: also writes the segment-relative raw position of every kept base (the run starts, i.e. poses).
@@ -275,7 +290,7 @@ template <int NT>
 __global__ void __launch_bounds__(NT) k_collapse(SegTable seg, const uint64_t* __restrict__ packed, uint64_t* __restrict__ sym,
 	uint32_t* __restrict__ seg_c1, uint32_t* __restrict__ pos1, int keep_all)
 {
-	__shared__ unsigned long long stage[NT + 2];
+	__shared__ uint32_t stage_lo[NT + 2], stage_hi[NT + 2];
 	__shared__ uint32_t warp_tmp[NT / 32];
 	const uint32_t g = blockIdx.x;
 	if (g >= seg.n) return;
@@ -284,54 +299,56 @@ __global__ void __launch_bounds__(NT) k_collapse(SegTable seg, const uint64_t* _
 	const uint64_t out0 = seg.out_base[g];
 	uint64_t* __restrict__ out = sym + (out0 >> 5);
 	uint32_t carry = 0; // symbols written so far
-	if (threadIdx.x == 0) stage[0] = 0;
+	if (threadIdx.x == 0) { stage_lo[0] = 0; stage_hi[0] = 0; }
 	for (uint32_t tile = 0; tile < len; tile += NT * 32)
 	{
 		const uint32_t base0 = tile + threadIdx.x * 32;
-		uint64_t x = 0, keep = 0;
+		uint32_t lo = 0, hi = 0, keep = 0;
 		if (base0 < len)
 		{
 			const uint32_t nvalid = min(32u, len - base0);
-			x = window64(packed, in0 + base0);
-			if (keep_all) keep = 0x5555555555555555ull;
+			const uint64_t at = in0 + base0;
+			const Planes x = window32(packed, at);
+			lo = x.lo; hi = x.hi;
+			if (keep_all) keep = 0xffffffffu;
+			else if (base0 == 0) keep = (((lo ^ (lo << 1)) | (hi ^ (hi << 1)))) | 1u;
 			else
 			{
-				uint64_t y = base0 == 0 ? (x << 2) : window64(packed, in0 + base0 - 1);
-				uint64_t d = x ^ y;
-				keep = (d | (d >> 1)) & 0x5555555555555555ull;
-				if (base0 == 0) keep |= 1;
+				const uint32_t pv = symbol_at(packed, at - 1);
+				keep = (lo ^ ((lo << 1) | (pv & 1))) | (hi ^ ((hi << 1) | (pv >> 1)));
 			}
-			keep &= low_pairs(nvalid);
+			keep &= low_bits(nvalid);
 		}
-		const uint32_t cnt = __popcll(keep);
+		const uint32_t cnt = __popc(keep);
 		uint32_t tile_total;
 		const uint32_t excl = block_exclusive_sum<NT>(cnt, warp_tmp, tile_total);
 		// the staging tile holds symbols [carry & ~31, ...): word 0 keeps the partial word of the previous tile
-		for (uint32_t i = 1 + threadIdx.x; i < NT + 2; i += NT) stage[i] = 0;
+		for (uint32_t i = 1 + threadIdx.x; i < NT + 2; i += NT) { stage_lo[i] = 0; stage_hi[i] = 0; }
 		__syncthreads();
 		if (cnt)
 		{
-			const uint64_t c = compress_pairs(x, keep);
-			const uint32_t o = (carry & 31) + excl;
-			const uint32_t sh = (o & 31) * 2;
-			atomicOr(&stage[o >> 5], (unsigned long long)(c << sh));
-			if (sh && (cnt * 2 + sh > 64)) atomicOr(&stage[(o >> 5) + 1], (unsigned long long)(c >> (64 - sh)));
 			if (pos1)
 			{
 				uint32_t idx = carry + excl;
-				uint64_t kk = keep;
-				while (kk) { uint32_t b = __ffsll((long long)kk) - 1; kk &= kk - 1; pos1[out0 + idx++] = base0 + (b >> 1); }
+				uint32_t kk = keep;
+				while (kk) { const uint32_t b = __ffs(kk) - 1; kk &= kk - 1; pos1[out0 + idx++] = base0 + b; }
 			}
+			compress_planes(lo, hi, keep);
+			const uint32_t o = (carry & 31) + excl;
+			const uint32_t sh = o & 31;
+			atomicOr(&stage_lo[o >> 5], lo << sh);
+			atomicOr(&stage_hi[o >> 5], hi << sh);
+			if (sh && cnt + sh > 32) { atomicOr(&stage_lo[(o >> 5) + 1], lo >> (32 - sh)); atomicOr(&stage_hi[(o >> 5) + 1], hi >> (32 - sh)); }
 		}
 		__syncthreads();
 		const uint32_t filled = (carry & 31) + tile_total;       // symbols now in the staging tile
 		const bool last = tile + NT * 32 >= len;
 		const uint32_t n_words = last ? (filled + 31) / 32 : filled / 32;
 		const uint32_t w0 = carry >> 5;
-		for (uint32_t i = threadIdx.x; i < n_words; i += NT) out[w0 + i] = stage[i];
-		const unsigned long long partial = (filled & 31) ? stage[filled >> 5] : 0ull;
+		for (uint32_t i = threadIdx.x; i < n_words; i += NT) out[w0 + i] = word_of(stage_lo[i], stage_hi[i]);
+		const uint32_t part_lo = (filled & 31) ? stage_lo[filled >> 5] : 0u, part_hi = (filled & 31) ? stage_hi[filled >> 5] : 0u;
 		__syncthreads();
-		if (threadIdx.x == 0) stage[0] = partial;
+		if (threadIdx.x == 0) { stage_lo[0] = part_lo; stage_hi[0] = part_hi; }
 		carry += tile_total;
 	}
 	if (threadIdx.x == 0)
@@ -343,12 +360,45 @@ __global__ void __launch_bounds__(NT) k_collapse(SegTable seg, const uint64_t* _
 
 // ------------------------------------------------------------------------------- K2: microsatellite coding
 
-// 1 bit per symbol (at the even bit) where sym[p] == sym[p+m], from 32 symbols x and the 32 that follow (nx)
-__device__ __forceinline__ uint64_t eq_shift(uint64_t x, uint64_t nx, uint32_t m)
+// 1 bit per position p of word a where sym[p] == sym[p+m]; b = the 32 symbols that follow a
+__device__ __forceinline__ uint32_t eq_shift(Planes a, Planes b, uint32_t m)
 {
-	uint64_t y = (x >> (2 * m)) | (nx << (64 - 2 * m));
-	uint64_t d = x ^ y;
-	return ~(d | (d >> 1)) & 0x5555555555555555ull;
+	return ~((a.lo ^ funnel_r(a.lo, b.lo, m)) | (a.hi ^ funnel_r(a.hi, b.hi, m)));
+}
+
+// bits 0..5 of x moved to the even positions 0, 2, .., 10
+__device__ __forceinline__ uint32_t spread6(uint32_t x)
+{
+	x = (x | (x << 4)) & 0x0f0fu;
+	x = (x | (x << 2)) & 0x3333u;
+	x = (x | (x << 1)) & 0x5555u;
+	return x;
+}
+
+// floor(v / m) for m in 2..6 and v < 2^29 as one multiply-high by ceil(2^32 / m)
+__constant__ uint32_t RECIP32[8] = { 0, 0, 0x80000000u, 0x55555556u, 0x40000000u, 0x33333334u, 0x2aaaaaabu, 0 };
+
+// code of a run-length stretch (MBG/ErrorMaskHelper.cpp:107-127) and of its reverse complement (:43-73) from the
+// first m symbols of the stretch (planes, first symbol at bit 0) and its length: code = numBefore[m] + motif * m +
+// (len mod m), motif = the m symbols as base-4 digits, first symbol most significant.  Reverse complement: rotate the
+// motif left by the overhang, complement every digit, reverse the digit order -- which, on the little-endian digit
+// string the planes give directly, is just a digit rotation followed by XOR with all-ones.
+__device__ __forceinline__ void stretch_codes(Planes first, uint32_t m, uint32_t len, uint32_t& code, uint32_t& rc_code)
+{
+	const uint32_t mask = (1u << (2 * m)) - 1;
+	const uint32_t le = (spread6(first.lo & low_bits(m)) | (spread6(first.hi & low_bits(m)) << 1));   // digit j = symbol j
+#ifdef MBGFE_EMU_BUILD
+	uint32_t be = 0;
+	for (uint32_t j = 0; j < m; j++) be = (be << 2) | ((le >> (2 * j)) & 3);
+	const uint32_t oh = m > 1 ? len % m : 0;
+#else
+	const uint32_t y = __brev(le) >> (32 - 2 * m);                 // digit order reversed, bits inside each digit swapped
+	const uint32_t be = ((y & 0xaaau) >> 1) | ((y & 0x555u) << 1);
+	const uint32_t oh = m > 1 ? len - __umulhi(len, RECIP32[m]) * m : 0;
+#endif
+	code = CODES_BEFORE[m] + be * m + oh;
+	const uint32_t rot = ((le >> (2 * oh)) | (le << (2 * (m - oh)))) & mask;   // oh == 0: le | le << 2m, masked = le
+	rc_code = CODES_BEFORE[m] + (rot ^ mask) * m + oh;
 }
 
 // K2: multiRLECompress (MBG/ErrorMaskHelper.cpp:169-342) in scan-parallel form (DESIGN.md "K2"; the sequential
@@ -357,15 +407,19 @@ __device__ __forceinline__ uint64_t eq_shift(uint64_t x, uint64_t nx, uint32_t m
 //   emitted    : candidate end > exclusive prefix maximum of candidate ends           (block max-scan + carry)
 //   cover      : 1 = inside exactly one emitted run, else single-symbol codes        (from the two carried ends)
 //   code start : p == 0 | cover(p) != 1 | cover(p-1) != 1 | a run is emitted at p     (popcount + block sum-scan)
-// One CTA per segment, one 64-bit word (32 symbols) per thread and tile; three block scans per tile.
+// One CTA per segment, 32 symbols per thread and tile, every mask one bit per position; the tile's words sit in shared
+// memory (with the word before and the three after), three block scans per tile.  Codes are written in two sweeps:
+// the single-symbol codes of the word, then the stretches that END in the word (by the thread that owns the symbol
+// after them).  The reverse-complement array rrc is written alongside (rrc[rr0 - i] = complement(code i)).
 // Segments with fewer than 32 symbols produce no part (MBG/ReadHelper.h:847,858,882,893): seg_c2 = 0.
-// Algorithmic bytes: 1/4 read per symbol + 2 written per code (+ 4 per code when poses are requested).
+// Algorithmic bytes: 1/4 read per symbol + 2 written per code (+ 2 for rrc, + 4 per code when poses are requested).
 template <int NT>
 __global__ void __launch_bounds__(NT) k_msat(SegTable seg, const uint64_t* __restrict__ sym, const uint32_t* __restrict__ seg_c1,
-	uint16_t* __restrict__ codes, uint16_t* __restrict__ rrc, const uint16_t* __restrict__ tab_comp, uint32_t* __restrict__ seg_c2, const uint32_t* __restrict__ pos1,
+	uint16_t* __restrict__ codes, uint16_t* __restrict__ rrc, uint32_t* __restrict__ seg_c2, const uint32_t* __restrict__ pos1,
 	uint32_t* __restrict__ pos2, uint32_t max_motif)
 {
-	__shared__ uint32_t cand[NT * 33];      // per symbol of the tile: (run end << 3) | (7 - motif length), 0 = none (row stride 33: no bank conflicts)
+	__shared__ uint32_t cand[NT * 33];      // per symbol of the tile: (run end << 3) | (7 - motif length) (row stride 33: no bank conflicts)
+	__shared__ uint64_t tile_w[NT + 4];     // planar words tile_word0 - 1 .. tile_word0 + NT + 2
 	__shared__ uint32_t warp_tmp[NT / 32];
 	__shared__ LastRun warp_last[NT / 32];
 	const uint32_t g = blockIdx.x;
@@ -382,11 +436,30 @@ __global__ void __launch_bounds__(NT) k_msat(SegTable seg, const uint64_t* __res
 	uint32_t carry_codes = 0;
 	for (uint32_t tile = 0; tile < n; tile += NT * 32)
 	{
+		const uint32_t jb = tile >> 5;     // first word of the tile
+		for (uint32_t i = threadIdx.x; i < NT + 4; i += NT)
+		{
+			const uint32_t jj = jb + i;    // word jj - 1
+			tile_w[i] = (jj >= 1 && jj - 1 < n_words) ? __ldg(s + (jj - 1)) : 0ull;
+		}
+		__syncthreads();
+		// 32 symbols starting at segment position q, from the staged words when they cover it
+		auto win = [&](uint32_t q) -> Planes
+		{
+			const uint32_t jq = q >> 5, sh = q & 31;
+			if (jq + 1 >= jb && jq + 1 - jb + 1 < NT + 4)
+			{
+				const Planes a = planes_of(tile_w[jq + 1 - jb]);
+				return sh ? shift_in(a, planes_of(tile_w[jq + 2 - jb]), sh) : a;
+			}
+			Planes a = planes_of(jq < n_words ? __ldg(s + jq) : 0ull);
+			if (sh) a = shift_in(a, planes_of(jq + 1 < n_words ? __ldg(s + jq + 1) : 0ull), sh);
+			return a;
+		};
 		const uint32_t p0 = tile + threadIdx.x * 32;
-		const uint32_t j = p0 >> 5;
 		const bool active = p0 < n;
-		uint64_t w0 = 0, w1 = 0;
-		if (active) { w0 = __ldg(s + j); if (j + 1 < n_words) w1 = __ldg(s + j + 1); }
+		const Planes am = planes_of(tile_w[threadIdx.x]), a0 = planes_of(tile_w[threadIdx.x + 1]), a1 = planes_of(tile_w[threadIdx.x + 2]),
+			a2 = planes_of(tile_w[threadIdx.x + 3]);
 		// ---- candidates: starts of stretches of eq_m of length >= m, with the end of the run they open
 		uint32_t local_max = 0;
 		uint32_t cand_bits = 0;
@@ -396,28 +469,33 @@ __global__ void __launch_bounds__(NT) k_msat(SegTable seg, const uint64_t* __res
 			{
 				if (n < 2 * m) break;
 				const uint32_t lim = n - m;            // eq_m(p) is defined for p < lim
-				uint64_t e0 = eq_shift(w0, w1, m);
-				uint64_t e1 = eq_shift(w1, 0, m) & low_pairs(32 - m); // what w1 alone determines
-				e0 &= lim > p0 ? low_pairs(min(32u, lim - p0)) : 0ull;
-				e1 &= lim > p0 + 32 ? low_pairs(min(32u, lim - p0 - 32)) : 0ull;
-				uint64_t prev = 0;
-				if (p0 > 0 && p0 - 1 < lim) prev = symbol_at(s, p0 - 1) == symbol_at(s, p0 - 1 + m) ? 1ull : 0ull;
-				uint64_t run = e0 & ~((e0 << 2) | prev);
-				for (uint32_t t = 1; t < m; t++) run &= (e0 >> (2 * t)) | (e1 << (64 - 2 * t));
+				uint32_t e0 = eq_shift(a0, a1, m), e1 = eq_shift(a1, a2, m);
+				e0 &= lim > p0 ? low_bits(min(32u, lim - p0)) : 0u;
+				e1 &= lim > p0 + 32 ? low_bits(min(32u, lim - p0 - 32)) : 0u;
+				uint32_t prev = 0;
+				if (p0 > 0 && p0 - 1 < lim) prev = eq_shift(am, a0, m) >> 31;
+				uint32_t run = e0 & ~((e0 << 1) | prev);
+				for (uint32_t t = 1; t < m; t++) run &= funnel_r(e0, e1, t);
+				const uint64_t e64 = word_of(e0, e1);
 				while (run)
 				{
-					const uint32_t b = (uint32_t)(__ffsll((long long)run) - 1) >> 1;
+					const uint32_t b = __ffs(run) - 1;
 					run &= run - 1;
-					// eq_m holds on [a, a+m); walk on, 32 symbols per step, to the first p with sym[p] != sym[p+m]
-					uint32_t q = p0 + b + m;
-					while (q < lim)
+					// eq_m holds from b to the first zero of e64 above it; beyond the 64 positions this thread sees, walk on
+					const uint64_t stop = ~(e64 >> b);
+					uint32_t q = p0 + b + (stop ? (uint32_t)(__ffsll((long long)stop) - 1) : 64u);
+					if (q >= p0 + 64)
 					{
-						const uint64_t d = window64(s, q) ^ window64(s, q + m);
-						uint64_t ne = (d | (d >> 1)) & 0x5555555555555555ull;
-						const uint32_t room = lim - q;
-						if (room < 32) ne |= ~low_pairs(room) & 0x5555555555555555ull;
-						if (ne) { q += (uint32_t)(__ffsll((long long)ne) - 1) >> 1; break; }
-						q += 32;
+						q = p0 + 64;
+						while (q < lim)
+						{
+							const Planes x = win(q), y = win(q + m);
+							uint32_t ne = (x.lo ^ y.lo) | (x.hi ^ y.hi);
+							const uint32_t room = lim - q;
+							if (room < 32) ne |= ~low_bits(room);
+							if (ne) { q += __ffs(ne) - 1; break; }
+							q += 32;
+						}
 					}
 					if (q > lim) q = lim;
 					const uint32_t end = q + m;
@@ -462,20 +540,20 @@ __global__ void __launch_bounds__(NT) k_msat(SegTable seg, const uint64_t* __res
 		if (active)
 		{
 			const uint32_t nvalid = min(32u, n - p0);
-			const uint32_t valid = nvalid >= 32 ? FULL : ((1u << nvalid) - 1);
+			const uint32_t valid = low_bits(nvalid);
 			const uint32_t pe_in = last_in.m ? last_in.prev_end : 0;
-			uint32_t ge1 = pm_in > p0 ? (pm_in - p0 >= 32 ? FULL : ((1u << (pm_in - p0)) - 1)) : 0;
-			uint32_t ge2 = pe_in > p0 ? (pe_in - p0 >= 32 ? FULL : ((1u << (pe_in - p0)) - 1)) : 0;
+			uint32_t ge1 = pm_in > p0 ? low_bits(pm_in - p0) : 0;
+			uint32_t ge2 = pe_in > p0 ? low_bits(pe_in - p0) : 0;
 			uint32_t running = pm_in;
 			uint32_t eb = emit_bits;
 			while (eb)
 			{
 				const uint32_t b = __ffs(eb) - 1; eb &= eb - 1;
 				const uint32_t end = my_cand[b] >> 3;
-				const uint32_t from = ~((1u << b) - 1);
-				ge1 |= from & (end - p0 >= 32 ? FULL : ((1u << (end - p0)) - 1));
+				const uint32_t from = ~low_bits(b);
+				ge1 |= from & low_bits(end - p0);
 				ge2 &= ~from;
-				if (running > p0 + b) ge2 |= from & (running - p0 >= 32 ? FULL : ((1u << (running - p0)) - 1));
+				if (running > p0 + b) ge2 |= from & low_bits(running - p0);
 				running = end;
 			}
 			cover1 = ge1 & ~ge2 & valid;
@@ -486,60 +564,56 @@ __global__ void __launch_bounds__(NT) k_msat(SegTable seg, const uint64_t* __res
 		}
 		// ---- scan 3: index of the first code that starts in this word
 		uint32_t tile_codes;
-		uint32_t idx = block_exclusive_sum<NT>(__popc(flags), warp_tmp, tile_codes) + carry_codes;
-		// ---- codes: a single-symbol code at every flag outside cover == 1; a stretch of cover == 1 is written when
-		//      it ends (at the next flag, or at n), by the thread that owns the symbol after it
+		const uint32_t idx = block_exclusive_sum<NT>(__popc(flags), warp_tmp, tile_codes) + carry_codes;
 		if (active)
 		{
-			LastRun cur = last_in;          // latest emitted run starting before the cursor
-			uint32_t run_end = pm_in;       // end of that run (== prefix maximum)
-			uint32_t eb = emit_bits;
-			uint32_t fb = flags;
-			const bool owns_end = p0 + 32 >= n;
-			while (true)
+			// ---- single-symbol codes: every code start outside cover == 1
+			uint32_t sb = flags & ~cover1;
+			while (sb)
+			{
+				const uint32_t b = __ffs(sb) - 1; sb &= sb - 1;
+				const uint32_t oi = idx + __popc(flags & low_bits(b));
+				const uint32_t sc = ((a0.lo >> b) & 1) | (((a0.hi >> b) & 1) << 1);
+				codes[out0 + oi] = (uint16_t)sc;
+				rrc[rr0 - oi] = (uint16_t)(3 - sc);
+				if (pos2) pos2[out0 + oi] = pos1 ? pos1[out0 + p0 + b] : p0 + b;
+			}
+			// ---- stretches of cover == 1 that end in this word: at a code start whose predecessor is covered once, or at n
+			uint32_t ends = flags & ((cover1 << 1) | (prev_cover1 ? 1u : 0u));
+			const uint32_t nvalid = min(32u, n - p0);
+			bool tail = p0 + 32 >= n && ((cover1 >> (nvalid - 1)) & 1);    // the segment ends inside a stretch
+			while (ends || tail)
 			{
 				uint32_t b;
-				bool at_end = false;
-				if (fb) { b = __ffs(fb) - 1; fb &= fb - 1; }
-				else if (owns_end) { b = n - p0; at_end = true; }
-				else break;
-				// runs emitted at symbols before b now precede the cursor
-				while (eb && (uint32_t)(__ffs(eb) - 1) < b)
-				{
-					const uint32_t bb = __ffs(eb) - 1; eb &= eb - 1;
-					cur.start = p0 + bb; cur.prev_end = run_end; cur.m = 7 - (my_cand[bb] & 7);
-					run_end = my_cand[bb] >> 3;
-				}
+				if (ends) { b = __ffs(ends) - 1; ends &= ends - 1; } else { b = nvalid; tail = false; }
 				const uint32_t q = p0 + b;
-				const bool before_cover1 = b == 0 ? prev_cover1 : ((cover1 >> (b - 1)) & 1) != 0;
-				if (before_cover1)
+				const uint32_t oi = idx + __popc(flags & low_bits(b)) - 1;
+				// the latest emitted run that starts before q, and the end of the run emitted before it
+				LastRun cur = last_in;
+				const uint32_t below = emit_bits & low_bits(b);
+				if (below)
 				{
-					// symbols [ps, q) are covered by `cur` alone: one code with its motif length (clamped to the stretch)
-					const uint32_t ps = max(cur.start, cur.prev_end);
-					const uint32_t slen = q - ps;
-					const uint32_t m = min(cur.m, slen);
-					uint32_t motif = 0;
-					for (uint32_t i = 0; i < m; i++) motif = (motif << 2) | symbol_at(s, ps + i);
-					const uint32_t oi = idx - 1;
-					const uint32_t code = CODES_BEFORE[m] + motif * m + (slen % m);
-					codes[out0 + oi] = (uint16_t)code;
-					rrc[rr0 - oi] = code < 4 ? (uint16_t)(3 - code) : __ldg(tab_comp + code);
-					if (pos2) pos2[out0 + oi] = pos1 ? pos1[out0 + ps] : ps;
+					const uint32_t bb = 31 - __clz(below);
+					const uint32_t below2 = below & low_bits(bb);
+					cur.start = p0 + bb;
+					cur.m = 7 - (my_cand[bb] & 7);
+					cur.prev_end = below2 ? (my_cand[31 - __clz(below2)] >> 3) : pm_in;
 				}
-				if (at_end) break;
-				if (!((cover1 >> b) & 1))
-				{
-					const uint32_t sc = (uint32_t)(w0 >> (2 * b)) & 3;
-					codes[out0 + idx] = (uint16_t)sc;
-					rrc[rr0 - idx] = (uint16_t)(3 - sc);
-					if (pos2) pos2[out0 + idx] = pos1 ? pos1[out0 + q] : q;
-				}
-				idx++;
+				// symbols [ps, q) are covered by `cur` alone: one code with its motif length (clamped to the stretch)
+				const uint32_t ps = max(cur.start, cur.prev_end);
+				const uint32_t slen = q - ps;
+				const uint32_t m = min(cur.m, slen);
+				uint32_t code, rc_code;
+				stretch_codes(win(ps), m, slen, code, rc_code);
+				codes[out0 + oi] = (uint16_t)code;
+				rrc[rr0 - oi] = (uint16_t)rc_code;
+				if (pos2) pos2[out0 + oi] = pos1 ? pos1[out0 + ps] : ps;
 			}
 		}
 		carry_max = max(carry_max, tile_max);
 		if (tile_last.m) carry_last = tile_last;
 		carry_codes += tile_codes;
+		__syncthreads();    // the staged words are replaced at the top of the next tile
 	}
 	if (threadIdx.x == 0)
 	{
@@ -561,7 +635,7 @@ __global__ void __launch_bounds__(NT) k_unpack_symbols(SegTable seg, const uint6
 	const uint64_t* __restrict__ s = sym + (out0 >> 5);
 	for (uint32_t p = threadIdx.x; p < n; p += NT)
 	{
-		const uint32_t sc = (uint32_t)(__ldg(s + (p >> 5)) >> ((p & 31) * 2)) & 3;
+		const uint32_t sc = symbol_at(s, p);
 		codes[out0 + p] = (uint16_t)sc;
 		rrc[rr0 - p] = (uint16_t)(3 - sc);
 		if (pos2) pos2[out0 + p] = pos1 ? pos1[out0 + p] : p;

@@ -531,9 +531,9 @@ int mbgfe_upload(mbgfe* h)
 	tick(h, 1);
 	if (n_bases)
 	{
-		const uint64_t chunks = (n_bases + 15) / 16;
+		const uint64_t chunks = (n_bases + 31) / 32;
 		const unsigned grid = (unsigned)std::min<uint64_t>((chunks + 255) / 256, (uint64_t)h->sm_count * 16);
-		MBGFE_LAUNCH(k_pack_ascii, grid, 256, 0, h->stream, (const uint4*)h->d_ascii.p, n_bases, (uint64_t)0, chunks, h->d_packed.as<uint32_t>(), h->d_nonacgt.as<uint64_t>(),
+		MBGFE_LAUNCH(k_pack_ascii, grid, 256, 0, h->stream, (const uint4*)h->d_ascii.p, n_bases, (uint64_t)0, chunks, h->d_packed.as<uint64_t>(), h->d_nonacgt.as<uint64_t>(),
 			h->d_counters.as<unsigned long long>() + CTR_NONACGT, bad_cap);
 	}
 	tick(h, 2);
@@ -609,7 +609,7 @@ uint32_t launch_front(mbgfe* h, uint32_t g0, uint32_t cnt, bool timed)
 	if (timed) tick(h, 4);
 	if (h->msat)
 		MBGFE_LAUNCH(k_msat<NT_MSAT>, cnt, NT_MSAT, 0, h->stream, st, h->d_sym.as<uint64_t>(), c1, h->d_codes.as<uint16_t>(), h->d_rrc.as<uint16_t>(),
-			h->tab_comp.as<uint16_t>(), c2, (const uint32_t*)pos1, pos2, h->max_motif);
+			c2, (const uint32_t*)pos1, pos2, h->max_motif);
 	else
 		MBGFE_LAUNCH(k_unpack_symbols<NT_MSAT>, cnt, NT_MSAT, 0, h->stream, st, h->d_sym.as<uint64_t>(), c1, h->d_codes.as<uint16_t>(),
 			h->d_rrc.as<uint16_t>(), c2, (const uint32_t*)pos1, pos2);
@@ -794,12 +794,12 @@ int mbgfe_run(mbgfe* h)
 			piece++;
 			pos += len;
 			const bool last = pos == n_bases;
-			const uint64_t pack_to = last ? n_bases : (pos & ~(uint64_t)15);
+			const uint64_t pack_to = last ? n_bases : (pos & ~(uint64_t)31);
 			if (pack_to > packed_upto)
 			{
-				const uint64_t c0 = packed_upto / 16, c1 = (pack_to + 15) / 16;
+				const uint64_t c0 = packed_upto / 32, c1 = (pack_to + 31) / 32;
 				const unsigned grid = (unsigned)std::min<uint64_t>((c1 - c0 + 255) / 256, (uint64_t)h->sm_count * 16);
-				MBGFE_LAUNCH(k_pack_ascii, grid, 256, 0, h->stream, (const uint4*)h->d_ascii.p, n_bases, c0, c1, h->d_packed.as<uint32_t>(), h->d_nonacgt.as<uint64_t>(),
+				MBGFE_LAUNCH(k_pack_ascii, grid, 256, 0, h->stream, (const uint4*)h->d_ascii.p, n_bases, c0, c1, h->d_packed.as<uint64_t>(), h->d_nonacgt.as<uint64_t>(),
 					h->d_counters.as<unsigned long long>() + CTR_NONACGT, bad_cap);
 				launches++;
 				packed_upto = pack_to;
