@@ -157,16 +157,36 @@ int mbgfe_get_stats(const mbgfe* h, mbgfe_stats* out);
 int mbgfe_timer_start(mbgfe* h);
 int mbgfe_timer_stop(mbgfe* h, float* ms);
 
-/* Multi-GPU sharding by k-mer owner.  After mbgfe_process() with MBGFE_NO_TABLE on every rank:
- *   mbgfe_exchange_counts  fills send_counts[world] = records this rank holds for each owner;
- *   mbgfe_exchange_pack    writes the records, grouped by owner, into a device buffer and returns its address;
- *   (the caller moves them with an NCCL all-to-all-v between device buffers)
- *   mbgfe_exchange_insert  counts n_records received records (device pointer) into this rank's table partition.
- * A record is 32 bytes: canonical hash lo, hi, flags (bit 0 tip), reserved. */
+/* Multi-GPU sharding by k-mer owner (the reference has no multi-device path -- its HashList is one
+ * process-wide map behind a mutex, MBG/HashList.h:15-48).  One process and one handle per GPU, reads sharded by rank in
+ * contiguous blocks, canonical hashes range-partitioned (owner = floor(hash.hi * world / 2^64)), so that concatenating
+ * the ranks' sorted partitions IS the global sortByHash order.  After mbgfe_process() with MBGFE_NO_TABLE on every rank:
+ *
+ *   nodes   mbgfe_exchange_counts   send_counts[world] = records this rank holds for each owner
+ *           mbgfe_exchange_pack     writes the 32-byte records {canonical hash lo, hi, flags (bit 0 tip), reserved},
+ *                                   grouped by owner, into a device buffer and returns its address
+ *           (the caller moves them with an NCCL all-to-all-v between device buffers)
+ *           mbgfe_exchange_insert   counts n_records received records (device pointer) into this rank's partition
+ *   ids     mbgfe_exchange_node_ids global node id (id_base = nodes owned by lower ranks, + rank in the partition) of
+ *                                   every received record, uint32 each, in the order received; the caller sends them
+ *                                   back with the reverse all-to-all-v, so every rank learns the ids of its own k-mers
+ *   edges   mbgfe_exchange_edge_counts / _pack   16-byte records {canonical (from, to) key, (global instance index
+ *                                   << 24) | overlap} for every consecutive selected pair, grouped by the rank that owns
+ *                                   `from` (id_begin[world + 1] = first node id of every rank); device_ids = the ids
+ *                                   received for this rank's packed records; inst_base = selected k-mers on lower
+ *                                   ranks (keeps "last observation in input order" global, MBG/HashList.cpp:67-72)
+ *           mbgfe_exchange_insert_edges          counts received edge records into this rank's edge partition
+ *   mbgfe_exchange_scratch  device scratch buffer `which` (0..3) of at least `bytes` bytes for the caller's receives.
+ * Afterwards MBGFE_NODE_* / MBGFE_EDGES return this rank's partition with GLOBAL node ids (limit 2^31-1 nodes). */
 int mbgfe_exchange_counts(mbgfe* h, uint64_t* send_counts);
 int mbgfe_exchange_pack(mbgfe* h, void** device_records);
 int mbgfe_exchange_reserve(mbgfe* h, uint64_t n_records, void** device_recv);
 int mbgfe_exchange_insert(mbgfe* h, const void* device_records, uint64_t n_records);
+int mbgfe_exchange_scratch(mbgfe* h, uint32_t which, uint64_t bytes, void** device_ptr);
+int mbgfe_exchange_node_ids(mbgfe* h, uint64_t id_base, const void* device_records, uint64_t n_records, void** device_ids);
+int mbgfe_exchange_edge_counts(mbgfe* h, const void* device_ids, const uint64_t* id_begin, uint64_t inst_base, uint64_t* send_counts);
+int mbgfe_exchange_edge_pack(mbgfe* h, const uint64_t* send_counts, void** device_records);
+int mbgfe_exchange_insert_edges(mbgfe* h, const void* device_records, uint64_t n_records);
 
 /* Known-answer access to the device primitives (each runs a tiny kernel): per-code hash of the rolling hasher
  * (MBG/FastHasher.cpp:33-43), code complement (MBG/ErrorMaskHelper.cpp:43-100), k-mer hash (MBG/MBGCommon.cpp:25-35). */

@@ -30,13 +30,15 @@ def _worker(rank, world, port, emu, out_dir):
     fe.run()
     counter = DistributedCounter(fe, world, rank, on_gpu=False)
     counter.exchange_and_count()
-    np.savez(os.path.join(out_dir, f"rank{rank}.npz"), node_hash=fe.node_hashes(), node_cov=fe.node_coverage(), node_tip=fe.node_tip())
+    np.savez(os.path.join(out_dir, f"rank{rank}.npz"), node_hash=fe.node_hashes(), node_cov=fe.node_coverage(), node_tip=fe.node_tip(), edges=fe.edges(),
+             id_begin=counter.id_begin)
     fe.close()
     dist.barrier()
     dist.destroy_process_group()
 
 
-def test_two_rank_partitioned_counting(oracle, emu_library, tmp_path):
+@pytest.mark.parametrize("world", [2, 3])
+def test_partitioned_counting(oracle, emu_library, tmp_path, world):
     import socket
     import workloads
     from verkko_b200.distributed import owner_of
@@ -44,7 +46,6 @@ def test_two_rank_partitioned_counting(oracle, emu_library, tmp_path):
     s.bind(("127.0.0.1", 0))
     port = s.getsockname()[1]
     s.close()
-    world = 2
     mp.spawn(_worker, args=(world, port, emu_library, str(tmp_path)), nprocs=world, join=True)
     want = oracle.run("collapse-msat", 501, 50, workloads.coverage_reads(n_reads=8))
     parts = [np.load(tmp_path / f"rank{r}.npz") for r in range(world)]
@@ -55,3 +56,12 @@ def test_two_rank_partitioned_counting(oracle, emu_library, tmp_path):
     cov = np.concatenate([p["node_cov"] for p in parts])
     tip = np.concatenate([p["node_tip"] for p in parts])
     assert np.array_equal(nh, want.node_hash) and np.array_equal(cov, want.node_cov) and np.array_equal(tip, want.node_tip)
+    # edges: every rank holds the edges whose `from` node it owns, with global ids, each partition sorted like the
+    # single-GPU export; concatenated they are the oracle's edge table
+    id_begin = parts[0]["id_begin"]
+    for r, p in enumerate(parts):
+        e = p["edges"]
+        assert np.all((e[:, 0] >= id_begin[r]) & (e[:, 0] < id_begin[r + 1])), "edge on the wrong owner"
+    from oracle_lib import sorted_edges
+    edges = np.concatenate([p["edges"] for p in parts])
+    assert np.array_equal(sorted_edges(edges), sorted_edges(want.edges))

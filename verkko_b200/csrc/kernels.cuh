@@ -1338,9 +1338,53 @@ __global__ void __launch_bounds__(256) k_edge_clear(EdgeSlot* __restrict__ table
 	}
 }
 
-// K4b: adjacency.  One thread per instance that has a predecessor in its part: canonical edge
-// (MBG/MBGCommon.cpp:78-89, decided by comparing canonical hashes, which is the id order after sortByHash),
-// coverage += 1, overlap = prev_pos + k - pos (MBG/MBG.cpp:59-67).
+// Canonical edge between two consecutive selected k-mers of a part (MBG/MBGCommon.cpp:78-89): the pair is reversed
+// when the target's canonical hash is smaller (== smaller id after sortByHash), or when both are the same node in
+// reverse orientation.  a_id / b_id are whatever names the nodes in the table being built (table slots on one GPU,
+// global node ids when the table is sharded); the decision itself only looks at the hashes.
+__device__ __forceinline__ unsigned long long canonical_edge_key(uint64_t a_lo, uint64_t a_hi, uint64_t b_lo, uint64_t b_hi, uint32_t a_id, uint32_t b_id)
+{
+	uint64_t ak_lo, ak_hi, bk_lo, bk_hi; uint32_t afw, bfw;
+	canonical_key(a_lo, a_hi, ak_lo, ak_hi, afw);
+	canonical_key(b_lo, b_hi, bk_lo, bk_hi, bfw);
+	uint32_t from = a_id, to = b_id;
+	uint32_t from_fw = afw, to_fw = bfw;
+	const bool to_smaller = bk_hi < ak_hi || (bk_hi == ak_hi && bk_lo < ak_lo);
+	const bool same = bk_hi == ak_hi && bk_lo == ak_lo;
+	if (to_smaller || (same && !to_fw && !from_fw))
+	{
+		const uint32_t t = from; from = to; to = t;
+		const uint32_t f = from_fw; from_fw = !to_fw; to_fw = !f;
+	}
+	return ((unsigned long long)(((uint64_t)from << 1) | from_fw) << 32) | (((uint64_t)to << 1) | to_fw);
+}
+
+// insert-or-update of one edge observation: coverage += 1, overlap of the latest observation in input order
+__device__ __forceinline__ bool edge_insert(EdgeSlot* __restrict__ table, uint64_t mask, unsigned long long key, unsigned long long ordered)
+{
+	uint64_t slot = slot_hash(key, key >> 17) & mask;
+	bool is_new = false;
+	while (true)
+	{
+		EdgeSlot* sp = table + slot;
+		unsigned long long cur = *(volatile unsigned long long*)&sp->key;
+		if (cur == ~0ull)
+		{
+			const unsigned long long old = atomicCAS(&sp->key, ~0ull, key);
+			if (old == ~0ull) { is_new = true; cur = key; } else cur = old;
+		}
+		if (cur == key)
+		{
+			atomicAdd(&sp->count, 1u);
+			atomicMax(&sp->ordered, ordered);
+			return is_new;
+		}
+		slot = (slot + 1) & mask;
+	}
+}
+
+// K4b: adjacency.  One thread per instance that has a predecessor in its part: canonical edge, coverage += 1,
+// overlap = prev_pos + k - pos (MBG/MBG.cpp:59-67).
 __global__ void __launch_bounds__(256) k_insert_edges(const uint64_t* __restrict__ inst_hash, const uint32_t* __restrict__ inst_pos, const uint8_t* __restrict__ inst_flag,
 	const uint32_t* __restrict__ inst_slot, uint64_t n_inst, EdgeSlot* __restrict__ table, uint64_t mask, unsigned long long* __restrict__ distinct, uint32_t k)
 {
@@ -1348,39 +1392,9 @@ __global__ void __launch_bounds__(256) k_insert_edges(const uint64_t* __restrict
 	bool is_new = false;
 	if (i < n_inst && i > 0 && !(inst_flag[i] & 1) && inst_slot[i] != 0xffffffffu && inst_slot[i - 1] != 0xffffffffu)
 	{
-		uint64_t ak_lo, ak_hi, bk_lo, bk_hi; uint32_t afw, bfw;
-		canonical_key(inst_hash[2 * (i - 1)], inst_hash[2 * (i - 1) + 1], ak_lo, ak_hi, afw);
-		canonical_key(inst_hash[2 * i], inst_hash[2 * i + 1], bk_lo, bk_hi, bfw);
-		uint32_t from = inst_slot[i - 1], to = inst_slot[i];
-		uint32_t from_fw = afw, to_fw = bfw;
-		const bool to_smaller = bk_hi < ak_hi || (bk_hi == ak_hi && bk_lo < ak_lo);
-		const bool same = bk_hi == ak_hi && bk_lo == ak_lo;
-		if (to_smaller || (same && !to_fw && !from_fw))
-		{
-			const uint32_t t = from; from = to; to = t;
-			const uint32_t f = from_fw; from_fw = !to_fw; to_fw = !f;
-		}
-		const unsigned long long key = ((unsigned long long)(((uint64_t)from << 1) | from_fw) << 32) | (((uint64_t)to << 1) | to_fw);
+		const unsigned long long key = canonical_edge_key(inst_hash[2 * (i - 1)], inst_hash[2 * (i - 1) + 1], inst_hash[2 * i], inst_hash[2 * i + 1], inst_slot[i - 1], inst_slot[i]);
 		const uint32_t overlap = inst_pos[i - 1] + k - inst_pos[i];
-		const unsigned long long ordered = ((unsigned long long)i << 24) | overlap;
-		uint64_t slot = slot_hash(key, key >> 17) & mask;
-		while (true)
-		{
-			EdgeSlot* sp = table + slot;
-			unsigned long long cur = *(volatile unsigned long long*)&sp->key;
-			if (cur == ~0ull)
-			{
-				const unsigned long long old = atomicCAS(&sp->key, ~0ull, key);
-				if (old == ~0ull) { is_new = true; cur = key; } else cur = old;
-			}
-			if (cur == key)
-			{
-				atomicAdd(&sp->count, 1u);
-				atomicMax(&sp->ordered, ordered);
-				break;
-			}
-			slot = (slot + 1) & mask;
-		}
+		is_new = edge_insert(table, mask, key, ((unsigned long long)i << 24) | overlap);
 	}
 	warp_count(distinct, is_new);
 }
@@ -1455,8 +1469,10 @@ __device__ __forceinline__ EdgeRec edge_record(const EdgeSlot& s, const NodeSlot
 {
 	const uint32_t a = (uint32_t)(s.key >> 32), b = (uint32_t)s.key;
 	EdgeRec r;
-	r.from = (uint32_t)nodes[a >> 1].rank; r.from_fw = a & 1;
-	r.to = (uint32_t)nodes[b >> 1].rank; r.to_fw = b & 1;
+	// single GPU: the key names table slots, translated to ids through the ranks left by the node export;
+	// sharded table (nodes == nullptr): the key already holds global node ids
+	r.from = nodes ? (uint32_t)nodes[a >> 1].rank : (a >> 1); r.from_fw = a & 1;
+	r.to = nodes ? (uint32_t)nodes[b >> 1].rank : (b >> 1); r.to_fw = b & 1;
 	r.coverage = s.count;
 	r.overlap = (uint32_t)(s.ordered & 0xffffff);
 	return r;
@@ -1468,26 +1484,26 @@ __device__ __forceinline__ uint64_t edge_order_key(const EdgeRec& r)
 }
 
 __global__ void __launch_bounds__(256) k_edge_bucket_count(const EdgeSlot* __restrict__ table, uint64_t n_slots, const NodeSlot* __restrict__ nodes, uint32_t shift,
-	uint32_t* __restrict__ counts)
+	uint32_t id_base, uint32_t* __restrict__ counts)
 {
 	for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n_slots; i += (uint64_t)gridDim.x * blockDim.x)
 	{
 		const unsigned long long key = table[i].key;
 		if (key == ~0ull) continue;
-		const uint32_t from = (uint32_t)nodes[key >> 33].rank;
-		atomicAdd(counts + (from >> shift), 1u);
+		const uint32_t from = nodes ? (uint32_t)nodes[key >> 33].rank : (uint32_t)(key >> 33);
+		atomicAdd(counts + ((from - id_base) >> shift), 1u);
 	}
 }
 
 __global__ void __launch_bounds__(256) k_edge_bucket_scatter(const EdgeSlot* __restrict__ table, uint64_t n_slots, const NodeSlot* __restrict__ nodes, uint32_t shift,
-	const uint64_t* __restrict__ bucket_begin, uint32_t* __restrict__ fill, EdgeRec* __restrict__ tmp)
+	uint32_t id_base, const uint64_t* __restrict__ bucket_begin, uint32_t* __restrict__ fill, EdgeRec* __restrict__ tmp)
 {
 	for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n_slots; i += (uint64_t)gridDim.x * blockDim.x)
 	{
 		const EdgeSlot s = table[i];
 		if (s.key == ~0ull) continue;
 		const EdgeRec r = edge_record(s, nodes);
-		const uint32_t b = r.from >> shift;
+		const uint32_t b = (r.from - id_base) >> shift;
 		tmp[bucket_begin[b] + atomicAdd(fill + b, 1u)] = r;
 	}
 }
@@ -1531,16 +1547,86 @@ __global__ void __launch_bounds__(256) k_owner_count(const uint64_t* __restrict_
 }
 
 __global__ void __launch_bounds__(256) k_owner_pack(const uint64_t* __restrict__ inst_hash, const uint8_t* __restrict__ inst_flag, uint64_t n_inst, uint32_t world,
-	unsigned long long* __restrict__ cursors, uint64_t* __restrict__ records)
+	unsigned long long* __restrict__ cursors, uint64_t* __restrict__ records, uint32_t* __restrict__ inst_packpos)
 {
 	const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
 	if (i >= n_inst) return;
 	uint64_t lo = inst_hash[2 * i], hi = inst_hash[2 * i + 1];
-	if (lo == hi) return;
+	if (lo == hi) { inst_packpos[i] = 0xffffffffu; return; }
 	uint64_t key_lo, key_hi; uint32_t fw;
 	canonical_key(lo, hi, key_lo, key_hi, fw);
 	unsigned long long o = atomicAdd(cursors + owner_of(key_hi, world), 1ull);
 	records[4 * o] = key_lo; records[4 * o + 1] = key_hi; records[4 * o + 2] = inst_flag[i] ? 1 : 0; records[4 * o + 3] = 0;
+	inst_packpos[i] = (uint32_t)o;     // where the owner's answer (the global node id) will come back
+}
+
+// owner side: global node id of every received record, in the order received.  Needs the ranks left in the table by
+// the node export (k_node_bucket_rank); id = id_base (number of nodes owned by lower ranks) + rank.
+__global__ void __launch_bounds__(256) k_record_ids(const uint64_t* __restrict__ rec, uint64_t n_rec, const NodeSlot* __restrict__ table, uint64_t mask, uint32_t id_base,
+	uint32_t* __restrict__ ids)
+{
+	const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+	if (i >= n_rec) return;
+	const uint64_t key_lo = rec[4 * i], key_hi = rec[4 * i + 1];
+	uint64_t slot = slot_hash(key_lo, key_hi) & mask;
+	while (true)
+	{
+		const NodeSlot* sp = table + slot;
+		if (sp->key_lo == key_lo && sp->key_hi == key_hi) { ids[i] = id_base + (uint32_t)sp->rank; return; }
+		slot = (slot + 1) & mask;      // every received record was inserted, so the probe always ends on its key
+	}
+}
+
+// sender side: edge observations as 16-byte records {canonical (from id, to id) key, (global instance index << 24) |
+// overlap}, sent to the rank that owns `from` (node ids are dealt to ranks in contiguous ranges: id_begin[r] ..
+// id_begin[r+1]), so each rank's sorted edge partition continues the previous one.
+__device__ __forceinline__ bool edge_observation(uint64_t i, uint64_t n_inst, const uint64_t* __restrict__ inst_hash, const uint32_t* __restrict__ inst_pos,
+	const uint8_t* __restrict__ inst_flag, const uint32_t* __restrict__ inst_packpos, const uint32_t* __restrict__ packed_ids, uint64_t inst_base, uint32_t k,
+	unsigned long long& key, unsigned long long& ordered)
+{
+	if (i >= n_inst || i == 0 || (inst_flag[i] & 1)) return false;
+	const uint32_t pa = inst_packpos[i - 1], pb = inst_packpos[i];
+	if (pa == 0xffffffffu || pb == 0xffffffffu) return false;
+	key = canonical_edge_key(inst_hash[2 * (i - 1)], inst_hash[2 * (i - 1) + 1], inst_hash[2 * i], inst_hash[2 * i + 1], packed_ids[pa], packed_ids[pb]);
+	ordered = ((unsigned long long)(inst_base + i) << 24) | (inst_pos[i - 1] + k - inst_pos[i]);
+	return true;
+}
+
+__device__ __forceinline__ uint32_t id_owner(uint32_t id, const uint64_t* __restrict__ id_begin, uint32_t world)
+{
+	uint32_t r = 0;
+	while (r + 1 < world && (uint64_t)id >= id_begin[r + 1]) r++;
+	return r;
+}
+
+__global__ void __launch_bounds__(256) k_edge_owner_count(const uint64_t* __restrict__ inst_hash, const uint32_t* __restrict__ inst_pos, const uint8_t* __restrict__ inst_flag,
+	const uint32_t* __restrict__ inst_packpos, const uint32_t* __restrict__ packed_ids, uint64_t n_inst, uint64_t inst_base, uint32_t k, const uint64_t* __restrict__ id_begin,
+	uint32_t world, unsigned long long* __restrict__ counts)
+{
+	const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+	unsigned long long key, ordered;
+	if (!edge_observation(i, n_inst, inst_hash, inst_pos, inst_flag, inst_packpos, packed_ids, inst_base, k, key, ordered)) return;
+	atomicAdd(counts + id_owner((uint32_t)(key >> 33), id_begin, world), 1ull);
+}
+
+__global__ void __launch_bounds__(256) k_edge_owner_pack(const uint64_t* __restrict__ inst_hash, const uint32_t* __restrict__ inst_pos, const uint8_t* __restrict__ inst_flag,
+	const uint32_t* __restrict__ inst_packpos, const uint32_t* __restrict__ packed_ids, uint64_t n_inst, uint64_t inst_base, uint32_t k, const uint64_t* __restrict__ id_begin,
+	uint32_t world, unsigned long long* __restrict__ cursors, unsigned long long* __restrict__ records)
+{
+	const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+	unsigned long long key, ordered;
+	if (!edge_observation(i, n_inst, inst_hash, inst_pos, inst_flag, inst_packpos, packed_ids, inst_base, k, key, ordered)) return;
+	const unsigned long long o = atomicAdd(cursors + id_owner((uint32_t)(key >> 33), id_begin, world), 1ull);
+	records[2 * o] = key; records[2 * o + 1] = ordered;
+}
+
+__global__ void __launch_bounds__(256) k_insert_edge_records(const unsigned long long* __restrict__ rec, uint64_t n_rec, EdgeSlot* __restrict__ table, uint64_t mask,
+	unsigned long long* __restrict__ distinct)
+{
+	const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+	bool is_new = false;
+	if (i < n_rec) is_new = edge_insert(table, mask, rec[2 * i], rec[2 * i + 1]);
+	warp_count(distinct, is_new);
 }
 
 // KAT helper: complement table and per-code hash are read back directly; the k-mer hash runs k_kmer_hash on one

@@ -90,6 +90,11 @@ struct mbgfe
 	DevBuf d_sym, d_codes, d_rrc, d_selmask, d_pos1, d_pos2;
 	DevBuf d_inst_pos, d_inst_seg, d_inst_flag, d_inst_hash, d_inst_slot, d_pal_list;
 	DevBuf d_nodes, d_edges, d_node_out, d_edge_out, d_records, d_recv;
+	DevBuf d_inst_packpos, d_ids_out, d_id_begin, d_edge_records, d_xbuf[4];   // sharded table: id replies and edge records
+	const void* x_packed_ids = nullptr;                                      // ids of this rank's packed records, as received
+	uint64_t x_inst_base = 0;
+	uint32_t id_base = 0;                                                    // nodes owned by lower ranks
+	bool nodes_ranked = false, edges_global = false;
 	DevBuf d_bucket_count, d_bucket_begin, d_scan_tot, d_scan_off;      // export: bucket tables and scan scratch
 	DevBuf d_node_hash_sorted, d_node_cov, d_node_tip, d_edges_sorted;    // export: final layout, device resident
 	uint64_t node_slots = 0, edge_slots = 0;
@@ -277,6 +282,7 @@ int download(mbgfe* h, std::vector<T>& dst, const DevBuf& src, size_t count, siz
 void clear_results(mbgfe* h)
 {
 	h->processed = false; h->exported_parts = false; h->exported_table = false; h->exported_codes = false; h->have_table = false;
+	h->nodes_ranked = false; h->edges_global = false; h->id_base = 0; h->x_packed_ids = nullptr;
 	h->parts.clear(); h->h_codes.clear(); h->h_poses.clear(); h->h_positions.clear(); h->h_hashes.clear();
 	h->n_nodes_out = 0; h->n_edges_out = 0;
 	h->n_inst = 0;
@@ -435,7 +441,8 @@ void mbgfe_destroy(mbgfe* h)
 		&h->d_seg_len, &h->d_seg_c1, &h->d_seg_c2, &h->d_seg_nsel, &h->d_sel_begin, &h->d_sym, &h->d_codes, &h->d_rrc, &h->d_selmask, &h->d_pos1, &h->d_pos2,
 		&h->d_inst_pos, &h->d_inst_seg, &h->d_inst_flag, &h->d_inst_hash, &h->d_inst_slot, &h->d_pal_list, &h->d_nodes, &h->d_edges, &h->d_node_out,
 		&h->d_edge_out, &h->d_records, &h->d_recv, &h->d_bucket_count, &h->d_bucket_begin, &h->d_scan_tot, &h->d_scan_off, &h->d_node_hash_sorted, &h->d_node_cov,
-		&h->d_node_tip, &h->d_edges_sorted }) release(*b);
+		&h->d_node_tip, &h->d_edges_sorted, &h->d_inst_packpos, &h->d_ids_out, &h->d_id_begin, &h->d_edge_records, &h->d_xbuf[0], &h->d_xbuf[1], &h->d_xbuf[2],
+		&h->d_xbuf[3] }) release(*b);
 	for (HostBuf* b : { &h->p_node_hashes, &h->p_node_cov, &h->p_node_tip, &h->p_edges }) release_host(*b);
 	for (auto& e : h->ev) if (e) cudaEventDestroy(e);
 	for (auto& e : h->piece_events) cudaEventDestroy(e);
@@ -947,14 +954,14 @@ int device_scan(mbgfe* h, const uint32_t* in, uint64_t* out, uint32_t n)
 // HashList::sortByHash (MBG/HashList.cpp:245-353): ids = ranks of the canonical hashes; edges renumbered with those
 // ids (already canonical: the device compared the hashes themselves), listed per node forward side first.
 // Everything is ordered on the device (kernels.cuh "export"); the host only receives the finished arrays by DMA.
-int export_table(mbgfe* h)
+// node ids: device-side bucket + rank sort of the table; leaves the sorted node arrays in HBM and every entry's rank
+// in its table slot.  Idempotent until the table changes.
+int rank_nodes(mbgfe* h)
 {
-	if (h->exported_table) return 0;
-	if (!h->have_table) return fail(h, MBGFE_E_STATE, "table requested but none was built (MBGFE_NO_TABLE without mbgfe_exchange_insert)");
-	tick(h, 10);
-	const uint64_t n_nodes = h->stats.distinct, n_edges = h->edge_slots ? h->stats.distinct_edges : 0;
+	if (h->nodes_ranked) return 0;
+	const uint64_t n_nodes = h->stats.distinct;
 	const unsigned grid = (unsigned)std::min<uint64_t>((h->node_slots + 255) / 256, (uint64_t)h->sm_count * 16);
-	// ---- nodes: buckets of ~32 entries on the top bits of the canonical hash
+	// buckets of ~32 entries on the top bits of the canonical hash
 	uint32_t bits = 0;
 	while (bits < 26 && (n_nodes >> bits) > 32) bits++;
 	const uint32_t n_buckets = 1u << bits;
@@ -965,9 +972,6 @@ int export_table(mbgfe* h)
 	if (int rc = ensure(h, h->d_node_hash_sorted, (n_nodes + 1) * 16)) return rc;
 	if (int rc = ensure(h, h->d_node_cov, (n_nodes + 1) * 4)) return rc;
 	if (int rc = ensure(h, h->d_node_tip, n_nodes + 64)) return rc;
-	if (int rc = ensure_host(h, h->p_node_hashes, (n_nodes + 1) * 16)) return rc;
-	if (int rc = ensure_host(h, h->p_node_cov, (n_nodes + 1) * 4)) return rc;
-	if (int rc = ensure_host(h, h->p_node_tip, n_nodes + 64)) return rc;
 	const unsigned rank_grid = (unsigned)std::min<uint64_t>(((uint64_t)n_buckets * 32 + 255) / 256, (uint64_t)h->sm_count * 32);
 	CU(h, cudaMemsetAsync(h->d_bucket_count.p, 0, (size_t)n_buckets * 4, h->stream));
 	MBGFE_LAUNCH(k_node_bucket_count, grid, 256, 0, h->stream, h->d_nodes.as<NodeSlot>(), h->node_slots, shift, h->d_bucket_count.as<uint32_t>());
@@ -977,6 +981,20 @@ int export_table(mbgfe* h)
 		h->d_bucket_count.as<uint32_t>(), h->d_node_out.as<NodeOut>());
 	MBGFE_LAUNCH(k_node_bucket_rank, rank_grid, 256, 0, h->stream, h->d_node_out.as<NodeOut>(), h->d_bucket_begin.as<uint64_t>(), n_buckets,
 		h->d_node_hash_sorted.as<uint64_t>(), h->d_node_cov.as<uint32_t>(), h->d_node_tip.as<uint8_t>(), h->d_nodes.as<NodeSlot>());
+	h->nodes_ranked = true;
+	return 0;
+}
+
+int export_table(mbgfe* h)
+{
+	if (h->exported_table) return 0;
+	if (!h->have_table) return fail(h, MBGFE_E_STATE, "table requested but none was built (MBGFE_NO_TABLE without mbgfe_exchange_insert)");
+	tick(h, 10);
+	const uint64_t n_nodes = h->stats.distinct, n_edges = h->edge_slots ? h->stats.distinct_edges : 0;
+	if (int rc = rank_nodes(h)) return rc;
+	if (int rc = ensure_host(h, h->p_node_hashes, (n_nodes + 1) * 16)) return rc;
+	if (int rc = ensure_host(h, h->p_node_cov, (n_nodes + 1) * 4)) return rc;
+	if (int rc = ensure_host(h, h->p_node_tip, n_nodes + 64)) return rc;
 	if (n_nodes)
 	{
 		CU(h, cudaMemcpyAsync(h->p_node_hashes.p, h->d_node_hash_sorted.p, n_nodes * 16, cudaMemcpyDeviceToHost, h->stream));
@@ -998,10 +1016,11 @@ int export_table(mbgfe* h)
 		const unsigned egrid = (unsigned)std::min<uint64_t>((h->edge_slots + 255) / 256, (uint64_t)h->sm_count * 16);
 		const unsigned erank_grid = (unsigned)std::min<uint64_t>(((uint64_t)n_eb * 32 + 255) / 256, (uint64_t)h->sm_count * 32);
 		CU(h, cudaMemsetAsync(h->d_bucket_count.p, 0, (size_t)n_eb * 4, h->stream));
-		MBGFE_LAUNCH(k_edge_bucket_count, egrid, 256, 0, h->stream, h->d_edges.as<EdgeSlot>(), h->edge_slots, h->d_nodes.as<NodeSlot>(), eshift, h->d_bucket_count.as<uint32_t>());
+		const NodeSlot* slot_names = h->edges_global ? nullptr : h->d_nodes.as<NodeSlot>();     // sharded table: edge keys already hold global ids
+		MBGFE_LAUNCH(k_edge_bucket_count, egrid, 256, 0, h->stream, h->d_edges.as<EdgeSlot>(), h->edge_slots, slot_names, eshift, h->id_base, h->d_bucket_count.as<uint32_t>());
 		if (int rc = device_scan(h, h->d_bucket_count.as<uint32_t>(), h->d_bucket_begin.as<uint64_t>(), n_eb)) return rc;
 		CU(h, cudaMemsetAsync(h->d_bucket_count.p, 0, (size_t)n_eb * 4, h->stream));
-		MBGFE_LAUNCH(k_edge_bucket_scatter, egrid, 256, 0, h->stream, h->d_edges.as<EdgeSlot>(), h->edge_slots, h->d_nodes.as<NodeSlot>(), eshift,
+		MBGFE_LAUNCH(k_edge_bucket_scatter, egrid, 256, 0, h->stream, h->d_edges.as<EdgeSlot>(), h->edge_slots, slot_names, eshift, h->id_base,
 			h->d_bucket_begin.as<uint64_t>(), h->d_bucket_count.as<uint32_t>(), h->d_edge_out.as<EdgeRec>());
 		MBGFE_LAUNCH(k_edge_bucket_rank, erank_grid, 256, 0, h->stream, h->d_edge_out.as<EdgeRec>(), h->d_bucket_begin.as<uint64_t>(), n_eb, h->d_edges_sorted.as<EdgeRec>());
 		CU(h, cudaMemcpyAsync(h->p_edges.p, h->d_edges_sorted.p, n_edges * sizeof(mbgfe_edge), cudaMemcpyDeviceToHost, h->stream));
@@ -1108,10 +1127,11 @@ int mbgfe_exchange_pack(mbgfe* h, void** device_records)
 	uint64_t total = 0;
 	for (uint32_t i = 0; i < world; i++) { cursors[i] = total; total += counts[i]; }
 	if (int rc = ensure(h, h->d_records, (total + 1) * 32)) return rc;
+	if (int rc = ensure(h, h->d_inst_packpos, (h->n_inst + 1) * 4)) return rc;
 	unsigned long long* ctr = h->d_counters.as<unsigned long long>();
 	CU(h, cudaMemcpyAsync(ctr + CTR_OWNER, cursors.data(), world * 8, cudaMemcpyHostToDevice, h->stream));
 	if (h->n_inst) MBGFE_LAUNCH(k_owner_pack, (unsigned)((h->n_inst + 255) / 256), 256, 0, h->stream, h->d_inst_hash.as<uint64_t>(), h->d_inst_flag.as<uint8_t>(), h->n_inst, world,
-		ctr + CTR_OWNER, h->d_records.as<uint64_t>());
+		ctr + CTR_OWNER, h->d_records.as<uint64_t>(), h->d_inst_packpos.as<uint32_t>());
 	CU(h, cudaStreamSynchronize(h->stream));
 	CU(h, cudaGetLastError());
 	*device_records = h->d_records.p;
@@ -1146,8 +1166,111 @@ int mbgfe_exchange_insert(mbgfe* h, const void* device_records, uint64_t n_recor
 	CU(h, cudaGetLastError());
 	h->stats.distinct = d; h->stats.distinct_edges = 0; h->stats.table_slots = slots;
 	h->stats.ms_nodes = elapsed(h, 12, 13);
-	h->exported_table = false;
+	h->exported_table = false; h->nodes_ranked = false; h->edges_global = false;
 	h->have_table = true;
+	return 0;
+}
+
+int mbgfe_exchange_scratch(mbgfe* h, uint32_t which, uint64_t bytes, void** device_ptr)
+{
+	if (!h || !device_ptr || which >= 4) return MBGFE_E_PARAM;
+	if (int rc = ensure(h, h->d_xbuf[which], bytes + 64)) return rc;
+	*device_ptr = h->d_xbuf[which].p;
+	return 0;
+}
+
+int mbgfe_exchange_node_ids(mbgfe* h, uint64_t id_base, const void* device_records, uint64_t n_records, void** device_ids)
+{
+	if (!h || !device_ids) return MBGFE_E_PARAM;
+	if (!h->have_table) return fail(h, MBGFE_E_STATE, "node ids requested before mbgfe_exchange_insert");
+	if (id_base + h->stats.distinct >= (1ull << 31)) return fail(h, MBGFE_E_LIMIT, "more than 2^31-1 nodes in the sharded table");
+	h->id_base = (uint32_t)id_base;
+	if (int rc = rank_nodes(h)) return rc;
+	if (int rc = ensure(h, h->d_ids_out, (n_records + 1) * 4)) return rc;
+	if (n_records) MBGFE_LAUNCH(k_record_ids, (unsigned)((n_records + 255) / 256), 256, 0, h->stream, (const uint64_t*)device_records, n_records, h->d_nodes.as<NodeSlot>(),
+		h->node_slots - 1, h->id_base, h->d_ids_out.as<uint32_t>());
+	CU(h, cudaStreamSynchronize(h->stream));
+	CU(h, cudaGetLastError());
+	*device_ids = h->d_ids_out.p;
+	return 0;
+}
+
+static int edge_exchange_launch(mbgfe* h, bool pack)
+{
+	unsigned long long* ctr = h->d_counters.as<unsigned long long>();
+	if (!h->n_inst) return 0;
+	const unsigned grid = (unsigned)((h->n_inst + 255) / 256);
+	if (!pack)
+		MBGFE_LAUNCH(k_edge_owner_count, grid, 256, 0, h->stream, h->d_inst_hash.as<uint64_t>(), h->d_inst_pos.as<uint32_t>(), h->d_inst_flag.as<uint8_t>(),
+			h->d_inst_packpos.as<uint32_t>(), (const uint32_t*)h->x_packed_ids, h->n_inst, h->x_inst_base, h->prm.k, h->d_id_begin.as<uint64_t>(), h->prm.world, ctr + CTR_OWNER);
+	else
+		MBGFE_LAUNCH(k_edge_owner_pack, grid, 256, 0, h->stream, h->d_inst_hash.as<uint64_t>(), h->d_inst_pos.as<uint32_t>(), h->d_inst_flag.as<uint8_t>(),
+			h->d_inst_packpos.as<uint32_t>(), (const uint32_t*)h->x_packed_ids, h->n_inst, h->x_inst_base, h->prm.k, h->d_id_begin.as<uint64_t>(), h->prm.world, ctr + CTR_OWNER,
+			h->d_edge_records.as<unsigned long long>());
+	return 0;
+}
+
+int mbgfe_exchange_edge_counts(mbgfe* h, const void* device_ids, const uint64_t* id_begin, uint64_t inst_base, uint64_t* send_counts)
+{
+	if (!h || !id_begin || !send_counts) return MBGFE_E_PARAM;
+	if (!h->processed || !h->d_inst_packpos.p) return fail(h, MBGFE_E_STATE, "edge exchange before mbgfe_exchange_pack");
+	if (h->n_inst && !device_ids) return fail(h, MBGFE_E_PARAM, "null id array");
+	const uint32_t world = h->prm.world;
+	h->x_packed_ids = device_ids; h->x_inst_base = inst_base;
+	if (int rc = ensure(h, h->d_id_begin, (world + 1) * 8)) return rc;
+	unsigned long long* ctr = h->d_counters.as<unsigned long long>();
+	CU(h, cudaMemcpyAsync(h->d_id_begin.p, id_begin, (world + 1) * 8, cudaMemcpyHostToDevice, h->stream));
+	CU(h, cudaMemsetAsync(ctr + CTR_OWNER, 0, world * 8, h->stream));
+	if (int rc = edge_exchange_launch(h, false)) return rc;
+	std::vector<unsigned long long> c(world);
+	CU(h, cudaMemcpyAsync(c.data(), ctr + CTR_OWNER, world * 8, cudaMemcpyDeviceToHost, h->stream));
+	CU(h, cudaStreamSynchronize(h->stream));
+	CU(h, cudaGetLastError());
+	for (uint32_t i = 0; i < world; i++) send_counts[i] = c[i];
+	return 0;
+}
+
+int mbgfe_exchange_edge_pack(mbgfe* h, const uint64_t* send_counts, void** device_records)
+{
+	if (!h || !send_counts || !device_records) return MBGFE_E_PARAM;
+	if (!h->d_id_begin.p) return fail(h, MBGFE_E_STATE, "mbgfe_exchange_edge_pack before mbgfe_exchange_edge_counts");
+	const uint32_t world = h->prm.world;
+	std::vector<unsigned long long> cursors(world);
+	uint64_t total = 0;
+	for (uint32_t i = 0; i < world; i++) { cursors[i] = total; total += send_counts[i]; }
+	if (int rc = ensure(h, h->d_edge_records, (total + 1) * 16)) return rc;
+	unsigned long long* ctr = h->d_counters.as<unsigned long long>();
+	CU(h, cudaMemcpyAsync(ctr + CTR_OWNER, cursors.data(), world * 8, cudaMemcpyHostToDevice, h->stream));
+	if (int rc = edge_exchange_launch(h, true)) return rc;
+	CU(h, cudaStreamSynchronize(h->stream));
+	CU(h, cudaGetLastError());
+	*device_records = h->d_edge_records.p;
+	return 0;
+}
+
+int mbgfe_exchange_insert_edges(mbgfe* h, const void* device_records, uint64_t n_records)
+{
+	if (!h) return MBGFE_E_PARAM;
+	if (!h->have_table) return fail(h, MBGFE_E_STATE, "edges before nodes: call mbgfe_exchange_insert first");
+	unsigned long long* ctr = h->d_counters.as<unsigned long long>();
+	const uint64_t slots = next_pow2(std::max<uint64_t>(2 * n_records, 1024));
+	if (slots >= (1ull << 31)) return fail(h, MBGFE_E_LIMIT, "edge table would need %llu slots (limit 2^31 per GPU)", (unsigned long long)slots);
+	if (int rc = ensure(h, h->d_edges, slots * sizeof(EdgeSlot))) return rc;
+	h->edge_slots = slots;
+	CU(h, cudaMemsetAsync(ctr + CTR_EDGES, 0, 8, h->stream));
+	tick(h, 12);
+	const unsigned clear_grid = (unsigned)std::min<uint64_t>((slots + 255) / 256, (uint64_t)h->sm_count * 8);
+	MBGFE_LAUNCH(k_edge_clear, clear_grid, 256, 0, h->stream, h->d_edges.as<EdgeSlot>(), slots);
+	if (n_records) MBGFE_LAUNCH(k_insert_edge_records, (unsigned)((n_records + 255) / 256), 256, 0, h->stream, (const unsigned long long*)device_records, n_records,
+		h->d_edges.as<EdgeSlot>(), slots - 1, ctr + CTR_EDGES);
+	tick(h, 13);
+	uint64_t d = 0;
+	if (int rc = read_counter(h, CTR_EDGES, &d)) return rc;
+	CU(h, cudaGetLastError());
+	h->stats.distinct_edges = d;
+	h->stats.ms_edges = elapsed(h, 12, 13);
+	h->edges_global = true;
+	h->exported_table = false;
 	return 0;
 }
 

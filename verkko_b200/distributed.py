@@ -1,6 +1,7 @@
 """Multi-GPU sharding of the k-mer table: reads are sharded across ranks, every selected k-mer is sent
-to the rank that owns its canonical hash range with one all-to-all-v (NCCL over NVLink on GPUs), and each rank counts
-its partition.  torch.distributed is plumbing only; the records live in the library's device buffers.
+to the rank that owns its canonical hash range with one all-to-all-v (NCCL over NVLink on GPUs), each rank counts its
+partition, answers with global node ids, and the edge observations follow to the owner of their `from` node.
+torch.distributed is plumbing only; records are produced and consumed by the library's kernels in its device buffers.
 
 The same code runs on the GPU-less emulator build with the gloo backend (tests), where "device" pointers are host
 pointers.
@@ -11,22 +12,26 @@ import numpy as np
 import torch
 import torch.distributed as dist
 
-RECORD_WORDS = 4  # 32-byte records: canonical hash lo, hi, flags, reserved
+RECORD_WORDS = 4       # node records: 32 bytes = canonical hash lo, hi, flags, reserved (int64 words)
+EDGE_RECORD_WORDS = 2  # edge records: 16 bytes = canonical (from, to) key, (instance << 24) | overlap
+
+_TYPESTR = {torch.int64: ("<i8", np.int64, C.c_int64), torch.int32: ("<i4", np.int32, C.c_int32)}
 
 
 class _DevicePointer:
-    def __init__(self, ptr, n_words):
-        self.__cuda_array_interface__ = {"shape": (n_words,), "typestr": "<i8", "data": (ptr, False), "version": 3}
+    def __init__(self, ptr, n, typestr):
+        self.__cuda_array_interface__ = {"shape": (n,), "typestr": typestr, "data": (ptr, False), "version": 3}
 
 
-def wrap_pointer(ptr, n_words, on_gpu):
-    """int64 tensor over n_words 8-byte words at ptr (zero-copy)"""
-    if n_words == 0:
-        return torch.empty(0, dtype=torch.int64, device="cuda" if on_gpu else "cpu")
+def wrap_pointer(ptr, n, on_gpu, dtype=torch.int64):
+    """tensor over n elements at ptr (zero-copy)"""
+    typestr, npdt, cdt = _TYPESTR[dtype]
+    if n == 0:
+        return torch.empty(0, dtype=dtype, device="cuda" if on_gpu else "cpu")
     if on_gpu:
-        return torch.as_tensor(_DevicePointer(ptr, n_words), device="cuda")
-    buf = (C.c_int64 * n_words).from_address(ptr)
-    return torch.from_numpy(np.frombuffer(buf, dtype=np.int64))
+        return torch.as_tensor(_DevicePointer(ptr, n, typestr), device="cuda")
+    buf = (cdt * n).from_address(ptr)
+    return torch.from_numpy(np.frombuffer(buf, dtype=npdt))
 
 
 def owner_of(hash_hi, world):
@@ -35,39 +40,89 @@ def owner_of(hash_hi, world):
 
 
 class DistributedCounter:
-    def __init__(self, fe, world, rank, on_gpu=True):
-        self.fe, self.world, self.rank, self.on_gpu = fe, world, rank, on_gpu
+    """Drives the exchange steps of include/mbgfe.h for one rank."""
+
+    def __init__(self, fe, world, rank, on_gpu=True, edges=True):
+        self.fe, self.world, self.rank, self.on_gpu, self.edges = fe, world, rank, on_gpu, edges
         self.last_exchange_ms = 0.0
-        self.launches = 4  # owner count (x2), owner pack, table clear + insert per step
+        # owner count (x2) + pack, table clear + insert;  with edges: 7 export-sort launches for the ranks, id lookup,
+        # edge owner count + pack, edge clear + insert
+        self.launches = 5 + (12 if edges else 0)
         self.n_recv = 0
+        self.sent_bytes = 0
+        self.id_begin = None
+
+    def _dev(self):
+        return "cuda" if self.on_gpu else "cpu"
+
+    def _counts_exchange(self, send_counts):
+        sc = torch.from_numpy(send_counts.astype(np.int64)).to(self._dev())
+        rc = torch.empty_like(sc)
+        dist.all_to_all_single(rc, sc)
+        return rc.cpu().numpy()
+
+    def _timed(self, fn):
+        if not self.on_gpu:
+            fn()
+            return
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        fn()
+        e1.record()
+        torch.cuda.synchronize()
+        self.last_exchange_ms += e0.elapsed_time(e1)
 
     def exchange_and_count(self):
         fe, world = self.fe, self.world
-        dev = "cuda" if self.on_gpu else "cpu"
+        self.last_exchange_ms = 0.0
+        # ---- nodes: k-mer records to their owners
         send_counts = fe.exchange_counts().astype(np.int64)
-        sc = torch.from_numpy(send_counts).to(dev)
-        rc = torch.empty_like(sc)
-        dist.all_to_all_single(rc, sc)
-        recv_counts = rc.cpu().numpy()
+        recv_counts = self._counts_exchange(send_counts)
         n_send, n_recv = int(send_counts.sum()), int(recv_counts.sum())
         send_ptr = fe.exchange_pack()
         recv_ptr = fe.exchange_reserve(n_recv)
         send_t = wrap_pointer(send_ptr, n_send * RECORD_WORDS, self.on_gpu)
         recv_t = wrap_pointer(recv_ptr, n_recv * RECORD_WORDS, self.on_gpu)
-        if self.on_gpu:
-            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-            e0.record()
-        dist.all_to_all_single(recv_t, send_t, output_split_sizes=(recv_counts * RECORD_WORDS).tolist(),
-                               input_split_sizes=(send_counts * RECORD_WORDS).tolist())
-        if self.on_gpu:
-            e1.record()
-            torch.cuda.synchronize()
-            self.last_exchange_ms = e0.elapsed_time(e1)
+        self._timed(lambda: dist.all_to_all_single(recv_t, send_t, output_split_sizes=(recv_counts * RECORD_WORDS).tolist(),
+                                                   input_split_sizes=(send_counts * RECORD_WORDS).tolist()))
         fe.exchange_insert(recv_ptr, n_recv)
         self.n_recv = n_recv
         self.sent_bytes = n_send * 32
+        if not self.edges:
+            return
+        # ---- ids: partition sizes -> id ranges; owners answer every record with its global node id
+        n_local = fe.stats()["distinct"]
+        mine = torch.tensor([n_local, fe.count_selected()], dtype=torch.int64, device=self._dev())
+        both = [torch.zeros(2, dtype=torch.int64, device=self._dev()) for _ in range(world)]
+        dist.all_gather(both, mine)
+        sizes = np.array([int(b[0]) for b in both], dtype=np.uint64)
+        n_inst = np.array([int(b[1]) for b in both], dtype=np.uint64)
+        id_begin = np.zeros(world + 1, dtype=np.uint64)
+        id_begin[1:] = np.cumsum(sizes)
+        self.id_begin = id_begin
+        inst_base = int(n_inst[:self.rank].sum())
+        ids_ptr = fe.exchange_node_ids(int(id_begin[self.rank]), recv_ptr, n_recv)
+        back_ptr = fe.exchange_scratch(0, n_send * 4)
+        ids_t = wrap_pointer(ids_ptr, n_recv, self.on_gpu, torch.int32)
+        back_t = wrap_pointer(back_ptr, n_send, self.on_gpu, torch.int32)
+        self._timed(lambda: dist.all_to_all_single(back_t, ids_t, output_split_sizes=send_counts.tolist(), input_split_sizes=recv_counts.tolist()))
+        # ---- edges: observations to the owner of their `from` node
+        e_send = fe.exchange_edge_counts(back_ptr, id_begin, inst_base).astype(np.int64)
+        e_recv = self._counts_exchange(e_send)
+        ne_send, ne_recv = int(e_send.sum()), int(e_recv.sum())
+        es_ptr = fe.exchange_edge_pack(e_send)
+        er_ptr = fe.exchange_scratch(1, ne_recv * 16)
+        es_t = wrap_pointer(es_ptr, ne_send * EDGE_RECORD_WORDS, self.on_gpu)
+        er_t = wrap_pointer(er_ptr, ne_recv * EDGE_RECORD_WORDS, self.on_gpu)
+        self._timed(lambda: dist.all_to_all_single(er_t, es_t, output_split_sizes=(e_recv * EDGE_RECORD_WORDS).tolist(),
+                                                   input_split_sizes=(e_send * EDGE_RECORD_WORDS).tolist()))
+        fe.exchange_insert_edges(er_ptr, ne_recv)
+        self.sent_bytes += n_recv * 4 + ne_send * 16
 
     def download_counts(self):
         cov = self.fe.node_coverage(copy=False)
         self.fe.node_hashes(copy=False)
-        return int(cov.sum(dtype=np.uint64))
+        total = int(cov.sum(dtype=np.uint64))
+        if self.edges:
+            total += len(self.fe.edges(copy=False))
+        return total

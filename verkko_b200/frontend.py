@@ -81,6 +81,11 @@ def load_library(path=None):
     L.mbgfe_exchange_pack.argtypes = [C.c_void_p, C.POINTER(C.c_void_p)]
     L.mbgfe_exchange_reserve.argtypes = [C.c_void_p, C.c_uint64, C.POINTER(C.c_void_p)]
     L.mbgfe_exchange_insert.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64]
+    L.mbgfe_exchange_scratch.argtypes = [C.c_void_p, C.c_uint32, C.c_uint64, C.POINTER(C.c_void_p)]
+    L.mbgfe_exchange_node_ids.argtypes = [C.c_void_p, C.c_uint64, C.c_void_p, C.c_uint64, C.POINTER(C.c_void_p)]
+    L.mbgfe_exchange_edge_counts.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p]
+    L.mbgfe_exchange_edge_pack.argtypes = [C.c_void_p, C.c_void_p, C.POINTER(C.c_void_p)]
+    L.mbgfe_exchange_insert_edges.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64]
     L.mbgfe_kat_tables.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
     L.mbgfe_kat_kmer_hash.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p]
     if path == library_path():
@@ -193,6 +198,9 @@ class MbgFrontEnd:
             self._check(-6)
         return _array(ptr, n * per, dtype, copy)
 
+    def count_selected(self):
+        return self.count(POSITIONS)
+
     def parts(self):
         return self._data(PARTS, PART_DTYPE)
 
@@ -254,6 +262,31 @@ class MbgFrontEnd:
 
     def exchange_insert(self, device_ptr, n_records):
         self._check(self.lib.mbgfe_exchange_insert(self.handle, device_ptr, n_records))
+
+    def exchange_scratch(self, which, nbytes):
+        p = C.c_void_p()
+        self._check(self.lib.mbgfe_exchange_scratch(self.handle, which, nbytes, C.byref(p)))
+        return p.value or 0
+
+    def exchange_node_ids(self, id_base, device_ptr, n_records):
+        p = C.c_void_p()
+        self._check(self.lib.mbgfe_exchange_node_ids(self.handle, id_base, device_ptr, n_records, C.byref(p)))
+        return p.value or 0
+
+    def exchange_edge_counts(self, device_ids, id_begin, inst_base):
+        id_begin = np.ascontiguousarray(id_begin, dtype=np.uint64)
+        out = np.zeros(self.params.world, dtype=np.uint64)
+        self._check(self.lib.mbgfe_exchange_edge_counts(self.handle, device_ids, id_begin.ctypes.data, inst_base, out.ctypes.data))
+        return out
+
+    def exchange_edge_pack(self, send_counts):
+        send_counts = np.ascontiguousarray(send_counts, dtype=np.uint64)
+        p = C.c_void_p()
+        self._check(self.lib.mbgfe_exchange_edge_pack(self.handle, send_counts.ctypes.data, C.byref(p)))
+        return p.value or 0
+
+    def exchange_insert_edges(self, device_ptr, n_records):
+        self._check(self.lib.mbgfe_exchange_insert_edges(self.handle, device_ptr, n_records))
 
     # ---- known-answer access
     def kat_tables(self):
