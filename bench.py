@@ -261,6 +261,8 @@ def main():
         raise SystemExit("bench.py needs a GPU: libmbgfe has no CPU path")
     torch.cuda.set_device(local_rank)
     if world > 1:
+        if os.environ.get("NCCL_DEBUG", "VERSION").upper() == "VERSION":
+            os.environ["NCCL_DEBUG"] = "WARN"       # keep NCCL's version banner off stdout: rank 0 prints ONE JSON line
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
     from verkko_b200 import MbgFrontEnd
     from verkko_b200.distributed import DistributedCounter
@@ -300,6 +302,8 @@ def main():
             stage_ms[kname] = stage_ms.get(kname, 0.0) + st[kname]
         if counter:
             stage_ms["ms_exchange"] = stage_ms.get("ms_exchange", 0.0) + counter.last_exchange_ms
+            for name, v in counter.wall_ms.items():
+                stage_ms["wall_" + name] = stage_ms.get("wall_" + name, 0.0) + v
     device_ms = fe.timer_stop()
     barrier()
     wall_ms = (time.time() - t0) * 1e3

@@ -56,7 +56,7 @@ typedef struct {
 	int32_t  device;          /* CUDA device ordinal */
 	uint32_t rank;            /* this process's shard of the k-mer space, 0 <= rank < world (single GPU: 0 of 1) */
 	uint32_t world;
-	uint32_t reserved;
+	uint32_t piece_bytes;     /* mbgfe_run: size of one pipelined H2D piece (0 = 48 MiB); small values exist for tests */
 	uint64_t table_slots;     /* initial node-table capacity in slots (0 = sized from the input); it grows on demand */
 } mbgfe_params;
 

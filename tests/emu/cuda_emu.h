@@ -35,6 +35,8 @@
 
 struct uint3 { unsigned x, y, z; };
 struct uint4 { unsigned x, y, z, w; };
+struct alignas(16) ulonglong2 { unsigned long long x, y; };
+struct alignas(32) ulonglong4 { unsigned long long x, y, z, w; };
 inline uint4 make_uint4(unsigned x, unsigned y, unsigned z, unsigned w) { uint4 v = { x, y, z, w }; return v; }
 struct dim3 { unsigned x, y, z; dim3(unsigned a = 1, unsigned b = 1, unsigned c = 1) : x(a), y(b), z(c) {} };
 
@@ -154,7 +156,7 @@ inline cudaError_t cudaStreamCreate(cudaStream_t* s) { *s = nullptr; return 0; }
 inline cudaError_t cudaStreamDestroy(cudaStream_t) { return 0; }
 inline cudaError_t cudaStreamSynchronize(cudaStream_t) { return 0; }
 inline cudaError_t cudaDeviceSynchronize() { return 0; }
-inline cudaError_t cudaMalloc(void** p, size_t n) { *p = calloc(1, n ? n : 1); return *p ? 0 : 2; }
+inline cudaError_t cudaMalloc(void** p, size_t n) { n = n ? n : 1; if (posix_memalign(p, 256, n)) { *p = nullptr; return 2; } memset(*p, 0, n); return 0; }
 inline cudaError_t cudaFree(void* p) { free(p); return 0; }
 inline cudaError_t cudaMallocHost(void** p, size_t n) { *p = malloc(n ? n : 1); return *p ? 0 : 2; }
 inline cudaError_t cudaFreeHost(void* p) { free(p); return 0; }

@@ -29,3 +29,21 @@ def test_emulated_palindrome_rule(oracle, emu_library):
     with pytest.raises(MbgfeError) as e:
         run_frontend("dinuc", 63, 33, [workloads.palindrome_read(1021)], library=emu_library)
     assert e.value.code == -4
+
+
+def test_emulated_pipelined_run_in_small_pieces(oracle, emu_library):
+    """mbgfe_run with tiny H2D pieces: many pieces, per-piece tail launches, sizes extrapolated from the first piece"""
+    reads = workloads.coverage_reads(n_reads=6)
+    got = run_frontend("collapse-msat", 501, 50, reads, library=emu_library, piece_bytes=9000)
+    compare_runs(got, oracle.run("collapse-msat", 501, 50, reads), what="small pieces")
+    assert got["stats"]["table_grows"] == 0
+
+
+def test_emulated_pipelined_run_estimate_overflow(oracle, emu_library):
+    """first piece = a read whose collapse leaves almost nothing (so the extrapolated sizes are far too small): the
+    kernels refuse to write past them and the exact tail reruns"""
+    poor = (b"A" * 320 + b"C" * 320) * 5          # exactly one piece
+    reads = [poor] + [workloads.read_a()[:2500] for _ in range(3)]
+    got = run_frontend("collapse", 31, 1, reads, library=emu_library, piece_bytes=3200)
+    compare_runs(got, oracle.run("collapse", 31, 1, reads), what="overflow fallback")
+    assert got["stats"]["table_grows"] >= 1

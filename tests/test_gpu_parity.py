@@ -141,3 +141,23 @@ def test_file_input(tmp_path, oracle):
     assert fe.read_name(0) == "read0 some description" and fe.read_name(3) == "q0"
     assert np.array_equal(fe.hashes(), want.hashes) and np.array_equal(fe.node_coverage(), want.node_cov)
     fe.close()
+
+
+@pytest.mark.gpu
+def test_pipelined_run_in_small_pieces(oracle):
+    """mbgfe_run with small H2D pieces (many pieces, tail launched per piece, sizes extrapolated from the first one)"""
+    reads = workloads.coverage_reads(n_reads=24)
+    got = run_frontend("collapse-msat", 1001, 100, reads, piece_bytes=20000)
+    compare_runs(got, oracle.run("collapse-msat", 1001, 100, reads), what="small pieces")
+    assert got["stats"]["table_grows"] == 0
+
+
+@pytest.mark.gpu
+def test_pipelined_run_estimate_overflow(oracle):
+    """extrapolated sizes far too small (first piece collapses to almost nothing): refused writes are counted and the
+    exact tail reruns; results are the reference's"""
+    poor = (b"A" * 320 + b"C" * 320) * 20         # exactly one piece
+    reads = [poor] + [workloads.repeat_rich(s, 9000) for s in (3, 4)] + [workloads.read_a()[:9000] for _ in range(6)]
+    got = run_frontend("collapse", 31, 1, reads, piece_bytes=12800)
+    compare_runs(got, oracle.run("collapse", 31, 1, reads), what="overflow fallback")
+    assert got["stats"]["table_grows"] >= 1

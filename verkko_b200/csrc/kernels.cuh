@@ -899,12 +899,15 @@ __global__ void __launch_bounds__(NT) k_select(SegTable seg, const uint16_t* __r
 
 // --------------------------------------------------------------------------- K3b: positions and k-mer hashes
 
-// exclusive prefix sum of a small uint32 array into uint64 (one CTA; segment tables are small)
+// exclusive prefix sum of a small uint32 array into uint64 (one CTA; segment tables are small).  carry_in: the sum
+// starts from *carry_in (it may alias out[0]: the pipelined run scans one piece of the segment table at a time and
+// each piece continues from the total the previous one left in its out[n]); nullptr = 0.
 template <int NT>
-__global__ void __launch_bounds__(NT) k_scan_u32(const uint32_t* __restrict__ in, uint64_t* __restrict__ out, uint32_t n)
+__global__ void __launch_bounds__(NT) k_scan_u32(const uint32_t* __restrict__ in, uint64_t* out, uint32_t n, const uint64_t* carry_in)
 {
 	__shared__ uint32_t warp_tmp[NT / 32];
-	uint64_t carry = 0;
+	uint64_t carry = carry_in ? *carry_in : 0;
+	__syncthreads();
 	for (uint32_t base = 0; base < n; base += NT)
 	{
 		uint32_t i = base + threadIdx.x;
@@ -949,19 +952,23 @@ __global__ void __launch_bounds__(SCAN_NT) k_scan_tiles(const uint32_t* __restri
 // K3b1: selection bitmask -> instance list.  One CTA per segment; inst_pos = part-local k-mer position,
 // inst_seg = segment, inst_flag bit0 = first selected k-mer of its part, bit1 = last (the tips, MBG/MBG.cpp:58).
 template <int NT>
-__global__ void __launch_bounds__(NT) k_list_selected(SegTable seg, const uint32_t* __restrict__ selmask32, const uint32_t* __restrict__ seg_c2,
+__global__ void __launch_bounds__(NT) k_list_selected(SegTable seg, uint32_t g_first, const uint32_t* __restrict__ selmask32, const uint32_t* __restrict__ seg_c2,
 	const uint32_t* __restrict__ seg_nsel, const uint64_t* __restrict__ sel_begin, uint32_t* __restrict__ inst_pos, uint32_t* __restrict__ inst_seg,
-	uint8_t* __restrict__ inst_flag, uint32_t k)
+	uint8_t* __restrict__ inst_flag, uint32_t k, uint64_t inst_cap, unsigned long long* __restrict__ overflow)
 {
+	// seg, seg_c2, seg_nsel and sel_begin are already offset to segment g_first (a piece of the batch); inst_seg holds
+	// batch-wide segment numbers.  Instances beyond inst_cap are not written (the caller sized the lists from an
+	// estimate; it sees the overflow count and reruns with the exact size).
 	__shared__ uint32_t warp_tmp[NT / 32];
 	const uint32_t g = blockIdx.x;
 	if (g >= seg.n) return;
 	const uint32_t nsel = seg_nsel[g];
 	if (nsel == 0) return;
+	const uint64_t begin = sel_begin[g];
+	if (begin + nsel > inst_cap) { if (threadIdx.x == 0) atomicAdd(overflow, 1ull); return; }
 	const uint32_t n_kmers = seg_c2[g] - k + 1;
 	const uint64_t out0 = seg.out_base[g];
 	const uint32_t* __restrict__ mw = selmask32 + (out0 >> 5);
-	const uint64_t begin = sel_begin[g];
 	uint32_t carry = 0;
 	for (uint32_t base = 0; base < n_kmers; base += NT * 32)
 	{
@@ -979,7 +986,7 @@ __global__ void __launch_bounds__(NT) k_list_selected(SegTable seg, const uint32
 		{
 			uint32_t b = __ffs(bits) - 1; bits &= bits - 1;
 			inst_pos[begin + idx] = p0 + b;
-			inst_seg[begin + idx] = g;
+			inst_seg[begin + idx] = g_first + g;
 			inst_flag[begin + idx] = (uint8_t)((idx == 0 ? 1 : 0) | (idx == nsel - 1 ? 2 : 0));
 			idx++;
 		}
@@ -1010,68 +1017,75 @@ struct Murmur
 // so that no global load is scattered and the serial part of the hash is 5 instructions per block.
 // Algorithmic bytes: 2 read per code (codes of a read stay cache resident across the ~k/50 k-mers that cover them,
 // both directions) + 16 written per instance.
+// The instance range [range[0], range[1]) is read from device memory (two entries of sel_begin), and CTAs stride over
+// it, so the pipelined run can launch the kernel for a piece whose instance count the host does not know yet.
 constexpr int HASH_WARPS = 4;
 __global__ void __launch_bounds__(HASH_WARPS * 32) k_kmer_hash(const uint64_t* __restrict__ seg_out_base, const uint16_t* __restrict__ codes,
-	const uint16_t* __restrict__ rrc, const uint32_t* __restrict__ inst_pos, const uint32_t* __restrict__ inst_seg, uint64_t n_inst,
-	uint64_t* __restrict__ inst_hash, uint32_t k)
+	const uint16_t* __restrict__ rrc, const uint32_t* __restrict__ inst_pos, const uint32_t* __restrict__ inst_seg, const uint64_t* __restrict__ range_begin,
+	const uint64_t* __restrict__ range_end, uint64_t inst_cap, uint64_t* __restrict__ inst_hash, uint32_t k)
 {
 	__shared__ uint64_t premixed[HASH_WARPS][32][33];
 	const uint32_t lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
-	const uint64_t t = ((uint64_t)blockIdx.x * HASH_WARPS + wid) * 32 + lane;
-	const bool valid = t < 2 * n_inst;
-	const uint16_t* my = codes;        // lanes past the end walk the start of the array and discard the result
-	if (valid)
-	{
-		const uint64_t i = t >> 1;
-		const uint32_t g = inst_seg[i], pos = inst_pos[i];
-		const uint64_t ob = seg_out_base[g];
-		my = (t & 1) ? rrc + (seg_out_base[g + 1] - k - pos) : codes + ob + pos;
-	}
-	const uint64_t my_addr = (uint64_t)my;
+	const uint64_t first = *range_begin, last = min(*range_end, inst_cap);
+	const uint64_t n_pairs = last > first ? 2 * (last - first) : 0;
 	const uint32_t half = (k + 1) / 2;
 	const uint32_t n_blocks = half / 4, rem = half & 3;
-	Murmur mm;
-	mm.init((uint64_t)half * 2);
-	for (uint32_t c0 = 0; c0 < n_blocks; c0 += 32)
+	for (uint64_t t0 = (uint64_t)blockIdx.x * (HASH_WARPS * 32); t0 < n_pairs; t0 += (uint64_t)gridDim.x * (HASH_WARPS * 32))
 	{
-		const uint32_t nb = min(32u, n_blocks - c0);
-		// four pairs per round: all twelve loads are issued before the first one is consumed
-		for (uint32_t j0 = 0; j0 < 32; j0 += 4)
+		const uint64_t t = t0 + wid * 32 + lane;
+		const bool valid = t < n_pairs;
+		const uint64_t i = first + (t >> 1);
+		const uint16_t* my = codes;        // lanes past the end walk the start of the array and discard the result
+		if (valid)
 		{
-			uint32_t w0[4], w1[4], w2[4], sh[4];
-#pragma unroll
-			for (int u = 0; u < 4; u++)
-			{
-				const uint64_t a = __shfl_sync(FULL, my_addr, j0 + u) + 8ull * (c0 + lane);
-				const uint32_t* __restrict__ p = (const uint32_t*)(a & ~3ull);
-				sh[u] = ((uint32_t)a & 2) * 8;          // 0 or 16: the block starts in the middle of a 32-bit word
-				w0[u] = 0; w1[u] = 0; w2[u] = 0;
-				if (lane < nb) { w0[u] = __ldg(p); w1[u] = __ldg(p + 1); w2[u] = __ldg(p + 2); }
-			}
-#pragma unroll
-			for (int u = 0; u < 4; u++)
-			{
-#ifdef MBGFE_EMU_BUILD
-				const uint32_t lo = sh[u] ? (w0[u] >> 16) | (w1[u] << 16) : w0[u], hi = sh[u] ? (w1[u] >> 16) | (w2[u] << 16) : w1[u];
-#else
-				const uint32_t lo = __funnelshift_r(w0[u], w1[u], sh[u]), hi = __funnelshift_r(w1[u], w2[u], sh[u]);
-#endif
-				uint64_t wd = u64_of(lo, hi);
-				wd *= Murmur::MUL; wd ^= wd >> 47; wd *= Murmur::MUL;
-				if (lane < nb) premixed[wid][j0 + u][lane] = wd;
-			}
+			const uint32_t g = inst_seg[i], pos = inst_pos[i];
+			const uint64_t ob = seg_out_base[g];
+			my = (t & 1) ? rrc + (seg_out_base[g + 1] - k - pos) : codes + ob + pos;
 		}
-		__syncwarp();
-		for (uint32_t b = 0; b < nb; b++) { mm.h ^= premixed[wid][lane][b]; mm.h *= Murmur::MUL; }
-		__syncwarp();
+		const uint64_t my_addr = (uint64_t)my;
+		Murmur mm;
+		mm.init((uint64_t)half * 2);
+		for (uint32_t c0 = 0; c0 < n_blocks; c0 += 32)
+		{
+			const uint32_t nb = min(32u, n_blocks - c0);
+			// four pairs per round: all twelve loads are issued before the first one is consumed
+			for (uint32_t j0 = 0; j0 < 32; j0 += 4)
+			{
+				uint32_t w0[4], w1[4], w2[4], sh[4];
+#pragma unroll
+				for (int u = 0; u < 4; u++)
+				{
+					const uint64_t a = __shfl_sync(FULL, my_addr, j0 + u) + 8ull * (c0 + lane);
+					const uint32_t* __restrict__ p = (const uint32_t*)(a & ~3ull);
+					sh[u] = ((uint32_t)a & 2) * 8;          // 0 or 16: the block starts in the middle of a 32-bit word
+					w0[u] = 0; w1[u] = 0; w2[u] = 0;
+					if (lane < nb) { w0[u] = __ldg(p); w1[u] = __ldg(p + 1); w2[u] = __ldg(p + 2); }
+				}
+#pragma unroll
+				for (int u = 0; u < 4; u++)
+				{
+#ifdef MBGFE_EMU_BUILD
+					const uint32_t lo = sh[u] ? (w0[u] >> 16) | (w1[u] << 16) : w0[u], hi = sh[u] ? (w1[u] >> 16) | (w2[u] << 16) : w1[u];
+#else
+					const uint32_t lo = __funnelshift_r(w0[u], w1[u], sh[u]), hi = __funnelshift_r(w1[u], w2[u], sh[u]);
+#endif
+					uint64_t wd = u64_of(lo, hi);
+					wd *= Murmur::MUL; wd ^= wd >> 47; wd *= Murmur::MUL;
+					if (lane < nb) premixed[wid][j0 + u][lane] = wd;
+				}
+			}
+			__syncwarp();
+			for (uint32_t b = 0; b < nb; b++) { mm.h ^= premixed[wid][lane][b]; mm.h *= Murmur::MUL; }
+			__syncwarp();
+		}
+		if (rem)
+		{
+			uint64_t wd = 0;
+			for (uint32_t j = 0; j < rem; j++) wd |= (uint64_t)my[4 * n_blocks + j] << (16 * j);
+			mm.tail(wd);
+		}
+		if (valid) inst_hash[2 * first + t] = mm.finish();
 	}
-	if (rem)
-	{
-		uint64_t wd = 0;
-		for (uint32_t j = 0; j < rem; j++) wd |= (uint64_t)my[4 * n_blocks + j] << (16 * j);
-		mm.tail(wd);
-	}
-	if (valid) inst_hash[t] = mm.finish();
 }
 
 // KAT helper: rrc for one stand-alone code array of n codes (cap == n)
@@ -1082,15 +1096,17 @@ __global__ void k_revcomp_codes(const uint16_t* __restrict__ codes, uint32_t n, 
 }
 
 // instances whose two halves hash alike: palindromes or (practically impossible) collisions
-__global__ void __launch_bounds__(256) k_find_palindromes(const uint64_t* __restrict__ inst_hash, uint64_t n_inst, unsigned long long* __restrict__ count,
-	uint64_t* __restrict__ list, uint64_t cap)
+__global__ void __launch_bounds__(256) k_find_palindromes(const uint64_t* __restrict__ inst_hash, const uint64_t* __restrict__ range_begin, const uint64_t* __restrict__ range_end,
+	uint64_t inst_cap, unsigned long long* __restrict__ count, uint64_t* __restrict__ list, uint64_t cap)
 {
-	const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
-	if (i >= n_inst) return;
-	if (inst_hash[2 * i] == inst_hash[2 * i + 1])
+	const uint64_t first = *range_begin, last = min(*range_end, inst_cap);
+	for (uint64_t i = first + (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < last; i += (uint64_t)gridDim.x * blockDim.x)
 	{
-		unsigned long long slot = atomicAdd(count, 1ull);
-		if (slot < cap) list[slot] = i;
+		if (inst_hash[2 * i] == inst_hash[2 * i + 1])
+		{
+			unsigned long long slot = atomicAdd(count, 1ull);
+			if (slot < cap) list[slot] = i;
+		}
 	}
 }
 
@@ -1208,11 +1224,15 @@ __device__ __forceinline__ void canonical_key(uint64_t lo, uint64_t hi, uint64_t
 // Lock-free insert-or-update.  Slots only ever go from empty to one key, so a loaded value with no all-ones half is a
 // complete key; a value with an all-ones half may be empty or half-visible and is settled by the CAS, whose return
 // value is authoritative.  Returns the slot; is_new reports whether this call created the entry.
+// Probe limit: with the tables at most half full a run of this many occupied slots does not happen; it does when the
+// pipelined run under-estimated the table, and then the insert gives up (reported, and the exact path reruns) instead of
+// crawling through a full table.
+constexpr uint32_t MAX_PROBES = 2048;
 __device__ __forceinline__ uint64_t node_insert(NodeSlot* __restrict__ table, uint64_t mask, uint64_t key_lo, uint64_t key_hi, uint32_t add, uint32_t flags, bool& is_new)
 {
 	uint64_t slot = slot_hash(key_lo, key_hi) & mask;
 	is_new = false;
-	while (true)
+	for (uint32_t probes = 0; probes < MAX_PROBES; probes++)
 	{
 		NodeSlot* sp = table + slot;
 		uint64_t cur_lo, cur_hi;
@@ -1231,6 +1251,7 @@ __device__ __forceinline__ uint64_t node_insert(NodeSlot* __restrict__ table, ui
 		}
 		slot = (slot + 1) & mask;
 	}
+	return ~0ull;     // MAX_PROBES occupied slots in a row: the table (sized from an estimate by the pipelined run) is as good as full
 }
 
 // one atomicAdd per warp for a per-thread 0/1 contribution; every thread of the warp must call it
@@ -1259,26 +1280,33 @@ __global__ void __launch_bounds__(256) k_table_clear(NodeSlot* __restrict__ tabl
 	}
 }
 
-// K4a: count k-mers.  One thread per instance: canonical key, probe, 128-bit CAS claim, atomic add / or
-// (HashList::addNode + setTipKmer, MBG/HashList.cpp:120-149,23-26).
+// K4a: count k-mers.  One thread per instance of [*range_begin, *range_end): canonical key, probe, 128-bit CAS claim,
+// atomic add / or (HashList::addNode + setTipKmer, MBG/HashList.cpp:120-149,23-26).
 // Algorithmic bytes: 16 read per instance + one 32-byte slot read and written (random access: sector-bound).
-__global__ void __launch_bounds__(256) k_insert_nodes(const uint64_t* __restrict__ inst_hash, const uint8_t* __restrict__ inst_flag, uint64_t n_inst,
-	NodeSlot* __restrict__ table, uint64_t mask, uint32_t* __restrict__ inst_slot, unsigned long long* __restrict__ distinct)
+__global__ void __launch_bounds__(256) k_insert_nodes(const uint64_t* __restrict__ inst_hash, const uint8_t* __restrict__ inst_flag, const uint64_t* __restrict__ range_begin,
+	const uint64_t* __restrict__ range_end, uint64_t inst_cap, NodeSlot* __restrict__ table, uint64_t mask, uint32_t* __restrict__ inst_slot,
+	unsigned long long* __restrict__ distinct, unsigned long long* __restrict__ overflow)
 {
-	const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
-	bool is_new = false;
-	if (i < n_inst)
+	const uint64_t first = *range_begin, last = min(*range_end, inst_cap);
+	for (uint64_t base = first + (uint64_t)blockIdx.x * blockDim.x; base < last; base += (uint64_t)gridDim.x * blockDim.x)
 	{
-		const uint64_t lo = inst_hash[2 * i], hi = inst_hash[2 * i + 1];
-		if (lo == hi) inst_slot[i] = 0xffffffffu; // palindrome (rare; the host resolves these before the table pass)
-		else
+		const uint64_t i = base + threadIdx.x;
+		bool is_new = false;
+		if (i < last)
 		{
-			uint64_t key_lo, key_hi; uint32_t fw;
-			canonical_key(lo, hi, key_lo, key_hi, fw);
-			inst_slot[i] = (uint32_t)node_insert(table, mask, key_lo, key_hi, 1, inst_flag[i] ? 1u : 0u, is_new);
+			const uint64_t lo = inst_hash[2 * i], hi = inst_hash[2 * i + 1];
+			if (lo == hi) inst_slot[i] = 0xffffffffu; // palindrome (rare; resolved before the table pass that counts)
+			else
+			{
+				uint64_t key_lo, key_hi; uint32_t fw;
+				canonical_key(lo, hi, key_lo, key_hi, fw);
+				const uint64_t slot = node_insert(table, mask, key_lo, key_hi, 1, inst_flag[i] ? 1u : 0u, is_new);
+				if (slot == ~0ull) atomicAdd(overflow, 1ull);
+				inst_slot[i] = (uint32_t)slot;
+			}
 		}
+		warp_count(distinct, is_new);
 	}
-	warp_count(distinct, is_new);
 }
 
 // records received from other ranks: {key_lo, key_hi, flags, reserved}
@@ -1359,19 +1387,20 @@ __device__ __forceinline__ unsigned long long canonical_edge_key(uint64_t a_lo, 
 	return ((unsigned long long)(((uint64_t)from << 1) | from_fw) << 32) | (((uint64_t)to << 1) | to_fw);
 }
 
-// insert-or-update of one edge observation: coverage += 1, overlap of the latest observation in input order
-__device__ __forceinline__ bool edge_insert(EdgeSlot* __restrict__ table, uint64_t mask, unsigned long long key, unsigned long long ordered)
+// insert-or-update of one edge observation: coverage += 1, overlap of the latest observation in input order.
+// Returns 1 when the edge is new, 0 when it was known, 2 when the table is full.
+__device__ __forceinline__ uint32_t edge_insert(EdgeSlot* __restrict__ table, uint64_t mask, unsigned long long key, unsigned long long ordered)
 {
 	uint64_t slot = slot_hash(key, key >> 17) & mask;
-	bool is_new = false;
-	while (true)
+	uint32_t is_new = 0;
+	for (uint32_t probes = 0; probes < MAX_PROBES; probes++)
 	{
 		EdgeSlot* sp = table + slot;
 		unsigned long long cur = *(volatile unsigned long long*)&sp->key;
 		if (cur == ~0ull)
 		{
 			const unsigned long long old = atomicCAS(&sp->key, ~0ull, key);
-			if (old == ~0ull) { is_new = true; cur = key; } else cur = old;
+			if (old == ~0ull) { is_new = 1; cur = key; } else cur = old;
 		}
 		if (cur == key)
 		{
@@ -1381,22 +1410,29 @@ __device__ __forceinline__ bool edge_insert(EdgeSlot* __restrict__ table, uint64
 		}
 		slot = (slot + 1) & mask;
 	}
+	return 2;
 }
 
-// K4b: adjacency.  One thread per instance that has a predecessor in its part: canonical edge, coverage += 1,
-// overlap = prev_pos + k - pos (MBG/MBG.cpp:59-67).
+// K4b: adjacency.  One thread per instance of the range that has a predecessor in its part: canonical edge,
+// coverage += 1, overlap = prev_pos + k - pos (MBG/MBG.cpp:59-67).
 __global__ void __launch_bounds__(256) k_insert_edges(const uint64_t* __restrict__ inst_hash, const uint32_t* __restrict__ inst_pos, const uint8_t* __restrict__ inst_flag,
-	const uint32_t* __restrict__ inst_slot, uint64_t n_inst, EdgeSlot* __restrict__ table, uint64_t mask, unsigned long long* __restrict__ distinct, uint32_t k)
+	const uint32_t* __restrict__ inst_slot, const uint64_t* __restrict__ range_begin, const uint64_t* __restrict__ range_end, uint64_t inst_cap,
+	EdgeSlot* __restrict__ table, uint64_t mask, unsigned long long* __restrict__ distinct, unsigned long long* __restrict__ overflow, uint32_t k)
 {
-	const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
-	bool is_new = false;
-	if (i < n_inst && i > 0 && !(inst_flag[i] & 1) && inst_slot[i] != 0xffffffffu && inst_slot[i - 1] != 0xffffffffu)
+	const uint64_t first = *range_begin, last = min(*range_end, inst_cap);
+	for (uint64_t base = first + (uint64_t)blockIdx.x * blockDim.x; base < last; base += (uint64_t)gridDim.x * blockDim.x)
 	{
-		const unsigned long long key = canonical_edge_key(inst_hash[2 * (i - 1)], inst_hash[2 * (i - 1) + 1], inst_hash[2 * i], inst_hash[2 * i + 1], inst_slot[i - 1], inst_slot[i]);
-		const uint32_t overlap = inst_pos[i - 1] + k - inst_pos[i];
-		is_new = edge_insert(table, mask, key, ((unsigned long long)i << 24) | overlap);
+		const uint64_t i = base + threadIdx.x;
+		uint32_t res = 0;
+		if (i < last && i > 0 && !(inst_flag[i] & 1) && inst_slot[i] != 0xffffffffu && inst_slot[i - 1] != 0xffffffffu)
+		{
+			const unsigned long long key = canonical_edge_key(inst_hash[2 * (i - 1)], inst_hash[2 * (i - 1) + 1], inst_hash[2 * i], inst_hash[2 * i + 1], inst_slot[i - 1], inst_slot[i]);
+			const uint32_t overlap = inst_pos[i - 1] + k - inst_pos[i];
+			res = edge_insert(table, mask, key, ((unsigned long long)i << 24) | overlap);
+			if (res == 2) atomicAdd(overflow, 1ull);
+		}
+		warp_count(distinct, res == 1);
 	}
-	warp_count(distinct, is_new);
 }
 
 // ------------------------------------------------------------------------------------------------ export
@@ -1535,28 +1571,53 @@ __device__ __forceinline__ uint32_t owner_of(uint64_t key_hi, uint32_t world)
 	return (uint32_t)__umul64hi(key_hi, (uint64_t)world); // range partition of the canonical hash space
 }
 
+// Per-owner allocation without hammering `world` global counters from millions of threads: a shared-memory histogram
+// per CTA, one global atomicAdd per owner and CTA, then base + local rank.  Every thread of the CTA must call it
+// (owner == NO_OWNER: nothing to place).  Used with a counter array (counting pass: result ignored) and with a
+// cursor array (packing pass: result = output index).
+constexpr uint32_t MAX_WORLD = 64, NO_OWNER = 0xffffffffu;
+__device__ __forceinline__ unsigned long long block_owner_alloc(uint32_t owner, unsigned long long* __restrict__ cursors, uint32_t world)
+{
+	__shared__ uint32_t hist[MAX_WORLD];
+	__shared__ unsigned long long base[MAX_WORLD];
+	if (threadIdx.x < MAX_WORLD) hist[threadIdx.x] = 0;
+	__syncthreads();
+	uint32_t local = 0;
+	if (owner != NO_OWNER) local = atomicAdd(&hist[owner], 1u);
+	__syncthreads();
+	if (threadIdx.x < world && hist[threadIdx.x]) base[threadIdx.x] = atomicAdd(cursors + threadIdx.x, (unsigned long long)hist[threadIdx.x]);
+	__syncthreads();
+	return owner != NO_OWNER ? base[owner] + local : 0ull;
+}
+
 __global__ void __launch_bounds__(256) k_owner_count(const uint64_t* __restrict__ inst_hash, uint64_t n_inst, uint32_t world, unsigned long long* __restrict__ counts)
 {
 	const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
-	if (i >= n_inst) return;
-	uint64_t lo = inst_hash[2 * i], hi = inst_hash[2 * i + 1];
-	if (lo == hi) return;
-	uint64_t key_lo, key_hi; uint32_t fw;
-	canonical_key(lo, hi, key_lo, key_hi, fw);
-	atomicAdd(counts + owner_of(key_hi, world), 1ull);
+	uint32_t owner = NO_OWNER;
+	if (i < n_inst)
+	{
+		const uint64_t lo = inst_hash[2 * i], hi = inst_hash[2 * i + 1];
+		if (lo != hi) { uint64_t key_lo, key_hi; uint32_t fw; canonical_key(lo, hi, key_lo, key_hi, fw); owner = owner_of(key_hi, world); }
+	}
+	block_owner_alloc(owner, counts, world);
 }
 
 __global__ void __launch_bounds__(256) k_owner_pack(const uint64_t* __restrict__ inst_hash, const uint8_t* __restrict__ inst_flag, uint64_t n_inst, uint32_t world,
 	unsigned long long* __restrict__ cursors, uint64_t* __restrict__ records, uint32_t* __restrict__ inst_packpos)
 {
 	const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+	uint32_t owner = NO_OWNER;
+	uint64_t key_lo = 0, key_hi = 0;
+	if (i < n_inst)
+	{
+		const uint64_t lo = inst_hash[2 * i], hi = inst_hash[2 * i + 1];
+		if (lo != hi) { uint32_t fw; canonical_key(lo, hi, key_lo, key_hi, fw); owner = owner_of(key_hi, world); }
+	}
+	const unsigned long long o = block_owner_alloc(owner, cursors, world);
 	if (i >= n_inst) return;
-	uint64_t lo = inst_hash[2 * i], hi = inst_hash[2 * i + 1];
-	if (lo == hi) { inst_packpos[i] = 0xffffffffu; return; }
-	uint64_t key_lo, key_hi; uint32_t fw;
-	canonical_key(lo, hi, key_lo, key_hi, fw);
-	unsigned long long o = atomicAdd(cursors + owner_of(key_hi, world), 1ull);
-	records[4 * o] = key_lo; records[4 * o + 1] = key_hi; records[4 * o + 2] = inst_flag[i] ? 1 : 0; records[4 * o + 3] = 0;
+	if (owner == NO_OWNER) { inst_packpos[i] = 0xffffffffu; return; }
+	ulonglong4 r; r.x = key_lo; r.y = key_hi; r.z = inst_flag[i] ? 1 : 0; r.w = 0;
+	*(ulonglong4*)(records + 4 * o) = r;
 	inst_packpos[i] = (uint32_t)o;     // where the owner's answer (the global node id) will come back
 }
 
@@ -1605,8 +1666,8 @@ __global__ void __launch_bounds__(256) k_edge_owner_count(const uint64_t* __rest
 {
 	const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
 	unsigned long long key, ordered;
-	if (!edge_observation(i, n_inst, inst_hash, inst_pos, inst_flag, inst_packpos, packed_ids, inst_base, k, key, ordered)) return;
-	atomicAdd(counts + id_owner((uint32_t)(key >> 33), id_begin, world), 1ull);
+	const bool have = edge_observation(i, n_inst, inst_hash, inst_pos, inst_flag, inst_packpos, packed_ids, inst_base, k, key, ordered);
+	block_owner_alloc(have ? id_owner((uint32_t)(key >> 33), id_begin, world) : NO_OWNER, counts, world);
 }
 
 __global__ void __launch_bounds__(256) k_edge_owner_pack(const uint64_t* __restrict__ inst_hash, const uint32_t* __restrict__ inst_pos, const uint8_t* __restrict__ inst_flag,
@@ -1615,9 +1676,9 @@ __global__ void __launch_bounds__(256) k_edge_owner_pack(const uint64_t* __restr
 {
 	const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
 	unsigned long long key, ordered;
-	if (!edge_observation(i, n_inst, inst_hash, inst_pos, inst_flag, inst_packpos, packed_ids, inst_base, k, key, ordered)) return;
-	const unsigned long long o = atomicAdd(cursors + id_owner((uint32_t)(key >> 33), id_begin, world), 1ull);
-	records[2 * o] = key; records[2 * o + 1] = ordered;
+	const bool have = edge_observation(i, n_inst, inst_hash, inst_pos, inst_flag, inst_packpos, packed_ids, inst_base, k, key, ordered);
+	const unsigned long long o = block_owner_alloc(have ? id_owner((uint32_t)(key >> 33), id_begin, world) : NO_OWNER, cursors, world);
+	if (have) { ulonglong2 r; r.x = key; r.y = ordered; *(ulonglong2*)(records + 2 * o) = r; }
 }
 
 __global__ void __launch_bounds__(256) k_insert_edge_records(const unsigned long long* __restrict__ rec, uint64_t n_rec, EdgeSlot* __restrict__ table, uint64_t mask,
@@ -1625,7 +1686,7 @@ __global__ void __launch_bounds__(256) k_insert_edge_records(const unsigned long
 {
 	const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
 	bool is_new = false;
-	if (i < n_rec) is_new = edge_insert(table, mask, rec[2 * i], rec[2 * i + 1]);
+	if (i < n_rec) is_new = edge_insert(table, mask, rec[2 * i], rec[2 * i + 1]) == 1;
 	warp_count(distinct, is_new);
 }
 

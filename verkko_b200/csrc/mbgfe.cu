@@ -93,12 +93,14 @@ struct mbgfe
 	DevBuf d_inst_packpos, d_ids_out, d_id_begin, d_edge_records, d_xbuf[4];   // sharded table: id replies and edge records
 	const void* x_packed_ids = nullptr;                                      // ids of this rank's packed records, as received
 	uint64_t x_inst_base = 0;
+	std::vector<uint64_t> x_counts;                                          // per-owner record counts of the last mbgfe_exchange_counts
 	uint32_t id_base = 0;                                                    // nodes owned by lower ranks
 	bool nodes_ranked = false, edges_global = false;
 	DevBuf d_bucket_count, d_bucket_begin, d_scan_tot, d_scan_off;      // export: bucket tables and scan scratch
 	DevBuf d_node_hash_sorted, d_node_cov, d_node_tip, d_edges_sorted;    // export: final layout, device resident
 	uint64_t node_slots = 0, edge_slots = 0;
 	uint64_t n_inst = 0;
+	uint64_t inst_cap = 0;                            // capacity of the instance lists (entries)
 
 	// host results
 	std::vector<mbgfe_part> parts;
@@ -156,7 +158,8 @@ uint64_t next_pow2(uint64_t v) { uint64_t p = 1; while (p < v) p <<= 1; return p
 
 bool is_acgt(char c) { c &= (char)0xdf; return c == 'A' || c == 'C' || c == 'G' || c == 'T'; }
 
-enum { CTR_NONACGT = 0, CTR_PALINDROME = 1, CTR_DISTINCT = 2, CTR_EDGES = 3, CTR_CURSOR = 4, CTR_OWNER = 8 /* .. 8+world */ };
+enum { CTR_NONACGT = 0, CTR_PALINDROME = 1, CTR_DISTINCT = 2, CTR_EDGES = 3, CTR_CURSOR = 4 /* and 5 */, CTR_OVERFLOW = 6, CTR_OWNER = 8 /* .. 8+world */ };
+constexpr uint64_t PAL_CAP = 1 << 20;
 
 constexpr int NT_COLLAPSE = 128, NT_MSAT = 128, NT_SELECT = 256, NT_LIST = 128;
 
@@ -282,7 +285,7 @@ int download(mbgfe* h, std::vector<T>& dst, const DevBuf& src, size_t count, siz
 void clear_results(mbgfe* h)
 {
 	h->processed = false; h->exported_parts = false; h->exported_table = false; h->exported_codes = false; h->have_table = false;
-	h->nodes_ranked = false; h->edges_global = false; h->id_base = 0; h->x_packed_ids = nullptr;
+	h->nodes_ranked = false; h->edges_global = false; h->id_base = 0; h->x_packed_ids = nullptr; h->x_counts.clear();
 	h->parts.clear(); h->h_codes.clear(); h->h_poses.clear(); h->h_positions.clear(); h->h_hashes.clear();
 	h->n_nodes_out = 0; h->n_edges_out = 0;
 	h->n_inst = 0;
@@ -400,6 +403,7 @@ int mbgfe_create(const mbgfe_params* prm, mbgfe** out)
 	if (prm->w == 0) return fail(nullptr, MBGFE_E_PARAM, "w must be at least 1");
 	if (prm->w > prm->k - 30) return fail(nullptr, MBGFE_E_PARAM, "w must be at most k-30");
 	if (prm->error_masking > MBGFE_MASK_COLLAPSE_MSAT) return fail(nullptr, MBGFE_E_PARAM, "unknown error masking mode %u", prm->error_masking);
+	if (prm->world > MAX_WORLD) return fail(nullptr, MBGFE_E_PARAM, "world %u: at most %u ranks", prm->world, MAX_WORLD);
 	if (prm->world == 0 || prm->rank >= prm->world) return fail(nullptr, MBGFE_E_PARAM, "rank %u outside world %u", prm->rank, prm->world);
 	int n_dev = 0;
 	cudaError_t e = cudaGetDeviceCount(&n_dev);
@@ -626,15 +630,116 @@ uint32_t launch_front(mbgfe* h, uint32_t g0, uint32_t cnt, bool timed)
 	return 3;
 }
 
-// everything after selection: instance list, k-mer hashes, palindrome rule, node and edge tables
+// ---- everything after selection: instance list, k-mer hashes, palindrome rule, node and edge tables.
+// All of it is driven by instance ranges read from device memory (entries of sel_begin), so the same launches serve the
+// whole batch (mbgfe_process: exact sizes known) and one piece of it (mbgfe_run: sizes estimated, checked afterwards).
+
+int ensure_instances(mbgfe* h, uint64_t cap)
+{
+	if (int rc = ensure(h, h->d_inst_pos, cap * 4 + 64)) return rc;
+	if (int rc = ensure(h, h->d_inst_seg, cap * 4 + 64)) return rc;
+	if (int rc = ensure(h, h->d_inst_flag, cap + 64)) return rc;
+	if (int rc = ensure(h, h->d_inst_hash, cap * 16 + 64)) return rc;
+	if (int rc = ensure(h, h->d_inst_slot, cap * 4 + 64)) return rc;
+	if (int rc = ensure(h, h->d_pal_list, PAL_CAP * 8)) return rc;
+	h->inst_cap = cap;
+	return 0;
+}
+
+// empty node (and edge) tables of `slots` slots
+int clear_tables(mbgfe* h, uint64_t slots, uint32_t& launches)
+{
+	if (slots >= (1ull << 31)) return fail(h, MBGFE_E_LIMIT, "node table would need %llu slots (limit 2^31 per GPU)", (unsigned long long)slots);
+	if (int rc = ensure(h, h->d_nodes, slots * sizeof(NodeSlot))) return rc;
+	h->node_slots = slots;
+	const unsigned clear_grid = (unsigned)std::min<uint64_t>((slots + 255) / 256, (uint64_t)h->sm_count * 8);
+	MBGFE_LAUNCH(k_table_clear, clear_grid, 256, 0, h->stream, h->d_nodes.as<NodeSlot>(), slots);
+	launches++;
+	if (!(h->prm.flags & MBGFE_NO_EDGES))
+	{
+		if (int rc = ensure(h, h->d_edges, slots * sizeof(EdgeSlot))) return rc;
+		h->edge_slots = slots;
+		MBGFE_LAUNCH(k_edge_clear, clear_grid, 256, 0, h->stream, h->d_edges.as<EdgeSlot>(), slots);
+		launches++;
+	}
+	else h->edge_slots = 0;
+	return 0;
+}
+
+// selected-count scan of segments [g0, g1): sel_begin[g0] must hold the instances before g0 (0 for g0 == 0)
+void launch_scan(mbgfe* h, uint32_t g0, uint32_t g1, uint32_t& launches)
+{
+	uint64_t* sb = h->d_sel_begin.as<uint64_t>();
+	MBGFE_LAUNCH(k_scan_u32<1024>, 1, 1024, 0, h->stream, h->d_seg_nsel.as<uint32_t>() + g0, sb + g0, g1 - g0, g0 ? (const uint64_t*)(sb + g0) : (const uint64_t*)nullptr);
+	launches++;
+}
+
+// K3b for the instances of segments [g0, g1).  n_hint: instance count when the host knows it (exact grids), else 0.
+void launch_list_hash(mbgfe* h, uint32_t g0, uint32_t g1, uint64_t n_hint, uint32_t& launches)
+{
+	if (g1 == g0) return;
+	const uint32_t k = h->prm.k;
+	unsigned long long* ctr = h->d_counters.as<unsigned long long>();
+	SegTable st = seg_table(h);
+	st.in_start += g0; st.len += g0; st.out_base += g0; st.n = g1 - g0;
+	const uint64_t* sb = h->d_sel_begin.as<uint64_t>();
+	MBGFE_LAUNCH(k_list_selected<NT_LIST>, g1 - g0, NT_LIST, 0, h->stream, st, g0, h->d_selmask.as<uint32_t>(), h->d_seg_c2.as<uint32_t>() + g0, h->d_seg_nsel.as<uint32_t>() + g0,
+		sb + g0, h->d_inst_pos.as<uint32_t>(), h->d_inst_seg.as<uint32_t>(), h->d_inst_flag.as<uint8_t>(), k, h->inst_cap, ctr + CTR_OVERFLOW);
+	const unsigned hash_grid = n_hint ? (unsigned)((2 * n_hint + HASH_WARPS * 32 - 1) / (HASH_WARPS * 32)) : (unsigned)h->sm_count * 6;
+	MBGFE_LAUNCH(k_kmer_hash, hash_grid, HASH_WARPS * 32, 0, h->stream, h->d_seg_out.as<uint64_t>(), h->d_codes.as<uint16_t>(), h->d_rrc.as<uint16_t>(), h->d_inst_pos.as<uint32_t>(),
+		h->d_inst_seg.as<uint32_t>(), sb + g0, sb + g1, h->inst_cap, h->d_inst_hash.as<uint64_t>(), k);
+	const unsigned pal_grid = n_hint ? (unsigned)((n_hint + 255) / 256) : (unsigned)h->sm_count * 4;
+	MBGFE_LAUNCH(k_find_palindromes, pal_grid, 256, 0, h->stream, h->d_inst_hash.as<uint64_t>(), sb + g0, sb + g1, h->inst_cap, ctr + CTR_PALINDROME, h->d_pal_list.as<uint64_t>(), PAL_CAP);
+	launches += 3;
+}
+
+// K4a + K4b for the instances of segments [g0, g1)
+void launch_tables(mbgfe* h, uint32_t g0, uint32_t g1, uint64_t n_hint, uint32_t& launches, bool timed)
+{
+	if (h->prm.flags & MBGFE_NO_TABLE) { if (timed) { tick(h, 8); tick(h, 9); } return; }
+	unsigned long long* ctr = h->d_counters.as<unsigned long long>();
+	const uint64_t* sb = h->d_sel_begin.as<uint64_t>();
+	const unsigned grid = n_hint ? (unsigned)((n_hint + 255) / 256) : (unsigned)h->sm_count * 8;
+	if (g1 > g0)
+	{
+		MBGFE_LAUNCH(k_insert_nodes, grid, 256, 0, h->stream, h->d_inst_hash.as<uint64_t>(), h->d_inst_flag.as<uint8_t>(), sb + g0, sb + g1, h->inst_cap, h->d_nodes.as<NodeSlot>(),
+			h->node_slots - 1, h->d_inst_slot.as<uint32_t>(), ctr + CTR_DISTINCT, ctr + CTR_OVERFLOW);
+		launches++;
+	}
+	if (timed) tick(h, 8);
+	if (g1 > g0 && !(h->prm.flags & MBGFE_NO_EDGES))
+	{
+		MBGFE_LAUNCH(k_insert_edges, grid, 256, 0, h->stream, h->d_inst_hash.as<uint64_t>(), h->d_inst_pos.as<uint32_t>(), h->d_inst_flag.as<uint8_t>(), h->d_inst_slot.as<uint32_t>(),
+			sb + g0, sb + g1, h->inst_cap, h->d_edges.as<EdgeSlot>(), h->edge_slots - 1, ctr + CTR_EDGES, ctr + CTR_OVERFLOW, h->prm.k);
+		launches++;
+	}
+	if (timed) tick(h, 9);
+}
+
+void finish_stats(mbgfe* h, uint64_t n_inst, uint32_t launches, bool staged)
+{
+	h->stats.ms_collapse = staged ? elapsed(h, 3, 4) : 0;
+	h->stats.ms_msat = staged ? elapsed(h, 4, 5) : 0;
+	h->stats.ms_select = staged ? elapsed(h, 5, 6) : 0;
+	h->stats.ms_hash = staged ? elapsed(h, 6, 7) : 0;
+	h->stats.ms_nodes = staged ? elapsed(h, 7, 8) : 0;
+	h->stats.ms_edges = staged ? elapsed(h, 8, 9) : 0;
+	h->stats.ms_process = elapsed(h, 3, 9);
+	h->stats.selected = n_inst;
+	h->stats.launches = launches;
+	h->processed = true;
+}
+
+// The tail with exact sizes: scan, read the instance count, size the lists, hash, apply the palindrome rule, build the
+// tables.  Used by mbgfe_process, and by mbgfe_run when its estimates did not hold or palindromes were found.
 int process_tail(mbgfe* h, uint32_t launches)
 {
 	const uint32_t k = h->prm.k;
 	const uint32_t n_seg = (uint32_t)h->seg_len.size();
 	unsigned long long* ctr = h->d_counters.as<unsigned long long>();
 	const SegTable st = seg_table(h);
-	MBGFE_LAUNCH(k_scan_u32<1024>, 1, 1024, 0, h->stream, h->d_seg_nsel.as<uint32_t>(), h->d_sel_begin.as<uint64_t>(), n_seg);
-	launches++;
+	CU(h, cudaMemsetAsync(ctr + CTR_PALINDROME, 0, (CTR_OWNER - CTR_PALINDROME) * 8, h->stream));
+	launch_scan(h, 0, n_seg, launches);
 	tick(h, 6);
 	uint64_t n_inst = 0;
 	CU(h, cudaMemcpyAsync(&n_inst, h->d_sel_begin.as<uint64_t>() + n_seg, 8, cudaMemcpyDeviceToHost, h->stream));
@@ -642,32 +747,17 @@ int process_tail(mbgfe* h, uint32_t launches)
 	CU(h, cudaGetLastError());
 	h->stats.d2h_bytes += 8;
 	h->n_inst = n_inst;
-	if (int rc = ensure(h, h->d_inst_pos, n_inst * 4 + 64)) return rc;
-	if (int rc = ensure(h, h->d_inst_seg, n_inst * 4 + 64)) return rc;
-	if (int rc = ensure(h, h->d_inst_flag, n_inst + 64)) return rc;
-	if (int rc = ensure(h, h->d_inst_hash, n_inst * 16 + 64)) return rc;
-	if (int rc = ensure(h, h->d_inst_slot, n_inst * 4 + 64)) return rc;
-	const uint64_t pal_cap = 1 << 20;
-	if (int rc = ensure(h, h->d_pal_list, pal_cap * 8)) return rc;
+	if (int rc = ensure_instances(h, std::max<uint64_t>(n_inst, h->inst_cap))) return rc;
 	for (int pass = 0; pass < 2; pass++)
 	{
-		if (n_inst)
-		{
-			MBGFE_LAUNCH(k_list_selected<NT_LIST>, n_seg, NT_LIST, 0, h->stream, st, h->d_selmask.as<uint32_t>(), h->d_seg_c2.as<uint32_t>(), h->d_seg_nsel.as<uint32_t>(),
-				h->d_sel_begin.as<uint64_t>(), h->d_inst_pos.as<uint32_t>(), h->d_inst_seg.as<uint32_t>(), h->d_inst_flag.as<uint8_t>(), k);
-			MBGFE_LAUNCH(k_kmer_hash, (unsigned)((2 * n_inst + HASH_WARPS * 32 - 1) / (HASH_WARPS * 32)), HASH_WARPS * 32, 0, h->stream, h->d_seg_out.as<uint64_t>(),
-				h->d_codes.as<uint16_t>(), h->d_rrc.as<uint16_t>(), h->d_inst_pos.as<uint32_t>(), h->d_inst_seg.as<uint32_t>(), n_inst, h->d_inst_hash.as<uint64_t>(), k);
-			MBGFE_LAUNCH(k_find_palindromes, (unsigned)((n_inst + 255) / 256), 256, 0, h->stream, h->d_inst_hash.as<uint64_t>(), n_inst, ctr + CTR_PALINDROME,
-				h->d_pal_list.as<uint64_t>(), pal_cap);
-			launches += 3;
-		}
+		if (n_inst) launch_list_hash(h, 0, n_seg, n_inst, launches);
 		if (pass == 0) tick(h, 7);
 		uint64_t n_pal = 0;
 		if (int rc = read_counter(h, CTR_PALINDROME, &n_pal)) return rc;
 		if (n_pal == 0) break;
 		// rare path (MBG/ReadHelper.h:755-785): drop what the reference drops, fail where it aborts, rebuild the list
 		if (pass == 1) return fail(h, MBGFE_E_PALINDROME, "palindromic k-mers remain after dropping");
-		if (n_pal > pal_cap) return fail(h, MBGFE_E_LIMIT, "%llu palindromic k-mers (limit %llu)", (unsigned long long)n_pal, (unsigned long long)pal_cap);
+		if (n_pal > PAL_CAP) return fail(h, MBGFE_E_LIMIT, "%llu palindromic k-mers (limit %llu)", (unsigned long long)n_pal, (unsigned long long)PAL_CAP);
 		MBGFE_LAUNCH(k_resolve_palindromes, (unsigned)((n_pal + 127) / 128), 128, 0, h->stream, h->d_pal_list.as<uint64_t>(), n_pal, h->d_inst_pos.as<uint32_t>(),
 			h->d_inst_seg.as<uint32_t>(), h->d_inst_flag.as<uint8_t>(), h->d_seg_out.as<uint64_t>(), h->d_codes.as<uint16_t>(), h->tab_comp.as<uint16_t>(),
 			h->d_selmask.as<uint32_t>(), k, ctr + CTR_CURSOR);
@@ -677,45 +767,20 @@ int process_tail(mbgfe* h, uint32_t launches)
 		if (errs[1]) return fail(h, MBGFE_E_UNHASHABLE, "unhashable k-mer: forward and reverse hashes agree on a non-palindrome (%llu)", errs[1]);
 		if (errs[0]) return fail(h, MBGFE_E_PALINDROME, "the genome has a palindromic k-mer (%llu); cannot build a graph, try a different -w", errs[0]);
 		MBGFE_LAUNCH(k_recount_selected<NT_LIST>, n_seg, NT_LIST, 0, h->stream, st, h->d_selmask.as<uint32_t>(), h->d_seg_c2.as<uint32_t>(), h->d_seg_nsel.as<uint32_t>(), k);
-		MBGFE_LAUNCH(k_scan_u32<1024>, 1, 1024, 0, h->stream, h->d_seg_nsel.as<uint32_t>(), h->d_sel_begin.as<uint64_t>(), n_seg);
+		launches++;
+		launch_scan(h, 0, n_seg, launches);
 		CU(h, cudaMemsetAsync(ctr + CTR_PALINDROME, 0, 8, h->stream));
 		CU(h, cudaMemcpyAsync(&n_inst, h->d_sel_begin.as<uint64_t>() + n_seg, 8, cudaMemcpyDeviceToHost, h->stream));
 		CU(h, cudaStreamSynchronize(h->stream));
 		h->n_inst = n_inst;
-		launches += 3;
+		launches++;
 	}
 	h->stats.distinct = 0; h->stats.distinct_edges = 0;
 	if (!(h->prm.flags & MBGFE_NO_TABLE))
 	{
 		const uint64_t slots = std::max<uint64_t>(next_pow2(std::max<uint64_t>(2 * n_inst, 1024)), h->prm.table_slots ? next_pow2(h->prm.table_slots) : 0);
-		if (slots >= (1ull << 31)) return fail(h, MBGFE_E_LIMIT, "node table would need %llu slots (limit 2^31 per GPU)", (unsigned long long)slots);
-		if (int rc = ensure(h, h->d_nodes, slots * sizeof(NodeSlot))) return rc;
-		h->node_slots = slots;
-		const unsigned clear_grid = (unsigned)std::min<uint64_t>((slots + 255) / 256, (uint64_t)h->sm_count * 8);
-		MBGFE_LAUNCH(k_table_clear, clear_grid, 256, 0, h->stream, h->d_nodes.as<NodeSlot>(), slots);
-		launches++;
-		if (n_inst)
-		{
-			MBGFE_LAUNCH(k_insert_nodes, (unsigned)((n_inst + 255) / 256), 256, 0, h->stream, h->d_inst_hash.as<uint64_t>(), h->d_inst_flag.as<uint8_t>(), n_inst,
-				h->d_nodes.as<NodeSlot>(), slots - 1, h->d_inst_slot.as<uint32_t>(), ctr + CTR_DISTINCT);
-			launches++;
-		}
-		tick(h, 8);
-		if (!(h->prm.flags & MBGFE_NO_EDGES))
-		{
-			if (int rc = ensure(h, h->d_edges, slots * sizeof(EdgeSlot))) return rc;
-			h->edge_slots = slots;
-			MBGFE_LAUNCH(k_edge_clear, clear_grid, 256, 0, h->stream, h->d_edges.as<EdgeSlot>(), slots);
-			launches++;
-			if (n_inst)
-			{
-				MBGFE_LAUNCH(k_insert_edges, (unsigned)((n_inst + 255) / 256), 256, 0, h->stream, h->d_inst_hash.as<uint64_t>(), h->d_inst_pos.as<uint32_t>(),
-					h->d_inst_flag.as<uint8_t>(), h->d_inst_slot.as<uint32_t>(), n_inst, h->d_edges.as<EdgeSlot>(), slots - 1, ctr + CTR_EDGES, k);
-				launches++;
-			}
-		}
-		else h->edge_slots = 0;
-		tick(h, 9);
+		if (int rc = clear_tables(h, slots, launches)) return rc;
+		launch_tables(h, 0, n_seg, n_inst, launches, true);
 		unsigned long long two[2] = { 0, 0 };
 		CU(h, cudaMemcpyAsync(two, ctr + CTR_DISTINCT, 16, cudaMemcpyDeviceToHost, h->stream));
 		CU(h, cudaStreamSynchronize(h->stream));
@@ -726,16 +791,7 @@ int process_tail(mbgfe* h, uint32_t launches)
 	}
 	else { tick(h, 8); tick(h, 9); CU(h, cudaStreamSynchronize(h->stream)); }
 	CU(h, cudaGetLastError());
-	h->stats.ms_collapse = elapsed(h, 3, 4);
-	h->stats.ms_msat = elapsed(h, 4, 5);
-	h->stats.ms_select = elapsed(h, 5, 6);
-	h->stats.ms_hash = elapsed(h, 6, 7);
-	h->stats.ms_nodes = elapsed(h, 7, 8);
-	h->stats.ms_edges = elapsed(h, 8, 9);
-	h->stats.ms_process = elapsed(h, 3, 9);
-	h->stats.selected = n_inst;
-	h->stats.launches = launches;
-	h->processed = true;
+	finish_stats(h, n_inst, launches, true);
 	return 0;
 }
 
@@ -781,48 +837,91 @@ int mbgfe_run(mbgfe* h)
 	if (int rc = upload_segments(h)) return rc;
 	if (int rc = prepare_process(h)) return rc;
 	tick(h, 0);
-	tick(h, 3); tick(h, 4); tick(h, 5);     // pipelined: the whole front end is reported under ms_select
+	tick(h, 3);
 	CU(h, cudaStreamWaitEvent(h->copy_stream, h->ev[0], 0));
-	const uint64_t PIECE = 48ull << 20;
-	uint64_t pos = 0, packed_upto = 0;
-	uint32_t g_done = 0, launches = 0;
-	size_t piece = 0;
-	for (size_t ci = 0; ci < h->pending.size(); ci++)
+	// ---- phase A: every H2D piece is queued on the copy stream up front, so the copy engine never waits for the host
+	const uint64_t PIECE = h->prm.piece_bytes ? std::max<uint64_t>(h->prm.piece_bytes, 64) : (48ull << 20);
+	std::vector<uint64_t> piece_end;
 	{
-		const HostChunk& c = h->pending[ci];
-		const uint64_t first = c.offsets[0], bytes = c.offsets[c.n_reads] - first;
-		for (uint64_t off = 0; off < bytes; off += PIECE)
+		uint64_t pos = 0;
+		for (const HostChunk& c : h->pending)
 		{
-			const uint64_t len = std::min(PIECE, bytes - off);
-			if (piece >= h->piece_events.size()) { cudaEvent_t e; CU(h, cudaEventCreate(&e)); h->piece_events.push_back(e); }
-			CU(h, cudaMemcpyAsync(h->d_ascii.as<char>() + pos, c.bases + first + off, len, cudaMemcpyHostToDevice, h->copy_stream));
-			CU(h, cudaEventRecord(h->piece_events[piece], h->copy_stream));
-			CU(h, cudaStreamWaitEvent(h->stream, h->piece_events[piece], 0));
-			piece++;
-			pos += len;
-			const bool last = pos == n_bases;
-			const uint64_t pack_to = last ? n_bases : (pos & ~(uint64_t)31);
-			if (pack_to > packed_upto)
+			const uint64_t first = c.offsets[0], bytes = c.offsets[c.n_reads] - first;
+			for (uint64_t off = 0; off < bytes; off += PIECE)
 			{
-				const uint64_t c0 = packed_upto / 32, c1 = (pack_to + 31) / 32;
-				const unsigned grid = (unsigned)std::min<uint64_t>((c1 - c0 + 255) / 256, (uint64_t)h->sm_count * 16);
-				MBGFE_LAUNCH(k_pack_ascii, grid, 256, 0, h->stream, (const uint4*)h->d_ascii.p, n_bases, c0, c1, h->d_packed.as<uint64_t>(), h->d_nonacgt.as<uint64_t>(),
-					h->d_counters.as<unsigned long long>() + CTR_NONACGT, bad_cap);
-				launches++;
-				packed_upto = pack_to;
+				const uint64_t len = std::min(PIECE, bytes - off);
+				const size_t piece = piece_end.size();
+				if (piece >= h->piece_events.size()) { cudaEvent_t e; CU(h, cudaEventCreate(&e)); h->piece_events.push_back(e); }
+				CU(h, cudaMemcpyAsync(h->d_ascii.as<char>() + pos, c.bases + first + off, len, cudaMemcpyHostToDevice, h->copy_stream));
+				CU(h, cudaEventRecord(h->piece_events[piece], h->copy_stream));
+				pos += len;
+				piece_end.push_back(pos);
 			}
-			uint32_t g_end = g_done;
-			while (g_end < n_seg && h->read_off[h->seg_read[g_end] + 1] <= packed_upto) g_end++;
-			launches += launch_front(h, g_done, g_end - g_done, false);
-			g_done = g_end;
 		}
+		CU(h, cudaEventRecord(h->ev[1], h->copy_stream));
 	}
-	CU(h, cudaEventRecord(h->ev[1], h->copy_stream));
-	launches += launch_front(h, g_done, n_seg - g_done, false);
 	h->stats.h2d_bytes += n_bases;
-	uint64_t n_bad = 0;
-	if (int rc = read_counter(h, CTR_NONACGT, &n_bad)) return rc;
+	// ---- phase B: behind each piece, K0 on its bytes and K1 .. K4 on the segments it completes.  The instance lists and
+	// the tables are sized from the first piece that completes segments (selected k-mers per base, extrapolated); the
+	// kernels refuse to write past those sizes and count what they refused, and the exact path reruns the tail then.
+	const bool want_table = !(h->prm.flags & MBGFE_NO_TABLE);
+	unsigned long long* ctr = h->d_counters.as<unsigned long long>();
+	uint64_t packed_upto = 0;
+	uint32_t g_done = 0, g_tail = 0, launches = 0;
+	bool sized = false;
+	for (size_t piece = 0; piece < piece_end.size(); piece++)
+	{
+		CU(h, cudaStreamWaitEvent(h->stream, h->piece_events[piece], 0));
+		const uint64_t pos = piece_end[piece];
+		const bool last = pos == n_bases;
+		const uint64_t pack_to = last ? n_bases : (pos & ~(uint64_t)31);
+		if (pack_to > packed_upto)
+		{
+			const uint64_t c0 = packed_upto / 32, c1 = (pack_to + 31) / 32;
+			const unsigned grid = (unsigned)std::min<uint64_t>((c1 - c0 + 255) / 256, (uint64_t)h->sm_count * 16);
+			MBGFE_LAUNCH(k_pack_ascii, grid, 256, 0, h->stream, (const uint4*)h->d_ascii.p, n_bases, c0, c1, h->d_packed.as<uint64_t>(), h->d_nonacgt.as<uint64_t>(),
+				h->d_counters.as<unsigned long long>() + CTR_NONACGT, bad_cap);
+			launches++;
+			packed_upto = pack_to;
+		}
+		uint32_t g_end = g_done;
+		while (g_end < n_seg && h->read_off[h->seg_read[g_end] + 1] <= packed_upto) g_end++;
+		if (g_end == g_done) continue;
+		launches += launch_front(h, g_done, g_end - g_done, false);
+		launch_scan(h, g_done, g_end, launches);
+		g_done = g_end;
+		if (!sized)
+		{
+			uint64_t n0 = 0;
+			CU(h, cudaMemcpyAsync(&n0, h->d_sel_begin.as<uint64_t>() + g_end, 8, cudaMemcpyDeviceToHost, h->stream));
+			CU(h, cudaStreamSynchronize(h->stream));
+			h->stats.d2h_bytes += 8;
+			const uint64_t bases0 = h->read_off[h->seg_read[g_end - 1] + 1];
+			const double per_base = (double)n0 / (double)std::max<uint64_t>(bases0, 1);
+			const uint64_t est = (uint64_t)(per_base * (double)n_bases) + 1;
+			if (int rc = ensure_instances(h, std::max<uint64_t>(est + est / 4 + 4096, h->inst_cap))) return rc;
+			if (want_table)
+			{
+				const uint64_t slots = std::max<uint64_t>(next_pow2(std::max<uint64_t>(2 * est, 1024)), h->prm.table_slots ? next_pow2(h->prm.table_slots) : 0);
+				if (int rc = clear_tables(h, slots, launches)) return rc;
+				h->stats.table_slots = slots;
+			}
+			sized = true;
+		}
+		launch_list_hash(h, g_tail, g_end, 0, launches);
+		launch_tables(h, g_tail, g_end, 0, launches, false);
+		g_tail = g_end;
+	}
+	tick(h, 9);
+	// ---- one read-back decides whether the pipelined result stands
+	unsigned long long c8[8] = { 0 };
+	uint64_t n_inst = 0;
+	CU(h, cudaMemcpyAsync(c8, ctr, sizeof(c8), cudaMemcpyDeviceToHost, h->stream));
+	if (n_seg) CU(h, cudaMemcpyAsync(&n_inst, h->d_sel_begin.as<uint64_t>() + n_seg, 8, cudaMemcpyDeviceToHost, h->stream));
+	CU(h, cudaStreamSynchronize(h->stream));
 	CU(h, cudaGetLastError());
+	h->stats.d2h_bytes += sizeof(c8) + 8;
+	const uint64_t n_bad = c8[CTR_NONACGT];
 	h->stats.ms_upload = elapsed(h, 0, 1);
 	h->stats.ms_pack = 0;
 	h->stats.reads = n_reads; h->stats.raw_bases = n_bases; h->stats.nonacgt = n_bad;
@@ -844,7 +943,19 @@ int mbgfe_run(mbgfe* h)
 	}
 	h->stats.segments = n_seg;
 	h->resident = true;
-	return process_tail(h, launches);
+	if (!sized || g_tail != n_seg || c8[CTR_PALINDROME] || c8[CTR_OVERFLOW] || n_inst > h->inst_cap)
+	{
+		// estimates exceeded, or palindromic k-mers to resolve (MBG/ReadHelper.h:755-785): the exact tail on the resident results
+		tick(h, 4); tick(h, 5);
+		h->stats.table_grows += (c8[CTR_OVERFLOW] || n_inst > h->inst_cap) ? 1 : 0;
+		return process_tail(h, launches);
+	}
+	h->n_inst = n_inst;
+	h->stats.distinct = want_table ? c8[CTR_DISTINCT] : 0;
+	h->stats.distinct_edges = (want_table && h->edge_slots) ? c8[CTR_EDGES] : 0;
+	h->have_table = want_table;
+	finish_stats(h, n_inst, launches, false);
+	return 0;
 }
 
 }
@@ -946,7 +1057,7 @@ int device_scan(mbgfe* h, const uint32_t* in, uint64_t* out, uint32_t n)
 	if (int rc = ensure(h, h->d_scan_tot, (size_t)(n_tiles + 1) * 4)) return rc;
 	if (int rc = ensure(h, h->d_scan_off, (size_t)(n_tiles + 2) * 8)) return rc;
 	MBGFE_LAUNCH(k_scan_tile_totals, n_tiles, SCAN_NT, 0, h->stream, in, h->d_scan_tot.as<uint32_t>(), n);
-	MBGFE_LAUNCH(k_scan_u32<1024>, 1, 1024, 0, h->stream, h->d_scan_tot.as<uint32_t>(), h->d_scan_off.as<uint64_t>(), n_tiles);
+	MBGFE_LAUNCH(k_scan_u32<1024>, 1, 1024, 0, h->stream, h->d_scan_tot.as<uint32_t>(), h->d_scan_off.as<uint64_t>(), n_tiles, (const uint64_t*)nullptr);
 	MBGFE_LAUNCH(k_scan_tiles, n_tiles, SCAN_NT, 0, h->stream, in, h->d_scan_off.as<uint64_t>(), out, n);
 	return 0;
 }
@@ -1113,6 +1224,7 @@ int mbgfe_exchange_counts(mbgfe* h, uint64_t* send_counts)
 	CU(h, cudaMemcpyAsync(c.data(), ctr + CTR_OWNER, world * 8, cudaMemcpyDeviceToHost, h->stream));
 	CU(h, cudaStreamSynchronize(h->stream));
 	for (uint32_t i = 0; i < world; i++) send_counts[i] = c[i];
+	h->x_counts.assign(send_counts, send_counts + world);
 	return 0;
 }
 
@@ -1122,7 +1234,8 @@ int mbgfe_exchange_pack(mbgfe* h, void** device_records)
 	if (!h->processed) return fail(h, MBGFE_E_STATE, "exchange before mbgfe_process");
 	const uint32_t world = h->prm.world;
 	std::vector<uint64_t> counts(world);
-	if (int rc = mbgfe_exchange_counts(h, counts.data())) return rc;
+	if (h->x_counts.size() == world) counts = h->x_counts;        // counted by the caller a moment ago
+	else if (int rc = mbgfe_exchange_counts(h, counts.data())) return rc;
 	std::vector<unsigned long long> cursors(world);
 	uint64_t total = 0;
 	for (uint32_t i = 0; i < world; i++) { cursors[i] = total; total += counts[i]; }
@@ -1289,7 +1402,7 @@ int mbgfe_kat_kmer_hash(mbgfe* h, const uint16_t* codes, uint32_t k, mbgfe_hash1
 	DevBuf d_codes, d_rrc, d_misc;
 	int rc = ensure(h, d_codes, (size_t)k * 2 + 64);
 	if (!rc) rc = ensure(h, d_rrc, (size_t)k * 2 + 64);
-	if (!rc) rc = ensure(h, d_misc, 64);
+	if (!rc) rc = ensure(h, d_misc, 128);
 	if (rc) { release(d_codes); release(d_rrc); release(d_misc); return rc; }
 	// one synthetic instance: a single segment whose slot is exactly the k codes, position 0
 	const uint64_t bases[2] = { 0, k };
@@ -1300,9 +1413,12 @@ int mbgfe_kat_kmer_hash(mbgfe* h, const uint16_t* codes, uint32_t k, mbgfe_hash1
 	cudaMemcpyAsync(d_misc.as<char>() + 0, bases, 16, cudaMemcpyHostToDevice, h->stream);   // seg_out_base[0..1]
 	cudaMemcpyAsync(d_misc.as<char>() + 16, &zero32, 4, cudaMemcpyHostToDevice, h->stream);  // inst_pos[0]
 	cudaMemcpyAsync(d_misc.as<char>() + 20, &zero32, 4, cudaMemcpyHostToDevice, h->stream);  // inst_seg[0]
+	const uint64_t range[2] = { 0, 1 };
+	cudaMemcpyAsync(d_misc.as<char>() + 64, range, 16, cudaMemcpyHostToDevice, h->stream);   // instance range [0, 1)
 	MBGFE_LAUNCH(k_revcomp_codes, (k + 255) / 256, 256, 0, h->stream, d_codes.as<uint16_t>(), k, h->tab_comp.as<uint16_t>(), d_rrc.as<uint16_t>());
 	MBGFE_LAUNCH(k_kmer_hash, 1, HASH_WARPS * 32, 0, h->stream, (const uint64_t*)d_misc.p, d_codes.as<uint16_t>(), d_rrc.as<uint16_t>(), (const uint32_t*)(d_misc.as<char>() + 16),
-		(const uint32_t*)(d_misc.as<char>() + 20), (uint64_t)1, (uint64_t*)(d_misc.as<char>() + 32), k);
+		(const uint32_t*)(d_misc.as<char>() + 20), (const uint64_t*)(d_misc.as<char>() + 64), (const uint64_t*)(d_misc.as<char>() + 72), (uint64_t)1,
+		(uint64_t*)(d_misc.as<char>() + 32), k);
 	cudaStreamSynchronize(h->stream);
 	uint64_t res[2] = { 0, 0 };
 	cudaError_t e = cudaMemcpy(res, d_misc.as<char>() + 32, 16, cudaMemcpyDeviceToHost);

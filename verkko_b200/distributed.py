@@ -7,6 +7,7 @@ The same code runs on the GPU-less emulator build with the gloo backend (tests),
 pointers.
 """
 import ctypes as C
+import time
 
 import numpy as np
 import torch
@@ -51,6 +52,12 @@ class DistributedCounter:
         self.n_recv = 0
         self.sent_bytes = 0
         self.id_begin = None
+        self.wall_ms = {}        # host wall clock per phase of the last exchange (where the step's host gaps are)
+
+    def _mark(self, name):
+        now = time.perf_counter()
+        self.wall_ms[name] = self.wall_ms.get(name, 0.0) + (now - self._t) * 1e3
+        self._t = now
 
     def _dev(self):
         return "cuda" if self.on_gpu else "cpu"
@@ -75,17 +82,24 @@ class DistributedCounter:
     def exchange_and_count(self):
         fe, world = self.fe, self.world
         self.last_exchange_ms = 0.0
+        self.wall_ms = {}
+        self._t = time.perf_counter()
         # ---- nodes: k-mer records to their owners
         send_counts = fe.exchange_counts().astype(np.int64)
+        self._mark("node_counts")
         recv_counts = self._counts_exchange(send_counts)
+        self._mark("node_counts_a2a")
         n_send, n_recv = int(send_counts.sum()), int(recv_counts.sum())
         send_ptr = fe.exchange_pack()
+        self._mark("node_pack")
         recv_ptr = fe.exchange_reserve(n_recv)
         send_t = wrap_pointer(send_ptr, n_send * RECORD_WORDS, self.on_gpu)
         recv_t = wrap_pointer(recv_ptr, n_recv * RECORD_WORDS, self.on_gpu)
         self._timed(lambda: dist.all_to_all_single(recv_t, send_t, output_split_sizes=(recv_counts * RECORD_WORDS).tolist(),
                                                    input_split_sizes=(send_counts * RECORD_WORDS).tolist()))
+        self._mark("node_a2a")
         fe.exchange_insert(recv_ptr, n_recv)
+        self._mark("node_insert")
         self.n_recv = n_recv
         self.sent_bytes = n_send * 32
         if not self.edges:
@@ -101,22 +115,30 @@ class DistributedCounter:
         id_begin[1:] = np.cumsum(sizes)
         self.id_begin = id_begin
         inst_base = int(n_inst[:self.rank].sum())
+        self._mark("sizes_allgather")
         ids_ptr = fe.exchange_node_ids(int(id_begin[self.rank]), recv_ptr, n_recv)
+        self._mark("rank_and_ids")
         back_ptr = fe.exchange_scratch(0, n_send * 4)
         ids_t = wrap_pointer(ids_ptr, n_recv, self.on_gpu, torch.int32)
         back_t = wrap_pointer(back_ptr, n_send, self.on_gpu, torch.int32)
         self._timed(lambda: dist.all_to_all_single(back_t, ids_t, output_split_sizes=send_counts.tolist(), input_split_sizes=recv_counts.tolist()))
+        self._mark("ids_a2a")
         # ---- edges: observations to the owner of their `from` node
         e_send = fe.exchange_edge_counts(back_ptr, id_begin, inst_base).astype(np.int64)
+        self._mark("edge_counts")
         e_recv = self._counts_exchange(e_send)
         ne_send, ne_recv = int(e_send.sum()), int(e_recv.sum())
+        self._mark("edge_counts_a2a")
         es_ptr = fe.exchange_edge_pack(e_send)
+        self._mark("edge_pack")
         er_ptr = fe.exchange_scratch(1, ne_recv * 16)
         es_t = wrap_pointer(es_ptr, ne_send * EDGE_RECORD_WORDS, self.on_gpu)
         er_t = wrap_pointer(er_ptr, ne_recv * EDGE_RECORD_WORDS, self.on_gpu)
         self._timed(lambda: dist.all_to_all_single(er_t, es_t, output_split_sizes=(e_recv * EDGE_RECORD_WORDS).tolist(),
                                                    input_split_sizes=(e_send * EDGE_RECORD_WORDS).tolist()))
+        self._mark("edge_a2a")
         fe.exchange_insert_edges(er_ptr, ne_recv)
+        self._mark("edge_insert")
         self.sent_bytes += n_recv * 4 + ne_send * 16
 
     def download_counts(self):

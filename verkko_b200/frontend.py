@@ -23,7 +23,7 @@ PART_DTYPE = np.dtype([
 class Params(C.Structure):
     _fields_ = [("abi_version", C.c_uint32), ("k", C.c_uint32), ("w", C.c_uint32), ("error_masking", C.c_uint32),
                 ("kmer_abundance", C.c_uint32), ("flags", C.c_uint32), ("device", C.c_int32), ("rank", C.c_uint32),
-                ("world", C.c_uint32), ("reserved", C.c_uint32), ("table_slots", C.c_uint64)]
+                ("world", C.c_uint32), ("piece_bytes", C.c_uint32), ("table_slots", C.c_uint64)]
 
 
 class Stats(C.Structure):
@@ -124,10 +124,10 @@ class MbgFrontEnd:
     """ReadpartIterator{k, w, errorMasking} + HashList{k} on one B200."""
 
     def __init__(self, k, w, error_masking="collapse-msat", kmer_abundance=1, flags=0, device=0, rank=0, world=1,
-                 table_slots=0, library=None):
+                 table_slots=0, library=None, piece_bytes=0):
         self.lib = load_library(library)
         mode = MODES[error_masking] if isinstance(error_masking, str) else int(error_masking)
-        self.params = Params(1, k, w, mode, kmer_abundance, flags, device, rank, world, 0, table_slots)
+        self.params = Params(1, k, w, mode, kmer_abundance, flags, device, rank, world, piece_bytes, table_slots)
         self.handle = C.c_void_p()
         rc = self.lib.mbgfe_create(C.byref(self.params), C.byref(self.handle))
         if rc != 0:
