@@ -47,3 +47,8 @@ def test_emulated_pipelined_run_estimate_overflow(oracle, emu_library):
     got = run_frontend("collapse", 31, 1, reads, library=emu_library, piece_bytes=3200)
     compare_runs(got, oracle.run("collapse", 31, 1, reads), what="overflow fallback")
     assert got["stats"]["table_grows"] >= 1
+
+
+def test_emulated_tandem_repeats_longer_than_a_tile(oracle, emu_library):
+    reads = workloads.long_tandem_reads()[:3] + [workloads.repeat_rich(22, 5000)]
+    compare_runs(run_frontend("msat", 63, 33, reads, library=emu_library), oracle.run("msat", 63, 33, reads), what="long tandem")

@@ -161,3 +161,10 @@ def test_pipelined_run_estimate_overflow(oracle):
     got = run_frontend("collapse", 31, 1, reads, piece_bytes=12800)
     compare_runs(got, oracle.run("collapse", 31, 1, reads), what="overflow fallback")
     assert got["stats"]["table_grows"] >= 1
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("mode,k,w", [("msat", 63, 33), ("collapse-msat", 31, 1), ("dinuc", 101, 20), ("collapse-msat", 1001, 100)])
+def test_tandem_repeats_longer_than_a_tile(oracle, mode, k, w):
+    reads = workloads.long_tandem_reads() + [workloads.repeat_rich(21, 20000), workloads.repeat_rich(22, 5000)]
+    compare_runs(run_frontend(mode, k, w, reads), oracle.run(mode, k, w, reads), what=f"long tandem {mode}")

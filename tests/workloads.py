@@ -61,3 +61,17 @@ def palindrome_read(seed):
     comp = {65: 84, 67: 71, 71: 67, 84: 65}
     x = lcg_bases(seed, 400)
     return x + b"AT" * 6 + bytes(comp[c] for c in reversed(x))
+
+
+def long_tandem_reads(seed=5):
+    """tandem repeats much longer than a K2 tile (1024 symbols) at assorted alignments, between random flanks: one code
+    spans several tiles, its slot leaves with an earlier tile than the one that computes it"""
+    rng = np.random.default_rng(seed)
+    acgt = np.frombuffer(b"ACGT", dtype=np.uint8)
+
+    def rnd(n):
+        return bytes(acgt[rng.integers(0, 4, n)])
+    reads = []
+    for motif, copies, lead in ((b"AC", 900, 700), (b"ACG", 800, 1000), (b"ACGT", 300, 1019), (b"ACGTC", 500, 33), (b"ACGTCA", 400, 2040), (b"AC", 2000, 5)):
+        reads.append(rnd(lead) + motif * copies + rnd(1500))
+    return reads

@@ -36,7 +36,17 @@ struct Planes { uint32_t lo, hi; };    // 32 symbols: bit i of lo / hi = low / h
 __device__ __forceinline__ Planes planes_of(uint64_t w) { Planes p; p.lo = (uint32_t)w; p.hi = (uint32_t)(w >> 32); return p; }
 __device__ __forceinline__ uint64_t word_of(uint32_t lo, uint32_t hi) { return ((uint64_t)hi << 32) | lo; }
 // low n bits set (n in 0..32)
-__device__ __forceinline__ uint32_t low_bits(uint32_t n) { return n >= 32 ? 0xffffffffu : ((1u << n) - 1); }
+// (one clamped funnel shift on the device: the high word of 0x00000000ffffffff << min(n, 32))
+__device__ __forceinline__ uint32_t low_bits(uint32_t n)
+{
+#ifdef MBGFE_EMU_BUILD
+	return n >= 32 ? 0xffffffffu : ((1u << n) - 1);
+#else
+	return __funnelshift_lc(0xffffffffu, 0u, n);
+#endif
+}
+// low max(a - b, 0) bits set
+__device__ __forceinline__ uint32_t low_bits_sat(uint32_t a, uint32_t b) { return low_bits(max(a, b) - b); }
 // (hi:lo) >> sh, low 32 bits (sh in 0..31)
 __device__ __forceinline__ uint32_t funnel_r(uint32_t lo, uint32_t hi, uint32_t sh)
 {
@@ -404,50 +414,68 @@ __device__ __forceinline__ void stretch_codes(Planes first, uint32_t m, uint32_t
 // K2: multiRLECompress (MBG/ErrorMaskHelper.cpp:169-342) in scan-parallel form (DESIGN.md "K2"; the sequential
 // statement of exactly this algorithm is oracle/mbg_oracle.c:orc_msat_scanform, fuzzed against the reference).
 //   candidates : starts a of maximal stretches of eq_m (sym[p]==sym[p+m]) of length L >= m; run = [a, a+L+m)
-//   emitted    : candidate end > exclusive prefix maximum of candidate ends           (block max-scan + carry)
+//   emitted    : candidate end > exclusive prefix maximum of candidate ends           (max-scan + carry)
 //   cover      : 1 = inside exactly one emitted run, else single-symbol codes        (from the two carried ends)
-//   code start : p == 0 | cover(p) != 1 | cover(p-1) != 1 | a run is emitted at p     (popcount + block sum-scan)
-// One CTA per segment, 32 symbols per thread and tile, every mask one bit per position; the tile's words sit in shared
-// memory (with the word before and the three after), three block scans per tile.  Codes are written in two sweeps:
-// the single-symbol codes of the word, then the stretches that END in the word (by the thread that owns the symbol
-// after them).  The reverse-complement array rrc is written alongside (rrc[rr0 - i] = complement(code i)).
+//   code start : p == 0 | cover(p) != 1 | cover(p-1) != 1 | a run is emitted at p     (popcount + sum-scan)
+// One WARP per segment, one 32-symbol planar word per lane and tile (1024 symbols): every mask is one bit per
+// position, the three scans are warp shuffles (no CTA barrier anywhere), carries between tiles live in registers.
+// A lane walks its candidates once in position order (ends by count-trailing-zeros on the 64 positions it sees; longer
+// stretches walk on through the staged words), then once more to mark the emitted ones and build the cover masks.
+// Codes are not stored to HBM one by one: the tile's codes and reverse-complement codes are staged in shared memory
+// (the staging index is kept congruent to the output index mod 8) and leave as coalesced 128-bit stores; an unfinished
+// group of 8 is carried into the next tile.  A stretch is coded by the lane that owns the symbol after it; when its
+// slot was flushed by an earlier tile (stretches longer than a tile) the code goes to HBM directly.
+// The reverse-complement array rrc is written alongside (rrc[rr0 - i] = complement(code i)).
 // Segments with fewer than 32 symbols produce no part (MBG/ReadHelper.h:847,858,882,893): seg_c2 = 0.
 // Algorithmic bytes: 1/4 read per symbol + 2 written per code (+ 2 for rrc, + 4 per code when poses are requested).
-template <int NT>
-__global__ void __launch_bounds__(NT) k_msat(SegTable seg, const uint64_t* __restrict__ sym, const uint32_t* __restrict__ seg_c1,
+#ifdef MBGFE_EMU_BUILD
+constexpr int MSAT_WARPS = 1;      // the emulator's warp primitives are CTA-wide barriers: one warp per CTA there
+#else
+constexpr int MSAT_WARPS = 4;
+#endif
+constexpr uint32_t MSAT_TILE = 1024, MSAT_STAGE = MSAT_TILE + 8;
+
+__global__ void __launch_bounds__(MSAT_WARPS * 32) k_msat(SegTable seg, const uint64_t* __restrict__ sym, const uint32_t* __restrict__ seg_c1,
 	uint16_t* __restrict__ codes, uint16_t* __restrict__ rrc, uint32_t* __restrict__ seg_c2, const uint32_t* __restrict__ pos1,
 	uint32_t* __restrict__ pos2, uint32_t max_motif)
 {
-	__shared__ uint32_t cand[NT * 33];      // per symbol of the tile: (run end << 3) | (7 - motif length) (row stride 33: no bank conflicts)
-	__shared__ uint64_t tile_w[NT + 4];     // planar words tile_word0 - 1 .. tile_word0 + NT + 2
-	__shared__ uint32_t warp_tmp[NT / 32];
-	__shared__ LastRun warp_last[NT / 32];
-	const uint32_t g = blockIdx.x;
+	__shared__ uint64_t s_words[MSAT_WARPS][36];                       // planar words tile_word0 - 1 .. tile_word0 + 34
+	__shared__ uint32_t s_cand[MSAT_WARPS][32 * 33];                   // per lane: (run end << 3) | (7 - motif) of its candidates, in position order
+	__align__(16) __shared__ uint16_t s_codes[MSAT_WARPS][MSAT_STAGE];
+	__align__(16) __shared__ uint16_t s_rrc[MSAT_WARPS][MSAT_STAGE];   // reversed: entry i of the stage at [MSAT_STAGE - 1 - i]
+	const uint32_t lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+	const uint32_t g = blockIdx.x * MSAT_WARPS + wid;
 	if (g >= seg.n) return;
 	const uint32_t n = seg_c1[g];
-	if (n < 32) { if (threadIdx.x == 0) seg_c2[g] = 0; return; }
+	if (n < 32) { if (lane == 0) seg_c2[g] = 0; return; }
 	const uint64_t out0 = seg.out_base[g];
 	const uint64_t rr0 = seg.out_base[g + 1] - 1;          // rrc[rr0 - i] = complement(code i): the reverse complement reads forwards
 	const uint64_t* __restrict__ s = sym + (out0 >> 5);   // segment-local words
+	uint16_t* __restrict__ codes_g = codes + out0;
+	uint16_t* __restrict__ rrc_g = rrc + rr0;             // rrc_g[-i]
 	const uint32_t n_words = (n + 31) / 32;
-	uint32_t* my_cand = cand + threadIdx.x * 33;
+	uint64_t* tile_w = s_words[wid];
+	uint32_t* my_cand = s_cand[wid] + lane * 33;
+	uint16_t* st_c = s_codes[wid];
+	uint16_t* st_r = s_rrc[wid];
+	const uint32_t lt_mask = low_bits(lane);               // lanes below this one
 	uint32_t carry_max = 0;            // maximum run end over all candidates of earlier tiles
-	LastRun carry_last; carry_last.m = 0; carry_last.start = 0; carry_last.prev_end = 0;
+	uint32_t carry_last_sm = 0, carry_last_pe = 0;   // latest emitted run so far: start | m << 29 (m == 0: none), end of the run emitted before it
 	uint32_t carry_codes = 0;
-	for (uint32_t tile = 0; tile < n; tile += NT * 32)
+	for (uint32_t tile = 0; tile < n; tile += MSAT_TILE)
 	{
 		const uint32_t jb = tile >> 5;     // first word of the tile
-		for (uint32_t i = threadIdx.x; i < NT + 4; i += NT)
+		for (uint32_t i = lane; i < 36; i += 32)
 		{
 			const uint32_t jj = jb + i;    // word jj - 1
 			tile_w[i] = (jj >= 1 && jj - 1 < n_words) ? __ldg(s + (jj - 1)) : 0ull;
 		}
-		__syncthreads();
+		__syncwarp();
 		// 32 symbols starting at segment position q, from the staged words when they cover it
 		auto win = [&](uint32_t q) -> Planes
 		{
 			const uint32_t jq = q >> 5, sh = q & 31;
-			if (jq + 1 >= jb && jq + 1 - jb + 1 < NT + 4)
+			if (jq + 1 >= jb && jq + 1 - jb + 1 < 36)
 			{
 				const Planes a = planes_of(tile_w[jq + 1 - jb]);
 				return sh ? shift_in(a, planes_of(tile_w[jq + 2 - jb]), sh) : a;
@@ -456,106 +484,131 @@ __global__ void __launch_bounds__(NT) k_msat(SegTable seg, const uint64_t* __res
 			if (sh) a = shift_in(a, planes_of(jq + 1 < n_words ? __ldg(s + jq + 1) : 0ull), sh);
 			return a;
 		};
-		const uint32_t p0 = tile + threadIdx.x * 32;
+		const uint32_t p0 = tile + lane * 32;
 		const bool active = p0 < n;
-		const Planes am = planes_of(tile_w[threadIdx.x]), a0 = planes_of(tile_w[threadIdx.x + 1]), a1 = planes_of(tile_w[threadIdx.x + 2]),
-			a2 = planes_of(tile_w[threadIdx.x + 3]);
-		// ---- candidates: starts of stretches of eq_m of length >= m, with the end of the run they open
-		uint32_t local_max = 0;
-		uint32_t cand_bits = 0;
-		if (active)
+		const Planes am = planes_of(tile_w[lane]), a0 = planes_of(tile_w[lane + 1]), a1 = planes_of(tile_w[lane + 2]), a2 = planes_of(tile_w[lane + 3]);
+		// ---- candidates: starts of stretches of eq_m of length >= m (one mask per motif length)
+		uint32_t e0[7], e1[7], cm[7];
+		uint32_t cand_any = 0;
+#pragma unroll
+		for (uint32_t m = 2; m <= 6; m++)
 		{
-			for (uint32_t m = 2; m <= max_motif; m++)
+			e0[m] = 0; e1[m] = 0; cm[m] = 0;
+			if (m <= max_motif && n >= 2 * m && active)
 			{
-				if (n < 2 * m) break;
 				const uint32_t lim = n - m;            // eq_m(p) is defined for p < lim
-				uint32_t e0 = eq_shift(a0, a1, m), e1 = eq_shift(a1, a2, m);
-				e0 &= lim > p0 ? low_bits(min(32u, lim - p0)) : 0u;
-				e1 &= lim > p0 + 32 ? low_bits(min(32u, lim - p0 - 32)) : 0u;
+				e0[m] = eq_shift(a0, a1, m) & low_bits_sat(lim, p0);
+				e1[m] = eq_shift(a1, a2, m) & low_bits_sat(lim, p0 + 32);
 				uint32_t prev = 0;
 				if (p0 > 0 && p0 - 1 < lim) prev = eq_shift(am, a0, m) >> 31;
-				uint32_t run = e0 & ~((e0 << 1) | prev);
-				for (uint32_t t = 1; t < m; t++) run &= funnel_r(e0, e1, t);
-				const uint64_t e64 = word_of(e0, e1);
-				while (run)
+				uint32_t run = e0[m] & ~((e0[m] << 1) | prev);
+#pragma unroll
+				for (uint32_t t = 1; t < m; t++) run &= funnel_r(e0[m], e1[m], t);
+				cm[m] = run;
+				cand_any |= run;
+			}
+		}
+		// ---- pass 1: every candidate position in order -> largest end (then smallest motif) among the runs starting there
+		uint32_t local_max = 0;
+		{
+			uint32_t cb = cand_any, j = 0;
+			while (cb)
+			{
+				const uint32_t b = __ffs(cb) - 1;
+				cb &= cb - 1;
+				uint32_t best = 0;
+#pragma unroll
+				for (uint32_t m = 2; m <= 6; m++)
 				{
-					const uint32_t b = __ffs(run) - 1;
-					run &= run - 1;
-					// eq_m holds from b to the first zero of e64 above it; beyond the 64 positions this thread sees, walk on
-					const uint64_t stop = ~(e64 >> b);
-					uint32_t q = p0 + b + (stop ? (uint32_t)(__ffsll((long long)stop) - 1) : 64u);
-					if (q >= p0 + 64)
+					if ((cm[m] >> b) & 1)
 					{
-						q = p0 + 64;
-						while (q < lim)
+						// eq_m holds from b to the first zero above it; beyond the 64 positions this lane sees, walk on
+						const uint32_t stop_lo = ~funnel_r(e0[m], e1[m], b), stop_hi = ~(e1[m] >> b);
+						uint32_t q = p0 + 64;
+						if (stop_lo) q = p0 + b + (__ffs(stop_lo) - 1);
+						else if (stop_hi) q = p0 + b + 32 + (__ffs(stop_hi) - 1);      // (the shifted-in zeros stop it at p0 + 64 at the latest)
+						if (q >= p0 + 64)
 						{
-							const Planes x = win(q), y = win(q + m);
-							uint32_t ne = (x.lo ^ y.lo) | (x.hi ^ y.hi);
-							const uint32_t room = lim - q;
-							if (room < 32) ne |= ~low_bits(room);
-							if (ne) { q += __ffs(ne) - 1; break; }
-							q += 32;
+							const uint32_t lim = n - m;
+							q = p0 + 64;
+							while (q < lim)
+							{
+								const Planes x = win(q), y = win(q + m);
+								uint32_t ne = (x.lo ^ y.lo) | (x.hi ^ y.hi);
+								const uint32_t room = lim - q;
+								if (room < 32) ne |= ~low_bits(room);
+								if (ne) { q += __ffs(ne) - 1; break; }
+								q += 32;
+							}
+							if (q > lim) q = lim;
 						}
+						const uint32_t val = ((q + m) << 3) | (7 - m);   // larger end wins, then smaller motif
+						best = max(best, val);
 					}
-					if (q > lim) q = lim;
-					const uint32_t end = q + m;
-					const uint32_t val = (end << 3) | (7 - m);   // larger end wins, then smaller motif
-					if (!((cand_bits >> b) & 1) || val > my_cand[b]) my_cand[b] = val;
-					cand_bits |= 1u << b;
-					local_max = max(local_max, end);
 				}
+				my_cand[j++] = best;
+				local_max = max(local_max, best >> 3);
 			}
 		}
 		// ---- scan 1: exclusive prefix maximum of candidate ends
-		uint32_t tile_max;
-		const uint32_t pm_in = max(block_exclusive_max<NT>(local_max, warp_tmp, tile_max), carry_max);
-		// ---- emitted runs of this word: end beyond everything seen before
-		uint32_t emit_bits = 0;
-		LastRun my_last; my_last.m = 0; my_last.start = 0; my_last.prev_end = 0;
+		uint32_t pm_in, tile_max;
 		{
-			uint32_t running = pm_in;
-			uint32_t cb = cand_bits;
+			uint32_t inc = local_max;
+#pragma unroll
+			for (int d = 1; d < 32; d <<= 1) { const uint32_t t = __shfl_up_sync(FULL, inc, d); if (lane >= (uint32_t)d) inc = max(inc, t); }
+			uint32_t excl = __shfl_up_sync(FULL, inc, 1);
+			if (lane == 0) excl = 0;
+			tile_max = __shfl_sync(FULL, inc, 31);
+			pm_in = max(excl, carry_max);
+		}
+		// ---- pass 2: emitted runs of this word (end beyond everything seen before), kept as a compacted list at the front of
+		// my_cand, and their share of the cover masks:
+		//   ge1(p): some run covers p      <=> (maximum run end over candidates at or before p) > p
+		//   ge2(p): two runs cover p       <=> (prev_end of the latest emitted run at or before p) > p
+		uint32_t emit_bits = 0, n_emit = 0, ge1 = 0, ge2_own = 0;
+		uint32_t my_sm = 0, my_pe = 0;     // latest emitted run of this word: start | m << 29, end of the run emitted before it
+		{
+			uint32_t running = pm_in, cb = cand_any, j = 0;
 			while (cb)
 			{
-				const uint32_t b = __ffs(cb) - 1; cb &= cb - 1;
-				const uint32_t val = my_cand[b];
+				const uint32_t b = __ffs(cb) - 1;
+				cb &= cb - 1;
+				const uint32_t val = my_cand[j++];
 				const uint32_t end = val >> 3;
 				if (end > running)
 				{
+					const uint32_t from = 0xffffffffu << b;
 					emit_bits |= 1u << b;
-					my_last.start = p0 + b; my_last.prev_end = running; my_last.m = 7 - (val & 7);
+					ge1 |= from & low_bits(end - p0);
+					ge2_own = (ge2_own & ~from) | (from & low_bits_sat(running, p0));
+					my_sm = (p0 + b) | ((7 - (val & 7)) << 29);
+					my_pe = running;
+					my_cand[n_emit++] = val;
 					running = end;
 				}
 			}
 		}
-		// ---- scan 2: latest emitted run that starts before this word
-		LastRun tile_last;
-		LastRun last_in = block_exclusive_last<NT>(my_last, warp_last, tile_last);
-		if (last_in.m == 0) last_in = carry_last;
+		// ---- scan 2: latest emitted run that starts before this word (the nearest lower lane that has one, else the carry)
+		uint32_t in_sm, in_pe;
+		const uint32_t has = __ballot_sync(FULL, my_sm != 0);
+		{
+			const uint32_t below = has & lt_mask;
+			const uint32_t src = below ? 31 - __clz(below) : 0;
+			in_sm = __shfl_sync(FULL, my_sm, src);
+			in_pe = __shfl_sync(FULL, my_pe, src);
+			if (!below) { in_sm = carry_last_sm; in_pe = carry_last_pe; }
+		}
 		// ---- coverage of the 32 symbols of this word
-		//   ge1(p): some run covers p      <=> (maximum run end over candidates at or before p) > p
-		//   ge2(p): two runs cover p       <=> (prev_end of the latest emitted run at or before p) > p
 		uint32_t flags = 0, cover1 = 0;
 		bool prev_cover1 = false;
 		if (active)
 		{
 			const uint32_t nvalid = min(32u, n - p0);
 			const uint32_t valid = low_bits(nvalid);
-			const uint32_t pe_in = last_in.m ? last_in.prev_end : 0;
-			uint32_t ge1 = pm_in > p0 ? low_bits(pm_in - p0) : 0;
-			uint32_t ge2 = pe_in > p0 ? low_bits(pe_in - p0) : 0;
-			uint32_t running = pm_in;
-			uint32_t eb = emit_bits;
-			while (eb)
-			{
-				const uint32_t b = __ffs(eb) - 1; eb &= eb - 1;
-				const uint32_t end = my_cand[b] >> 3;
-				const uint32_t from = ~low_bits(b);
-				ge1 |= from & low_bits(end - p0);
-				ge2 &= ~from;
-				if (running > p0 + b) ge2 |= from & low_bits(running - p0);
-				running = end;
-			}
+			const uint32_t pe_in = in_sm ? in_pe : 0;
+			ge1 |= low_bits_sat(pm_in, p0);
+			const uint32_t first_from = emit_bits ? (0xffffffffu << (__ffs(emit_bits) - 1)) : 0u;
+			const uint32_t ge2 = (low_bits_sat(pe_in, p0) & ~first_from) | ge2_own;
 			cover1 = ge1 & ~ge2 & valid;
 			if (p0 > 0) prev_cover1 = (pm_in > p0 - 1) && !(pe_in > p0 - 1);
 			const uint32_t not1 = ~cover1;
@@ -563,8 +616,16 @@ __global__ void __launch_bounds__(NT) k_msat(SegTable seg, const uint64_t* __res
 			flags = (not1 | prev_not1 | emit_bits) & valid;
 		}
 		// ---- scan 3: index of the first code that starts in this word
-		uint32_t tile_codes;
-		const uint32_t idx = block_exclusive_sum<NT>(__popc(flags), warp_tmp, tile_codes) + carry_codes;
+		uint32_t idx, tile_codes;
+		{
+			const uint32_t v = __popc(flags);
+			uint32_t inc = v;
+#pragma unroll
+			for (int d = 1; d < 32; d <<= 1) { const uint32_t t = __shfl_up_sync(FULL, inc, d); if (lane >= (uint32_t)d) inc += t; }
+			tile_codes = __shfl_sync(FULL, inc, 31);
+			idx = carry_codes + inc - v;
+		}
+		const uint32_t base8 = carry_codes & ~7u;      // stage entry i holds code base8 + i
 		if (active)
 		{
 			// ---- single-symbol codes: every code start outside cover == 1
@@ -574,8 +635,8 @@ __global__ void __launch_bounds__(NT) k_msat(SegTable seg, const uint64_t* __res
 				const uint32_t b = __ffs(sb) - 1; sb &= sb - 1;
 				const uint32_t oi = idx + __popc(flags & low_bits(b));
 				const uint32_t sc = ((a0.lo >> b) & 1) | (((a0.hi >> b) & 1) << 1);
-				codes[out0 + oi] = (uint16_t)sc;
-				rrc[rr0 - oi] = (uint16_t)(3 - sc);
+				st_c[oi - base8] = (uint16_t)sc;
+				st_r[MSAT_STAGE - 1 - (oi - base8)] = (uint16_t)(3 - sc);
 				if (pos2) pos2[out0 + oi] = pos1 ? pos1[out0 + p0 + b] : p0 + b;
 			}
 			// ---- stretches of cover == 1 that end in this word: at a code start whose predecessor is covered once, or at n
@@ -589,33 +650,55 @@ __global__ void __launch_bounds__(NT) k_msat(SegTable seg, const uint64_t* __res
 				const uint32_t q = p0 + b;
 				const uint32_t oi = idx + __popc(flags & low_bits(b)) - 1;
 				// the latest emitted run that starts before q, and the end of the run emitted before it
-				LastRun cur = last_in;
+				uint32_t cur_start = in_sm & 0x1fffffffu, cur_m = in_sm >> 29, cur_pe = in_pe;
 				const uint32_t below = emit_bits & low_bits(b);
 				if (below)
 				{
-					const uint32_t bb = 31 - __clz(below);
-					const uint32_t below2 = below & low_bits(bb);
-					cur.start = p0 + bb;
-					cur.m = 7 - (my_cand[bb] & 7);
-					cur.prev_end = below2 ? (my_cand[31 - __clz(below2)] >> 3) : pm_in;
+					const uint32_t ie = __popc(below) - 1;
+					const uint32_t val = my_cand[ie];
+					cur_start = p0 + (31 - __clz(below));
+					cur_m = 7 - (val & 7);
+					cur_pe = ie ? (my_cand[ie - 1] >> 3) : pm_in;
 				}
-				// symbols [ps, q) are covered by `cur` alone: one code with its motif length (clamped to the stretch)
-				const uint32_t ps = max(cur.start, cur.prev_end);
+				// symbols [ps, q) are covered by that run alone: one code with its motif length (clamped to the stretch)
+				const uint32_t ps = max(cur_start, cur_pe);
 				const uint32_t slen = q - ps;
-				const uint32_t m = min(cur.m, slen);
+				const uint32_t m = min(cur_m, slen);
 				uint32_t code, rc_code;
 				stretch_codes(win(ps), m, slen, code, rc_code);
-				codes[out0 + oi] = (uint16_t)code;
-				rrc[rr0 - oi] = (uint16_t)rc_code;
+				if (oi >= base8) { st_c[oi - base8] = (uint16_t)code; st_r[MSAT_STAGE - 1 - (oi - base8)] = (uint16_t)rc_code; }
+				else { codes_g[oi] = (uint16_t)code; *(rrc_g - oi) = (uint16_t)rc_code; }     // its slot left with an earlier tile
 				if (pos2) pos2[out0 + oi] = pos1 ? pos1[out0 + ps] : ps;
 			}
 		}
+		__syncwarp();
+		// ---- the finished groups of 8 codes leave as 128-bit stores; the unfinished group moves to the front of the stage
+		{
+			const uint32_t filled = (carry_codes - base8) + tile_codes;
+			const bool last = tile + MSAT_TILE >= n;
+			const uint32_t n_groups = last ? (filled + 7) / 8 : filled / 8;
+			for (uint32_t gq = lane; gq < n_groups; gq += 32)
+			{
+				*(uint4*)(codes_g + base8 + 8 * gq) = *(const uint4*)(st_c + 8 * gq);
+				*(uint4*)(rrc_g - (base8 + 8 * gq + 7)) = *(const uint4*)(st_r + (MSAT_STAGE - 8 - 8 * gq));
+			}
+			const uint32_t keep = last ? 0 : filled - 8 * n_groups;
+			uint16_t kc = 0, kr = 0;
+			if (lane < keep) { kc = st_c[8 * n_groups + lane]; kr = st_r[MSAT_STAGE - 1 - (8 * n_groups + lane)]; }
+			__syncwarp();
+			if (lane < keep) { st_c[lane] = kc; st_r[MSAT_STAGE - 1 - lane] = kr; }
+		}
 		carry_max = max(carry_max, tile_max);
-		if (tile_last.m) carry_last = tile_last;
+		if (has)
+		{
+			const uint32_t top = 31 - __clz(has);
+			carry_last_sm = __shfl_sync(FULL, my_sm, top);
+			carry_last_pe = __shfl_sync(FULL, my_pe, top);
+		}
 		carry_codes += tile_codes;
-		__syncthreads();    // the staged words are replaced at the top of the next tile
+		__syncwarp();    // the staged words are replaced at the top of the next tile
 	}
-	if (threadIdx.x == 0)
+	if (lane == 0)
 	{
 		seg_c2[g] = carry_codes;
 		if (pos2) pos2[out0 + carry_codes] = pos1 ? pos1[out0 + n] : n;

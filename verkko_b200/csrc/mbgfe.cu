@@ -619,7 +619,7 @@ uint32_t launch_front(mbgfe* h, uint32_t g0, uint32_t cnt, bool timed)
 		h->prm.error_masking == MBGFE_MASK_NO ? 1 : 0);
 	if (timed) tick(h, 4);
 	if (h->msat)
-		MBGFE_LAUNCH(k_msat<NT_MSAT>, cnt, NT_MSAT, 0, h->stream, st, h->d_sym.as<uint64_t>(), c1, h->d_codes.as<uint16_t>(), h->d_rrc.as<uint16_t>(),
+		MBGFE_LAUNCH(k_msat, (cnt + MSAT_WARPS - 1) / MSAT_WARPS, MSAT_WARPS * 32, 0, h->stream, st, h->d_sym.as<uint64_t>(), c1, h->d_codes.as<uint16_t>(), h->d_rrc.as<uint16_t>(),
 			c2, (const uint32_t*)pos1, pos2, h->max_motif);
 	else
 		MBGFE_LAUNCH(k_unpack_symbols<NT_MSAT>, cnt, NT_MSAT, 0, h->stream, st, h->d_sym.as<uint64_t>(), c1, h->d_codes.as<uint16_t>(),
