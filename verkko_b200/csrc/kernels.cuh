@@ -1092,82 +1092,137 @@ struct Murmur
 // K3b2: 128-bit k-mer hash (MBG/MBGCommon.cpp:25-35): low 64 bits = Murmur over the first (k+1)/2 codes of the k-mer,
 // high 64 bits = Murmur over the first (k+1)/2 codes of its reverse complement.  `rrc` holds every segment's
 // complemented codes in reverse order (written by K2), so both halves are the same forward walk over a code array.
-// A warp owns 32 (instance, half) pairs and alternates two phases over chunks of 32 blocks of 8 bytes:
-//   mix    for each of its 32 pairs in turn, the 32 lanes load 32 consecutive blocks (coalesced) and apply the part
-//          of Murmur that does not depend on the running hash (two of its three multiplications); the results go
-//          to shared memory, transposed
-//   chain  lane j folds the 32 premixed blocks of pair j into its running hash (h = (h ^ f) * m), conflict-free
-// so that no global load is scattered and the serial part of the hash is 5 instructions per block.
-// Algorithmic bytes: 2 read per code (codes of a read stay cache resident across the ~k/50 k-mers that cover them,
-// both directions) + 16 written per instance.
-// The instance range [range[0], range[1]) is read from device memory (two entries of sel_begin), and CTAs stride over
-// it, so the pipelined run can launch the kernel for a piece whose instance count the host does not know yet.
-constexpr int HASH_WARPS = 4;
-__global__ void __launch_bounds__(HASH_WARPS * 32) k_kmer_hash(const uint64_t* __restrict__ seg_out_base, const uint16_t* __restrict__ codes,
-	const uint16_t* __restrict__ rrc, const uint32_t* __restrict__ inst_pos, const uint32_t* __restrict__ inst_seg, const uint64_t* __restrict__ range_begin,
-	const uint64_t* __restrict__ range_end, uint64_t inst_cap, uint64_t* __restrict__ inst_hash, uint32_t k)
+//
+// Murmur64A is h = (h ^ f(block)) * M with f (two of the three multiplications) independent of h, and the selected
+// k-mers of a read overlap heavily (one every ~w/2 codes, each (k+1)/2 codes long), so f is shared: one CTA per segment
+// walks the code array (and, in step, the reverse-complement array) in tiles of HASH_TILE offsets and alternates
+//   premix  f of the 8-byte block at EVERY code offset of the tile -> shared memory (all four alignments at once;
+//           coalesced, no divergence, each f serves every k-mer of that alignment that covers it)
+//   chain   one thread per k-mer (and direction) whose blocks fall into the tile folds them into its running hash:
+//           one shared-memory load, one xor and one multiplication per block
+// A k-mer that continues into the next tile parks its running hash in its (not yet final) result slot.  The k-mers of a
+// tile are found by binary search in the segment's sorted position list (kept in shared memory when it fits).
+// Algorithmic bytes: 2 read per code and direction + 16 written per instance.
+constexpr int HASH_NT = 256;
+constexpr uint32_t HASH_TILE = 2048, HASH_POS_CAP = 1024;
+
+__device__ __forceinline__ uint32_t lower_bound_u32(const uint32_t* p, uint32_t n, int64_t key)
 {
-	__shared__ uint64_t premixed[HASH_WARPS][32][33];
-	const uint32_t lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
-	const uint64_t first = *range_begin, last = min(*range_end, inst_cap);
-	const uint64_t n_pairs = last > first ? 2 * (last - first) : 0;
-	const uint32_t half = (k + 1) / 2;
-	const uint32_t n_blocks = half / 4, rem = half & 3;
-	for (uint64_t t0 = (uint64_t)blockIdx.x * (HASH_WARPS * 32); t0 < n_pairs; t0 += (uint64_t)gridDim.x * (HASH_WARPS * 32))
+	// first index with p[i] >= key (p ascending)
+	uint32_t lo = 0, hi = n;
+	while (lo < hi)
 	{
-		const uint64_t t = t0 + wid * 32 + lane;
-		const bool valid = t < n_pairs;
-		const uint64_t i = first + (t >> 1);
-		const uint16_t* my = codes;        // lanes past the end walk the start of the array and discard the result
-		if (valid)
+		const uint32_t mid = (lo + hi) >> 1;
+		if ((int64_t)p[mid] < key) lo = mid + 1; else hi = mid;
+	}
+	return lo;
+}
+
+__global__ void __launch_bounds__(HASH_NT) k_kmer_hash(const uint64_t* __restrict__ seg_out_base, const uint16_t* __restrict__ codes, const uint16_t* __restrict__ rrc,
+	const uint32_t* __restrict__ inst_pos, const uint64_t* __restrict__ sel_begin, uint64_t inst_cap, uint64_t* __restrict__ inst_hash, uint32_t k)
+{
+	// seg_out_base and sel_begin are offset to the first segment of the launch; blockIdx.x = segment within it
+	__shared__ uint64_t s_f[2][HASH_TILE];
+	__align__(16) __shared__ uint16_t s_c[2][HASH_TILE + 8];
+	__shared__ uint32_t s_pos[HASH_POS_CAP];
+	__shared__ uint32_t s_range[4];
+	const uint32_t g = blockIdx.x;
+	const uint64_t begin = sel_begin[g], end = sel_begin[g + 1];
+	if (end <= begin || end > inst_cap) return;
+	const uint32_t n_sel = (uint32_t)(end - begin);
+	const uint64_t ob = seg_out_base[g];
+	const uint32_t cap = (uint32_t)(seg_out_base[g + 1] - ob);
+	const uint16_t* __restrict__ arr[2] = { codes + ob, rrc + ob };     // forward codes; reverse-complement codes (k-mer at pos starts at cap - k - pos)
+	const uint32_t* __restrict__ gpos = inst_pos + begin;
+	uint64_t* __restrict__ out = inst_hash + 2 * begin;
+	const uint32_t half = (k + 1) / 2;
+	const uint32_t nb = half / 4, rem = half & 3;
+	const uint32_t reach = nb ? 4 * (nb - 1) : 0;          // offset of a k-mer's last whole block, from its start
+	const bool pos_in_smem = n_sel <= HASH_POS_CAP;
+	if (pos_in_smem) for (uint32_t i = threadIdx.x; i < n_sel; i += HASH_NT) s_pos[i] = gpos[i];
+	const uint32_t* pos = pos_in_smem ? s_pos : gpos;
+	const uint32_t pos_first = gpos[0], pos_last = gpos[n_sel - 1];
+	// both directions cover the same number of offsets; their first tiles start at the (8-aligned) first block of either
+	const uint32_t t0f = pos_first & ~7u, t0r = (cap - k - pos_last) & ~7u;
+	const uint32_t span = (pos_last - pos_first) + reach + 4 + 8;
+	uint64_t h_init;
+	{ Murmur mm; mm.init((uint64_t)half * 2); h_init = mm.h; }
+	__syncthreads();
+	for (uint32_t toff = 0; toff < span; toff += HASH_TILE)
+	{
+		const uint32_t T0[2] = { t0f + toff, t0r + toff };
+		// ---- stage the codes of both tiles (8 extra for the blocks that start in the last offsets)
+		for (uint32_t i = threadIdx.x; i < 2 * (HASH_TILE / 8 + 1); i += HASH_NT)
 		{
-			const uint32_t g = inst_seg[i], pos = inst_pos[i];
-			const uint64_t ob = seg_out_base[g];
-			my = (t & 1) ? rrc + (seg_out_base[g + 1] - k - pos) : codes + ob + pos;
+			const uint32_t d = i >= HASH_TILE / 8 + 1 ? 1 : 0, q = i - d * (HASH_TILE / 8 + 1);
+			const uint32_t o = T0[d] + 8 * q;
+			uint4 v = make_uint4(0, 0, 0, 0);
+			if (o < cap) v = __ldg((const uint4*)(arr[d] + o));
+			*(uint4*)(s_c[d] + 8 * q) = v;
 		}
-		const uint64_t my_addr = (uint64_t)my;
-		Murmur mm;
-		mm.init((uint64_t)half * 2);
-		for (uint32_t c0 = 0; c0 < n_blocks; c0 += 32)
+		// ---- warp 0 meanwhile finds the k-mers of the tile: forward starts in [T0f - reach, T0f + TILE), reverse starts
+		// cap - k - pos in [T0r - reach, T0r + TILE)
+		if (threadIdx.x < 4)
 		{
-			const uint32_t nb = min(32u, n_blocks - c0);
-			// four pairs per round: all twelve loads are issued before the first one is consumed
-			for (uint32_t j0 = 0; j0 < 32; j0 += 4)
+			int64_t key;
+			switch (threadIdx.x)
 			{
-				uint32_t w0[4], w1[4], w2[4], sh[4];
-#pragma unroll
-				for (int u = 0; u < 4; u++)
-				{
-					const uint64_t a = __shfl_sync(FULL, my_addr, j0 + u) + 8ull * (c0 + lane);
-					const uint32_t* __restrict__ p = (const uint32_t*)(a & ~3ull);
-					sh[u] = ((uint32_t)a & 2) * 8;          // 0 or 16: the block starts in the middle of a 32-bit word
-					w0[u] = 0; w1[u] = 0; w2[u] = 0;
-					if (lane < nb) { w0[u] = __ldg(p); w1[u] = __ldg(p + 1); w2[u] = __ldg(p + 2); }
-				}
-#pragma unroll
-				for (int u = 0; u < 4; u++)
-				{
-#ifdef MBGFE_EMU_BUILD
-					const uint32_t lo = sh[u] ? (w0[u] >> 16) | (w1[u] << 16) : w0[u], hi = sh[u] ? (w1[u] >> 16) | (w2[u] << 16) : w1[u];
-#else
-					const uint32_t lo = __funnelshift_r(w0[u], w1[u], sh[u]), hi = __funnelshift_r(w1[u], w2[u], sh[u]);
-#endif
-					uint64_t wd = u64_of(lo, hi);
-					wd *= Murmur::MUL; wd ^= wd >> 47; wd *= Murmur::MUL;
-					if (lane < nb) premixed[wid][j0 + u][lane] = wd;
-				}
+				case 0: key = (int64_t)T0[0] - reach; break;
+				case 1: key = (int64_t)T0[0] + HASH_TILE; break;
+				case 2: key = (int64_t)cap - k - (int64_t)T0[1] - HASH_TILE + 1; break;       // pos > cap - k - T0r - TILE
+				default: key = (int64_t)cap - k - (int64_t)T0[1] + reach + 1; break;          // pos <= cap - k - T0r + reach
 			}
-			__syncwarp();
-			for (uint32_t b = 0; b < nb; b++) { mm.h ^= premixed[wid][lane][b]; mm.h *= Murmur::MUL; }
-			__syncwarp();
+			s_range[threadIdx.x] = lower_bound_u32(pos, n_sel, key);
 		}
-		if (rem)
+		__syncthreads();
+		// ---- premix: f(block) for every offset of both tiles
+#pragma unroll 4
+		for (uint32_t i = threadIdx.x; i < 2 * HASH_TILE; i += HASH_NT)
 		{
-			uint64_t wd = 0;
-			for (uint32_t j = 0; j < rem; j++) wd |= (uint64_t)my[4 * n_blocks + j] << (16 * j);
-			mm.tail(wd);
+			const uint32_t d = i / HASH_TILE, o = i % HASH_TILE;
+			const uint32_t* cw = (const uint32_t*)s_c[d] + (o >> 1);
+			const uint32_t w0 = cw[0], w1 = cw[1], w2 = cw[2];
+#ifdef MBGFE_EMU_BUILD
+			const uint32_t lo = (o & 1) ? (w0 >> 16) | (w1 << 16) : w0, hi = (o & 1) ? (w1 >> 16) | (w2 << 16) : w1;
+#else
+			const uint32_t sh = (o & 1) * 16;
+			const uint32_t lo = __funnelshift_r(w0, w1, sh), hi = __funnelshift_r(w1, w2, sh);
+#endif
+			uint64_t wd = u64_of(lo, hi);
+			wd *= Murmur::MUL; wd ^= wd >> 47; wd *= Murmur::MUL;
+			s_f[d][o] = wd;
 		}
-		if (valid) inst_hash[2 * first + t] = mm.finish();
+		__syncthreads();
+		// ---- chain: the tile's share of every k-mer that touches it
+		const uint32_t fa = s_range[0], fb = s_range[1], ra = s_range[2], rb = s_range[3];
+		const uint32_t nf = fb > fa ? fb - fa : 0, nr = rb > ra ? rb - ra : 0;
+		for (uint32_t it = threadIdx.x; it < nf + nr; it += HASH_NT)
+		{
+			const uint32_t d = it >= nf ? 1 : 0;
+			const uint32_t i = d ? ra + (it - nf) : fa + it;
+			const uint32_t st = d ? cap - k - pos[i] : pos[i];
+			const int64_t rel = (int64_t)st - (int64_t)T0[d];                   // start relative to the tile
+			const uint32_t t_lo = rel >= 0 ? 0u : (uint32_t)((-rel + 3) >> 2);
+			const int64_t room = (int64_t)HASH_TILE - rel;                       // offsets of the tile from the start on
+			const uint32_t t_hi = (uint32_t)min((int64_t)nb, (room + 3) >> 2);
+			if (t_lo >= t_hi && !(nb == 0 && rel >= 0)) continue;
+			uint64_t hcur = t_lo == 0 ? h_init : out[2 * i + d];
+			const uint64_t* f = s_f[d] + rel;
+			for (uint32_t t = t_lo; t < t_hi; t++) { hcur ^= f[4 * (int64_t)t]; hcur *= Murmur::MUL; }
+			if (t_hi == nb)
+			{
+				Murmur mm; mm.h = hcur;
+				if (rem)
+				{
+					uint64_t wd = 0;
+					for (uint32_t j = 0; j < rem; j++) wd |= (uint64_t)arr[d][st + 4 * nb + j] << (16 * j);
+					mm.tail(wd);
+				}
+				hcur = mm.finish();
+			}
+			out[2 * i + d] = hcur;
+		}
+		__syncthreads();
 	}
 }
 

@@ -685,9 +685,8 @@ void launch_list_hash(mbgfe* h, uint32_t g0, uint32_t g1, uint64_t n_hint, uint3
 	const uint64_t* sb = h->d_sel_begin.as<uint64_t>();
 	MBGFE_LAUNCH(k_list_selected<NT_LIST>, g1 - g0, NT_LIST, 0, h->stream, st, g0, h->d_selmask.as<uint32_t>(), h->d_seg_c2.as<uint32_t>() + g0, h->d_seg_nsel.as<uint32_t>() + g0,
 		sb + g0, h->d_inst_pos.as<uint32_t>(), h->d_inst_seg.as<uint32_t>(), h->d_inst_flag.as<uint8_t>(), k, h->inst_cap, ctr + CTR_OVERFLOW);
-	const unsigned hash_grid = n_hint ? (unsigned)((2 * n_hint + HASH_WARPS * 32 - 1) / (HASH_WARPS * 32)) : (unsigned)h->sm_count * 6;
-	MBGFE_LAUNCH(k_kmer_hash, hash_grid, HASH_WARPS * 32, 0, h->stream, h->d_seg_out.as<uint64_t>(), h->d_codes.as<uint16_t>(), h->d_rrc.as<uint16_t>(), h->d_inst_pos.as<uint32_t>(),
-		h->d_inst_seg.as<uint32_t>(), sb + g0, sb + g1, h->inst_cap, h->d_inst_hash.as<uint64_t>(), k);
+	MBGFE_LAUNCH(k_kmer_hash, g1 - g0, HASH_NT, 0, h->stream, h->d_seg_out.as<uint64_t>() + g0, h->d_codes.as<uint16_t>(), h->d_rrc.as<uint16_t>(), h->d_inst_pos.as<uint32_t>(),
+		sb + g0, h->inst_cap, h->d_inst_hash.as<uint64_t>(), k);
 	const unsigned pal_grid = n_hint ? (unsigned)((n_hint + 255) / 256) : (unsigned)h->sm_count * 4;
 	MBGFE_LAUNCH(k_find_palindromes, pal_grid, 256, 0, h->stream, h->d_inst_hash.as<uint64_t>(), sb + g0, sb + g1, h->inst_cap, ctr + CTR_PALINDROME, h->d_pal_list.as<uint64_t>(), PAL_CAP);
 	launches += 3;
@@ -1416,9 +1415,8 @@ int mbgfe_kat_kmer_hash(mbgfe* h, const uint16_t* codes, uint32_t k, mbgfe_hash1
 	const uint64_t range[2] = { 0, 1 };
 	cudaMemcpyAsync(d_misc.as<char>() + 64, range, 16, cudaMemcpyHostToDevice, h->stream);   // instance range [0, 1)
 	MBGFE_LAUNCH(k_revcomp_codes, (k + 255) / 256, 256, 0, h->stream, d_codes.as<uint16_t>(), k, h->tab_comp.as<uint16_t>(), d_rrc.as<uint16_t>());
-	MBGFE_LAUNCH(k_kmer_hash, 1, HASH_WARPS * 32, 0, h->stream, (const uint64_t*)d_misc.p, d_codes.as<uint16_t>(), d_rrc.as<uint16_t>(), (const uint32_t*)(d_misc.as<char>() + 16),
-		(const uint32_t*)(d_misc.as<char>() + 20), (const uint64_t*)(d_misc.as<char>() + 64), (const uint64_t*)(d_misc.as<char>() + 72), (uint64_t)1,
-		(uint64_t*)(d_misc.as<char>() + 32), k);
+	MBGFE_LAUNCH(k_kmer_hash, 1, HASH_NT, 0, h->stream, (const uint64_t*)d_misc.p, d_codes.as<uint16_t>(), d_rrc.as<uint16_t>(), (const uint32_t*)(d_misc.as<char>() + 16),
+		(const uint64_t*)(d_misc.as<char>() + 64), (uint64_t)1, (uint64_t*)(d_misc.as<char>() + 32), k);
 	cudaStreamSynchronize(h->stream);
 	uint64_t res[2] = { 0, 0 };
 	cudaError_t e = cudaMemcpy(res, d_misc.as<char>() + 32, 16, cudaMemcpyDeviceToHost);
