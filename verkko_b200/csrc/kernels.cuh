@@ -1175,22 +1175,30 @@ __global__ void __launch_bounds__(HASH_NT) k_kmer_hash(const uint64_t* __restric
 			s_range[threadIdx.x] = lower_bound_u32(pos, n_sel, key);
 		}
 		__syncthreads();
-		// ---- premix: f(block) for every offset of both tiles
-#pragma unroll 4
-		for (uint32_t i = threadIdx.x; i < 2 * HASH_TILE; i += HASH_NT)
+		// ---- premix: f(block) for every offset of both tiles that a k-mer can still need.  A thread takes two
+		// neighbouring offsets: the same three words give the even block as they are and the odd one shifted by 16 bits
+		const uint32_t need = min(HASH_TILE, span - toff);
+#pragma unroll
+		for (uint32_t d = 0; d < 2; d++)
 		{
-			const uint32_t d = i / HASH_TILE, o = i % HASH_TILE;
-			const uint32_t* cw = (const uint32_t*)s_c[d] + (o >> 1);
-			const uint32_t w0 = cw[0], w1 = cw[1], w2 = cw[2];
+			const uint32_t* cw = (const uint32_t*)s_c[d];
+			uint64_t* fo = s_f[d];
+#pragma unroll 2
+			for (uint32_t pr = threadIdx.x; 2 * pr < need; pr += HASH_NT)
+			{
+				const uint32_t w0 = cw[pr], w1 = cw[pr + 1], w2 = cw[pr + 2];
 #ifdef MBGFE_EMU_BUILD
-			const uint32_t lo = (o & 1) ? (w0 >> 16) | (w1 << 16) : w0, hi = (o & 1) ? (w1 >> 16) | (w2 << 16) : w1;
+				const uint32_t lo1 = (w0 >> 16) | (w1 << 16), hi1 = (w1 >> 16) | (w2 << 16);
 #else
-			const uint32_t sh = (o & 1) * 16;
-			const uint32_t lo = __funnelshift_r(w0, w1, sh), hi = __funnelshift_r(w1, w2, sh);
+				const uint32_t lo1 = __funnelshift_r(w0, w1, 16), hi1 = __funnelshift_r(w1, w2, 16);
 #endif
-			uint64_t wd = u64_of(lo, hi);
-			wd *= Murmur::MUL; wd ^= wd >> 47; wd *= Murmur::MUL;
-			s_f[d][o] = wd;
+				uint64_t wa = u64_of(w0, w1), wb = u64_of(lo1, hi1);
+				wa *= Murmur::MUL; wb *= Murmur::MUL;
+				wa ^= wa >> 47; wb ^= wb >> 47;
+				wa *= Murmur::MUL; wb *= Murmur::MUL;
+				ulonglong2 v; v.x = wa; v.y = wb;
+				*(ulonglong2*)(fo + 2 * pr) = v;
+			}
 		}
 		__syncthreads();
 		// ---- chain: the tile's share of every k-mer that touches it
@@ -1205,10 +1213,12 @@ __global__ void __launch_bounds__(HASH_NT) k_kmer_hash(const uint64_t* __restric
 			const uint32_t t_lo = rel >= 0 ? 0u : (uint32_t)((-rel + 3) >> 2);
 			const int64_t room = (int64_t)HASH_TILE - rel;                       // offsets of the tile from the start on
 			const uint32_t t_hi = (uint32_t)min((int64_t)nb, (room + 3) >> 2);
-			if (t_lo >= t_hi && !(nb == 0 && rel >= 0)) continue;
+			if (t_lo >= t_hi) continue;
 			uint64_t hcur = t_lo == 0 ? h_init : out[2 * i + d];
-			const uint64_t* f = s_f[d] + rel;
-			for (uint32_t t = t_lo; t < t_hi; t++) { hcur ^= f[4 * (int64_t)t]; hcur *= Murmur::MUL; }
+			const uint64_t* f = s_f[d] + (rel + 4 * (int64_t)t_lo);
+			const uint32_t cnt = t_hi - t_lo;
+#pragma unroll 4
+			for (uint32_t t = 0; t < cnt; t++) { hcur ^= f[4 * t]; hcur *= Murmur::MUL; }
 			if (t_hi == nb)
 			{
 				Murmur mm; mm.h = hcur;
