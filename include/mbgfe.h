@@ -135,6 +135,14 @@ int mbgfe_add_reads(mbgfe* h, const char* bases, const uint64_t* offsets, uint64
 int mbgfe_add_file(mbgfe* h, const char* path);
 const char* mbgfe_read_name(const mbgfe* h, uint64_t read_idx);
 
+/* hpc variants for pass 3 of runMBG (MBG/MBG.cpp:1564-1570): replaces ReadpartIterator::addHpcVariants
+ * (MBG/ReadHelper.cpp:63-70), all entries in one call -- entry e == addHpcVariants(hashes[e], offsets[e],
+ * lengths[len_begin[e] .. len_begin[e+1])).  From then on every selected k-mer whose forward or swapped hash is
+ * registered gets the hash of its clustered run lengths XORed in (MBG/ReadHelper.h:680-737) before MBGFE_HASHES is
+ * reported and before it is counted.  n_entries == 0 clears the set.  Survives mbgfe_reset(). */
+int mbgfe_set_variants(mbgfe* h, const mbgfe_hash128* hashes, const uint32_t* offsets, const uint64_t* len_begin,
+                       const uint32_t* lengths, uint64_t n_entries);
+
 /* Forget reads and results, keep parameters and device buffers. */
 int mbgfe_reset(mbgfe* h);
 

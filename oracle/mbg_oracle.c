@@ -412,6 +412,13 @@ struct orc {
 	vec parts, codes, poses, positions, hashes;
 	vec node_hash, node_cov, node_tip, edges;
 	uint64_t total_selected;
+	/* hpc variants (ReadpartIterator::hpcVariants, MBG/ReadHelper.h:250): entries grouped by hash, pairs sorted by
+	 * offset, lengths sorted (what addHpcVariants leaves, MBG/ReadHelper.cpp:63-70) */
+	uint64_t n_var;
+	uint64_t* var_hash;      /* lo, hi per entry, entries sorted by (hi, lo, offset) */
+	uint32_t* var_offset;
+	uint64_t* var_len_begin; /* n_var + 1 */
+	uint32_t* var_len;
 };
 
 orc* orc_create(int mode, uint32_t k, uint32_t w)
@@ -429,6 +436,7 @@ void orc_free(orc* o)
 	if (!o) return;
 	free(o->parts.p); free(o->codes.p); free(o->poses.p); free(o->positions.p); free(o->hashes.p);
 	free(o->node_hash.p); free(o->node_cov.p); free(o->node_tip.p); free(o->edges.p);
+	free(o->var_hash); free(o->var_offset); free(o->var_len_begin); free(o->var_len);
 	free(o);
 }
 
@@ -442,6 +450,119 @@ static int base_code(char c)
 		case 'T': case 't': return 3;
 	}
 	return -1;
+}
+
+/* ---- hpc variants (pass 3 of runMBG): MBG/ReadHelper.h:680-737, MBG/MBGCommon.h:33-45, MBG/ReadHelper.cpp:63-70 */
+
+typedef struct { uint64_t lo, hi; uint32_t offset; uint64_t idx; } var_key;
+static int cmp_var_key(const void* a, const void* b)
+{
+	const var_key* x = (const var_key*)a; const var_key* y = (const var_key*)b;
+	if (x->hi != y->hi) return x->hi < y->hi ? -1 : 1;
+	if (x->lo != y->lo) return x->lo < y->lo ? -1 : 1;
+	if (x->offset != y->offset) return x->offset < y->offset ? -1 : 1;
+	return x->idx < y->idx ? -1 : x->idx > y->idx;
+}
+static int cmp_u32(const void* a, const void* b) { uint32_t x = *(const uint32_t*)a, y = *(const uint32_t*)b; return x < y ? -1 : x > y; }
+
+/* entry e == one addHpcVariants(hash e, offsets[e], lengths[len_begin[e] .. len_begin[e+1])) call */
+void orc_set_variants(orc* o, const uint64_t* hashes_lo_hi, const uint32_t* offsets, const uint64_t* len_begin, const uint32_t* lengths, uint64_t n)
+{
+	free(o->var_hash); free(o->var_offset); free(o->var_len_begin); free(o->var_len);
+	o->n_var = n;
+	o->var_hash = (uint64_t*)malloc((n + 1) * 16); o->var_offset = (uint32_t*)malloc((n + 1) * 4);
+	o->var_len_begin = (uint64_t*)malloc((n + 1) * 8); o->var_len = (uint32_t*)malloc((len_begin[n] + 1) * 4);
+	var_key* keys = (var_key*)malloc((n + 1) * sizeof(var_key));
+	for (uint64_t e = 0; e < n; e++) { keys[e].lo = hashes_lo_hi[2 * e]; keys[e].hi = hashes_lo_hi[2 * e + 1]; keys[e].offset = offsets[e]; keys[e].idx = e; }
+	qsort(keys, n, sizeof(var_key), cmp_var_key);
+	uint64_t at = 0;
+	for (uint64_t e = 0; e < n; e++)
+	{
+		const uint64_t src = keys[e].idx, cnt = len_begin[src + 1] - len_begin[src];
+		o->var_hash[2 * e] = keys[e].lo; o->var_hash[2 * e + 1] = keys[e].hi; o->var_offset[e] = keys[e].offset;
+		o->var_len_begin[e] = at;
+		memcpy(o->var_len + at, lengths + len_begin[src], cnt * 4);
+		qsort(o->var_len + at, cnt, 4, cmp_u32);
+		at += cnt;
+	}
+	o->var_len_begin[n] = at;
+	free(keys);
+}
+
+/* first entry with hash >= (lo, hi); entries of one hash are contiguous */
+static uint64_t var_lower_bound(const orc* o, uint64_t lo, uint64_t hi)
+{
+	uint64_t a = 0, b = o->n_var;
+	while (a < b)
+	{
+		uint64_t m = (a + b) / 2;
+		uint64_t mlo = o->var_hash[2 * m], mhi = o->var_hash[2 * m + 1];
+		if (mhi < hi || (mhi == hi && mlo < lo)) a = m + 1; else b = m;
+	}
+	return a;
+}
+
+/* std::hash<const std::vector<size_t>&> (MBG/MBGCommon.h:33-45); std::hash<size_t> is the identity in libstdc++ */
+static uint64_t var_vec_hash_step(uint64_t h, uint64_t x) { h ^= x; return (h << 3) + (h >> 61); }
+
+/* the XOR perturbation of one selected k-mer at part position `pos` (MBG/ReadHelper.h:684-730) */
+static void apply_variants(const orc* o, const uint32_t* poses, uint32_t pos, uint64_t* lo, uint64_t* hi)
+{
+	if (o->n_var == 0) return;
+	const uint32_t k = o->k;
+	uint64_t first = 0, second = 0;
+	uint64_t e = var_lower_bound(o, *lo, *hi);
+	if (e < o->n_var && o->var_hash[2 * e] == *lo && o->var_hash[2 * e + 1] == *hi)
+	{
+		/* forward: first = offsets <= k/2 in ascending order, second = offsets >= k/2 reversed */
+		uint64_t end = e;
+		while (end < o->n_var && o->var_hash[2 * end] == *lo && o->var_hash[2 * end + 1] == *hi) end++;
+		for (uint64_t i = e; i < end; i++)
+		{
+			uint32_t off = o->var_offset[i];
+			if (off > k / 2) continue;
+			uint32_t here = poses[pos + off + 1] - poses[pos + off];
+			const uint32_t* l = o->var_len + o->var_len_begin[i]; uint64_t nl = o->var_len_begin[i + 1] - o->var_len_begin[i];
+			uint64_t j = 0; while (j + 1 < nl && l[j] < here) j++;
+			first = var_vec_hash_step(first, l[j]);
+		}
+		for (uint64_t i = end; i-- > e; )
+		{
+			uint32_t off = o->var_offset[i];
+			if (off < k / 2) continue;
+			uint32_t here = poses[pos + off + 1] - poses[pos + off];
+			const uint32_t* l = o->var_len + o->var_len_begin[i]; uint64_t nl = o->var_len_begin[i + 1] - o->var_len_begin[i];
+			uint64_t j = 0; while (j + 1 < nl && l[j] < here) j++;
+			second = var_vec_hash_step(second, l[j]);
+		}
+	}
+	else
+	{
+		/* the map holds the reverse complement: same walk with mirrored offsets and swapped roles */
+		e = var_lower_bound(o, *hi, *lo);
+		if (!(e < o->n_var && o->var_hash[2 * e] == *hi && o->var_hash[2 * e + 1] == *lo)) return;
+		uint64_t end = e;
+		while (end < o->n_var && o->var_hash[2 * end] == *hi && o->var_hash[2 * end + 1] == *lo) end++;
+		for (uint64_t i = end; i-- > e; )
+		{
+			uint32_t off = o->var_offset[i];
+			if (off < k / 2) continue;
+			uint32_t here = poses[pos + k - off] - poses[pos + k - off - 1];
+			const uint32_t* l = o->var_len + o->var_len_begin[i]; uint64_t nl = o->var_len_begin[i + 1] - o->var_len_begin[i];
+			uint64_t j = 0; while (j + 1 < nl && l[j] < here) j++;
+			first = var_vec_hash_step(first, l[j]);
+		}
+		for (uint64_t i = e; i < end; i++)
+		{
+			uint32_t off = o->var_offset[i];
+			if (off > k / 2) continue;
+			uint32_t here = poses[pos + k - off] - poses[pos + k - off - 1];
+			const uint32_t* l = o->var_len + o->var_len_begin[i]; uint64_t nl = o->var_len_begin[i + 1] - o->var_len_begin[i];
+			uint64_t j = 0; while (j + 1 < nl && l[j] < here) j++;
+			second = var_vec_hash_step(second, l[j]);
+		}
+	}
+	*lo ^= first; *hi ^= second;
 }
 
 /* k-mer selection + hashing + palindrome rule for one part (MBG/ReadHelper.h:740-799, 1075-1102) */
@@ -472,6 +593,7 @@ static int hash_part(orc* o, orc_part* part, const uint16_t* codes)
 			break;
 		}
 		push_u32(&o->positions, cp[i]);
+		apply_variants(o, (const uint32_t*)o->poses.p + part->pose_begin, cp[i], &lo, &hi);
 		uint64_t* h = (uint64_t*)vec_push(&o->hashes);
 		h[0] = lo; h[1] = hi;
 		part->n_sel++;

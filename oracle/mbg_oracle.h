@@ -31,6 +31,9 @@ void orc_free(orc* o);
 int orc_add_read(orc* o, const char* seq, uint64_t len);
 int orc_add_reads(orc* o, const char* bases, const uint64_t* offsets, uint64_t n_reads);
 void orc_build_table(orc* o);
+/* hpc variants of pass 3 (MBG/ReadHelper.h:680-737): entry e == one ReadpartIterator::addHpcVariants(hash e, offsets[e],
+ * lengths[len_begin[e] .. len_begin[e+1])) call; call before orc_add_read(s).  hashes: lo, hi per entry */
+void orc_set_variants(orc* o, const uint64_t* hashes_lo_hi, const uint32_t* offsets, const uint64_t* len_begin, const uint32_t* lengths, uint64_t n);
 /* what: 0 parts 1 codes 2 poses 3 selected 4 nodes 5 edges 6 total selected k-mer instances in the table */
 uint64_t orc_count(const orc* o, int what);
 /* what: 0 parts 1 codes(u16) 2 poses(u32) 3 positions(u32) 4 hashes(u64 lo,hi) 5 node hashes(u64 lo,hi)

@@ -14,6 +14,7 @@
 #include <cstdint>
 #include <chrono>
 #include <cstring>
+#include <cstdio>
 #include <sstream>
 #include <string>
 #include <vector>
@@ -139,6 +140,88 @@ void* refshim_run(int mode, uint64_t k, uint64_t w, const char* bases, const uin
 			}
 		}
 	}
+	return run;
+}
+
+// Pass 3 of runMBG (MBG.cpp:1570): the file-driven iterator with hpc variants registered (ReadpartIterator::addHpcVariants,
+// ReadHelper.cpp:63-70; applied in iterateHashesFromFiles, ReadHelper.h:672-737 -- only the file path applies them, so
+// the reads are written to a scratch FASTA first).  Entry e == one addHpcVariants(hash e, offsets[e], lengths[...]) call.
+// One worker thread => callbacks arrive in file order.  Fills parts (hashed ones only), positions, hashes and the table.
+void* refshim_run_variants(int mode, uint64_t k, uint64_t w, const char* bases, const uint64_t* offsets, uint64_t n_reads, const char* scratch_fasta,
+	const uint64_t* var_hashes_lo_hi, const uint32_t* var_offsets, const uint64_t* var_len_begin, const uint32_t* var_lengths, uint64_t n_var)
+{
+	Run* run = new Run;
+	{
+		FILE* f = fopen(scratch_fasta, "w");
+		if (!f) return run;
+		for (uint64_t r = 0; r < n_reads; r++)
+		{
+			fprintf(f, ">%llu\n", (unsigned long long)r);
+			fwrite(bases + offsets[r], 1, offsets[r+1] - offsets[r], f);
+			fputc('\n', f);
+		}
+		fclose(f);
+	}
+	std::vector<std::string> files { std::string(scratch_fasta) };
+	ReadpartIterator iterator { (size_t)k, (size_t)w, (ErrorMasking)mode, 1, files, false, "" };
+	for (uint64_t e = 0; e < n_var; e++)
+	{
+		HashType h = ((HashType)var_hashes_lo_hi[2*e+1] << 64) + (HashType)var_hashes_lo_hi[2*e];
+		std::vector<size_t> lens { var_lengths + var_len_begin[e], var_lengths + var_len_begin[e+1] };
+		iterator.addHpcVariants(h, var_offsets[e], lens);
+	}
+	iterator.iterateHashes([run](const ReadInfo& read, const SequenceCharType& codes, const SequenceLengthType& poses, const std::string& raw, const std::vector<size_t>& positions, const std::vector<HashType>& hashes)
+	{
+		Part p;
+		p.read_idx = (uint32_t)std::stoull(read.readName.first);
+		p.part_offset = (uint32_t)read.readName.second;
+		p.raw_len = (uint32_t)read.readLength;
+		p.n_codes = (uint32_t)codes.size();
+		p.code_begin = 0; p.pose_begin = 0;
+		p.sel_begin = run->positions.size();
+		p.n_sel = (uint32_t)positions.size();
+		p.hashed = 1;
+		for (size_t j = 0; j < positions.size(); j++)
+		{
+			run->positions.push_back((uint32_t)positions[j]);
+			run->hashes.push_back((uint64_t)hashes[j]);
+			run->hashes.push_back((uint64_t)(hashes[j] >> 64));
+		}
+		run->parts.push_back(p);
+	});
+	HashList list { (size_t)k };
+	std::ostringstream log;
+	loadReadsAsHashesMultithread(list, k, iterator, 1, log);
+	list.sortByHash();
+	size_t n = list.size();
+	run->node_hash.resize(2*n);
+	run->node_cov.resize(n);
+	run->node_tip.resize(n);
+	for (auto pair : list.hashToNode)
+	{
+		run->node_hash[2*pair.second] = (uint64_t)pair.first;
+		run->node_hash[2*pair.second+1] = (uint64_t)(pair.first >> 64);
+	}
+	for (size_t i = 0; i < n; i++)
+	{
+		run->node_cov[i] = (uint32_t)list.coverage.get(i);
+		run->node_tip[i] = list.isTipKmer(i) ? 1 : 0;
+		run->total_selected += list.coverage.get(i);
+		for (int fw = 1; fw >= 0; fw--)
+		{
+			std::pair<size_t, bool> from { i, fw == 1 };
+			for (auto edge : list.getEdgeCoverages(from))
+			{
+				run->edges.push_back((uint32_t)i);
+				run->edges.push_back((uint32_t)fw);
+				run->edges.push_back((uint32_t)edge.first.first);
+				run->edges.push_back(edge.first.second ? 1 : 0);
+				run->edges.push_back((uint32_t)edge.second);
+				run->edges.push_back((uint32_t)list.getOverlap(from, edge.first));
+			}
+		}
+	}
+	remove(scratch_fasta);
 	return run;
 }
 

@@ -3,13 +3,15 @@ from oracle_lib import RunResult
 from verkko_b200.frontend import KEEP_CODES, KEEP_POSES, MbgFrontEnd
 
 
-def run_frontend(mode, k, w, reads, library=None, flags=KEEP_CODES | KEEP_POSES, table=True, **kw):
+def run_frontend(mode, k, w, reads, library=None, flags=KEEP_CODES | KEEP_POSES, table=True, variants=None, **kw):
     fe = MbgFrontEnd(k, w, mode, flags=flags, library=library, **kw)
     try:
         if isinstance(reads, tuple):
             fe.add_reads(*reads)
         else:
             fe.add_read_list(reads)
+        if variants is not None:
+            fe.set_variants(variants.hashes, variants.offsets, variants.len_begin, variants.lengths)
         fe.run()
         res = RunResult(parts=fe.parts(), codes=fe.codes(), poses=fe.poses(), positions=fe.positions(), hashes=fe.hashes())
         if table:

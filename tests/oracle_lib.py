@@ -79,6 +79,7 @@ class Oracle:
         L.orc_add_reads.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint64]
         L.orc_add_reads.restype = C.c_int
         L.orc_build_table.argtypes = [C.c_void_p]
+        L.orc_set_variants.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint64]
         L.orc_count.argtypes = [C.c_void_p, C.c_int]
         L.orc_count.restype = C.c_uint64
         L.orc_data.argtypes = [C.c_void_p, C.c_int]
@@ -100,11 +101,14 @@ class Oracle:
         L.orc_syncmers_bruteforce.argtypes = [C.c_void_p, C.c_uint64, C.c_uint32, C.c_uint32, C.c_void_p]
         L.orc_syncmers_bruteforce.restype = C.c_uint64
 
-    def run(self, mode, k, w, reads, table=True):
+    def run(self, mode, k, w, reads, table=True, variants=None):
         bases, offsets = reads if isinstance(reads, tuple) else pack_reads(reads)
         L = self.lib
         h = L.orc_create(MODES[mode] if isinstance(mode, str) else mode, k, w)
         try:
+            if variants is not None:
+                v = variants
+                L.orc_set_variants(h, v.hashes.ctypes.data, v.offsets.ctypes.data, v.len_begin.ctypes.data, v.lengths.ctypes.data, len(v.offsets))
             rc = L.orc_add_reads(h, bases.ctypes.data, offsets.ctypes.data, len(offsets) - 1)
             if rc != 0:
                 raise RuntimeError("oracle: palindromic k-mer" if rc == -1 else "oracle: unhashable k-mer")
@@ -166,6 +170,9 @@ class Reference:
         L.refshim_run.restype = C.c_void_p
         L.refshim_run.argtypes = [C.c_int, C.c_uint64, C.c_uint64, C.c_void_p, C.c_void_p, C.c_uint64, C.c_int]
         L.refshim_free.argtypes = [C.c_void_p]
+        L.refshim_run_variants.restype = C.c_void_p
+        L.refshim_run_variants.argtypes = [C.c_int, C.c_uint64, C.c_uint64, C.c_void_p, C.c_void_p, C.c_uint64, C.c_char_p,
+                                           C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint64]
         L.refshim_count.argtypes = [C.c_void_p, C.c_int]
         L.refshim_count.restype = C.c_uint64
         L.refshim_data.argtypes = [C.c_void_p, C.c_int]
@@ -188,6 +195,17 @@ class Reference:
         h = L.refshim_run(MODES[mode] if isinstance(mode, str) else mode, k, w, bases.ctypes.data, offsets.ctypes.data, len(offsets) - 1, 1 if table else 0)
         try:
             return _collect(lambda w_: L.refshim_count(h, w_), lambda w_: L.refshim_data(h, w_), table)
+        finally:
+            L.refshim_free(h)
+
+    def run_variants(self, mode, k, w, reads, variants, scratch):
+        """pass 3 of runMBG: file-driven iterator with hpc variants; parts = hashed parts in file order"""
+        bases, offsets = reads if isinstance(reads, tuple) else pack_reads(reads)
+        L, v = self.lib, variants
+        h = L.refshim_run_variants(MODES[mode] if isinstance(mode, str) else mode, k, w, bases.ctypes.data, offsets.ctypes.data, len(offsets) - 1,
+                                   str(scratch).encode(), v.hashes.ctypes.data, v.offsets.ctypes.data, v.len_begin.ctypes.data, v.lengths.ctypes.data, len(v.offsets))
+        try:
+            return _collect(lambda w_: L.refshim_count(h, w_), lambda w_: L.refshim_data(h, w_), True)
         finally:
             L.refshim_free(h)
 
@@ -216,6 +234,45 @@ class Reference:
         op = np.zeros(len(sym) + 2, dtype=np.uint64)
         n = self.lib.refshim_msat(sym.ctypes.data, poses.ctypes.data, len(sym), max_motif, oc.ctypes.data, op.ctypes.data)
         return oc[:n].copy(), op[:n + 1].copy()
+
+
+class Variants:
+    """entry e == one ReadpartIterator::addHpcVariants(hash e, offsets[e], lengths[len_begin[e]:len_begin[e+1]]) call"""
+
+    def __init__(self, hashes, offsets, len_begin, lengths):
+        self.hashes = np.ascontiguousarray(hashes, dtype=np.uint64).reshape(-1, 2)
+        self.offsets = np.ascontiguousarray(offsets, dtype=np.uint32)
+        self.len_begin = np.ascontiguousarray(len_begin, dtype=np.uint64)
+        self.lengths = np.ascontiguousarray(lengths, dtype=np.uint32)
+
+
+def make_variants(run, k, n_kmers, seed=5, per_kmer=3):
+    """hpc-variant entries for n_kmers of the k-mers selected in `run` (a RunResult without variants): a few code offsets
+    per k-mer (below, at and above k/2), each with a sorted list of run-length clusters that covers every run length seen
+    in the reads.  Half of the k-mers are registered under the swapped hash, so both branches of
+    MBG/ReadHelper.h:690-727 are taken; a k-mer is registered under one orientation only (the reference asserts that)."""
+    rng = np.random.default_rng(seed)
+    n_sel = len(run.positions)
+    pick = rng.choice(n_sel, size=min(n_kmers, n_sel), replace=False)
+    canon = {}
+    hashes, offsets, len_begin, lengths = [], [], [0], []
+    max_len = int(np.max(np.diff(run.poses.astype(np.int64)))) + 2 if len(run.poses) > 1 else 8
+    for i, idx in enumerate(pick):
+        lo, hi = int(run.hashes[idx, 0]), int(run.hashes[idx, 1])
+        key = (min(lo, hi), max(lo, hi))
+        if key in canon or lo == hi:
+            continue
+        canon[key] = True
+        reg = (lo, hi) if i % 2 == 0 else (hi, lo)
+        offs = {int(rng.integers(0, k // 2)), k // 2, int(rng.integers(k // 2 + 1, k))} if per_kmer >= 3 else {int(rng.integers(0, k))}
+        for off in sorted(offs):
+            hashes.append(reg)
+            offsets.append(off)
+            cl = sorted(set(int(x) for x in rng.integers(1, max_len, size=int(rng.integers(1, 4)))) | {max_len})
+            rng.shuffle(cl)
+            lengths.extend(cl)
+            len_begin.append(len(lengths))
+    return Variants(np.array(hashes, dtype=np.uint64).reshape(-1, 2), offsets, len_begin, lengths)
 
 
 def sorted_edges(edges):

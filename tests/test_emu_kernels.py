@@ -1,6 +1,7 @@
 """Kernel logic checked WITHOUT a GPU: the CUDA sources compiled against tests/emu/cuda_emu.h (an execution-model
 emulator used for debugging; see that header) and driven through the same C ABI, compared with the oracle.
 These are not the parity tests proper -- those are tests/test_gpu_parity.py on a real B200."""
+import numpy as np
 import pytest
 
 import workloads
@@ -52,3 +53,18 @@ def test_emulated_pipelined_run_estimate_overflow(oracle, emu_library):
 def test_emulated_tandem_repeats_longer_than_a_tile(oracle, emu_library):
     reads = workloads.long_tandem_reads()[:3] + [workloads.repeat_rich(22, 5000)]
     compare_runs(run_frontend("msat", 63, 33, reads, library=emu_library), oracle.run("msat", 63, 33, reads), what="long tandem")
+
+
+@pytest.mark.parametrize("mode,k,w,flags", [("collapse-msat", 301, 30, None), ("hpc", 63, 33, 0)])
+def test_emulated_hpc_variant_rehash(oracle, emu_library, mode, k, w, flags):
+    """row a11 (MBG/ReadHelper.h:680-737); flags=0: the library keeps poses on its own when variants are registered"""
+    from oracle_lib import make_variants
+    reads = workloads.coverage_reads(n_reads=10)
+    variants = make_variants(oracle.run(mode, k, w, reads), k, 150)
+    kw = {} if flags is None else {"flags": flags}
+    got = run_frontend(mode, k, w, reads, library=emu_library, variants=variants, **kw)
+    want = oracle.run(mode, k, w, reads, variants=variants)
+    if flags is None:
+        compare_runs(got, want, what="emu variants")
+    else:
+        assert np.array_equal(got.hashes, want.hashes) and np.array_equal(got.node_hash, want.node_hash) and np.array_equal(got.node_cov, want.node_cov)

@@ -9,6 +9,7 @@ import pytest
 import workloads
 from fe_helpers import run_frontend
 from oracle_lib import MODES, RunResult, compare_runs
+from verkko_b200.frontend import MbgFrontEnd
 
 pytestmark = pytest.mark.gpu
 GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
@@ -168,3 +169,31 @@ def test_pipelined_run_estimate_overflow(oracle):
 def test_tandem_repeats_longer_than_a_tile(oracle, mode, k, w):
     reads = workloads.long_tandem_reads() + [workloads.repeat_rich(21, 20000), workloads.repeat_rich(22, 5000)]
     compare_runs(run_frontend(mode, k, w, reads), oracle.run(mode, k, w, reads), what=f"long tandem {mode}")
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("mode,k,w", [("collapse-msat", 1001, 100), ("collapse-msat", 301, 30), ("hpc", 63, 33), ("no", 101, 20)])
+def test_hpc_variant_rehash(oracle, mode, k, w):
+    """row a11: pass 3 of runMBG, hashes of k-mers with registered hpc variants are perturbed by their clustered run
+    lengths (MBG/ReadHelper.h:680-737); the oracle's version is pinned on the reference's file-driven iterator in
+    tests/test_oracle.py::test_hpc_variants_equal_reference"""
+    from oracle_lib import make_variants
+    reads = workloads.coverage_reads(n_reads=24) if k < 1001 else workloads.coverage_reads(genome_len=60000, n_reads=24, len_min=12000, len_max=20000)
+    plain = oracle.run(mode, k, w, reads)
+    variants = make_variants(plain, k, 300)
+    got = run_frontend(mode, k, w, reads, variants=variants)
+    want = oracle.run(mode, k, w, reads, variants=variants)
+    compare_runs(got, want, what=f"variants {mode} k={k}")
+    assert not np.array_equal(want.hashes, plain.hashes)
+    # the library keeps poses by itself when variants are registered, and clearing the set restores the plain hashes
+    fe = MbgFrontEnd(k, w, mode, flags=0)
+    fe.add_reads(*workloads.as_pair(reads))
+    fe.set_variants(variants.hashes, variants.offsets, variants.len_begin, variants.lengths)
+    fe.run()
+    assert np.array_equal(fe.hashes(), want.hashes) and np.array_equal(fe.node_hashes(), want.node_hash)
+    fe.set_variants(np.zeros((0, 2), np.uint64), [], [0], [])
+    fe.reset()
+    fe.add_reads(*workloads.as_pair(reads))
+    fe.run()
+    assert np.array_equal(fe.hashes(), plain.hashes)
+    fe.close()

@@ -110,3 +110,32 @@ def test_golden_fixtures(oracle, path):
     got = oracle.run(mode, k, w, (z["bases"], z["offsets"]))
     want = RunResult({f: z[f] for f in ("parts", "codes", "poses", "positions", "hashes", "node_hash", "node_cov", "node_tip", "edges")})
     compare_runs(got, want, what=os.path.basename(path))
+
+
+def compare_hashed(a, b, what):
+    """a: RunResult with every part; b: hashed parts only (the file-driven reference iterator), same order"""
+    pa = a.parts[a.parts["hashed"] == 1]
+    assert len(pa) == len(b.parts), f"{what}: hashed part count"
+    for f in ("read_idx", "part_offset", "n_codes", "n_sel"):
+        assert np.array_equal(pa[f], b.parts[f]), f"{what}: parts.{f}"
+    assert np.array_equal(a.positions, b.positions), f"{what}: positions"
+    assert np.array_equal(a.hashes, b.hashes), f"{what}: hashes"
+    assert np.array_equal(a.node_hash, b.node_hash) and np.array_equal(a.node_cov, b.node_cov) and np.array_equal(a.node_tip, b.node_tip), f"{what}: nodes"
+    from oracle_lib import sorted_edges
+    assert np.array_equal(sorted_edges(a.edges), sorted_edges(b.edges)), f"{what}: edges"
+
+
+@pytest.mark.parametrize("mode,k,w", [("collapse-msat", 301, 30), ("hpc", 301, 30), ("hpc", 63, 33), ("no", 101, 20)])
+def test_hpc_variants_equal_reference(oracle, reference, tmp_path, mode, k, w):
+    """row a11: the pass-3 re-hash with registered hpc variants (MBG/ReadHelper.h:680-737) against the reference's
+    file-driven iterator; both strands of a k-mer must still meet in one node"""
+    from oracle_lib import make_variants
+    reads = workloads.coverage_reads(n_reads=16)
+    plain = oracle.run(mode, k, w, reads)
+    variants = make_variants(plain, k, 200)
+    assert len(variants.offsets) > 100
+    got = oracle.run(mode, k, w, reads, variants=variants)
+    want = reference.run_variants(mode, k, w, reads, variants, tmp_path / "reads.fa")
+    compare_hashed(got, want, f"variants {mode} k={k}")
+    assert not np.array_equal(got.hashes, plain.hashes)
+    assert np.array_equal(got.positions, plain.positions)

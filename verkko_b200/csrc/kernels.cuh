@@ -1236,6 +1236,93 @@ __global__ void __launch_bounds__(HASH_NT) k_kmer_hash(const uint64_t* __restric
 	}
 }
 
+// ------------------------------------------------------------------ a11: hpc-variant re-hash (pass 3 of runMBG)
+
+// The variant map of ReadpartIterator (MBG/ReadHelper.h:250, filled by addHpcVariants, MBG/ReadHelper.cpp:63-70) as
+// sorted arrays: entries ordered by (hash.hi, hash.lo, offset), each with a sorted list of run-length clusters.
+struct VariantTable
+{
+	const uint64_t* hash;        // lo, hi per entry
+	const uint32_t* offset;      // code offset inside the k-mer
+	const uint64_t* len_begin;   // n + 1
+	const uint32_t* len;         // cluster lengths, ascending per entry
+	uint64_t n;
+};
+
+__device__ __forceinline__ uint64_t variant_lower_bound(const VariantTable& vt, uint64_t lo, uint64_t hi)
+{
+	uint64_t a = 0, b = vt.n;
+	while (a < b)
+	{
+		const uint64_t m = (a + b) >> 1;
+		const uint64_t mlo = __ldg(vt.hash + 2 * m), mhi = __ldg(vt.hash + 2 * m + 1);
+		if (mhi < hi || (mhi == hi && mlo < lo)) a = m + 1; else b = m;
+	}
+	return a;
+}
+
+// *std::lower_bound(clusters, lengthHere) (MBG/ReadHelper.h:699, 718)
+__device__ __forceinline__ uint64_t variant_cluster(const VariantTable& vt, uint64_t e, uint32_t here)
+{
+	const uint64_t b = __ldg(vt.len_begin + e), n = __ldg(vt.len_begin + e + 1) - b;
+	uint64_t j = 0;
+	while (j + 1 < n && __ldg(vt.len + b + j) < here) j++;
+	return __ldg(vt.len + b + j);
+}
+
+// std::hash<const std::vector<size_t>&> step (MBG/MBGCommon.h:33-45)
+__device__ __forceinline__ uint64_t variant_fold(uint64_t h, uint64_t x) { h ^= x; return (h << 3) + (h >> 61); }
+
+// One thread per selected k-mer: if its forward hash (or the swapped, reverse-complement hash) is in the variant map,
+// XOR the hash of the clustered run lengths at the recorded offsets into the two halves (MBG/ReadHelper.h:684-730).
+// pos2 = per-code positions (poses) of every segment slot; only differences of neighbours are used.
+__global__ void __launch_bounds__(256) k_apply_variants(uint64_t* __restrict__ inst_hash, const uint32_t* __restrict__ inst_pos, const uint32_t* __restrict__ inst_seg,
+	uint64_t n_inst, const uint64_t* __restrict__ seg_out_base, const uint32_t* __restrict__ pos2, VariantTable vt, uint32_t k)
+{
+	for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n_inst; i += (uint64_t)gridDim.x * blockDim.x)
+	{
+		const uint64_t lo = inst_hash[2 * i], hi = inst_hash[2 * i + 1];
+		const uint32_t* __restrict__ poses = pos2 + seg_out_base[inst_seg[i]] + inst_pos[i];
+		uint64_t first = 0, second = 0;
+		uint64_t e = variant_lower_bound(vt, lo, hi);
+		if (e < vt.n && __ldg(vt.hash + 2 * e) == lo && __ldg(vt.hash + 2 * e + 1) == hi)
+		{
+			uint64_t end = e;
+			while (end < vt.n && __ldg(vt.hash + 2 * end) == lo && __ldg(vt.hash + 2 * end + 1) == hi) end++;
+			for (uint64_t j = e; j < end; j++)
+			{
+				const uint32_t off = __ldg(vt.offset + j);
+				if (off <= k / 2) first = variant_fold(first, variant_cluster(vt, j, poses[off + 1] - poses[off]));
+			}
+			for (uint64_t j = end; j-- > e; )
+			{
+				const uint32_t off = __ldg(vt.offset + j);
+				if (off >= k / 2) second = variant_fold(second, variant_cluster(vt, j, poses[off + 1] - poses[off]));
+			}
+		}
+		else
+		{
+			e = variant_lower_bound(vt, hi, lo);
+			if (!(e < vt.n && __ldg(vt.hash + 2 * e) == hi && __ldg(vt.hash + 2 * e + 1) == lo)) continue;
+			uint64_t end = e;
+			while (end < vt.n && __ldg(vt.hash + 2 * end) == hi && __ldg(vt.hash + 2 * end + 1) == lo) end++;
+			for (uint64_t j = end; j-- > e; )
+			{
+				const uint32_t off = __ldg(vt.offset + j);
+				if (off >= k / 2) first = variant_fold(first, variant_cluster(vt, j, poses[k - off] - poses[k - off - 1]));
+			}
+			for (uint64_t j = e; j < end; j++)
+			{
+				const uint32_t off = __ldg(vt.offset + j);
+				if (off <= k / 2) second = variant_fold(second, variant_cluster(vt, j, poses[k - off] - poses[k - off - 1]));
+			}
+		}
+		inst_hash[2 * i] = lo ^ first;
+		inst_hash[2 * i + 1] = hi ^ second;
+	}
+}
+
+
 // KAT helper: rrc for one stand-alone code array of n codes (cap == n)
 __global__ void k_revcomp_codes(const uint16_t* __restrict__ codes, uint32_t n, const uint16_t* __restrict__ tab_comp, uint16_t* __restrict__ rrc)
 {

@@ -96,6 +96,8 @@ struct mbgfe
 	std::vector<uint64_t> x_counts;                                          // per-owner record counts of the last mbgfe_exchange_counts
 	uint32_t id_base = 0;                                                    // nodes owned by lower ranks
 	bool nodes_ranked = false, edges_global = false;
+	DevBuf d_var_hash, d_var_offset, d_var_len_begin, d_var_len;       // hpc variants (mbgfe_set_variants), sorted
+	uint64_t n_var = 0;
 	DevBuf d_bucket_count, d_bucket_begin, d_scan_tot, d_scan_off;      // export: bucket tables and scan scratch
 	DevBuf d_node_hash_sorted, d_node_cov, d_node_tip, d_edges_sorted;    // export: final layout, device resident
 	uint64_t node_slots = 0, edge_slots = 0;
@@ -153,6 +155,9 @@ int ensure_host(mbgfe* h, HostBuf& b, size_t bytes)
 }
 
 void release_host(HostBuf& b) { if (b.p) cudaFreeHost(b.p); b.p = nullptr; b.cap = 0; }
+
+// poses are kept on request, and whenever hpc variants are registered (the re-hash reads run lengths from them)
+bool want_poses_of(const mbgfe* h) { return (h->prm.flags & MBGFE_KEEP_POSES) != 0 || h->n_var != 0; }
 
 uint64_t next_pow2(uint64_t v) { uint64_t p = 1; while (p < v) p <<= 1; return p; }
 
@@ -446,7 +451,7 @@ void mbgfe_destroy(mbgfe* h)
 		&h->d_inst_pos, &h->d_inst_seg, &h->d_inst_flag, &h->d_inst_hash, &h->d_inst_slot, &h->d_pal_list, &h->d_nodes, &h->d_edges, &h->d_node_out,
 		&h->d_edge_out, &h->d_records, &h->d_recv, &h->d_bucket_count, &h->d_bucket_begin, &h->d_scan_tot, &h->d_scan_off, &h->d_node_hash_sorted, &h->d_node_cov,
 		&h->d_node_tip, &h->d_edges_sorted, &h->d_inst_packpos, &h->d_ids_out, &h->d_id_begin, &h->d_edge_records, &h->d_xbuf[0], &h->d_xbuf[1], &h->d_xbuf[2],
-		&h->d_xbuf[3] }) release(*b);
+		&h->d_xbuf[3], &h->d_var_hash, &h->d_var_offset, &h->d_var_len_begin, &h->d_var_len }) release(*b);
 	for (HostBuf* b : { &h->p_node_hashes, &h->p_node_cov, &h->p_node_tip, &h->p_edges }) release_host(*b);
 	for (auto& e : h->ev) if (e) cudaEventDestroy(e);
 	for (auto& e : h->piece_events) cudaEventDestroy(e);
@@ -584,7 +589,7 @@ namespace {
 // device buffers of one pass over the resident batch + counter reset
 int prepare_process(mbgfe* h)
 {
-	const bool want_poses = (h->prm.flags & MBGFE_KEEP_POSES) != 0;
+	const bool want_poses = want_poses_of(h);
 	const bool need_pos1 = want_poses && !h->collapse;
 	const uint64_t tot = h->total_out;
 	if (int rc = ensure(h, h->d_sym, tot / 4 + 64)) return rc;
@@ -604,7 +609,7 @@ uint32_t launch_front(mbgfe* h, uint32_t g0, uint32_t cnt, bool timed)
 {
 	if (cnt == 0) { if (timed) { tick(h, 4); tick(h, 5); } return 0; }
 	const uint32_t k = h->prm.k, w = h->prm.w;
-	const bool want_poses = (h->prm.flags & MBGFE_KEEP_POSES) != 0;
+	const bool want_poses = want_poses_of(h);
 	const bool need_pos1 = want_poses && !h->collapse;
 	SegTable st;
 	st.in_start = h->d_seg_in.as<uint64_t>() + g0;
@@ -775,6 +780,17 @@ int process_tail(mbgfe* h, uint32_t launches)
 		launches++;
 	}
 	h->stats.distinct = 0; h->stats.distinct_edges = 0;
+	if (h->n_var && n_inst)
+	{
+		// pass 3 of runMBG: hashes of k-mers with registered hpc variants are perturbed after the palindrome rule
+		// (MBG/ReadHelper.h:672-737) and before anything is counted
+		VariantTable vt;
+		vt.hash = h->d_var_hash.as<uint64_t>(); vt.offset = h->d_var_offset.as<uint32_t>();
+		vt.len_begin = h->d_var_len_begin.as<uint64_t>(); vt.len = h->d_var_len.as<uint32_t>(); vt.n = h->n_var;
+		MBGFE_LAUNCH(k_apply_variants, (unsigned)std::min<uint64_t>((n_inst + 255) / 256, (uint64_t)h->sm_count * 16), 256, 0, h->stream, h->d_inst_hash.as<uint64_t>(),
+			h->d_inst_pos.as<uint32_t>(), h->d_inst_seg.as<uint32_t>(), n_inst, h->d_seg_out.as<uint64_t>(), h->d_pos2.as<uint32_t>(), vt, k);
+		launches++;
+	}
 	if (!(h->prm.flags & MBGFE_NO_TABLE))
 	{
 		const uint64_t slots = std::max<uint64_t>(next_pow2(std::max<uint64_t>(2 * n_inst, 1024)), h->prm.table_slots ? next_pow2(h->prm.table_slots) : 0);
@@ -806,6 +822,12 @@ extern "C" {
 int mbgfe_run(mbgfe* h)
 {
 	if (!h) return MBGFE_E_PARAM;
+	if (h->n_var)
+	{
+		// the variant re-hash sits between hashing and counting: take the unpipelined path
+		if (int rc = mbgfe_upload(h)) return rc;
+		return mbgfe_process(h);
+	}
 	clear_results(h);
 	h->resident = false;
 	h->stats.h2d_bytes = 0; h->stats.d2h_bytes = 0;
@@ -1383,6 +1405,52 @@ int mbgfe_exchange_insert_edges(mbgfe* h, const void* device_records, uint64_t n
 	h->stats.ms_edges = elapsed(h, 12, 13);
 	h->edges_global = true;
 	h->exported_table = false;
+	return 0;
+}
+
+int mbgfe_set_variants(mbgfe* h, const mbgfe_hash128* hashes, const uint32_t* offsets, const uint64_t* len_begin, const uint32_t* lengths, uint64_t n_entries)
+{
+	if (!h) return MBGFE_E_PARAM;
+	if (n_entries && (!hashes || !offsets || !len_begin || !lengths)) return fail(h, MBGFE_E_PARAM, "mbgfe_set_variants: null array");
+	h->n_var = 0;
+	if (n_entries == 0) return 0;
+	for (uint64_t e = 0; e < n_entries; e++)
+	{
+		if (offsets[e] >= h->prm.k) return fail(h, MBGFE_E_PARAM, "variant offset %u outside the k-mer", offsets[e]);
+		if (len_begin[e + 1] <= len_begin[e]) return fail(h, MBGFE_E_PARAM, "variant entry %llu has no lengths", (unsigned long long)e);
+	}
+	// what addHpcVariants leaves (MBG/ReadHelper.cpp:63-70): per hash the entries ordered by offset, lengths ascending
+	std::vector<uint64_t> order(n_entries);
+	for (uint64_t e = 0; e < n_entries; e++) order[e] = e;
+	std::sort(order.begin(), order.end(), [&](uint64_t a, uint64_t b)
+	{
+		if (hashes[a].hi != hashes[b].hi) return hashes[a].hi < hashes[b].hi;
+		if (hashes[a].lo != hashes[b].lo) return hashes[a].lo < hashes[b].lo;
+		if (offsets[a] != offsets[b]) return offsets[a] < offsets[b];
+		return a < b;
+	});
+	std::vector<uint64_t> vh(2 * n_entries), vb(n_entries + 1);
+	std::vector<uint32_t> vo(n_entries), vl;
+	vl.reserve(len_begin[n_entries]);
+	for (uint64_t e = 0; e < n_entries; e++)
+	{
+		const uint64_t src = order[e];
+		vh[2 * e] = hashes[src].lo; vh[2 * e + 1] = hashes[src].hi; vo[e] = offsets[src];
+		vb[e] = vl.size();
+		vl.insert(vl.end(), lengths + len_begin[src], lengths + len_begin[src + 1]);
+		std::sort(vl.begin() + vb[e], vl.end());
+	}
+	vb[n_entries] = vl.size();
+	if (int rc = ensure(h, h->d_var_hash, vh.size() * 8)) return rc;
+	if (int rc = ensure(h, h->d_var_offset, vo.size() * 4)) return rc;
+	if (int rc = ensure(h, h->d_var_len_begin, vb.size() * 8)) return rc;
+	if (int rc = ensure(h, h->d_var_len, vl.size() * 4)) return rc;
+	CU(h, cudaMemcpyAsync(h->d_var_hash.p, vh.data(), vh.size() * 8, cudaMemcpyHostToDevice, h->stream));
+	CU(h, cudaMemcpyAsync(h->d_var_offset.p, vo.data(), vo.size() * 4, cudaMemcpyHostToDevice, h->stream));
+	CU(h, cudaMemcpyAsync(h->d_var_len_begin.p, vb.data(), vb.size() * 8, cudaMemcpyHostToDevice, h->stream));
+	CU(h, cudaMemcpyAsync(h->d_var_len.p, vl.data(), vl.size() * 4, cudaMemcpyHostToDevice, h->stream));
+	CU(h, cudaStreamSynchronize(h->stream));
+	h->n_var = n_entries;
 	return 0;
 }
 

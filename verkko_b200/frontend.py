@@ -86,6 +86,7 @@ def load_library(path=None):
     L.mbgfe_exchange_edge_counts.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p]
     L.mbgfe_exchange_edge_pack.argtypes = [C.c_void_p, C.c_void_p, C.POINTER(C.c_void_p)]
     L.mbgfe_exchange_insert_edges.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64]
+    L.mbgfe_set_variants.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint64]
     L.mbgfe_kat_tables.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
     L.mbgfe_kat_kmer_hash.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p]
     if path == library_path():
@@ -170,6 +171,14 @@ class MbgFrontEnd:
 
     def read_name(self, idx):
         return self.lib.mbgfe_read_name(self.handle, idx).decode()
+
+    def set_variants(self, hashes, offsets, len_begin, lengths):
+        """ReadpartIterator::addHpcVariants for every entry at once (MBG/ReadHelper.cpp:63-70); hashes[n,2] = (lo, hi)"""
+        hashes = np.ascontiguousarray(hashes, dtype=np.uint64).reshape(-1, 2)
+        offsets = np.ascontiguousarray(offsets, dtype=np.uint32)
+        len_begin = np.ascontiguousarray(len_begin, dtype=np.uint64)
+        lengths = np.ascontiguousarray(lengths, dtype=np.uint32)
+        self._check(self.lib.mbgfe_set_variants(self.handle, hashes.ctypes.data, offsets.ctypes.data, len_begin.ctypes.data, lengths.ctypes.data, len(offsets)))
 
     def reset(self):
         self._check(self.lib.mbgfe_reset(self.handle))
