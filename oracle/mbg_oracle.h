@@ -40,6 +40,18 @@ uint64_t orc_count(const orc* o, int what);
  *       6 node coverage(u32) 7 node tip(u8) 8 edges(u32 x6: from,from_fw,to,to_fw,coverage,overlap) */
 const void* orc_data(const orc* o, int what);
 
+/* The step after the table (mbg_unitig_oracle.c): getUnitigGraph's coverage filter (edges >= min_cov, chains with mean
+ * coverage >= min_unitig_cov; MBG/MBG.cpp:629-696, oneCovHeuristic = keepGaps = false), HashList::filter
+ * (MBG/HashList.cpp:159-232) and the unitig chains of the filtered list (MBG/MBG.cpp:689-745).  Needs orc_build_table. */
+typedef struct orc_unitigs orc_unitigs;
+orc_unitigs* orc_build_unitigs(const orc* o, uint32_t min_cov, double min_unitig_cov);
+void orc_unitigs_free(orc_unitigs* u);
+/* what: 0 nodes of the input table, 1 kept nodes, 2 filtered edges, 3 unitigs, 4 unitig nodes */
+uint64_t orc_unitigs_count(const orc_unitigs* u, int what);
+/* what: 0 kept(u8 per input node) 1 filtered hashes(u64 lo,hi) 2 filtered coverage(u32) 3 filtered tip(u8)
+ *       4 filtered edges(u32 x6) 5 unitig_begin(u64, n+1) 6 unitig nodes(u32 = 2*filtered id + fw) */
+const void* orc_unitigs_data(const orc_unitigs* u, int what);
+
 /* primitives, exported for the known-answer tests */
 uint64_t orc_char_hash(uint64_t code);
 uint16_t orc_complement(uint16_t code);

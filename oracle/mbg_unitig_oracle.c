@@ -1,0 +1,205 @@
+/* oracle/mbg_unitig_oracle.c -- TEST INFRASTRUCTURE ONLY, never linked into or called by the product.
+ *
+ * Plain-C sequential restatement of the step right after the k-mer table in MBG:
+ *   getCoveredEdges                      MBG/MBG.cpp:367-388   edges with coverage >= -a, both directions, deduplicated
+ *                                        (SparseEdgeContainer::addEdge has set semantics, MBG/SparseEdgeContainer.cpp:12-24)
+ *   getUnitigHashes / checkUnitigHashes  MBG/MBG.cpp:305-344   maximal non-branching chain; kept iff mean coverage >= -u
+ *   getUnitigGraph, first block          MBG/MBG.cpp:629-696   which chains are visited (oneCovHeuristic = keepGaps = false)
+ *   HashList::filter                     MBG/HashList.cpp:159-232  kept nodes renumbered in order, edges between kept nodes
+ *   getUnitigGraph, second block         MBG/MBG.cpp:689-760   unitigs = the same chains on the filtered list, coverage >= -a
+ * Input is the table mbg_oracle.c builds (node order = ascending canonical hash).  The reference runs this on the
+ * arrival-ordered list; the kept set and the chains do not depend on the order, the unitig numbering does (tests compare
+ * order-normalised).  Pinned against the reference's own getUnitigGraph in tests/test_oracle.py.
+ */
+#include <stdint.h>
+#include <stdlib.h>
+#include <string.h>
+#include "mbg_oracle.h"
+
+typedef struct {
+	uint64_t n;            /* nodes */
+	uint64_t* begin;       /* 2n + 1: successors of oriented node x = 2*id + fw (SparseEdgeContainer::pairToInt) */
+	uint32_t* to;
+} adjacency;
+
+static int cmp_u64(const void* a, const void* b) { uint64_t x = *(const uint64_t*)a, y = *(const uint64_t*)b; return x < y ? -1 : x > y; }
+
+/* getCoveredEdges: edges = u32 x6 records (from, from_fw, to, to_fw, coverage, overlap) */
+static adjacency covered_edges(uint64_t n_nodes, const uint32_t* edges, uint64_t n_edges, uint32_t min_cov)
+{
+	adjacency a;
+	a.n = n_nodes;
+	uint64_t* pairs = (uint64_t*)malloc((2 * n_edges + 1) * 8);
+	uint64_t np = 0;
+	for (uint64_t e = 0; e < n_edges; e++)
+	{
+		const uint32_t* r = edges + 6 * e;
+		if (r[4] < min_cov) continue;
+		uint64_t x = 2ull * r[0] + r[1], y = 2ull * r[2] + r[3];
+		pairs[np++] = (x << 32) | y;
+		pairs[np++] = ((y ^ 1) << 32) | (x ^ 1);
+	}
+	qsort(pairs, np, 8, cmp_u64);
+	uint64_t nu = 0;
+	for (uint64_t i = 0; i < np; i++) if (i == 0 || pairs[i] != pairs[nu - 1]) pairs[nu++] = pairs[i];
+	a.begin = (uint64_t*)calloc(2 * n_nodes + 2, 8);
+	a.to = (uint32_t*)malloc((nu + 1) * 4);
+	for (uint64_t i = 0; i < nu; i++) { a.begin[(pairs[i] >> 32) + 1]++; a.to[i] = (uint32_t)pairs[i]; }
+	for (uint64_t x = 0; x < 2 * n_nodes; x++) a.begin[x + 1] += a.begin[x];
+	free(pairs);
+	return a;
+}
+static void adjacency_free(adjacency* a) { free(a->begin); free(a->to); }
+static uint64_t deg(const adjacency* a, uint32_t x) { return a->begin[x + 1] - a->begin[x]; }
+static uint32_t first(const adjacency* a, uint32_t x) { return a->to[a->begin[x]]; }
+
+/* getUnitigHashes (MBG/MBG.cpp:305-320): returns the chain length, nodes written to out */
+static uint64_t unitig_hashes(const adjacency* a, uint32_t start, uint32_t* out)
+{
+	uint64_t n = 0;
+	out[n++] = start;
+	for (;;)
+	{
+		uint32_t back = out[n - 1];
+		if (deg(a, back) != 1) break;
+		uint32_t next = first(a, back);
+		if (deg(a, next ^ 1) != 1) break;
+		if (next == start) break;
+		if ((next >> 1) == (back >> 1)) break;
+		out[n++] = next;
+	}
+	return n;
+}
+
+/* checkUnitigHashes (MBG/MBG.cpp:322-344) */
+static void check_unitig(const adjacency* a, uint32_t start, uint8_t* checked, const uint32_t* cov, double min_unitig_cov, uint8_t* kept, uint32_t* scratch)
+{
+	uint64_t n = unitig_hashes(a, start, scratch);
+	double total = 0;
+	for (uint64_t i = 0; i < n; i++) { checked[scratch[i] >> 1] = 1; total += cov[scratch[i] >> 1]; }
+	total /= (double)n;
+	if (total >= min_unitig_cov) for (uint64_t i = 0; i < n; i++) kept[scratch[i] >> 1] = 1;
+}
+
+struct orc_unitigs {
+	uint64_t n_nodes, n_kept, n_fedges, n_unitigs, n_unitig_nodes;
+	uint8_t* kept;          /* per node of the input table */
+	uint64_t* f_hash;       /* lo, hi per kept node */
+	uint32_t* f_cov;
+	uint8_t* f_tip;
+	uint32_t* f_edges;      /* u32 x6 with renumbered ids */
+	uint64_t* unitig_begin; /* n_unitigs + 1 */
+	uint32_t* unitig_nodes; /* 2*filtered id + fw, in traversal order */
+};
+
+void orc_unitigs_free(orc_unitigs* u)
+{
+	if (!u) return;
+	free(u->kept); free(u->f_hash); free(u->f_cov); free(u->f_tip); free(u->f_edges); free(u->unitig_begin); free(u->unitig_nodes);
+	free(u);
+}
+
+/* getUnitigGraph's second block: which oriented node starts a unitig, in the reference's loop order */
+static void start_unitig(const adjacency* a, uint32_t start, uint8_t* belongs, orc_unitigs* u, uint32_t* scratch)
+{
+	uint64_t n = unitig_hashes(a, start, scratch);
+	for (uint64_t i = 0; i < n; i++) { belongs[scratch[i] >> 1] = 1; u->unitig_nodes[u->n_unitig_nodes++] = scratch[i]; }
+	u->unitig_begin[++u->n_unitigs] = u->n_unitig_nodes;
+}
+
+orc_unitigs* orc_build_unitigs(const orc* o, uint32_t min_cov, double min_unitig_cov)
+{
+	const uint64_t n = orc_count(o, 4), m = orc_count(o, 5);
+	const uint64_t* hash = (const uint64_t*)orc_data(o, 5);
+	const uint32_t* cov = (const uint32_t*)orc_data(o, 6);
+	const uint8_t* tip = (const uint8_t*)orc_data(o, 7);
+	const uint32_t* edges = (const uint32_t*)orc_data(o, 8);
+	orc_unitigs* u = (orc_unitigs*)calloc(1, sizeof(orc_unitigs));
+	u->n_nodes = n;
+	u->kept = (uint8_t*)calloc(n + 1, 1);
+	uint8_t* checked = (uint8_t*)calloc(n + 1, 1);
+	uint32_t* scratch = (uint32_t*)malloc((n + 1) * 4);
+	/* ---- first block, MBG/MBG.cpp:637-690 */
+	adjacency a = covered_edges(n, edges, m, min_cov);
+	for (uint64_t i = 0; i < n; i++)
+	{
+		uint32_t fw = (uint32_t)(2 * i + 1), bw = (uint32_t)(2 * i);
+		if (deg(&a, bw) != 1 || first(&a, bw) == fw)
+		{
+			if (!checked[i]) check_unitig(&a, fw, checked, cov, min_unitig_cov, u->kept, scratch);
+			for (uint64_t j = a.begin[bw]; j < a.begin[bw + 1]; j++)
+				if (!checked[a.to[j] >> 1]) check_unitig(&a, a.to[j], checked, cov, min_unitig_cov, u->kept, scratch);
+		}
+		if (deg(&a, fw) != 1 || first(&a, fw) == bw)
+		{
+			if (!checked[i]) check_unitig(&a, bw, checked, cov, min_unitig_cov, u->kept, scratch);
+			for (uint64_t j = a.begin[fw]; j < a.begin[fw + 1]; j++)
+				if (!checked[a.to[j] >> 1]) check_unitig(&a, a.to[j], checked, cov, min_unitig_cov, u->kept, scratch);
+		}
+	}
+	for (uint64_t i = 0; i < n; i++) if (!checked[i]) check_unitig(&a, (uint32_t)(2 * i + 1), checked, cov, min_unitig_cov, u->kept, scratch);
+	adjacency_free(&a);
+	/* ---- HashList::filter, MBG/HashList.cpp:159-232 */
+	uint32_t* rank = (uint32_t*)malloc((n + 1) * 4);
+	for (uint64_t i = 0; i < n; i++) { rank[i] = (uint32_t)u->n_kept; if (u->kept[i]) u->n_kept++; }
+	u->f_hash = (uint64_t*)malloc((u->n_kept + 1) * 16);
+	u->f_cov = (uint32_t*)malloc((u->n_kept + 1) * 4);
+	u->f_tip = (uint8_t*)malloc(u->n_kept + 1);
+	for (uint64_t i = 0; i < n; i++) if (u->kept[i])
+	{
+		u->f_hash[2 * rank[i]] = hash[2 * i]; u->f_hash[2 * rank[i] + 1] = hash[2 * i + 1];
+		u->f_cov[rank[i]] = cov[i]; u->f_tip[rank[i]] = tip[i];
+	}
+	u->f_edges = (uint32_t*)malloc((m + 1) * 24);
+	for (uint64_t e = 0; e < m; e++)
+	{
+		const uint32_t* r = edges + 6 * e;
+		if (!u->kept[r[0]] || !u->kept[r[2]]) continue;
+		uint32_t* w = u->f_edges + 6 * u->n_fedges++;
+		memcpy(w, r, 24);
+		w[0] = rank[r[0]]; w[2] = rank[r[2]];
+	}
+	/* ---- second block, MBG/MBG.cpp:689-745, on the filtered list */
+	const uint64_t nk = u->n_kept;
+	a = covered_edges(nk, u->f_edges, u->n_fedges, min_cov);
+	uint8_t* belongs = (uint8_t*)calloc(nk + 1, 1);
+	u->unitig_begin = (uint64_t*)calloc(nk + 2, 8);
+	u->unitig_nodes = (uint32_t*)malloc((nk + 1) * 4);
+	for (uint64_t i = 0; i < nk; i++)
+	{
+		if (u->f_cov[i] < min_cov) continue;
+		uint32_t fw = (uint32_t)(2 * i + 1), bw = (uint32_t)(2 * i);
+		if (deg(&a, bw) != 1 || first(&a, bw) == fw)
+		{
+			if (!belongs[i]) start_unitig(&a, fw, belongs, u, scratch);
+			for (uint64_t j = a.begin[bw]; j < a.begin[bw + 1]; j++) if (!belongs[a.to[j] >> 1]) start_unitig(&a, a.to[j], belongs, u, scratch);
+		}
+		if (deg(&a, fw) != 1 || first(&a, fw) == bw)
+		{
+			if (!belongs[i]) start_unitig(&a, bw, belongs, u, scratch);
+			for (uint64_t j = a.begin[fw]; j < a.begin[fw + 1]; j++) if (!belongs[a.to[j] >> 1]) start_unitig(&a, a.to[j], belongs, u, scratch);
+		}
+	}
+	for (uint64_t i = 0; i < nk; i++)
+	{
+		if (belongs[i] || u->f_cov[i] < min_cov) continue;
+		start_unitig(&a, (uint32_t)(2 * i + 1), belongs, u, scratch);
+	}
+	adjacency_free(&a);
+	free(belongs); free(rank); free(checked); free(scratch);
+	return u;
+}
+
+/* what: 0 nodes of the input table, 1 kept nodes, 2 filtered edges, 3 unitigs, 4 unitig nodes */
+uint64_t orc_unitigs_count(const orc_unitigs* u, int what)
+{
+	switch (what) { case 0: return u->n_nodes; case 1: return u->n_kept; case 2: return u->n_fedges; case 3: return u->n_unitigs; case 4: return u->n_unitig_nodes; }
+	return 0;
+}
+/* what: 0 kept(u8 per input node) 1 filtered hashes(u64 lo,hi) 2 filtered coverage(u32) 3 filtered tip(u8)
+ *       4 filtered edges(u32 x6) 5 unitig_begin(u64, n+1) 6 unitig nodes(u32 = 2*filtered id + fw) */
+const void* orc_unitigs_data(const orc_unitigs* u, int what)
+{
+	switch (what) { case 0: return u->kept; case 1: return u->f_hash; case 2: return u->f_cov; case 3: return u->f_tip; case 4: return u->f_edges; case 5: return u->unitig_begin; case 6: return u->unitig_nodes; }
+	return 0;
+}

@@ -26,6 +26,8 @@
 
 uint64_t getHash(uint64_t key); // FastHasher.cpp:33
 void loadReadsAsHashesMultithread(HashList& result, const size_t kmerSize, const ReadpartIterator& partIterator, const size_t numThreads, std::ostream& log);
+#include "UnitigGraph.h"
+UnitigGraph getUnitigGraph(HashList& hashlist, const size_t minCoverage, const double minUnitigCoverage, const bool keepGaps, const bool oneCovHeuristic); // MBG.cpp:629
 
 namespace {
 
@@ -222,6 +224,68 @@ void* refshim_run_variants(int mode, uint64_t k, uint64_t w, const char* bases, 
 		}
 	}
 	remove(scratch_fasta);
+	return run;
+}
+
+// The step after the table exactly as runMBG takes it in pass 1 (MBG.cpp:1557-1558): loadReadsAsHashesMultithread, then
+// getUnitigGraph(reads, minCoverage, minUnitigCoverage, keepGaps = false, oneCovHeuristic = false) on the ARRIVAL-ordered
+// list; it filters the HashList in place (HashList::filter) and returns the unitigs.  Output, keyed by hash so that it
+// does not depend on node numbering: the filtered list in the Run's node_* / edges arrays (ids = filtered arrival
+// order), and every unitig as a run of (node id, fw) pairs in `positions` (2*id + fw) with `parts[u].sel_begin/n_sel`.
+void* refshim_unitigs(int mode, uint64_t k, uint64_t w, const char* bases, const uint64_t* offsets, uint64_t n_reads, uint64_t min_cov, double min_unitig_cov)
+{
+	Run* run = new Run;
+	std::vector<std::string> nofiles;
+	std::vector<std::pair<std::string, std::string>> memoryReads;
+	for (uint64_t r = 0; r < n_reads; r++)
+	{
+		std::string seq { bases + offsets[r], bases + offsets[r+1] };
+		if (seq.size() < 32) continue;
+		memoryReads.emplace_back(std::to_string(r), seq);
+	}
+	ReadpartIterator tableIterator { (size_t)k, (size_t)w, (ErrorMasking)mode, 1, nofiles, false, "" };
+	tableIterator.setMemoryReads(memoryReads);
+	HashList list { (size_t)k };
+	std::ostringstream log;
+	if (memoryReads.size() > 0) loadReadsAsHashesMultithread(list, k, tableIterator, 1, log);
+	UnitigGraph unitigs = getUnitigGraph(list, min_cov, min_unitig_cov, false, false);
+	size_t n = list.size();
+	run->node_hash.resize(2*n);
+	run->node_cov.resize(n);
+	run->node_tip.resize(n);
+	for (auto pair : list.hashToNode)
+	{
+		run->node_hash[2*pair.second] = (uint64_t)pair.first;
+		run->node_hash[2*pair.second+1] = (uint64_t)(pair.first >> 64);
+	}
+	for (size_t i = 0; i < n; i++)
+	{
+		run->node_cov[i] = (uint32_t)list.coverage.get(i);
+		run->node_tip[i] = list.isTipKmer(i) ? 1 : 0;
+		for (int fw = 1; fw >= 0; fw--)
+		{
+			std::pair<size_t, bool> from { i, fw == 1 };
+			for (auto edge : list.getEdgeCoverages(from))
+			{
+				run->edges.push_back((uint32_t)i);
+				run->edges.push_back((uint32_t)fw);
+				run->edges.push_back((uint32_t)edge.first.first);
+				run->edges.push_back(edge.first.second ? 1 : 0);
+				run->edges.push_back((uint32_t)edge.second);
+				run->edges.push_back((uint32_t)list.getOverlap(from, edge.first));
+			}
+		}
+	}
+	for (size_t u = 0; u < unitigs.unitigs.size(); u++)
+	{
+		Part p;
+		memset(&p, 0, sizeof(p));
+		p.read_idx = (uint32_t)u;
+		p.sel_begin = run->positions.size();
+		p.n_sel = (uint32_t)unitigs.unitigs[u].size();
+		for (auto node : unitigs.unitigs[u]) run->positions.push_back((uint32_t)(2 * node.first + (node.second ? 1 : 0)));
+		run->parts.push_back(p);
+	}
 	return run;
 }
 

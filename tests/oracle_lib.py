@@ -25,7 +25,8 @@ assert PART_DTYPE.itemsize == 48
 
 
 def build_oracle():
-    if not os.path.exists(ORACLE_SO) or os.path.getmtime(ORACLE_SO) < os.path.getmtime(os.path.join(ROOT, "oracle", "mbg_oracle.c")):
+    srcs = [os.path.join(ROOT, "oracle", f) for f in ("mbg_oracle.c", "mbg_unitig_oracle.c", "mbg_oracle.h")]
+    if not os.path.exists(ORACLE_SO) or os.path.getmtime(ORACLE_SO) < max(os.path.getmtime(f) for f in srcs):
         subprocess.check_call(["make", "-C", os.path.join(ROOT, "oracle"), "libmbg_oracle.so"], stdout=subprocess.DEVNULL)
     return ORACLE_SO
 
@@ -118,6 +119,38 @@ class Oracle:
         finally:
             L.orc_free(h)
 
+    def run_unitigs(self, mode, k, w, reads, min_cov, min_unitig_cov, variants=None):
+        """table + the filter/unitig step after it -> (RunResult, UnitigResult)"""
+        bases, offsets = reads if isinstance(reads, tuple) else pack_reads(reads)
+        L = self.lib
+        L.orc_build_unitigs.restype = C.c_void_p
+        L.orc_build_unitigs.argtypes = [C.c_void_p, C.c_uint32, C.c_double]
+        L.orc_unitigs_free.argtypes = [C.c_void_p]
+        L.orc_unitigs_count.argtypes = [C.c_void_p, C.c_int]
+        L.orc_unitigs_count.restype = C.c_uint64
+        L.orc_unitigs_data.argtypes = [C.c_void_p, C.c_int]
+        L.orc_unitigs_data.restype = C.c_void_p
+        h = L.orc_create(MODES[mode] if isinstance(mode, str) else mode, k, w)
+        u = None
+        try:
+            if variants is not None:
+                v = variants
+                L.orc_set_variants(h, v.hashes.ctypes.data, v.offsets.ctypes.data, v.len_begin.ctypes.data, v.lengths.ctypes.data, len(v.offsets))
+            if L.orc_add_reads(h, bases.ctypes.data, offsets.ctypes.data, len(offsets) - 1) != 0:
+                raise RuntimeError("oracle: palindromic or unhashable k-mer")
+            L.orc_build_table(h)
+            table = _collect(lambda w_: L.orc_count(h, w_), lambda w_: L.orc_data(h, w_), True)
+            u = L.orc_build_unitigs(h, min_cov, float(min_unitig_cov))
+            cnt, dat = (lambda w_: L.orc_unitigs_count(u, w_)), (lambda w_: L.orc_unitigs_data(u, w_))
+            res = UnitigResult(kept=_arr(dat(0), cnt(0), "u1"), node_hash=_arr(dat(1), cnt(1) * 2, "<u8").reshape(-1, 2), node_cov=_arr(dat(2), cnt(1), "<u4"),
+                               node_tip=_arr(dat(3), cnt(1), "u1"), edges=_arr(dat(4), cnt(2) * 6, "<u4").reshape(-1, 6),
+                               unitig_begin=_arr(dat(5), cnt(3) + 1, "<u8"), unitig_nodes=_arr(dat(6), cnt(4), "<u4"))
+            return table, res
+        finally:
+            if u:
+                L.orc_unitigs_free(u)
+            L.orc_free(h)
+
     def char_hash(self, c):
         return int(self.lib.orc_char_hash(c))
 
@@ -198,6 +231,20 @@ class Reference:
         finally:
             L.refshim_free(h)
 
+    def run_unitigs(self, mode, k, w, reads, min_cov, min_unitig_cov):
+        """the reference's own getUnitigGraph after its table build (ids = filtered arrival order) -> UnitigResult"""
+        bases, offsets = reads if isinstance(reads, tuple) else pack_reads(reads)
+        L = self.lib
+        L.refshim_unitigs.restype = C.c_void_p
+        L.refshim_unitigs.argtypes = [C.c_int, C.c_uint64, C.c_uint64, C.c_void_p, C.c_void_p, C.c_uint64, C.c_uint64, C.c_double]
+        h = L.refshim_unitigs(MODES[mode] if isinstance(mode, str) else mode, k, w, bases.ctypes.data, offsets.ctypes.data, len(offsets) - 1, min_cov, float(min_unitig_cov))
+        try:
+            r = _collect(lambda w_: L.refshim_count(h, w_), lambda w_: L.refshim_data(h, w_), True)
+            begin = np.concatenate([r.parts["sel_begin"], [len(r.positions)]]).astype(np.uint64) if len(r.parts) else np.zeros(1, np.uint64)
+            return UnitigResult(kept=None, node_hash=r.node_hash, node_cov=r.node_cov, node_tip=r.node_tip, edges=r.edges, unitig_begin=begin, unitig_nodes=r.positions)
+        finally:
+            L.refshim_free(h)
+
     def run_variants(self, mode, k, w, reads, variants, scratch):
         """pass 3 of runMBG: file-driven iterator with hpc variants; parts = hashed parts in file order"""
         bases, offsets = reads if isinstance(reads, tuple) else pack_reads(reads)
@@ -234,6 +281,56 @@ class Reference:
         op = np.zeros(len(sym) + 2, dtype=np.uint64)
         n = self.lib.refshim_msat(sym.ctypes.data, poses.ctypes.data, len(sym), max_motif, oc.ctypes.data, op.ctypes.data)
         return oc[:n].copy(), op[:n + 1].copy()
+
+
+class UnitigResult(dict):
+    """kept[u8 per table node] (None for the reference), node_hash/node_cov/node_tip/edges of the filtered list,
+    unitig_begin[u+1], unitig_nodes[2*filtered id + fw]"""
+    __getattr__ = dict.__getitem__
+
+
+def normalise_unitigs(u):
+    """numbering-free form of a UnitigResult: nodes renumbered by ascending canonical hash, edges canonical in that
+    numbering and sorted, unitigs as direction-normalised tuples of (2*id + fw)."""
+    order = np.lexsort((u.node_hash[:, 0], u.node_hash[:, 1]))
+    new_id = np.empty(len(order), dtype=np.int64)
+    new_id[order] = np.arange(len(order))
+    e = u.edges.astype(np.int64).copy()
+    if len(e):
+        e[:, 0] = new_id[e[:, 0]]
+        e[:, 2] = new_id[e[:, 2]]
+        swap = (e[:, 2] < e[:, 0]) | ((e[:, 2] == e[:, 0]) & (e[:, 1] == 0) & (e[:, 3] == 0))
+        f, ffw, t, tfw = e[swap, 0].copy(), e[swap, 1].copy(), e[swap, 2].copy(), e[swap, 3].copy()
+        e[swap, 0], e[swap, 1], e[swap, 2], e[swap, 3] = t, 1 - tfw, f, 1 - ffw
+        e = sorted_edges(e)
+    seqs = []
+    b = u.unitig_begin.astype(np.int64)
+    for i in range(len(b) - 1):
+        raw = u.unitig_nodes[b[i]:b[i + 1]].astype(np.int64)
+        seq = tuple((2 * new_id[raw >> 1] + (raw & 1)).tolist())
+        rev = tuple((x ^ 1) for x in reversed(seq))
+        seqs.append(min(seq, rev))
+    return dict(node_hash=u.node_hash[order], node_cov=u.node_cov[order], node_tip=u.node_tip[order], edges=e, unitigs=sorted(seqs))
+
+
+def compare_unitigs(a, b, what=""):
+    """a, b: UnitigResults; equal up to node / unitig numbering (circular unitigs also up to rotation)"""
+    na, nb = normalise_unitigs(a), normalise_unitigs(b)
+    for f in ("node_hash", "node_cov", "node_tip", "edges"):
+        assert na[f].shape == nb[f].shape and np.array_equal(na[f], nb[f]), f"{what}: filtered {f} differ ({na[f].shape} vs {nb[f].shape})"
+    if na["unitigs"] != nb["unitigs"]:
+        def rot(seq):
+            out = []
+            for s in (seq, tuple((x ^ 1) for x in reversed(seq))):
+                i = min(range(len(s)), key=lambda j: s[j] >> 1)
+                out.append(s[i:] + s[:i])
+            return min(out)
+        sa, sb = set(na["unitigs"]), set(nb["unitigs"])
+        links = set((int(r[0]) * 2 + int(r[1]), int(r[2]) * 2 + int(r[3])) for r in na["edges"]) | set(((int(r[2]) * 2 + int(r[3])) ^ 1, (int(r[0]) * 2 + int(r[1])) ^ 1) for r in na["edges"])
+        for s in (sa ^ sb):
+            assert (s[-1], s[0]) in links, f"{what}: unitig differs and is not circular: {s[:6]}... len {len(s)}"
+        assert sorted(rot(s) for s in sa - sb) == sorted(rot(s) for s in sb - sa), f"{what}: circular unitigs differ"
+    assert len(na["unitigs"]) == len(nb["unitigs"]), f"{what}: unitig count"
 
 
 class Variants:

@@ -139,3 +139,16 @@ def test_hpc_variants_equal_reference(oracle, reference, tmp_path, mode, k, w):
     compare_hashed(got, want, f"variants {mode} k={k}")
     assert not np.array_equal(got.hashes, plain.hashes)
     assert np.array_equal(got.positions, plain.positions)
+
+
+@pytest.mark.parametrize("mode,k,w,a,u", [("collapse-msat", 301, 30, 1, 2), ("hpc", 301, 30, 2, 2), ("hpc", 63, 33, 1, 3), ("collapse-msat", 101, 20, 2, 3.5), ("no", 63, 5, 1, 1)])
+def test_unitig_filter_equals_reference(oracle, reference, mode, k, w, a, u):
+    """rows a14 / f1: getUnitigGraph's abundance filter, HashList::filter and the unitig chains against the reference's
+    own getUnitigGraph (MBG/MBG.cpp:629-760) on the same reads"""
+    from oracle_lib import compare_unitigs
+    for reads in (workloads.coverage_reads(n_reads=40, error_ppm=4000), workloads.coverage_reads(seed=3, genome_len=20000, n_reads=12, error_ppm=10000),
+                  [workloads.repeat_rich(3, 6000), workloads.repeat_rich(3, 6000), workloads.repeat_rich(4, 3000)]):
+        table, got = oracle.run_unitigs(mode, k, w, reads, a, u)
+        want = reference.run_unitigs(mode, k, w, reads, a, u)
+        compare_unitigs(got, want, what=f"unitigs {mode} k={k} a={a} u={u}")
+        assert got.kept.sum() == len(got.node_cov) and len(got.kept) == len(table.node_cov)
