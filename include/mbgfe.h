@@ -93,7 +93,16 @@ enum {
 	MBGFE_NODE_HASHES = 5,/* mbgfe_hash128[] canonical hashes, ascending == node id order after sortByHash   */
 	MBGFE_NODE_COVERAGE = 6, /* uint32_t[] HashList::coverage                                                */
 	MBGFE_NODE_TIP = 7,   /* uint8_t[]   HashList::isTipKmer                                                 */
-	MBGFE_EDGES = 8       /* mbgfe_edge[] sorted by (from, from_fw descending, to, to_fw)                     */
+	MBGFE_EDGES = 8,      /* mbgfe_edge[] sorted by (from, from_fw descending, to, to_fw)                     */
+	/* after mbgfe_build_unitigs(): */
+	MBGFE_NODE_KEPT = 9,        /* uint8_t[]  per node of the table: survives the abundance filter (RankBitvector kept) */
+	MBGFE_F_NODE_HASHES = 10,   /* mbgfe_hash128[] the HashList after HashList::filter: kept nodes, order unchanged   */
+	MBGFE_F_NODE_COVERAGE = 11, /* uint32_t[]                                                                          */
+	MBGFE_F_NODE_TIP = 12,      /* uint8_t[]                                                                           */
+	MBGFE_F_EDGES = 13,         /* mbgfe_edge[] edges between kept nodes (every coverage), renumbered, same order      */
+	MBGFE_UNITIG_BEGIN = 14,    /* uint64_t[n_unitigs + 1] offsets into MBGFE_UNITIG_NODES                             */
+	MBGFE_UNITIG_NODES = 15,    /* uint32_t[] 2 * filtered node id + fw, in unitig order (UnitigGraph::unitigs)        */
+	MBGFE_F_NODE_UNITIG = 16    /* uint32_t[] unitig of each filtered node, 0xffffffff when its coverage is below -a   */
 };
 
 typedef struct {
@@ -110,8 +119,8 @@ typedef struct {
 	uint64_t h2d_bytes, d2h_bytes;       /* copied by the last upload / process / result download */
 	/* device time of the last run, milliseconds, CUDA events on the library's stream */
 	float ms_upload, ms_pack, ms_collapse, ms_msat, ms_select, ms_hash, ms_nodes, ms_edges, ms_process, ms_export;
-	uint32_t launches;                   /* kernels launched by the last mbgfe_process() */
-	uint32_t reserved;
+	uint32_t launches;                   /* kernels launched by the last mbgfe_process() / mbgfe_build_unitigs() */
+	float ms_unitigs;                    /* device time of the last mbgfe_build_unitigs() */
 } mbgfe_stats;
 
 typedef struct mbgfe mbgfe;
@@ -160,6 +169,19 @@ int mbgfe_run(mbgfe* h);
 uint64_t mbgfe_count(mbgfe* h, int what);
 const void* mbgfe_data(mbgfe* h, int what);
 int mbgfe_get_stats(const mbgfe* h, mbgfe_stats* out);
+
+/* The step after the table: getUnitigGraph (MBG/MBG.cpp:629-760) with oneCovHeuristic = keepGaps = false, i.e. what
+ * runMBG does in pass 1 (MBG/MBG.cpp:1558).  On the device, from the ordered table of the last run:
+ *   1. covered edges = edges with coverage >= kmer_abundance (getCoveredEdges, MBG/MBG.cpp:367-388)
+ *   2. every maximal non-branching chain (getUnitigHashes, MBG/MBG.cpp:305-320) whose mean k-mer coverage is
+ *      >= unitig_abundance keeps its nodes (checkUnitigHashes, MBG/MBG.cpp:322-344)       -> MBGFE_NODE_KEPT
+ *   3. HashList::filter (MBG/HashList.cpp:159-232)                                        -> MBGFE_F_*
+ *   4. unitigs = the chains of the filtered list over nodes with coverage >= kmer_abundance (MBG/MBG.cpp:689-760)
+ *      -> MBGFE_UNITIG_BEGIN / MBGFE_UNITIG_NODES / MBGFE_F_NODE_UNITIG.  The reference numbers and orients unitigs in
+ *      the order its sequential walk meets them (arrival order of the k-mers); here a unitig starts at its end with the
+ *      smaller node id (a circular one at its smallest node, forward) and unitigs are numbered by that first node.
+ * kmer_abundance == 0 takes mbgfe_params.kmer_abundance.  Needs the edge table and world == 1. */
+int mbgfe_build_unitigs(mbgfe* h, uint32_t kmer_abundance, double unitig_abundance);
 
 /* Device-side stopwatch on the library's stream (CUDA events): start, any number of calls, stop -> milliseconds. */
 int mbgfe_timer_start(mbgfe* h);

@@ -20,3 +20,21 @@ def run_frontend(mode, k, w, reads, library=None, flags=KEEP_CODES | KEEP_POSES,
         return res
     finally:
         fe.close()
+
+
+def run_frontend_unitigs(mode, k, w, reads, min_cov, min_unitig_cov, library=None, **kw):
+    """table + mbgfe_build_unitigs -> (RunResult of the table, UnitigResult)"""
+    from oracle_lib import UnitigResult
+    fe = MbgFrontEnd(k, w, mode, library=library, **kw)
+    try:
+        if isinstance(reads, tuple):
+            fe.add_reads(*reads)
+        else:
+            fe.add_read_list(reads)
+        fe.run()
+        table = RunResult(node_hash=fe.node_hashes(), node_cov=fe.node_coverage(), node_tip=fe.node_tip(), edges=fe.edges())
+        u = UnitigResult(fe.build_unitigs(min_cov, min_unitig_cov))
+        u["stats"] = fe.stats()
+        return table, u
+    finally:
+        fe.close()

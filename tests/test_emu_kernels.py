@@ -68,3 +68,29 @@ def test_emulated_hpc_variant_rehash(oracle, emu_library, mode, k, w, flags):
         compare_runs(got, want, what="emu variants")
     else:
         assert np.array_equal(got.hashes, want.hashes) and np.array_equal(got.node_hash, want.node_hash) and np.array_equal(got.node_cov, want.node_cov)
+
+
+def check_unitigs(got, want, what):
+    from oracle_lib import compare_unitigs
+    assert np.array_equal(got.kept, want.kept), f"{what}: kept flags differ"
+    compare_unitigs(got, want, what)
+    # internal consistency of the unitig arrays: a partition of the nodes with coverage >= -a
+    b = got.unitig_begin.astype(np.int64)
+    ids = got.unitig_nodes >> 1
+    assert len(np.unique(ids)) == len(ids)
+    for u in range(len(b) - 1):
+        assert np.all(got.node_unitig[ids[b[u]:b[u + 1]]] == u)
+
+
+@pytest.mark.parametrize("mode,k,w,a,u,which", [("collapse-msat", 301, 30, 1, 2, "coverage"), ("hpc", 63, 33, 2, 2, "repeats"), ("no", 63, 5, 1, 2, "circular")])
+def test_emulated_unitig_filter(oracle, emu_library, mode, k, w, a, u, which):
+    """rows a14 / f1 on the emulator build (the GPU versions are tests/test_gpu_parity.py::test_unitig_filter*)"""
+    from fe_helpers import run_frontend_unitigs
+    reads = {"coverage": lambda: workloads.coverage_reads(n_reads=16, error_ppm=4000),
+             "repeats": lambda: [workloads.repeat_rich(3, 4000), workloads.repeat_rich(3, 4000), workloads.repeat_rich(4, 2000)],
+             "circular": lambda: workloads.circular_reads(genome_len=1500, read_len=1200, step=300) + [workloads.lcg_bases(77, 800)]}[which]()
+    _, got = run_frontend_unitigs(mode, k, w, reads, a, u, library=emu_library)
+    _, want = oracle.run_unitigs(mode, k, w, reads, a, u)
+    check_unitigs(got, want, f"emu unitigs {mode} k={k} a={a} u={u}")
+    if which == "circular":
+        assert len(want.unitig_begin) == 2 and want.unitig_begin[1] > 100      # one circular unitig; the lone read is filtered out

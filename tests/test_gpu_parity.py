@@ -8,7 +8,7 @@ import pytest
 
 import workloads
 from fe_helpers import run_frontend
-from oracle_lib import MODES, RunResult, compare_runs
+from oracle_lib import MODES, RunResult, compare_runs, lcg_bases
 from verkko_b200.frontend import MbgFrontEnd
 
 pytestmark = pytest.mark.gpu
@@ -197,3 +197,73 @@ def test_hpc_variant_rehash(oracle, mode, k, w):
     fe.run()
     assert np.array_equal(fe.hashes(), plain.hashes)
     fe.close()
+
+
+def check_unitigs(got, want, what):
+    from oracle_lib import compare_unitigs
+    assert np.array_equal(got.kept, want.kept), f"{what}: kept flags differ"
+    compare_unitigs(got, want, what)
+    b = got.unitig_begin.astype(np.int64)
+    ids = got.unitig_nodes >> 1
+    assert len(np.unique(ids)) == len(ids), f"{what}: a node sits in two unitigs"
+    of = got.node_unitig[ids]
+    assert np.array_equal(of, np.repeat(np.arange(len(b) - 1), np.diff(b))), f"{what}: node -> unitig map"
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("mode,k,w,a,u", [("collapse-msat", 1001, 100, 1, 2), ("collapse-msat", 301, 30, 1, 2), ("hpc", 63, 33, 2, 2), ("collapse-msat", 101, 20, 2, 3.5),
+                                           ("no", 63, 5, 1, 1), ("hpc", 301, 30, 3, 2)])
+def test_unitig_filter_against_oracle(oracle, mode, k, w, a, u):
+    """rows a14 / f1: abundance filter (edges >= -a, chain mean >= -u), HashList::filter and the unitig chains, on the
+    device, against the oracle (itself pinned on the reference's getUnitigGraph in tests/test_oracle.py)"""
+    from fe_helpers import run_frontend_unitigs
+    big = workloads.coverage_reads(genome_len=120000, n_reads=200, len_min=9000, len_max=14000, error_ppm=3000) if k < 1001 else \
+        workloads.coverage_reads(genome_len=200000, n_reads=300, len_min=12000, len_max=20000, error_ppm=2000)
+    for reads in (big, workloads.coverage_reads(seed=3, genome_len=20000, n_reads=12, error_ppm=10000),
+                  [workloads.repeat_rich(3, 6000), workloads.repeat_rich(3, 6000), workloads.repeat_rich(4, 3000)]):
+        table, got = run_frontend_unitigs(mode, k, w, reads, a, u)
+        otable, want = oracle.run_unitigs(mode, k, w, reads, a, u)
+        assert np.array_equal(table.node_hash, otable.node_hash)
+        check_unitigs(got, want, f"unitigs {mode} k={k} a={a} u={u}")
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("mode,k,w,a,u", [("no", 63, 5, 1, 2), ("hpc", 63, 33, 1, 1), ("collapse-msat", 101, 20, 2, 2)])
+def test_unitig_filter_circular_genomes(oracle, mode, k, w, a, u):
+    """chains that are cycles (no tip, no branch): the ranking detects them by its round limit, cuts them in front of
+    their smallest node and ranks again; the reference starts them at that node too (MBG/MBG.cpp:682-690, 746-760)"""
+    from fe_helpers import run_frontend_unitigs
+    reads = workloads.circular_reads() + workloads.circular_reads(seed=10, genome_len=2000, read_len=1500, step=250) + [lcg_bases(77, 1500)]
+    _, got = run_frontend_unitigs(mode, k, w, reads, a, u)
+    _, want = oracle.run_unitigs(mode, k, w, reads, a, u)
+    check_unitigs(got, want, f"circular {mode} k={k}")
+    # circular unitigs start at their smallest node in forward orientation
+    b = got.unitig_begin.astype(np.int64)
+    for i in range(len(b) - 1):
+        seq = got.unitig_nodes[b[i]:b[i + 1]]
+        assert (seq[0] >> 1) == (seq >> 1).min() or (seq[-1] >> 1) > (seq[0] >> 1)
+
+
+@pytest.mark.gpu
+def test_unitig_filter_properties_at_scale():
+    """size-independent properties on a larger graph: kept nodes are exactly those of chains with mean coverage >= u;
+    unitigs partition the kept nodes; consecutive unitig nodes are joined by a covered edge"""
+    from fe_helpers import run_frontend_unitigs
+    reads = workloads.coverage_reads(genome_len=2000000, n_reads=3000, len_min=15000, len_max=20000, error_ppm=1000)
+    table, got = run_frontend_unitigs("collapse-msat", 1001, 100, reads, 1, 2)
+    assert len(got.kept) == len(table.node_cov) and got.kept.sum() == len(got.node_cov)
+    assert np.array_equal(got.node_hash, table.node_hash[got.kept == 1]) and np.array_equal(got.node_cov, table.node_cov[got.kept == 1])
+    b = got.unitig_begin.astype(np.int64)
+    assert b[-1] == len(got.unitig_nodes) == len(got.node_cov)
+    assert np.array_equal(np.sort(got.unitig_nodes >> 1), np.arange(len(got.node_cov)))
+    e = got.edges.astype(np.int64)
+    links = set(zip((2 * e[:, 0] + e[:, 1]).tolist(), (2 * e[:, 2] + e[:, 3]).tolist())) | set(zip(((2 * e[:, 2] + e[:, 3]) ^ 1).tolist(), ((2 * e[:, 0] + e[:, 1]) ^ 1).tolist()))
+    seq = got.unitig_nodes.astype(np.int64)
+    inner = np.ones(len(seq), bool)
+    inner[b[1:-1] - 1] = False
+    inner[-1] = False
+    pairs = list(zip(seq[:-1][inner[:-1]].tolist(), seq[1:][inner[:-1]].tolist()))
+    assert all(p in links for p in pairs)
+    # mean coverage of every kept chain is >= 2: check through unitig means being >= 2 is NOT implied (unitigs of the
+    # filtered list can be shorter), but every dropped node must have coverage-1 neighbours only in dropped chains
+    assert got.stats["ms_unitigs"] > 0

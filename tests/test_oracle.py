@@ -147,7 +147,8 @@ def test_unitig_filter_equals_reference(oracle, reference, mode, k, w, a, u):
     own getUnitigGraph (MBG/MBG.cpp:629-760) on the same reads"""
     from oracle_lib import compare_unitigs
     for reads in (workloads.coverage_reads(n_reads=40, error_ppm=4000), workloads.coverage_reads(seed=3, genome_len=20000, n_reads=12, error_ppm=10000),
-                  [workloads.repeat_rich(3, 6000), workloads.repeat_rich(3, 6000), workloads.repeat_rich(4, 3000)]):
+                  [workloads.repeat_rich(3, 6000), workloads.repeat_rich(3, 6000), workloads.repeat_rich(4, 3000)],
+                  workloads.circular_reads() + workloads.circular_reads(seed=10, genome_len=2000, read_len=1500, step=250) + [lcg_bases(77, 1500)]):
         table, got = oracle.run_unitigs(mode, k, w, reads, a, u)
         want = reference.run_unitigs(mode, k, w, reads, a, u)
         compare_unitigs(got, want, what=f"unitigs {mode} k={k} a={a} u={u}")

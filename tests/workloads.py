@@ -75,3 +75,18 @@ def long_tandem_reads(seed=5):
     for motif, copies, lead in ((b"AC", 900, 700), (b"ACG", 800, 1000), (b"ACGT", 300, 1019), (b"ACGTC", 500, 33), (b"ACGTCA", 400, 2040), (b"AC", 2000, 5)):
         reads.append(rnd(lead) + motif * copies + rnd(1500))
     return reads
+
+
+def circular_reads(seed=9, genome_len=3000, read_len=2500, step=300, both_strands=True):
+    """error-free reads tiled around a circular random genome: the k-mer graph is one cycle without tips or branches
+    (plus, with extra=..., whatever the caller appends), the case getUnitigGraph handles in its last loops"""
+    g = lcg_bases(seed, genome_len)
+    comp = {65: 84, 67: 71, 71: 67, 84: 65}
+    gg = g + g + g
+    reads = []
+    for i, off in enumerate(range(0, genome_len, step)):
+        r = gg[off:off + read_len]
+        if both_strands and i % 2:
+            r = bytes(comp[c] for c in reversed(r))
+        reads.append(r)
+    return reads

@@ -24,7 +24,7 @@ def _stale(target, sources):
 
 def build_mbgfe(force=False, verbose=False):
     target = os.path.join(HERE, "libmbgfe.so")
-    sources = [os.path.join(CSRC, "mbgfe.cu"), os.path.join(CSRC, "kernels.cuh"),
+    sources = [os.path.join(CSRC, "mbgfe.cu"), os.path.join(CSRC, "kernels.cuh"), os.path.join(CSRC, "graph.cuh"),
                os.path.join(HERE, "..", "include", "mbgfe.h")]
     if not force and not _stale(target, sources):
         return target

@@ -1,0 +1,208 @@
+// graph.cuh -- sm_100a device code of the step right after the k-mer table:
+// the abundance filter of getUnitigGraph, HashList::filter and the unitig chains.
+//
+//   getCoveredEdges                      MBG/MBG.cpp:367-388   edges with coverage >= -a in both directions
+//   getUnitigHashes / checkUnitigHashes  MBG/MBG.cpp:305-344   maximal non-branching chain; kept iff mean coverage >= -u
+//   getUnitigGraph                       MBG/MBG.cpp:629-760   which chains exist (oneCovHeuristic = keepGaps = false)
+//   HashList::filter                     MBG/HashList.cpp:159-232
+//
+// The reference walks every chain sequentially.  A chain is a connected component of the LINK relation
+//     x -> y   iff   out(x) = {y},  out(rev y) = {rev x}  and  y is not x's own node
+// over oriented nodes x = 2*id + fw (rev x = x ^ 1; out() = covered successors).  Links are mirrored (x -> y  <=>
+// rev y -> rev x), every oriented node has at most one link out and one in, so components are simple paths or cycles and
+// the walk order of the reference does not matter for which nodes share a chain.  Here every oriented node ranks itself
+// against the end of its chain by pointer doubling (Wyllie list ranking): after ceil(log2 L) rounds it knows the coverage
+// sum and node count from itself to the chain end and which oriented node that end is; a node's chain total is the sum
+// of its two directions minus itself.  Cycles never finish; they are detected by the round limit, cut in front of their
+// smallest node id (where the reference, which visits nodes in id order, starts them) and ranked again as paths.
+// All of it is 32-byte random access: bound by DRAM sector throughput like the table itself.
+#pragma once
+#include "kernels.cuh"
+
+namespace mbgfe_dev {
+
+constexpr uint32_t NO_LINK = 0xffffffffu;
+
+// one oriented node while ranking: everything from itself up to (not including) nxt
+struct __align__(32) ChainState
+{
+	unsigned long long acc;   // coverage sum
+	uint32_t cnt;             // nodes
+	uint32_t nxt;             // next oriented node not yet folded in, NO_LINK = reached the chain end
+	uint32_t last;            // last oriented node folded in
+	uint32_t lab;             // smallest node id folded in
+	uint32_t pad[2];
+};
+
+// getCoveredEdges (MBG/MBG.cpp:367-388): out-degree and one successor of every oriented node.  The table holds each edge
+// once, in canonical form; its mirror image is the same edge unless it is its own mirror (x -> rev x).
+__global__ void __launch_bounds__(256) k_graph_degrees(const EdgeRec* __restrict__ edges, uint64_t n_edges, uint32_t min_cov, uint32_t* __restrict__ deg, uint32_t* __restrict__ nb)
+{
+	for (uint64_t e = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; e < n_edges; e += (uint64_t)gridDim.x * blockDim.x)
+	{
+		const EdgeRec r = edges[e];
+		if (r.coverage < min_cov) continue;
+		const uint32_t x = 2 * r.from + r.from_fw, y = 2 * r.to + r.to_fw;
+		atomicAdd(deg + x, 1u);
+		nb[x] = y;
+		if ((y ^ 1) != x || (x ^ 1) != y)
+		{
+			atomicAdd(deg + (y ^ 1), 1u);
+			nb[y ^ 1] = x ^ 1;
+		}
+	}
+}
+
+// the link relation (the continuation test of getUnitigHashes, MBG/MBG.cpp:311-317; its `newPos == start` test only ends
+// cycles and is replaced by the cut below)
+__global__ void __launch_bounds__(256) k_graph_links(const uint32_t* __restrict__ deg, const uint32_t* __restrict__ nb, uint64_t n_oriented, uint32_t* __restrict__ link)
+{
+	for (uint64_t x = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; x < n_oriented; x += (uint64_t)gridDim.x * blockDim.x)
+	{
+		uint32_t l = NO_LINK;
+		if (deg[x] == 1)
+		{
+			const uint32_t y = nb[x];
+			if (deg[y ^ 1] == 1 && (y >> 1) != (uint32_t)(x >> 1)) l = y;
+		}
+		link[x] = l;
+	}
+}
+
+__global__ void __launch_bounds__(256) k_chain_init(const uint32_t* __restrict__ link, const uint32_t* __restrict__ cov, uint64_t n_oriented, ChainState* __restrict__ st)
+{
+	for (uint64_t x = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; x < n_oriented; x += (uint64_t)gridDim.x * blockDim.x)
+	{
+		ChainState s;
+		s.acc = cov[x >> 1]; s.cnt = 1; s.nxt = link[x]; s.last = (uint32_t)x; s.lab = (uint32_t)(x >> 1); s.pad[0] = 0; s.pad[1] = 0;
+		st[x] = s;
+	}
+}
+
+// one doubling round, out of place (a state is one 32-byte sector: one load of the own state, one random load)
+__global__ void __launch_bounds__(256) k_chain_jump(const ChainState* __restrict__ in, ChainState* __restrict__ out, uint64_t n_oriented, uint32_t* __restrict__ unfinished)
+{
+	bool open = false;
+	for (uint64_t x = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; x < n_oriented; x += (uint64_t)gridDim.x * blockDim.x)
+	{
+		ChainState s = in[x];
+		if (s.nxt != NO_LINK)
+		{
+			const ChainState t = in[s.nxt];
+			s.acc += t.acc; s.cnt += t.cnt; s.last = t.last; s.lab = min(s.lab, t.lab); s.nxt = t.nxt;
+			open |= s.nxt != NO_LINK;
+		}
+		out[x] = s;
+	}
+	if (open) *unfinished = 1;      // every writer stores the same value
+}
+
+// after the round limit only cycle members are unfinished, and lab is the smallest node id of their cycle.  The
+// reference starts a cycle at the forward orientation of its first unvisited node (MBG/MBG.cpp:682-690, 746-760), i.e.
+// of its smallest id: remove the link that enters (lab, fw) and its mirror image, the link that leaves (lab, bw).
+__global__ void __launch_bounds__(256) k_chain_cut(const ChainState* __restrict__ st, uint64_t n_oriented, uint32_t* __restrict__ link)
+{
+	for (uint64_t x = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; x < n_oriented; x += (uint64_t)gridDim.x * blockDim.x)
+	{
+		const ChainState s = st[x];
+		if (s.nxt == NO_LINK) continue;
+		if (link[x] == 2 * s.lab + 1 || (uint32_t)x == 2 * s.lab) link[x] = NO_LINK;
+	}
+}
+
+// checkUnitigHashes (MBG/MBG.cpp:322-344): kept iff (double) coverage sum / (double) chain length >= minUnitigCoverage
+__global__ void __launch_bounds__(256) k_chain_kept(const ChainState* __restrict__ st, const uint32_t* __restrict__ cov, uint64_t n_nodes, double min_unitig_cov, uint32_t* __restrict__ kept)
+{
+	for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n_nodes; i += (uint64_t)gridDim.x * blockDim.x)
+	{
+		const ChainState b = st[2 * i], f = st[2 * i + 1];
+		const double total = (double)(f.acc + b.acc - cov[i]);
+		const double n = (double)(f.cnt + b.cnt - 1);
+		kept[i] = (total / n >= min_unitig_cov) ? 1u : 0u;
+	}
+}
+
+// HashList::filter (MBG/HashList.cpp:159-232), nodes: kept nodes keep their order; new_id = exclusive scan of kept
+__global__ void __launch_bounds__(256) k_filter_nodes(const uint32_t* __restrict__ kept, const uint64_t* __restrict__ new_id, uint64_t n_nodes, const uint4* __restrict__ hash,
+	const uint32_t* __restrict__ cov, const uint8_t* __restrict__ tip, uint4* __restrict__ f_hash, uint32_t* __restrict__ f_cov, uint8_t* __restrict__ f_tip, uint8_t* __restrict__ kept8)
+{
+	for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n_nodes; i += (uint64_t)gridDim.x * blockDim.x)
+	{
+		kept8[i] = (uint8_t)kept[i];
+		if (!kept[i]) continue;
+		const uint64_t j = new_id[i];
+		f_hash[j] = hash[i]; f_cov[j] = cov[i]; f_tip[j] = tip[i];
+	}
+}
+
+// edges between kept nodes (every coverage), flags for the scan
+__global__ void __launch_bounds__(256) k_filter_edge_flags(const EdgeRec* __restrict__ edges, uint64_t n_edges, const uint32_t* __restrict__ kept, uint32_t* __restrict__ flag)
+{
+	for (uint64_t e = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; e < n_edges; e += (uint64_t)gridDim.x * blockDim.x)
+		flag[e] = (kept[edges[e].from] && kept[edges[e].to]) ? 1u : 0u;
+}
+
+// renumbering is monotone, so canonical form and order of the edge list survive
+__global__ void __launch_bounds__(256) k_filter_edges(const EdgeRec* __restrict__ edges, uint64_t n_edges, const uint32_t* __restrict__ flag, const uint64_t* __restrict__ at,
+	const uint64_t* __restrict__ new_id, EdgeRec* __restrict__ out)
+{
+	for (uint64_t e = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; e < n_edges; e += (uint64_t)gridDim.x * blockDim.x)
+	{
+		if (!flag[e]) continue;
+		EdgeRec r = edges[e];
+		r.from = (uint32_t)new_id[r.from]; r.to = (uint32_t)new_id[r.to];
+		out[at[e]] = r;
+	}
+}
+
+// Unitigs of the filtered list (getUnitigGraph's second block, MBG/MBG.cpp:689-760): the chains again, over nodes with
+// coverage >= -a.  The reference numbers and orients them by its walk order; here a unitig is read from its end with the
+// smaller node id (a cut cycle: from its smallest node, forward), and unitigs are numbered by the id of that first node.
+//   first[i]  oriented first node of i's unitig (NO_LINK when coverage < -a)
+//   start_len[i] = unitig length when i is that first node, else 0   (scanned into unitig_begin)
+__device__ __forceinline__ void unitig_place(const ChainState& b, const ChainState& f, uint32_t& first, uint32_t& pos, uint32_t& same)
+{
+	// in the direction of (i, fw) the unitig reads  A ... i ... B
+	const uint32_t A = b.last ^ 1, B = f.last;
+	same = (A >> 1) <= (B >> 1) ? 1u : 0u;
+	first = same ? A : (B ^ 1);
+	pos = same ? b.cnt - 1 : f.cnt - 1;
+}
+
+__global__ void __launch_bounds__(256) k_unitig_starts(const ChainState* __restrict__ st, const uint32_t* __restrict__ cov, uint64_t n_nodes, uint32_t min_cov,
+	uint32_t* __restrict__ is_start, uint32_t* __restrict__ start_len)
+{
+	for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n_nodes; i += (uint64_t)gridDim.x * blockDim.x)
+	{
+		uint32_t s = 0, len = 0;
+		if (cov[i] >= min_cov)
+		{
+			const ChainState b = st[2 * i], f = st[2 * i + 1];
+			uint32_t first, pos, same;
+			unitig_place(b, f, first, pos, same);
+			if ((first >> 1) == (uint32_t)i) { s = 1; len = f.cnt + b.cnt - 1; }
+		}
+		is_start[i] = s; start_len[i] = len;
+	}
+}
+
+// unitig_id = exclusive scan of is_start, unitig_at = exclusive scan of start_len (both indexed by node)
+__global__ void __launch_bounds__(256) k_unitig_write(const ChainState* __restrict__ st, const uint32_t* __restrict__ cov, uint64_t n_nodes, uint32_t min_cov,
+	const uint32_t* __restrict__ is_start, const uint64_t* __restrict__ unitig_id, const uint64_t* __restrict__ unitig_at,
+	uint64_t* __restrict__ unitig_begin, uint32_t* __restrict__ unitig_nodes, uint32_t* __restrict__ node_unitig)
+{
+	for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n_nodes; i += (uint64_t)gridDim.x * blockDim.x)
+	{
+		if (cov[i] < min_cov) { node_unitig[i] = NO_LINK; continue; }
+		const ChainState b = st[2 * i], f = st[2 * i + 1];
+		uint32_t first, pos, same;
+		unitig_place(b, f, first, pos, same);
+		const uint32_t head = first >> 1;
+		const uint64_t at = unitig_at[head];
+		unitig_nodes[at + pos] = 2 * (uint32_t)i + same;
+		node_unitig[i] = (uint32_t)unitig_id[head];
+		if (is_start[i]) unitig_begin[unitig_id[i]] = at;
+	}
+}
+
+}

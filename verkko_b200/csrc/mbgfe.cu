@@ -14,6 +14,7 @@
 #include <zlib.h>
 
 #include "kernels.cuh"
+#include "graph.cuh"
 #include "../../include/mbgfe.h"
 
 static_assert(sizeof(mbgfe_dev::EdgeRec) == sizeof(mbgfe_edge), "device edge record is the ABI edge record");
@@ -97,6 +98,16 @@ struct mbgfe
 	uint32_t id_base = 0;                                                    // nodes owned by lower ranks
 	bool nodes_ranked = false, edges_global = false;
 	DevBuf d_var_hash, d_var_offset, d_var_len_begin, d_var_len;       // hpc variants (mbgfe_set_variants), sorted
+	// mbgfe_build_unitigs: graph scratch (degrees, successor, link, two ranking states, flags, scans) and results
+	DevBuf d_g_deg, d_g_nb, d_g_link, d_g_st[2], d_g_kept, d_g_newid, d_g_flag, d_g_at, d_g_flag2, d_g_at2, d_g_flag_byte;
+	DevBuf d_f_hash, d_f_cov, d_f_tip, d_f_edges, d_u_begin, d_u_nodes, d_u_of_node;
+	bool have_unitigs = false;
+	uint64_t n_kept = 0, n_fedges = 0, n_unitigs = 0, n_unitig_nodes = 0;
+	std::vector<uint8_t> h_kept, h_f_tip;
+	std::vector<mbgfe_hash128> h_f_hash;
+	std::vector<uint32_t> h_f_cov, h_u_nodes, h_u_of_node;
+	std::vector<mbgfe_edge> h_f_edges;
+	std::vector<uint64_t> h_u_begin;
 	uint64_t n_var = 0;
 	DevBuf d_bucket_count, d_bucket_begin, d_scan_tot, d_scan_off;      // export: bucket tables and scan scratch
 	DevBuf d_node_hash_sorted, d_node_cov, d_node_tip, d_edges_sorted;    // export: final layout, device resident
@@ -294,6 +305,7 @@ void clear_results(mbgfe* h)
 	h->parts.clear(); h->h_codes.clear(); h->h_poses.clear(); h->h_positions.clear(); h->h_hashes.clear();
 	h->n_nodes_out = 0; h->n_edges_out = 0;
 	h->n_inst = 0;
+	h->have_unitigs = false;
 }
 
 // ---------------------------------------------------------------------------------------------- file input
@@ -451,7 +463,9 @@ void mbgfe_destroy(mbgfe* h)
 		&h->d_inst_pos, &h->d_inst_seg, &h->d_inst_flag, &h->d_inst_hash, &h->d_inst_slot, &h->d_pal_list, &h->d_nodes, &h->d_edges, &h->d_node_out,
 		&h->d_edge_out, &h->d_records, &h->d_recv, &h->d_bucket_count, &h->d_bucket_begin, &h->d_scan_tot, &h->d_scan_off, &h->d_node_hash_sorted, &h->d_node_cov,
 		&h->d_node_tip, &h->d_edges_sorted, &h->d_inst_packpos, &h->d_ids_out, &h->d_id_begin, &h->d_edge_records, &h->d_xbuf[0], &h->d_xbuf[1], &h->d_xbuf[2],
-		&h->d_xbuf[3], &h->d_var_hash, &h->d_var_offset, &h->d_var_len_begin, &h->d_var_len }) release(*b);
+		&h->d_xbuf[3], &h->d_var_hash, &h->d_var_offset, &h->d_var_len_begin, &h->d_var_len, &h->d_g_deg, &h->d_g_nb, &h->d_g_link, &h->d_g_st[0], &h->d_g_st[1],
+		&h->d_g_kept, &h->d_g_newid, &h->d_g_flag, &h->d_g_at, &h->d_g_flag2, &h->d_g_at2, &h->d_g_flag_byte, &h->d_f_hash, &h->d_f_cov, &h->d_f_tip, &h->d_f_edges,
+		&h->d_u_begin, &h->d_u_nodes, &h->d_u_of_node }) release(*b);
 	for (HostBuf* b : { &h->p_node_hashes, &h->p_node_cov, &h->p_node_tip, &h->p_edges }) release_host(*b);
 	for (auto& e : h->ev) if (e) cudaEventDestroy(e);
 	for (auto& e : h->piece_events) cudaEventDestroy(e);
@@ -1167,6 +1181,155 @@ int export_table(mbgfe* h)
 	return 0;
 }
 
+
+// ---- the step after the table: abundance filter + unitig chains (graph.cuh)
+
+unsigned grid_for(const mbgfe* h, uint64_t n) { return (unsigned)std::max<uint64_t>(1, std::min<uint64_t>((n + 255) / 256, (uint64_t)h->sm_count * 16)); }
+
+// degrees -> links -> pointer doubling; leaves the final states in d_g_st[*which].  cov/edges describe the graph to rank.
+int rank_chains(mbgfe* h, const EdgeRec* edges, uint64_t n_edges, const uint32_t* cov, uint64_t n_nodes, uint32_t min_cov, int* which, uint32_t& launches)
+{
+	const uint64_t n2 = 2 * n_nodes;
+	if (int rc = ensure(h, h->d_g_deg, n2 * 4 + 64)) return rc;
+	if (int rc = ensure(h, h->d_g_nb, n2 * 4 + 64)) return rc;
+	if (int rc = ensure(h, h->d_g_link, n2 * 4 + 64)) return rc;
+	for (int i = 0; i < 2; i++) if (int rc = ensure(h, h->d_g_st[i], (n2 + 1) * sizeof(ChainState))) return rc;
+	if (int rc = ensure(h, h->d_g_flag_byte, 64)) return rc;
+	CU(h, cudaMemsetAsync(h->d_g_deg.p, 0, n2 * 4 + 64, h->stream));
+	if (n_edges) { MBGFE_LAUNCH(k_graph_degrees, grid_for(h, n_edges), 256, 0, h->stream, edges, n_edges, min_cov, h->d_g_deg.as<uint32_t>(), h->d_g_nb.as<uint32_t>()); launches++; }
+	MBGFE_LAUNCH(k_graph_links, grid_for(h, n2), 256, 0, h->stream, h->d_g_deg.as<uint32_t>(), h->d_g_nb.as<uint32_t>(), n2, h->d_g_link.as<uint32_t>());
+	launches++;
+	uint32_t* flag = h->d_g_flag_byte.as<uint32_t>();
+	for (int attempt = 0; attempt < 2; attempt++)
+	{
+		int cur = 0;
+		MBGFE_LAUNCH(k_chain_init, grid_for(h, n2), 256, 0, h->stream, h->d_g_link.as<uint32_t>(), cov, n2, h->d_g_st[0].as<ChainState>());
+		launches++;
+		uint32_t open = 1;
+		for (int round = 0; round < 34 && open; round++)
+		{
+			CU(h, cudaMemsetAsync(flag, 0, 4, h->stream));
+			MBGFE_LAUNCH(k_chain_jump, grid_for(h, n2), 256, 0, h->stream, h->d_g_st[cur].as<ChainState>(), h->d_g_st[cur ^ 1].as<ChainState>(), n2, flag);
+			launches++;
+			cur ^= 1;
+			CU(h, cudaMemcpyAsync(&open, flag, 4, cudaMemcpyDeviceToHost, h->stream));
+			CU(h, cudaStreamSynchronize(h->stream));
+		}
+		*which = cur;
+		if (!open) return 0;
+		// what is still open after 2^34 steps is circular: cut every cycle in front of its smallest node, rank again
+		if (attempt == 1) return fail(h, MBGFE_E_STATE, "chain ranking did not terminate");
+		MBGFE_LAUNCH(k_chain_cut, grid_for(h, n2), 256, 0, h->stream, h->d_g_st[cur].as<ChainState>(), n2, h->d_g_link.as<uint32_t>());
+		launches++;
+	}
+	return 0;
+}
+
+template <typename T>
+int fetch(mbgfe* h, std::vector<T>& dst, const DevBuf& src, size_t count)
+{
+	dst.resize(count);
+	if (count) CU(h, cudaMemcpyAsync(dst.data(), src.p, count * sizeof(T), cudaMemcpyDeviceToHost, h->stream));
+	h->stats.d2h_bytes += count * sizeof(T);
+	return 0;
+}
+
+}
+
+extern "C" {
+
+// getUnitigGraph (MBG/MBG.cpp:629-760) without oneCovHeuristic / keepGaps, on the ordered table
+int mbgfe_build_unitigs(mbgfe* h, uint32_t kmer_abundance, double unitig_abundance)
+{
+	if (!h) return MBGFE_E_PARAM;
+	if (!h->processed || !h->have_table) return fail(h, MBGFE_E_STATE, "mbgfe_build_unitigs needs the k-mer table of a finished run");
+	if (h->prm.world != 1) return fail(h, MBGFE_E_STATE, "mbgfe_build_unitigs runs on a whole table (world == 1); gather the partitions first");
+	if (h->prm.flags & MBGFE_NO_EDGES) return fail(h, MBGFE_E_STATE, "mbgfe_build_unitigs needs the edge table");
+	if (kmer_abundance == 0) kmer_abundance = std::max<uint32_t>(1, h->prm.kmer_abundance);
+	if (int rc = export_table(h)) return rc;
+	const uint64_t n = h->n_nodes_out, m = h->n_edges_out;
+	h->have_unitigs = false;
+	uint32_t launches = 0;
+	tick(h, 12);
+	const EdgeRec* edges = h->d_edges_sorted.as<EdgeRec>();
+	const uint32_t* cov = h->d_node_cov.as<uint32_t>();
+	// ---- which nodes survive: chains over edges with coverage >= -a, mean coverage >= -u
+	int which = 0;
+	if (int rc = rank_chains(h, edges, m, cov, n, kmer_abundance, &which, launches)) return rc;
+	if (int rc = ensure(h, h->d_g_kept, (n + 1) * 4)) return rc;
+	if (int rc = ensure(h, h->d_g_newid, (n + 2) * 8)) return rc;
+	if (int rc = ensure(h, h->d_g_flag, (std::max(n, m) + 1) * 4)) return rc;
+	if (int rc = ensure(h, h->d_g_at, (std::max(n, m) + 2) * 8)) return rc;
+	if (int rc = ensure(h, h->d_g_flag2, (n + 1) * 4)) return rc;
+	if (int rc = ensure(h, h->d_g_at2, (n + 2) * 8)) return rc;
+	if (int rc = ensure(h, h->d_f_hash, (n + 1) * 16)) return rc;
+	if (int rc = ensure(h, h->d_f_cov, (n + 1) * 4)) return rc;
+	if (int rc = ensure(h, h->d_f_tip, n + 64)) return rc;
+	if (int rc = ensure(h, h->d_f_edges, (m + 1) * sizeof(EdgeRec))) return rc;
+	if (int rc = ensure(h, h->d_u_begin, (n + 2) * 8)) return rc;
+	if (int rc = ensure(h, h->d_u_nodes, (n + 1) * 4)) return rc;
+	if (int rc = ensure(h, h->d_u_of_node, (n + 1) * 4)) return rc;
+	uint64_t n_kept = 0, n_fedges = 0, n_unitigs = 0, n_unitig_nodes = 0;
+	if (n)
+	{
+		MBGFE_LAUNCH(k_chain_kept, grid_for(h, n), 256, 0, h->stream, h->d_g_st[which].as<ChainState>(), cov, n, unitig_abundance, h->d_g_kept.as<uint32_t>());
+		if (int rc = device_scan(h, h->d_g_kept.as<uint32_t>(), h->d_g_newid.as<uint64_t>(), (uint32_t)n)) return rc;
+		// ---- HashList::filter
+		uint8_t* kept8 = (uint8_t*)h->d_u_of_node.p;      // borrowed until the unitig pass writes it
+		MBGFE_LAUNCH(k_filter_nodes, grid_for(h, n), 256, 0, h->stream, h->d_g_kept.as<uint32_t>(), h->d_g_newid.as<uint64_t>(), n, h->d_node_hash_sorted.as<uint4>(), cov,
+			h->d_node_tip.as<uint8_t>(), h->d_f_hash.as<uint4>(), h->d_f_cov.as<uint32_t>(), h->d_f_tip.as<uint8_t>(), kept8);
+		launches += 5;
+		fetch(h, h->h_kept, h->d_u_of_node, n);
+		CU(h, cudaMemcpyAsync(&n_kept, h->d_g_newid.as<uint64_t>() + n, 8, cudaMemcpyDeviceToHost, h->stream));
+		if (m)
+		{
+			MBGFE_LAUNCH(k_filter_edge_flags, grid_for(h, m), 256, 0, h->stream, edges, m, h->d_g_kept.as<uint32_t>(), h->d_g_flag.as<uint32_t>());
+			if (int rc = device_scan(h, h->d_g_flag.as<uint32_t>(), h->d_g_at.as<uint64_t>(), (uint32_t)m)) return rc;
+			MBGFE_LAUNCH(k_filter_edges, grid_for(h, m), 256, 0, h->stream, edges, m, h->d_g_flag.as<uint32_t>(), h->d_g_at.as<uint64_t>(), h->d_g_newid.as<uint64_t>(), h->d_f_edges.as<EdgeRec>());
+			launches += 5;
+			CU(h, cudaMemcpyAsync(&n_fedges, h->d_g_at.as<uint64_t>() + m, 8, cudaMemcpyDeviceToHost, h->stream));
+		}
+		CU(h, cudaStreamSynchronize(h->stream));
+	}
+	else h->h_kept.clear();
+	// ---- unitigs of the filtered list
+	if (n_kept)
+	{
+		const uint32_t* fcov = h->d_f_cov.as<uint32_t>();
+		if (int rc = rank_chains(h, h->d_f_edges.as<EdgeRec>(), n_fedges, fcov, n_kept, kmer_abundance, &which, launches)) return rc;
+		const ChainState* st = h->d_g_st[which].as<ChainState>();
+		MBGFE_LAUNCH(k_unitig_starts, grid_for(h, n_kept), 256, 0, h->stream, st, fcov, n_kept, kmer_abundance, h->d_g_flag.as<uint32_t>(), h->d_g_flag2.as<uint32_t>());
+		if (int rc = device_scan(h, h->d_g_flag.as<uint32_t>(), h->d_g_at.as<uint64_t>(), (uint32_t)n_kept)) return rc;
+		if (int rc = device_scan(h, h->d_g_flag2.as<uint32_t>(), h->d_g_at2.as<uint64_t>(), (uint32_t)n_kept)) return rc;
+		MBGFE_LAUNCH(k_unitig_write, grid_for(h, n_kept), 256, 0, h->stream, st, fcov, n_kept, kmer_abundance, h->d_g_flag.as<uint32_t>(), h->d_g_at.as<uint64_t>(),
+			h->d_g_at2.as<uint64_t>(), h->d_u_begin.as<uint64_t>(), h->d_u_nodes.as<uint32_t>(), h->d_u_of_node.as<uint32_t>());
+		launches += 8;
+		CU(h, cudaMemcpyAsync(&n_unitigs, h->d_g_at.as<uint64_t>() + n_kept, 8, cudaMemcpyDeviceToHost, h->stream));
+		CU(h, cudaMemcpyAsync(&n_unitig_nodes, h->d_g_at2.as<uint64_t>() + n_kept, 8, cudaMemcpyDeviceToHost, h->stream));
+		CU(h, cudaStreamSynchronize(h->stream));
+		CU(h, cudaMemcpyAsync(h->d_u_begin.as<uint64_t>() + n_unitigs, &n_unitig_nodes, 8, cudaMemcpyHostToDevice, h->stream));
+	}
+	tick(h, 13);
+	fetch(h, h->h_f_hash, h->d_f_hash, n_kept);
+	fetch(h, h->h_f_cov, h->d_f_cov, n_kept);
+	fetch(h, h->h_f_tip, h->d_f_tip, n_kept);
+	fetch(h, h->h_f_edges, h->d_f_edges, n_fedges);
+	fetch(h, h->h_u_nodes, h->d_u_nodes, n_unitig_nodes);
+	fetch(h, h->h_u_of_node, h->d_u_of_node, n_kept ? n_kept : 0);
+	if (n_kept) fetch(h, h->h_u_begin, h->d_u_begin, n_unitigs + 1); else h->h_u_begin.assign(1, 0);
+	CU(h, cudaStreamSynchronize(h->stream));
+	CU(h, cudaGetLastError());
+	h->n_kept = n_kept; h->n_fedges = n_fedges; h->n_unitigs = n_unitigs; h->n_unitig_nodes = n_unitig_nodes;
+	h->stats.ms_unitigs = elapsed(h, 12, 13);
+	h->stats.launches = launches;
+	h->have_unitigs = true;
+	return 0;
+}
+
+}
+
+namespace {
+
 }
 
 extern "C" {
@@ -1182,6 +1345,11 @@ uint64_t mbgfe_count(mbgfe* h, int what)
 		case MBGFE_POSITIONS: case MBGFE_HASHES: return h->n_inst;
 		case MBGFE_NODE_HASHES: case MBGFE_NODE_COVERAGE: case MBGFE_NODE_TIP: return h->have_table ? h->stats.distinct : 0;
 		case MBGFE_EDGES: return (h->have_table && h->edge_slots) ? h->stats.distinct_edges : 0;
+		case MBGFE_NODE_KEPT: return h->have_unitigs ? h->h_kept.size() : 0;
+		case MBGFE_F_NODE_HASHES: case MBGFE_F_NODE_COVERAGE: case MBGFE_F_NODE_TIP: case MBGFE_F_NODE_UNITIG: return h->have_unitigs ? h->n_kept : 0;
+		case MBGFE_F_EDGES: return h->have_unitigs ? h->n_fedges : 0;
+		case MBGFE_UNITIG_BEGIN: return h->have_unitigs ? h->n_unitigs + 1 : 0;
+		case MBGFE_UNITIG_NODES: return h->have_unitigs ? h->n_unitig_nodes : 0;
 	}
 	return 0;
 }
@@ -1205,6 +1373,20 @@ const void* mbgfe_data(mbgfe* h, int what)
 		case MBGFE_NODE_COVERAGE: if (export_table(h)) return nullptr; return h->p_node_cov.p;
 		case MBGFE_NODE_TIP: if (export_table(h)) return nullptr; return h->p_node_tip.p;
 		case MBGFE_EDGES: if (export_table(h)) return nullptr; return h->p_edges.p;
+		case MBGFE_NODE_KEPT: case MBGFE_F_NODE_HASHES: case MBGFE_F_NODE_COVERAGE: case MBGFE_F_NODE_TIP: case MBGFE_F_NODE_UNITIG: case MBGFE_F_EDGES:
+		case MBGFE_UNITIG_BEGIN: case MBGFE_UNITIG_NODES:
+			if (!h->have_unitigs) { fail(h, MBGFE_E_STATE, "filtered table / unitigs requested before mbgfe_build_unitigs"); return nullptr; }
+			switch (what)
+			{
+				case MBGFE_NODE_KEPT: return h->h_kept.data();
+				case MBGFE_F_NODE_HASHES: return h->h_f_hash.data();
+				case MBGFE_F_NODE_COVERAGE: return h->h_f_cov.data();
+				case MBGFE_F_NODE_TIP: return h->h_f_tip.data();
+				case MBGFE_F_NODE_UNITIG: return h->h_u_of_node.data();
+				case MBGFE_F_EDGES: return h->h_f_edges.data();
+				case MBGFE_UNITIG_BEGIN: return h->h_u_begin.data();
+				default: return h->h_u_nodes.data();
+			}
 	}
 	fail(h, MBGFE_E_PARAM, "unknown result array %d", what);
 	return nullptr;
