@@ -352,6 +352,14 @@ def main():
                 e2e_parts[name] = e2e_parts.get(name, 0.0) + dt * 1e3 / args.e2e_steps
         st_e = fe.stats()
         h2d, d2h = st_up["h2d_bytes"], st_e["d2h_bytes"]
+    # ---- the step after the table (rows a14 / f1), outside the timed regions: abundance filter + unitig chains on the device
+    unitig_info = None
+    if world == 1:
+        fe.build_unitigs(1, 2.0)                      # Verkko's buildGraph flags: --kmer-abundance 1 --unitig-abundance 2
+        u = fe.build_unitigs(1, 2.0)
+        st_u = fe.stats()
+        unitig_info = {"ms": st_u["ms_unitigs"], "kmer_abundance": 1, "unitig_abundance": 2.0, "nodes": int(len(u["kept"])), "kept_nodes": int(len(u["node_cov"])),
+                       "kept_edges": int(len(u["edges"])), "unitigs": int(len(u["unitig_begin"]) - 1), "launches": st_u["launches"]}
     e2e_t = torch.tensor([float(np.mean(e2e_ms))], dtype=torch.float64, device="cuda")
     if world > 1:
         dist.all_reduce(e2e_t, op=dist.ReduceOp.MAX)
@@ -391,6 +399,12 @@ def main():
                          "peak_source": peak_src,
                          "all_kernels_GBps": {n: (b / (m * 1e-3) / 1e9 if m > 0 else None) for n, (b, m) in alg.items()}},
         }
+        if unitig_info:
+            line["unitig_stage"] = unitig_info
+        traffic_file = os.path.join(ROOT, "profiles", "ncu_traffic.json")
+        if os.path.exists(traffic_file) and args.scale == 1.0 and args.workload == "chr20":
+            # dram__bytes_read.sum + dram__bytes_write.sum of one launch, from the committed `ncu --set full` capture of this workload
+            line["roofline"]["traffic"] = json.load(open(traffic_file)).get(dominant)
         if world == 1 and not args.no_cpu_baseline:
             line["cpu_baseline"] = cpu_baseline(wl, args.scale)
         print(json.dumps(line))
