@@ -35,6 +35,7 @@
 
 struct uint3 { unsigned x, y, z; };
 struct uint4 { unsigned x, y, z, w; };
+struct uint2 { unsigned x, y; };
 struct alignas(16) ulonglong2 { unsigned long long x, y; };
 struct alignas(32) ulonglong4 { unsigned long long x, y, z, w; };
 inline uint4 make_uint4(unsigned x, unsigned y, unsigned z, unsigned w) { uint4 v = { x, y, z, w }; return v; }

@@ -94,3 +94,12 @@ def test_emulated_unitig_filter(oracle, emu_library, mode, k, w, a, u, which):
     check_unitigs(got, want, f"emu unitigs {mode} k={k} a={a} u={u}")
     if which == "circular":
         assert len(want.unitig_begin) == 2 and want.unitig_begin[1] > 100      # one circular unitig; the lone read is filtered out
+
+
+def test_emulated_hash_in_groups(oracle, emu_library, monkeypatch):
+    """k_kmer_hash_lanes with a staging area much smaller than a read: k-mers are hashed in groups of consecutive ones"""
+    monkeypatch.setenv("MBGFE_HASH_LANES", "1")
+    monkeypatch.setenv("MBGFE_HASH_CAP", "400")
+    reads = workloads.coverage_reads(n_reads=6)
+    compare_runs(run_frontend("collapse-msat", 301, 30, reads, library=emu_library), oracle.run("collapse-msat", 301, 30, reads), what="emu grouped hash")
+    compare_runs(run_frontend("hpc", 63, 33, reads, library=emu_library), oracle.run("hpc", 63, 33, reads), what="emu grouped hash hpc")

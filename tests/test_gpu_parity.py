@@ -267,3 +267,15 @@ def test_unitig_filter_properties_at_scale():
     # mean coverage of every kept chain is >= 2: check through unitig means being >= 2 is NOT implied (unitigs of the
     # filtered list can be shorter), but every dropped node must have coverage-1 neighbours only in dropped chains
     assert got.stats["ms_unitigs"] > 0
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("cap", ["", "700"])
+def test_lane_per_kmer_hash_kernel(oracle, monkeypatch, cap):
+    """the alternative k-mer hash kernel (MBGFE_HASH_LANES=1), whole reads and groups of k-mers"""
+    monkeypatch.setenv("MBGFE_HASH_LANES", "1")
+    if cap:
+        monkeypatch.setenv("MBGFE_HASH_CAP", cap)
+    reads = workloads.coverage_reads(n_reads=12)
+    for mode, k, w in (("collapse-msat", 1001, 100), ("hpc", 63, 33), ("no", 255, 225)):
+        compare_runs(run_frontend(mode, k, w, reads), oracle.run(mode, k, w, reads), what=f"lanes hash {mode} k={k}")

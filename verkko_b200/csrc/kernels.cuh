@@ -1236,6 +1236,109 @@ __global__ void __launch_bounds__(HASH_NT) k_kmer_hash(const uint64_t* __restric
 	}
 }
 
+// K3b2, lane-per-k-mer form (alternative, selected with MBGFE_HASH_LANES=1; same results, same speed on the bench).
+// The chain h = (h ^ f(block)) * M is a serial dependency of (k+1)/8 steps per k-mer and direction; k_kmer_hash above
+// shares f between overlapping k-mers but keeps only the ~90 k-mers of a tile in flight while everybody else waits at its
+// barriers, so it runs at the latency of that chain.  Here every thread is a chain all the time: a CTA of two warps
+// stages the codes its k-mers span (both directions, as aligned 64-bit pairs) in shared memory, then each lane walks one
+// (k-mer, direction) after the other, computing f itself -- three 64-bit multiplications per block instead of one and a
+// shared two, no barrier inside.  Measured (chr20 bench, ncu): 5.16 ms, the same as the tiled kernel, and bound by the
+// integer-multiply half of the fma pipe (sm__pipe_fmaheavy_cycles_active 79 %): a 64-bit product is 3 IMAD + 1 add, the
+// kernel does 11.7 G of them.  A read whose span exceeds the staging capacity is done in groups of consecutive k-mers.
+// cap_codes = staged codes per direction (multiple of 8); dynamic shared memory = 4 * cap_codes bytes.
+constexpr int HASHL_NT = 64;
+
+__global__ void __launch_bounds__(HASHL_NT) k_kmer_hash_lanes(const uint64_t* __restrict__ seg_out_base, const uint16_t* __restrict__ codes, const uint16_t* __restrict__ rrc,
+	const uint32_t* __restrict__ inst_pos, const uint64_t* __restrict__ sel_begin, uint64_t inst_cap, uint64_t* __restrict__ inst_hash, uint32_t k, uint32_t cap_codes)
+{
+	MBGFE_DYN_SMEM(smem_raw);
+	const uint32_t g = blockIdx.x;
+	const uint64_t begin = sel_begin[g], end = sel_begin[g + 1];
+	if (end <= begin || end > inst_cap) return;
+	const uint32_t n_sel = (uint32_t)(end - begin);
+	const uint64_t ob = seg_out_base[g];
+	const uint32_t cap = (uint32_t)(seg_out_base[g + 1] - ob);
+	const uint32_t* __restrict__ pos = inst_pos + begin;
+	uint64_t* __restrict__ out = inst_hash + 2 * begin;
+	const uint32_t half = (k + 1) / 2;
+	const uint32_t nb = half / 4, rem = half & 3;
+	uint64_t h_init;
+	{ Murmur mm; mm.init((uint64_t)half * 2); h_init = mm.h; }
+	uint2* const s_fw = (uint2*)smem_raw;                 // 4 codes per pair
+	uint2* const s_rc = s_fw + cap_codes / 4;
+	// positions a group may span: what fits, evened out over the groups the read needs (no short last group)
+	const uint32_t room_max = cap_codes - half - 16;
+	const uint32_t reach_all = pos[n_sel - 1] - pos[0] + 1;
+	const uint32_t n_groups = (reach_all + room_max - 1) / room_max;
+	const uint32_t room = min(room_max, (reach_all + n_groups - 1) / n_groups + 64);
+	uint32_t i0 = 0;
+	while (i0 < n_sel)
+	{
+		// ---- group [i0, i1): consecutive k-mers whose codes fit the staging area (every thread finds the same i1)
+		const uint32_t p0 = pos[i0];
+		uint32_t i1 = n_sel;
+		if (pos[n_sel - 1] - p0 > room)
+		{
+			uint32_t lo = i0 + 1, hi = n_sel;                // first index whose position is out of reach
+			while (lo < hi) { const uint32_t mid = (lo + hi) >> 1; if (pos[mid] - p0 > room) hi = mid; else lo = mid + 1; }
+			i1 = lo;
+		}
+		const uint32_t p1 = pos[i1 - 1];
+		// staged ranges start on a multiple of 8 codes (16 bytes): forward from p0, reverse from the start of the LAST k-mer
+		const uint32_t a0f = p0 & ~7u, a0r = (cap - k - p1) & ~7u;
+		const uint32_t n_stage = ((p1 - p0) + half + 16 + 7) >> 3;       // uint4 per direction
+		for (uint32_t q = threadIdx.x; q < 2 * n_stage; q += HASHL_NT)
+		{
+			const uint32_t d = q >= n_stage ? 1 : 0, j = q - d * n_stage;
+			const uint32_t o = (d ? a0r : a0f) + 8 * j;
+			uint4 v = make_uint4(0, 0, 0, 0);
+			if (o < cap) v = __ldg((const uint4*)((d ? rrc : codes) + ob + o));
+			*(uint4*)((d ? s_rc : s_fw) + 2 * j) = v;
+		}
+		__syncthreads();
+		// ---- chains: 2 * (i1 - i0) of them, lanes take them round robin (a warp's lanes: neighbouring k-mers, one direction)
+		const uint32_t n_chain = 2 * (i1 - i0);
+		for (uint32_t c = threadIdx.x; c < n_chain; c += HASHL_NT)
+		{
+			const uint32_t d = c >= (i1 - i0) ? 1 : 0;
+			const uint32_t i = i0 + c - d * (i1 - i0);
+			const uint32_t st = d ? cap - k - pos[i] : pos[i];
+			const uint32_t rel = st - (d ? a0r : a0f);
+			const uint2* __restrict__ pp = (d ? s_rc : s_fw) + (rel >> 2);
+			const bool wodd = (rel & 2) != 0;
+			const uint32_t sh = (rel & 1) * 16;
+			uint64_t hcur = h_init;
+			uint2 pa = pp[0];
+#pragma unroll 4
+			for (uint32_t t = 0; t < nb; t++)
+			{
+				const uint2 pb = pp[t + 1];
+				const uint32_t x0 = wodd ? pa.y : pa.x, x1 = wodd ? pb.x : pa.y, x2 = wodd ? pb.y : pb.x;
+#ifdef MBGFE_EMU_BUILD
+				const uint32_t lo = sh ? ((x0 >> 16) | (x1 << 16)) : x0, hi = sh ? ((x1 >> 16) | (x2 << 16)) : x1;
+#else
+				const uint32_t lo = __funnelshift_r(x0, x1, sh), hi = __funnelshift_r(x1, x2, sh);
+#endif
+				uint64_t wd = u64_of(lo, hi);
+				wd *= Murmur::MUL; wd ^= wd >> 47; wd *= Murmur::MUL;
+				hcur ^= wd; hcur *= Murmur::MUL;
+				pa = pb;
+			}
+			Murmur mm; mm.h = hcur;
+			if (rem)
+			{
+				const uint16_t* __restrict__ arr = (d ? rrc : codes) + ob;
+				uint64_t wd = 0;
+				for (uint32_t j = 0; j < rem; j++) wd |= (uint64_t)arr[st + 4 * nb + j] << (16 * j);
+				mm.tail(wd);
+			}
+			out[2 * i + d] = mm.finish();
+		}
+		__syncthreads();
+		i0 = i1;
+	}
+}
+
 // ------------------------------------------------------------------ a11: hpc-variant re-hash (pass 3 of runMBG)
 
 // The variant map of ReadpartIterator (MBG/ReadHelper.h:250, filled by addHpcVariants, MBG/ReadHelper.cpp:63-70) as

@@ -66,6 +66,7 @@ struct mbgfe
 	int sm_count = 148;
 	size_t max_smem = 0;
 	SelectPlan plan;
+	uint32_t hash_cap_codes = 9216;                   // k_kmer_hash_lanes: codes staged per direction
 
 	// code tables
 	DevBuf tab_hash, tab_pair, tab_comp;
@@ -449,6 +450,11 @@ int mbgfe_create(const mbgfe_params* prm, mbgfe** out)
 		ensure(h, h->d_counters, (CTR_OWNER + prm->world + 8) * 8)) return bail(MBGFE_E_CUDA);
 	MBGFE_LAUNCH(k_build_tables, (MAX_CODE + 255) / 256, 256, 0, h->stream, h->tab_hash.as<uint64_t>(), h->tab_pair.as<uint4>(), h->tab_comp.as<uint16_t>());
 	cudaFuncSetAttribute(k_select<NT_SELECT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->plan.smem_bytes);
+	// staged codes per direction of k_kmer_hash_lanes (4096: best on the bench, 13 CTAs per SM); large k needs room for
+	// at least one k-mer
+	h->hash_cap_codes = std::max<uint32_t>(4096, (((prm->k + 1) / 2 + 16 + 1024) + 7) & ~7u);
+	if (const char* e = getenv("MBGFE_HASH_CAP")) h->hash_cap_codes = std::max<uint32_t>((uint32_t)atoi(e) & ~7u, (((prm->k + 1) / 2 + 16 + 64) + 7) & ~7u);
+	cudaFuncSetAttribute(k_kmer_hash_lanes, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(4 * h->hash_cap_codes));
 	if (cudaStreamSynchronize(h->stream) != cudaSuccess || cudaGetLastError() != cudaSuccess)
 		return bail(fail(h, MBGFE_E_CUDA, "table kernel failed: is this an sm_100 device?"));
 	*out = h;
@@ -704,8 +710,13 @@ void launch_list_hash(mbgfe* h, uint32_t g0, uint32_t g1, uint64_t n_hint, uint3
 	const uint64_t* sb = h->d_sel_begin.as<uint64_t>();
 	MBGFE_LAUNCH(k_list_selected<NT_LIST>, g1 - g0, NT_LIST, 0, h->stream, st, g0, h->d_selmask.as<uint32_t>(), h->d_seg_c2.as<uint32_t>() + g0, h->d_seg_nsel.as<uint32_t>() + g0,
 		sb + g0, h->d_inst_pos.as<uint32_t>(), h->d_inst_seg.as<uint32_t>(), h->d_inst_flag.as<uint8_t>(), k, h->inst_cap, ctr + CTR_OVERFLOW);
-	MBGFE_LAUNCH(k_kmer_hash, g1 - g0, HASH_NT, 0, h->stream, h->d_seg_out.as<uint64_t>() + g0, h->d_codes.as<uint16_t>(), h->d_rrc.as<uint16_t>(), h->d_inst_pos.as<uint32_t>(),
-		sb + g0, h->inst_cap, h->d_inst_hash.as<uint64_t>(), k);
+	const bool lanes_hash = getenv("MBGFE_HASH_LANES") != nullptr;          // the lane-per-k-mer kernel, kept for comparison
+	if (!lanes_hash)
+		MBGFE_LAUNCH(k_kmer_hash, g1 - g0, HASH_NT, 0, h->stream, h->d_seg_out.as<uint64_t>() + g0, h->d_codes.as<uint16_t>(), h->d_rrc.as<uint16_t>(), h->d_inst_pos.as<uint32_t>(),
+			sb + g0, h->inst_cap, h->d_inst_hash.as<uint64_t>(), k);
+	else
+		MBGFE_LAUNCH(k_kmer_hash_lanes, g1 - g0, HASHL_NT, 4 * h->hash_cap_codes, h->stream, h->d_seg_out.as<uint64_t>() + g0, h->d_codes.as<uint16_t>(), h->d_rrc.as<uint16_t>(),
+			h->d_inst_pos.as<uint32_t>(), sb + g0, h->inst_cap, h->d_inst_hash.as<uint64_t>(), k, h->hash_cap_codes);
 	const unsigned pal_grid = n_hint ? (unsigned)((n_hint + 255) / 256) : (unsigned)h->sm_count * 4;
 	MBGFE_LAUNCH(k_find_palindromes, pal_grid, 256, 0, h->stream, h->d_inst_hash.as<uint64_t>(), sb + g0, sb + g1, h->inst_cap, ctr + CTR_PALINDROME, h->d_pal_list.as<uint64_t>(), PAL_CAP);
 	launches += 3;
