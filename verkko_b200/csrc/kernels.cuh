@@ -809,8 +809,10 @@ __global__ void __launch_bounds__(NT) k_select(SegTable seg, const uint16_t* __r
 	uint32_t curBp = (NBP - (LH >> 3) % NBP) % NBP;                // pq block of prefix index t0 - LH
 	uint32_t curBh = (NBH - (LH >> 3) % NBH) % NBH;                // h block of s-mer t0 - LH
 	uint32_t curC = (NBH - ((LH + LW) >> 3) % NBH) % NBH;          // h block of k-mer t0 - LH - LW
-	Xor2 carry = { 0, 0 };
 	uint32_t my_sel = 0;
+	// the codes of the next tile are requested one tile ahead, so that their latency hides behind stages B and C
+	uint4 cw_next = make_uint4(0, 0, 0, 0);
+	if (8 * threadIdx.x < n) cw_next = __ldg((const uint4*)(c + 8 * threadIdx.x));
 	__syncthreads();
 	for (uint32_t t0 = 0; t0 < n + LH + LW; t0 += T)
 	{
@@ -818,8 +820,9 @@ __global__ void __launch_bounds__(NT) k_select(SegTable seg, const uint16_t* __r
 		if (t0 < n)
 		{
 			const uint32_t j0 = t0 + 8 * threadIdx.x;
-			uint4 cw = make_uint4(0, 0, 0, 0);
-			if (j0 < n) cw = __ldg((const uint4*)(c + j0));
+			const uint4 cw = cw_next;
+			cw_next = make_uint4(0, 0, 0, 0);
+			if (j0 + T < n) cw_next = __ldg((const uint4*)(c + j0 + T));
 			const uint32_t cws[4] = { cw.x, cw.y, cw.z, cw.w };
 			uint64_t hf[8], hb[8];
 #pragma unroll
@@ -845,9 +848,13 @@ __global__ void __launch_bounds__(NT) k_select(SegTable seg, const uint16_t* __r
 			uint64_t ep = __shfl_up_sync(FULL, ip, 1), eq = __shfl_up_sync(FULL, iq, 1);
 			if (lane == 0) { ep = 0; eq = 0; }
 			__syncthreads();
-			Xor2 wbase = carry;
+			// prefix at the start of the tile: index t0 sits at offset 0 of the block stage A writes first (left there by
+			// the previous tile; P'[0] = Q'[0] = 0 before the first).  A tile spans a multiple of 64 positions, so it
+			// enters every warp's base as it is.
+			Xor2 wbase;
+			{ const uint4 v = pq[(size_t)curA * 9]; wbase.a = u64_of(v.x, v.y); wbase.b = u64_of(v.z, v.w); }
 #pragma unroll
-			for (int i = 0; i < NT / 32; i++) { const Xor2 t = warp_tot[i]; if (i < (int)wid) { wbase.a ^= t.a; wbase.b ^= t.b; } carry.a ^= t.a; carry.b ^= t.b; }
+			for (int i = 0; i < NT / 32 - 1; i++) { const Xor2 t = warp_tot[i]; if (i < (int)wid) { wbase.a ^= t.a; wbase.b ^= t.b; } }
 			uint64_t pv = rotl_c(wbase.a, (8 * lane) & 63) ^ ep, qv = rotr_c(wbase.b, (8 * lane) & 63) ^ eq;
 			// prefix index j0+e+1 lives in block curA + thread (offsets 1..7) and the next block (offset 0)
 			uint32_t blk = curA + threadIdx.x; if (blk >= NBP) blk -= NBP;

@@ -55,6 +55,8 @@ struct Timer
 
 }
 
+constexpr int NT_SELECT_DEFAULT = 128;
+
 struct mbgfe
 {
 	mbgfe_params prm;
@@ -66,6 +68,7 @@ struct mbgfe
 	int sm_count = 148;
 	size_t max_smem = 0;
 	SelectPlan plan;
+	int select_nt = NT_SELECT_DEFAULT;                              // threads per CTA of k_select
 	uint32_t hash_cap_codes = 9216;                   // k_kmer_hash_lanes: codes staged per direction
 
 	// code tables
@@ -178,7 +181,7 @@ bool is_acgt(char c) { c &= (char)0xdf; return c == 'A' || c == 'C' || c == 'G' 
 enum { CTR_NONACGT = 0, CTR_PALINDROME = 1, CTR_DISTINCT = 2, CTR_EDGES = 3, CTR_CURSOR = 4 /* and 5 */, CTR_OVERFLOW = 6, CTR_OWNER = 8 /* .. 8+world */ };
 constexpr uint64_t PAL_CAP = 1 << 20;
 
-constexpr int NT_COLLAPSE = 128, NT_MSAT = 128, NT_SELECT = 256, NT_LIST = 128;
+constexpr int NT_COLLAPSE = 128, NT_MSAT = 128, NT_SELECT = 128, NT_LIST = 128;   // k_select: 128 beats 64 / 256 / 512 on the bench (7.1 / 7.6 / 8.1 / 10.8 ms)
 
 SegTable seg_table(const mbgfe* h)
 {
@@ -261,14 +264,14 @@ int upload_segments(mbgfe* h)
 	return 0;
 }
 
-SelectPlan make_plan(uint32_t k, uint32_t w, size_t max_smem, bool& ok)
+SelectPlan make_plan(uint32_t k, uint32_t w, size_t max_smem, bool& ok, uint32_t nt = NT_SELECT)
 {
 	SelectPlan p;
-	const uint32_t s = k - w + 1, a = (w - 1) >> 3, T = NT_SELECT * 8;
+	const uint32_t s = k - w + 1, a = (w - 1) >> 3, T = nt * 8;
 	p.LH = (s - 1 + 7) & ~7u;
 	p.LW = 8 * (a + 1);
 	p.NBP = (p.LH + T) / 8 + 2;
-	p.NBH = NT_SELECT + p.LW / 8 + 2;
+	p.NBH = nt + p.LW / 8 + 2;
 	const size_t bytes = (size_t)p.NBP * 9 * 16 + (size_t)p.NBH * 10 * 8 + (size_t)p.NBH * 16 + 64;
 	p.smem_bytes = (uint32_t)bytes;
 	ok = bytes + 2048 <= max_smem;
@@ -449,7 +452,17 @@ int mbgfe_create(const mbgfe_params* prm, mbgfe** out)
 	if (ensure(h, h->tab_hash, MAX_CODE * 8) || ensure(h, h->tab_pair, MAX_CODE * 16) || ensure(h, h->tab_comp, MAX_CODE * 2) ||
 		ensure(h, h->d_counters, (CTR_OWNER + prm->world + 8) * 8)) return bail(MBGFE_E_CUDA);
 	MBGFE_LAUNCH(k_build_tables, (MAX_CODE + 255) / 256, 256, 0, h->stream, h->tab_hash.as<uint64_t>(), h->tab_pair.as<uint4>(), h->tab_comp.as<uint16_t>());
+	if (const char* e = getenv("MBGFE_SELECT_NT"))
+	{
+		// experiment knob: threads per CTA of k_select (64 / 256 / 512 instead of 128); the tile is 8 codes per thread
+		const int nt = atoi(e);
+		bool ok2 = false;
+		if (nt == 64 || nt == 256 || nt == 512) { SelectPlan p2 = make_plan(prm->k, prm->w, h->max_smem, ok2, (uint32_t)nt); if (ok2) { h->plan = p2; h->select_nt = nt; } }
+	}
 	cudaFuncSetAttribute(k_select<NT_SELECT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->plan.smem_bytes);
+	cudaFuncSetAttribute(k_select<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->plan.smem_bytes);
+	cudaFuncSetAttribute(k_select<256>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->plan.smem_bytes);
+	cudaFuncSetAttribute(k_select<512>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->plan.smem_bytes);
 	// staged codes per direction of k_kmer_hash_lanes (4096: best on the bench, 13 CTAs per SM); large k needs room for
 	// at least one k-mer
 	h->hash_cap_codes = std::max<uint32_t>(4096, (((prm->k + 1) / 2 + 16 + 1024) + 7) & ~7u);
@@ -650,8 +663,18 @@ uint32_t launch_front(mbgfe* h, uint32_t g0, uint32_t cnt, bool timed)
 		MBGFE_LAUNCH(k_unpack_symbols<NT_MSAT>, cnt, NT_MSAT, 0, h->stream, st, h->d_sym.as<uint64_t>(), c1, h->d_codes.as<uint16_t>(),
 			h->d_rrc.as<uint16_t>(), c2, (const uint32_t*)pos1, pos2);
 	if (timed) tick(h, 5);
-	MBGFE_LAUNCH(k_select<NT_SELECT>, cnt, NT_SELECT, h->plan.smem_bytes, h->stream, st, h->d_codes.as<uint16_t>(), c2, h->tab_pair.as<uint4>(),
-		h->d_selmask.as<uint8_t>(), h->d_seg_nsel.as<uint32_t>() + g0, k, w, h->plan);
+	if (h->select_nt == 64)
+		MBGFE_LAUNCH(k_select<64>, cnt, 64, h->plan.smem_bytes, h->stream, st, h->d_codes.as<uint16_t>(), c2, h->tab_pair.as<uint4>(),
+			h->d_selmask.as<uint8_t>(), h->d_seg_nsel.as<uint32_t>() + g0, k, w, h->plan);
+	else if (h->select_nt == 256)
+		MBGFE_LAUNCH(k_select<256>, cnt, 256, h->plan.smem_bytes, h->stream, st, h->d_codes.as<uint16_t>(), c2, h->tab_pair.as<uint4>(),
+			h->d_selmask.as<uint8_t>(), h->d_seg_nsel.as<uint32_t>() + g0, k, w, h->plan);
+	else if (h->select_nt == 512)
+		MBGFE_LAUNCH(k_select<512>, cnt, 512, h->plan.smem_bytes, h->stream, st, h->d_codes.as<uint16_t>(), c2, h->tab_pair.as<uint4>(),
+			h->d_selmask.as<uint8_t>(), h->d_seg_nsel.as<uint32_t>() + g0, k, w, h->plan);
+	else
+		MBGFE_LAUNCH(k_select<NT_SELECT>, cnt, NT_SELECT, h->plan.smem_bytes, h->stream, st, h->d_codes.as<uint16_t>(), c2, h->tab_pair.as<uint4>(),
+			h->d_selmask.as<uint8_t>(), h->d_seg_nsel.as<uint32_t>() + g0, k, w, h->plan);
 	return 3;
 }
 
