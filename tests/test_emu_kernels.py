@@ -103,3 +103,15 @@ def test_emulated_hash_in_groups(oracle, emu_library, monkeypatch):
     reads = workloads.coverage_reads(n_reads=6)
     compare_runs(run_frontend("collapse-msat", 301, 30, reads, library=emu_library), oracle.run("collapse-msat", 301, 30, reads), what="emu grouped hash")
     compare_runs(run_frontend("hpc", 63, 33, reads, library=emu_library), oracle.run("hpc", 63, 33, reads), what="emu grouped hash hpc")
+
+
+@pytest.mark.parametrize("pct", ["100", "50", "0"])
+def test_emulated_host_packed_pieces(oracle, emu_library, monkeypatch, pct):
+    """the two upload routes of mbgfe_run (ASCII + K0 on the device, 2-bit packing on host threads) mixed piece by piece,
+    with lower case and characters outside ACGT in host-packed pieces"""
+    monkeypatch.setenv("MBGFE_HOST_PACK", pct)
+    reads = [workloads.read_a()] + workloads.edge_case_reads()
+    reads += [workloads.lcg_bases(5, 9000).replace(b"ACGTA", b"ACNNA", 3), workloads.lcg_bases(6, 7000).lower(), workloads.lcg_bases(8, 4097)]
+    for mode, k, w in (("collapse-msat", 301, 30), ("hpc", 63, 33)):
+        got = run_frontend(mode, k, w, reads, library=emu_library, piece_bytes=3200)
+        compare_runs(got, oracle.run(mode, k, w, reads), what=f"host pack {pct}% {mode}")

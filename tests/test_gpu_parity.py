@@ -279,3 +279,18 @@ def test_lane_per_kmer_hash_kernel(oracle, monkeypatch, cap):
     reads = workloads.coverage_reads(n_reads=12)
     for mode, k, w in (("collapse-msat", 1001, 100), ("hpc", 63, 33), ("no", 255, 225)):
         compare_runs(run_frontend(mode, k, w, reads), oracle.run(mode, k, w, reads), what=f"lanes hash {mode} k={k}")
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("pct", ["100", "70", "0"])
+def test_host_packed_upload_pieces(oracle, monkeypatch, pct):
+    """the two upload routes of mbgfe_run mixed piece by piece (ASCII + K0 on the device / 2-bit packing on host threads),
+    with lower-case reads and characters outside ACGT inside host-packed pieces"""
+    monkeypatch.setenv("MBGFE_HOST_PACK", pct)
+    reads = [workloads.read_a()] + workloads.edge_case_reads()
+    reads += [lcg_bases(5, 9000).replace(b"ACGTA", b"ACNNA", 3), lcg_bases(6, 7000).lower(), lcg_bases(8, 4097)]
+    for mode, k, w in (("collapse-msat", 301, 30), ("hpc", 63, 33), ("no", 101, 20)):
+        got = run_frontend(mode, k, w, reads, piece_bytes=3200)
+        compare_runs(got, oracle.run(mode, k, w, reads), what=f"host pack {pct}% {mode}")
+    big = workloads.coverage_reads(genome_len=400000, n_reads=600, len_min=12000, len_max=20000)
+    compare_runs(run_frontend("collapse-msat", 1001, 100, big, piece_bytes=1 << 20), oracle.run("collapse-msat", 1001, 100, big), what=f"host pack {pct}% big")

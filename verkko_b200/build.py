@@ -25,10 +25,13 @@ def _stale(target, sources):
 def build_mbgfe(force=False, verbose=False):
     target = os.path.join(HERE, "libmbgfe.so")
     sources = [os.path.join(CSRC, "mbgfe.cu"), os.path.join(CSRC, "kernels.cuh"), os.path.join(CSRC, "graph.cuh"),
-               os.path.join(HERE, "..", "include", "mbgfe.h")]
+               os.path.join(CSRC, "hostpack.cpp"), os.path.join(CSRC, "hostpack.h"), os.path.join(HERE, "..", "include", "mbgfe.h")]
     if not force and not _stale(target, sources):
         return target
-    cmd = [NVCC] + NVCC_FLAGS + ["-o", target, sources[0], "-lz"]
+    # the host half of the read loader is plain C++ (AVX2 behind a run-time check): compiled by g++, linked by nvcc
+    hostpack_o = os.path.join(HERE, "hostpack.o")
+    subprocess.check_call([HOST_CXX, "-O3", "-std=c++17", "-fPIC", "-pthread", "-c", "-o", hostpack_o, os.path.join(CSRC, "hostpack.cpp")])
+    cmd = [NVCC] + NVCC_FLAGS + ["-o", target, sources[0], hostpack_o, "-lz"]
     res = subprocess.run(cmd, capture_output=True, text=True)
     log = os.path.join(HERE, "build_mbgfe.log")
     with open(log, "w") as f:

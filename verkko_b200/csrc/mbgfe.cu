@@ -15,6 +15,7 @@
 
 #include "kernels.cuh"
 #include "graph.cuh"
+#include "hostpack.h"
 #include "../../include/mbgfe.h"
 
 static_assert(sizeof(mbgfe_dev::EdgeRec) == sizeof(mbgfe_edge), "device edge record is the ABI edge record");
@@ -64,6 +65,8 @@ struct mbgfe
 	bool collapse = false, msat = false;
 	uint32_t max_motif = 6;
 	cudaStream_t stream = nullptr, copy_stream = nullptr;
+	cudaStream_t front_stream[2] = { nullptr, nullptr };   // mbgfe_run: K0..K3a of consecutive pieces alternate between these
+	std::vector<cudaEvent_t> front_events, pack_events;   // per piece: K3a done / K0 done
 	std::vector<cudaEvent_t> piece_events;            // one per H2D piece of the pipelined upload
 	int sm_count = 148;
 	size_t max_smem = 0;
@@ -124,6 +127,7 @@ struct mbgfe
 	std::vector<uint16_t> h_codes;
 	std::vector<uint32_t> h_poses, h_positions;
 	std::vector<mbgfe_hash128> h_hashes;
+	HostBuf p_stage;                                                  // pinned staging of the host-packed pieces
 	HostBuf p_node_hashes, p_node_cov, p_node_tip, p_edges;           // pinned: the table arrives by DMA at full rate
 	uint64_t n_nodes_out = 0, n_edges_out = 0;
 	std::vector<uint32_t> h_seg_c1, h_seg_c2, h_seg_nsel;
@@ -403,7 +407,7 @@ int load_file(mbgfe* h, const char* path)
 
 namespace {
 int prepare_process(mbgfe* h);
-uint32_t launch_front(mbgfe* h, uint32_t g0, uint32_t cnt, bool timed);
+uint32_t launch_front(mbgfe* h, uint32_t g0, uint32_t cnt, bool timed, cudaStream_t on = nullptr);
 int process_tail(mbgfe* h, uint32_t launches);
 }
 
@@ -447,7 +451,8 @@ int mbgfe_create(const mbgfe_params* prm, mbgfe** out)
 	bool ok = false;
 	h->plan = make_plan(prm->k, prm->w, h->max_smem, ok);
 	if (!ok) return bail(fail(h, MBGFE_E_LIMIT, "k=%u needs more shared memory than one SM has (limit about k=11000)", prm->k));
-	if (cudaStreamCreate(&h->stream) != cudaSuccess || cudaStreamCreate(&h->copy_stream) != cudaSuccess) return bail(fail(h, MBGFE_E_CUDA, "cudaStreamCreate failed"));
+	if (cudaStreamCreate(&h->stream) != cudaSuccess || cudaStreamCreate(&h->copy_stream) != cudaSuccess || cudaStreamCreate(&h->front_stream[0]) != cudaSuccess ||
+		cudaStreamCreate(&h->front_stream[1]) != cudaSuccess) return bail(fail(h, MBGFE_E_CUDA, "cudaStreamCreate failed"));
 	for (auto& e2 : h->ev) if (cudaEventCreate(&e2) != cudaSuccess) return bail(fail(h, MBGFE_E_CUDA, "cudaEventCreate failed"));
 	if (ensure(h, h->tab_hash, MAX_CODE * 8) || ensure(h, h->tab_pair, MAX_CODE * 16) || ensure(h, h->tab_comp, MAX_CODE * 2) ||
 		ensure(h, h->d_counters, (CTR_OWNER + prm->world + 8) * 8)) return bail(MBGFE_E_CUDA);
@@ -485,10 +490,13 @@ void mbgfe_destroy(mbgfe* h)
 		&h->d_xbuf[3], &h->d_var_hash, &h->d_var_offset, &h->d_var_len_begin, &h->d_var_len, &h->d_g_deg, &h->d_g_nb, &h->d_g_link, &h->d_g_st[0], &h->d_g_st[1],
 		&h->d_g_kept, &h->d_g_newid, &h->d_g_flag, &h->d_g_at, &h->d_g_flag2, &h->d_g_at2, &h->d_g_flag_byte, &h->d_f_hash, &h->d_f_cov, &h->d_f_tip, &h->d_f_edges,
 		&h->d_u_begin, &h->d_u_nodes, &h->d_u_of_node }) release(*b);
-	for (HostBuf* b : { &h->p_node_hashes, &h->p_node_cov, &h->p_node_tip, &h->p_edges }) release_host(*b);
+	for (HostBuf* b : { &h->p_node_hashes, &h->p_node_cov, &h->p_node_tip, &h->p_edges, &h->p_stage }) release_host(*b);
 	for (auto& e : h->ev) if (e) cudaEventDestroy(e);
 	for (auto& e : h->piece_events) cudaEventDestroy(e);
 	if (h->copy_stream) cudaStreamDestroy(h->copy_stream);
+	for (auto& fs : h->front_stream) if (fs) cudaStreamDestroy(fs);
+	for (auto& e : h->front_events) cudaEventDestroy(e);
+	for (auto& e : h->pack_events) cudaEventDestroy(e);
 	if (h->stream) cudaStreamDestroy(h->stream);
 	for (auto* v : h->owned_bases) delete v;
 	for (auto* v : h->owned_offsets) delete v;
@@ -638,8 +646,9 @@ int prepare_process(mbgfe* h)
 
 // K1 -> K2 -> K3a on segments [g0, g0 + cnt).  Segments are independent, so the pipelined upload can run each piece's
 // segments while later pieces are still crossing PCIe.  timed: record the per-stage events (whole-batch launches only).
-uint32_t launch_front(mbgfe* h, uint32_t g0, uint32_t cnt, bool timed)
+uint32_t launch_front(mbgfe* h, uint32_t g0, uint32_t cnt, bool timed, cudaStream_t on)
 {
+	if (!on) on = h->stream;
 	if (cnt == 0) { if (timed) { tick(h, 4); tick(h, 5); } return 0; }
 	const uint32_t k = h->prm.k, w = h->prm.w;
 	const bool want_poses = want_poses_of(h);
@@ -653,27 +662,27 @@ uint32_t launch_front(mbgfe* h, uint32_t g0, uint32_t cnt, bool timed)
 	uint32_t* pos2 = want_poses ? h->d_pos2.as<uint32_t>() : nullptr;
 	uint32_t* c1 = h->d_seg_c1.as<uint32_t>() + g0;
 	uint32_t* c2 = h->d_seg_c2.as<uint32_t>() + g0;
-	MBGFE_LAUNCH(k_collapse<NT_COLLAPSE>, cnt, NT_COLLAPSE, 0, h->stream, st, h->d_packed.as<uint64_t>(), h->d_sym.as<uint64_t>(), c1, pos1,
+	MBGFE_LAUNCH(k_collapse<NT_COLLAPSE>, cnt, NT_COLLAPSE, 0, on, st, h->d_packed.as<uint64_t>(), h->d_sym.as<uint64_t>(), c1, pos1,
 		h->prm.error_masking == MBGFE_MASK_NO ? 1 : 0);
 	if (timed) tick(h, 4);
 	if (h->msat)
-		MBGFE_LAUNCH(k_msat, (cnt + MSAT_WARPS - 1) / MSAT_WARPS, MSAT_WARPS * 32, 0, h->stream, st, h->d_sym.as<uint64_t>(), c1, h->d_codes.as<uint16_t>(), h->d_rrc.as<uint16_t>(),
+		MBGFE_LAUNCH(k_msat, (cnt + MSAT_WARPS - 1) / MSAT_WARPS, MSAT_WARPS * 32, 0, on, st, h->d_sym.as<uint64_t>(), c1, h->d_codes.as<uint16_t>(), h->d_rrc.as<uint16_t>(),
 			c2, (const uint32_t*)pos1, pos2, h->max_motif);
 	else
-		MBGFE_LAUNCH(k_unpack_symbols<NT_MSAT>, cnt, NT_MSAT, 0, h->stream, st, h->d_sym.as<uint64_t>(), c1, h->d_codes.as<uint16_t>(),
+		MBGFE_LAUNCH(k_unpack_symbols<NT_MSAT>, cnt, NT_MSAT, 0, on, st, h->d_sym.as<uint64_t>(), c1, h->d_codes.as<uint16_t>(),
 			h->d_rrc.as<uint16_t>(), c2, (const uint32_t*)pos1, pos2);
 	if (timed) tick(h, 5);
 	if (h->select_nt == 64)
-		MBGFE_LAUNCH(k_select<64>, cnt, 64, h->plan.smem_bytes, h->stream, st, h->d_codes.as<uint16_t>(), c2, h->tab_pair.as<uint4>(),
+		MBGFE_LAUNCH(k_select<64>, cnt, 64, h->plan.smem_bytes, on, st, h->d_codes.as<uint16_t>(), c2, h->tab_pair.as<uint4>(),
 			h->d_selmask.as<uint8_t>(), h->d_seg_nsel.as<uint32_t>() + g0, k, w, h->plan);
 	else if (h->select_nt == 256)
-		MBGFE_LAUNCH(k_select<256>, cnt, 256, h->plan.smem_bytes, h->stream, st, h->d_codes.as<uint16_t>(), c2, h->tab_pair.as<uint4>(),
+		MBGFE_LAUNCH(k_select<256>, cnt, 256, h->plan.smem_bytes, on, st, h->d_codes.as<uint16_t>(), c2, h->tab_pair.as<uint4>(),
 			h->d_selmask.as<uint8_t>(), h->d_seg_nsel.as<uint32_t>() + g0, k, w, h->plan);
 	else if (h->select_nt == 512)
-		MBGFE_LAUNCH(k_select<512>, cnt, 512, h->plan.smem_bytes, h->stream, st, h->d_codes.as<uint16_t>(), c2, h->tab_pair.as<uint4>(),
+		MBGFE_LAUNCH(k_select<512>, cnt, 512, h->plan.smem_bytes, on, st, h->d_codes.as<uint16_t>(), c2, h->tab_pair.as<uint4>(),
 			h->d_selmask.as<uint8_t>(), h->d_seg_nsel.as<uint32_t>() + g0, k, w, h->plan);
 	else
-		MBGFE_LAUNCH(k_select<NT_SELECT>, cnt, NT_SELECT, h->plan.smem_bytes, h->stream, st, h->d_codes.as<uint16_t>(), c2, h->tab_pair.as<uint4>(),
+		MBGFE_LAUNCH(k_select<NT_SELECT>, cnt, NT_SELECT, h->plan.smem_bytes, on, st, h->d_codes.as<uint16_t>(), c2, h->tab_pair.as<uint4>(),
 			h->d_selmask.as<uint8_t>(), h->d_seg_nsel.as<uint32_t>() + g0, k, w, h->plan);
 	return 3;
 }
@@ -908,28 +917,86 @@ int mbgfe_run(mbgfe* h)
 	tick(h, 0);
 	tick(h, 3);
 	CU(h, cudaStreamWaitEvent(h->copy_stream, h->ev[0], 0));
-	// ---- phase A: every H2D piece is queued on the copy stream up front, so the copy engine never waits for the host
-	const uint64_t PIECE = h->prm.piece_bytes ? std::max<uint64_t>(h->prm.piece_bytes, 64) : (48ull << 20);
+	// ---- phase A: the pieces of the batch and their routes.  A piece either crosses PCIe as ASCII (packed by K0 on the
+	// device) or is packed to 2 bits by host worker threads first (hostpack.cpp) and crosses as a quarter of the bytes.
+	// Both resources work at once: on the bench box 16 cores pack 83 GB/s of ASCII and PCIe carries 55 GB/s of it, so about
+	// 7 pieces in 10 go through the host.  H2D copies are queued in piece order, a few pieces ahead of the kernels.
+	uint64_t PIECE = h->prm.piece_bytes ? std::max<uint64_t>(h->prm.piece_bytes, 64) : (48ull << 20);
+	if (const char* e = getenv("MBGFE_PIECE_MB")) if (!h->prm.piece_bytes && atoi(e) > 0) PIECE = (uint64_t)atoi(e) << 20;
+	struct Piece { const char* src; uint64_t pos, len; bool host; uint64_t stage_word; };
+	std::vector<Piece> pieces;
 	std::vector<uint64_t> piece_end;
+	uint32_t host_pct = 65;
+	if (const char* e = getenv("MBGFE_HOST_PACK")) host_pct = (uint32_t)std::min(100, std::max(0, atoi(e)));
+	const unsigned hw = std::thread::hardware_concurrency();
+	const unsigned n_workers = hw > 2 ? std::min(hw - 1, 31u) : 0;
+	if (n_workers == 0) host_pct = 0;
+	uint64_t stage_words = 0;
 	{
-		uint64_t pos = 0;
+		uint64_t pos = 0, credit = 0;
 		for (const HostChunk& c : h->pending)
 		{
 			const uint64_t first = c.offsets[0], bytes = c.offsets[c.n_reads] - first;
 			for (uint64_t off = 0; off < bytes; off += PIECE)
 			{
 				const uint64_t len = std::min(PIECE, bytes - off);
-				const size_t piece = piece_end.size();
-				if (piece >= h->piece_events.size()) { cudaEvent_t e; CU(h, cudaEventCreate(&e)); h->piece_events.push_back(e); }
-				CU(h, cudaMemcpyAsync(h->d_ascii.as<char>() + pos, c.bases + first + off, len, cudaMemcpyHostToDevice, h->copy_stream));
-				CU(h, cudaEventRecord(h->piece_events[piece], h->copy_stream));
+				Piece pc { c.bases + first + off, pos, len, false, 0 };
+				// the host route needs word-aligned pieces (only the very last one may end inside a word); the first piece
+				// always goes as ASCII so that the device starts at once
+				const bool eligible = pos % 32 == 0 && (len % 32 == 0 || pos + len == n_bases) && !pieces.empty();
+				credit += host_pct;
+				if (eligible && credit >= 100) { credit -= 100; pc.host = true; pc.stage_word = stage_words; stage_words += (len + 31) / 32; }
+				else if (credit >= 100) credit = 100;
+				pieces.push_back(pc);
 				pos += len;
 				piece_end.push_back(pos);
 			}
 		}
-		CU(h, cudaEventRecord(h->ev[1], h->copy_stream));
 	}
-	h->stats.h2d_bytes += n_bases;
+	mbgfe_host::PackPool pool;
+	if (stage_words)
+	{
+		if (int rc = ensure_host(h, h->p_stage, stage_words * 8)) return rc;
+		std::vector<mbgfe_host::PackTask> tasks;
+		const uint64_t SUB = 1ull << 20;                                   // characters per task (a multiple of 32)
+		for (size_t i = 0; i < pieces.size(); i++) if (pieces[i].host)
+			for (uint64_t o = 0; o < pieces[i].len; o += SUB)
+				tasks.push_back({ i, pieces[i].src + o, std::min(SUB, pieces[i].len - o), (uint64_t*)h->p_stage.p + pieces[i].stage_word + o / 32, pieces[i].pos + o });
+		pool.start(std::move(tasks), pieces.size(), n_workers);
+	}
+	while (h->piece_events.size() < pieces.size())
+	{
+		cudaEvent_t e;
+		CU(h, cudaEventCreate(&e)); h->piece_events.push_back(e);
+		CU(h, cudaEventCreateWithFlags(&e, cudaEventDisableTiming)); h->front_events.push_back(e);
+		CU(h, cudaEventCreateWithFlags(&e, cudaEventDisableTiming)); h->pack_events.push_back(e);
+	}
+	size_t queued = 0;
+	uint64_t h2d_bytes = 0;
+	auto queue_upto = [&](size_t upto) -> int
+	{
+		for (; queued < std::min(upto, pieces.size()); queued++)
+		{
+			const Piece& pc = pieces[queued];
+			if (pc.host)
+			{
+				pool.wait_piece(queued);
+				const uint64_t bytes = (pc.len + 31) / 32 * 8;
+				CU(h, cudaMemcpyAsync(h->d_packed.as<char>() + pc.pos / 4, (const char*)h->p_stage.p + pc.stage_word * 8, bytes, cudaMemcpyHostToDevice, h->copy_stream));
+				h2d_bytes += bytes;
+			}
+			else
+			{
+				CU(h, cudaMemcpyAsync(h->d_ascii.as<char>() + pc.pos, pc.src, pc.len, cudaMemcpyHostToDevice, h->copy_stream));
+				h2d_bytes += pc.len;
+			}
+			CU(h, cudaEventRecord(h->piece_events[queued], h->copy_stream));
+			if (queued + 1 == pieces.size()) CU(h, cudaEventRecord(h->ev[1], h->copy_stream));
+		}
+		return 0;
+	};
+	constexpr size_t LOOKAHEAD = 6;
+	if (pieces.empty()) CU(h, cudaEventRecord(h->ev[1], h->copy_stream));
 	// ---- phase B: behind each piece, K0 on its bytes and K1 .. K4 on the segments it completes.  The instance lists and
 	// the tables are sized from the first piece that completes segments (selected k-mers per base, extrapolated); the
 	// kernels refuse to write past those sizes and count what they refused, and the exact path reruns the tail then.
@@ -940,23 +1007,35 @@ int mbgfe_run(mbgfe* h)
 	bool sized = false;
 	for (size_t piece = 0; piece < piece_end.size(); piece++)
 	{
-		CU(h, cudaStreamWaitEvent(h->stream, h->piece_events[piece], 0));
+		// the copies run a few pieces ahead; at the start only as far as the host packers have got, so that the device
+		// is not kept waiting for them
+		if (int rc = queue_upto(piece + (piece < 2 ? 1 : LOOKAHEAD))) return rc;
+		// K0 .. K3a of consecutive pieces alternate between two streams: the tail of one piece's kernels overlaps the
+		// head of the next piece's (every kernel here is a few waves of CTAs).  A piece's segments may begin in the piece
+		// before it, so its stream also waits for that piece's bases (landed packed, or packed by K0 on the other stream).
+		const cudaStream_t fs = h->front_stream[piece & 1];
+		CU(h, cudaStreamWaitEvent(fs, h->piece_events[piece], 0));
+		if (piece) { CU(h, cudaStreamWaitEvent(fs, h->piece_events[piece - 1], 0)); CU(h, cudaStreamWaitEvent(fs, h->pack_events[piece - 1], 0)); }
 		const uint64_t pos = piece_end[piece];
 		const bool last = pos == n_bases;
 		const uint64_t pack_to = last ? n_bases : (pos & ~(uint64_t)31);
-		if (pack_to > packed_upto)
+		if (pieces[piece].host) packed_upto = pack_to;            // arrived packed: nothing for K0 to do
+		else if (pack_to > packed_upto)
 		{
 			const uint64_t c0 = packed_upto / 32, c1 = (pack_to + 31) / 32;
 			const unsigned grid = (unsigned)std::min<uint64_t>((c1 - c0 + 255) / 256, (uint64_t)h->sm_count * 16);
-			MBGFE_LAUNCH(k_pack_ascii, grid, 256, 0, h->stream, (const uint4*)h->d_ascii.p, n_bases, c0, c1, h->d_packed.as<uint64_t>(), h->d_nonacgt.as<uint64_t>(),
+			MBGFE_LAUNCH(k_pack_ascii, grid, 256, 0, fs, (const uint4*)h->d_ascii.p, n_bases, c0, c1, h->d_packed.as<uint64_t>(), h->d_nonacgt.as<uint64_t>(),
 				h->d_counters.as<unsigned long long>() + CTR_NONACGT, bad_cap);
 			launches++;
 			packed_upto = pack_to;
 		}
+		CU(h, cudaEventRecord(h->pack_events[piece], fs));
 		uint32_t g_end = g_done;
 		while (g_end < n_seg && h->read_off[h->seg_read[g_end] + 1] <= packed_upto) g_end++;
-		if (g_end == g_done) continue;
-		launches += launch_front(h, g_done, g_end - g_done, false);
+		if (g_end == g_done) { CU(h, cudaStreamWaitEvent(h->stream, h->pack_events[piece], 0)); continue; }
+		launches += launch_front(h, g_done, g_end - g_done, false, fs);
+		CU(h, cudaEventRecord(h->front_events[piece], fs));
+		CU(h, cudaStreamWaitEvent(h->stream, h->front_events[piece], 0));
 		launch_scan(h, g_done, g_end, launches);
 		g_done = g_end;
 		if (!sized)
@@ -990,7 +1069,10 @@ int mbgfe_run(mbgfe* h)
 	CU(h, cudaStreamSynchronize(h->stream));
 	CU(h, cudaGetLastError());
 	h->stats.d2h_bytes += sizeof(c8) + 8;
-	const uint64_t n_bad = c8[CTR_NONACGT];
+	pool.finish();
+	h->stats.h2d_bytes += h2d_bytes;
+	const uint64_t n_bad_dev = c8[CTR_NONACGT];
+	const uint64_t n_bad = n_bad_dev + pool.bad.size();
 	h->stats.ms_upload = elapsed(h, 0, 1);
 	h->stats.ms_pack = 0;
 	h->stats.reads = n_reads; h->stats.raw_bases = n_bases; h->stats.nonacgt = n_bad;
@@ -1001,7 +1083,8 @@ int mbgfe_run(mbgfe* h)
 		// rare: cut the reads at the characters outside ACGT and run the resident batch again
 		if (n_bad > bad_cap) return fail(h, MBGFE_E_LIMIT, "%llu characters outside ACGT in %llu bases: more than 1 in 16", (unsigned long long)n_bad, (unsigned long long)n_bases);
 		std::vector<uint64_t> bad;
-		if (int rc = download(h, bad, h->d_nonacgt, n_bad)) return rc;
+		if (int rc = download(h, bad, h->d_nonacgt, n_bad_dev)) return rc;
+		bad.insert(bad.end(), pool.bad.begin(), pool.bad.end());      // found by the host packers
 		std::sort(bad.begin(), bad.end());
 		build_segments(h, bad, read_ptr);
 		if (int rc = upload_segments(h)) return rc;
