@@ -1260,9 +1260,13 @@ int export_table(mbgfe* h)
 	if (int rc = ensure_host(h, h->p_node_tip, n_nodes + 64)) return rc;
 	if (n_nodes)
 	{
-		CU(h, cudaMemcpyAsync(h->p_node_hashes.p, h->d_node_hash_sorted.p, n_nodes * 16, cudaMemcpyDeviceToHost, h->stream));
-		CU(h, cudaMemcpyAsync(h->p_node_cov.p, h->d_node_cov.p, n_nodes * 4, cudaMemcpyDeviceToHost, h->stream));
-		CU(h, cudaMemcpyAsync(h->p_node_tip.p, h->d_node_tip.p, n_nodes, cudaMemcpyDeviceToHost, h->stream));
+		// the node arrays leave on the copy stream while the edges are still being ordered on the compute stream
+		CU(h, cudaEventRecord(h->ev[2], h->stream));
+		CU(h, cudaStreamWaitEvent(h->copy_stream, h->ev[2], 0));
+		CU(h, cudaMemcpyAsync(h->p_node_hashes.p, h->d_node_hash_sorted.p, n_nodes * 16, cudaMemcpyDeviceToHost, h->copy_stream));
+		CU(h, cudaMemcpyAsync(h->p_node_cov.p, h->d_node_cov.p, n_nodes * 4, cudaMemcpyDeviceToHost, h->copy_stream));
+		CU(h, cudaMemcpyAsync(h->p_node_tip.p, h->d_node_tip.p, n_nodes, cudaMemcpyDeviceToHost, h->copy_stream));
+		CU(h, cudaEventRecord(h->ev[2], h->copy_stream));
 		h->stats.d2h_bytes += n_nodes * 21;
 	}
 	// ---- edges: node slots -> node ids, buckets of ~32 edges on `from`
@@ -1289,6 +1293,7 @@ int export_table(mbgfe* h)
 		CU(h, cudaMemcpyAsync(h->p_edges.p, h->d_edges_sorted.p, n_edges * sizeof(mbgfe_edge), cudaMemcpyDeviceToHost, h->stream));
 		h->stats.d2h_bytes += n_edges * sizeof(mbgfe_edge);
 	}
+	if (n_nodes) CU(h, cudaStreamWaitEvent(h->stream, h->ev[2], 0));
 	tick(h, 11);
 	CU(h, cudaStreamSynchronize(h->stream));
 	CU(h, cudaGetLastError());
