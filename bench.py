@@ -260,18 +260,25 @@ def main():
     if not torch.cuda.is_available():
         raise SystemExit("bench.py needs a GPU: libmbgfe has no CPU path")
     torch.cuda.set_device(local_rank)
-    if world > 1:
+    # MBGFE_FORCE_EXCHANGE=1: run the sharded-table path (owner exchange, id replies, edge records) on ONE GPU, so that its
+    # kernels can be profiled with ncu (which must not wrap a multi-rank command)
+    force_exchange = world == 1 and os.environ.get("MBGFE_FORCE_EXCHANGE") == "1"
+    if world > 1 or force_exchange:
         if os.environ.get("NCCL_DEBUG", "VERSION").upper() == "VERSION":
             os.environ["NCCL_DEBUG"] = "WARN"       # keep NCCL's version banner off stdout: rank 0 prints ONE JSON line
-        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+        if force_exchange:
+            dist.init_process_group("nccl", init_method="tcp://127.0.0.1:29577", rank=0, world_size=1, device_id=torch.device("cuda", local_rank))
+        else:
+            dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
     from verkko_b200 import MbgFrontEnd
     from verkko_b200.distributed import DistributedCounter
     from verkko_b200.frontend import NO_TABLE
 
-    fe = MbgFrontEnd(wl["k"], wl["w"], "collapse-msat", device=local_rank, rank=rank, world=world, flags=NO_TABLE if world > 1 else 0)
+    sharded = world > 1 or force_exchange
+    fe = MbgFrontEnd(wl["k"], wl["w"], "collapse-msat", device=local_rank, rank=rank, world=world, flags=NO_TABLE if sharded else 0)
     bases, offsets, pinned = make_reads(wl, world, rank, args.scale, pinned_alloc=fe.pinned)
     n_bases = int(offsets[-1])
-    counter = DistributedCounter(fe, world, rank) if world > 1 else None
+    counter = DistributedCounter(fe, world, rank) if sharded else None
 
     def barrier():
         torch.cuda.synchronize()
@@ -354,7 +361,7 @@ def main():
         h2d, d2h = st_up["h2d_bytes"], st_e["d2h_bytes"]
     # ---- the step after the table (rows a14 / f1), outside the timed regions: abundance filter + unitig chains on the device
     unitig_info = None
-    if world == 1:
+    if world == 1 and not sharded:
         fe.build_unitigs(1, 2.0)                      # Verkko's buildGraph flags: --kmer-abundance 1 --unitig-abundance 2
         u = fe.build_unitigs(1, 2.0)
         st_u = fe.stats()
@@ -410,6 +417,7 @@ def main():
         print(json.dumps(line))
     if world > 1:
         dist.barrier()
+    if sharded:
         dist.destroy_process_group()
 
 
