@@ -237,6 +237,14 @@ def cpu_baseline(wl, scale):
 
 
 def main():
+    # stdout carries exactly ONE JSON line (rank 0).  Libraries chat on fd 1 (NCCL prints its version banner there when the
+    # first communicator is made), so fd 1 is pointed at stderr for the whole run and the line goes to the saved descriptor.
+    sys.stdout.flush()
+    json_fd = os.dup(1)
+    os.dup2(2, 1)
+    global emit
+    def emit(text):
+        os.write(json_fd, (text + "\n").encode())
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=5)
@@ -414,7 +422,7 @@ def main():
             line["roofline"]["traffic"] = json.load(open(traffic_file)).get(dominant)
         if world == 1 and not args.no_cpu_baseline:
             line["cpu_baseline"] = cpu_baseline(wl, args.scale)
-        print(json.dumps(line))
+        emit(json.dumps(line))
     if world > 1:
         dist.barrier()
     if sharded:

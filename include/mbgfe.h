@@ -189,7 +189,8 @@ int mbgfe_timer_stop(mbgfe* h, float* ms);
 
 /* Multi-GPU sharding by k-mer owner (the reference has no multi-device path -- its HashList is one
  * process-wide map behind a mutex, MBG/HashList.h:15-48).  One process and one handle per GPU, reads sharded by rank in
- * contiguous blocks, canonical hashes range-partitioned (owner = floor(hash.hi * world / 2^64)), so that concatenating
+ * contiguous blocks, canonical hashes range-partitioned in equal shares (owner = floor(world * F(hash.hi)); F(x) = x + x (1 - x) is the
+ * distribution of the canonical high word, the smaller of two uniform words), so that concatenating
  * the ranks' sorted partitions IS the global sortByHash order.  After mbgfe_process() with MBGFE_NO_TABLE on every rank:
  *
  *   nodes   mbgfe_exchange_counts   send_counts[world] = records this rank holds for each owner

@@ -46,10 +46,11 @@ const void* orc_data(const orc* o, int what);
 typedef struct orc_unitigs orc_unitigs;
 orc_unitigs* orc_build_unitigs(const orc* o, uint32_t min_cov, double min_unitig_cov);
 void orc_unitigs_free(orc_unitigs* u);
-/* what: 0 nodes of the input table, 1 kept nodes, 2 filtered edges, 3 unitigs, 4 unitig nodes */
+/* what: 0 nodes of the input table, 1 kept nodes, 2 filtered edges, 3 unitigs, 4 unitig nodes, 5 unitig edges */
 uint64_t orc_unitigs_count(const orc_unitigs* u, int what);
 /* what: 0 kept(u8 per input node) 1 filtered hashes(u64 lo,hi) 2 filtered coverage(u32) 3 filtered tip(u8)
- *       4 filtered edges(u32 x6) 5 unitig_begin(u64, n+1) 6 unitig nodes(u32 = 2*filtered id + fw) */
+ *       4 filtered edges(u32 x6) 5 unitig_begin(u64, n+1) 6 unitig nodes(u32 = 2*filtered id + fw)
+ *       7 unitig edges(u32 x6: from unitig, from_fw, to unitig, to_fw, coverage, 0; UnitigGraph::edges / edgeCov) */
 const void* orc_unitigs_data(const orc_unitigs* u, int what);
 
 /* primitives, exported for the known-answer tests */

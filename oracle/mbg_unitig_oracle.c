@@ -90,12 +90,14 @@ struct orc_unitigs {
 	uint32_t* f_edges;      /* u32 x6 with renumbered ids */
 	uint64_t* unitig_begin; /* n_unitigs + 1 */
 	uint32_t* unitig_nodes; /* 2*filtered id + fw, in traversal order */
+	uint64_t n_uedges;
+	uint32_t* uedges;       /* u32 x6: from unitig, from_fw, to unitig, to_fw, coverage, 0 -- canonical (MBG/MBGCommon.cpp:78-89) */
 };
 
 void orc_unitigs_free(orc_unitigs* u)
 {
 	if (!u) return;
-	free(u->kept); free(u->f_hash); free(u->f_cov); free(u->f_tip); free(u->f_edges); free(u->unitig_begin); free(u->unitig_nodes);
+	free(u->kept); free(u->f_hash); free(u->f_cov); free(u->f_tip); free(u->f_edges); free(u->unitig_begin); free(u->unitig_nodes); free(u->uedges);
 	free(u);
 }
 
@@ -185,6 +187,52 @@ orc_unitigs* orc_build_unitigs(const orc* o, uint32_t min_cov, double min_unitig
 		if (belongs[i] || u->f_cov[i] < min_cov) continue;
 		start_unitig(&a, (uint32_t)(2 * i + 1), belongs, u, scratch);
 	}
+	/* ---- unitig edges, MBG/MBG.cpp:746-760: from every unitig tip along the covered edges of its end k-mer */
+	{
+		uint32_t* tip_of = (uint32_t*)malloc((2 * nk + 2) * 4);      /* oriented node -> 2*unitig + fw, or none */
+		for (uint64_t x = 0; x < 2 * nk + 2; x++) tip_of[x] = 0xffffffffu;
+		for (uint64_t t = 0; t < u->n_unitigs; t++)
+		{
+			uint32_t first_node = u->unitig_nodes[u->unitig_begin[t]], last_node = u->unitig_nodes[u->unitig_begin[t + 1] - 1];
+			tip_of[last_node] = (uint32_t)(2 * t + 1);
+			tip_of[first_node ^ 1] = (uint32_t)(2 * t);
+		}
+		uint64_t cap = 2 * u->n_fedges + 1;
+		uint64_t* keys = (uint64_t*)malloc(cap * 8);
+		uint32_t* covs = (uint32_t*)malloc(cap * 4);
+		uint64_t nkey = 0;
+		for (uint64_t e = 0; e < u->n_fedges; e++)
+		{
+			const uint32_t* r = u->f_edges + 6 * e;
+			if (r[4] < min_cov) continue;
+			/* the edge as stored and its mirror image: each is seen from the tip it leaves */
+			for (int side = 0; side < 2; side++)
+			{
+				uint32_t x = 2 * r[0] + r[1], y = 2 * r[2] + r[3];
+				if (side) { uint32_t t = x; x = y ^ 1; y = t ^ 1; }
+				if (tip_of[x] == 0xffffffffu) continue;
+				uint32_t from = tip_of[x], to = tip_of[y ^ 1] ^ 1;
+				uint32_t fu = from >> 1, ffw = from & 1, tu = to >> 1, tfw = to & 1;
+				if (tu < fu || (tu == fu && !tfw && !ffw)) { uint32_t a1 = fu, b1 = ffw; fu = tu; ffw = !tfw; tu = a1; tfw = !b1; }
+				keys[nkey] = ((uint64_t)fu << 34) | ((uint64_t)ffw << 33) | ((uint64_t)tu << 1) | tfw;
+				covs[nkey++] = r[4];
+			}
+		}
+		/* set semantics: sort, drop duplicates (both tips report the same unitig edge) */
+		uint64_t* order = (uint64_t*)malloc((nkey + 1) * 16);
+		for (uint64_t i = 0; i < nkey; i++) { order[2 * i] = keys[i]; order[2 * i + 1] = covs[i]; }
+		qsort(order, nkey, 16, cmp_u64);
+		u->uedges = (uint32_t*)malloc((nkey + 1) * 24);
+		for (uint64_t i = 0; i < nkey; i++)
+		{
+			if (i && order[2 * i] == order[2 * (i - 1)]) continue;
+			uint32_t* w = u->uedges + 6 * u->n_uedges++;
+			w[0] = (uint32_t)(order[2 * i] >> 34); w[1] = (uint32_t)((order[2 * i] >> 33) & 1);
+			w[2] = (uint32_t)((order[2 * i] >> 1) & 0xffffffffu); w[3] = (uint32_t)(order[2 * i] & 1);
+			w[4] = (uint32_t)order[2 * i + 1]; w[5] = 0;
+		}
+		free(order); free(keys); free(covs); free(tip_of);
+	}
 	adjacency_free(&a);
 	free(belongs); free(rank); free(checked); free(scratch);
 	return u;
@@ -193,13 +241,13 @@ orc_unitigs* orc_build_unitigs(const orc* o, uint32_t min_cov, double min_unitig
 /* what: 0 nodes of the input table, 1 kept nodes, 2 filtered edges, 3 unitigs, 4 unitig nodes */
 uint64_t orc_unitigs_count(const orc_unitigs* u, int what)
 {
-	switch (what) { case 0: return u->n_nodes; case 1: return u->n_kept; case 2: return u->n_fedges; case 3: return u->n_unitigs; case 4: return u->n_unitig_nodes; }
+	switch (what) { case 0: return u->n_nodes; case 1: return u->n_kept; case 2: return u->n_fedges; case 3: return u->n_unitigs; case 4: return u->n_unitig_nodes; case 5: return u->n_uedges; }
 	return 0;
 }
 /* what: 0 kept(u8 per input node) 1 filtered hashes(u64 lo,hi) 2 filtered coverage(u32) 3 filtered tip(u8)
  *       4 filtered edges(u32 x6) 5 unitig_begin(u64, n+1) 6 unitig nodes(u32 = 2*filtered id + fw) */
 const void* orc_unitigs_data(const orc_unitigs* u, int what)
 {
-	switch (what) { case 0: return u->kept; case 1: return u->f_hash; case 2: return u->f_cov; case 3: return u->f_tip; case 4: return u->f_edges; case 5: return u->unitig_begin; case 6: return u->unitig_nodes; }
+	switch (what) { case 0: return u->kept; case 1: return u->f_hash; case 2: return u->f_cov; case 3: return u->f_tip; case 4: return u->f_edges; case 5: return u->unitig_begin; case 6: return u->unitig_nodes; case 7: return u->uedges; }
 	return 0;
 }

@@ -48,6 +48,7 @@ struct Run {
 	std::vector<uint32_t> node_cov;
 	std::vector<uint8_t> node_tip;
 	std::vector<uint32_t> edges; // from_id, from_fw, to_id, to_fw, coverage, overlap
+	std::vector<uint32_t> uedges; // unitig graph edges: from unitig, from_fw, to unitig, to_fw, coverage, overlap -- canonical
 	uint64_t total_selected = 0;
 };
 
@@ -286,6 +287,23 @@ void* refshim_unitigs(int mode, uint64_t k, uint64_t w, const char* bases, const
 		for (auto node : unitigs.unitigs[u]) run->positions.push_back((uint32_t)(2 * node.first + (node.second ? 1 : 0)));
 		run->parts.push_back(p);
 	}
+	// UnitigGraph::edges / edgeCov (set by getUnitigGraph's last loop, MBG.cpp:746-760), every edge once in canon() form
+	for (size_t u = 0; u < unitigs.unitigs.size(); u++)
+	{
+		for (int fw = 1; fw >= 0; fw--)
+		{
+			std::pair<size_t, bool> from { u, fw == 1 };
+			for (auto to : unitigs.edges[from])
+			{
+				auto c = canon(from, to);
+				if (c.first != from || c.second != to) continue;       // listed from its mirror image
+				run->uedges.push_back((uint32_t)from.first); run->uedges.push_back(from.second ? 1 : 0);
+				run->uedges.push_back((uint32_t)to.first); run->uedges.push_back(to.second ? 1 : 0);
+				run->uedges.push_back((uint32_t)unitigs.edgeCoverage(from, to));
+				run->uedges.push_back((uint32_t)unitigs.edgeOverlap(from, to));
+			}
+		}
+	}
 	return run;
 }
 
@@ -303,6 +321,7 @@ uint64_t refshim_count(void* h, int what)
 		case 4: return r->node_cov.size();
 		case 5: return r->edges.size() / 6;
 		case 6: return r->total_selected;
+		case 7: return r->uedges.size() / 6;
 	}
 	return 0;
 }
@@ -321,6 +340,7 @@ const void* refshim_data(void* h, int what)
 		case 6: return r->node_cov.data();
 		case 7: return r->node_tip.data();
 		case 8: return r->edges.data();
+		case 9: return r->uedges.data();
 	}
 	return nullptr;
 }

@@ -144,7 +144,8 @@ class Oracle:
             cnt, dat = (lambda w_: L.orc_unitigs_count(u, w_)), (lambda w_: L.orc_unitigs_data(u, w_))
             res = UnitigResult(kept=_arr(dat(0), cnt(0), "u1"), node_hash=_arr(dat(1), cnt(1) * 2, "<u8").reshape(-1, 2), node_cov=_arr(dat(2), cnt(1), "<u4"),
                                node_tip=_arr(dat(3), cnt(1), "u1"), edges=_arr(dat(4), cnt(2) * 6, "<u4").reshape(-1, 6),
-                               unitig_begin=_arr(dat(5), cnt(3) + 1, "<u8"), unitig_nodes=_arr(dat(6), cnt(4), "<u4"))
+                               unitig_begin=_arr(dat(5), cnt(3) + 1, "<u8"), unitig_nodes=_arr(dat(6), cnt(4), "<u4"),
+                               unitig_edges=_arr(dat(7), cnt(5) * 6, "<u4").reshape(-1, 6))
             return table, res
         finally:
             if u:
@@ -241,7 +242,9 @@ class Reference:
         try:
             r = _collect(lambda w_: L.refshim_count(h, w_), lambda w_: L.refshim_data(h, w_), True)
             begin = np.concatenate([r.parts["sel_begin"], [len(r.positions)]]).astype(np.uint64) if len(r.parts) else np.zeros(1, np.uint64)
-            return UnitigResult(kept=None, node_hash=r.node_hash, node_cov=r.node_cov, node_tip=r.node_tip, edges=r.edges, unitig_begin=begin, unitig_nodes=r.positions)
+            ue = _arr(L.refshim_data(h, 9), L.refshim_count(h, 7) * 6, "<u4").reshape(-1, 6)
+            return UnitigResult(kept=None, node_hash=r.node_hash, node_cov=r.node_cov, node_tip=r.node_tip, edges=r.edges, unitig_begin=begin, unitig_nodes=r.positions,
+                                unitig_edges=ue)
         finally:
             L.refshim_free(h)
 
@@ -303,14 +306,35 @@ def normalise_unitigs(u):
         f, ffw, t, tfw = e[swap, 0].copy(), e[swap, 1].copy(), e[swap, 2].copy(), e[swap, 3].copy()
         e[swap, 0], e[swap, 1], e[swap, 2], e[swap, 3] = t, 1 - tfw, f, 1 - ffw
         e = sorted_edges(e)
-    seqs = []
+    seqs, flipped, name = [], [], []
     b = u.unitig_begin.astype(np.int64)
     for i in range(len(b) - 1):
         raw = u.unitig_nodes[b[i]:b[i + 1]].astype(np.int64)
         seq = tuple((2 * new_id[raw >> 1] + (raw & 1)).tolist())
         rev = tuple((x ^ 1) for x in reversed(seq))
         seqs.append(min(seq, rev))
-    return dict(node_hash=u.node_hash[order], node_cov=u.node_cov[order], node_tip=u.node_tip[order], edges=e, unitigs=sorted(seqs))
+        flipped.append(rev < seq)
+        name.append(min(x >> 1 for x in seq))           # a unitig is named by its smallest node: nodes sit in one unitig only
+    res = dict(node_hash=u.node_hash[order], node_cov=u.node_cov[order], node_tip=u.node_tip[order], edges=e, unitigs=sorted(seqs))
+    if "unitig_edges" in u:
+        # an oriented unitig end is named by the oriented k-mer at that end (numbering- and rotation-free)
+        ue = set()
+        for r in u.unitig_edges.astype(np.int64):
+            def end_node(t, fw, last):
+                raw = u.unitig_nodes[b[t]:b[t + 1]].astype(np.int64)
+                seq = [int(2 * new_id[x >> 1] + (x & 1)) for x in raw]
+                if not fw:
+                    seq = [x ^ 1 for x in reversed(seq)]
+                return seq[-1] if last else seq[0]
+            if r[0] == r[2] and r[1] == r[3]:
+                # a circular unitig closing on itself: which of its k-mer edges closes it (and so the coverage shown)
+                # depends on where the walk started, i.e. on the node numbering; named by its smallest node only
+                ue.add((-1, name[r[0]], 0))
+                continue
+            x, y = end_node(r[0], r[1], True), end_node(r[2], r[3], False)
+            ue.add(min((x, y, int(r[4])), (y ^ 1, x ^ 1, int(r[4]))))
+        res["unitig_edges"] = sorted(ue)
+    return res
 
 
 def compare_unitigs(a, b, what=""):
@@ -331,6 +355,8 @@ def compare_unitigs(a, b, what=""):
             assert (s[-1], s[0]) in links, f"{what}: unitig differs and is not circular: {s[:6]}... len {len(s)}"
         assert sorted(rot(s) for s in sa - sb) == sorted(rot(s) for s in sb - sa), f"{what}: circular unitigs differ"
     assert len(na["unitigs"]) == len(nb["unitigs"]), f"{what}: unitig count"
+    if "unitig_edges" in na and "unitig_edges" in nb:
+        assert na["unitig_edges"] == nb["unitig_edges"], f"{what}: unitig edges differ ({len(na['unitig_edges'])} vs {len(nb['unitig_edges'])})"
 
 
 class Variants:

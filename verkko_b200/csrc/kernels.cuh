@@ -1911,9 +1911,16 @@ __global__ void __launch_bounds__(256) k_edge_bucket_rank(const EdgeRec* __restr
 
 // ------------------------------------------------------------------------------------- multi-GPU exchange
 
+// Range partition of the canonical hash space with EQUAL SHARES.  The canonical hash is the smaller of (hi:lo) and (lo:hi),
+// so its high word is the minimum of two uniform words: P(key_hi < x) = 1 - (1 - x)^2 = x + x (1 - x), far from uniform
+// (cutting the range itself into equal parts gives rank 0 of 8 a share of 23 %).  Ranks own equal parts of that
+// distribution instead: owner = floor(world * F(key_hi)), F in 64-bit fixed point.  F is non-decreasing in key_hi (its
+// increment is 1 + a floor term that drops by at most 1), so ranks still own consecutive hash ranges and concatenating
+// their sorted partitions is the global sortByHash order.
 __device__ __forceinline__ uint32_t owner_of(uint64_t key_hi, uint32_t world)
 {
-	return (uint32_t)__umul64hi(key_hi, (uint64_t)world); // range partition of the canonical hash space
+	const uint64_t f = key_hi + __umul64hi(key_hi, ~key_hi);
+	return (uint32_t)__umul64hi(f, (uint64_t)world);
 }
 
 // Per-owner allocation without hammering `world` global counters from millions of threads: a shared-memory histogram

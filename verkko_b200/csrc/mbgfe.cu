@@ -929,7 +929,9 @@ int mbgfe_run(mbgfe* h)
 	uint32_t host_pct = 65;
 	if (const char* e = getenv("MBGFE_HOST_PACK")) host_pct = (uint32_t)std::min(100, std::max(0, atoi(e)));
 	const unsigned hw = std::thread::hardware_concurrency();
-	const unsigned n_workers = hw > 2 ? std::min(hw - 1, 31u) : 0;
+	// one process per GPU: the ranks of a box share its cores
+	const unsigned share = std::max(1u, h->prm.world);
+	const unsigned n_workers = hw / share > 2 ? std::min(hw / share - 1, 31u) : 0;
 	if (n_workers == 0) host_pct = 0;
 	uint64_t stage_words = 0;
 	{

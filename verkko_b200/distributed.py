@@ -36,8 +36,14 @@ def wrap_pointer(ptr, n, on_gpu, dtype=torch.int64):
 
 
 def owner_of(hash_hi, world):
-    """range partition of the canonical hash space: owner = floor(hi * world / 2^64)"""
-    return (np.asarray(hash_hi, dtype=np.uint64).astype(object) * world) >> 64
+    """owner rank of canonical hashes (k_owner_* in csrc/kernels.cuh): equal shares of the distribution of the canonical
+    high word, which is the smaller of two uniform words: F(x) = x + x (1 - x) in 64-bit fixed point, owner = floor(world F)"""
+    mask = (1 << 64) - 1
+    out = []
+    for h in np.asarray(hash_hi, dtype=np.uint64).tolist():
+        f = h + ((h * (mask - h)) >> 64)
+        out.append((f * world) >> 64)
+    return np.array(out, dtype=np.int64)
 
 
 class DistributedCounter:
