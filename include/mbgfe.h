@@ -102,7 +102,9 @@ enum {
 	MBGFE_F_EDGES = 13,         /* mbgfe_edge[] edges between kept nodes (every coverage), renumbered, same order      */
 	MBGFE_UNITIG_BEGIN = 14,    /* uint64_t[n_unitigs + 1] offsets into MBGFE_UNITIG_NODES                             */
 	MBGFE_UNITIG_NODES = 15,    /* uint32_t[] 2 * filtered node id + fw, in unitig order (UnitigGraph::unitigs)        */
-	MBGFE_F_NODE_UNITIG = 16    /* uint32_t[] unitig of each filtered node, 0xffffffff when its coverage is below -a   */
+	MBGFE_F_NODE_UNITIG = 16,   /* uint32_t[] unitig of each filtered node, 0xffffffff when its coverage is below -a   */
+	MBGFE_UNITIG_EDGES = 17     /* mbgfe_edge[] between unitig ends (UnitigGraph::edges / edgeCov, MBG/MBG.cpp:746-760):
+	                               from / to = unitig, *_fw = read forward, coverage of the k-mer edge, overlap 0          */
 };
 
 typedef struct {
@@ -177,7 +179,8 @@ int mbgfe_get_stats(const mbgfe* h, mbgfe_stats* out);
  *      >= unitig_abundance keeps its nodes (checkUnitigHashes, MBG/MBG.cpp:322-344)       -> MBGFE_NODE_KEPT
  *   3. HashList::filter (MBG/HashList.cpp:159-232)                                        -> MBGFE_F_*
  *   4. unitigs = the chains of the filtered list over nodes with coverage >= kmer_abundance (MBG/MBG.cpp:689-760)
- *      -> MBGFE_UNITIG_BEGIN / MBGFE_UNITIG_NODES / MBGFE_F_NODE_UNITIG.  The reference numbers and orients unitigs in
+ *      -> MBGFE_UNITIG_BEGIN / MBGFE_UNITIG_NODES / MBGFE_F_NODE_UNITIG, and the edges between unitig ends (every covered
+ *      edge that is not inside a chain) -> MBGFE_UNITIG_EDGES.  The reference numbers and orients unitigs in
  *      the order its sequential walk meets them (arrival order of the k-mers); here a unitig starts at its end with the
  *      smaller node id (a circular one at its smallest node, forward) and unitigs are numbered by that first node.
  * kmer_abundance == 0 takes mbgfe_params.kmer_abundance.  Needs the edge table and world == 1. */

@@ -189,7 +189,7 @@ __global__ void __launch_bounds__(256) k_unitig_starts(const ChainState* __restr
 // unitig_id = exclusive scan of is_start, unitig_at = exclusive scan of start_len (both indexed by node)
 __global__ void __launch_bounds__(256) k_unitig_write(const ChainState* __restrict__ st, const uint32_t* __restrict__ cov, uint64_t n_nodes, uint32_t min_cov,
 	const uint32_t* __restrict__ is_start, const uint64_t* __restrict__ unitig_id, const uint64_t* __restrict__ unitig_at,
-	uint64_t* __restrict__ unitig_begin, uint32_t* __restrict__ unitig_nodes, uint32_t* __restrict__ node_unitig)
+	uint64_t* __restrict__ unitig_begin, uint32_t* __restrict__ unitig_nodes, uint32_t* __restrict__ node_unitig, uint32_t* __restrict__ node_ufw)
 {
 	for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n_nodes; i += (uint64_t)gridDim.x * blockDim.x)
 	{
@@ -201,7 +201,43 @@ __global__ void __launch_bounds__(256) k_unitig_write(const ChainState* __restri
 		const uint64_t at = unitig_at[head];
 		unitig_nodes[at + pos] = 2 * (uint32_t)i + same;
 		node_unitig[i] = (uint32_t)unitig_id[head];
+		node_ufw[i] = same;
 		if (is_start[i]) unitig_begin[unitig_id[i]] = at;
+	}
+}
+// UnitigGraph::edges / edgeCov (the last loop of getUnitigGraph, MBG/MBG.cpp:746-760): every covered edge of the filtered
+// list that is not a link inside a chain leaves the last k-mer of one unitig and enters the first k-mer of another (or of
+// the same one: a circular unitig closes through the link the ranking cut).  flag / at = compaction as for the edges.
+__device__ __forceinline__ bool unitig_edge_of(const EdgeRec& r, uint32_t min_cov, const uint32_t* __restrict__ link, const uint32_t* __restrict__ node_unitig,
+	const uint32_t* __restrict__ node_ufw, EdgeRec& out)
+{
+	if (r.coverage < min_cov) return false;
+	const uint32_t x = 2 * r.from + r.from_fw, y = 2 * r.to + r.to_fw;
+	if (link[x] == y) return false;
+	uint32_t fu = node_unitig[r.from], ffw = r.from_fw == node_ufw[r.from] ? 1u : 0u;
+	uint32_t tu = node_unitig[r.to], tfw = r.to_fw == node_ufw[r.to] ? 1u : 0u;
+	if (tu < fu || (tu == fu && !tfw && !ffw)) { const uint32_t a = fu, b = ffw; fu = tu; ffw = tfw ^ 1; tu = a; tfw = b ^ 1; }   // canon(), MBG/MBGCommon.cpp:78-89
+	out.from = fu; out.from_fw = ffw; out.to = tu; out.to_fw = tfw; out.coverage = r.coverage; out.overlap = 0;
+	return true;
+}
+
+__global__ void __launch_bounds__(256) k_unitig_edge_flags(const EdgeRec* __restrict__ edges, uint64_t n_edges, uint32_t min_cov, const uint32_t* __restrict__ link,
+	const uint32_t* __restrict__ node_unitig, const uint32_t* __restrict__ node_ufw, uint32_t* __restrict__ flag)
+{
+	for (uint64_t e = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; e < n_edges; e += (uint64_t)gridDim.x * blockDim.x)
+	{
+		EdgeRec o;
+		flag[e] = unitig_edge_of(edges[e], min_cov, link, node_unitig, node_ufw, o) ? 1u : 0u;
+	}
+}
+
+__global__ void __launch_bounds__(256) k_unitig_edge_write(const EdgeRec* __restrict__ edges, uint64_t n_edges, uint32_t min_cov, const uint32_t* __restrict__ link,
+	const uint32_t* __restrict__ node_unitig, const uint32_t* __restrict__ node_ufw, const uint64_t* __restrict__ at, EdgeRec* __restrict__ out)
+{
+	for (uint64_t e = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; e < n_edges; e += (uint64_t)gridDim.x * blockDim.x)
+	{
+		EdgeRec o;
+		if (unitig_edge_of(edges[e], min_cov, link, node_unitig, node_ufw, o)) out[at[e]] = o;
 	}
 }
 

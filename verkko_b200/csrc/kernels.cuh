@@ -1789,24 +1789,33 @@ __global__ void __launch_bounds__(256) k_insert_edges(const uint64_t* __restrict
 // slot so that edges (keyed by slot) can be renumbered.
 struct NodeOut { uint64_t key_lo, key_hi; uint32_t count, flags; uint64_t slot; };
 
-__global__ void __launch_bounds__(256) k_node_bucket_count(const NodeSlot* __restrict__ table, uint64_t n_slots, uint32_t shift, uint32_t* __restrict__ counts)
+// Bucket coordinate of a canonical hash inside its owner's range: the canonical high word is the smaller of two uniform
+// words (see owner_of below), F(x) = x + x (1 - x) makes it uniform again, F * world has the owner in its high word and the
+// position inside the owner's range in its low word.  Non-decreasing in key_hi within one owner, so buckets stay ordered.
+__device__ __forceinline__ uint64_t bucket_coordinate(uint64_t key_hi, uint32_t world)
+{
+	const uint64_t f = key_hi + __umul64hi(key_hi, ~key_hi);
+	return f * (uint64_t)world;
+}
+
+__global__ void __launch_bounds__(256) k_node_bucket_count(const NodeSlot* __restrict__ table, uint64_t n_slots, uint32_t shift, uint32_t world, uint32_t* __restrict__ counts)
 {
 	for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n_slots; i += (uint64_t)gridDim.x * blockDim.x)
 	{
 		const uint64_t hi = table[i].key_hi, lo = table[i].key_lo;
 		if (hi == ~0ull && lo == ~0ull) continue;
-		atomicAdd(counts + (shift >= 64 ? 0 : (hi >> shift)), 1u);
+		atomicAdd(counts + (shift >= 64 ? 0 : (bucket_coordinate(hi, world) >> shift)), 1u);
 	}
 }
 
-__global__ void __launch_bounds__(256) k_node_bucket_scatter(const NodeSlot* __restrict__ table, uint64_t n_slots, uint32_t shift, const uint64_t* __restrict__ bucket_begin,
+__global__ void __launch_bounds__(256) k_node_bucket_scatter(const NodeSlot* __restrict__ table, uint64_t n_slots, uint32_t shift, uint32_t world, const uint64_t* __restrict__ bucket_begin,
 	uint32_t* __restrict__ fill, NodeOut* __restrict__ tmp)
 {
 	for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n_slots; i += (uint64_t)gridDim.x * blockDim.x)
 	{
 		const NodeSlot s = table[i];
 		if (s.key_hi == ~0ull && s.key_lo == ~0ull) continue;
-		const uint64_t b = shift >= 64 ? 0 : (s.key_hi >> shift);
+		const uint64_t b = shift >= 64 ? 0 : (bucket_coordinate(s.key_hi, world) >> shift);
 		const uint64_t o = bucket_begin[b] + atomicAdd(fill + b, 1u);
 		NodeOut r; r.key_lo = s.key_lo; r.key_hi = s.key_hi; r.count = s.count; r.flags = s.flags; r.slot = i;
 		tmp[o] = r;

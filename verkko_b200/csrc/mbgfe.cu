@@ -104,12 +104,14 @@ struct mbgfe
 	std::vector<uint64_t> x_counts;                                          // per-owner record counts of the last mbgfe_exchange_counts
 	uint32_t id_base = 0;                                                    // nodes owned by lower ranks
 	bool nodes_ranked = false, edges_global = false;
+	bool table_sharded = false;                                              // the node table holds this rank's owner range only (built by mbgfe_exchange_insert)
 	DevBuf d_var_hash, d_var_offset, d_var_len_begin, d_var_len;       // hpc variants (mbgfe_set_variants), sorted
 	// mbgfe_build_unitigs: graph scratch (degrees, successor, link, two ranking states, flags, scans) and results
 	DevBuf d_g_deg, d_g_nb, d_g_link, d_g_st[2], d_g_kept, d_g_newid, d_g_flag, d_g_at, d_g_flag2, d_g_at2, d_g_flag_byte;
-	DevBuf d_f_hash, d_f_cov, d_f_tip, d_f_edges, d_u_begin, d_u_nodes, d_u_of_node;
+	DevBuf d_f_hash, d_f_cov, d_f_tip, d_f_edges, d_u_begin, d_u_nodes, d_u_of_node, d_u_fw, d_u_edges;
 	bool have_unitigs = false;
-	uint64_t n_kept = 0, n_fedges = 0, n_unitigs = 0, n_unitig_nodes = 0;
+	uint64_t n_kept = 0, n_fedges = 0, n_unitigs = 0, n_unitig_nodes = 0, n_uedges = 0;
+	std::vector<mbgfe_edge> h_u_edges;
 	std::vector<uint8_t> h_kept, h_f_tip;
 	std::vector<mbgfe_hash128> h_f_hash;
 	std::vector<uint32_t> h_f_cov, h_u_nodes, h_u_of_node;
@@ -309,7 +311,7 @@ int download(mbgfe* h, std::vector<T>& dst, const DevBuf& src, size_t count, siz
 void clear_results(mbgfe* h)
 {
 	h->processed = false; h->exported_parts = false; h->exported_table = false; h->exported_codes = false; h->have_table = false;
-	h->nodes_ranked = false; h->edges_global = false; h->id_base = 0; h->x_packed_ids = nullptr; h->x_counts.clear();
+	h->nodes_ranked = false; h->edges_global = false; h->table_sharded = false; h->id_base = 0; h->x_packed_ids = nullptr; h->x_counts.clear();
 	h->parts.clear(); h->h_codes.clear(); h->h_poses.clear(); h->h_positions.clear(); h->h_hashes.clear();
 	h->n_nodes_out = 0; h->n_edges_out = 0;
 	h->n_inst = 0;
@@ -489,7 +491,7 @@ void mbgfe_destroy(mbgfe* h)
 		&h->d_node_tip, &h->d_edges_sorted, &h->d_inst_packpos, &h->d_ids_out, &h->d_id_begin, &h->d_edge_records, &h->d_xbuf[0], &h->d_xbuf[1], &h->d_xbuf[2],
 		&h->d_xbuf[3], &h->d_var_hash, &h->d_var_offset, &h->d_var_len_begin, &h->d_var_len, &h->d_g_deg, &h->d_g_nb, &h->d_g_link, &h->d_g_st[0], &h->d_g_st[1],
 		&h->d_g_kept, &h->d_g_newid, &h->d_g_flag, &h->d_g_at, &h->d_g_flag2, &h->d_g_at2, &h->d_g_flag_byte, &h->d_f_hash, &h->d_f_cov, &h->d_f_tip, &h->d_f_edges,
-		&h->d_u_begin, &h->d_u_nodes, &h->d_u_of_node }) release(*b);
+		&h->d_u_begin, &h->d_u_nodes, &h->d_u_of_node, &h->d_u_fw, &h->d_u_edges }) release(*b);
 	for (HostBuf* b : { &h->p_node_hashes, &h->p_node_cov, &h->p_node_tip, &h->p_edges, &h->p_stage }) release_host(*b);
 	for (auto& e : h->ev) if (e) cudaEventDestroy(e);
 	for (auto& e : h->piece_events) cudaEventDestroy(e);
@@ -1239,10 +1241,10 @@ int rank_nodes(mbgfe* h)
 	if (int rc = ensure(h, h->d_node_tip, n_nodes + 64)) return rc;
 	const unsigned rank_grid = (unsigned)std::min<uint64_t>(((uint64_t)n_buckets * 32 + 255) / 256, (uint64_t)h->sm_count * 32);
 	CU(h, cudaMemsetAsync(h->d_bucket_count.p, 0, (size_t)n_buckets * 4, h->stream));
-	MBGFE_LAUNCH(k_node_bucket_count, grid, 256, 0, h->stream, h->d_nodes.as<NodeSlot>(), h->node_slots, shift, h->d_bucket_count.as<uint32_t>());
+	MBGFE_LAUNCH(k_node_bucket_count, grid, 256, 0, h->stream, h->d_nodes.as<NodeSlot>(), h->node_slots, shift, h->table_sharded ? h->prm.world : 1u, h->d_bucket_count.as<uint32_t>());
 	if (int rc = device_scan(h, h->d_bucket_count.as<uint32_t>(), h->d_bucket_begin.as<uint64_t>(), n_buckets)) return rc;
 	CU(h, cudaMemsetAsync(h->d_bucket_count.p, 0, (size_t)n_buckets * 4, h->stream));
-	MBGFE_LAUNCH(k_node_bucket_scatter, grid, 256, 0, h->stream, h->d_nodes.as<NodeSlot>(), h->node_slots, shift, h->d_bucket_begin.as<uint64_t>(),
+	MBGFE_LAUNCH(k_node_bucket_scatter, grid, 256, 0, h->stream, h->d_nodes.as<NodeSlot>(), h->node_slots, shift, h->table_sharded ? h->prm.world : 1u, h->d_bucket_begin.as<uint64_t>(),
 		h->d_bucket_count.as<uint32_t>(), h->d_node_out.as<NodeOut>());
 	MBGFE_LAUNCH(k_node_bucket_rank, rank_grid, 256, 0, h->stream, h->d_node_out.as<NodeOut>(), h->d_bucket_begin.as<uint64_t>(), n_buckets,
 		h->d_node_hash_sorted.as<uint64_t>(), h->d_node_cov.as<uint32_t>(), h->d_node_tip.as<uint8_t>(), h->d_nodes.as<NodeSlot>());
@@ -1393,7 +1395,9 @@ int mbgfe_build_unitigs(mbgfe* h, uint32_t kmer_abundance, double unitig_abundan
 	if (int rc = ensure(h, h->d_u_begin, (n + 2) * 8)) return rc;
 	if (int rc = ensure(h, h->d_u_nodes, (n + 1) * 4)) return rc;
 	if (int rc = ensure(h, h->d_u_of_node, (n + 1) * 4)) return rc;
-	uint64_t n_kept = 0, n_fedges = 0, n_unitigs = 0, n_unitig_nodes = 0;
+	if (int rc = ensure(h, h->d_u_fw, (n + 1) * 4)) return rc;
+	if (int rc = ensure(h, h->d_u_edges, (m + 1) * sizeof(EdgeRec))) return rc;
+	uint64_t n_kept = 0, n_fedges = 0, n_unitigs = 0, n_unitig_nodes = 0, n_uedges = 0;
 	if (n)
 	{
 		MBGFE_LAUNCH(k_chain_kept, grid_for(h, n), 256, 0, h->stream, h->d_g_st[which].as<ChainState>(), cov, n, unitig_abundance, h->d_g_kept.as<uint32_t>());
@@ -1426,10 +1430,21 @@ int mbgfe_build_unitigs(mbgfe* h, uint32_t kmer_abundance, double unitig_abundan
 		if (int rc = device_scan(h, h->d_g_flag.as<uint32_t>(), h->d_g_at.as<uint64_t>(), (uint32_t)n_kept)) return rc;
 		if (int rc = device_scan(h, h->d_g_flag2.as<uint32_t>(), h->d_g_at2.as<uint64_t>(), (uint32_t)n_kept)) return rc;
 		MBGFE_LAUNCH(k_unitig_write, grid_for(h, n_kept), 256, 0, h->stream, st, fcov, n_kept, kmer_abundance, h->d_g_flag.as<uint32_t>(), h->d_g_at.as<uint64_t>(),
-			h->d_g_at2.as<uint64_t>(), h->d_u_begin.as<uint64_t>(), h->d_u_nodes.as<uint32_t>(), h->d_u_of_node.as<uint32_t>());
+			h->d_g_at2.as<uint64_t>(), h->d_u_begin.as<uint64_t>(), h->d_u_nodes.as<uint32_t>(), h->d_u_of_node.as<uint32_t>(), h->d_u_fw.as<uint32_t>());
 		launches += 8;
-		CU(h, cudaMemcpyAsync(&n_unitigs, h->d_g_at.as<uint64_t>() + n_kept, 8, cudaMemcpyDeviceToHost, h->stream));
+		CU(h, cudaMemcpyAsync(&n_unitigs, h->d_g_at.as<uint64_t>() + n_kept, 8, cudaMemcpyDeviceToHost, h->stream));       // before the scans are reused
 		CU(h, cudaMemcpyAsync(&n_unitig_nodes, h->d_g_at2.as<uint64_t>() + n_kept, 8, cudaMemcpyDeviceToHost, h->stream));
+		if (n_fedges)
+		{
+			// unitig edges: the covered edges that are not links (d_g_link still holds the links of this ranking, cycles cut)
+			MBGFE_LAUNCH(k_unitig_edge_flags, grid_for(h, n_fedges), 256, 0, h->stream, h->d_f_edges.as<EdgeRec>(), n_fedges, kmer_abundance, h->d_g_link.as<uint32_t>(),
+				h->d_u_of_node.as<uint32_t>(), h->d_u_fw.as<uint32_t>(), h->d_g_flag.as<uint32_t>());
+			if (int rc = device_scan(h, h->d_g_flag.as<uint32_t>(), h->d_g_at.as<uint64_t>(), (uint32_t)n_fedges)) return rc;
+			MBGFE_LAUNCH(k_unitig_edge_write, grid_for(h, n_fedges), 256, 0, h->stream, h->d_f_edges.as<EdgeRec>(), n_fedges, kmer_abundance, h->d_g_link.as<uint32_t>(),
+				h->d_u_of_node.as<uint32_t>(), h->d_u_fw.as<uint32_t>(), h->d_g_at.as<uint64_t>(), h->d_u_edges.as<EdgeRec>());
+			launches += 5;
+			CU(h, cudaMemcpyAsync(&n_uedges, h->d_g_at.as<uint64_t>() + n_fedges, 8, cudaMemcpyDeviceToHost, h->stream));
+		}
 		CU(h, cudaStreamSynchronize(h->stream));
 		CU(h, cudaMemcpyAsync(h->d_u_begin.as<uint64_t>() + n_unitigs, &n_unitig_nodes, 8, cudaMemcpyHostToDevice, h->stream));
 	}
@@ -1441,9 +1456,23 @@ int mbgfe_build_unitigs(mbgfe* h, uint32_t kmer_abundance, double unitig_abundan
 	fetch(h, h->h_u_nodes, h->d_u_nodes, n_unitig_nodes);
 	fetch(h, h->h_u_of_node, h->d_u_of_node, n_kept ? n_kept : 0);
 	if (n_kept) fetch(h, h->h_u_begin, h->d_u_begin, n_unitigs + 1); else h->h_u_begin.assign(1, 0);
-	CU(h, cudaStreamSynchronize(h->stream));
+	{
+		std::vector<EdgeRec> ue;
+		fetch(h, ue, h->d_u_edges, n_uedges);
+		CU(h, cudaStreamSynchronize(h->stream));
+		// listed like MBGFE_EDGES: by (from, forward side first, to, to_fw); unitig edges are few, the host orders them
+		std::sort(ue.begin(), ue.end(), [](const EdgeRec& a, const EdgeRec& b)
+		{
+			if (a.from != b.from) return a.from < b.from;
+			if (a.from_fw != b.from_fw) return a.from_fw > b.from_fw;
+			if (a.to != b.to) return a.to < b.to;
+			return a.to_fw < b.to_fw;
+		});
+		h->h_u_edges.resize(ue.size());
+		if (!ue.empty()) memcpy(h->h_u_edges.data(), ue.data(), ue.size() * sizeof(mbgfe_edge));
+	}
 	CU(h, cudaGetLastError());
-	h->n_kept = n_kept; h->n_fedges = n_fedges; h->n_unitigs = n_unitigs; h->n_unitig_nodes = n_unitig_nodes;
+	h->n_kept = n_kept; h->n_fedges = n_fedges; h->n_unitigs = n_unitigs; h->n_unitig_nodes = n_unitig_nodes; h->n_uedges = n_uedges;
 	h->stats.ms_unitigs = elapsed(h, 12, 13);
 	h->stats.launches = launches;
 	h->have_unitigs = true;
@@ -1474,6 +1503,7 @@ uint64_t mbgfe_count(mbgfe* h, int what)
 		case MBGFE_F_EDGES: return h->have_unitigs ? h->n_fedges : 0;
 		case MBGFE_UNITIG_BEGIN: return h->have_unitigs ? h->n_unitigs + 1 : 0;
 		case MBGFE_UNITIG_NODES: return h->have_unitigs ? h->n_unitig_nodes : 0;
+		case MBGFE_UNITIG_EDGES: return h->have_unitigs ? h->n_uedges : 0;
 	}
 	return 0;
 }
@@ -1498,7 +1528,7 @@ const void* mbgfe_data(mbgfe* h, int what)
 		case MBGFE_NODE_TIP: if (export_table(h)) return nullptr; return h->p_node_tip.p;
 		case MBGFE_EDGES: if (export_table(h)) return nullptr; return h->p_edges.p;
 		case MBGFE_NODE_KEPT: case MBGFE_F_NODE_HASHES: case MBGFE_F_NODE_COVERAGE: case MBGFE_F_NODE_TIP: case MBGFE_F_NODE_UNITIG: case MBGFE_F_EDGES:
-		case MBGFE_UNITIG_BEGIN: case MBGFE_UNITIG_NODES:
+		case MBGFE_UNITIG_BEGIN: case MBGFE_UNITIG_NODES: case MBGFE_UNITIG_EDGES:
 			if (!h->have_unitigs) { fail(h, MBGFE_E_STATE, "filtered table / unitigs requested before mbgfe_build_unitigs"); return nullptr; }
 			switch (what)
 			{
@@ -1509,6 +1539,7 @@ const void* mbgfe_data(mbgfe* h, int what)
 				case MBGFE_F_NODE_UNITIG: return h->h_u_of_node.data();
 				case MBGFE_F_EDGES: return h->h_f_edges.data();
 				case MBGFE_UNITIG_BEGIN: return h->h_u_begin.data();
+				case MBGFE_UNITIG_EDGES: return h->h_u_edges.data();
 				default: return h->h_u_nodes.data();
 			}
 	}
@@ -1607,6 +1638,7 @@ int mbgfe_exchange_insert(mbgfe* h, const void* device_records, uint64_t n_recor
 	h->stats.distinct = d; h->stats.distinct_edges = 0; h->stats.table_slots = slots;
 	h->stats.ms_nodes = elapsed(h, 12, 13);
 	h->exported_table = false; h->nodes_ranked = false; h->edges_global = false;
+	h->table_sharded = true;
 	h->have_table = true;
 	return 0;
 }

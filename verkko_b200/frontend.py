@@ -14,7 +14,7 @@ MODES = {"no": 0, "hpc": 1, "collapse": 2, "dinuc": 3, "msat": 4, "collapse-dinu
 
 KEEP_CODES, KEEP_POSES, NO_TABLE, NO_EDGES = 1, 2, 4, 8
 PARTS, CODES, POSES, POSITIONS, HASHES, NODE_HASHES, NODE_COVERAGE, NODE_TIP, EDGES = range(9)
-NODE_KEPT, F_NODE_HASHES, F_NODE_COVERAGE, F_NODE_TIP, F_EDGES, UNITIG_BEGIN, UNITIG_NODES, F_NODE_UNITIG = range(9, 17)
+NODE_KEPT, F_NODE_HASHES, F_NODE_COVERAGE, F_NODE_TIP, F_EDGES, UNITIG_BEGIN, UNITIG_NODES, F_NODE_UNITIG, UNITIG_EDGES = range(9, 18)
 
 PART_DTYPE = np.dtype([
     ("read_idx", "<u4"), ("part_offset", "<u4"), ("raw_len", "<u4"), ("n_codes", "<u4"),
@@ -246,7 +246,8 @@ class MbgFrontEnd:
         return dict(kept=self._data(NODE_KEPT, "u1"), node_hash=self._data(F_NODE_HASHES, "<u8", 2).reshape(-1, 2),
                     node_cov=self._data(F_NODE_COVERAGE, "<u4"), node_tip=self._data(F_NODE_TIP, "u1"),
                     edges=self._data(F_EDGES, "<u4", 6).reshape(-1, 6), unitig_begin=self._data(UNITIG_BEGIN, "<u8"),
-                    unitig_nodes=self._data(UNITIG_NODES, "<u4"), node_unitig=self._data(F_NODE_UNITIG, "<u4"))
+                    unitig_nodes=self._data(UNITIG_NODES, "<u4"), node_unitig=self._data(F_NODE_UNITIG, "<u4"),
+                    unitig_edges=self._data(UNITIG_EDGES, "<u4", 6).reshape(-1, 6))
 
     def stats(self):
         s = Stats()
