@@ -375,6 +375,12 @@ def main():
         st_u = fe.stats()
         unitig_info = {"ms": st_u["ms_unitigs"], "kmer_abundance": 1, "unitig_abundance": 2.0, "nodes": int(len(u["kept"])), "kept_nodes": int(len(u["node_cov"])),
                        "kept_edges": int(len(u["edges"])), "unitigs": int(len(u["unitig_begin"]) - 1), "launches": st_u["launches"]}
+        # the same with getUnitigGraph's oneCovHeuristic, as runMBG builds its final graph under Verkko's flags (MBG.cpp:1573)
+        fe.build_unitigs(1, 2.0, one_cov_heuristic=True)
+        u = fe.build_unitigs(1, 2.0, one_cov_heuristic=True)
+        st_u = fe.stats()
+        unitig_info["one_cov_heuristic"] = {"ms": st_u["ms_unitigs"], "kept_nodes": int(len(u["node_cov"])), "kept_edges": int(len(u["edges"])),
+                                            "unitigs": int(len(u["unitig_begin"]) - 1), "unitig_edges": int(len(u["unitig_edges"])), "launches": st_u["launches"]}
     e2e_t = torch.tensor([float(np.mean(e2e_ms))], dtype=torch.float64, device="cuda")
     if world > 1:
         dist.all_reduce(e2e_t, op=dist.ReduceOp.MAX)

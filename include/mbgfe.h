@@ -173,7 +173,7 @@ const void* mbgfe_data(mbgfe* h, int what);
 int mbgfe_get_stats(const mbgfe* h, mbgfe_stats* out);
 
 /* The step after the table: getUnitigGraph (MBG/MBG.cpp:629-760) with oneCovHeuristic = keepGaps = false, i.e. what
- * runMBG does in pass 1 (MBG/MBG.cpp:1558).  On the device, from the ordered table of the last run:
+ * runMBG does in pass 1 (MBG/MBG.cpp:1558); mbgfe_build_unitigs_ex below adds the heuristic.  On the device, from the ordered table of the last run:
  *   1. covered edges = edges with coverage >= kmer_abundance (getCoveredEdges, MBG/MBG.cpp:367-388)
  *   2. every maximal non-branching chain (getUnitigHashes, MBG/MBG.cpp:305-320) whose mean k-mer coverage is
  *      >= unitig_abundance keeps its nodes (checkUnitigHashes, MBG/MBG.cpp:322-344)       -> MBGFE_NODE_KEPT
@@ -185,6 +185,15 @@ int mbgfe_get_stats(const mbgfe* h, mbgfe_stats* out);
  *      smaller node id (a circular one at its smallest node, forward) and unitigs are numbered by that first node.
  * kmer_abundance == 0 takes mbgfe_params.kmer_abundance.  Needs the edge table and world == 1. */
 int mbgfe_build_unitigs(mbgfe* h, uint32_t kmer_abundance, double unitig_abundance);
+
+/* getUnitigGraph's oneCovHeuristic argument (MBG/MBG.cpp:629-635): removeOnecovNodes (MBG/MBG.cpp:527-627) runs twice on
+ * the list before step 1 -- first over tips only, then over every run.  A run is a maximal stretch of coverage-1 k-mers
+ * along non-branching edges (all edges, coverage >= 1); it is dropped when everything its two ends lead to is also entered
+ * from a k-mer of coverage >= 2 (tips pass: and exactly one end leads nowhere).  runMBG sets it for its final graph when
+ * -u >= 2, -r > 0 and --do-unsafe-guesswork-resolutions (MBG/MBG.cpp:1573) -- Verkko's flags (Snakefiles/1-buildGraph.sm).
+ * MBGFE_NODE_KEPT then marks the survivors of all three filters. */
+#define MBGFE_UNITIG_ONECOV_HEURISTIC 1u
+int mbgfe_build_unitigs_ex(mbgfe* h, uint32_t kmer_abundance, double unitig_abundance, uint32_t flags);
 
 /* Device-side stopwatch on the library's stream (CUDA events): start, any number of calls, stop -> milliseconds. */
 int mbgfe_timer_start(mbgfe* h);

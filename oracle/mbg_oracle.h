@@ -45,6 +45,8 @@ const void* orc_data(const orc* o, int what);
  * (MBG/HashList.cpp:159-232) and the unitig chains of the filtered list (MBG/MBG.cpp:689-745).  Needs orc_build_table. */
 typedef struct orc_unitigs orc_unitigs;
 orc_unitigs* orc_build_unitigs(const orc* o, uint32_t min_cov, double min_unitig_cov);
+/* one_cov_heuristic: run removeOnecovNodes (tips, then all) first, as getUnitigGraph does under Verkko's flags (MBG/MBG.cpp:631-635, 1573) */
+orc_unitigs* orc_build_unitigs_ex(const orc* o, uint32_t min_cov, double min_unitig_cov, int one_cov_heuristic);
 void orc_unitigs_free(orc_unitigs* u);
 /* what: 0 nodes of the input table, 1 kept nodes, 2 filtered edges, 3 unitigs, 4 unitig nodes, 5 unitig edges */
 uint64_t orc_unitigs_count(const orc_unitigs* u, int what);

@@ -4,7 +4,8 @@
  *   getCoveredEdges                      MBG/MBG.cpp:367-388   edges with coverage >= -a, both directions, deduplicated
  *                                        (SparseEdgeContainer::addEdge has set semantics, MBG/SparseEdgeContainer.cpp:12-24)
  *   getUnitigHashes / checkUnitigHashes  MBG/MBG.cpp:305-344   maximal non-branching chain; kept iff mean coverage >= -u
- *   getUnitigGraph, first block          MBG/MBG.cpp:629-696   which chains are visited (oneCovHeuristic = keepGaps = false)
+ *   getUnitigGraph, first block          MBG/MBG.cpp:629-696   which chains are visited (keepGaps = false)
+ *   removeOnecovNodes                    MBG/MBG.cpp:527-627   oneCovHeuristic (on under Verkko's flags: -u 2, -r > 0, guesswork)
  *   HashList::filter                     MBG/HashList.cpp:159-232  kept nodes renumbered in order, edges between kept nodes
  *   getUnitigGraph, second block         MBG/MBG.cpp:689-760   unitigs = the same chains on the filtered list, coverage >= -a
  * Input is the table mbg_oracle.c builds (node order = ascending canonical hash).  The reference runs this on the
@@ -109,16 +110,129 @@ static void start_unitig(const adjacency* a, uint32_t start, uint8_t* belongs, o
 	u->unitig_begin[++u->n_unitigs] = u->n_unitig_nodes;
 }
 
-orc_unitigs* orc_build_unitigs(const orc* o, uint32_t min_cov, double min_unitig_cov)
+/* a HashList as this step sees it: nodes in order, edges as u32 x6 records, and where each node sat in the input table */
+typedef struct { uint64_t n, m; uint64_t* hash; uint32_t* cov; uint8_t* tip; uint32_t* edges; uint32_t* orig; } hlist;
+
+static hlist list_copy(uint64_t n, uint64_t m, const uint64_t* hash, const uint32_t* cov, const uint8_t* tip, const uint32_t* edges)
 {
-	const uint64_t n = orc_count(o, 4), m = orc_count(o, 5);
-	const uint64_t* hash = (const uint64_t*)orc_data(o, 5);
-	const uint32_t* cov = (const uint32_t*)orc_data(o, 6);
-	const uint8_t* tip = (const uint8_t*)orc_data(o, 7);
-	const uint32_t* edges = (const uint32_t*)orc_data(o, 8);
+	hlist l;
+	l.n = n; l.m = m;
+	l.hash = (uint64_t*)malloc((n + 1) * 16); memcpy(l.hash, hash, n * 16);
+	l.cov = (uint32_t*)malloc((n + 1) * 4); memcpy(l.cov, cov, n * 4);
+	l.tip = (uint8_t*)malloc(n + 1); memcpy(l.tip, tip, n);
+	l.edges = (uint32_t*)malloc((m + 1) * 24); memcpy(l.edges, edges, m * 24);
+	l.orig = (uint32_t*)malloc((n + 1) * 4);
+	for (uint64_t i = 0; i < n; i++) l.orig[i] = (uint32_t)i;
+	return l;
+}
+
+/* HashList::filter (MBG/HashList.cpp:159-232): kept nodes renumbered in order, edges between kept nodes.  In place. */
+static void list_filter(hlist* l, const uint8_t* kept)
+{
+	uint32_t* rank = (uint32_t*)malloc((l->n + 1) * 4);
+	uint64_t nk = 0;
+	for (uint64_t i = 0; i < l->n; i++) { rank[i] = (uint32_t)nk; if (kept[i]) nk++; }
+	for (uint64_t i = 0; i < l->n; i++) if (kept[i])
+	{
+		const uint32_t j = rank[i];
+		l->hash[2 * j] = l->hash[2 * i]; l->hash[2 * j + 1] = l->hash[2 * i + 1];
+		l->cov[j] = l->cov[i]; l->tip[j] = l->tip[i]; l->orig[j] = l->orig[i];
+	}
+	uint64_t mk = 0;
+	for (uint64_t e = 0; e < l->m; e++)
+	{
+		const uint32_t* r = l->edges + 6 * e;
+		if (!kept[r[0]] || !kept[r[2]]) continue;
+		uint32_t* w = l->edges + 6 * mk++;
+		memmove(w, r, 24);
+		w[0] = rank[w[0]]; w[2] = rank[w[2]];
+	}
+	l->n = nk; l->m = mk;
+	free(rank);
+}
+
+/* extendOneCoverageKmers (MBG/MBG.cpp:527-546) */
+static uint32_t extend_onecov(const adjacency* a, const uint32_t* cov, uint32_t pos)
+{
+	const uint32_t start = pos;
+	for (;;)
+	{
+		if (deg(a, pos) != 1) return pos;
+		const uint32_t next = first(a, pos);
+		if (deg(a, next ^ 1) != 1) return pos;
+		if ((next >> 1) == (pos >> 1)) return pos;
+		if ((next >> 1) == (start >> 1)) return pos;
+		if (cov[next >> 1] != 1) return pos;
+		pos = next;
+	}
+}
+
+/* the neighbour test of removeOnecovNodes (MBG/MBG.cpp:583-612): everything this end leads to is also reached from a
+ * k-mer of coverage >= 2 */
+static int onecov_end_replaceable(const adjacency* a, const uint32_t* cov, uint32_t end)
+{
+	for (uint64_t j = a->begin[end]; j < a->begin[end + 1]; j++)
+	{
+		const uint32_t back = a->to[j] ^ 1;
+		int other = 0;
+		for (uint64_t j2 = a->begin[back]; j2 < a->begin[back + 1]; j2++)
+		{
+			const uint32_t e2 = a->to[j2];
+			if (e2 == (end ^ 1)) continue;
+			if (cov[e2 >> 1] >= 2) other = 1;
+		}
+		if (!other) return 0;
+	}
+	return 1;
+}
+
+/* removeOnecovNodes (MBG/MBG.cpp:548-627) */
+static void remove_onecov(hlist* l, int only_tips)
+{
+	const uint64_t n = l->n;
+	adjacency a = covered_edges(n, l->edges, l->m, 1);
+	uint8_t* kept = (uint8_t*)malloc(n + 1);
+	uint8_t* checked = (uint8_t*)calloc(n + 1, 1);
+	memset(kept, 1, n + 1);
+	int removed_any = 0;
+	for (uint64_t i = 0; i < n; i++)
+	{
+		if (l->cov[i] != 1 || checked[i]) continue;
+		const uint32_t fw_node = extend_onecov(&a, l->cov, (uint32_t)(2 * i + 1));
+		const uint32_t bw_node = extend_onecov(&a, l->cov, (uint32_t)(2 * i));
+		for (uint32_t c = bw_node ^ 1; c != fw_node; c = first(&a, c)) checked[c >> 1] = 1;
+		checked[fw_node >> 1] = 1;
+		if (l->cov[fw_node >> 1] != 1 || l->cov[bw_node >> 1] != 1) continue;
+		if (only_tips)
+		{
+			if (deg(&a, fw_node) != 0 && deg(&a, bw_node) != 0) continue;
+			if (deg(&a, fw_node) == 0 && deg(&a, bw_node) == 0) continue;
+		}
+		if (!onecov_end_replaceable(&a, l->cov, fw_node)) continue;
+		if (!onecov_end_replaceable(&a, l->cov, bw_node)) continue;
+		uint32_t c = bw_node ^ 1;
+		for (; c != fw_node; c = first(&a, c)) kept[c >> 1] = 0;
+		kept[c >> 1] = 0;
+		removed_any = 1;
+	}
+	adjacency_free(&a);
+	if (removed_any) list_filter(l, kept);
+	free(kept); free(checked);
+}
+
+orc_unitigs* orc_build_unitigs_ex(const orc* o, uint32_t min_cov, double min_unitig_cov, int one_cov_heuristic)
+{
+	const uint64_t n_in = orc_count(o, 4);
+	hlist l = list_copy(n_in, orc_count(o, 5), (const uint64_t*)orc_data(o, 5), (const uint32_t*)orc_data(o, 6), (const uint8_t*)orc_data(o, 7), (const uint32_t*)orc_data(o, 8));
 	orc_unitigs* u = (orc_unitigs*)calloc(1, sizeof(orc_unitigs));
-	u->n_nodes = n;
-	u->kept = (uint8_t*)calloc(n + 1, 1);
+	u->n_nodes = n_in;
+	u->kept = (uint8_t*)calloc(n_in + 1, 1);
+	/* ---- MBG/MBG.cpp:631-635 */
+	if (one_cov_heuristic) { remove_onecov(&l, 1); remove_onecov(&l, 0); }
+	const uint64_t n = l.n, m = l.m;
+	const uint32_t* cov = l.cov;
+	const uint32_t* edges = l.edges;
+	uint8_t* kept = (uint8_t*)calloc(n + 1, 1);
 	uint8_t* checked = (uint8_t*)calloc(n + 1, 1);
 	uint32_t* scratch = (uint32_t*)malloc((n + 1) * 4);
 	/* ---- first block, MBG/MBG.cpp:637-690 */
@@ -128,39 +242,26 @@ orc_unitigs* orc_build_unitigs(const orc* o, uint32_t min_cov, double min_unitig
 		uint32_t fw = (uint32_t)(2 * i + 1), bw = (uint32_t)(2 * i);
 		if (deg(&a, bw) != 1 || first(&a, bw) == fw)
 		{
-			if (!checked[i]) check_unitig(&a, fw, checked, cov, min_unitig_cov, u->kept, scratch);
+			if (!checked[i]) check_unitig(&a, fw, checked, cov, min_unitig_cov, kept, scratch);
 			for (uint64_t j = a.begin[bw]; j < a.begin[bw + 1]; j++)
-				if (!checked[a.to[j] >> 1]) check_unitig(&a, a.to[j], checked, cov, min_unitig_cov, u->kept, scratch);
+				if (!checked[a.to[j] >> 1]) check_unitig(&a, a.to[j], checked, cov, min_unitig_cov, kept, scratch);
 		}
 		if (deg(&a, fw) != 1 || first(&a, fw) == bw)
 		{
-			if (!checked[i]) check_unitig(&a, bw, checked, cov, min_unitig_cov, u->kept, scratch);
+			if (!checked[i]) check_unitig(&a, bw, checked, cov, min_unitig_cov, kept, scratch);
 			for (uint64_t j = a.begin[fw]; j < a.begin[fw + 1]; j++)
-				if (!checked[a.to[j] >> 1]) check_unitig(&a, a.to[j], checked, cov, min_unitig_cov, u->kept, scratch);
+				if (!checked[a.to[j] >> 1]) check_unitig(&a, a.to[j], checked, cov, min_unitig_cov, kept, scratch);
 		}
 	}
-	for (uint64_t i = 0; i < n; i++) if (!checked[i]) check_unitig(&a, (uint32_t)(2 * i + 1), checked, cov, min_unitig_cov, u->kept, scratch);
+	for (uint64_t i = 0; i < n; i++) if (!checked[i]) check_unitig(&a, (uint32_t)(2 * i + 1), checked, cov, min_unitig_cov, kept, scratch);
 	adjacency_free(&a);
 	/* ---- HashList::filter, MBG/HashList.cpp:159-232 */
-	uint32_t* rank = (uint32_t*)malloc((n + 1) * 4);
-	for (uint64_t i = 0; i < n; i++) { rank[i] = (uint32_t)u->n_kept; if (u->kept[i]) u->n_kept++; }
-	u->f_hash = (uint64_t*)malloc((u->n_kept + 1) * 16);
-	u->f_cov = (uint32_t*)malloc((u->n_kept + 1) * 4);
-	u->f_tip = (uint8_t*)malloc(u->n_kept + 1);
-	for (uint64_t i = 0; i < n; i++) if (u->kept[i])
-	{
-		u->f_hash[2 * rank[i]] = hash[2 * i]; u->f_hash[2 * rank[i] + 1] = hash[2 * i + 1];
-		u->f_cov[rank[i]] = cov[i]; u->f_tip[rank[i]] = tip[i];
-	}
-	u->f_edges = (uint32_t*)malloc((m + 1) * 24);
-	for (uint64_t e = 0; e < m; e++)
-	{
-		const uint32_t* r = edges + 6 * e;
-		if (!u->kept[r[0]] || !u->kept[r[2]]) continue;
-		uint32_t* w = u->f_edges + 6 * u->n_fedges++;
-		memcpy(w, r, 24);
-		w[0] = rank[r[0]]; w[2] = rank[r[2]];
-	}
+	list_filter(&l, kept);
+	free(kept);
+	for (uint64_t i = 0; i < l.n; i++) u->kept[l.orig[i]] = 1;
+	u->n_kept = l.n; u->n_fedges = l.m;
+	u->f_hash = l.hash; u->f_cov = l.cov; u->f_tip = l.tip; u->f_edges = l.edges;
+	free(l.orig);
 	/* ---- second block, MBG/MBG.cpp:689-745, on the filtered list */
 	const uint64_t nk = u->n_kept;
 	a = covered_edges(nk, u->f_edges, u->n_fedges, min_cov);
@@ -234,9 +335,11 @@ orc_unitigs* orc_build_unitigs(const orc* o, uint32_t min_cov, double min_unitig
 		free(order); free(keys); free(covs); free(tip_of);
 	}
 	adjacency_free(&a);
-	free(belongs); free(rank); free(checked); free(scratch);
+	free(belongs); free(checked); free(scratch);
 	return u;
 }
+
+orc_unitigs* orc_build_unitigs(const orc* o, uint32_t min_cov, double min_unitig_cov) { return orc_build_unitigs_ex(o, min_cov, min_unitig_cov, 0); }
 
 /* what: 0 nodes of the input table, 1 kept nodes, 2 filtered edges, 3 unitigs, 4 unitig nodes */
 uint64_t orc_unitigs_count(const orc_unitigs* u, int what)

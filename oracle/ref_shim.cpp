@@ -233,7 +233,14 @@ void* refshim_run_variants(int mode, uint64_t k, uint64_t w, const char* bases, 
 // list; it filters the HashList in place (HashList::filter) and returns the unitigs.  Output, keyed by hash so that it
 // does not depend on node numbering: the filtered list in the Run's node_* / edges arrays (ids = filtered arrival
 // order), and every unitig as a run of (node id, fw) pairs in `positions` (2*id + fw) with `parts[u].sel_begin/n_sel`.
+void* refshim_unitigs_ex(int mode, uint64_t k, uint64_t w, const char* bases, const uint64_t* offsets, uint64_t n_reads, uint64_t min_cov, double min_unitig_cov, int one_cov_heuristic);
 void* refshim_unitigs(int mode, uint64_t k, uint64_t w, const char* bases, const uint64_t* offsets, uint64_t n_reads, uint64_t min_cov, double min_unitig_cov)
+{
+	return refshim_unitigs_ex(mode, k, w, bases, offsets, n_reads, min_cov, min_unitig_cov, 0);
+}
+
+// one_cov_heuristic: getUnitigGraph's last argument (MBG.cpp:629-635; runMBG sets it when -u >= 2, -r > 0 and guesswork, MBG.cpp:1573)
+void* refshim_unitigs_ex(int mode, uint64_t k, uint64_t w, const char* bases, const uint64_t* offsets, uint64_t n_reads, uint64_t min_cov, double min_unitig_cov, int one_cov_heuristic)
 {
 	Run* run = new Run;
 	std::vector<std::string> nofiles;
@@ -249,7 +256,7 @@ void* refshim_unitigs(int mode, uint64_t k, uint64_t w, const char* bases, const
 	HashList list { (size_t)k };
 	std::ostringstream log;
 	if (memoryReads.size() > 0) loadReadsAsHashesMultithread(list, k, tableIterator, 1, log);
-	UnitigGraph unitigs = getUnitigGraph(list, min_cov, min_unitig_cov, false, false);
+	UnitigGraph unitigs = getUnitigGraph(list, min_cov, min_unitig_cov, false, one_cov_heuristic != 0);
 	size_t n = list.size();
 	run->node_hash.resize(2*n);
 	run->node_cov.resize(n);

@@ -22,7 +22,7 @@ def run_frontend(mode, k, w, reads, library=None, flags=KEEP_CODES | KEEP_POSES,
         fe.close()
 
 
-def run_frontend_unitigs(mode, k, w, reads, min_cov, min_unitig_cov, library=None, **kw):
+def run_frontend_unitigs(mode, k, w, reads, min_cov, min_unitig_cov, library=None, one_cov=False, **kw):
     """table + mbgfe_build_unitigs -> (RunResult of the table, UnitigResult)"""
     from oracle_lib import UnitigResult
     fe = MbgFrontEnd(k, w, mode, library=library, **kw)
@@ -33,7 +33,7 @@ def run_frontend_unitigs(mode, k, w, reads, min_cov, min_unitig_cov, library=Non
             fe.add_read_list(reads)
         fe.run()
         table = RunResult(node_hash=fe.node_hashes(), node_cov=fe.node_coverage(), node_tip=fe.node_tip(), edges=fe.edges())
-        u = UnitigResult(fe.build_unitigs(min_cov, min_unitig_cov))
+        u = UnitigResult(fe.build_unitigs(min_cov, min_unitig_cov, one_cov_heuristic=one_cov))
         u["stats"] = fe.stats()
         return table, u
     finally:

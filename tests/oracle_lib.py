@@ -119,12 +119,12 @@ class Oracle:
         finally:
             L.orc_free(h)
 
-    def run_unitigs(self, mode, k, w, reads, min_cov, min_unitig_cov, variants=None):
-        """table + the filter/unitig step after it -> (RunResult, UnitigResult)"""
+    def run_unitigs(self, mode, k, w, reads, min_cov, min_unitig_cov, variants=None, one_cov=False):
+        """table + the filter/unitig step after it -> (RunResult, UnitigResult); one_cov = getUnitigGraph's oneCovHeuristic"""
         bases, offsets = reads if isinstance(reads, tuple) else pack_reads(reads)
         L = self.lib
-        L.orc_build_unitigs.restype = C.c_void_p
-        L.orc_build_unitigs.argtypes = [C.c_void_p, C.c_uint32, C.c_double]
+        L.orc_build_unitigs_ex.restype = C.c_void_p
+        L.orc_build_unitigs_ex.argtypes = [C.c_void_p, C.c_uint32, C.c_double, C.c_int]
         L.orc_unitigs_free.argtypes = [C.c_void_p]
         L.orc_unitigs_count.argtypes = [C.c_void_p, C.c_int]
         L.orc_unitigs_count.restype = C.c_uint64
@@ -140,7 +140,7 @@ class Oracle:
                 raise RuntimeError("oracle: palindromic or unhashable k-mer")
             L.orc_build_table(h)
             table = _collect(lambda w_: L.orc_count(h, w_), lambda w_: L.orc_data(h, w_), True)
-            u = L.orc_build_unitigs(h, min_cov, float(min_unitig_cov))
+            u = L.orc_build_unitigs_ex(h, min_cov, float(min_unitig_cov), 1 if one_cov else 0)
             cnt, dat = (lambda w_: L.orc_unitigs_count(u, w_)), (lambda w_: L.orc_unitigs_data(u, w_))
             res = UnitigResult(kept=_arr(dat(0), cnt(0), "u1"), node_hash=_arr(dat(1), cnt(1) * 2, "<u8").reshape(-1, 2), node_cov=_arr(dat(2), cnt(1), "<u4"),
                                node_tip=_arr(dat(3), cnt(1), "u1"), edges=_arr(dat(4), cnt(2) * 6, "<u4").reshape(-1, 6),
@@ -232,13 +232,14 @@ class Reference:
         finally:
             L.refshim_free(h)
 
-    def run_unitigs(self, mode, k, w, reads, min_cov, min_unitig_cov):
+    def run_unitigs(self, mode, k, w, reads, min_cov, min_unitig_cov, one_cov=False):
         """the reference's own getUnitigGraph after its table build (ids = filtered arrival order) -> UnitigResult"""
         bases, offsets = reads if isinstance(reads, tuple) else pack_reads(reads)
         L = self.lib
-        L.refshim_unitigs.restype = C.c_void_p
-        L.refshim_unitigs.argtypes = [C.c_int, C.c_uint64, C.c_uint64, C.c_void_p, C.c_void_p, C.c_uint64, C.c_uint64, C.c_double]
-        h = L.refshim_unitigs(MODES[mode] if isinstance(mode, str) else mode, k, w, bases.ctypes.data, offsets.ctypes.data, len(offsets) - 1, min_cov, float(min_unitig_cov))
+        L.refshim_unitigs_ex.restype = C.c_void_p
+        L.refshim_unitigs_ex.argtypes = [C.c_int, C.c_uint64, C.c_uint64, C.c_void_p, C.c_void_p, C.c_uint64, C.c_uint64, C.c_double, C.c_int]
+        h = L.refshim_unitigs_ex(MODES[mode] if isinstance(mode, str) else mode, k, w, bases.ctypes.data, offsets.ctypes.data, len(offsets) - 1, min_cov, float(min_unitig_cov),
+                                 1 if one_cov else 0)
         try:
             r = _collect(lambda w_: L.refshim_count(h, w_), lambda w_: L.refshim_data(h, w_), True)
             begin = np.concatenate([r.parts["sel_begin"], [len(r.positions)]]).astype(np.uint64) if len(r.parts) else np.zeros(1, np.uint64)

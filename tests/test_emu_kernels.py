@@ -96,6 +96,22 @@ def test_emulated_unitig_filter(oracle, emu_library, mode, k, w, a, u, which):
         assert len(want.unitig_begin) == 2 and want.unitig_begin[1] > 100      # one circular unitig; the lone read is filtered out
 
 
+@pytest.mark.parametrize("mode,k,w,a,u,which", [("collapse-msat", 301, 30, 1, 2, "coverage"), ("hpc", 63, 33, 1, 3, "noisy"), ("no", 63, 5, 1, 2, "circular")])
+def test_emulated_onecov_heuristic(oracle, emu_library, mode, k, w, a, u, which):
+    """row a14: removeOnecovNodes (MBG/MBG.cpp:527-627) on the emulator build, against the oracle (itself pinned on the
+    reference's getUnitigGraph(…, oneCovHeuristic = true) in tests/test_oracle.py)"""
+    from fe_helpers import run_frontend_unitigs
+    reads = {"coverage": lambda: workloads.coverage_reads(n_reads=16, error_ppm=4000),
+             "noisy": lambda: workloads.coverage_reads(seed=3, genome_len=8000, n_reads=10, error_ppm=10000),
+             "circular": lambda: workloads.circular_reads(genome_len=1500, read_len=1200, step=300) + [workloads.lcg_bases(77, 800)]}[which]()
+    _, got = run_frontend_unitigs(mode, k, w, reads, a, u, library=emu_library, one_cov=True)
+    _, want = oracle.run_unitigs(mode, k, w, reads, a, u, one_cov=True)
+    check_unitigs(got, want, f"emu onecov unitigs {mode} k={k} a={a} u={u}")
+    if which == "coverage":
+        _, plain = oracle.run_unitigs(mode, k, w, reads, a, u)
+        assert not np.array_equal(plain.kept, want.kept), "the heuristic did not change anything on this workload"
+
+
 def test_emulated_hash_in_groups(oracle, emu_library, monkeypatch):
     """k_kmer_hash_lanes with a staging area much smaller than a read: k-mers are hashed in groups of consecutive ones"""
     monkeypatch.setenv("MBGFE_HASH_LANES", "1")

@@ -228,6 +228,28 @@ def test_unitig_filter_against_oracle(oracle, mode, k, w, a, u):
 
 
 @pytest.mark.gpu
+@pytest.mark.parametrize("mode,k,w,a,u", [("collapse-msat", 1001, 100, 1, 2), ("collapse-msat", 301, 30, 1, 2), ("hpc", 63, 33, 1, 3), ("collapse-msat", 101, 20, 2, 2), ("no", 63, 5, 1, 2)])
+def test_onecov_heuristic_against_oracle(oracle, mode, k, w, a, u):
+    """row a14: getUnitigGraph with oneCovHeuristic (removeOnecovNodes twice, MBG/MBG.cpp:527-635) -- what runMBG builds
+    its final graph with under Verkko's flags -- on the device, against the oracle (pinned on the reference's own
+    getUnitigGraph(..., true) in tests/test_oracle.py)"""
+    from fe_helpers import run_frontend_unitigs
+    big = workloads.coverage_reads(genome_len=120000, n_reads=200, len_min=9000, len_max=14000, error_ppm=3000) if k < 1001 else \
+        workloads.coverage_reads(genome_len=200000, n_reads=300, len_min=12000, len_max=20000, error_ppm=2000)
+    changed = 0
+    for reads in (big, workloads.coverage_reads(seed=3, genome_len=20000, n_reads=12, error_ppm=10000),
+                  [workloads.repeat_rich(3, 6000), workloads.repeat_rich(3, 6000), workloads.repeat_rich(4, 3000)],
+                  workloads.circular_reads() + workloads.circular_reads(seed=10, genome_len=2000, read_len=1500, step=250) + [lcg_bases(77, 1500)]):
+        table, got = run_frontend_unitigs(mode, k, w, reads, a, u, one_cov=True)
+        otable, want = oracle.run_unitigs(mode, k, w, reads, a, u, one_cov=True)
+        assert np.array_equal(table.node_hash, otable.node_hash)
+        check_unitigs(got, want, f"onecov unitigs {mode} k={k} a={a} u={u}")
+        _, plain = oracle.run_unitigs(mode, k, w, reads, a, u)
+        changed += int(not np.array_equal(plain.kept, want.kept))
+    assert changed > 0 or (mode, k) != ("collapse-msat", 301), "the heuristic never changed the kept set"
+
+
+@pytest.mark.gpu
 @pytest.mark.parametrize("mode,k,w,a,u", [("no", 63, 5, 1, 2), ("hpc", 63, 33, 1, 1), ("collapse-msat", 101, 20, 2, 2)])
 def test_unitig_filter_circular_genomes(oracle, mode, k, w, a, u):
     """chains that are cycles (no tip, no branch): the ranking detects them by its round limit, cuts them in front of

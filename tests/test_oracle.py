@@ -153,3 +153,21 @@ def test_unitig_filter_equals_reference(oracle, reference, mode, k, w, a, u):
         want = reference.run_unitigs(mode, k, w, reads, a, u)
         compare_unitigs(got, want, what=f"unitigs {mode} k={k} a={a} u={u}")
         assert got.kept.sum() == len(got.node_cov) and len(got.kept) == len(table.node_cov)
+
+
+@pytest.mark.parametrize("mode,k,w,a,u", [("collapse-msat", 301, 30, 1, 2), ("hpc", 301, 30, 1, 2), ("hpc", 63, 33, 1, 3), ("collapse-msat", 101, 20, 2, 2), ("no", 63, 5, 1, 2)])
+def test_onecov_heuristic_equals_reference(oracle, reference, mode, k, w, a, u):
+    """row a14: removeOnecovNodes (MBG/MBG.cpp:527-627), the two passes getUnitigGraph runs first under Verkko's flags
+    (oneCovHeuristic, MBG.cpp:631-635, 1573), against the reference's own getUnitigGraph"""
+    from oracle_lib import compare_unitigs
+    changed = 0
+    for reads in (workloads.coverage_reads(n_reads=40, error_ppm=4000), workloads.coverage_reads(seed=3, genome_len=20000, n_reads=12, error_ppm=10000),
+                  workloads.coverage_reads(seed=5, genome_len=30000, n_reads=60, error_ppm=2000),
+                  [workloads.repeat_rich(3, 6000), workloads.repeat_rich(3, 6000), workloads.repeat_rich(4, 3000)],
+                  workloads.circular_reads() + workloads.circular_reads(seed=10, genome_len=2000, read_len=1500, step=250) + [lcg_bases(77, 1500)]):
+        table, got = oracle.run_unitigs(mode, k, w, reads, a, u, one_cov=True)
+        want = reference.run_unitigs(mode, k, w, reads, a, u, one_cov=True)
+        compare_unitigs(got, want, what=f"onecov unitigs {mode} k={k} a={a} u={u}")
+        _, plain = oracle.run_unitigs(mode, k, w, reads, a, u)
+        changed += int(not np.array_equal(plain.kept, got.kept))
+    assert changed > 0 or a > 1, "the heuristic never changed the kept set: the workloads do not exercise it"

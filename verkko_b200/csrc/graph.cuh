@@ -3,7 +3,8 @@
 //
 //   getCoveredEdges                      MBG/MBG.cpp:367-388   edges with coverage >= -a in both directions
 //   getUnitigHashes / checkUnitigHashes  MBG/MBG.cpp:305-344   maximal non-branching chain; kept iff mean coverage >= -u
-//   getUnitigGraph                       MBG/MBG.cpp:629-760   which chains exist (oneCovHeuristic = keepGaps = false)
+//   getUnitigGraph                       MBG/MBG.cpp:629-760   which chains exist (keepGaps = false)
+//   removeOnecovNodes                    MBG/MBG.cpp:527-627   oneCovHeuristic
 //   HashList::filter                     MBG/HashList.cpp:159-232
 //
 // The reference walks every chain sequentially.  A chain is a connected component of the LINK relation
@@ -122,16 +123,108 @@ __global__ void __launch_bounds__(256) k_chain_kept(const ChainState* __restrict
 	}
 }
 
-// HashList::filter (MBG/HashList.cpp:159-232), nodes: kept nodes keep their order; new_id = exclusive scan of kept
-__global__ void __launch_bounds__(256) k_filter_nodes(const uint32_t* __restrict__ kept, const uint64_t* __restrict__ new_id, uint64_t n_nodes, const uint4* __restrict__ hash,
-	const uint32_t* __restrict__ cov, const uint8_t* __restrict__ tip, uint4* __restrict__ f_hash, uint32_t* __restrict__ f_cov, uint8_t* __restrict__ f_tip, uint8_t* __restrict__ kept8)
+// ---- removeOnecovNodes (MBG/MBG.cpp:527-627), the oneCovHeuristic passes getUnitigGraph runs first under Verkko's flags.
+// A RUN is a maximal stretch of coverage-1 k-mers along links (extendOneCoverageKmers: the link test plus coverage(next) == 1;
+// its `next == start` test only stops circular runs, which the neighbour test below never removes).  The run goes when
+// both of its ends are "replaceable": every k-mer an end leads to is also entered from some k-mer of coverage >= 2
+// (MBG.cpp:583-612; the end itself has coverage 1, so "another predecessor with coverage >= 2" is "any").  With onlyTips
+// exactly one end must have no successor at all.  The reference walks the runs one by one; here
+//   strong[y] = 1   some predecessor of oriented node y has coverage >= 2          (edge pass)
+//   bad[x]    = 1   some successor of x has no strong predecessor                  (edge pass)
+//   run_end[x]      last oriented node of x's run in x's direction                 (pointer jumping, RUN_END = final)
+// and every coverage-1 node reads the verdict of its own run from its two ends.
+constexpr uint32_t RUN_END = 0x80000000u;
+
+__global__ void __launch_bounds__(256) k_onecov_strong(const EdgeRec* __restrict__ edges, uint64_t n_edges, const uint32_t* __restrict__ cov, uint32_t* __restrict__ strong)
+{
+	for (uint64_t e = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; e < n_edges; e += (uint64_t)gridDim.x * blockDim.x)
+	{
+		const EdgeRec r = edges[e];
+		if (r.coverage < 1) continue;
+		const uint32_t x = 2 * r.from + r.from_fw, y = 2 * r.to + r.to_fw;
+		if (cov[r.from] >= 2) strong[y] = 1;            // x -> y
+		if (cov[r.to] >= 2) strong[x ^ 1] = 1;          // its mirror image rev y -> rev x
+	}
+}
+
+__global__ void __launch_bounds__(256) k_onecov_bad(const EdgeRec* __restrict__ edges, uint64_t n_edges, const uint32_t* __restrict__ strong, uint32_t* __restrict__ bad)
+{
+	for (uint64_t e = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; e < n_edges; e += (uint64_t)gridDim.x * blockDim.x)
+	{
+		const EdgeRec r = edges[e];
+		if (r.coverage < 1) continue;
+		const uint32_t x = 2 * r.from + r.from_fw, y = 2 * r.to + r.to_fw;
+		if (!strong[y]) bad[x] = 1;
+		if (!strong[x ^ 1]) bad[y ^ 1] = 1;
+	}
+}
+
+__global__ void __launch_bounds__(256) k_onecov_init(const uint32_t* __restrict__ link, const uint32_t* __restrict__ cov, uint64_t n_oriented, uint32_t* __restrict__ run_end)
+{
+	for (uint64_t x = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; x < n_oriented; x += (uint64_t)gridDim.x * blockDim.x)
+	{
+		const uint32_t l = link[x];
+		const bool on = cov[x >> 1] == 1 && l != NO_LINK && cov[l >> 1] == 1;
+		run_end[x] = on ? l : ((uint32_t)x | RUN_END);
+	}
+}
+
+// one jumping round, in place: a pointer only ever moves further along its own run, so reading a neighbour's pointer
+// before or after that neighbour's update of the same round are both right
+__global__ void __launch_bounds__(256) k_onecov_jump(uint32_t* run_end, uint64_t n_oriented, uint32_t* __restrict__ unfinished)
+{
+	bool open = false;
+	for (uint64_t x = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; x < n_oriented; x += (uint64_t)gridDim.x * blockDim.x)
+	{
+		const uint32_t p = run_end[x];
+		if (p & RUN_END) continue;
+		const uint32_t q = ((volatile uint32_t*)run_end)[p];
+		run_end[x] = q;
+		open |= !(q & RUN_END);
+	}
+	if (open) *unfinished = 1;
+}
+
+// kept = 0 for every node of a run that goes.  A pointer that is not final after the round limit belongs to a circular
+// run: kept.
+__global__ void __launch_bounds__(256) k_onecov_verdict(const uint32_t* __restrict__ run_end, const uint32_t* __restrict__ deg, const uint32_t* __restrict__ bad,
+	const uint32_t* __restrict__ cov, uint64_t n_nodes, uint32_t only_tips, uint32_t* __restrict__ kept)
 {
 	for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n_nodes; i += (uint64_t)gridDim.x * blockDim.x)
 	{
-		kept8[i] = (uint8_t)kept[i];
+		uint32_t keep = 1;
+		if (cov[i] == 1)
+		{
+			const uint32_t f = run_end[2 * i + 1], b = run_end[2 * i];
+			if (f & b & RUN_END)
+			{
+				const uint32_t fw_node = f & ~RUN_END, bw_node = b & ~RUN_END;
+				bool go = !bad[fw_node] && !bad[bw_node];
+				if (only_tips) go = go && ((deg[fw_node] == 0) != (deg[bw_node] == 0));
+				if (go) keep = 0;
+			}
+		}
+		kept[i] = keep;
+	}
+}
+
+// kept flags of the input table from the survivors' original indices
+__global__ void __launch_bounds__(256) k_mark_kept(const uint32_t* __restrict__ orig, uint64_t n_kept, uint8_t* __restrict__ kept8)
+{
+	for (uint64_t j = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; j < n_kept; j += (uint64_t)gridDim.x * blockDim.x) kept8[orig[j]] = 1;
+}
+
+// HashList::filter (MBG/HashList.cpp:159-232), nodes: kept nodes keep their order; new_id = exclusive scan of kept
+__global__ void __launch_bounds__(256) k_filter_nodes(const uint32_t* __restrict__ kept, const uint64_t* __restrict__ new_id, uint64_t n_nodes, const uint4* __restrict__ hash,
+	const uint32_t* __restrict__ cov, const uint8_t* __restrict__ tip, const uint32_t* __restrict__ orig, uint4* __restrict__ f_hash, uint32_t* __restrict__ f_cov, uint8_t* __restrict__ f_tip,
+	uint32_t* __restrict__ f_orig)
+{
+	for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n_nodes; i += (uint64_t)gridDim.x * blockDim.x)
+	{
 		if (!kept[i]) continue;
 		const uint64_t j = new_id[i];
 		f_hash[j] = hash[i]; f_cov[j] = cov[i]; f_tip[j] = tip[i];
+		f_orig[j] = orig ? orig[i] : (uint32_t)i;      // where the node sat in the table the caller exported (orig == nullptr: this is that table)
 	}
 }
 

@@ -108,7 +108,7 @@ struct mbgfe
 	DevBuf d_var_hash, d_var_offset, d_var_len_begin, d_var_len;       // hpc variants (mbgfe_set_variants), sorted
 	// mbgfe_build_unitigs: graph scratch (degrees, successor, link, two ranking states, flags, scans) and results
 	DevBuf d_g_deg, d_g_nb, d_g_link, d_g_st[2], d_g_kept, d_g_newid, d_g_flag, d_g_at, d_g_flag2, d_g_at2, d_g_flag_byte;
-	DevBuf d_f_hash, d_f_cov, d_f_tip, d_f_edges, d_u_begin, d_u_nodes, d_u_of_node, d_u_fw, d_u_edges;
+	DevBuf d_f_hash, d_f_cov, d_f_tip, d_f_edges, d_f_orig, d_t_hash, d_t_cov, d_t_tip, d_t_edges, d_t_orig, d_g_kept8, d_u_begin, d_u_nodes, d_u_of_node, d_u_fw, d_u_edges;
 	bool have_unitigs = false;
 	uint64_t n_kept = 0, n_fedges = 0, n_unitigs = 0, n_unitig_nodes = 0, n_uedges = 0;
 	std::vector<mbgfe_edge> h_u_edges;
@@ -490,7 +490,7 @@ void mbgfe_destroy(mbgfe* h)
 		&h->d_edge_out, &h->d_records, &h->d_recv, &h->d_bucket_count, &h->d_bucket_begin, &h->d_scan_tot, &h->d_scan_off, &h->d_node_hash_sorted, &h->d_node_cov,
 		&h->d_node_tip, &h->d_edges_sorted, &h->d_inst_packpos, &h->d_ids_out, &h->d_id_begin, &h->d_edge_records, &h->d_xbuf[0], &h->d_xbuf[1], &h->d_xbuf[2],
 		&h->d_xbuf[3], &h->d_var_hash, &h->d_var_offset, &h->d_var_len_begin, &h->d_var_len, &h->d_g_deg, &h->d_g_nb, &h->d_g_link, &h->d_g_st[0], &h->d_g_st[1],
-		&h->d_g_kept, &h->d_g_newid, &h->d_g_flag, &h->d_g_at, &h->d_g_flag2, &h->d_g_at2, &h->d_g_flag_byte, &h->d_f_hash, &h->d_f_cov, &h->d_f_tip, &h->d_f_edges,
+		&h->d_g_kept, &h->d_g_newid, &h->d_g_flag, &h->d_g_at, &h->d_g_flag2, &h->d_g_at2, &h->d_g_flag_byte, &h->d_f_hash, &h->d_f_cov, &h->d_f_tip, &h->d_f_edges, &h->d_f_orig, &h->d_t_hash, &h->d_t_cov, &h->d_t_tip, &h->d_t_edges, &h->d_t_orig, &h->d_g_kept8,
 		&h->d_u_begin, &h->d_u_nodes, &h->d_u_of_node, &h->d_u_fw, &h->d_u_edges }) release(*b);
 	for (HostBuf* b : { &h->p_node_hashes, &h->p_node_cov, &h->p_node_tip, &h->p_edges, &h->p_stage }) release_host(*b);
 	for (auto& e : h->ev) if (e) cudaEventDestroy(e);
@@ -1360,12 +1360,113 @@ int fetch(mbgfe* h, std::vector<T>& dst, const DevBuf& src, size_t count)
 	return 0;
 }
 
+
+// a HashList on the device while the graph stage filters it: the exported table, or one of the two scratch sets
+struct GList
+{
+	const uint4* hash; const uint32_t* cov; const uint8_t* tip; const EdgeRec* edges; const uint32_t* orig;     // orig == nullptr: the exported table itself
+	uint64_t n, m;
+	int set;      // -1 the exported table, 0 the d_f_* buffers, 1 the d_t_* buffers
+};
+
+// HashList::filter (MBG/HashList.cpp:159-232): d_g_kept holds the 0/1 flags and d_g_newid their exclusive scan (total at [n]);
+// writes the survivors into the scratch set `in` does not live in
+int filter_list(mbgfe* h, GList& l, uint64_t n_kept, uint32_t& launches)
+{
+	const int to = l.set == 0 ? 1 : 0;
+	DevBuf& o_hash = to ? h->d_t_hash : h->d_f_hash; DevBuf& o_cov = to ? h->d_t_cov : h->d_f_cov; DevBuf& o_tip = to ? h->d_t_tip : h->d_f_tip;
+	DevBuf& o_edges = to ? h->d_t_edges : h->d_f_edges; DevBuf& o_orig = to ? h->d_t_orig : h->d_f_orig;
+	if (int rc = ensure(h, o_hash, (n_kept + 1) * 16)) return rc;
+	if (int rc = ensure(h, o_cov, (n_kept + 1) * 4)) return rc;
+	if (int rc = ensure(h, o_tip, n_kept + 64)) return rc;
+	if (int rc = ensure(h, o_orig, (n_kept + 1) * 4)) return rc;
+	if (int rc = ensure(h, o_edges, (l.m + 1) * sizeof(EdgeRec))) return rc;
+	MBGFE_LAUNCH(k_filter_nodes, grid_for(h, l.n), 256, 0, h->stream, h->d_g_kept.as<uint32_t>(), h->d_g_newid.as<uint64_t>(), l.n, l.hash, l.cov, l.tip, l.orig,
+		o_hash.as<uint4>(), o_cov.as<uint32_t>(), o_tip.as<uint8_t>(), o_orig.as<uint32_t>());
+	launches++;
+	uint64_t m_kept = 0;
+	if (l.m)
+	{
+		MBGFE_LAUNCH(k_filter_edge_flags, grid_for(h, l.m), 256, 0, h->stream, l.edges, l.m, h->d_g_kept.as<uint32_t>(), h->d_g_flag.as<uint32_t>());
+		if (int rc = device_scan(h, h->d_g_flag.as<uint32_t>(), h->d_g_at.as<uint64_t>(), (uint32_t)l.m)) return rc;
+		MBGFE_LAUNCH(k_filter_edges, grid_for(h, l.m), 256, 0, h->stream, l.edges, l.m, h->d_g_flag.as<uint32_t>(), h->d_g_at.as<uint64_t>(), h->d_g_newid.as<uint64_t>(), o_edges.as<EdgeRec>());
+		launches += 5;
+		CU(h, cudaMemcpyAsync(&m_kept, h->d_g_at.as<uint64_t>() + l.m, 8, cudaMemcpyDeviceToHost, h->stream));
+		CU(h, cudaStreamSynchronize(h->stream));
+	}
+	l.hash = o_hash.as<uint4>(); l.cov = o_cov.as<uint32_t>(); l.tip = o_tip.as<uint8_t>(); l.edges = o_edges.as<EdgeRec>(); l.orig = o_orig.as<uint32_t>();
+	l.n = n_kept; l.m = m_kept; l.set = to;
+	return 0;
+}
+
+// scan of the kept flags in d_g_kept; returns how many survive
+int scan_kept(mbgfe* h, uint64_t n, uint64_t& n_kept, uint32_t& launches)
+{
+	n_kept = 0;
+	if (!n) return 0;
+	if (int rc = device_scan(h, h->d_g_kept.as<uint32_t>(), h->d_g_newid.as<uint64_t>(), (uint32_t)n)) return rc;
+	launches += 3;
+	CU(h, cudaMemcpyAsync(&n_kept, h->d_g_newid.as<uint64_t>() + n, 8, cudaMemcpyDeviceToHost, h->stream));
+	CU(h, cudaStreamSynchronize(h->stream));
+	return 0;
+}
+
+// removeOnecovNodes (MBG/MBG.cpp:548-627), one pass: kept flags -> filter when anything goes
+int onecov_pass(mbgfe* h, GList& l, bool only_tips, uint32_t& launches)
+{
+	if (!l.n) return 0;
+	const uint64_t n2 = 2 * l.n;
+	if (n2 >= 0x80000000ull) return fail(h, MBGFE_E_PARAM, "oneCovHeuristic: more than 2^30 k-mers in one table");
+	if (int rc = ensure(h, h->d_g_deg, n2 * 4 + 64)) return rc;
+	if (int rc = ensure(h, h->d_g_nb, n2 * 4 + 64)) return rc;
+	if (int rc = ensure(h, h->d_g_link, n2 * 4 + 64)) return rc;
+	for (int i = 0; i < 2; i++) if (int rc = ensure(h, h->d_g_st[i], (n2 + 1) * sizeof(ChainState))) return rc;
+	if (int rc = ensure(h, h->d_g_flag_byte, 64)) return rc;
+	uint32_t* run_end = h->d_g_st[0].as<uint32_t>();
+	uint32_t* strong = h->d_g_st[1].as<uint32_t>();
+	uint32_t* bad = strong + n2;
+	CU(h, cudaMemsetAsync(h->d_g_deg.p, 0, n2 * 4 + 64, h->stream));
+	CU(h, cudaMemsetAsync(strong, 0, 2 * n2 * 4, h->stream));
+	if (l.m)
+	{
+		MBGFE_LAUNCH(k_graph_degrees, grid_for(h, l.m), 256, 0, h->stream, l.edges, l.m, 1u, h->d_g_deg.as<uint32_t>(), h->d_g_nb.as<uint32_t>());
+		MBGFE_LAUNCH(k_onecov_strong, grid_for(h, l.m), 256, 0, h->stream, l.edges, l.m, l.cov, strong);
+		MBGFE_LAUNCH(k_onecov_bad, grid_for(h, l.m), 256, 0, h->stream, l.edges, l.m, strong, bad);
+		launches += 3;
+	}
+	MBGFE_LAUNCH(k_graph_links, grid_for(h, n2), 256, 0, h->stream, h->d_g_deg.as<uint32_t>(), h->d_g_nb.as<uint32_t>(), n2, h->d_g_link.as<uint32_t>());
+	MBGFE_LAUNCH(k_onecov_init, grid_for(h, n2), 256, 0, h->stream, h->d_g_link.as<uint32_t>(), l.cov, n2, run_end);
+	launches += 2;
+	uint32_t* flag = h->d_g_flag_byte.as<uint32_t>();
+	uint32_t open = 1;
+	int limit = 2;
+	while ((1ull << limit) < n2) limit++;
+	for (int round = 0; round <= limit && open; round++)      // what is still open after that is a circular run
+	{
+		CU(h, cudaMemsetAsync(flag, 0, 4, h->stream));
+		MBGFE_LAUNCH(k_onecov_jump, grid_for(h, n2), 256, 0, h->stream, run_end, n2, flag);
+		launches++;
+		CU(h, cudaMemcpyAsync(&open, flag, 4, cudaMemcpyDeviceToHost, h->stream));
+		CU(h, cudaStreamSynchronize(h->stream));
+	}
+	if (int rc = ensure(h, h->d_g_kept, (l.n + 1) * 4)) return rc;
+	if (int rc = ensure(h, h->d_g_newid, (l.n + 2) * 8)) return rc;
+	MBGFE_LAUNCH(k_onecov_verdict, grid_for(h, l.n), 256, 0, h->stream, run_end, h->d_g_deg.as<uint32_t>(), bad, l.cov, l.n, only_tips ? 1u : 0u, h->d_g_kept.as<uint32_t>());
+	launches++;
+	uint64_t n_kept = 0;
+	if (int rc = scan_kept(h, l.n, n_kept, launches)) return rc;
+	if (n_kept == l.n) return 0;                                // removedAny == false: the list stays as it is
+	return filter_list(h, l, n_kept, launches);
+}
+
 }
 
 extern "C" {
 
-// getUnitigGraph (MBG/MBG.cpp:629-760) without oneCovHeuristic / keepGaps, on the ordered table
-int mbgfe_build_unitigs(mbgfe* h, uint32_t kmer_abundance, double unitig_abundance)
+int mbgfe_build_unitigs(mbgfe* h, uint32_t kmer_abundance, double unitig_abundance) { return mbgfe_build_unitigs_ex(h, kmer_abundance, unitig_abundance, 0); }
+
+// getUnitigGraph (MBG/MBG.cpp:629-760) without keepGaps, on the ordered table
+int mbgfe_build_unitigs_ex(mbgfe* h, uint32_t kmer_abundance, double unitig_abundance, uint32_t flags)
 {
 	if (!h) return MBGFE_E_PARAM;
 	if (!h->processed || !h->have_table) return fail(h, MBGFE_E_STATE, "mbgfe_build_unitigs needs the k-mer table of a finished run");
@@ -1377,49 +1478,49 @@ int mbgfe_build_unitigs(mbgfe* h, uint32_t kmer_abundance, double unitig_abundan
 	h->have_unitigs = false;
 	uint32_t launches = 0;
 	tick(h, 12);
-	const EdgeRec* edges = h->d_edges_sorted.as<EdgeRec>();
-	const uint32_t* cov = h->d_node_cov.as<uint32_t>();
-	// ---- which nodes survive: chains over edges with coverage >= -a, mean coverage >= -u
-	int which = 0;
-	if (int rc = rank_chains(h, edges, m, cov, n, kmer_abundance, &which, launches)) return rc;
-	if (int rc = ensure(h, h->d_g_kept, (n + 1) * 4)) return rc;
-	if (int rc = ensure(h, h->d_g_newid, (n + 2) * 8)) return rc;
 	if (int rc = ensure(h, h->d_g_flag, (std::max(n, m) + 1) * 4)) return rc;
 	if (int rc = ensure(h, h->d_g_at, (std::max(n, m) + 2) * 8)) return rc;
-	if (int rc = ensure(h, h->d_g_flag2, (n + 1) * 4)) return rc;
-	if (int rc = ensure(h, h->d_g_at2, (n + 2) * 8)) return rc;
-	if (int rc = ensure(h, h->d_f_hash, (n + 1) * 16)) return rc;
-	if (int rc = ensure(h, h->d_f_cov, (n + 1) * 4)) return rc;
-	if (int rc = ensure(h, h->d_f_tip, n + 64)) return rc;
-	if (int rc = ensure(h, h->d_f_edges, (m + 1) * sizeof(EdgeRec))) return rc;
-	if (int rc = ensure(h, h->d_u_begin, (n + 2) * 8)) return rc;
-	if (int rc = ensure(h, h->d_u_nodes, (n + 1) * 4)) return rc;
-	if (int rc = ensure(h, h->d_u_of_node, (n + 1) * 4)) return rc;
-	if (int rc = ensure(h, h->d_u_fw, (n + 1) * 4)) return rc;
-	if (int rc = ensure(h, h->d_u_edges, (m + 1) * sizeof(EdgeRec))) return rc;
+	if (int rc = ensure(h, h->d_g_kept, (n + 1) * 4)) return rc;
+	if (int rc = ensure(h, h->d_g_newid, (n + 2) * 8)) return rc;
+	GList l { h->d_node_hash_sorted.as<uint4>(), h->d_node_cov.as<uint32_t>(), h->d_node_tip.as<uint8_t>(), h->d_edges_sorted.as<EdgeRec>(), nullptr, n, m, -1 };
+	// ---- oneCovHeuristic (MBG/MBG.cpp:631-635): tips first, then every run
+	if (flags & MBGFE_UNITIG_ONECOV_HEURISTIC)
+	{
+		if (int rc = onecov_pass(h, l, true, launches)) return rc;
+		if (int rc = onecov_pass(h, l, false, launches)) return rc;
+	}
+	// ---- which nodes survive: chains over edges with coverage >= -a, mean coverage >= -u
+	int which = 0;
 	uint64_t n_kept = 0, n_fedges = 0, n_unitigs = 0, n_unitig_nodes = 0, n_uedges = 0;
+	if (l.n)
+	{
+		if (int rc = rank_chains(h, l.edges, l.m, l.cov, l.n, kmer_abundance, &which, launches)) return rc;
+		MBGFE_LAUNCH(k_chain_kept, grid_for(h, l.n), 256, 0, h->stream, h->d_g_st[which].as<ChainState>(), l.cov, l.n, unitig_abundance, h->d_g_kept.as<uint32_t>());
+		launches++;
+		if (int rc = scan_kept(h, l.n, n_kept, launches)) return rc;
+		// ---- HashList::filter
+		if (int rc = filter_list(h, l, n_kept, launches)) return rc;
+		n_fedges = l.m;
+		if (l.set == 1)      // the result is read from the d_f_* set
+		{
+			std::swap(h->d_f_hash, h->d_t_hash); std::swap(h->d_f_cov, h->d_t_cov); std::swap(h->d_f_tip, h->d_t_tip); std::swap(h->d_f_edges, h->d_t_edges); std::swap(h->d_f_orig, h->d_t_orig);
+		}
+	}
+	// kept flags of the exported table: the survivors of every filter
+	if (int rc = ensure(h, h->d_g_kept8, n + 64)) return rc;
 	if (n)
 	{
-		MBGFE_LAUNCH(k_chain_kept, grid_for(h, n), 256, 0, h->stream, h->d_g_st[which].as<ChainState>(), cov, n, unitig_abundance, h->d_g_kept.as<uint32_t>());
-		if (int rc = device_scan(h, h->d_g_kept.as<uint32_t>(), h->d_g_newid.as<uint64_t>(), (uint32_t)n)) return rc;
-		// ---- HashList::filter
-		uint8_t* kept8 = (uint8_t*)h->d_u_of_node.p;      // borrowed until the unitig pass writes it
-		MBGFE_LAUNCH(k_filter_nodes, grid_for(h, n), 256, 0, h->stream, h->d_g_kept.as<uint32_t>(), h->d_g_newid.as<uint64_t>(), n, h->d_node_hash_sorted.as<uint4>(), cov,
-			h->d_node_tip.as<uint8_t>(), h->d_f_hash.as<uint4>(), h->d_f_cov.as<uint32_t>(), h->d_f_tip.as<uint8_t>(), kept8);
-		launches += 5;
-		fetch(h, h->h_kept, h->d_u_of_node, n);
-		CU(h, cudaMemcpyAsync(&n_kept, h->d_g_newid.as<uint64_t>() + n, 8, cudaMemcpyDeviceToHost, h->stream));
-		if (m)
-		{
-			MBGFE_LAUNCH(k_filter_edge_flags, grid_for(h, m), 256, 0, h->stream, edges, m, h->d_g_kept.as<uint32_t>(), h->d_g_flag.as<uint32_t>());
-			if (int rc = device_scan(h, h->d_g_flag.as<uint32_t>(), h->d_g_at.as<uint64_t>(), (uint32_t)m)) return rc;
-			MBGFE_LAUNCH(k_filter_edges, grid_for(h, m), 256, 0, h->stream, edges, m, h->d_g_flag.as<uint32_t>(), h->d_g_at.as<uint64_t>(), h->d_g_newid.as<uint64_t>(), h->d_f_edges.as<EdgeRec>());
-			launches += 5;
-			CU(h, cudaMemcpyAsync(&n_fedges, h->d_g_at.as<uint64_t>() + m, 8, cudaMemcpyDeviceToHost, h->stream));
-		}
-		CU(h, cudaStreamSynchronize(h->stream));
+		CU(h, cudaMemsetAsync(h->d_g_kept8.p, 0, n, h->stream));
+		if (n_kept) { MBGFE_LAUNCH(k_mark_kept, grid_for(h, n_kept), 256, 0, h->stream, h->d_f_orig.as<uint32_t>(), n_kept, h->d_g_kept8.as<uint8_t>()); launches++; }
 	}
-	else h->h_kept.clear();
+	fetch(h, h->h_kept, h->d_g_kept8, n);
+	if (int rc = ensure(h, h->d_g_flag2, (n_kept + 1) * 4)) return rc;
+	if (int rc = ensure(h, h->d_g_at2, (n_kept + 2) * 8)) return rc;
+	if (int rc = ensure(h, h->d_u_begin, (n_kept + 2) * 8)) return rc;
+	if (int rc = ensure(h, h->d_u_nodes, (n_kept + 1) * 4)) return rc;
+	if (int rc = ensure(h, h->d_u_of_node, (n_kept + 1) * 4)) return rc;
+	if (int rc = ensure(h, h->d_u_fw, (n_kept + 1) * 4)) return rc;
+	if (int rc = ensure(h, h->d_u_edges, (n_fedges + 1) * sizeof(EdgeRec))) return rc;
 	// ---- unitigs of the filtered list
 	if (n_kept)
 	{

@@ -15,6 +15,7 @@ MODES = {"no": 0, "hpc": 1, "collapse": 2, "dinuc": 3, "msat": 4, "collapse-dinu
 KEEP_CODES, KEEP_POSES, NO_TABLE, NO_EDGES = 1, 2, 4, 8
 PARTS, CODES, POSES, POSITIONS, HASHES, NODE_HASHES, NODE_COVERAGE, NODE_TIP, EDGES = range(9)
 NODE_KEPT, F_NODE_HASHES, F_NODE_COVERAGE, F_NODE_TIP, F_EDGES, UNITIG_BEGIN, UNITIG_NODES, F_NODE_UNITIG, UNITIG_EDGES = range(9, 18)
+UNITIG_ONECOV_HEURISTIC = 1      # mbgfe_build_unitigs_ex flag (include/mbgfe.h)
 
 PART_DTYPE = np.dtype([
     ("read_idx", "<u4"), ("part_offset", "<u4"), ("raw_len", "<u4"), ("n_codes", "<u4"),
@@ -88,6 +89,7 @@ def load_library(path=None):
     L.mbgfe_exchange_edge_pack.argtypes = [C.c_void_p, C.c_void_p, C.POINTER(C.c_void_p)]
     L.mbgfe_exchange_insert_edges.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64]
     L.mbgfe_build_unitigs.argtypes = [C.c_void_p, C.c_uint32, C.c_double]
+    L.mbgfe_build_unitigs_ex.argtypes = [C.c_void_p, C.c_uint32, C.c_double, C.c_uint32]
     L.mbgfe_set_variants.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint64]
     L.mbgfe_kat_tables.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
     L.mbgfe_kat_kmer_hash.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p]
@@ -239,10 +241,11 @@ class MbgFrontEnd:
     def edges(self, copy=True):
         return self._data(EDGES, "<u4", 6, copy).reshape(-1, 6)
 
-    def build_unitigs(self, kmer_abundance, unitig_abundance):
-        """getUnitigGraph (MBG/MBG.cpp:629-760, no oneCovHeuristic / keepGaps) on the device -> dict of the filtered
-        HashList and the unitig chains (names as in include/mbgfe.h)"""
-        self._check(self.lib.mbgfe_build_unitigs(self.handle, int(kmer_abundance), float(unitig_abundance)))
+    def build_unitigs(self, kmer_abundance, unitig_abundance, one_cov_heuristic=False):
+        """getUnitigGraph (MBG/MBG.cpp:629-760, no keepGaps) on the device -> dict of the filtered HashList and the
+        unitig chains (names as in include/mbgfe.h).  one_cov_heuristic = the function's last argument
+        (removeOnecovNodes, MBG/MBG.cpp:527-627; on for runMBG's final graph under Verkko's flags)"""
+        self._check(self.lib.mbgfe_build_unitigs_ex(self.handle, int(kmer_abundance), float(unitig_abundance), UNITIG_ONECOV_HEURISTIC if one_cov_heuristic else 0))
         return dict(kept=self._data(NODE_KEPT, "u1"), node_hash=self._data(F_NODE_HASHES, "<u8", 2).reshape(-1, 2),
                     node_cov=self._data(F_NODE_COVERAGE, "<u4"), node_tip=self._data(F_NODE_TIP, "u1"),
                     edges=self._data(F_EDGES, "<u4", 6).reshape(-1, 6), unitig_begin=self._data(UNITIG_BEGIN, "<u8"),
