@@ -55,6 +55,14 @@ uint64_t orc_unitigs_count(const orc_unitigs* u, int what);
  *       7 unitig edges(u32 x6: from unitig, from_fw, to unitig, to_fw, coverage, 0; UnitigGraph::edges / edgeCov) */
 const void* orc_unitigs_data(const orc_unitigs* u, int what);
 
+/* Read threading (row f2): getKmerLocator + iterateReadPaths (MBG/KmerMatcher.cpp:3-31, KmerMatcher.h:12-144) of every
+ * hashed part through the unitigs of `u`, in input order (getReadPaths, MBG/MBG.cpp:1235-1251) */
+typedef struct orc_paths orc_paths;
+orc_paths* orc_read_paths(const orc* o, const orc_unitigs* u, uint32_t k);
+void orc_paths_free(orc_paths* p);
+uint64_t orc_paths_count(const orc_paths* p, int what);   /* 0 paths, 1 path entries, 2 readPoses entries */
+const void* orc_paths_data(const orc_paths* p, int what); /* 0 heads (u64 x6: read, part offset, n path, n poses, leftClip, rightClip) 1 path (u32 = 2*unitig + fw) 2 readPoses (u32) */
+
 /* primitives, exported for the known-answer tests */
 uint64_t orc_char_hash(uint64_t code);
 uint16_t orc_complement(uint16_t code);

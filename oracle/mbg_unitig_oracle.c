@@ -354,3 +354,165 @@ const void* orc_unitigs_data(const orc_unitigs* u, int what)
 	switch (what) { case 0: return u->kept; case 1: return u->f_hash; case 2: return u->f_cov; case 3: return u->f_tip; case 4: return u->f_edges; case 5: return u->unitig_begin; case 6: return u->unitig_nodes; case 7: return u->uedges; }
 	return 0;
 }
+
+/* ---- read threading: getKmerLocator (MBG/KmerMatcher.cpp:3-31) and iterateReadPaths
+ * (MBG/KmerMatcher.h:12-144) over every hashed part, in input order (getReadPaths, MBG/MBG.cpp:1235-1251).
+ * Sequential, statement by statement; note that readPoses is NOT cleared when a path ends at a k-mer that sits in no
+ * unitig (KmerMatcher.h:31-47), so the next path of that part starts with the old entries. */
+struct orc_paths {
+	uint64_t n_paths, n_path, n_poses, cap_paths, cap_path, cap_poses;
+	uint64_t* head;      /* x6: read index, part offset, path entries, readPoses entries, leftClip, rightClip */
+	uint32_t* path;      /* 2*unitig + fw */
+	uint32_t* poses;
+};
+
+void orc_paths_free(orc_paths* p) { if (!p) return; free(p->head); free(p->path); free(p->poses); free(p); }
+
+typedef struct { uint32_t* path; uint64_t n_path, cap_path; uint32_t* poses; uint64_t n_poses, cap_poses; uint64_t left, right; } cur_path;
+
+static void emit_path(orc_paths* out, const orc_part* part, const cur_path* c)
+{
+	if (out->n_paths + 1 > out->cap_paths) { out->cap_paths = 2 * out->cap_paths + 64; out->head = (uint64_t*)realloc(out->head, out->cap_paths * 48); }
+	if (out->n_path + c->n_path > out->cap_path) { out->cap_path = 2 * (out->n_path + c->n_path) + 64; out->path = (uint32_t*)realloc(out->path, out->cap_path * 4); }
+	if (out->n_poses + c->n_poses > out->cap_poses) { out->cap_poses = 2 * (out->n_poses + c->n_poses) + 64; out->poses = (uint32_t*)realloc(out->poses, out->cap_poses * 4); }
+	uint64_t* h = out->head + 6 * out->n_paths++;
+	h[0] = part->read_idx; h[1] = part->part_offset; h[2] = c->n_path; h[3] = c->n_poses; h[4] = c->left; h[5] = c->right;
+	memcpy(out->path + out->n_path, c->path, c->n_path * 4); out->n_path += c->n_path;
+	memcpy(out->poses + out->n_poses, c->poses, c->n_poses * 4); out->n_poses += c->n_poses;
+}
+static void push_path(cur_path* c, uint32_t v) { if (c->n_path == c->cap_path) { c->cap_path = 2 * c->cap_path + 16; c->path = (uint32_t*)realloc(c->path, c->cap_path * 4); } c->path[c->n_path++] = v; }
+static void push_pos(cur_path* c, uint32_t v) { if (c->n_poses == c->cap_poses) { c->cap_poses = 2 * c->cap_poses + 16; c->poses = (uint32_t*)realloc(c->poses, c->cap_poses * 4); } c->poses[c->n_poses++] = v; }
+
+/* canon() (MBG/MBGCommon.cpp:78-89) of an oriented pair, packed */
+static uint64_t canon_key(uint32_t from, uint32_t ffw, uint32_t to, uint32_t tfw)
+{
+	if (to < from || (to == from && !tfw && !ffw)) { uint32_t a = from, b = ffw; from = to; ffw = !tfw; to = a; tfw = !b; }
+	return ((uint64_t)from << 34) | ((uint64_t)ffw << 33) | ((uint64_t)to << 1) | tfw;
+}
+static int cmp_pair(const void* a, const void* b) { return cmp_u64(a, b); }
+/* sorted (key, value) pairs from u32 x6 edge records */
+static uint64_t* edge_index(const uint32_t* edges, uint64_t m, int value_col)
+{
+	uint64_t* ix = (uint64_t*)malloc((m + 1) * 16);
+	for (uint64_t e = 0; e < m; e++) { const uint32_t* r = edges + 6 * e; ix[2 * e] = canon_key(r[0], r[1], r[2], r[3]); ix[2 * e + 1] = r[value_col]; }
+	qsort(ix, m, 16, cmp_pair);
+	return ix;
+}
+static int edge_find(const uint64_t* ix, uint64_t m, uint64_t key, uint64_t* value)
+{
+	uint64_t lo = 0, hi = m;
+	while (lo < hi) { uint64_t mid = (lo + hi) / 2; if (ix[2 * mid] < key) lo = mid + 1; else hi = mid; }
+	if (lo < m && ix[2 * lo] == key) { if (value) *value = ix[2 * lo + 1]; return 1; }
+	return 0;
+}
+
+orc_paths* orc_read_paths(const orc* o, const orc_unitigs* u, uint32_t k)
+{
+	const uint64_t NONE = ~0ull;
+	orc_paths* out = (orc_paths*)calloc(1, sizeof(orc_paths));
+	const uint64_t nk = u->n_kept;
+	/* getKmerLocator: node -> (unitig, position, fw) */
+	uint64_t* loc_unitig = (uint64_t*)malloc((nk + 1) * 8);
+	uint64_t* loc_pos = (uint64_t*)malloc((nk + 1) * 8);
+	uint8_t* loc_fw = (uint8_t*)malloc(nk + 1);
+	for (uint64_t i = 0; i < nk; i++) { loc_unitig[i] = NONE; loc_pos[i] = NONE; loc_fw[i] = 1; }
+	for (uint64_t t = 0; t < u->n_unitigs; t++)
+	{
+		const uint64_t b = u->unitig_begin[t], size = u->unitig_begin[t + 1] - b;
+		for (uint64_t j = 0; j < size; j++)
+		{
+			const uint32_t x = u->unitig_nodes[b + j];
+			loc_unitig[x >> 1] = t;
+			if (x & 1) { loc_pos[x >> 1] = j; loc_fw[x >> 1] = 1; } else { loc_pos[x >> 1] = size - 1 - j; loc_fw[x >> 1] = 0; }
+		}
+	}
+	uint64_t* overlap_ix = edge_index(u->f_edges, u->n_fedges, 5);
+	uint64_t* uedge_ix = edge_index(u->uedges, u->n_uedges, 4);
+	const orc_part* parts = (const orc_part*)orc_data(o, 0);
+	const uint64_t n_parts = orc_count(o, 0);
+	const uint32_t* positions = (const uint32_t*)orc_data(o, 3);
+	const uint64_t* hashes = (const uint64_t*)orc_data(o, 4);
+	cur_path cur;
+	memset(&cur, 0, sizeof(cur));
+	for (uint64_t pi = 0; pi < n_parts; pi++)
+	{
+		const orc_part* part = parts + pi;
+		if (!part->hashed) continue;
+		cur.n_path = 0; cur.n_poses = 0; cur.left = 0; cur.right = 0;      /* a fresh ReadPath per call */
+		uint64_t last_read_pos = NONE, last_kmer = NONE, last_kmer_fw = 1;
+		uint64_t last_unitig = NONE, last_upos = NONE, last_ufw = 1;
+		for (uint64_t i = 0; i < part->n_sel; i++)
+		{
+			const uint64_t read_pos = positions[part->sel_begin + i];
+			const uint64_t f_lo = hashes[2 * (part->sel_begin + i)], f_hi = hashes[2 * (part->sel_begin + i) + 1];
+			/* getNodeOrNull (MBG/HashList.cpp:85-101): bwHash = halves swapped */
+			const uint64_t b_lo = f_hi, b_hi = f_lo;
+			const int fw = (f_hi < b_hi) || (f_hi == b_hi && f_lo < b_lo);
+			const uint64_t c_lo = fw ? f_lo : b_lo, c_hi = fw ? f_hi : b_hi;
+			uint64_t lo = 0, hi = nk;
+			while (lo < hi) { uint64_t mid = (lo + hi) / 2; if (u->f_hash[2 * mid + 1] < c_hi || (u->f_hash[2 * mid + 1] == c_hi && u->f_hash[2 * mid] < c_lo)) lo = mid + 1; else hi = mid; }
+			if (!(lo < nk && u->f_hash[2 * lo] == c_lo && u->f_hash[2 * lo + 1] == c_hi)) continue;
+			const uint64_t kmer = lo;
+			if (loc_unitig[kmer] == NONE)
+			{
+				if (cur.n_path > 0) emit_path(out, part, &cur);
+				cur.n_path = 0; cur.left = 0; cur.right = 0;
+				last_unitig = NONE; last_upos = NONE; last_ufw = 1;
+				last_read_pos = read_pos; last_kmer = kmer; last_kmer_fw = fw;
+				continue;
+			}
+			uint64_t p_unitig = loc_unitig[kmer], p_pos = loc_pos[kmer], p_fw = loc_fw[kmer];
+			const uint64_t usize = u->unitig_begin[p_unitig + 1] - u->unitig_begin[p_unitig];
+			if (!fw) { p_fw = !p_fw; p_pos = usize - 1 - p_pos; }
+			if (last_unitig == NONE)
+			{
+				push_path(&cur, (uint32_t)(2 * p_unitig + p_fw));
+				push_pos(&cur, (uint32_t)read_pos);
+				cur.right = usize - 1 - p_pos; cur.left = p_pos;
+				last_unitig = p_unitig; last_upos = p_pos; last_ufw = p_fw; last_read_pos = read_pos; last_kmer = kmer; last_kmer_fw = fw;
+				continue;
+			}
+			int restart = 0;
+			if (last_kmer != NONE)
+			{
+				uint64_t ov = 0;
+				const int has = edge_find(overlap_ix, u->n_fedges, canon_key((uint32_t)last_kmer, (uint32_t)last_kmer_fw, (uint32_t)kmer, (uint32_t)fw), &ov);
+				if (!has || read_pos - last_read_pos != k - ov) restart = 1;
+			}
+			if (!restart)
+			{
+				if (p_unitig == last_unitig && p_fw == last_ufw && p_pos == last_upos + 1)
+				{
+					last_unitig = p_unitig; last_upos = p_pos; last_ufw = p_fw; last_read_pos = read_pos; last_kmer = kmer; last_kmer_fw = fw;
+					cur.right -= 1;
+					push_pos(&cur, (uint32_t)read_pos);
+					continue;
+				}
+				const uint64_t last_size = u->unitig_begin[last_unitig + 1] - u->unitig_begin[last_unitig];
+				if (edge_find(uedge_ix, u->n_uedges, canon_key((uint32_t)last_unitig, (uint32_t)last_ufw, (uint32_t)p_unitig, (uint32_t)p_fw), 0) && p_pos == 0 && last_upos == last_size - 1)
+				{
+					push_path(&cur, (uint32_t)(2 * p_unitig + p_fw));
+					push_pos(&cur, (uint32_t)read_pos);
+					cur.right = usize - 1;
+					last_unitig = p_unitig; last_upos = p_pos; last_ufw = p_fw; last_read_pos = read_pos; last_kmer = kmer; last_kmer_fw = fw;
+					continue;
+				}
+			}
+			emit_path(out, part, &cur);
+			cur.n_path = 0; cur.n_poses = 0;
+			push_path(&cur, (uint32_t)(2 * p_unitig + p_fw));
+			push_pos(&cur, (uint32_t)read_pos);
+			cur.left = p_pos; cur.right = usize - 1 - p_pos;
+			last_unitig = p_unitig; last_upos = p_pos; last_ufw = p_fw; last_read_pos = read_pos; last_kmer = kmer; last_kmer_fw = fw;
+		}
+		if (cur.n_path > 0) emit_path(out, part, &cur);
+	}
+	free(cur.path); free(cur.poses);
+	free(loc_unitig); free(loc_pos); free(loc_fw); free(overlap_ix); free(uedge_ix);
+	return out;
+}
+
+/* what: 0 paths, 1 path entries, 2 readPoses entries */
+uint64_t orc_paths_count(const orc_paths* p, int what) { switch (what) { case 0: return p->n_paths; case 1: return p->n_path; case 2: return p->n_poses; } return 0; }
+/* what: 0 heads (u64 x6) 1 path (u32 = 2*unitig + fw) 2 readPoses (u32) */
+const void* orc_paths_data(const orc_paths* p, int what) { switch (what) { case 0: return p->head; case 1: return p->path; case 2: return p->poses; } return 0; }

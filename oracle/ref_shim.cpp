@@ -27,6 +27,7 @@
 uint64_t getHash(uint64_t key); // FastHasher.cpp:33
 void loadReadsAsHashesMultithread(HashList& result, const size_t kmerSize, const ReadpartIterator& partIterator, const size_t numThreads, std::ostream& log);
 #include "UnitigGraph.h"
+#include "KmerMatcher.h"
 UnitigGraph getUnitigGraph(HashList& hashlist, const size_t minCoverage, const double minUnitigCoverage, const bool keepGaps, const bool oneCovHeuristic); // MBG.cpp:629
 
 namespace {
@@ -49,6 +50,10 @@ struct Run {
 	std::vector<uint8_t> node_tip;
 	std::vector<uint32_t> edges; // from_id, from_fw, to_id, to_fw, coverage, overlap
 	std::vector<uint32_t> uedges; // unitig graph edges: from unitig, from_fw, to unitig, to_fw, coverage, overlap -- canonical
+	// read paths (iterateReadPaths): per path read index, part offset, path entries, readPoses entries, leftClip, rightClip
+	std::vector<uint64_t> rp_head;
+	std::vector<uint32_t> rp_path;  // 2*unitig + fw
+	std::vector<uint32_t> rp_poses;
 	uint64_t total_selected = 0;
 };
 
@@ -311,6 +316,25 @@ void* refshim_unitigs_ex(int mode, uint64_t k, uint64_t w, const char* bases, co
 			}
 		}
 	}
+	// getReadPaths (MBG.cpp:1235-1251): every part threaded through the unitig graph (KmerMatcher.h:12-144), in input order
+	if (memoryReads.size() > 0)
+	{
+		std::vector<std::tuple<size_t, size_t, bool>> kmerLocator = getKmerLocator(unitigs);
+		tableIterator.iterateOnlyHashes([run, &kmerLocator, k, &unitigs, &list](const ReadInfo& read, const std::vector<size_t>& positions, const std::vector<HashType>& hashes)
+		{
+			iterateReadPaths(unitigs, list, (size_t)k, kmerLocator, read, positions, hashes, [run](ReadPath path)
+			{
+				run->rp_head.push_back(std::stoull(path.readName.first));
+				run->rp_head.push_back(path.readName.second);
+				run->rp_head.push_back(path.path.size());
+				run->rp_head.push_back(path.readPoses.size());
+				run->rp_head.push_back(path.leftClip);
+				run->rp_head.push_back(path.rightClip);
+				for (auto node : path.path) run->rp_path.push_back((uint32_t)(2 * node.id() + (node.forward() ? 1 : 0)));
+				for (auto pos : path.readPoses) run->rp_poses.push_back(pos);
+			});
+		});
+	}
 	return run;
 }
 
@@ -329,6 +353,9 @@ uint64_t refshim_count(void* h, int what)
 		case 5: return r->edges.size() / 6;
 		case 6: return r->total_selected;
 		case 7: return r->uedges.size() / 6;
+		case 8: return r->rp_head.size() / 6;
+		case 9: return r->rp_path.size();
+		case 10: return r->rp_poses.size();
 	}
 	return 0;
 }
@@ -348,6 +375,9 @@ const void* refshim_data(void* h, int what)
 		case 7: return r->node_tip.data();
 		case 8: return r->edges.data();
 		case 9: return r->uedges.data();
+		case 10: return r->rp_head.data();
+		case 11: return r->rp_path.data();
+		case 12: return r->rp_poses.data();
 	}
 	return nullptr;
 }

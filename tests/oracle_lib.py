@@ -119,7 +119,7 @@ class Oracle:
         finally:
             L.orc_free(h)
 
-    def run_unitigs(self, mode, k, w, reads, min_cov, min_unitig_cov, variants=None, one_cov=False):
+    def run_unitigs(self, mode, k, w, reads, min_cov, min_unitig_cov, variants=None, one_cov=False, paths=False):
         """table + the filter/unitig step after it -> (RunResult, UnitigResult); one_cov = getUnitigGraph's oneCovHeuristic"""
         bases, offsets = reads if isinstance(reads, tuple) else pack_reads(reads)
         L = self.lib
@@ -146,6 +146,20 @@ class Oracle:
                                node_tip=_arr(dat(3), cnt(1), "u1"), edges=_arr(dat(4), cnt(2) * 6, "<u4").reshape(-1, 6),
                                unitig_begin=_arr(dat(5), cnt(3) + 1, "<u8"), unitig_nodes=_arr(dat(6), cnt(4), "<u4"),
                                unitig_edges=_arr(dat(7), cnt(5) * 6, "<u4").reshape(-1, 6))
+            if paths:      # row f2: getReadPaths over the same run
+                L.orc_read_paths.restype = C.c_void_p
+                L.orc_read_paths.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32]
+                L.orc_paths_free.argtypes = [C.c_void_p]
+                L.orc_paths_count.argtypes = [C.c_void_p, C.c_int]
+                L.orc_paths_count.restype = C.c_uint64
+                L.orc_paths_data.argtypes = [C.c_void_p, C.c_int]
+                L.orc_paths_data.restype = C.c_void_p
+                rp = L.orc_read_paths(h, u, k)
+                try:
+                    res["paths"] = ReadPaths(heads=_arr(L.orc_paths_data(rp, 0), L.orc_paths_count(rp, 0) * 6, "<u8").reshape(-1, 6),
+                                             path=_arr(L.orc_paths_data(rp, 1), L.orc_paths_count(rp, 1), "<u4"), poses=_arr(L.orc_paths_data(rp, 2), L.orc_paths_count(rp, 2), "<u4"))
+                finally:
+                    L.orc_paths_free(rp)
             return table, res
         finally:
             if u:
@@ -244,8 +258,10 @@ class Reference:
             r = _collect(lambda w_: L.refshim_count(h, w_), lambda w_: L.refshim_data(h, w_), True)
             begin = np.concatenate([r.parts["sel_begin"], [len(r.positions)]]).astype(np.uint64) if len(r.parts) else np.zeros(1, np.uint64)
             ue = _arr(L.refshim_data(h, 9), L.refshim_count(h, 7) * 6, "<u4").reshape(-1, 6)
+            paths = ReadPaths(heads=_arr(L.refshim_data(h, 10), L.refshim_count(h, 8) * 6, "<u8").reshape(-1, 6), path=_arr(L.refshim_data(h, 11), L.refshim_count(h, 9), "<u4"),
+                              poses=_arr(L.refshim_data(h, 12), L.refshim_count(h, 10), "<u4"))
             return UnitigResult(kept=None, node_hash=r.node_hash, node_cov=r.node_cov, node_tip=r.node_tip, edges=r.edges, unitig_begin=begin, unitig_nodes=r.positions,
-                                unitig_edges=ue)
+                                unitig_edges=ue, paths=paths)
         finally:
             L.refshim_free(h)
 
@@ -285,6 +301,40 @@ class Reference:
         op = np.zeros(len(sym) + 2, dtype=np.uint64)
         n = self.lib.refshim_msat(sym.ctypes.data, poses.ctypes.data, len(sym), max_motif, oc.ctypes.data, op.ctypes.data)
         return oc[:n].copy(), op[:n + 1].copy()
+
+
+class ReadPaths(dict):
+    """getReadPaths' result, flat: heads[n, 6] = (read index, part offset, path entries, readPoses entries, leftClip,
+    rightClip), path[] = 2*unitig + fw, poses[] = readPoses"""
+    __getattr__ = dict.__getitem__
+
+
+def expand_paths(rp, u):
+    """numbering-free form of ReadPaths: every path as (read, part offset, oriented k-mers it covers as (hash lo, hash hi,
+    fw), readPoses).  Unitig numbering, orientation and where a circular unitig was cut all drop out."""
+    b = u.unitig_begin.astype(np.int64)
+    out = []
+    at_p = at_q = 0
+    for read, off, n_path, n_poses, left, right in rp.heads.astype(np.int64).tolist():
+        seq = []
+        for x in rp.path[at_p:at_p + n_path].tolist():
+            nodes = u.unitig_nodes[b[x >> 1]:b[(x >> 1) + 1]].astype(np.int64)
+            seq.append(nodes if x & 1 else (nodes[::-1] ^ 1))
+        seq = np.concatenate(seq) if seq else np.zeros(0, np.int64)
+        seq = seq[left:len(seq) - right]
+        kmers = tuple(zip(u.node_hash[seq >> 1, 0].tolist(), u.node_hash[seq >> 1, 1].tolist(), (seq & 1).tolist()))
+        out.append((read, off, kmers, tuple(rp.poses[at_q:at_q + n_poses].tolist())))
+        at_p += n_path
+        at_q += n_poses
+    return out
+
+
+def compare_paths(a, ua, b, ub, what=""):
+    """ReadPaths a over UnitigResult ua against b over ub, in order (paths come out in input order on one thread)"""
+    ea, eb = expand_paths(a, ua), expand_paths(b, ub)
+    assert len(ea) == len(eb), f"{what}: {len(ea)} read paths vs {len(eb)}"
+    for i, (x, y) in enumerate(zip(ea, eb)):
+        assert x == y, f"{what}: read path {i} differs (read {x[0]} part {x[1]}: {len(x[2])} k-mers / {len(x[3])} poses vs read {y[0]} part {y[1]}: {len(y[2])} / {len(y[3])})"
 
 
 class UnitigResult(dict):

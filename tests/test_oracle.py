@@ -171,3 +171,21 @@ def test_onecov_heuristic_equals_reference(oracle, reference, mode, k, w, a, u):
         _, plain = oracle.run_unitigs(mode, k, w, reads, a, u)
         changed += int(not np.array_equal(plain.kept, got.kept))
     assert changed > 0 or a > 1, "the heuristic never changed the kept set: the workloads do not exercise it"
+
+
+@pytest.mark.parametrize("mode,k,w,a,u,one_cov", [("collapse-msat", 301, 30, 1, 2, True), ("hpc", 301, 30, 2, 2, False), ("hpc", 63, 33, 1, 3, True), ("collapse-msat", 101, 20, 2, 2, False),
+                                                  ("no", 63, 5, 1, 2, False), ("no", 63, 5, 1, 1, True)])
+def test_read_paths_equal_reference(oracle, reference, mode, k, w, a, u, one_cov):
+    """row f2: getKmerLocator + iterateReadPaths (MBG/KmerMatcher.cpp:3-31, KmerMatcher.h:12-144) of every part through
+    the unitig graph, against the reference's own functions on its own graph; compared as the oriented k-mers and read
+    positions every path covers (unitig numbering drops out)"""
+    from oracle_lib import compare_paths
+    n_paths = 0
+    for reads in (workloads.coverage_reads(n_reads=40, error_ppm=4000), workloads.coverage_reads(seed=3, genome_len=20000, n_reads=12, error_ppm=10000),
+                  [workloads.repeat_rich(3, 6000), workloads.repeat_rich(3, 6000), workloads.repeat_rich(4, 3000)],
+                  workloads.circular_reads() + workloads.circular_reads(seed=10, genome_len=2000, read_len=1500, step=250) + [lcg_bases(77, 1500)]):
+        _, got = oracle.run_unitigs(mode, k, w, reads, a, u, one_cov=one_cov, paths=True)
+        want = reference.run_unitigs(mode, k, w, reads, a, u, one_cov=one_cov)
+        compare_paths(got.paths, got, want.paths, want, what=f"read paths {mode} k={k} a={a} u={u}")
+        n_paths += len(got.paths.heads)
+    assert n_paths > 20
