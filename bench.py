@@ -381,6 +381,13 @@ def main():
         st_u = fe.stats()
         unitig_info["one_cov_heuristic"] = {"ms": st_u["ms_unitigs"], "kept_nodes": int(len(u["node_cov"])), "kept_edges": int(len(u["edges"])),
                                             "unitigs": int(len(u["unitig_begin"]) - 1), "unitig_edges": int(len(u["unitig_edges"])), "launches": st_u["launches"]}
+        # row f2: every resident k-mer instance threaded through those unitigs (getReadPaths as a batched lookup)
+        fe.thread_reads()
+        th = fe.thread_reads()
+        st_t = fe.stats()
+        steps = np.bincount(th["step"], minlength=6)
+        unitig_info["thread_reads"] = {"ms": st_t["ms_unitigs"], "instances": int(len(th["step"])), "launches": st_t["launches"],
+                                       "located": int(steps[2:].sum()), "paths": int(steps[2] + steps[3]), "unitig_crossings": int(steps[5])}
     e2e_t = torch.tensor([float(np.mean(e2e_ms))], dtype=torch.float64, device="cuda")
     if world > 1:
         dist.all_reduce(e2e_t, op=dist.ReduceOp.MAX)

@@ -103,8 +103,13 @@ enum {
 	MBGFE_UNITIG_BEGIN = 14,    /* uint64_t[n_unitigs + 1] offsets into MBGFE_UNITIG_NODES                             */
 	MBGFE_UNITIG_NODES = 15,    /* uint32_t[] 2 * filtered node id + fw, in unitig order (UnitigGraph::unitigs)        */
 	MBGFE_F_NODE_UNITIG = 16,   /* uint32_t[] unitig of each filtered node, 0xffffffff when its coverage is below -a   */
-	MBGFE_UNITIG_EDGES = 17     /* mbgfe_edge[] between unitig ends (UnitigGraph::edges / edgeCov, MBG/MBG.cpp:746-760):
+	MBGFE_UNITIG_EDGES = 17,    /* mbgfe_edge[] between unitig ends (UnitigGraph::edges / edgeCov, MBG/MBG.cpp:746-760):
 	                               from / to = unitig, *_fw = read forward, coverage of the k-mer edge, overlap 0          */
+	/* after mbgfe_thread_reads(): one entry per selected k-mer instance, in MBGFE_POSITIONS order */
+	MBGFE_INST_UNITIG = 18,     /* uint32_t[] 2 * unitig + orientation as the read sees it; 0xffffffff = not located      */
+	MBGFE_INST_UNITIG_POS = 19, /* uint32_t[] position inside that oriented unitig (leftClip of a path = its first entry)   */
+	MBGFE_INST_UNITIG_REST = 20,/* uint32_t[] k-mers of the unitig behind it (rightClip of a path = its last entry)         */
+	MBGFE_INST_STEP = 21        /* uint8_t[]  what iterateReadPaths does at this k-mer, see mbgfe_thread_reads             */
 };
 
 typedef struct {
@@ -194,6 +199,21 @@ int mbgfe_build_unitigs(mbgfe* h, uint32_t kmer_abundance, double unitig_abundan
  * MBGFE_NODE_KEPT then marks the survivors of all three filters. */
 #define MBGFE_UNITIG_ONECOV_HEURISTIC 1u
 int mbgfe_build_unitigs_ex(mbgfe* h, uint32_t kmer_abundance, double unitig_abundance, uint32_t flags);
+
+/* Read threading: getReadPaths (MBG/MBG.cpp:1235-1251) = getKmerLocator (MBG/KmerMatcher.cpp:3-31) + iterateReadPaths
+ * (MBG/KmerMatcher.h:12-144) as one batched lookup.  The selected k-mers of the last run are still resident (the
+ * reference re-reads and re-hashes the input for this pass); each one is looked up in the filtered list and the unitigs
+ * of the last mbgfe_build_unitigs[_ex] and classified.  MBGFE_INST_STEP says what iterateReadPaths does there:
+ *   0  k-mer not in the filtered list: skipped, state unchanged (KmerMatcher.h:29)
+ *   1  k-mer in no unitig: the open path, if any, ends; its readPoses are NOT cleared (KmerMatcher.h:30-47)
+ *   2  first located k-mer of the part or after a 1: a path starts, readPoses is appended to (KmerMatcher.h:55-67)
+ *   3  a path starts after a break: readPoses cleared (KmerMatcher.h:68-93, 121-141)
+ *   4  next k-mer of the same unitig: readPoses gets the position, rightClip shrinks (KmerMatcher.h:95-104)
+ *   5  first k-mer of the next unitig: path gets MBGFE_INST_UNITIG (KmerMatcher.h:105-120)
+ * A ReadPath is a run 2|3, (4|5)*; path = MBGFE_INST_UNITIG of its 2|3|5 entries, readPoses = MBGFE_POSITIONS of all its
+ * entries, leftClip = MBGFE_INST_UNITIG_POS of the first, rightClip = MBGFE_INST_UNITIG_REST of the last.
+ * Unitigs are numbered as mbgfe_build_unitigs numbers them.  world == 1. */
+int mbgfe_thread_reads(mbgfe* h);
 
 /* Device-side stopwatch on the library's stream (CUDA events): start, any number of calls, stop -> milliseconds. */
 int mbgfe_timer_start(mbgfe* h);

@@ -22,7 +22,7 @@ def run_frontend(mode, k, w, reads, library=None, flags=KEEP_CODES | KEEP_POSES,
         fe.close()
 
 
-def run_frontend_unitigs(mode, k, w, reads, min_cov, min_unitig_cov, library=None, one_cov=False, **kw):
+def run_frontend_unitigs(mode, k, w, reads, min_cov, min_unitig_cov, library=None, one_cov=False, paths=False, **kw):
     """table + mbgfe_build_unitigs -> (RunResult of the table, UnitigResult)"""
     from oracle_lib import UnitigResult
     fe = MbgFrontEnd(k, w, mode, library=library, **kw)
@@ -35,6 +35,12 @@ def run_frontend_unitigs(mode, k, w, reads, min_cov, min_unitig_cov, library=Non
         table = RunResult(node_hash=fe.node_hashes(), node_cov=fe.node_coverage(), node_tip=fe.node_tip(), edges=fe.edges())
         u = UnitigResult(fe.build_unitigs(min_cov, min_unitig_cov, one_cov_heuristic=one_cov))
         u["stats"] = fe.stats()
+        if paths:      # row f2: mbgfe_thread_reads, assembled into ReadPaths by the host mirror
+            from oracle_lib import ReadPaths
+            rp = fe.read_paths()
+            u["paths"] = ReadPaths(heads=rp["heads"], path=rp["path"], poses=rp["poses"])
+            u["thread_arrays"] = rp["arrays"]
+            u["thread_stats"] = fe.stats()
         return table, u
     finally:
         fe.close()

@@ -112,6 +112,21 @@ def test_emulated_onecov_heuristic(oracle, emu_library, mode, k, w, a, u, which)
         assert not np.array_equal(plain.kept, want.kept), "the heuristic did not change anything on this workload"
 
 
+@pytest.mark.parametrize("mode,k,w,a,u,one_cov,which", [("collapse-msat", 301, 30, 1, 2, True, "coverage"), ("hpc", 63, 33, 2, 2, False, "noisy"), ("no", 63, 5, 1, 1, False, "circular")])
+def test_emulated_read_threading(oracle, emu_library, mode, k, w, a, u, one_cov, which):
+    """row f2: mbgfe_thread_reads (getKmerLocator + iterateReadPaths as a batched lookup) on the emulator build, against
+    the oracle's sequential restatement (pinned on the reference's own functions in tests/test_oracle.py)"""
+    from fe_helpers import run_frontend_unitigs
+    from oracle_lib import compare_paths
+    reads = {"coverage": lambda: workloads.coverage_reads(n_reads=16, error_ppm=4000),
+             "noisy": lambda: workloads.coverage_reads(seed=3, genome_len=8000, n_reads=10, error_ppm=10000),
+             "circular": lambda: workloads.circular_reads(genome_len=1500, read_len=1200, step=300) + [workloads.lcg_bases(77, 800)]}[which]()
+    _, got = run_frontend_unitigs(mode, k, w, reads, a, u, library=emu_library, one_cov=one_cov, paths=True)
+    _, want = oracle.run_unitigs(mode, k, w, reads, a, u, one_cov=one_cov, paths=True)
+    compare_paths(got.paths, got, want.paths, want, f"emu read paths {mode} k={k}")
+    assert len(want.paths.heads) > 0
+
+
 def test_emulated_hash_in_groups(oracle, emu_library, monkeypatch):
     """k_kmer_hash_lanes with a staging area much smaller than a read: k-mers are hashed in groups of consecutive ones"""
     monkeypatch.setenv("MBGFE_HASH_LANES", "1")

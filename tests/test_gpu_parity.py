@@ -250,6 +250,31 @@ def test_onecov_heuristic_against_oracle(oracle, mode, k, w, a, u):
 
 
 @pytest.mark.gpu
+@pytest.mark.parametrize("mode,k,w,a,u,one_cov", [("collapse-msat", 1001, 100, 1, 2, True), ("collapse-msat", 301, 30, 1, 2, True), ("hpc", 301, 30, 2, 2, False), ("hpc", 63, 33, 1, 3, True),
+                                                  ("collapse-msat", 101, 20, 2, 2, False), ("no", 63, 5, 1, 1, False)])
+def test_read_threading_against_oracle(oracle, mode, k, w, a, u, one_cov):
+    """row f2: mbgfe_thread_reads -- getKmerLocator + iterateReadPaths (MBG/KmerMatcher.cpp:3-31, KmerMatcher.h:12-144)
+    as a batched lookup over the resident k-mer instances -- against the oracle's sequential restatement (pinned on the
+    reference's own functions in tests/test_oracle.py); compared as the oriented k-mers and read positions every path covers"""
+    from fe_helpers import run_frontend_unitigs
+    from oracle_lib import compare_paths
+    big = workloads.coverage_reads(genome_len=60000, n_reads=100, len_min=9000, len_max=14000, error_ppm=3000) if k < 1001 else \
+        workloads.coverage_reads(genome_len=100000, n_reads=150, len_min=12000, len_max=20000, error_ppm=2000)
+    n_paths = 0
+    for reads in (big, workloads.coverage_reads(seed=3, genome_len=20000, n_reads=12, error_ppm=10000),
+                  [workloads.repeat_rich(3, 6000), workloads.repeat_rich(3, 6000), workloads.repeat_rich(4, 3000)],
+                  workloads.circular_reads() + workloads.circular_reads(seed=10, genome_len=2000, read_len=1500, step=250) + [lcg_bases(77, 1500)]):
+        _, got = run_frontend_unitigs(mode, k, w, reads, a, u, one_cov=one_cov, paths=True)
+        _, want = oracle.run_unitigs(mode, k, w, reads, a, u, one_cov=one_cov, paths=True)
+        compare_paths(got.paths, got, want.paths, want, f"read paths {mode} k={k} a={a} u={u}")
+        n_paths += len(want.paths.heads)
+        th = got.thread_arrays
+        located = th["unitig"] != 0xffffffff
+        assert np.all(th["step"][~located] <= 1) and np.all(th["step"][located] >= 2)
+    assert n_paths > 20
+
+
+@pytest.mark.gpu
 @pytest.mark.parametrize("mode,k,w,a,u", [("no", 63, 5, 1, 2), ("hpc", 63, 33, 1, 1), ("collapse-msat", 101, 20, 2, 2)])
 def test_unitig_filter_circular_genomes(oracle, mode, k, w, a, u):
     """chains that are cycles (no tip, no branch): the ranking detects them by its round limit, cuts them in front of

@@ -282,7 +282,7 @@ __global__ void __launch_bounds__(256) k_unitig_starts(const ChainState* __restr
 // unitig_id = exclusive scan of is_start, unitig_at = exclusive scan of start_len (both indexed by node)
 __global__ void __launch_bounds__(256) k_unitig_write(const ChainState* __restrict__ st, const uint32_t* __restrict__ cov, uint64_t n_nodes, uint32_t min_cov,
 	const uint32_t* __restrict__ is_start, const uint64_t* __restrict__ unitig_id, const uint64_t* __restrict__ unitig_at,
-	uint64_t* __restrict__ unitig_begin, uint32_t* __restrict__ unitig_nodes, uint32_t* __restrict__ node_unitig, uint32_t* __restrict__ node_ufw)
+	uint64_t* __restrict__ unitig_begin, uint32_t* __restrict__ unitig_nodes, uint32_t* __restrict__ node_unitig, uint32_t* __restrict__ node_ufw, uint32_t* __restrict__ node_upos)
 {
 	for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n_nodes; i += (uint64_t)gridDim.x * blockDim.x)
 	{
@@ -295,6 +295,7 @@ __global__ void __launch_bounds__(256) k_unitig_write(const ChainState* __restri
 		unitig_nodes[at + pos] = 2 * (uint32_t)i + same;
 		node_unitig[i] = (uint32_t)unitig_id[head];
 		node_ufw[i] = same;
+		node_upos[i] = pos;
 		if (is_start[i]) unitig_begin[unitig_id[i]] = at;
 	}
 }
@@ -331,6 +332,103 @@ __global__ void __launch_bounds__(256) k_unitig_edge_write(const EdgeRec* __rest
 	{
 		EdgeRec o;
 		if (unitig_edge_of(edges[e], min_cov, link, node_unitig, node_ufw, o)) out[at[e]] = o;
+	}
+}
+
+
+// ---- read threading: getKmerLocator (MBG/KmerMatcher.cpp:3-31) and iterateReadPaths
+// (MBG/KmerMatcher.h:12-144) as a batched lookup over the selected k-mer instances that are still resident.
+// The reference walks a part k-mer by k-mer with a small state (last k-mer, last unitig position); every decision it takes
+// at a k-mer depends only on that k-mer and the previous one that is in the filtered list, so each instance classifies
+// itself:
+//   0  not in the filtered list                    (KmerMatcher.h:29: skipped, the state does not change)
+//   1  in no unitig                                (:30-47: ends the open path; readPoses is NOT cleared)
+//   2  first located k-mer after the part start or after a 1   (:55-67: starts a path, readPoses appended to)
+//   3  starts a path after a break                 (:68-93 no sequence overlap / wrong distance, :121-141 no unitig edge)
+//   4  next k-mer of the same unitig               (:95-104)
+//   5  first k-mer of the next unitig of the path  (:105-120)
+// inst_unitig = 2*unitig + orientation as the read sees it, inst_upos = position in that orientation, inst_urest = k-mers
+// behind it (leftClip / rightClip of a path are inst_upos of its first and inst_urest of its last k-mer).
+__global__ void __launch_bounds__(256) k_invert_orig(const uint32_t* __restrict__ orig, uint64_t n_kept, uint32_t* __restrict__ final_of)
+{
+	for (uint64_t j = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; j < n_kept; j += (uint64_t)gridDim.x * blockDim.x) final_of[orig[j]] = (uint32_t)j;
+}
+
+__global__ void __launch_bounds__(256) k_thread_locate(const uint32_t* __restrict__ inst_slot, const uint64_t* __restrict__ inst_hash, uint64_t n_inst, const NodeSlot* __restrict__ table,
+	const uint32_t* __restrict__ final_of, const uint32_t* __restrict__ node_unitig, const uint32_t* __restrict__ node_ufw, const uint32_t* __restrict__ node_upos,
+	const uint64_t* __restrict__ unitig_begin, uint32_t* __restrict__ inst_node, uint32_t* __restrict__ inst_unitig, uint32_t* __restrict__ inst_upos, uint32_t* __restrict__ inst_urest)
+{
+	for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n_inst; i += (uint64_t)gridDim.x * blockDim.x)
+	{
+		uint32_t node = NO_LINK, unitig = NO_LINK, upos = 0, urest = 0;
+		const uint32_t slot = inst_slot[i];
+		if (slot != NO_LINK)
+		{
+			const uint32_t fid = final_of[(uint32_t)table[slot].rank];       // getNodeOrNull (MBG/HashList.cpp:85-101) on the filtered list
+			if (fid != NO_LINK)
+			{
+				const uint64_t lo = inst_hash[2 * i], hi = inst_hash[2 * i + 1];
+				uint64_t key_lo, key_hi; uint32_t fw;
+				canonical_key(lo, hi, key_lo, key_hi, fw);
+				node = 2 * fid + fw;
+				const uint32_t u = node_unitig[fid];
+				if (u != NO_LINK)
+				{
+					const uint32_t size = (uint32_t)(unitig_begin[u + 1] - unitig_begin[u]);
+					const uint32_t o = node_ufw[fid] == fw ? 1u : 0u;
+					const uint32_t j = node_upos[fid];
+					unitig = 2 * u + o;
+					upos = o ? j : size - 1 - j;
+					urest = size - 1 - upos;
+				}
+			}
+		}
+		inst_node[i] = node; inst_unitig[i] = unitig; inst_upos[i] = upos; inst_urest[i] = urest;
+	}
+}
+
+__device__ __forceinline__ bool edge_lookup(const EdgeSlot* __restrict__ table, uint64_t mask, unsigned long long key, uint32_t& count, uint32_t& overlap)
+{
+	uint64_t slot = slot_hash(key, key >> 17) & mask;
+	for (uint32_t probes = 0; probes < MAX_PROBES; probes++)
+	{
+		const unsigned long long cur = table[slot].key;
+		if (cur == key) { count = table[slot].count; overlap = (uint32_t)(table[slot].ordered & 0xffffff); return true; }
+		if (cur == ~0ull) return false;
+		slot = (slot + 1) & mask;
+	}
+	return false;
+}
+
+__global__ void __launch_bounds__(256) k_thread_steps(const uint32_t* __restrict__ inst_node, const uint32_t* __restrict__ inst_unitig, const uint32_t* __restrict__ inst_upos,
+	const uint32_t* __restrict__ inst_urest, const uint8_t* __restrict__ inst_flag, const uint32_t* __restrict__ inst_pos, const uint32_t* __restrict__ inst_slot,
+	const uint64_t* __restrict__ inst_hash, uint64_t n_inst, const EdgeSlot* __restrict__ edge_table, uint64_t edge_mask, uint32_t k, uint32_t min_cov, uint8_t* __restrict__ step)
+{
+	for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n_inst; i += (uint64_t)gridDim.x * blockDim.x)
+	{
+		uint32_t cls;
+		if (inst_node[i] == NO_LINK) cls = 0;
+		else if (inst_unitig[i] == NO_LINK) cls = 1;
+		else
+		{
+			// the previous k-mer of the part that is in the filtered list
+			uint64_t j = i;
+			bool have = false;
+			while (!(inst_flag[j] & 1)) { j--; if (inst_node[j] != NO_LINK) { have = true; break; } }
+			if (!have || inst_unitig[j] == NO_LINK) cls = 2;
+			else
+			{
+				cls = 3;
+				uint32_t count = 0, overlap = 0;
+				const unsigned long long key = canonical_edge_key(inst_hash[2 * j], inst_hash[2 * j + 1], inst_hash[2 * i], inst_hash[2 * i + 1], inst_slot[j], inst_slot[i]);
+				if (edge_lookup(edge_table, edge_mask, key, count, overlap) && inst_pos[i] - inst_pos[j] == k - overlap)
+				{
+					if (inst_unitig[i] == inst_unitig[j] && inst_upos[i] == inst_upos[j] + 1) cls = 4;
+					else if (count >= min_cov && inst_upos[i] == 0 && inst_urest[j] == 0) cls = 5;
+				}
+			}
+		}
+		step[i] = (uint8_t)cls;
 	}
 }
 

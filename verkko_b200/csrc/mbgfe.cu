@@ -108,11 +108,14 @@ struct mbgfe
 	DevBuf d_var_hash, d_var_offset, d_var_len_begin, d_var_len;       // hpc variants (mbgfe_set_variants), sorted
 	// mbgfe_build_unitigs: graph scratch (degrees, successor, link, two ranking states, flags, scans) and results
 	DevBuf d_g_deg, d_g_nb, d_g_link, d_g_st[2], d_g_kept, d_g_newid, d_g_flag, d_g_at, d_g_flag2, d_g_at2, d_g_flag_byte;
-	DevBuf d_f_hash, d_f_cov, d_f_tip, d_f_edges, d_f_orig, d_t_hash, d_t_cov, d_t_tip, d_t_edges, d_t_orig, d_g_kept8, d_u_begin, d_u_nodes, d_u_of_node, d_u_fw, d_u_edges;
+	DevBuf d_f_hash, d_f_cov, d_f_tip, d_f_edges, d_f_orig, d_t_hash, d_t_cov, d_t_tip, d_t_edges, d_t_orig, d_g_kept8, d_u_pos, d_th_final, d_th_node, d_th_unitig, d_th_upos, d_th_urest, d_th_step, d_u_begin, d_u_nodes, d_u_of_node, d_u_fw, d_u_edges;
 	bool have_unitigs = false;
 	uint64_t n_kept = 0, n_fedges = 0, n_unitigs = 0, n_unitig_nodes = 0, n_uedges = 0;
 	std::vector<mbgfe_edge> h_u_edges;
-	std::vector<uint8_t> h_kept, h_f_tip;
+	std::vector<uint8_t> h_kept, h_f_tip, h_th_step;
+	std::vector<uint32_t> h_th_unitig, h_th_upos, h_th_urest;
+	uint32_t unitig_min_cov = 1;
+	bool have_threads = false;
 	std::vector<mbgfe_hash128> h_f_hash;
 	std::vector<uint32_t> h_f_cov, h_u_nodes, h_u_of_node;
 	std::vector<mbgfe_edge> h_f_edges;
@@ -490,7 +493,7 @@ void mbgfe_destroy(mbgfe* h)
 		&h->d_edge_out, &h->d_records, &h->d_recv, &h->d_bucket_count, &h->d_bucket_begin, &h->d_scan_tot, &h->d_scan_off, &h->d_node_hash_sorted, &h->d_node_cov,
 		&h->d_node_tip, &h->d_edges_sorted, &h->d_inst_packpos, &h->d_ids_out, &h->d_id_begin, &h->d_edge_records, &h->d_xbuf[0], &h->d_xbuf[1], &h->d_xbuf[2],
 		&h->d_xbuf[3], &h->d_var_hash, &h->d_var_offset, &h->d_var_len_begin, &h->d_var_len, &h->d_g_deg, &h->d_g_nb, &h->d_g_link, &h->d_g_st[0], &h->d_g_st[1],
-		&h->d_g_kept, &h->d_g_newid, &h->d_g_flag, &h->d_g_at, &h->d_g_flag2, &h->d_g_at2, &h->d_g_flag_byte, &h->d_f_hash, &h->d_f_cov, &h->d_f_tip, &h->d_f_edges, &h->d_f_orig, &h->d_t_hash, &h->d_t_cov, &h->d_t_tip, &h->d_t_edges, &h->d_t_orig, &h->d_g_kept8,
+		&h->d_g_kept, &h->d_g_newid, &h->d_g_flag, &h->d_g_at, &h->d_g_flag2, &h->d_g_at2, &h->d_g_flag_byte, &h->d_f_hash, &h->d_f_cov, &h->d_f_tip, &h->d_f_edges, &h->d_f_orig, &h->d_t_hash, &h->d_t_cov, &h->d_t_tip, &h->d_t_edges, &h->d_t_orig, &h->d_g_kept8, &h->d_u_pos, &h->d_th_final, &h->d_th_node, &h->d_th_unitig, &h->d_th_upos, &h->d_th_urest, &h->d_th_step,
 		&h->d_u_begin, &h->d_u_nodes, &h->d_u_of_node, &h->d_u_fw, &h->d_u_edges }) release(*b);
 	for (HostBuf* b : { &h->p_node_hashes, &h->p_node_cov, &h->p_node_tip, &h->p_edges, &h->p_stage }) release_host(*b);
 	for (auto& e : h->ev) if (e) cudaEventDestroy(e);
@@ -1476,6 +1479,8 @@ int mbgfe_build_unitigs_ex(mbgfe* h, uint32_t kmer_abundance, double unitig_abun
 	if (int rc = export_table(h)) return rc;
 	const uint64_t n = h->n_nodes_out, m = h->n_edges_out;
 	h->have_unitigs = false;
+	h->have_threads = false;
+	h->unitig_min_cov = kmer_abundance;
 	uint32_t launches = 0;
 	tick(h, 12);
 	if (int rc = ensure(h, h->d_g_flag, (std::max(n, m) + 1) * 4)) return rc;
@@ -1520,6 +1525,7 @@ int mbgfe_build_unitigs_ex(mbgfe* h, uint32_t kmer_abundance, double unitig_abun
 	if (int rc = ensure(h, h->d_u_nodes, (n_kept + 1) * 4)) return rc;
 	if (int rc = ensure(h, h->d_u_of_node, (n_kept + 1) * 4)) return rc;
 	if (int rc = ensure(h, h->d_u_fw, (n_kept + 1) * 4)) return rc;
+	if (int rc = ensure(h, h->d_u_pos, (n_kept + 1) * 4)) return rc;
 	if (int rc = ensure(h, h->d_u_edges, (n_fedges + 1) * sizeof(EdgeRec))) return rc;
 	// ---- unitigs of the filtered list
 	if (n_kept)
@@ -1531,7 +1537,7 @@ int mbgfe_build_unitigs_ex(mbgfe* h, uint32_t kmer_abundance, double unitig_abun
 		if (int rc = device_scan(h, h->d_g_flag.as<uint32_t>(), h->d_g_at.as<uint64_t>(), (uint32_t)n_kept)) return rc;
 		if (int rc = device_scan(h, h->d_g_flag2.as<uint32_t>(), h->d_g_at2.as<uint64_t>(), (uint32_t)n_kept)) return rc;
 		MBGFE_LAUNCH(k_unitig_write, grid_for(h, n_kept), 256, 0, h->stream, st, fcov, n_kept, kmer_abundance, h->d_g_flag.as<uint32_t>(), h->d_g_at.as<uint64_t>(),
-			h->d_g_at2.as<uint64_t>(), h->d_u_begin.as<uint64_t>(), h->d_u_nodes.as<uint32_t>(), h->d_u_of_node.as<uint32_t>(), h->d_u_fw.as<uint32_t>());
+			h->d_g_at2.as<uint64_t>(), h->d_u_begin.as<uint64_t>(), h->d_u_nodes.as<uint32_t>(), h->d_u_of_node.as<uint32_t>(), h->d_u_fw.as<uint32_t>(), h->d_u_pos.as<uint32_t>());
 		launches += 8;
 		CU(h, cudaMemcpyAsync(&n_unitigs, h->d_g_at.as<uint64_t>() + n_kept, 8, cudaMemcpyDeviceToHost, h->stream));       // before the scans are reused
 		CU(h, cudaMemcpyAsync(&n_unitig_nodes, h->d_g_at2.as<uint64_t>() + n_kept, 8, cudaMemcpyDeviceToHost, h->stream));
@@ -1580,6 +1586,47 @@ int mbgfe_build_unitigs_ex(mbgfe* h, uint32_t kmer_abundance, double unitig_abun
 	return 0;
 }
 
+// getReadPaths (MBG/MBG.cpp:1235-1251) as a batched lookup: every selected k-mer instance of the last run located in the
+// unitigs of the last mbgfe_build_unitigs[_ex] and classified the way iterateReadPaths (MBG/KmerMatcher.h:12-144) would
+int mbgfe_thread_reads(mbgfe* h)
+{
+	if (!h) return MBGFE_E_PARAM;
+	if (!h->have_unitigs) return fail(h, MBGFE_E_STATE, "mbgfe_thread_reads needs mbgfe_build_unitigs first");
+	if (h->prm.world != 1 || !h->edge_slots) return fail(h, MBGFE_E_STATE, "mbgfe_thread_reads runs on a whole table with edges (world == 1)");
+	const uint64_t n_inst = h->n_inst, n = h->n_nodes_out, n_kept = h->n_kept;
+	uint32_t launches = 0;
+	tick(h, 12);
+	if (int rc = ensure(h, h->d_th_final, (n + 1) * 4)) return rc;
+	if (int rc = ensure(h, h->d_th_node, (n_inst + 1) * 4)) return rc;
+	if (int rc = ensure(h, h->d_th_unitig, (n_inst + 1) * 4)) return rc;
+	if (int rc = ensure(h, h->d_th_upos, (n_inst + 1) * 4)) return rc;
+	if (int rc = ensure(h, h->d_th_urest, (n_inst + 1) * 4)) return rc;
+	if (int rc = ensure(h, h->d_th_step, n_inst + 64)) return rc;
+	if (n_inst)
+	{
+		CU(h, cudaMemsetAsync(h->d_th_final.p, 0xff, (n + 1) * 4, h->stream));
+		if (n_kept) { MBGFE_LAUNCH(k_invert_orig, grid_for(h, n_kept), 256, 0, h->stream, h->d_f_orig.as<uint32_t>(), n_kept, h->d_th_final.as<uint32_t>()); launches++; }
+		MBGFE_LAUNCH(k_thread_locate, grid_for(h, n_inst), 256, 0, h->stream, h->d_inst_slot.as<uint32_t>(), h->d_inst_hash.as<uint64_t>(), n_inst, h->d_nodes.as<NodeSlot>(),
+			h->d_th_final.as<uint32_t>(), h->d_u_of_node.as<uint32_t>(), h->d_u_fw.as<uint32_t>(), h->d_u_pos.as<uint32_t>(), h->d_u_begin.as<uint64_t>(),
+			h->d_th_node.as<uint32_t>(), h->d_th_unitig.as<uint32_t>(), h->d_th_upos.as<uint32_t>(), h->d_th_urest.as<uint32_t>());
+		MBGFE_LAUNCH(k_thread_steps, grid_for(h, n_inst), 256, 0, h->stream, h->d_th_node.as<uint32_t>(), h->d_th_unitig.as<uint32_t>(), h->d_th_upos.as<uint32_t>(),
+			h->d_th_urest.as<uint32_t>(), h->d_inst_flag.as<uint8_t>(), h->d_inst_pos.as<uint32_t>(), h->d_inst_slot.as<uint32_t>(), h->d_inst_hash.as<uint64_t>(), n_inst,
+			h->d_edges.as<EdgeSlot>(), h->edge_slots - 1, h->prm.k, h->unitig_min_cov, h->d_th_step.as<uint8_t>());
+		launches += 2;
+	}
+	tick(h, 13);
+	fetch(h, h->h_th_unitig, h->d_th_unitig, n_inst);
+	fetch(h, h->h_th_upos, h->d_th_upos, n_inst);
+	fetch(h, h->h_th_urest, h->d_th_urest, n_inst);
+	fetch(h, h->h_th_step, h->d_th_step, n_inst);
+	CU(h, cudaStreamSynchronize(h->stream));
+	CU(h, cudaGetLastError());
+	h->stats.ms_unitigs = elapsed(h, 12, 13);
+	h->stats.launches = launches;
+	h->have_threads = true;
+	return 0;
+}
+
 }
 
 namespace {
@@ -1605,6 +1652,7 @@ uint64_t mbgfe_count(mbgfe* h, int what)
 		case MBGFE_UNITIG_BEGIN: return h->have_unitigs ? h->n_unitigs + 1 : 0;
 		case MBGFE_UNITIG_NODES: return h->have_unitigs ? h->n_unitig_nodes : 0;
 		case MBGFE_UNITIG_EDGES: return h->have_unitigs ? h->n_uedges : 0;
+		case MBGFE_INST_UNITIG: case MBGFE_INST_UNITIG_POS: case MBGFE_INST_UNITIG_REST: case MBGFE_INST_STEP: return h->have_threads ? h->h_th_step.size() : 0;
 	}
 	return 0;
 }
@@ -1642,6 +1690,15 @@ const void* mbgfe_data(mbgfe* h, int what)
 				case MBGFE_UNITIG_BEGIN: return h->h_u_begin.data();
 				case MBGFE_UNITIG_EDGES: return h->h_u_edges.data();
 				default: return h->h_u_nodes.data();
+			}
+		case MBGFE_INST_UNITIG: case MBGFE_INST_UNITIG_POS: case MBGFE_INST_UNITIG_REST: case MBGFE_INST_STEP:
+			if (!h->have_threads) { fail(h, MBGFE_E_STATE, "read threading requested before mbgfe_thread_reads"); return nullptr; }
+			switch (what)
+			{
+				case MBGFE_INST_UNITIG: return h->h_th_unitig.data();
+				case MBGFE_INST_UNITIG_POS: return h->h_th_upos.data();
+				case MBGFE_INST_UNITIG_REST: return h->h_th_urest.data();
+				default: return h->h_th_step.data();
 			}
 	}
 	fail(h, MBGFE_E_PARAM, "unknown result array %d", what);

@@ -15,6 +15,7 @@ MODES = {"no": 0, "hpc": 1, "collapse": 2, "dinuc": 3, "msat": 4, "collapse-dinu
 KEEP_CODES, KEEP_POSES, NO_TABLE, NO_EDGES = 1, 2, 4, 8
 PARTS, CODES, POSES, POSITIONS, HASHES, NODE_HASHES, NODE_COVERAGE, NODE_TIP, EDGES = range(9)
 NODE_KEPT, F_NODE_HASHES, F_NODE_COVERAGE, F_NODE_TIP, F_EDGES, UNITIG_BEGIN, UNITIG_NODES, F_NODE_UNITIG, UNITIG_EDGES = range(9, 18)
+INST_UNITIG, INST_UNITIG_POS, INST_UNITIG_REST, INST_STEP = range(18, 22)
 UNITIG_ONECOV_HEURISTIC = 1      # mbgfe_build_unitigs_ex flag (include/mbgfe.h)
 
 PART_DTYPE = np.dtype([
@@ -90,6 +91,7 @@ def load_library(path=None):
     L.mbgfe_exchange_insert_edges.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64]
     L.mbgfe_build_unitigs.argtypes = [C.c_void_p, C.c_uint32, C.c_double]
     L.mbgfe_build_unitigs_ex.argtypes = [C.c_void_p, C.c_uint32, C.c_double, C.c_uint32]
+    L.mbgfe_thread_reads.argtypes = [C.c_void_p]
     L.mbgfe_set_variants.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint64]
     L.mbgfe_kat_tables.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
     L.mbgfe_kat_kmer_hash.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p]
@@ -251,6 +253,53 @@ class MbgFrontEnd:
                     edges=self._data(F_EDGES, "<u4", 6).reshape(-1, 6), unitig_begin=self._data(UNITIG_BEGIN, "<u8"),
                     unitig_nodes=self._data(UNITIG_NODES, "<u4"), node_unitig=self._data(F_NODE_UNITIG, "<u4"),
                     unitig_edges=self._data(UNITIG_EDGES, "<u4", 6).reshape(-1, 6))
+
+    def thread_reads(self):
+        """getReadPaths (MBG/MBG.cpp:1235-1251; KmerMatcher.h:12-144) as a batched lookup -> dict of the per-instance
+        arrays of include/mbgfe.h (unitig, unitig_pos, unitig_rest, step), in positions() order"""
+        self._check(self.lib.mbgfe_thread_reads(self.handle))
+        return dict(unitig=self._data(INST_UNITIG, "<u4"), unitig_pos=self._data(INST_UNITIG_POS, "<u4"), unitig_rest=self._data(INST_UNITIG_REST, "<u4"),
+                    step=self._data(INST_STEP, "u1"))
+
+    def read_paths(self):
+        """the ReadPath list of getReadPaths (MBG/MBG.cpp:1235-1251) put together from thread_reads() the way
+        INTEGRATION.md 2c shows: (heads[n, 6] = read index, part offset, path entries, readPoses entries, leftClip,
+        rightClip; path[] = 2*unitig + fw; poses[] = readPoses).  Host loop over the instances: meant for inspection and
+        tests, the arrays themselves are the product."""
+        th = self.thread_reads()
+        parts, positions = self.parts(), self.positions()
+        unitig, upos, urest, step = th["unitig"], th["unitig_pos"], th["unitig_rest"], th["step"]
+        heads, path, poses = [], [], []
+        for p in parts:
+            if not p["hashed"]:
+                continue
+            cur_path, cur_poses, left, right = [], [], 0, 0
+
+            def emit():
+                heads.append((int(p["read_idx"]), int(p["part_offset"]), len(cur_path), len(cur_poses), left, right))
+                path.extend(cur_path)
+                poses.extend(cur_poses)
+            b = int(p["sel_begin"])
+            for i in range(b, b + int(p["n_sel"])):
+                s = int(step[i])
+                if s == 0:
+                    continue
+                if s == 1:                       # KmerMatcher.h:30-47: path ends, readPoses stays
+                    if cur_path:
+                        emit()
+                    cur_path, left, right = [], 0, 0
+                elif s == 2:
+                    cur_path.append(int(unitig[i])); cur_poses.append(int(positions[i])); left, right = int(upos[i]), int(urest[i])
+                elif s == 3:
+                    emit()
+                    cur_path, cur_poses, left, right = [int(unitig[i])], [int(positions[i])], int(upos[i]), int(urest[i])
+                elif s == 4:
+                    cur_poses.append(int(positions[i])); right = int(urest[i])
+                else:
+                    cur_path.append(int(unitig[i])); cur_poses.append(int(positions[i])); right = int(urest[i])
+            if cur_path:
+                emit()
+        return dict(heads=np.array(heads, dtype=np.uint64).reshape(-1, 6), path=np.array(path, dtype=np.uint32), poses=np.array(poses, dtype=np.uint32), arrays=th)
 
     def stats(self):
         s = Stats()
