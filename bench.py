@@ -254,8 +254,13 @@ def main():
     ap.add_argument("--scale", type=float, default=1.0, help="shrink the genome (and read count) for quick runs")
     ap.add_argument("--e2e-steps", type=int, default=2)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--k", type=int, default=0, help="k-mer size override (BASELINE.json configs[4]: the k/w sweep)")
+    ap.add_argument("--w", type=int, default=0, help="window size override")
     args = ap.parse_args()
-    wl = WORKLOADS[args.workload]
+    wl = dict(WORKLOADS[args.workload])
+    if args.k or args.w:
+        wl["k"], wl["w"] = args.k or wl["k"], args.w or wl["w"]
+        wl["desc"] = wl["desc"].replace("k=1001 w=100", f"k={wl['k']} w={wl['w']}")
     if args.impl == "reference":
         reference_arm(args, wl)
         return
@@ -430,7 +435,7 @@ def main():
         if unitig_info:
             line["unitig_stage"] = unitig_info
         traffic_file = os.path.join(ROOT, "profiles", "ncu_traffic.json")
-        if os.path.exists(traffic_file) and args.scale == 1.0 and args.workload == "chr20":
+        if os.path.exists(traffic_file) and args.scale == 1.0 and args.workload == "chr20" and not (args.k or args.w):
             # dram__bytes_read.sum + dram__bytes_write.sum of one launch, from the committed `ncu --set full` capture of this workload
             line["roofline"]["traffic"] = json.load(open(traffic_file)).get(dominant)
         if world == 1 and not args.no_cpu_baseline:

@@ -931,12 +931,14 @@ int mbgfe_run(mbgfe* h)
 	struct Piece { const char* src; uint64_t pos, len; bool host; uint64_t stage_word; };
 	std::vector<Piece> pieces;
 	std::vector<uint64_t> piece_end;
-	uint32_t host_pct = 65;
-	if (const char* e = getenv("MBGFE_HOST_PACK")) host_pct = (uint32_t)std::min(100, std::max(0, atoi(e)));
 	const unsigned hw = std::thread::hardware_concurrency();
 	// one process per GPU: the ranks of a box share its cores
 	const unsigned share = std::max(1u, h->prm.world);
 	const unsigned n_workers = hw / share > 2 ? std::min(hw / share - 1, 31u) : 0;
+	// share H of the bytes through the host so that both routes finish together: H / (r T) = (1 - 3/4 H) / P with r = 5.5 GB/s
+	// of ASCII packed per worker, T workers, P = 55 GB/s of PCIe (measured on the bench box; 15 workers -> 65 %, 7 -> 46 %, 3 -> 24 %)
+	uint32_t host_pct = (uint32_t)std::min(65.0, 100.0 * 5.5 * n_workers / (55.0 + 0.75 * 5.5 * n_workers));
+	if (const char* e = getenv("MBGFE_HOST_PACK")) host_pct = (uint32_t)std::min(100, std::max(0, atoi(e)));
 	if (n_workers == 0) host_pct = 0;
 	uint64_t stage_words = 0;
 	{
