@@ -195,7 +195,7 @@ def reference_arm(args, wl):
         "e2e": {"value": value, "unit": "bases/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
-    print(json.dumps(line))
+    emit(json.dumps(line))      # stdout proper (fd 1 itself points at stderr during the run, see main)
 
 
 def cpu_baseline(wl, scale):

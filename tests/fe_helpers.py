@@ -22,7 +22,7 @@ def run_frontend(mode, k, w, reads, library=None, flags=KEEP_CODES | KEEP_POSES,
         fe.close()
 
 
-def run_frontend_unitigs(mode, k, w, reads, min_cov, min_unitig_cov, library=None, one_cov=False, paths=False, **kw):
+def run_frontend_unitigs(mode, k, w, reads, min_cov, min_unitig_cov, library=None, one_cov=False, paths=False, variants=None, **kw):
     """table + mbgfe_build_unitigs -> (RunResult of the table, UnitigResult)"""
     from oracle_lib import UnitigResult
     fe = MbgFrontEnd(k, w, mode, library=library, **kw)
@@ -31,6 +31,8 @@ def run_frontend_unitigs(mode, k, w, reads, min_cov, min_unitig_cov, library=Non
             fe.add_reads(*reads)
         else:
             fe.add_read_list(reads)
+        if variants is not None:
+            fe.set_variants(variants.hashes, variants.offsets, variants.len_begin, variants.lengths)
         fe.run()
         table = RunResult(node_hash=fe.node_hashes(), node_cov=fe.node_coverage(), node_tip=fe.node_tip(), edges=fe.edges())
         u = UnitigResult(fe.build_unitigs(min_cov, min_unitig_cov, one_cov_heuristic=one_cov))

@@ -127,6 +127,18 @@ def test_emulated_read_threading(oracle, emu_library, mode, k, w, a, u, one_cov,
     assert len(want.paths.heads) > 0
 
 
+def test_emulated_graph_stage_on_empty_and_tiny_tables(oracle, emu_library):
+    """edge cases of rows a14 / f1 / f2: no k-mer at all, a single read whose k-mers all have coverage 1 (everything is
+    filtered), reads shorter than 32 bases"""
+    from fe_helpers import run_frontend_unitigs
+    for reads in ([workloads.lcg_bases(5, 200)], [workloads.lcg_bases(5, 2000)], [workloads.lcg_bases(5, 40), "ACGT" * 3]):
+        for one_cov in (False, True):
+            table, got = run_frontend_unitigs("collapse-msat", 301, 30, reads, 1, 2, library=emu_library, one_cov=one_cov, paths=True)
+            otable, want = oracle.run_unitigs("collapse-msat", 301, 30, reads, 1, 2, one_cov=one_cov, paths=True)
+            assert len(table.node_cov) == len(otable.node_cov) and np.array_equal(got.kept, want.kept)
+            assert len(got.node_cov) == len(want.node_cov) == 0 and len(got.unitig_begin) == 1 and len(got.paths.heads) == len(want.paths.heads) == 0
+
+
 def test_emulated_hash_in_groups(oracle, emu_library, monkeypatch):
     """k_kmer_hash_lanes with a staging area much smaller than a read: k-mers are hashed in groups of consecutive ones"""
     monkeypatch.setenv("MBGFE_HASH_LANES", "1")

@@ -275,6 +275,24 @@ def test_read_threading_against_oracle(oracle, mode, k, w, a, u, one_cov):
 
 
 @pytest.mark.gpu
+@pytest.mark.parametrize("mode,k,w", [("collapse-msat", 301, 30), ("hpc", 63, 33)])
+def test_pass3_variants_unitigs_and_read_paths(oracle, mode, k, w):
+    """pass 3 of runMBG end to end on the device: hpc variants registered (row a11), table, getUnitigGraph with
+    oneCovHeuristic (a14 / f1) and read threading (f2) -- the calls of MBG/MBG.cpp:1570-1590 -- against the oracle"""
+    from fe_helpers import run_frontend_unitigs
+    from oracle_lib import compare_paths, make_variants
+    reads = workloads.coverage_reads(genome_len=60000, n_reads=100, len_min=9000, len_max=14000, error_ppm=3000)
+    variants = make_variants(oracle.run(mode, k, w, reads), k, 300)
+    table, got = run_frontend_unitigs(mode, k, w, reads, 1, 2, one_cov=True, paths=True, variants=variants)
+    otable, want = oracle.run_unitigs(mode, k, w, reads, 1, 2, variants=variants, one_cov=True, paths=True)
+    assert np.array_equal(table.node_hash, otable.node_hash)
+    check_unitigs(got, want, f"pass 3 unitigs {mode} k={k}")
+    compare_paths(got.paths, got, want.paths, want, f"pass 3 read paths {mode} k={k}")
+    _, plain = oracle.run_unitigs(mode, k, w, reads, 1, 2, one_cov=True)
+    assert not np.array_equal(plain.node_hash, want.node_hash), "the variants did not change any hash"
+
+
+@pytest.mark.gpu
 @pytest.mark.parametrize("mode,k,w,a,u", [("no", 63, 5, 1, 2), ("hpc", 63, 33, 1, 1), ("collapse-msat", 101, 20, 2, 2)])
 def test_unitig_filter_circular_genomes(oracle, mode, k, w, a, u):
     """chains that are cycles (no tip, no branch): the ranking detects them by its round limit, cuts them in front of
