@@ -290,51 +290,65 @@ struct SegTable
 	uint32_t n;
 };
 
-// K1: homopolymer collapse (MBG/ReadHelper.h:864-876 collapse, :899-1018 run-length symbols).  One CTA per segment;
-// each thread owns 32 bases per tile: neighbour compare on both planes -> keep mask -> popcount -> block prefix sum
-// -> bit-compress -> merged into a shared-memory staging tile -> coalesced 64-bit stores.
+// K1: homopolymer collapse (MBG/ReadHelper.h:864-876 collapse, :899-1018 run-length symbols).  One WARP per segment,
+// each lane owns 32 bases of a 1024-base tile: neighbour compare on both planes -> keep mask -> popcount -> warp prefix
+// sum -> bit-compress -> merged into a shared-memory staging tile -> coalesced 64-bit stores.  No CTA barrier anywhere:
+// the base before a lane's 32 comes from the lane below (shuffle; lane 0: the last base of the previous tile, kept in a
+// register), the partial output word between tiles lives in a register, the next tile's bases are requested one tile
+// ahead.  (The earlier CTA-per-segment form with a block scan and three barriers per tile took 0.73 ms on the bench, this
+// one 0.63 ms; ncu: ALU pipe, the 5-round compress is ~110 of the ~290 instructions per 32 bases.)
 // keep_all != 0 (--error-masking=no): every base is a symbol (the kernel only re-aligns the segment).
 // pos1 != nullptr: also writes the segment-relative raw position of every kept base (the run starts, i.e. poses).
 // Algorithmic bytes: 1/4 read per base + 1/4 written per symbol (+ 4 per symbol when pos1 is requested).
-template <int NT>
-__global__ void __launch_bounds__(NT) k_collapse(SegTable seg, const uint64_t* __restrict__ packed, uint64_t* __restrict__ sym,
+#ifdef MBGFE_EMU_BUILD
+constexpr int COLLAPSE_WARPS = 1;      // the emulator's warp primitives are CTA-wide barriers
+#else
+constexpr int COLLAPSE_WARPS = 4;
+#endif
+
+__global__ void __launch_bounds__(COLLAPSE_WARPS * 32) k_collapse(SegTable seg, const uint64_t* __restrict__ packed, uint64_t* __restrict__ sym,
 	uint32_t* __restrict__ seg_c1, uint32_t* __restrict__ pos1, int keep_all)
 {
-	__shared__ uint32_t stage_lo[NT + 2], stage_hi[NT + 2];
-	__shared__ uint32_t warp_tmp[NT / 32];
-	const uint32_t g = blockIdx.x;
+	__shared__ uint32_t s_lo[COLLAPSE_WARPS][34], s_hi[COLLAPSE_WARPS][34];
+	const uint32_t lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+	const uint32_t g = blockIdx.x * COLLAPSE_WARPS + wid;
 	if (g >= seg.n) return;
 	const uint64_t in0 = seg.in_start[g];
 	const uint32_t len = seg.len[g];
 	const uint64_t out0 = seg.out_base[g];
 	uint64_t* __restrict__ out = sym + (out0 >> 5);
-	uint32_t carry = 0; // symbols written so far
-	if (threadIdx.x == 0) { stage_lo[0] = 0; stage_hi[0] = 0; }
-	for (uint32_t tile = 0; tile < len; tile += NT * 32)
+	uint32_t* st_lo = s_lo[wid];
+	uint32_t* st_hi = s_hi[wid];
+	uint32_t carry = 0;                     // symbols written so far
+	uint32_t part_lo = 0, part_hi = 0;      // the unfinished output word
+	uint32_t prev_lo = 0, prev_hi = 0;      // last base of the previous tile
+	Planes next;                            // the lane's 32 bases of the next tile, requested one tile ahead
+	next.lo = 0; next.hi = 0;
+	if (lane * 32 < len) next = window32(packed, in0 + lane * 32);
+	for (uint32_t tile = 0; tile < len; tile += 1024)
 	{
-		const uint32_t base0 = tile + threadIdx.x * 32;
-		uint32_t lo = 0, hi = 0, keep = 0;
-		if (base0 < len)
-		{
-			const uint32_t nvalid = min(32u, len - base0);
-			const uint64_t at = in0 + base0;
-			const Planes x = window32(packed, at);
-			lo = x.lo; hi = x.hi;
-			if (keep_all) keep = 0xffffffffu;
-			else if (base0 == 0) keep = (((lo ^ (lo << 1)) | (hi ^ (hi << 1)))) | 1u;
-			else
-			{
-				const uint32_t pv = symbol_at(packed, at - 1);
-				keep = (lo ^ ((lo << 1) | (pv & 1))) | (hi ^ ((hi << 1) | (pv >> 1)));
-			}
-			keep &= low_bits(nvalid);
-		}
+		const uint32_t base0 = tile + lane * 32;
+		uint32_t lo = next.lo, hi = next.hi;
+		const uint32_t nvalid = base0 < len ? min(32u, len - base0) : 0u;
+		next.lo = 0; next.hi = 0;
+		if (base0 + 1024 < len) next = window32(packed, in0 + base0 + 1024);
+		uint32_t below_lo = __shfl_up_sync(FULL, lo >> 31, 1), below_hi = __shfl_up_sync(FULL, hi >> 31, 1);
+		if (lane == 0) { below_lo = prev_lo; below_hi = prev_hi; }
+		uint32_t keep = (lo ^ ((lo << 1) | below_lo)) | (hi ^ ((hi << 1) | below_hi));
+		if (base0 == 0) keep |= 1u;
+		if (keep_all) keep = 0xffffffffu;
+		keep &= low_bits(nvalid);
+		prev_lo = __shfl_sync(FULL, lo >> 31, 31); prev_hi = __shfl_sync(FULL, hi >> 31, 31);
 		const uint32_t cnt = __popc(keep);
-		uint32_t tile_total;
-		const uint32_t excl = block_exclusive_sum<NT>(cnt, warp_tmp, tile_total);
-		// the staging tile holds symbols [carry & ~31, ...): word 0 keeps the partial word of the previous tile
-		for (uint32_t i = 1 + threadIdx.x; i < NT + 2; i += NT) { stage_lo[i] = 0; stage_hi[i] = 0; }
-		__syncthreads();
+		uint32_t inc = cnt;
+#pragma unroll
+		for (int d = 1; d < 32; d <<= 1) { const uint32_t t = __shfl_up_sync(FULL, inc, d); if (lane >= (uint32_t)d) inc += t; }
+		const uint32_t tile_total = __shfl_sync(FULL, inc, 31);
+		const uint32_t excl = inc - cnt;
+		// the staging tile holds symbols [carry & ~31, ...): word 0 is the partial word of the previous tile
+		st_lo[1 + lane] = 0; st_hi[1 + lane] = 0;
+		if (lane == 0) { st_lo[0] = part_lo; st_hi[0] = part_hi; st_lo[33] = 0; st_hi[33] = 0; }
+		__syncwarp();
 		if (cnt)
 		{
 			if (pos1)
@@ -346,22 +360,23 @@ __global__ void __launch_bounds__(NT) k_collapse(SegTable seg, const uint64_t* _
 			compress_planes(lo, hi, keep);
 			const uint32_t o = (carry & 31) + excl;
 			const uint32_t sh = o & 31;
-			atomicOr(&stage_lo[o >> 5], lo << sh);
-			atomicOr(&stage_hi[o >> 5], hi << sh);
-			if (sh && cnt + sh > 32) { atomicOr(&stage_lo[(o >> 5) + 1], lo >> (32 - sh)); atomicOr(&stage_hi[(o >> 5) + 1], hi >> (32 - sh)); }
+			atomicOr(&st_lo[o >> 5], lo << sh);
+			atomicOr(&st_hi[o >> 5], hi << sh);
+			if (sh && cnt + sh > 32) { atomicOr(&st_lo[(o >> 5) + 1], lo >> (32 - sh)); atomicOr(&st_hi[(o >> 5) + 1], hi >> (32 - sh)); }
 		}
-		__syncthreads();
+		__syncwarp();
 		const uint32_t filled = (carry & 31) + tile_total;       // symbols now in the staging tile
-		const bool last = tile + NT * 32 >= len;
+		const bool last = tile + 1024 >= len;
 		const uint32_t n_words = last ? (filled + 31) / 32 : filled / 32;
 		const uint32_t w0 = carry >> 5;
-		for (uint32_t i = threadIdx.x; i < n_words; i += NT) out[w0 + i] = word_of(stage_lo[i], stage_hi[i]);
-		const uint32_t part_lo = (filled & 31) ? stage_lo[filled >> 5] : 0u, part_hi = (filled & 31) ? stage_hi[filled >> 5] : 0u;
-		__syncthreads();
-		if (threadIdx.x == 0) { stage_lo[0] = part_lo; stage_hi[0] = part_hi; }
+		if (lane < n_words) out[w0 + lane] = word_of(st_lo[lane], st_hi[lane]);             // at most 33 words
+		if (lane == 0 && n_words == 33) out[w0 + 32] = word_of(st_lo[32], st_hi[32]);
+		part_lo = (filled & 31) ? st_lo[filled >> 5] : 0u;
+		part_hi = (filled & 31) ? st_hi[filled >> 5] : 0u;
 		carry += tile_total;
+		__syncwarp();      // the stage is rewritten at the top of the next tile
 	}
-	if (threadIdx.x == 0)
+	if (lane == 0)
 	{
 		seg_c1[g] = carry;
 		if (pos1) pos1[out0 + carry] = len;

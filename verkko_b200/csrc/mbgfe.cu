@@ -190,7 +190,7 @@ bool is_acgt(char c) { c &= (char)0xdf; return c == 'A' || c == 'C' || c == 'G' 
 enum { CTR_NONACGT = 0, CTR_PALINDROME = 1, CTR_DISTINCT = 2, CTR_EDGES = 3, CTR_CURSOR = 4 /* and 5 */, CTR_OVERFLOW = 6, CTR_OWNER = 8 /* .. 8+world */ };
 constexpr uint64_t PAL_CAP = 1 << 20;
 
-constexpr int NT_COLLAPSE = 128, NT_MSAT = 128, NT_SELECT = 128, NT_LIST = 128;   // k_select: 128 beats 64 / 256 / 512 on the bench (7.1 / 7.6 / 8.1 / 10.8 ms)
+constexpr int NT_MSAT = 128, NT_SELECT = 128, NT_LIST = 128;   // k_select: 128 beats 64 / 256 / 512 on the bench (7.1 / 7.6 / 8.1 / 10.8 ms)
 
 SegTable seg_table(const mbgfe* h)
 {
@@ -667,7 +667,7 @@ uint32_t launch_front(mbgfe* h, uint32_t g0, uint32_t cnt, bool timed, cudaStrea
 	uint32_t* pos2 = want_poses ? h->d_pos2.as<uint32_t>() : nullptr;
 	uint32_t* c1 = h->d_seg_c1.as<uint32_t>() + g0;
 	uint32_t* c2 = h->d_seg_c2.as<uint32_t>() + g0;
-	MBGFE_LAUNCH(k_collapse<NT_COLLAPSE>, cnt, NT_COLLAPSE, 0, on, st, h->d_packed.as<uint64_t>(), h->d_sym.as<uint64_t>(), c1, pos1,
+	MBGFE_LAUNCH(k_collapse, (cnt + COLLAPSE_WARPS - 1) / COLLAPSE_WARPS, COLLAPSE_WARPS * 32, 0, on, st, h->d_packed.as<uint64_t>(), h->d_sym.as<uint64_t>(), c1, pos1,
 		h->prm.error_masking == MBGFE_MASK_NO ? 1 : 0);
 	if (timed) tick(h, 4);
 	if (h->msat)
