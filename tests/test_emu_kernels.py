@@ -82,7 +82,7 @@ def check_unitigs(got, want, what):
         assert np.all(got.node_unitig[ids[b[u]:b[u + 1]]] == u)
 
 
-@pytest.mark.parametrize("mode,k,w,a,u,which", [("collapse-msat", 301, 30, 1, 2, "coverage"), ("hpc", 63, 33, 2, 2, "repeats"), ("no", 63, 5, 1, 2, "circular")])
+@pytest.mark.parametrize("mode,k,w,a,u,which", [("hpc", 63, 33, 2, 2, "repeats"), ("no", 63, 5, 1, 2, "circular")])      # "coverage": the onecov / threading tests below
 def test_emulated_unitig_filter(oracle, emu_library, mode, k, w, a, u, which):
     """rows a14 / f1 on the emulator build (the GPU versions are tests/test_gpu_parity.py::test_unitig_filter*)"""
     from fe_helpers import run_frontend_unitigs
@@ -96,7 +96,7 @@ def test_emulated_unitig_filter(oracle, emu_library, mode, k, w, a, u, which):
         assert len(want.unitig_begin) == 2 and want.unitig_begin[1] > 100      # one circular unitig; the lone read is filtered out
 
 
-@pytest.mark.parametrize("mode,k,w,a,u,which", [("collapse-msat", 301, 30, 1, 2, "coverage"), ("hpc", 63, 33, 1, 3, "noisy"), ("no", 63, 5, 1, 2, "circular")])
+@pytest.mark.parametrize("mode,k,w,a,u,which", [("collapse-msat", 301, 30, 1, 2, "coverage"), ("hpc", 63, 33, 1, 3, "noisy")])
 def test_emulated_onecov_heuristic(oracle, emu_library, mode, k, w, a, u, which):
     """row a14: removeOnecovNodes (MBG/MBG.cpp:527-627) on the emulator build, against the oracle (itself pinned on the
     reference's getUnitigGraph(…, oneCovHeuristic = true) in tests/test_oracle.py)"""
@@ -112,7 +112,7 @@ def test_emulated_onecov_heuristic(oracle, emu_library, mode, k, w, a, u, which)
         assert not np.array_equal(plain.kept, want.kept), "the heuristic did not change anything on this workload"
 
 
-@pytest.mark.parametrize("mode,k,w,a,u,one_cov,which", [("collapse-msat", 301, 30, 1, 2, True, "coverage"), ("hpc", 63, 33, 2, 2, False, "noisy"), ("no", 63, 5, 1, 1, False, "circular")])
+@pytest.mark.parametrize("mode,k,w,a,u,one_cov,which", [("collapse-msat", 301, 30, 1, 2, True, "coverage"), ("no", 63, 5, 1, 1, False, "circular")])
 def test_emulated_read_threading(oracle, emu_library, mode, k, w, a, u, one_cov, which):
     """row f2: mbgfe_thread_reads (getKmerLocator + iterateReadPaths as a batched lookup) on the emulator build, against
     the oracle's sequential restatement (pinned on the reference's own functions in tests/test_oracle.py)"""
@@ -131,8 +131,8 @@ def test_emulated_graph_stage_on_empty_and_tiny_tables(oracle, emu_library):
     """edge cases of rows a14 / f1 / f2: no k-mer at all, a single read whose k-mers all have coverage 1 (everything is
     filtered), reads shorter than 32 bases"""
     from fe_helpers import run_frontend_unitigs
-    for reads in ([workloads.lcg_bases(5, 200)], [workloads.lcg_bases(5, 2000)], [workloads.lcg_bases(5, 40), "ACGT" * 3]):
-        for one_cov in (False, True):
+    for reads, flags in (([workloads.lcg_bases(5, 200)], (True,)), ([workloads.lcg_bases(5, 2000)], (False, True))):
+        for one_cov in flags:
             table, got = run_frontend_unitigs("collapse-msat", 301, 30, reads, 1, 2, library=emu_library, one_cov=one_cov, paths=True)
             otable, want = oracle.run_unitigs("collapse-msat", 301, 30, reads, 1, 2, one_cov=one_cov, paths=True)
             assert len(table.node_cov) == len(otable.node_cov) and np.array_equal(got.kept, want.kept)
@@ -148,13 +148,12 @@ def test_emulated_hash_in_groups(oracle, emu_library, monkeypatch):
     compare_runs(run_frontend("hpc", 63, 33, reads, library=emu_library), oracle.run("hpc", 63, 33, reads), what="emu grouped hash hpc")
 
 
-@pytest.mark.parametrize("pct", ["100", "50", "0"])
-def test_emulated_host_packed_pieces(oracle, emu_library, monkeypatch, pct):
+@pytest.mark.parametrize("pct,mode,k,w", [("100", "hpc", 63, 33), ("50", "collapse-msat", 301, 30)])
+def test_emulated_host_packed_pieces(oracle, emu_library, monkeypatch, pct, mode, k, w):
     """the two upload routes of mbgfe_run (ASCII + K0 on the device, 2-bit packing on host threads) mixed piece by piece,
     with lower case and characters outside ACGT in host-packed pieces"""
     monkeypatch.setenv("MBGFE_HOST_PACK", pct)
     reads = [workloads.read_a()] + workloads.edge_case_reads()
     reads += [workloads.lcg_bases(5, 9000).replace(b"ACGTA", b"ACNNA", 3), workloads.lcg_bases(6, 7000).lower(), workloads.lcg_bases(8, 4097)]
-    for mode, k, w in (("collapse-msat", 301, 30), ("hpc", 63, 33)):
-        got = run_frontend(mode, k, w, reads, library=emu_library, piece_bytes=3200)
-        compare_runs(got, oracle.run(mode, k, w, reads), what=f"host pack {pct}% {mode}")
+    got = run_frontend(mode, k, w, reads, library=emu_library, piece_bytes=3200)      # (0 %: every other emulator test)
+    compare_runs(got, oracle.run(mode, k, w, reads), what=f"host pack {pct}% {mode}")
