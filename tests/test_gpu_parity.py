@@ -275,6 +275,49 @@ def test_read_threading_against_oracle(oracle, mode, k, w, a, u, one_cov):
 
 
 @pytest.mark.gpu
+def test_read_threading_properties_at_scale():
+    """size-independent properties of mbgfe_thread_reads on a larger graph (2 Mbp, 3000 reads): every located instance
+    names the unitig slot that holds exactly its k-mer; position + rest + 1 is the unitig's size; a step-4 instance
+    follows its predecessor inside the same oriented unitig; every path start is a located k-mer"""
+    from verkko_b200.frontend import MbgFrontEnd
+    reads = workloads.coverage_reads(genome_len=2000000, n_reads=3000, len_min=15000, len_max=20000, error_ppm=1000)
+    fe = MbgFrontEnd(1001, 100, "collapse-msat")
+    try:
+        fe.add_reads(*reads) if isinstance(reads, tuple) else fe.add_read_list(reads)
+        fe.run()
+        hashes = fe.hashes().copy()
+        u = fe.build_unitigs(1, 2, one_cov_heuristic=True)
+        th = fe.thread_reads()
+    finally:
+        fe.close()
+    unitig, upos, urest, step = (th[x].astype(np.int64) for x in ("unitig", "unitig_pos", "unitig_rest", "step"))
+    located = unitig != 0xffffffff
+    assert located.sum() > 100000 and np.all(step[located] >= 2) and np.all(step[~located] <= 1)
+    b = u["unitig_begin"].astype(np.int64)
+    size = np.diff(b)
+    ut, o = unitig[located] >> 1, unitig[located] & 1
+    assert np.all(upos[located] + urest[located] + 1 == size[ut])
+    slot = b[ut] + np.where(o == 1, upos[located], size[ut] - 1 - upos[located])
+    node = u["unitig_nodes"].astype(np.int64)[slot]
+    # the k-mer: canonical hash = the smaller of (hi, lo) and its halves swapped (MBG/HashList.cpp:85-101)
+    lo, hi = hashes[located, 0], hashes[located, 1]
+    fw = (hi < lo) | ((hi == lo) & (lo < hi))
+    canon = np.where(fw[:, None], np.stack([lo, hi], 1), np.stack([hi, lo], 1))
+    assert np.array_equal(u["node_hash"][node >> 1], canon), "a located instance points at a unitig slot that holds another k-mer"
+    assert np.array_equal((node & 1) == o, fw), "orientation of a located instance inside its unitig"
+    cont = np.flatnonzero(step == 4)
+    prev = cont - 1
+    while True:                       # the previous instance that is in the filtered list (step != 0); never leaves the part
+        skip = step[prev] == 0
+        if not skip.any():
+            break
+        prev[skip] -= 1
+    assert np.array_equal(unitig[cont], unitig[prev]) and np.array_equal(upos[cont], upos[prev] + 1)
+    cross = np.flatnonzero(step == 5)
+    assert len(cross) > 0 and np.all(upos[cross] == 0)
+
+
+@pytest.mark.gpu
 @pytest.mark.parametrize("mode,k,w", [("collapse-msat", 301, 30), ("hpc", 63, 33)])
 def test_pass3_variants_unitigs_and_read_paths(oracle, mode, k, w):
     """pass 3 of runMBG end to end on the device: hpc variants registered (row a11), table, getUnitigGraph with
