@@ -430,6 +430,11 @@ def main():
             "gpu_launches": int(launches),
             "roofline": {"bound": "hbm", "kernel": dominant, "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": None,
                          "peak_source": peak_src,
+                         # what ncu says limits each kernel (profiles/r01_ncu_full_*.txt); none of them is DRAM-bound
+                         "limiter": {"k_select": "ALU pipe (64-bit rotate/xor/compare), sm__pipe_alu_cycles_active 69 %",
+                                     "k_kmer_hash": "integer-multiply half of the FMA pipe (Murmur64A), sm__pipe_fmaheavy_cycles_active 79 %",
+                                     "k_msat": "instruction issue 73 % with 17.8 of 32 lanes active", "k_collapse": "ALU pipe (bit-compress), issue 77 %",
+                                     "k_insert_nodes": "DRAM sectors + atomics (random 32-byte slots)", "k_insert_edges": "DRAM sectors + atomics (random 32-byte slots)"},
                          "all_kernels_GBps": {n: (b / (m * 1e-3) / 1e9 if m > 0 else None) for n, (b, m) in alg.items()}},
         }
         if unitig_info:
