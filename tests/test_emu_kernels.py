@@ -139,6 +139,35 @@ def test_emulated_graph_stage_on_empty_and_tiny_tables(oracle, emu_library):
             assert len(got.node_cov) == len(want.node_cov) == 0 and len(got.unitig_begin) == 1 and len(got.paths.heads) == len(want.paths.heads) == 0
 
 
+def test_emulated_unitig_numbering_is_unitiggraph_sort(reference, emu_library):
+    """the numbering and orientation mbgfe_build_unitigs returns is what UnitigGraph::sort (MBG/UnitigGraph.cpp:278-340)
+    leaves after sortByHash: node ids in hash order, every unitig read from its end with the smaller node id (a single
+    k-mer forwards), unitigs ordered by that first node -- checked against the reference's own unitigs with that rule
+    applied (linear unitigs; circular ones are cut elsewhere)"""
+    from fe_helpers import run_frontend_unitigs
+    reads = workloads.coverage_reads(seed=3, genome_len=8000, n_reads=10, error_ppm=10000)
+    _, got = run_frontend_unitigs("hpc", 63, 33, reads, 1, 2, library=emu_library, one_cov=True)
+    want = reference.run_unitigs("hpc", 63, 33, reads, 1, 2, one_cov=True)
+    order = np.lexsort((want.node_hash[:, 0], want.node_hash[:, 1]))
+    new_id = np.empty(len(order), np.int64)
+    new_id[order] = np.arange(len(order))
+    b = want.unitig_begin.astype(np.int64)
+    seqs = []
+    for i in range(len(b) - 1):
+        x = want.unitig_nodes[b[i]:b[i + 1]].astype(np.int64)
+        x = 2 * new_id[x >> 1] + (x & 1)
+        if len(x) == 1:
+            x = x | 1
+        elif (x[-1] >> 1) < (x[0] >> 1):
+            x = x[::-1] ^ 1
+        seqs.append(x)
+    seqs.sort(key=lambda x: min(x[0] >> 1, x[-1] >> 1))
+    gb = got.unitig_begin.astype(np.int64)
+    assert len(gb) - 1 == len(seqs) > 5 and any(len(x) == 1 for x in seqs)
+    for i, x in enumerate(seqs):
+        assert np.array_equal(got.unitig_nodes[gb[i]:gb[i + 1]].astype(np.int64), x), f"unitig {i}"
+
+
 def test_emulated_hash_in_groups(oracle, emu_library, monkeypatch):
     """k_kmer_hash_lanes with a staging area much smaller than a read: k-mers are hashed in groups of consecutive ones"""
     monkeypatch.setenv("MBGFE_HASH_LANES", "1")
