@@ -48,6 +48,9 @@ orc_unitigs* orc_build_unitigs(const orc* o, uint32_t min_cov, double min_unitig
 /* one_cov_heuristic: run removeOnecovNodes (tips, then all) first, as getUnitigGraph does under Verkko's flags (MBG/MBG.cpp:631-635, 1573) */
 orc_unitigs* orc_build_unitigs_ex(const orc* o, uint32_t min_cov, double min_unitig_cov, int one_cov_heuristic);
 void orc_unitigs_free(orc_unitigs* u);
+/* filterKmersToUnitigKmers (MBG/MBG.cpp:1065-1185) with filterWithinUnitig = true (MBG's default), in place: thins the k-mers
+ * inside every unitig, filters the list again, adds the sequence overlaps of the new neighbours (array 8 / count 6) */
+void orc_thin_unitigs(orc_unitigs* u, uint32_t k);
 /* what: 0 nodes of the input table, 1 kept nodes, 2 filtered edges, 3 unitigs, 4 unitig nodes, 5 unitig edges */
 uint64_t orc_unitigs_count(const orc_unitigs* u, int what);
 /* what: 0 kept(u8 per input node) 1 filtered hashes(u64 lo,hi) 2 filtered coverage(u32) 3 filtered tip(u8)

@@ -85,6 +85,9 @@ static void check_unitig(const adjacency* a, uint32_t start, uint8_t* checked, c
 struct orc_unitigs {
 	uint64_t n_nodes, n_kept, n_fedges, n_unitigs, n_unitig_nodes;
 	uint8_t* kept;          /* per node of the input table */
+	uint32_t* orig;         /* input-table index of every kept node */
+	uint64_t n_overlaps;    /* HashList::sequenceOverlap of the filtered list: u32 x5 from, from_fw, to, to_fw, overlap (canonical) */
+	uint32_t* overlaps;
 	uint64_t* f_hash;       /* lo, hi per kept node */
 	uint32_t* f_cov;
 	uint8_t* f_tip;
@@ -98,7 +101,7 @@ struct orc_unitigs {
 void orc_unitigs_free(orc_unitigs* u)
 {
 	if (!u) return;
-	free(u->kept); free(u->f_hash); free(u->f_cov); free(u->f_tip); free(u->f_edges); free(u->unitig_begin); free(u->unitig_nodes); free(u->uedges);
+	free(u->kept); free(u->f_hash); free(u->f_cov); free(u->f_tip); free(u->f_edges); free(u->unitig_begin); free(u->unitig_nodes); free(u->uedges); free(u->orig); free(u->overlaps);
 	free(u);
 }
 
@@ -261,7 +264,7 @@ orc_unitigs* orc_build_unitigs_ex(const orc* o, uint32_t min_cov, double min_uni
 	for (uint64_t i = 0; i < l.n; i++) u->kept[l.orig[i]] = 1;
 	u->n_kept = l.n; u->n_fedges = l.m;
 	u->f_hash = l.hash; u->f_cov = l.cov; u->f_tip = l.tip; u->f_edges = l.edges;
-	free(l.orig);
+	u->orig = l.orig;
 	/* ---- second block, MBG/MBG.cpp:689-745, on the filtered list */
 	const uint64_t nk = u->n_kept;
 	a = covered_edges(nk, u->f_edges, u->n_fedges, min_cov);
@@ -335,6 +338,9 @@ orc_unitigs* orc_build_unitigs_ex(const orc* o, uint32_t min_cov, double min_uni
 		free(order); free(keys); free(covs); free(tip_of);
 	}
 	adjacency_free(&a);
+	u->n_overlaps = u->n_fedges;
+	u->overlaps = (uint32_t*)malloc((u->n_fedges + 1) * 20);
+	for (uint64_t e = 0; e < u->n_fedges; e++) { memcpy(u->overlaps + 5 * e, u->f_edges + 6 * e, 16); u->overlaps[5 * e + 4] = u->f_edges[6 * e + 5]; }
 	free(belongs); free(checked); free(scratch);
 	return u;
 }
@@ -344,15 +350,127 @@ orc_unitigs* orc_build_unitigs(const orc* o, uint32_t min_cov, double min_unitig
 /* what: 0 nodes of the input table, 1 kept nodes, 2 filtered edges, 3 unitigs, 4 unitig nodes */
 uint64_t orc_unitigs_count(const orc_unitigs* u, int what)
 {
-	switch (what) { case 0: return u->n_nodes; case 1: return u->n_kept; case 2: return u->n_fedges; case 3: return u->n_unitigs; case 4: return u->n_unitig_nodes; case 5: return u->n_uedges; }
+	switch (what) { case 0: return u->n_nodes; case 1: return u->n_kept; case 2: return u->n_fedges; case 3: return u->n_unitigs; case 4: return u->n_unitig_nodes; case 5: return u->n_uedges; case 6: return u->n_overlaps; }
 	return 0;
 }
 /* what: 0 kept(u8 per input node) 1 filtered hashes(u64 lo,hi) 2 filtered coverage(u32) 3 filtered tip(u8)
  *       4 filtered edges(u32 x6) 5 unitig_begin(u64, n+1) 6 unitig nodes(u32 = 2*filtered id + fw) */
 const void* orc_unitigs_data(const orc_unitigs* u, int what)
 {
-	switch (what) { case 0: return u->kept; case 1: return u->f_hash; case 2: return u->f_cov; case 3: return u->f_tip; case 4: return u->f_edges; case 5: return u->unitig_begin; case 6: return u->unitig_nodes; case 7: return u->uedges; }
+	switch (what) { case 0: return u->kept; case 1: return u->f_hash; case 2: return u->f_cov; case 3: return u->f_tip; case 4: return u->f_edges; case 5: return u->unitig_begin; case 6: return u->unitig_nodes; case 7: return u->uedges; case 8: return u->overlaps; }
 	return 0;
+}
+
+/* ---- filterKmersToUnitigKmers (MBG/MBG.cpp:1065-1185) with filterWithinUnitig = true, MBG's default: inside a unitig only
+ * its ends, tip k-mers and the k-mers needed to keep consecutive kept k-mers overlapping stay; the list is filtered again
+ * (HashList::filter) and consecutive kept k-mers get a sequence overlap of their own.  Unitig edges are untouched (ends stay).
+ * canon_key / edge_index / edge_find are defined with the read threading below. */
+static uint64_t canon_key(uint32_t from, uint32_t ffw, uint32_t to, uint32_t tfw);
+static uint64_t* overlap_index(const uint32_t* ov, uint64_t m);
+static int edge_find(const uint64_t* ix, uint64_t m, uint64_t key, uint64_t* value);
+
+void orc_thin_unitigs(orc_unitigs* u, uint32_t k)
+{
+	const uint64_t n = u->n_kept;
+	uint64_t* ix = overlap_index(u->overlaps, u->n_overlaps);
+	uint8_t* kept = (uint8_t*)calloc(n + 1, 1);
+	uint32_t* new_nodes = (uint32_t*)malloc((u->n_unitig_nodes + 1) * 4);
+	uint64_t* new_begin = (uint64_t*)calloc(u->n_unitigs + 2, 8);
+	uint32_t* add = (uint32_t*)malloc((u->n_unitig_nodes + 1) * 20);     /* new overlaps: from, from_fw, to, to_fw, overlap (old ids) */
+	uint64_t n_add = 0, n_new = 0;
+	uint32_t* seq = (uint32_t*)malloc((u->n_unitig_nodes + 1) * 4);
+	for (uint64_t t = 0; t < u->n_unitigs; t++)
+	{
+		const uint64_t b = u->unitig_begin[t], len = u->unitig_begin[t + 1] - b;
+		/* walked from the end whose k-mer has the smaller hash (MBG.cpp:1069-1095); ids here are in hash order */
+		const int rev = (u->unitig_nodes[b + len - 1] >> 1) < (u->unitig_nodes[b] >> 1);
+		for (uint64_t j = 0; j < len; j++) seq[j] = rev ? (u->unitig_nodes[b + len - 1 - j] ^ 1) : u->unitig_nodes[b + j];
+		uint64_t last_start = 0, pos = 0, last_kmer = ~0ull;
+		const uint64_t out0 = n_new;
+		for (uint64_t j = 0; j < len; j++)
+		{
+			uint64_t ov = 0;
+			if (j > 0) { edge_find(ix, u->n_overlaps, canon_key(seq[j - 1] >> 1, seq[j - 1] & 1, seq[j] >> 1, seq[j] & 1), &ov); pos += k - ov; }
+			int skip = 1;
+			if (u->f_tip[seq[j] >> 1]) skip = 0;
+			else if (j == 0 || j == len - 1) skip = 0;
+			else
+			{
+				uint64_t ov2 = 0;
+				edge_find(ix, u->n_overlaps, canon_key(seq[j] >> 1, seq[j] & 1, seq[j + 1] >> 1, seq[j + 1] & 1), &ov2);
+				if (pos + (k - ov2) >= last_start + k) skip = 0;
+			}
+			if (skip) continue;
+			kept[seq[j] >> 1] = 1;
+			if (last_kmer != ~0ull)
+			{
+				uint32_t* w = add + 5 * n_add++;
+				w[0] = (uint32_t)(last_kmer >> 1); w[1] = (uint32_t)(last_kmer & 1); w[2] = seq[j] >> 1; w[3] = seq[j] & 1; w[4] = (uint32_t)(k - (pos - last_start));
+			}
+			new_nodes[n_new++] = seq[j];
+			last_start = pos; last_kmer = seq[j];
+		}
+		if (rev) for (uint64_t i = out0, j = n_new - 1; i < j; i++, j--) { uint32_t x = new_nodes[i] ^ 1; new_nodes[i] = new_nodes[j] ^ 1; new_nodes[j] = x; }
+		if (rev && ((n_new - out0) & 1)) new_nodes[out0 + (n_new - out0) / 2] ^= 1;
+		new_begin[t + 1] = n_new;
+	}
+	free(ix); free(seq);
+	/* ranks, HashList::filter, renumbering */
+	uint32_t* rank = (uint32_t*)malloc((n + 1) * 4);
+	uint64_t nk = 0;
+	for (uint64_t i = 0; i < n; i++) { rank[i] = (uint32_t)nk; if (kept[i]) nk++; }
+	for (uint64_t i = 0; i < n; i++) if (kept[i])
+	{
+		const uint32_t j = rank[i];
+		u->f_hash[2 * j] = u->f_hash[2 * i]; u->f_hash[2 * j + 1] = u->f_hash[2 * i + 1]; u->f_cov[j] = u->f_cov[i]; u->f_tip[j] = u->f_tip[i]; u->orig[j] = u->orig[i];
+	}
+	memset(u->kept, 0, u->n_nodes);
+	for (uint64_t j = 0; j < nk; j++) u->kept[u->orig[j]] = 1;
+	uint64_t mk = 0;
+	for (uint64_t e = 0; e < u->n_fedges; e++)
+	{
+		uint32_t* r = u->f_edges + 6 * e;
+		if (!kept[r[0]] || !kept[r[2]]) continue;
+		uint32_t* w = u->f_edges + 6 * mk++;
+		memmove(w, r, 24); w[0] = rank[w[0]]; w[2] = rank[w[2]];
+	}
+	u->n_fedges = mk;
+	/* sequence overlaps: the surviving old ones, then the new ones (set semantics on the canonical pair: a new value replaces) */
+	uint64_t mo = 0;
+	uint32_t* ov_all = (uint32_t*)malloc((u->n_overlaps + n_add + 1) * 20);
+	for (uint64_t e = 0; e < u->n_overlaps; e++)
+	{
+		const uint32_t* r = u->overlaps + 5 * e;
+		if (!kept[r[0]] || !kept[r[2]]) continue;
+		uint32_t* w = ov_all + 5 * mo++;
+		memcpy(w, r, 20); w[0] = rank[w[0]]; w[2] = rank[w[2]];
+	}
+	{
+		const uint64_t mo_old = mo;
+		uint64_t* old_ix = overlap_index(ov_all, mo_old);      /* sorted (key, value); find to replace */
+		for (uint64_t e = 0; e < n_add; e++)
+		{
+			const uint32_t* r = add + 5 * e;
+			uint32_t from = rank[r[0]], ffw = r[1], to = rank[r[2]], tfw = r[3];
+			const uint64_t key = canon_key(from, ffw, to, tfw);
+			int replaced = 0;
+			uint64_t have = 0;
+			if (edge_find(old_ix, mo_old, key, &have) && have == r[4]) continue;      /* neighbours that were neighbours before */
+			if (edge_find(old_ix, mo_old, key, 0))
+				for (uint64_t q = 0; q < mo_old && !replaced; q++)
+					if (canon_key(ov_all[5 * q], ov_all[5 * q + 1], ov_all[5 * q + 2], ov_all[5 * q + 3]) == key) { ov_all[5 * q + 4] = r[4]; replaced = 1; }
+			if (replaced) continue;
+			uint32_t* w = ov_all + 5 * mo++;
+			w[0] = (uint32_t)(key >> 34); w[1] = (uint32_t)((key >> 33) & 1); w[2] = (uint32_t)((key >> 1) & 0xffffffffu); w[3] = (uint32_t)(key & 1); w[4] = r[4];
+		}
+		free(old_ix);
+	}
+	free(u->overlaps);
+	u->overlaps = ov_all; u->n_overlaps = mo;
+	for (uint64_t i = 0; i < n_new; i++) new_nodes[i] = 2 * rank[new_nodes[i] >> 1] + (new_nodes[i] & 1);
+	free(u->unitig_nodes); free(u->unitig_begin);
+	u->unitig_nodes = new_nodes; u->unitig_begin = new_begin; u->n_unitig_nodes = n_new; u->n_kept = nk;
+	free(kept); free(rank); free(add);
 }
 
 /* ---- read threading: getKmerLocator (MBG/KmerMatcher.cpp:3-31) and iterateReadPaths
@@ -398,6 +516,14 @@ static uint64_t* edge_index(const uint32_t* edges, uint64_t m, int value_col)
 	qsort(ix, m, 16, cmp_pair);
 	return ix;
 }
+/* the same from u32 x5 overlap records */
+static uint64_t* overlap_index(const uint32_t* ov, uint64_t m)
+{
+	uint64_t* ix = (uint64_t*)malloc((m + 1) * 16);
+	for (uint64_t e = 0; e < m; e++) { const uint32_t* r = ov + 5 * e; ix[2 * e] = canon_key(r[0], r[1], r[2], r[3]); ix[2 * e + 1] = r[4]; }
+	qsort(ix, m, 16, cmp_pair);
+	return ix;
+}
 static int edge_find(const uint64_t* ix, uint64_t m, uint64_t key, uint64_t* value)
 {
 	uint64_t lo = 0, hi = m;
@@ -426,7 +552,7 @@ orc_paths* orc_read_paths(const orc* o, const orc_unitigs* u, uint32_t k)
 			if (x & 1) { loc_pos[x >> 1] = j; loc_fw[x >> 1] = 1; } else { loc_pos[x >> 1] = size - 1 - j; loc_fw[x >> 1] = 0; }
 		}
 	}
-	uint64_t* overlap_ix = edge_index(u->f_edges, u->n_fedges, 5);
+	uint64_t* overlap_ix = overlap_index(u->overlaps, u->n_overlaps);
 	uint64_t* uedge_ix = edge_index(u->uedges, u->n_uedges, 4);
 	const orc_part* parts = (const orc_part*)orc_data(o, 0);
 	const uint64_t n_parts = orc_count(o, 0);
@@ -476,7 +602,7 @@ orc_paths* orc_read_paths(const orc* o, const orc_unitigs* u, uint32_t k)
 			if (last_kmer != NONE)
 			{
 				uint64_t ov = 0;
-				const int has = edge_find(overlap_ix, u->n_fedges, canon_key((uint32_t)last_kmer, (uint32_t)last_kmer_fw, (uint32_t)kmer, (uint32_t)fw), &ov);
+				const int has = edge_find(overlap_ix, u->n_overlaps, canon_key((uint32_t)last_kmer, (uint32_t)last_kmer_fw, (uint32_t)kmer, (uint32_t)fw), &ov);
 				if (!has || read_pos - last_read_pos != k - ov) restart = 1;
 			}
 			if (!restart)

@@ -29,6 +29,9 @@ void loadReadsAsHashesMultithread(HashList& result, const size_t kmerSize, const
 #include "UnitigGraph.h"
 #include "KmerMatcher.h"
 UnitigGraph getUnitigGraph(HashList& hashlist, const size_t minCoverage, const double minUnitigCoverage, const bool keepGaps, const bool oneCovHeuristic); // MBG.cpp:629
+UnitigGraph getUnitigs(const UnitigGraph& oldgraph); // MBG.cpp:782
+void filterKmersToUnitigKmers(UnitigGraph& unitigs, HashList& reads, const size_t kmerSize, const bool filterWithinUnitig); // MBG.cpp:1065
+void sortKmersByHashes(UnitigGraph& unitigs, HashList& reads); // MBG.cpp:1059
 
 namespace {
 
@@ -54,6 +57,7 @@ struct Run {
 	std::vector<uint64_t> rp_head;
 	std::vector<uint32_t> rp_path;  // 2*unitig + fw
 	std::vector<uint32_t> rp_poses;
+	std::vector<uint32_t> overlaps; // HashList::sequenceOverlap, canonical pairs: from, from_fw, to, to_fw, overlap
 	uint64_t total_selected = 0;
 };
 
@@ -261,7 +265,14 @@ void* refshim_unitigs_ex(int mode, uint64_t k, uint64_t w, const char* bases, co
 	HashList list { (size_t)k };
 	std::ostringstream log;
 	if (memoryReads.size() > 0) loadReadsAsHashesMultithread(list, k, tableIterator, 1, log);
-	UnitigGraph unitigs = getUnitigGraph(list, min_cov, min_unitig_cov, false, one_cov_heuristic != 0);
+	UnitigGraph unitigs = getUnitigGraph(list, min_cov, min_unitig_cov, false, (one_cov_heuristic & 1) != 0);
+	if (one_cov_heuristic & 2)
+	{
+		// the rest of runMBG's pass 3 up to the read paths (MBG.cpp:1575-1581) with MBG's defaults
+		if (min_unitig_cov > (double)min_cov) unitigs = getUnitigs(unitigs.filterUnitigsByCoverage(min_unitig_cov, false));
+		filterKmersToUnitigKmers(unitigs, list, (size_t)k, true);
+		sortKmersByHashes(unitigs, list);
+	}
 	size_t n = list.size();
 	run->node_hash.resize(2*n);
 	run->node_cov.resize(n);
@@ -316,6 +327,19 @@ void* refshim_unitigs_ex(int mode, uint64_t k, uint64_t w, const char* bases, co
 			}
 		}
 	}
+	for (size_t i = 0; i < n; i++)
+	{
+		for (int fw = 1; fw >= 0; fw--)
+		{
+			std::pair<size_t, bool> from { i, fw == 1 };
+			for (auto pair : list.getSequenceOverlaps(from))
+			{
+				run->overlaps.push_back((uint32_t)i); run->overlaps.push_back((uint32_t)fw);
+				run->overlaps.push_back((uint32_t)pair.first.first); run->overlaps.push_back(pair.first.second ? 1 : 0);
+				run->overlaps.push_back((uint32_t)pair.second);
+			}
+		}
+	}
 	// getReadPaths (MBG.cpp:1235-1251): every part threaded through the unitig graph (KmerMatcher.h:12-144), in input order
 	if (memoryReads.size() > 0)
 	{
@@ -356,6 +380,7 @@ uint64_t refshim_count(void* h, int what)
 		case 8: return r->rp_head.size() / 6;
 		case 9: return r->rp_path.size();
 		case 10: return r->rp_poses.size();
+		case 11: return r->overlaps.size() / 5;
 	}
 	return 0;
 }
@@ -378,6 +403,7 @@ const void* refshim_data(void* h, int what)
 		case 10: return r->rp_head.data();
 		case 11: return r->rp_path.data();
 		case 12: return r->rp_poses.data();
+		case 13: return r->overlaps.data();
 	}
 	return nullptr;
 }

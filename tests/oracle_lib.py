@@ -119,7 +119,7 @@ class Oracle:
         finally:
             L.orc_free(h)
 
-    def run_unitigs(self, mode, k, w, reads, min_cov, min_unitig_cov, variants=None, one_cov=False, paths=False):
+    def run_unitigs(self, mode, k, w, reads, min_cov, min_unitig_cov, variants=None, one_cov=False, paths=False, thin=False):
         """table + the filter/unitig step after it -> (RunResult, UnitigResult); one_cov = getUnitigGraph's oneCovHeuristic"""
         bases, offsets = reads if isinstance(reads, tuple) else pack_reads(reads)
         L = self.lib
@@ -141,11 +141,14 @@ class Oracle:
             L.orc_build_table(h)
             table = _collect(lambda w_: L.orc_count(h, w_), lambda w_: L.orc_data(h, w_), True)
             u = L.orc_build_unitigs_ex(h, min_cov, float(min_unitig_cov), 1 if one_cov else 0)
+            if thin:       # filterKmersToUnitigKmers, MBG's default within-unitig thinning
+                L.orc_thin_unitigs.argtypes = [C.c_void_p, C.c_uint32]
+                L.orc_thin_unitigs(u, k)
             cnt, dat = (lambda w_: L.orc_unitigs_count(u, w_)), (lambda w_: L.orc_unitigs_data(u, w_))
             res = UnitigResult(kept=_arr(dat(0), cnt(0), "u1"), node_hash=_arr(dat(1), cnt(1) * 2, "<u8").reshape(-1, 2), node_cov=_arr(dat(2), cnt(1), "<u4"),
                                node_tip=_arr(dat(3), cnt(1), "u1"), edges=_arr(dat(4), cnt(2) * 6, "<u4").reshape(-1, 6),
                                unitig_begin=_arr(dat(5), cnt(3) + 1, "<u8"), unitig_nodes=_arr(dat(6), cnt(4), "<u4"),
-                               unitig_edges=_arr(dat(7), cnt(5) * 6, "<u4").reshape(-1, 6))
+                               unitig_edges=_arr(dat(7), cnt(5) * 6, "<u4").reshape(-1, 6), overlaps=_arr(dat(8), cnt(6) * 5, "<u4").reshape(-1, 5))
             if paths:      # row f2: getReadPaths over the same run
                 L.orc_read_paths.restype = C.c_void_p
                 L.orc_read_paths.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32]
@@ -246,14 +249,14 @@ class Reference:
         finally:
             L.refshim_free(h)
 
-    def run_unitigs(self, mode, k, w, reads, min_cov, min_unitig_cov, one_cov=False):
+    def run_unitigs(self, mode, k, w, reads, min_cov, min_unitig_cov, one_cov=False, pass3=False):
         """the reference's own getUnitigGraph after its table build (ids = filtered arrival order) -> UnitigResult"""
         bases, offsets = reads if isinstance(reads, tuple) else pack_reads(reads)
         L = self.lib
         L.refshim_unitigs_ex.restype = C.c_void_p
         L.refshim_unitigs_ex.argtypes = [C.c_int, C.c_uint64, C.c_uint64, C.c_void_p, C.c_void_p, C.c_uint64, C.c_uint64, C.c_double, C.c_int]
         h = L.refshim_unitigs_ex(MODES[mode] if isinstance(mode, str) else mode, k, w, bases.ctypes.data, offsets.ctypes.data, len(offsets) - 1, min_cov, float(min_unitig_cov),
-                                 1 if one_cov else 0)
+                                 (1 if one_cov else 0) | (2 if pass3 else 0))      # bit 1: the rest of runMBG's pass 3 (MBG.cpp:1575-1581)
         try:
             r = _collect(lambda w_: L.refshim_count(h, w_), lambda w_: L.refshim_data(h, w_), True)
             begin = np.concatenate([r.parts["sel_begin"], [len(r.positions)]]).astype(np.uint64) if len(r.parts) else np.zeros(1, np.uint64)
@@ -261,7 +264,7 @@ class Reference:
             paths = ReadPaths(heads=_arr(L.refshim_data(h, 10), L.refshim_count(h, 8) * 6, "<u8").reshape(-1, 6), path=_arr(L.refshim_data(h, 11), L.refshim_count(h, 9), "<u4"),
                               poses=_arr(L.refshim_data(h, 12), L.refshim_count(h, 10), "<u4"))
             return UnitigResult(kept=None, node_hash=r.node_hash, node_cov=r.node_cov, node_tip=r.node_tip, edges=r.edges, unitig_begin=begin, unitig_nodes=r.positions,
-                                unitig_edges=ue, paths=paths)
+                                unitig_edges=ue, paths=paths, overlaps=_arr(L.refshim_data(h, 13), L.refshim_count(h, 11) * 5, "<u4").reshape(-1, 5))
         finally:
             L.refshim_free(h)
 

@@ -189,3 +189,24 @@ def test_read_paths_equal_reference(oracle, reference, mode, k, w, a, u, one_cov
         compare_paths(got.paths, got, want.paths, want, what=f"read paths {mode} k={k} a={a} u={u}")
         n_paths += len(got.paths.heads)
     assert n_paths > 20
+
+
+@pytest.mark.parametrize("mode,k,w,a,u", [("collapse-msat", 301, 30, 1, 2), ("hpc", 63, 33, 1, 3), ("collapse-msat", 101, 20, 1, 2), ("no", 63, 5, 1, 2)])
+def test_unitig_kmer_thinning_equals_reference(oracle, reference, mode, k, w, a, u):
+    """the rest of runMBG's pass 3 (MBG/MBG.cpp:1575-1581) under MBG's defaults: getUnitigs(filterUnitigsByCoverage),
+    filterKmersToUnitigKmers with filterWithinUnitig = true, sortKmersByHashes, getReadPaths -- the oracle's restatement of
+    the thinning (orc_thin_unitigs) and its read paths on the thinned list against the reference's own calls"""
+    from oracle_lib import compare_paths, compare_unitigs
+    thinned = 0
+    for reads in (workloads.coverage_reads(n_reads=40, error_ppm=4000), workloads.coverage_reads(seed=3, genome_len=20000, n_reads=12, error_ppm=10000),
+                  workloads.coverage_reads(seed=5, genome_len=30000, n_reads=60, error_ppm=2000)):
+        _, full = oracle.run_unitigs(mode, k, w, reads, a, u, one_cov=True)
+        _, got = oracle.run_unitigs(mode, k, w, reads, a, u, one_cov=True, paths=True, thin=True)
+        want = reference.run_unitigs(mode, k, w, reads, a, u, one_cov=True, pass3=True)
+        compare_unitigs(got, want, what=f"thinned unitigs {mode} k={k}")
+        # ids are in hash order on both sides after sortKmersByHashes: the overlaps compare directly
+        rows = lambda x: x[np.lexsort(x.T[::-1])]
+        assert np.array_equal(rows(got.overlaps), rows(want.overlaps)), "sequence overlaps after the thinning"
+        compare_paths(got.paths, got, want.paths, want, what=f"read paths on the thinned list {mode} k={k}")
+        thinned += len(full.node_cov) - len(got.node_cov)
+    assert thinned > 0, "nothing was thinned"
