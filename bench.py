@@ -386,6 +386,11 @@ def main():
         st_u = fe.stats()
         unitig_info["one_cov_heuristic"] = {"ms": st_u["ms_unitigs"], "kept_nodes": int(len(u["node_cov"])), "kept_edges": int(len(u["edges"])),
                                             "unitigs": int(len(u["unitig_begin"]) - 1), "unitig_edges": int(len(u["unitig_edges"])), "launches": st_u["launches"]}
+        # the last step of row f1 under MBG's defaults: which k-mers stay inside the unitigs (filterKmersToUnitigKmers)
+        fe.thin_unitigs()
+        thin, _ = fe.thin_unitigs()
+        st_n = fe.stats()
+        unitig_info["thin_unitigs"] = {"ms": st_n["ms_unitigs"], "kmers_in": int(len(thin)), "kmers_kept": int(thin.sum()), "launches": st_n["launches"]}
         # row f2: every resident k-mer instance threaded through those unitigs (getReadPaths as a batched lookup)
         fe.thread_reads()
         th = fe.thread_reads()

@@ -109,7 +109,10 @@ enum {
 	MBGFE_INST_UNITIG = 18,     /* uint32_t[] 2 * unitig + orientation as the read sees it; 0xffffffff = not located      */
 	MBGFE_INST_UNITIG_POS = 19, /* uint32_t[] position inside that oriented unitig (leftClip of a path = its first entry)   */
 	MBGFE_INST_UNITIG_REST = 20,/* uint32_t[] k-mers of the unitig behind it (rightClip of a path = its last entry)         */
-	MBGFE_INST_STEP = 21        /* uint8_t[]  what iterateReadPaths does at this k-mer, see mbgfe_thread_reads             */
+	MBGFE_INST_STEP = 21,       /* uint8_t[]  what iterateReadPaths does at this k-mer, see mbgfe_thread_reads             */
+	/* after mbgfe_thin_unitigs(): one entry per filtered node */
+	MBGFE_F_NODE_THIN = 22,     /* uint8_t[]  1 when filterKmersToUnitigKmers keeps the k-mer                             */
+	MBGFE_F_NODE_UNITIG_OFFSET = 23 /* uint32_t[] start of the k-mer inside its unitig, in codes (currentPos of that walk)  */
 };
 
 typedef struct {
@@ -214,6 +217,14 @@ int mbgfe_build_unitigs_ex(mbgfe* h, uint32_t kmer_abundance, double unitig_abun
  * entries, leftClip = MBGFE_INST_UNITIG_POS of the first, rightClip = MBGFE_INST_UNITIG_REST of the last.
  * Unitigs are numbered as mbgfe_build_unitigs numbers them.  world == 1. */
 int mbgfe_thread_reads(mbgfe* h);
+
+/* filterKmersToUnitigKmers (MBG/MBG.cpp:1065-1185) with filterWithinUnitig = true, MBG's default: inside a unitig only its
+ * two ends, tip k-mers and the k-mers needed to keep neighbours overlapping stay.  Computes, for the unitigs of the last
+ * mbgfe_build_unitigs[_ex], MBGFE_F_NODE_THIN (the RankBitvector `kept` of that function) and MBGFE_F_NODE_UNITIG_OFFSET (two
+ * neighbours of the thinned unitig overlap by k minus the difference of their offsets: the newOverlaps of MBG.cpp:1136-1141).
+ * The reference applies them with reads.filter(kept) + addSequenceOverlap (MBG.cpp:1176-1184); that last renumbering is
+ * still the caller's. */
+int mbgfe_thin_unitigs(mbgfe* h);
 
 /* Device-side stopwatch on the library's stream (CUDA events): start, any number of calls, stop -> milliseconds. */
 int mbgfe_timer_start(mbgfe* h);

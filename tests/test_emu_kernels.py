@@ -168,6 +168,25 @@ def test_emulated_unitig_numbering_is_unitiggraph_sort(reference, emu_library):
         assert np.array_equal(got.unitig_nodes[gb[i]:gb[i + 1]].astype(np.int64), x), f"unitig {i}"
 
 
+def test_emulated_unitig_kmer_thinning(oracle, emu_library):
+    """filterKmersToUnitigKmers (MBG/MBG.cpp:1065-1185, MBG's default thinning) on the emulator build: next-pointers +
+    orbit marking by pointer doubling against the oracle's sequential walk (pinned on the reference in tests/test_oracle.py)"""
+    from fe_helpers import check_thinning
+    from verkko_b200.frontend import MbgFrontEnd
+    reads = workloads.coverage_reads(n_reads=16, error_ppm=4000)
+    fe = MbgFrontEnd(301, 30, "collapse-msat", library=emu_library)
+    try:
+        fe.add_reads(*reads) if isinstance(reads, tuple) else fe.add_read_list(reads)
+        fe.run()
+        ug = fe.build_unitigs(1, 2, one_cov_heuristic=True)
+        thin, off = fe.thin_unitigs()
+        thin, off = thin.copy(), off.copy()
+    finally:
+        fe.close()
+    _, want = oracle.run_unitigs("collapse-msat", 301, 30, reads, 1, 2, one_cov=True, thin=True)
+    assert check_thinning(ug, thin, off, want, 301, "emu thinning") > 10 and thin.sum() < len(thin)
+
+
 def test_emulated_hash_in_groups(oracle, emu_library, monkeypatch):
     """k_kmer_hash_lanes with a staging area much smaller than a read: k-mers are hashed in groups of consecutive ones"""
     monkeypatch.setenv("MBGFE_HASH_LANES", "1")

@@ -432,4 +432,75 @@ __global__ void __launch_bounds__(256) k_thread_steps(const uint32_t* __restrict
 	}
 }
 
+
+// ---- filterKmersToUnitigKmers (MBG/MBG.cpp:1065-1185, filterWithinUnitig = true, MBG's default): which k-mers of a unitig
+// stay.  The reference walks a unitig from its smaller-hash end (the orientation the unitigs already have here) and keeps
+// a k-mer when it is an end, a tip k-mer, or when dropping it would leave the next k-mer without overlap to the last kept
+// one.  Which k-mer is kept next depends only on the last kept one: next(p) = first t > p that is the last k-mer, a tip
+// k-mer, or has pos(t + 1) >= pos(p) + k.  The kept set is the orbit of the unitig head under next(), marked by pointer
+// doubling: after round r every k-mer within 2^r steps of the head is marked.
+__device__ __forceinline__ uint32_t list_overlap(const EdgeRec* __restrict__ edges, uint64_t n_edges, uint32_t x, uint32_t y)
+{
+	uint32_t from = x >> 1, ffw = x & 1, to = y >> 1, tfw = y & 1;
+	if (to < from || (to == from && !tfw && !ffw)) { const uint32_t a = from, b = ffw; from = to; ffw = !tfw; to = a; tfw = !b; }    // canon(), MBG/MBGCommon.cpp:78-89
+	EdgeRec want; want.from = from; want.from_fw = ffw; want.to = to; want.to_fw = tfw; want.coverage = 0; want.overlap = 0;
+	const uint64_t key = edge_order_key(want);
+	uint64_t lo = 0, hi = n_edges;
+	while (lo < hi) { const uint64_t mid = (lo + hi) >> 1; if (edge_order_key(edges[mid]) < key) lo = mid + 1; else hi = mid; }
+	return (lo < n_edges && edge_order_key(edges[lo]) == key) ? edges[lo].overlap : 0u;
+}
+
+// step of every unitig position: k - overlap with the k-mer before it (0 at a unitig head)
+__global__ void __launch_bounds__(256) k_thin_delta(const uint32_t* __restrict__ unitig_nodes, uint64_t n_pos, const uint32_t* __restrict__ node_unitig, const uint64_t* __restrict__ unitig_begin,
+	const EdgeRec* __restrict__ edges, uint64_t n_edges, uint32_t k, uint32_t* __restrict__ delta)
+{
+	for (uint64_t p = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; p < n_pos; p += (uint64_t)gridDim.x * blockDim.x)
+	{
+		const uint32_t x = unitig_nodes[p];
+		const uint64_t b = unitig_begin[node_unitig[x >> 1]];
+		delta[p] = p == b ? 0u : k - list_overlap(edges, n_edges, unitig_nodes[p - 1], x);
+	}
+}
+
+// next(p), the head marks, and the position of every k-mer inside its unitig (currentPos of the reference's walk)
+__global__ void __launch_bounds__(256) k_thin_next(const uint32_t* __restrict__ unitig_nodes, uint64_t n_pos, const uint32_t* __restrict__ node_unitig, const uint64_t* __restrict__ unitig_begin,
+	const uint8_t* __restrict__ tip, const uint32_t* __restrict__ delta, const uint64_t* __restrict__ scan, uint32_t k, uint32_t* __restrict__ next, uint32_t* __restrict__ mark,
+	uint32_t* __restrict__ node_pos)
+{
+	for (uint64_t p = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; p < n_pos; p += (uint64_t)gridDim.x * blockDim.x)
+	{
+		const uint32_t x = unitig_nodes[p];
+		const uint32_t u = node_unitig[x >> 1];
+		const uint64_t b = unitig_begin[u], last = unitig_begin[u + 1] - 1;
+		const uint64_t base = scan[b];                                  // delta[b] == 0
+		const uint64_t here = scan[p] + delta[p] - base;
+		node_pos[x >> 1] = (uint32_t)here;
+		mark[p] = p == b ? 1u : 0u;
+		uint64_t t = p;
+		if (p < last)
+			for (t = p + 1; t < last; t++)
+			{
+				if (tip[unitig_nodes[t] >> 1]) break;
+				if (scan[t + 1] + delta[t + 1] - base >= here + k) break;
+			}
+		next[p] = (uint32_t)t;
+	}
+}
+
+__global__ void __launch_bounds__(256) k_thin_mark(const uint32_t* __restrict__ jump, uint64_t n_pos, uint32_t* mark)
+{
+	for (uint64_t p = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; p < n_pos; p += (uint64_t)gridDim.x * blockDim.x)
+		if (((volatile uint32_t*)mark)[p]) mark[jump[p]] = 1;          // whatever gets marked is on the orbit
+}
+
+__global__ void __launch_bounds__(256) k_thin_double(const uint32_t* __restrict__ in, uint64_t n_pos, uint32_t* __restrict__ out)
+{
+	for (uint64_t p = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; p < n_pos; p += (uint64_t)gridDim.x * blockDim.x) out[p] = in[in[p]];
+}
+
+__global__ void __launch_bounds__(256) k_thin_flags(const uint32_t* __restrict__ unitig_nodes, uint64_t n_pos, const uint32_t* __restrict__ mark, uint8_t* __restrict__ thin)
+{
+	for (uint64_t p = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; p < n_pos; p += (uint64_t)gridDim.x * blockDim.x) thin[unitig_nodes[p] >> 1] = (uint8_t)mark[p];
+}
+
 }

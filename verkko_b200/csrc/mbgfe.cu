@@ -108,12 +108,14 @@ struct mbgfe
 	DevBuf d_var_hash, d_var_offset, d_var_len_begin, d_var_len;       // hpc variants (mbgfe_set_variants), sorted
 	// mbgfe_build_unitigs: graph scratch (degrees, successor, link, two ranking states, flags, scans) and results
 	DevBuf d_g_deg, d_g_nb, d_g_link, d_g_st[2], d_g_kept, d_g_newid, d_g_flag, d_g_at, d_g_flag2, d_g_at2, d_g_flag_byte;
-	DevBuf d_f_hash, d_f_cov, d_f_tip, d_f_edges, d_f_orig, d_t_hash, d_t_cov, d_t_tip, d_t_edges, d_t_orig, d_g_kept8, d_u_pos, d_th_final, d_th_node, d_th_unitig, d_th_upos, d_th_urest, d_th_step, d_u_begin, d_u_nodes, d_u_of_node, d_u_fw, d_u_edges;
+	DevBuf d_f_hash, d_f_cov, d_f_tip, d_f_edges, d_f_orig, d_t_hash, d_t_cov, d_t_tip, d_t_edges, d_t_orig, d_g_kept8, d_u_pos, d_th_final, d_th_node, d_th_unitig, d_th_upos, d_th_urest, d_th_step, d_thin, d_thin_pos, d_u_begin, d_u_nodes, d_u_of_node, d_u_fw, d_u_edges;
 	bool have_unitigs = false;
 	uint64_t n_kept = 0, n_fedges = 0, n_unitigs = 0, n_unitig_nodes = 0, n_uedges = 0;
 	std::vector<mbgfe_edge> h_u_edges;
 	std::vector<uint8_t> h_kept, h_f_tip, h_th_step;
-	std::vector<uint32_t> h_th_unitig, h_th_upos, h_th_urest;
+	std::vector<uint32_t> h_th_unitig, h_th_upos, h_th_urest, h_thin_pos;
+	std::vector<uint8_t> h_thin;
+	bool have_thin = false;
 	uint32_t unitig_min_cov = 1;
 	bool have_threads = false;
 	std::vector<mbgfe_hash128> h_f_hash;
@@ -493,7 +495,7 @@ void mbgfe_destroy(mbgfe* h)
 		&h->d_edge_out, &h->d_records, &h->d_recv, &h->d_bucket_count, &h->d_bucket_begin, &h->d_scan_tot, &h->d_scan_off, &h->d_node_hash_sorted, &h->d_node_cov,
 		&h->d_node_tip, &h->d_edges_sorted, &h->d_inst_packpos, &h->d_ids_out, &h->d_id_begin, &h->d_edge_records, &h->d_xbuf[0], &h->d_xbuf[1], &h->d_xbuf[2],
 		&h->d_xbuf[3], &h->d_var_hash, &h->d_var_offset, &h->d_var_len_begin, &h->d_var_len, &h->d_g_deg, &h->d_g_nb, &h->d_g_link, &h->d_g_st[0], &h->d_g_st[1],
-		&h->d_g_kept, &h->d_g_newid, &h->d_g_flag, &h->d_g_at, &h->d_g_flag2, &h->d_g_at2, &h->d_g_flag_byte, &h->d_f_hash, &h->d_f_cov, &h->d_f_tip, &h->d_f_edges, &h->d_f_orig, &h->d_t_hash, &h->d_t_cov, &h->d_t_tip, &h->d_t_edges, &h->d_t_orig, &h->d_g_kept8, &h->d_u_pos, &h->d_th_final, &h->d_th_node, &h->d_th_unitig, &h->d_th_upos, &h->d_th_urest, &h->d_th_step,
+		&h->d_g_kept, &h->d_g_newid, &h->d_g_flag, &h->d_g_at, &h->d_g_flag2, &h->d_g_at2, &h->d_g_flag_byte, &h->d_f_hash, &h->d_f_cov, &h->d_f_tip, &h->d_f_edges, &h->d_f_orig, &h->d_t_hash, &h->d_t_cov, &h->d_t_tip, &h->d_t_edges, &h->d_t_orig, &h->d_g_kept8, &h->d_u_pos, &h->d_th_final, &h->d_th_node, &h->d_th_unitig, &h->d_th_upos, &h->d_th_urest, &h->d_th_step, &h->d_thin, &h->d_thin_pos,
 		&h->d_u_begin, &h->d_u_nodes, &h->d_u_of_node, &h->d_u_fw, &h->d_u_edges }) release(*b);
 	for (HostBuf* b : { &h->p_node_hashes, &h->p_node_cov, &h->p_node_tip, &h->p_edges, &h->p_stage }) release_host(*b);
 	for (auto& e : h->ev) if (e) cudaEventDestroy(e);
@@ -1482,6 +1484,7 @@ int mbgfe_build_unitigs_ex(mbgfe* h, uint32_t kmer_abundance, double unitig_abun
 	const uint64_t n = h->n_nodes_out, m = h->n_edges_out;
 	h->have_unitigs = false;
 	h->have_threads = false;
+	h->have_thin = false;
 	h->unitig_min_cov = kmer_abundance;
 	uint32_t launches = 0;
 	tick(h, 12);
@@ -1588,6 +1591,62 @@ int mbgfe_build_unitigs_ex(mbgfe* h, uint32_t kmer_abundance, double unitig_abun
 	return 0;
 }
 
+// filterKmersToUnitigKmers (MBG/MBG.cpp:1065-1185) with filterWithinUnitig = true: which k-mers of the filtered list stay, and
+// where every k-mer sits inside its unitig (graph.cuh)
+int mbgfe_thin_unitigs(mbgfe* h)
+{
+	if (!h) return MBGFE_E_PARAM;
+	if (!h->have_unitigs) return fail(h, MBGFE_E_STATE, "mbgfe_thin_unitigs needs mbgfe_build_unitigs first");
+	const uint64_t n_kept = h->n_kept, n_pos = h->n_unitig_nodes, n_fedges = h->n_fedges;
+	uint32_t launches = 0;
+	tick(h, 12);
+	if (int rc = ensure(h, h->d_thin, n_kept + 64)) return rc;
+	if (int rc = ensure(h, h->d_thin_pos, (n_kept + 1) * 4)) return rc;
+	if (n_kept)
+	{
+		CU(h, cudaMemsetAsync(h->d_thin.p, 0, n_kept, h->stream));
+		CU(h, cudaMemsetAsync(h->d_thin_pos.p, 0, n_kept * 4, h->stream));
+	}
+	if (n_pos)
+	{
+		if (int rc = ensure(h, h->d_g_flag, (n_pos + 1) * 4)) return rc;
+		if (int rc = ensure(h, h->d_g_at, (n_pos + 2) * 8)) return rc;
+		if (int rc = ensure(h, h->d_g_flag2, (n_pos + 1) * 4)) return rc;
+		if (int rc = ensure(h, h->d_g_kept, (n_pos + 1) * 4)) return rc;
+		if (int rc = ensure(h, h->d_g_deg, (n_pos + 1) * 4)) return rc;
+		uint32_t* delta = h->d_g_flag.as<uint32_t>();
+		uint32_t* jump[2] = { h->d_g_flag2.as<uint32_t>(), h->d_g_kept.as<uint32_t>() };
+		uint32_t* mark = h->d_g_deg.as<uint32_t>();
+		CU(h, cudaMemsetAsync(delta + n_pos, 0, 4, h->stream));
+		MBGFE_LAUNCH(k_thin_delta, grid_for(h, n_pos), 256, 0, h->stream, h->d_u_nodes.as<uint32_t>(), n_pos, h->d_u_of_node.as<uint32_t>(), h->d_u_begin.as<uint64_t>(),
+			h->d_f_edges.as<EdgeRec>(), n_fedges, h->prm.k, delta);
+		if (int rc = device_scan(h, delta, h->d_g_at.as<uint64_t>(), (uint32_t)n_pos)) return rc;
+		MBGFE_LAUNCH(k_thin_next, grid_for(h, n_pos), 256, 0, h->stream, h->d_u_nodes.as<uint32_t>(), n_pos, h->d_u_of_node.as<uint32_t>(), h->d_u_begin.as<uint64_t>(),
+			h->d_f_tip.as<uint8_t>(), delta, h->d_g_at.as<uint64_t>(), h->prm.k, jump[0], mark, h->d_thin_pos.as<uint32_t>());
+		launches += 5;
+		int cur = 0;
+		for (uint64_t reach = 1; reach < n_pos; reach <<= 1)      // after the round every k-mer within 2 * reach - 1 steps of its head is marked
+		{
+			MBGFE_LAUNCH(k_thin_mark, grid_for(h, n_pos), 256, 0, h->stream, jump[cur], n_pos, mark);
+			MBGFE_LAUNCH(k_thin_double, grid_for(h, n_pos), 256, 0, h->stream, jump[cur], n_pos, jump[cur ^ 1]);
+			cur ^= 1;
+			launches += 2;
+		}
+		MBGFE_LAUNCH(k_thin_mark, grid_for(h, n_pos), 256, 0, h->stream, jump[cur], n_pos, mark);
+		MBGFE_LAUNCH(k_thin_flags, grid_for(h, n_pos), 256, 0, h->stream, h->d_u_nodes.as<uint32_t>(), n_pos, mark, h->d_thin.as<uint8_t>());
+		launches += 2;
+	}
+	tick(h, 13);
+	fetch(h, h->h_thin, h->d_thin, n_kept);
+	fetch(h, h->h_thin_pos, h->d_thin_pos, n_kept);
+	CU(h, cudaStreamSynchronize(h->stream));
+	CU(h, cudaGetLastError());
+	h->stats.ms_unitigs = elapsed(h, 12, 13);
+	h->stats.launches = launches;
+	h->have_thin = true;
+	return 0;
+}
+
 // getReadPaths (MBG/MBG.cpp:1235-1251) as a batched lookup: every selected k-mer instance of the last run located in the
 // unitigs of the last mbgfe_build_unitigs[_ex] and classified the way iterateReadPaths (MBG/KmerMatcher.h:12-144) would
 int mbgfe_thread_reads(mbgfe* h)
@@ -1655,6 +1714,7 @@ uint64_t mbgfe_count(mbgfe* h, int what)
 		case MBGFE_UNITIG_NODES: return h->have_unitigs ? h->n_unitig_nodes : 0;
 		case MBGFE_UNITIG_EDGES: return h->have_unitigs ? h->n_uedges : 0;
 		case MBGFE_INST_UNITIG: case MBGFE_INST_UNITIG_POS: case MBGFE_INST_UNITIG_REST: case MBGFE_INST_STEP: return h->have_threads ? h->h_th_step.size() : 0;
+		case MBGFE_F_NODE_THIN: case MBGFE_F_NODE_UNITIG_OFFSET: return h->have_thin ? h->h_thin.size() : 0;
 	}
 	return 0;
 }
@@ -1702,6 +1762,11 @@ const void* mbgfe_data(mbgfe* h, int what)
 				case MBGFE_INST_UNITIG_REST: return h->h_th_urest.data();
 				default: return h->h_th_step.data();
 			}
+	}
+	if (what == MBGFE_F_NODE_THIN || what == MBGFE_F_NODE_UNITIG_OFFSET)
+	{
+		if (!h->have_thin) { fail(h, MBGFE_E_STATE, "thinning requested before mbgfe_thin_unitigs"); return nullptr; }
+		return what == MBGFE_F_NODE_THIN ? (const void*)h->h_thin.data() : (const void*)h->h_thin_pos.data();
 	}
 	fail(h, MBGFE_E_PARAM, "unknown result array %d", what);
 	return nullptr;

@@ -16,6 +16,7 @@ KEEP_CODES, KEEP_POSES, NO_TABLE, NO_EDGES = 1, 2, 4, 8
 PARTS, CODES, POSES, POSITIONS, HASHES, NODE_HASHES, NODE_COVERAGE, NODE_TIP, EDGES = range(9)
 NODE_KEPT, F_NODE_HASHES, F_NODE_COVERAGE, F_NODE_TIP, F_EDGES, UNITIG_BEGIN, UNITIG_NODES, F_NODE_UNITIG, UNITIG_EDGES = range(9, 18)
 INST_UNITIG, INST_UNITIG_POS, INST_UNITIG_REST, INST_STEP = range(18, 22)
+F_NODE_THIN, F_NODE_UNITIG_OFFSET = 22, 23
 UNITIG_ONECOV_HEURISTIC = 1      # mbgfe_build_unitigs_ex flag (include/mbgfe.h)
 
 PART_DTYPE = np.dtype([
@@ -92,6 +93,7 @@ def load_library(path=None):
     L.mbgfe_build_unitigs.argtypes = [C.c_void_p, C.c_uint32, C.c_double]
     L.mbgfe_build_unitigs_ex.argtypes = [C.c_void_p, C.c_uint32, C.c_double, C.c_uint32]
     L.mbgfe_thread_reads.argtypes = [C.c_void_p]
+    L.mbgfe_thin_unitigs.argtypes = [C.c_void_p]
     L.mbgfe_set_variants.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint64]
     L.mbgfe_kat_tables.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
     L.mbgfe_kat_kmer_hash.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p]
@@ -260,6 +262,12 @@ class MbgFrontEnd:
         self._check(self.lib.mbgfe_thread_reads(self.handle))
         return dict(unitig=self._data(INST_UNITIG, "<u4"), unitig_pos=self._data(INST_UNITIG_POS, "<u4"), unitig_rest=self._data(INST_UNITIG_REST, "<u4"),
                     step=self._data(INST_STEP, "u1"))
+
+    def thin_unitigs(self):
+        """filterKmersToUnitigKmers (MBG/MBG.cpp:1065-1185, filterWithinUnitig = true) -> (kept flag, offset inside the
+        unitig) per filtered node"""
+        self._check(self.lib.mbgfe_thin_unitigs(self.handle))
+        return self._data(F_NODE_THIN, "u1"), self._data(F_NODE_UNITIG_OFFSET, "<u4")
 
     def read_paths(self):
         """the ReadPath list of getReadPaths (MBG/MBG.cpp:1235-1251) put together from thread_reads() the way
