@@ -252,7 +252,7 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default="chr20", choices=list(WORKLOADS))
     ap.add_argument("--scale", type=float, default=1.0, help="shrink the genome (and read count) for quick runs")
-    ap.add_argument("--e2e-steps", type=int, default=2)
+    ap.add_argument("--e2e-steps", type=int, default=0, help="timed end-to-end steps (0 = --steps)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--k", type=int, default=0, help="k-mer size override (BASELINE.json configs[4]: the k/w sweep)")
     ap.add_argument("--w", type=int, default=0, help="window size override")
@@ -261,6 +261,8 @@ def main():
     if args.k or args.w:
         wl["k"], wl["w"] = args.k or wl["k"], args.w or wl["w"]
         wl["desc"] = wl["desc"].replace("k=1001 w=100", f"k={wl['k']} w={wl['w']}")
+    if args.e2e_steps <= 0:
+        args.e2e_steps = args.steps
     if args.impl == "reference":
         reference_arm(args, wl)
         return

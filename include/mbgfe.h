@@ -8,8 +8,8 @@
  *
  * Errors: functions return 0 on success, a negative MBGFE_E_* otherwise; mbgfe_last_error() describes the failure.
  * The reference reports the same conditions with exit(1)/abort() (MBG/main.cpp:158-198, MBG/ReadHelper.h:775-783);
- * the MBG-compatible command line maps the codes back to those behaviours.  There is NO CPU fallback: without a
- * usable sm_100 device mbgfe_create() fails with MBGFE_E_CUDA.
+ * a caller that wants MBG's process-level behaviour maps the codes back.  There is NO CPU fallback:
+ * without a usable sm_100 device mbgfe_create() fails with MBGFE_E_CUDA.
  */
 #ifndef MBGFE_H
 #define MBGFE_H
@@ -43,7 +43,9 @@ enum {
 	MBGFE_KEEP_CODES = 1,   /* keep the per-part code arrays for mbgfe_data(MBGFE_CODES)         (iterateParts)  */
 	MBGFE_KEEP_POSES = 2,   /* also compute/keep the per-code positions (poses)                   (iterateParts)  */
 	MBGFE_NO_TABLE   = 4,   /* stop after k-mer hashing: no node/edge table                       (iterateHashes) */
-	MBGFE_NO_EDGES   = 8    /* count k-mers (nodes, tips) but skip the adjacency pass                              */
+	MBGFE_NO_EDGES   = 8,   /* count k-mers (nodes, tips) but skip the adjacency pass                              */
+	MBGFE_INCLUDE_END_KMERS = 16 /* --include-end-kmers (MBG/ReadHelper.cpp:20-30, 38-61): NOT built (Verkko never passes it);
+	                                mbgfe_create() rejects it with MBGFE_E_PARAM instead of silently ignoring it        */
 };
 
 typedef struct {

@@ -15,7 +15,7 @@
  *
  * Parity pinning: the reference holds no tests or golden vectors for this path.  This oracle is
  * pinned instead against (1) outputs of the reference itself, compiled here by oracle/Makefile into
- * oracle/_ref/libmbgref.so and compared in tests/test_oracle_vs_reference.py, and (2) fixtures generated from that
+ * oracle/_ref/libmbgref.so and compared in tests/test_oracle.py, and (2) fixtures generated from that
  * library and committed under tests/golden/ (generator: tools/make_golden.py).
  */
 #include "mbg_oracle.h"

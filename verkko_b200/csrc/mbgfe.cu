@@ -320,7 +320,8 @@ void clear_results(mbgfe* h)
 	h->parts.clear(); h->h_codes.clear(); h->h_poses.clear(); h->h_positions.clear(); h->h_hashes.clear();
 	h->n_nodes_out = 0; h->n_edges_out = 0;
 	h->n_inst = 0;
-	h->have_unitigs = false;
+	h->have_unitigs = false; h->have_thin = false; h->have_threads = false;
+	h->h_thin.clear(); h->h_thin_pos.clear(); h->h_th_unitig.clear(); h->h_th_upos.clear(); h->h_th_urest.clear(); h->h_th_step.clear();
 }
 
 // ---------------------------------------------------------------------------------------------- file input
@@ -435,6 +436,7 @@ int mbgfe_create(const mbgfe_params* prm, mbgfe** out)
 	if (prm->w == 0) return fail(nullptr, MBGFE_E_PARAM, "w must be at least 1");
 	if (prm->w > prm->k - 30) return fail(nullptr, MBGFE_E_PARAM, "w must be at most k-30");
 	if (prm->error_masking > MBGFE_MASK_COLLAPSE_MSAT) return fail(nullptr, MBGFE_E_PARAM, "unknown error masking mode %u", prm->error_masking);
+	if (prm->flags & MBGFE_INCLUDE_END_KMERS) return fail(nullptr, MBGFE_E_PARAM, "--include-end-kmers (MBG/ReadHelper.cpp:38-61) is not implemented");
 	if (prm->world > MAX_WORLD) return fail(nullptr, MBGFE_E_PARAM, "world %u: at most %u ranks", prm->world, MAX_WORLD);
 	if (prm->world == 0 || prm->rank >= prm->world) return fail(nullptr, MBGFE_E_PARAM, "rank %u outside world %u", prm->rank, prm->world);
 	int n_dev = 0;
@@ -860,11 +862,14 @@ int process_tail(mbgfe* h, uint32_t launches)
 		const uint64_t slots = std::max<uint64_t>(next_pow2(std::max<uint64_t>(2 * n_inst, 1024)), h->prm.table_slots ? next_pow2(h->prm.table_slots) : 0);
 		if (int rc = clear_tables(h, slots, launches)) return rc;
 		launch_tables(h, 0, n_seg, n_inst, launches, true);
-		unsigned long long two[2] = { 0, 0 };
-		CU(h, cudaMemcpyAsync(two, ctr + CTR_DISTINCT, 16, cudaMemcpyDeviceToHost, h->stream));
+		unsigned long long five[5] = { 0, 0, 0, 0, 0 };      // CTR_DISTINCT, CTR_EDGES, cursor x2, CTR_OVERFLOW
+		CU(h, cudaMemcpyAsync(five, ctr + CTR_DISTINCT, sizeof(five), cudaMemcpyDeviceToHost, h->stream));
 		CU(h, cudaStreamSynchronize(h->stream));
-		h->stats.d2h_bytes += 16;
-		h->stats.distinct = two[0]; h->stats.distinct_edges = two[1];
+		h->stats.d2h_bytes += sizeof(five);
+		// the probe limit (MAX_PROBES) gave up on some k-mer or edge: the result would silently miss it
+		if (five[CTR_OVERFLOW - CTR_DISTINCT]) return fail(h, MBGFE_E_LIMIT, "k-mer table of %llu slots overflowed (%llu inserts gave up); pass a larger mbgfe_params.table_slots",
+			(unsigned long long)slots, five[CTR_OVERFLOW - CTR_DISTINCT]);
+		h->stats.distinct = five[0]; h->stats.distinct_edges = five[1];
 		h->stats.table_slots = slots;
 		h->have_table = true;
 	}
@@ -1339,18 +1344,26 @@ int rank_chains(mbgfe* h, const EdgeRec* edges, uint64_t n_edges, const uint32_t
 		MBGFE_LAUNCH(k_chain_init, grid_for(h, n2), 256, 0, h->stream, h->d_g_link.as<uint32_t>(), cov, n2, h->d_g_st[0].as<ChainState>());
 		launches++;
 		uint32_t open = 1;
-		for (int round = 0; round < 34 && open; round++)
+		// a chain has at most n2 states, so ceil(log2 n2) + 1 doublings finish every open one; what is left then is circular.
+		// The flag comes back every third round only (a host synchronisation costs more than a round on a short list).
+		int limit = 2;
+		while ((1ull << limit) < n2) limit++;
+		limit += 1;
+		for (int round = 0; round < limit && open; round++)
 		{
 			CU(h, cudaMemsetAsync(flag, 0, 4, h->stream));
 			MBGFE_LAUNCH(k_chain_jump, grid_for(h, n2), 256, 0, h->stream, h->d_g_st[cur].as<ChainState>(), h->d_g_st[cur ^ 1].as<ChainState>(), n2, flag);
 			launches++;
 			cur ^= 1;
-			CU(h, cudaMemcpyAsync(&open, flag, 4, cudaMemcpyDeviceToHost, h->stream));
-			CU(h, cudaStreamSynchronize(h->stream));
+			if (round % 3 == 2 || round + 1 == limit)
+			{
+				CU(h, cudaMemcpyAsync(&open, flag, 4, cudaMemcpyDeviceToHost, h->stream));
+				CU(h, cudaStreamSynchronize(h->stream));
+			}
 		}
 		*which = cur;
 		if (!open) return 0;
-		// what is still open after 2^34 steps is circular: cut every cycle in front of its smallest node, rank again
+		// what is still open after that many doublings is circular: cut every cycle in front of its smallest node, rank again
 		if (attempt == 1) return fail(h, MBGFE_E_STATE, "chain ranking did not terminate");
 		MBGFE_LAUNCH(k_chain_cut, grid_for(h, n2), 256, 0, h->stream, h->d_g_st[cur].as<ChainState>(), n2, h->d_g_link.as<uint32_t>());
 		launches++;

@@ -45,8 +45,8 @@ class MbgfeError(RuntimeError):
 
 
 def library_path():
-    """The in-tree CUDA library.  MBGFE_LIBRARY overrides it (used by the GPU-less emulator tests only)."""
-    return os.environ.get("MBGFE_LIBRARY", os.path.join(HERE, "libmbgfe.so"))
+    """The in-tree CUDA library (no override: tests that want the GPU-less emulator build pass `library=` explicitly)."""
+    return os.path.join(HERE, "libmbgfe.so")
 
 
 _lib = None
