@@ -427,6 +427,64 @@ double refshim_time_file(int mode, uint64_t k, uint64_t w, const char* path, uin
 	return std::chrono::duration<double>(t1 - t0).count();
 }
 
+
+// Order-free digest of a HashList (independent of node numbering and of which mirror image of an edge is stored), so
+// that a table built elsewhere -- the CUDA path, on the same reads -- can be compared with the reference's without
+// moving the table: out[0] = sum of coverage (selected k-mers), [1] = distinct k-mers, [2] = distinct edges,
+// [3] = XOR of mix(hash) * (2 cov + 1), [4] = sum of mix(hash) * cov, [5] = tip k-mers, [6] = sum of edge coverage,
+// [7] = sum of sym(edge) * cov, [8] = XOR of sym(edge) * (2 cov + 1), [9] = sum of sym(edge) * overlap, all mod 2^64, with
+// mix(h) = lo * 0x9E3779B97F4A7C15 + hi * 0xC2B2AE3D27D4EB4F, v(node, fw) = mix * (fw ? 3 : 5),
+// e(a, b) = v(a) * 7 + v(b) * 11 and sym = e(from, to) + e(reverse to, reverse from).
+// Tips ([5]) and overlaps ([9]) are only deterministic with one worker thread.
+// tests/oracle_lib.py:table_digest computes the same from exported arrays.
+static void hashlist_digest(HashList& list, uint64_t* out)
+{
+	const size_t n = list.size();
+	std::vector<uint64_t> mix(n);
+	for (auto pair : list.hashToNode) mix[pair.second] = (uint64_t)pair.first * 0x9E3779B97F4A7C15ull + (uint64_t)(pair.first >> 64) * 0xC2B2AE3D27D4EB4Full;
+	for (int i = 0; i < 10; i++) out[i] = 0;
+	out[1] = n;
+	auto v = [&](std::pair<size_t, bool> node) { return mix[node.first] * (node.second ? 3ull : 5ull); };
+	for (size_t i = 0; i < n; i++)
+	{
+		const uint64_t cov = list.coverage.get(i);
+		out[0] += cov;
+		out[3] ^= mix[i] * (2 * cov + 1);
+		out[4] += mix[i] * cov;
+		out[5] += list.isTipKmer(i) ? 1 : 0;
+		for (int fw = 1; fw >= 0; fw--)
+		{
+			std::pair<size_t, bool> from { i, fw == 1 };
+			for (auto edge : list.getEdgeCoverages(from))
+			{
+				const std::pair<size_t, bool> to = edge.first;
+				const std::pair<size_t, bool> rto { to.first, !to.second }, rfrom { from.first, !from.second };
+				const uint64_t sym = (v(from) * 7 + v(to) * 11) + (v(rto) * 7 + v(rfrom) * 11);
+				const uint64_t ecov = edge.second;
+				out[2] += 1;
+				out[6] += ecov;
+				out[7] += sym * ecov;
+				out[8] ^= sym * (2 * ecov + 1);
+				out[9] += sym * (uint64_t)list.getOverlap(from, to);
+			}
+		}
+	}
+}
+
+// refshim_time_file + the digest of the table it built (10 words, see hashlist_digest)
+double refshim_time_file_digest(int mode, uint64_t k, uint64_t w, const char* path, uint64_t threads, uint64_t* digest10)
+{
+	std::vector<std::string> files { std::string(path) };
+	ReadpartIterator iterator { (size_t)k, (size_t)w, (ErrorMasking)mode, (size_t)threads, files, false, "" };
+	HashList list { (size_t)k };
+	std::ostringstream log;
+	auto t0 = std::chrono::steady_clock::now();
+	loadReadsAsHashesMultithread(list, k, iterator, threads, log);
+	auto t1 = std::chrono::steady_clock::now();
+	if (digest10) hashlist_digest(list, digest10);
+	return std::chrono::duration<double>(t1 - t0).count();
+}
+
 // Known-answer helpers (SURVEY.md 8c "tables", "FastHasher", "hash(vector)", "msat" rows).
 uint64_t refshim_max_code() { return maxCode(); }
 uint16_t refshim_complement(uint16_t c) { return complement(c); }

@@ -482,3 +482,57 @@ def lcg_bases(seed, n):
         x = (x * 6364136223846793005 + 1442695040888963407) & 0xFFFFFFFFFFFFFFFF
         out[i] = b"ACGT"[(x >> 33) & 3]
     return bytes(out)
+
+
+DIGEST_FIELDS = ("selected", "distinct", "distinct_edges", "node_xor", "node_sum", "tips", "edge_cov", "edge_sum", "edge_xor", "overlap_sum")
+
+
+def table_digest(node_hash, node_cov, node_tip, edges):
+    """order-free digest of a k-mer table from its exported arrays; the same ten words as oracle/ref_shim.cpp:hashlist_digest
+    computes from the reference's HashList (mod 2^64)"""
+    with np.errstate(over="ignore"):
+        nh = np.asarray(node_hash, dtype=np.uint64).reshape(-1, 2)
+        cov = np.asarray(node_cov).astype(np.uint64)
+        mix = nh[:, 0] * np.uint64(0x9E3779B97F4A7C15) + nh[:, 1] * np.uint64(0xC2B2AE3D27D4EB4F)
+        e = np.asarray(edges).reshape(-1, 6).astype(np.uint64)
+        three, five, seven, eleven, one, two = (np.uint64(x) for x in (3, 5, 7, 11, 1, 2))
+
+        def v(ids, fw):
+            return mix[ids.astype(np.int64)] * np.where(fw == one, three, five)
+        out = dict.fromkeys(DIGEST_FIELDS, 0)
+        out["selected"] = int(cov.sum(dtype=np.uint64))
+        out["distinct"] = len(cov)
+        out["distinct_edges"] = len(e)
+        out["node_xor"] = int(np.bitwise_xor.reduce(mix * (two * cov + one))) if len(cov) else 0
+        out["node_sum"] = int((mix * cov).sum(dtype=np.uint64))
+        out["tips"] = int(np.asarray(node_tip).astype(np.uint64).sum())
+        if len(e):
+            sym = (v(e[:, 0], e[:, 1]) * seven + v(e[:, 2], e[:, 3]) * eleven) + (v(e[:, 2], one - e[:, 3]) * seven + v(e[:, 0], one - e[:, 1]) * eleven)
+            out["edge_cov"] = int(e[:, 4].sum(dtype=np.uint64))
+            out["edge_sum"] = int((sym * e[:, 4]).sum(dtype=np.uint64))
+            out["edge_xor"] = int(np.bitwise_xor.reduce(sym * (two * e[:, 4] + one)))
+            out["overlap_sum"] = int((sym * e[:, 5]).sum(dtype=np.uint64))
+        return out
+
+
+def reference_file_digest(mode, k, w, fasta_path, threads):
+    """(seconds, digest dict) of the reference's loadReadsAsHashesMultithread over a FASTA/FASTQ file"""
+    lib = C.CDLL(REF_SO)
+    lib.refshim_time_file_digest.restype = C.c_double
+    lib.refshim_time_file_digest.argtypes = [C.c_int, C.c_uint64, C.c_uint64, C.c_char_p, C.c_uint64, C.c_void_p]
+    d = (C.c_uint64 * 10)()
+    t = lib.refshim_time_file_digest(MODES[mode] if isinstance(mode, str) else mode, k, w, str(fasta_path).encode(), threads, d)
+    return t, dict(zip(DIGEST_FIELDS, [int(x) for x in d]))
+
+
+def write_fasta(path, bases, offsets, line=0):
+    """reads -> FASTA (one sequence line per read unless line > 0)"""
+    with open(path, "wb") as f:
+        for i in range(len(offsets) - 1):
+            seq = bases[int(offsets[i]):int(offsets[i + 1])].tobytes()
+            f.write(b">r%d\n" % i)
+            if line:
+                for j in range(0, len(seq), line):
+                    f.write(seq[j:j + line] + b"\n")
+            else:
+                f.write(seq + b"\n")

@@ -210,3 +210,27 @@ def test_unitig_kmer_thinning_equals_reference(oracle, reference, mode, k, w, a,
         compare_paths(got.paths, got, want.paths, want, what=f"read paths on the thinned list {mode} k={k}")
         thinned += len(full.node_cov) - len(got.node_cov)
     assert thinned > 0, "nothing was thinned"
+
+
+def test_table_digest_equals_reference_hashlist_digest(oracle, reference, tmp_path):
+    """the order-free table digest (bench.py `parity_sample`, tests/test_gpu_configs.py): computed from exported arrays
+    (oracle table here) it equals what oracle/ref_shim.cpp computes straight from the reference's HashList built from a
+    FASTA file -- with one worker thread all ten words, with four all but the two the reference leaves to a race
+    (tips) or to arrival order (overlap of a pair seen with two spacings, H6)"""
+    from oracle_lib import reference_file_digest, table_digest, write_fasta
+    bases, offsets = workloads.as_pair(workloads.coverage_reads(genome_len=60000, n_reads=60, len_min=9000, len_max=14000, error_ppm=3000))
+    fa = tmp_path / "reads.fa"
+    write_fasta(fa, bases, offsets)
+    for mode, k, w in (("collapse-msat", 501, 50), ("hpc", 63, 33)):
+        run = oracle.run(mode, k, w, (bases, offsets))
+        mine = table_digest(run.node_hash, run.node_cov, run.node_tip, run.edges)
+        _, ref1 = reference_file_digest(mode, k, w, fa, 1)
+        assert mine == ref1, (mode, mine, ref1)
+        _, ref4 = reference_file_digest(mode, k, w, fa, 4)
+        for f in ("selected", "distinct", "distinct_edges", "node_xor", "node_sum", "edge_cov", "edge_sum", "edge_xor"):
+            assert mine[f] == ref4[f], (mode, f)
+    # and it notices a single changed coverage or a flipped edge orientation
+    cov = run.node_cov.copy(); cov[3] += 1
+    assert table_digest(run.node_hash, cov, run.node_tip, run.edges)["node_xor"] != mine["node_xor"]
+    e = run.edges.copy(); e[0, 1] ^= 1
+    assert table_digest(run.node_hash, run.node_cov, run.node_tip, e)["edge_sum"] != mine["edge_sum"]
