@@ -131,6 +131,38 @@ def make_reads(wl, world, rank, scale, pinned_alloc=None, max_reads=None):
     return bases, offsets, buf
 
 
+def sample_size(wl):
+    """reads of the bounded sample both arms push through the reference: ~25 s of CPU work at the producer-bound rate of
+    the reference's reader thread, at most 20 000 reads (the first reads of rank 0's shard of the workload)"""
+    cores = os.cpu_count() or 1
+    est_rate = 25e6 * min(cores, 8)
+    return max(64, int(min(est_rate * 25.0 / ((wl["len_min"] + wl["len_max"]) / 2), 20000)))
+
+
+DETERMINISTIC = ("selected", "distinct", "distinct_edges", "node_xor", "node_sum", "edge_cov", "edge_sum", "edge_xor")
+
+
+def write_sample_fasta(path, bases, offsets):
+    with open(path, "wb") as f:
+        for i in range(len(offsets) - 1):
+            f.write(b">r%d\n" % i)
+            f.write(bases[int(offsets[i]):int(offsets[i + 1])].tobytes())
+            f.write(b"\n")
+
+
+def quiet_reference(fn):
+    """the reference prints progress on stderr; keep it out of the bench output"""
+    devnull = os.open(os.devnull, os.O_WRONLY)
+    saved = os.dup(2)
+    os.dup2(devnull, 2)
+    try:
+        return fn()
+    finally:
+        os.dup2(saved, 2)
+        os.close(devnull)
+        os.close(saved)
+
+
 def reference_arm(args, wl):
     """the reference's own CPU implementation of the path on all host cores, on a bounded sample of the workload"""
     rank = int(os.environ.get("RANK", "0"))
@@ -140,40 +172,22 @@ def reference_arm(args, wl):
     import ctypes as C
     from oracle_lib import REF_SO, Oracle, have_reference
     cores = os.cpu_count() or 1
-    budget_s = 25.0
-    # sample size: ~25 s of work at ~25 Mbase/s per core, capped by the producer-bound scaling of the reference
-    est_rate = 25e6 * min(cores, 8)
-    sample_reads = max(64, int(min(est_rate * budget_s / ((wl["len_min"] + wl["len_max"]) / 2), 20000)))
-    bases, offsets, _ = make_reads(wl, 1, 0, args.scale, max_reads=sample_reads)
+    bases, offsets, _ = make_reads(wl, 1, 0, args.scale, max_reads=sample_size(wl))
     n_reads = len(offsets) - 1
     n_bases = int(offsets[-1])
     times = []
+    digest = None
     if have_reference():
+        from oracle_lib import reference_file_digest
         kind = "reference"
-        lib = C.CDLL(REF_SO)
-        lib.refshim_time_file.restype = C.c_double
-        lib.refshim_time_file.argtypes = [C.c_int, C.c_uint64, C.c_uint64, C.c_char_p, C.c_uint64, C.c_void_p, C.c_void_p]
         with tempfile.TemporaryDirectory() as d:
             fa = os.path.join(d, "sample.fa")
-            with open(fa, "wb") as f:
-                for i in range(n_reads):
-                    f.write(b">r%d\n" % i)
-                    f.write(bases[int(offsets[i]):int(offsets[i + 1])].tobytes())
-                    f.write(b"\n")
-            sel, dist = C.c_uint64(), C.c_uint64()
+            write_sample_fasta(fa, bases, offsets)
             for it in range(args.warmup + args.steps):
-                devnull = os.open(os.devnull, os.O_WRONLY)
-                saved = os.dup(2)
-                os.dup2(devnull, 2)
-                try:
-                    t = lib.refshim_time_file(6, wl["k"], wl["w"], fa.encode(), cores, C.byref(sel), C.byref(dist))
-                finally:
-                    os.dup2(saved, 2)
-                    os.close(devnull)
-                    os.close(saved)
+                t, digest = quiet_reference(lambda: reference_file_digest("collapse-msat", wl["k"], wl["w"], fa, cores))
                 if it >= args.warmup:
                     times.append(t)
-            selected = sel.value
+            selected = digest["selected"]
     else:
         kind, cores = "port", 1
         orc = Oracle()
@@ -183,6 +197,8 @@ def reference_arm(args, wl):
             if it >= args.warmup:
                 times.append(time.time() - t0)
         selected = len(r.positions)
+        from oracle_lib import table_digest
+        digest = table_digest(r.node_hash, r.node_cov, r.node_tip, r.edges)
     sec = float(np.mean(times))
     value = n_bases / sec
     sample = f"{n_reads} reads / {n_bases} bases of the workload (FASTA file, page cache warm), {cores} worker threads + reader, loadReadsAsHashesMultithread"
@@ -194,46 +210,47 @@ def reference_arm(args, wl):
         "cpu_baseline": {"value": value, "unit": "bases/s", "cores": cores, "kind": kind, "sample": sample},
         "e2e": {"value": value, "unit": "bases/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
+        # order-free digest of the table the reference built from the sample (oracle/ref_shim.cpp:hashlist_digest); the GPU arm
+        # prints the digest of ITS table of the same reads under the same key
+        "sample_digest": {f: digest[f] for f in DETERMINISTIC},
     }
     emit(json.dumps(line))      # stdout proper (fd 1 itself points at stderr during the run, see main)
 
 
-def cpu_baseline(wl, scale):
-    """bounded sample (about 10-30 s of CPU work) of the same workload through the reference's own code"""
+def cpu_baseline(wl, scale, device=0):
+    """the bounded sample (the one `--impl reference` times) through the reference's own code on the host cores, and --
+    parity at bench size -- the same reads through the CUDA path: the two tables must have the same order-free digest
+    (selected, distinct k-mers and edges, XOR / sum of canonical hashes x coverage; tests/oracle_lib.py:table_digest)"""
     sys.path.insert(0, os.path.join(ROOT, "tests"))
-    import ctypes as C
-    from oracle_lib import REF_SO, Oracle, have_reference
+    from oracle_lib import Oracle, have_reference, reference_file_digest, table_digest
+    from verkko_b200 import MbgFrontEnd
     cores = os.cpu_count() or 1
-    sample_reads = 3000 if have_reference() else 300
-    bases, offsets, _ = make_reads(wl, 1, 0, scale, max_reads=sample_reads)
+    bases, offsets, _ = make_reads(wl, 1, 0, scale, max_reads=sample_size(wl) if have_reference() else 300)
     n_reads, n_bases = len(offsets) - 1, int(offsets[-1])
     if have_reference():
-        lib = C.CDLL(REF_SO)
-        lib.refshim_time_file.restype = C.c_double
-        lib.refshim_time_file.argtypes = [C.c_int, C.c_uint64, C.c_uint64, C.c_char_p, C.c_uint64, C.c_void_p, C.c_void_p]
         with tempfile.TemporaryDirectory() as d:
             fa = os.path.join(d, "sample.fa")
-            with open(fa, "wb") as f:
-                for i in range(n_reads):
-                    f.write(b">r%d\n" % i + bases[int(offsets[i]):int(offsets[i + 1])].tobytes() + b"\n")
-            devnull = os.open(os.devnull, os.O_WRONLY)
-            saved = os.dup(2)
-            os.dup2(devnull, 2)
-            try:
-                lib.refshim_time_file(6, wl["k"], wl["w"], fa.encode(), cores, None, None)       # warm
-                t = lib.refshim_time_file(6, wl["k"], wl["w"], fa.encode(), cores, None, None)
-            finally:
-                os.dup2(saved, 2)
-                os.close(devnull)
-                os.close(saved)
-        return {"value": n_bases / t, "unit": "bases/s", "cores": cores, "kind": "reference",
-                "sample": f"{n_reads} reads / {n_bases} bases of the workload, MBG's loadReadsAsHashesMultithread with {cores} worker threads (oracle/_ref)"}
-    orc = Oracle()
-    t0 = time.time()
-    orc.run("collapse-msat", wl["k"], wl["w"], (bases, offsets))
-    t = time.time() - t0
-    return {"value": n_bases / t, "unit": "bases/s", "cores": 1, "kind": "port",
-            "sample": f"{n_reads} reads / {n_bases} bases of the workload, oracle/mbg_oracle.c single thread"}
+            write_sample_fasta(fa, bases, offsets)
+            t, ref = quiet_reference(lambda: reference_file_digest("collapse-msat", wl["k"], wl["w"], fa, cores))
+        out = {"value": n_bases / t, "unit": "bases/s", "cores": cores, "kind": "reference",
+               "sample": f"{n_reads} reads / {n_bases} bases of the workload, MBG's loadReadsAsHashesMultithread with {cores} worker threads (oracle/_ref)"}
+    else:
+        orc = Oracle()
+        t0 = time.time()
+        r = orc.run("collapse-msat", wl["k"], wl["w"], (bases, offsets))
+        t = time.time() - t0
+        ref = table_digest(r.node_hash, r.node_cov, r.node_tip, r.edges)
+        out = {"value": n_bases / t, "unit": "bases/s", "cores": 1, "kind": "port",
+               "sample": f"{n_reads} reads / {n_bases} bases of the workload, oracle/mbg_oracle.c single thread"}
+    fe = MbgFrontEnd(wl["k"], wl["w"], "collapse-msat", device=device)
+    try:
+        fe.add_reads(bases, offsets)
+        fe.run()
+        mine = table_digest(fe.node_hashes(copy=False), fe.node_coverage(copy=False), fe.node_tip(copy=False), fe.edges(copy=False))
+    finally:
+        fe.close()
+    bad = [f for f in DETERMINISTIC if mine[f] != ref[f]]
+    return out, {f: mine[f] for f in DETERMINISTIC}, bad
 
 
 def main():
@@ -451,7 +468,11 @@ def main():
             # dram__bytes_read.sum + dram__bytes_write.sum of one launch, from the committed `ncu --set full` capture of this workload
             line["roofline"]["traffic"] = json.load(open(traffic_file)).get(dominant)
         if world == 1 and not args.no_cpu_baseline:
-            line["cpu_baseline"] = cpu_baseline(wl, args.scale)
+            line["cpu_baseline"], line["sample_digest"], bad = cpu_baseline(wl, args.scale, local_rank)
+            line["parity_sample"] = "ok" if not bad else "MISMATCH in " + ",".join(bad)
+            if bad:
+                emit(json.dumps(line))
+                raise SystemExit("bench: the CUDA path and the reference disagree on the sample: " + ",".join(bad))
         emit(json.dumps(line))
     if world > 1:
         dist.barrier()
