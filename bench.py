@@ -271,6 +271,7 @@ def main():
     ap.add_argument("--scale", type=float, default=1.0, help="shrink the genome (and read count) for quick runs")
     ap.add_argument("--e2e-steps", type=int, default=0, help="timed end-to-end steps (0 = --steps)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-file", action="store_true", help="skip the from-a-file end-to-end leg (e2e_file)")
     ap.add_argument("--k", type=int, default=0, help="k-mer size override (BASELINE.json configs[4]: the k/w sweep)")
     ap.add_argument("--w", type=int, default=0, help="window size override")
     args = ap.parse_args()
@@ -391,6 +392,60 @@ def main():
                 e2e_parts[name] = e2e_parts.get(name, 0.0) + dt * 1e3 / args.e2e_steps
         st_e = fe.stats()
         h2d, d2h = st_up["h2d_bytes"], st_e["d2h_bytes"]
+    # ---- end to end FROM A FILE (row a1 inside the timed region, as in the reference arm, which parses its FASTA while it
+    # runs): mbgfe_add_file + mbgfe_run on the FASTA of this rank's reads (page cache warm, as for the reference) -> ordered table
+    # in host memory.  Plain FASTA goes through the streaming loader (pread + scan + 2-bit packing on worker threads, parse ==
+    # pack); a .gz is inflated by zlib on one thread, which is then the bound (measured on a bounded sample).
+    e2e_file = None
+    if world == 1 and not args.no_file:
+        import gzip
+        import shutil
+        tmp_root = "/dev/shm" if os.path.isdir("/dev/shm") and shutil.disk_usage("/dev/shm").free > 3 * n_bases else None
+        with tempfile.TemporaryDirectory(dir=tmp_root) as d:
+            fa = os.path.join(d, "reads.fasta")
+            write_sample_fasta(fa, bases, offsets)
+            file_bytes = os.path.getsize(fa)
+            with open(fa, "rb") as f:              # warm the page cache the way a just-written corrected-read file is
+                while f.read(1 << 26):
+                    pass
+            ms_file = []
+            for it in range(1 + args.e2e_steps):
+                barrier()
+                t0 = time.time()
+                fe.reset()
+                fe.add_file(fa)
+                fe.run()
+                cov = fe.node_coverage(copy=False)
+                hashes = fe.node_hashes(copy=False)
+                edges = fe.edges(copy=False)
+                checksum_file = int(cov[::1024].sum(dtype=np.uint64)) + len(hashes) + len(edges)
+                barrier()
+                if it > 0:
+                    ms_file.append((time.time() - t0) * 1e3)
+            st_f = fe.stats()
+            e2e_file = {"value": n_bases / (float(np.mean(ms_file)) * 1e-3), "unit": "bases/s", "ms_per_step": float(np.mean(ms_file)), "file_bytes": file_bytes,
+                        "h2d_bytes_per_step": int(st_f["h2d_bytes"]), "d2h_bytes_per_step": int(st_f["d2h_bytes"]), "checksum": checksum_file,
+                        "same_table_as_e2e": bool(checksum_file == checksum), "input": "plain FASTA, one sequence line per read, page cache warm"}
+            # .gz on a bounded sample (zlib inflate on one thread is the bound, as it is for the reference's zstr reader)
+            n_gz = min(len(offsets) - 1, 3000)
+            gz = os.path.join(d, "sample.fasta.gz")
+            with gzip.open(gz, "wb", compresslevel=1) as f:
+                for i in range(n_gz):
+                    f.write(b">r%d\n" % i + bases[int(offsets[i]):int(offsets[i + 1])].tobytes() + b"\n")
+            gz_bases = int(offsets[n_gz])
+            ms_gz = []
+            for it in range(2):
+                t0 = time.time()
+                fe.reset()
+                fe.add_file(gz)
+                fe.run()
+                fe.node_coverage(copy=False)
+                fe.edges(copy=False)
+                ms_gz.append((time.time() - t0) * 1e3)
+            e2e_file["gz"] = {"value": gz_bases / (min(ms_gz) * 1e-3), "unit": "bases/s", "sample": f"{n_gz} reads / {gz_bases} bases, gzip -1", "bound": "zlib inflate, one thread"}
+            fe.reset()
+            fe.add_reads(bases, offsets)          # back to the full in-memory batch for the stages below (untimed)
+            fe.run()
     # ---- the step after the table (rows a14 / f1), outside the timed regions: abundance filter + unitig chains on the device
     unitig_info = None
     if world == 1 and not sharded:
@@ -461,6 +516,8 @@ def main():
                                      "k_insert_nodes": "DRAM sectors + atomics (random 32-byte slots)", "k_insert_edges": "DRAM sectors + atomics (random 32-byte slots)"},
                          "all_kernels_GBps": {n: (b / (m * 1e-3) / 1e9 if m > 0 else None) for n, (b, m) in alg.items()}},
         }
+        if e2e_file:
+            line["e2e_file"] = e2e_file
         if unitig_info:
             line["unitig_stage"] = unitig_info
         traffic_file = os.path.join(ROOT, "profiles", "ncu_traffic.json")

@@ -114,7 +114,17 @@ enum {
 	MBGFE_INST_STEP = 21,       /* uint8_t[]  what iterateReadPaths does at this k-mer, see mbgfe_thread_reads             */
 	/* after mbgfe_thin_unitigs(): one entry per filtered node */
 	MBGFE_F_NODE_THIN = 22,     /* uint8_t[]  1 when filterKmersToUnitigKmers keeps the k-mer                             */
-	MBGFE_F_NODE_UNITIG_OFFSET = 23 /* uint32_t[] start of the k-mer inside its unitig, in codes (currentPos of that walk)  */
+	MBGFE_F_NODE_UNITIG_OFFSET = 23,/* uint32_t[] start of the k-mer inside its unitig, in codes (currentPos of that walk)  */
+	/* the thinning applied (MBG/MBG.cpp:1166-1184): the HashList after reads.filter(kept), ids = ranks among the k-mers that stay */
+	MBGFE_T_NODE_HASHES = 24,   /* mbgfe_hash128[]                                                                    */
+	MBGFE_T_NODE_COVERAGE = 25, /* uint32_t[]                                                                         */
+	MBGFE_T_NODE_TIP = 26,      /* uint8_t[]                                                                          */
+	MBGFE_T_EDGES = 27,         /* mbgfe_edge[] edges (coverage + sequence overlap) between k-mers that stay, renumbered */
+	MBGFE_T_UNITIG_BEGIN = 28,  /* uint64_t[n_unitigs + 1] the unitigs of MBGFE_UNITIG_*, thinned                       */
+	MBGFE_T_UNITIG_NODES = 29,  /* uint32_t[] 2 * thinned node id + fw                                                 */
+	MBGFE_T_NEW_OVERLAPS = 30   /* mbgfe_edge[] one per pair of neighbours of a thinned unitig, canon() form, coverage 0:
+	                               the (from, to, overlap) triples the reference hands to addSequenceOverlap (MBG.cpp:1178-1183),
+	                               which replace the overlap an edge of MBGFE_T_EDGES may hold for the same pair             */
 };
 
 typedef struct {
@@ -217,15 +227,17 @@ int mbgfe_build_unitigs_ex(mbgfe* h, uint32_t kmer_abundance, double unitig_abun
  *   5  first k-mer of the next unitig: path gets MBGFE_INST_UNITIG (KmerMatcher.h:105-120)
  * A ReadPath is a run 2|3, (4|5)*; path = MBGFE_INST_UNITIG of its 2|3|5 entries, readPoses = MBGFE_POSITIONS of all its
  * entries, leftClip = MBGFE_INST_UNITIG_POS of the first, rightClip = MBGFE_INST_UNITIG_REST of the last.
- * Unitigs are numbered as mbgfe_build_unitigs numbers them.  world == 1. */
+ * Unitigs are numbered as mbgfe_build_unitigs numbers them.  world == 1.
+ * After mbgfe_thin_unitigs() the reads are threaded through the THINNED list, which is what runMBG does by default (pass 4 follows
+ * filterKmersToUnitigKmers, MBG/MBG.cpp:1580-1586): k-mers the thinning dropped are step 0, positions and clips count the k-mers
+ * that stay (MBGFE_T_UNITIG_*), and neighbours of a thinned unitig are tested against their new overlap (KmerMatcher.h:71). */
 int mbgfe_thread_reads(mbgfe* h);
 
 /* filterKmersToUnitigKmers (MBG/MBG.cpp:1065-1185) with filterWithinUnitig = true, MBG's default: inside a unitig only its
  * two ends, tip k-mers and the k-mers needed to keep neighbours overlapping stay.  Computes, for the unitigs of the last
  * mbgfe_build_unitigs[_ex], MBGFE_F_NODE_THIN (the RankBitvector `kept` of that function) and MBGFE_F_NODE_UNITIG_OFFSET (two
- * neighbours of the thinned unitig overlap by k minus the difference of their offsets: the newOverlaps of MBG.cpp:1136-1141).
- * The reference applies them with reads.filter(kept) + addSequenceOverlap (MBG.cpp:1176-1184); that last renumbering is
- * still the caller's. */
+ * neighbours of the thinned unitig overlap by k minus the difference of their offsets: the newOverlaps of MBG.cpp:1136-1141),
+ * and applies them the way the reference does (reads.filter(kept), renumbered unitigs, MBG.cpp:1166-1177): MBGFE_T_*. */
 int mbgfe_thin_unitigs(mbgfe* h);
 
 /* Device-side stopwatch on the library's stream (CUDA events): start, any number of calls, stop -> milliseconds. */

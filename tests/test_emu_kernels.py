@@ -187,15 +187,6 @@ def test_emulated_unitig_kmer_thinning(oracle, emu_library):
     assert check_thinning(ug, thin, off, want, 301, "emu thinning") > 10 and thin.sum() < len(thin)
 
 
-def test_emulated_hash_in_groups(oracle, emu_library, monkeypatch):
-    """k_kmer_hash_lanes with a staging area much smaller than a read: k-mers are hashed in groups of consecutive ones"""
-    monkeypatch.setenv("MBGFE_HASH_LANES", "1")
-    monkeypatch.setenv("MBGFE_HASH_CAP", "400")
-    reads = workloads.coverage_reads(n_reads=6)
-    compare_runs(run_frontend("collapse-msat", 301, 30, reads, library=emu_library), oracle.run("collapse-msat", 301, 30, reads), what="emu grouped hash")
-    compare_runs(run_frontend("hpc", 63, 33, reads, library=emu_library), oracle.run("hpc", 63, 33, reads), what="emu grouped hash hpc")
-
-
 @pytest.mark.parametrize("pct,mode,k,w", [("100", "hpc", 63, 33), ("50", "collapse-msat", 301, 30)])
 def test_emulated_host_packed_pieces(oracle, emu_library, monkeypatch, pct, mode, k, w):
     """the two upload routes of mbgfe_run (ASCII + K0 on the device, 2-bit packing on host threads) mixed piece by piece,

@@ -1,0 +1,141 @@
+"""Row a1 (MBG/fastqloader.h:38-147): the streaming FASTA loader of mbgfe_run -- pread + scan + 2-bit packing in one pass on
+worker threads, record structure stitched from the scan events, the device image in file coordinates -- against the oracle fed
+the reads the reference's parser would hand over.  The CPU half runs on the GPU-less emulator build (host logic is the same
+code); the GPU half runs the real library."""
+import os
+
+import numpy as np
+import pytest
+
+import workloads
+from oracle_lib import compare_runs, lcg_bases
+from verkko_b200.frontend import KEEP_CODES, KEEP_POSES, MbgFrontEnd
+
+
+def reference_parse(data):
+    """streamFastqFastaFromStream (MBG/fastqloader.h:38-80) restated: names and upper-cased sequences"""
+    names, seqs = [], []
+    lines = data.split(b"\n")
+    i, n = 0, len(lines)
+    if data.endswith(b"\n"):
+        n -= 1                       # getline on the trailing newline yields no further line
+    cur = None
+    while i < n:
+        line = lines[i]
+        i += 1
+        if len(line) == 0:
+            continue
+        if line[:1] == b">":
+            if line.endswith(b"\r"):
+                line = line[:-1]
+            names.append(line[1:].decode())
+            seqs.append(b"")
+            cur = len(seqs) - 1
+            continue
+        if cur is None:
+            continue
+        if line.endswith(b"\r"):
+            line = line[:-1]
+        seqs[cur] += line.upper()
+    return names, seqs
+
+
+def run_file(paths, mode, k, w, library=None, **kw):
+    from oracle_lib import RunResult
+    fe = MbgFrontEnd(k, w, mode, flags=KEEP_CODES | KEEP_POSES, library=library, **kw)
+    try:
+        for p in paths:
+            fe.add_file(str(p))
+        fe.run()
+        res = RunResult(parts=fe.parts(), codes=fe.codes(), poses=fe.poses(), positions=fe.positions(), hashes=fe.hashes(),
+                        node_hash=fe.node_hashes(), node_cov=fe.node_coverage(), node_tip=fe.node_tip(), edges=fe.edges())
+        res["stats"] = fe.stats()
+        res["names"] = [fe.read_name(i) for i in range(res["stats"]["reads"])]
+        return res
+    finally:
+        fe.close()
+
+
+def awkward_fasta():
+    """single-line records with everything the parser has rules for"""
+    a = workloads.read_a()
+    recs = [
+        (b"plain read", a[:9000]),
+        (b"crlf line\r", a[1000:7000] + b"\r"),
+        (b"lower case", a[2000:6000].lower()),
+        (b"with N", workloads.read_with_other_characters()),
+        (b"short", a[:31]),
+        (b"empty", None),
+        (b"thirty-two", a[:32]),
+        (b"cr inside", a[:3000] + b"\r" + a[3000:6000]),
+        (b"gt inside", a[:2500] + b">" + a[2500:5000]),
+        (b"last one without newline", a[5000:12000]),
+    ]
+    out = b"text before the first header\nACGTACGTACGTACGTACGTACGTACGTACGTACGTACGT\n\n"
+    for i, (name, seq) in enumerate(recs):
+        out += b">" + name + b"\n"
+        if seq is not None:
+            out += seq
+            if i + 1 < len(recs):
+                out += b"\n"
+        if i % 3 == 0:
+            out += b"\n"            # empty lines between records
+    return out
+
+
+def check_against_oracle(oracle, got, datas, mode, k, w, what):
+    names, seqs = [], []
+    for d in datas:
+        n, s = reference_parse(d)
+        names += n
+        seqs += s
+    want = oracle.run(mode, k, w, seqs)
+    compare_runs(got, want, what=what)
+    assert got["names"] == names, what
+    assert got["stats"]["reads"] == len(seqs) and got["stats"]["raw_bases"] == sum(len(s) for s in seqs)
+
+
+@pytest.mark.parametrize("piece", [0, 1024, 96])
+def test_emulated_streaming_fasta(oracle, emu_library, tmp_path, piece):
+    data = awkward_fasta()
+    fa = tmp_path / "awkward.fa"
+    fa.write_bytes(data)
+    second = b">r0\n" + lcg_bases(3, 5000) + b"\n>r1 x\n" + lcg_bases(4, 4000).lower() + b"\n"
+    fb = tmp_path / "second.fasta"
+    fb.write_bytes(second)
+    for mode, k, w in (("collapse-msat", 301, 30), ("hpc", 63, 33)):
+        got = run_file([fa, fb], mode, k, w, library=emu_library, piece_bytes=piece)
+        check_against_oracle(oracle, got, [data, second], mode, k, w, f"streaming loader piece={piece} {mode}")
+        assert got["stats"]["h2d_bytes"] < (len(data) + len(second)) // 3, "the bus must carry packed bases, not the file"
+
+
+def test_emulated_streaming_fasta_falls_back_on_multiline(oracle, emu_library, tmp_path):
+    a = workloads.read_a()
+    data = b">one\n" + a[:5000] + b"\n>two\n" + b"\n".join(a[5000 + i:5000 + i + 70] for i in range(0, 4000, 70)) + b"\n>three\n" + a[9000:15000] + b"\n"
+    fa = tmp_path / "multi.fa"
+    fa.write_bytes(data)
+    got = run_file([fa], "collapse-msat", 301, 30, library=emu_library, piece_bytes=2048)
+    check_against_oracle(oracle, got, [data], "collapse-msat", 301, 30, "multi-line fallback")
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("piece", [0, 1 << 16, 4096])
+def test_streaming_fasta_on_gpu(oracle, tmp_path, piece):
+    from verkko_b200 import synth
+    g = synth.genome(7, 300000)
+    bases, offsets = synth.reads(11, g, 400, 11000, 19000, 1000)
+    from oracle_lib import write_fasta
+    fa = tmp_path / "reads.fa"
+    write_fasta(fa, bases, offsets)
+    data = awkward_fasta()
+    fb = tmp_path / "awkward.fasta"
+    fb.write_bytes(data)
+    got = run_file([fa, fb], "collapse-msat", 1001, 100, piece_bytes=piece)
+    check_against_oracle(oracle, got, [fa.read_bytes(), data], "collapse-msat", 1001, 100, f"gpu streaming piece={piece}")
+    # the same through the plain parser (MBGFE_FILE_LEGACY): identical arrays
+    os.environ["MBGFE_FILE_LEGACY"] = "1"
+    try:
+        plain = run_file([fa, fb], "collapse-msat", 1001, 100)
+    finally:
+        del os.environ["MBGFE_FILE_LEGACY"]
+    compare_runs(got, plain, what="streaming vs plain parser")

@@ -378,18 +378,6 @@ def test_unitig_filter_properties_at_scale():
 
 
 @pytest.mark.gpu
-@pytest.mark.parametrize("cap", ["", "700"])
-def test_lane_per_kmer_hash_kernel(oracle, monkeypatch, cap):
-    """the alternative k-mer hash kernel (MBGFE_HASH_LANES=1), whole reads and groups of k-mers"""
-    monkeypatch.setenv("MBGFE_HASH_LANES", "1")
-    if cap:
-        monkeypatch.setenv("MBGFE_HASH_CAP", cap)
-    reads = workloads.coverage_reads(n_reads=12)
-    for mode, k, w in (("collapse-msat", 1001, 100), ("hpc", 63, 33), ("no", 255, 225)):
-        compare_runs(run_frontend(mode, k, w, reads), oracle.run(mode, k, w, reads), what=f"lanes hash {mode} k={k}")
-
-
-@pytest.mark.gpu
 @pytest.mark.parametrize("pct", ["100", "70", "0"])
 def test_host_packed_upload_pieces(oracle, monkeypatch, pct):
     """the two upload routes of mbgfe_run mixed piece by piece (ASCII + K0 on the device / 2-bit packing on host threads),

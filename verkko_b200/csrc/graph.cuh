@@ -354,9 +354,12 @@ __global__ void __launch_bounds__(256) k_invert_orig(const uint32_t* __restrict_
 	for (uint64_t j = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; j < n_kept; j += (uint64_t)gridDim.x * blockDim.x) final_of[orig[j]] = (uint32_t)j;
 }
 
+// thin != nullptr: the list is the one filterKmersToUnitigKmers leaves (MBG's default): k-mers it dropped are unknown to getNodeOrNull,
+// positions and sizes count the k-mers that stayed (node_tpos, tscan = scan of the marks over the unitig positions)
 __global__ void __launch_bounds__(256) k_thread_locate(const uint32_t* __restrict__ inst_slot, const uint64_t* __restrict__ inst_hash, uint64_t n_inst, const NodeSlot* __restrict__ table,
 	const uint32_t* __restrict__ final_of, const uint32_t* __restrict__ node_unitig, const uint32_t* __restrict__ node_ufw, const uint32_t* __restrict__ node_upos,
-	const uint64_t* __restrict__ unitig_begin, uint32_t* __restrict__ inst_node, uint32_t* __restrict__ inst_unitig, uint32_t* __restrict__ inst_upos, uint32_t* __restrict__ inst_urest)
+	const uint64_t* __restrict__ unitig_begin, const uint8_t* __restrict__ thin, const uint32_t* __restrict__ node_tpos, const uint64_t* __restrict__ tscan,
+	uint32_t* __restrict__ inst_node, uint32_t* __restrict__ inst_unitig, uint32_t* __restrict__ inst_upos, uint32_t* __restrict__ inst_urest)
 {
 	for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n_inst; i += (uint64_t)gridDim.x * blockDim.x)
 	{
@@ -365,7 +368,7 @@ __global__ void __launch_bounds__(256) k_thread_locate(const uint32_t* __restric
 		if (slot != NO_LINK)
 		{
 			const uint32_t fid = final_of[(uint32_t)table[slot].rank];       // getNodeOrNull (MBG/HashList.cpp:85-101) on the filtered list
-			if (fid != NO_LINK)
+			if (fid != NO_LINK && (!thin || thin[fid]))
 			{
 				const uint64_t lo = inst_hash[2 * i], hi = inst_hash[2 * i + 1];
 				uint64_t key_lo, key_hi; uint32_t fw;
@@ -374,9 +377,9 @@ __global__ void __launch_bounds__(256) k_thread_locate(const uint32_t* __restric
 				const uint32_t u = node_unitig[fid];
 				if (u != NO_LINK)
 				{
-					const uint32_t size = (uint32_t)(unitig_begin[u + 1] - unitig_begin[u]);
+					const uint32_t size = thin ? (uint32_t)(tscan[unitig_begin[u + 1]] - tscan[unitig_begin[u]]) : (uint32_t)(unitig_begin[u + 1] - unitig_begin[u]);
 					const uint32_t o = node_ufw[fid] == fw ? 1u : 0u;
-					const uint32_t j = node_upos[fid];
+					const uint32_t j = thin ? node_tpos[fid] : node_upos[fid];
 					unitig = 2 * u + o;
 					upos = o ? j : size - 1 - j;
 					urest = size - 1 - upos;
@@ -402,8 +405,12 @@ __device__ __forceinline__ bool edge_lookup(const EdgeSlot* __restrict__ table, 
 
 __global__ void __launch_bounds__(256) k_thread_steps(const uint32_t* __restrict__ inst_node, const uint32_t* __restrict__ inst_unitig, const uint32_t* __restrict__ inst_upos,
 	const uint32_t* __restrict__ inst_urest, const uint8_t* __restrict__ inst_flag, const uint32_t* __restrict__ inst_pos, const uint32_t* __restrict__ inst_slot,
-	const uint64_t* __restrict__ inst_hash, uint64_t n_inst, const EdgeSlot* __restrict__ edge_table, uint64_t edge_mask, uint32_t k, uint32_t min_cov, uint8_t* __restrict__ step)
+	const uint64_t* __restrict__ inst_hash, uint64_t n_inst, const EdgeSlot* __restrict__ edge_table, uint64_t edge_mask, uint32_t k, uint32_t min_cov,
+	const uint32_t* __restrict__ node_off, uint8_t* __restrict__ step)
 {
+	// node_off != nullptr: thinned list.  Neighbours of a thinned unitig have the sequence overlap filterKmersToUnitigKmers gave them,
+	// k minus the distance of their starts inside the unitig (it replaces an older one of the same pair, HashList::addSequenceOverlap);
+	// every other pair has the overlap of its edge in the table, as before (edges between kept k-mers survive HashList::filter)
 	for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n_inst; i += (uint64_t)gridDim.x * blockDim.x)
 	{
 		uint32_t cls;
@@ -420,6 +427,14 @@ __global__ void __launch_bounds__(256) k_thread_steps(const uint32_t* __restrict
 			{
 				cls = 3;
 				uint32_t count = 0, overlap = 0;
+				if (node_off && inst_unitig[i] == inst_unitig[j] && inst_upos[i] == inst_upos[j] + 1)
+				{
+					const uint32_t oi = node_off[inst_node[i] >> 1], oj = node_off[inst_node[j] >> 1];
+					const uint32_t dist = oi > oj ? oi - oj : oj - oi;
+					if (inst_pos[i] - inst_pos[j] == dist) cls = 4;
+					step[i] = (uint8_t)cls;
+					continue;
+				}
 				const unsigned long long key = canonical_edge_key(inst_hash[2 * j], inst_hash[2 * j + 1], inst_hash[2 * i], inst_hash[2 * i + 1], inst_slot[j], inst_slot[i]);
 				if (edge_lookup(edge_table, edge_mask, key, count, overlap) && inst_pos[i] - inst_pos[j] == k - overlap)
 				{
@@ -501,6 +516,54 @@ __global__ void __launch_bounds__(256) k_thin_double(const uint32_t* __restrict_
 __global__ void __launch_bounds__(256) k_thin_flags(const uint32_t* __restrict__ unitig_nodes, uint64_t n_pos, const uint32_t* __restrict__ mark, uint8_t* __restrict__ thin)
 {
 	for (uint64_t p = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; p < n_pos; p += (uint64_t)gridDim.x * blockDim.x) thin[unitig_nodes[p] >> 1] = (uint8_t)mark[p];
+}
+
+
+// ---- applying the thinning (MBG/MBG.cpp:1166-1184): reads.filter(kept), the unitigs renumbered, and a sequence overlap for
+// every pair of neighbours of a thinned unitig.  tscan = exclusive scan of the marks over the unitig positions.
+__global__ void __launch_bounds__(256) k_thin_kept32(const uint8_t* __restrict__ thin, uint64_t n, uint32_t* __restrict__ kept32)
+{
+	for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (uint64_t)gridDim.x * blockDim.x) kept32[i] = thin[i] ? 1u : 0u;
+}
+
+// thinned position of every kept k-mer inside its unitig, and the thinned unitigs as flat arrays: nodes (new ids), offsets in codes
+// and the unitig each thinned position belongs to
+__global__ void __launch_bounds__(256) k_thin_compact(const uint32_t* __restrict__ unitig_nodes, uint64_t n_pos, const uint32_t* __restrict__ mark, const uint64_t* __restrict__ tscan,
+	const uint32_t* __restrict__ node_unitig, const uint64_t* __restrict__ unitig_begin, const uint64_t* __restrict__ newid, const uint32_t* __restrict__ node_off,
+	uint32_t* __restrict__ node_tpos, uint32_t* __restrict__ t_nodes, uint32_t* __restrict__ t_off, uint32_t* __restrict__ t_unitig)
+{
+	for (uint64_t p = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; p < n_pos; p += (uint64_t)gridDim.x * blockDim.x)
+	{
+		if (!mark[p]) continue;
+		const uint32_t x = unitig_nodes[p], fid = x >> 1;
+		const uint32_t u = node_unitig[fid];
+		const uint64_t tq = tscan[p];
+		node_tpos[fid] = (uint32_t)(tq - tscan[unitig_begin[u]]);
+		t_nodes[tq] = 2 * (uint32_t)newid[fid] + (x & 1);
+		t_off[tq] = node_off[fid];
+		t_unitig[tq] = u;
+	}
+}
+
+__global__ void __launch_bounds__(256) k_thin_begins(const uint64_t* __restrict__ unitig_begin, uint64_t n_unitigs, const uint64_t* __restrict__ tscan, uint64_t* __restrict__ t_begin)
+{
+	for (uint64_t u = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; u <= n_unitigs; u += (uint64_t)gridDim.x * blockDim.x) t_begin[u] = tscan[unitig_begin[u]];
+}
+
+// newOverlaps (MBG/MBG.cpp:1136-1141): neighbours of a thinned unitig overlap by k minus the distance of their starts; canon() form
+__global__ void __launch_bounds__(256) k_thin_overlaps(const uint32_t* __restrict__ t_nodes, const uint32_t* __restrict__ t_off, const uint32_t* __restrict__ t_unitig,
+	const uint64_t* __restrict__ t_begin, uint64_t n_tpos, uint32_t k, EdgeRec* __restrict__ out)
+{
+	for (uint64_t tq = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; tq < n_tpos; tq += (uint64_t)gridDim.x * blockDim.x)
+	{
+		const uint32_t u = t_unitig[tq];
+		if (tq == t_begin[u]) continue;
+		const uint32_t x = t_nodes[tq - 1], y = t_nodes[tq];
+		uint32_t from = x >> 1, ffw = x & 1, to = y >> 1, tfw = y & 1;
+		if (to < from || (to == from && !tfw && !ffw)) { const uint32_t a = from, b = ffw; from = to; ffw = !tfw; to = a; tfw = !b; }
+		EdgeRec r; r.from = from; r.from_fw = ffw; r.to = to; r.to_fw = tfw; r.coverage = 0; r.overlap = k - (t_off[tq] - t_off[tq - 1]);
+		out[tq - (u + 1)] = r;
+	}
 }
 
 }

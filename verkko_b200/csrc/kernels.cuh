@@ -403,14 +403,11 @@ __device__ __forceinline__ uint32_t spread6(uint32_t x)
 // floor(v / m) for m in 2..6 and v < 2^29 as one multiply-high by ceil(2^32 / m)
 __constant__ uint32_t RECIP32[8] = { 0, 0, 0x80000000u, 0x55555556u, 0x40000000u, 0x33333334u, 0x2aaaaaabu, 0 };
 
-// code of a run-length stretch (MBG/ErrorMaskHelper.cpp:107-127) and of its reverse complement (:43-73) from the
-// first m symbols of the stretch (planes, first symbol at bit 0) and its length: code = numBefore[m] + motif * m +
-// (len mod m), motif = the m symbols as base-4 digits, first symbol most significant.  Reverse complement: rotate the
-// motif left by the overhang, complement every digit, reverse the digit order -- which, on the little-endian digit
-// string the planes give directly, is just a digit rotation followed by XOR with all-ones.
-__device__ __forceinline__ void stretch_codes(Planes first, uint32_t m, uint32_t len, uint32_t& code, uint32_t& rc_code)
+// code of a run-length stretch (MBG/ErrorMaskHelper.cpp:107-127) from the first m symbols of the stretch (planes, first symbol
+// at bit 0) and its length: code = numBefore[m] + motif * m + (len mod m), motif = the m symbols as base-4 digits, first symbol
+// most significant.
+__device__ __forceinline__ uint32_t stretch_code(Planes first, uint32_t m, uint32_t len)
 {
-	const uint32_t mask = (1u << (2 * m)) - 1;
 	const uint32_t le = (spread6(first.lo & low_bits(m)) | (spread6(first.hi & low_bits(m)) << 1));   // digit j = symbol j
 #ifdef MBGFE_EMU_BUILD
 	uint32_t be = 0;
@@ -421,9 +418,7 @@ __device__ __forceinline__ void stretch_codes(Planes first, uint32_t m, uint32_t
 	const uint32_t be = ((y & 0xaaau) >> 1) | ((y & 0x555u) << 1);
 	const uint32_t oh = m > 1 ? len - __umulhi(len, RECIP32[m]) * m : 0;
 #endif
-	code = CODES_BEFORE[m] + be * m + oh;
-	const uint32_t rot = ((le >> (2 * oh)) | (le << (2 * (m - oh)))) & mask;   // oh == 0: le | le << 2m, masked = le
-	rc_code = CODES_BEFORE[m] + (rot ^ mask) * m + oh;
+	return CODES_BEFORE[m] + be * m + oh;
 }
 
 // K2: multiRLECompress (MBG/ErrorMaskHelper.cpp:169-342) in scan-parallel form (DESIGN.md "K2"; the sequential
@@ -440,9 +435,8 @@ __device__ __forceinline__ void stretch_codes(Planes first, uint32_t m, uint32_t
 // (the staging index is kept congruent to the output index mod 8) and leave as coalesced 128-bit stores; an unfinished
 // group of 8 is carried into the next tile.  A stretch is coded by the lane that owns the symbol after it; when its
 // slot was flushed by an earlier tile (stretches longer than a tile) the code goes to HBM directly.
-// The reverse-complement array rrc is written alongside (rrc[rr0 - i] = complement(code i)).
 // Segments with fewer than 32 symbols produce no part (MBG/ReadHelper.h:847,858,882,893): seg_c2 = 0.
-// Algorithmic bytes: 1/4 read per symbol + 2 written per code (+ 2 for rrc, + 4 per code when poses are requested).
+// Algorithmic bytes: 1/4 read per symbol + 2 written per code (+ 4 per code when poses are requested).
 #ifdef MBGFE_EMU_BUILD
 constexpr int MSAT_WARPS = 1;      // the emulator's warp primitives are CTA-wide barriers: one warp per CTA there
 #else
@@ -451,28 +445,24 @@ constexpr int MSAT_WARPS = 4;
 constexpr uint32_t MSAT_TILE = 1024, MSAT_STAGE = MSAT_TILE + 8;
 
 __global__ void __launch_bounds__(MSAT_WARPS * 32) k_msat(SegTable seg, const uint64_t* __restrict__ sym, const uint32_t* __restrict__ seg_c1,
-	uint16_t* __restrict__ codes, uint16_t* __restrict__ rrc, uint32_t* __restrict__ seg_c2, const uint32_t* __restrict__ pos1,
+	uint16_t* __restrict__ codes, uint32_t* __restrict__ seg_c2, const uint32_t* __restrict__ pos1,
 	uint32_t* __restrict__ pos2, uint32_t max_motif)
 {
 	__shared__ uint64_t s_words[MSAT_WARPS][36];                       // planar words tile_word0 - 1 .. tile_word0 + 34
 	__shared__ uint32_t s_cand[MSAT_WARPS][32 * 33];                   // per lane: (run end << 3) | (7 - motif) of its candidates, in position order
 	__align__(16) __shared__ uint16_t s_codes[MSAT_WARPS][MSAT_STAGE];
-	__align__(16) __shared__ uint16_t s_rrc[MSAT_WARPS][MSAT_STAGE];   // reversed: entry i of the stage at [MSAT_STAGE - 1 - i]
 	const uint32_t lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
 	const uint32_t g = blockIdx.x * MSAT_WARPS + wid;
 	if (g >= seg.n) return;
 	const uint32_t n = seg_c1[g];
 	if (n < 32) { if (lane == 0) seg_c2[g] = 0; return; }
 	const uint64_t out0 = seg.out_base[g];
-	const uint64_t rr0 = seg.out_base[g + 1] - 1;          // rrc[rr0 - i] = complement(code i): the reverse complement reads forwards
 	const uint64_t* __restrict__ s = sym + (out0 >> 5);   // segment-local words
 	uint16_t* __restrict__ codes_g = codes + out0;
-	uint16_t* __restrict__ rrc_g = rrc + rr0;             // rrc_g[-i]
 	const uint32_t n_words = (n + 31) / 32;
 	uint64_t* tile_w = s_words[wid];
 	uint32_t* my_cand = s_cand[wid] + lane * 33;
 	uint16_t* st_c = s_codes[wid];
-	uint16_t* st_r = s_rrc[wid];
 	const uint32_t lt_mask = low_bits(lane);               // lanes below this one
 	uint32_t carry_max = 0;            // maximum run end over all candidates of earlier tiles
 	uint32_t carry_last_sm = 0, carry_last_pe = 0;   // latest emitted run so far: start | m << 29 (m == 0: none), end of the run emitted before it
@@ -651,7 +641,6 @@ __global__ void __launch_bounds__(MSAT_WARPS * 32) k_msat(SegTable seg, const ui
 				const uint32_t oi = idx + __popc(flags & low_bits(b));
 				const uint32_t sc = ((a0.lo >> b) & 1) | (((a0.hi >> b) & 1) << 1);
 				st_c[oi - base8] = (uint16_t)sc;
-				st_r[MSAT_STAGE - 1 - (oi - base8)] = (uint16_t)(3 - sc);
 				if (pos2) pos2[out0 + oi] = pos1 ? pos1[out0 + p0 + b] : p0 + b;
 			}
 			// ---- stretches of cover == 1 that end in this word: at a code start whose predecessor is covered once, or at n
@@ -679,10 +668,9 @@ __global__ void __launch_bounds__(MSAT_WARPS * 32) k_msat(SegTable seg, const ui
 				const uint32_t ps = max(cur_start, cur_pe);
 				const uint32_t slen = q - ps;
 				const uint32_t m = min(cur_m, slen);
-				uint32_t code, rc_code;
-				stretch_codes(win(ps), m, slen, code, rc_code);
-				if (oi >= base8) { st_c[oi - base8] = (uint16_t)code; st_r[MSAT_STAGE - 1 - (oi - base8)] = (uint16_t)rc_code; }
-				else { codes_g[oi] = (uint16_t)code; *(rrc_g - oi) = (uint16_t)rc_code; }     // its slot left with an earlier tile
+				const uint32_t code = stretch_code(win(ps), m, slen);
+				if (oi >= base8) st_c[oi - base8] = (uint16_t)code;
+				else codes_g[oi] = (uint16_t)code;     // its slot left with an earlier tile
 				if (pos2) pos2[out0 + oi] = pos1 ? pos1[out0 + ps] : ps;
 			}
 		}
@@ -695,13 +683,12 @@ __global__ void __launch_bounds__(MSAT_WARPS * 32) k_msat(SegTable seg, const ui
 			for (uint32_t gq = lane; gq < n_groups; gq += 32)
 			{
 				*(uint4*)(codes_g + base8 + 8 * gq) = *(const uint4*)(st_c + 8 * gq);
-				*(uint4*)(rrc_g - (base8 + 8 * gq + 7)) = *(const uint4*)(st_r + (MSAT_STAGE - 8 - 8 * gq));
 			}
 			const uint32_t keep = last ? 0 : filled - 8 * n_groups;
-			uint16_t kc = 0, kr = 0;
-			if (lane < keep) { kc = st_c[8 * n_groups + lane]; kr = st_r[MSAT_STAGE - 1 - (8 * n_groups + lane)]; }
+			uint16_t kc = 0;
+			if (lane < keep) kc = st_c[8 * n_groups + lane];
 			__syncwarp();
-			if (lane < keep) { st_c[lane] = kc; st_r[MSAT_STAGE - 1 - lane] = kr; }
+			if (lane < keep) st_c[lane] = kc;
 		}
 		carry_max = max(carry_max, tile_max);
 		if (has)
@@ -723,19 +710,17 @@ __global__ void __launch_bounds__(MSAT_WARPS * 32) k_msat(SegTable seg, const ui
 // modes without microsatellite coding: codes are the symbols themselves (2-bit -> uint16), poses are pos1
 template <int NT>
 __global__ void __launch_bounds__(NT) k_unpack_symbols(SegTable seg, const uint64_t* __restrict__ sym, const uint32_t* __restrict__ seg_c1,
-	uint16_t* __restrict__ codes, uint16_t* __restrict__ rrc, uint32_t* __restrict__ seg_c2, const uint32_t* __restrict__ pos1, uint32_t* __restrict__ pos2)
+	uint16_t* __restrict__ codes, uint32_t* __restrict__ seg_c2, const uint32_t* __restrict__ pos1, uint32_t* __restrict__ pos2)
 {
 	const uint32_t g = blockIdx.x;
 	if (g >= seg.n) return;
 	const uint32_t n = seg_c1[g];
 	const uint64_t out0 = seg.out_base[g];
-	const uint64_t rr0 = seg.out_base[g + 1] - 1;
 	const uint64_t* __restrict__ s = sym + (out0 >> 5);
 	for (uint32_t p = threadIdx.x; p < n; p += NT)
 	{
 		const uint32_t sc = symbol_at(s, p);
 		codes[out0 + p] = (uint16_t)sc;
-		rrc[rr0 - p] = (uint16_t)(3 - sc);
 		if (pos2) pos2[out0 + p] = pos1 ? pos1[out0 + p] : p;
 	}
 	if (threadIdx.x == 0)
@@ -1112,8 +1097,8 @@ struct Murmur
 };
 
 // K3b2: 128-bit k-mer hash (MBG/MBGCommon.cpp:25-35): low 64 bits = Murmur over the first (k+1)/2 codes of the k-mer,
-// high 64 bits = Murmur over the first (k+1)/2 codes of its reverse complement.  `rrc` holds every segment's
-// complemented codes in reverse order (written by K2), so both halves are the same forward walk over a code array.
+// high 64 bits = Murmur over the first (k+1)/2 codes of its reverse complement.  The reverse strand is the same code array
+// read backwards and complemented while it is staged, so both halves are the same forward walk over a staged stream.
 //
 // Murmur64A is h = (h ^ f(block)) * M with f (two of the three multiplications) independent of h, and the selected
 // k-mers of a read overlap heavily (one every ~w/2 codes, each (k+1)/2 codes long), so f is shared: one CTA per segment
@@ -1140,7 +1125,16 @@ __device__ __forceinline__ uint32_t lower_bound_u32(const uint32_t* p, uint32_t 
 	return lo;
 }
 
-__global__ void __launch_bounds__(HASH_NT) k_kmer_hash(const uint64_t* __restrict__ seg_out_base, const uint16_t* __restrict__ codes, const uint16_t* __restrict__ rrc,
+__device__ __forceinline__ uint32_t complement_pair_swapped(uint32_t wd, const uint16_t* __restrict__ tab_comp)
+{
+	// two codes in one word -> their complements, halves swapped (the reverse strand reads them in the other order).  Branch-free:
+	// the table holds plain bases too (3 - c), so every code is one clamped lookup (entries past the end of a part are whatever the
+	// slot held: never used by a chain, but they must not index past the table)
+	const uint32_t a = min(wd & 0xffffu, MAX_CODE - 1), b = min(wd >> 16, MAX_CODE - 1);
+	return ((uint32_t)__ldg(tab_comp + a) << 16) | (uint32_t)__ldg(tab_comp + b);
+}
+
+__global__ void __launch_bounds__(HASH_NT) k_kmer_hash(const uint64_t* __restrict__ seg_out_base, const uint16_t* __restrict__ codes, const uint16_t* __restrict__ tab_comp,
 	const uint32_t* __restrict__ inst_pos, const uint64_t* __restrict__ sel_begin, uint64_t inst_cap, uint64_t* __restrict__ inst_hash, uint32_t k)
 {
 	// seg_out_base and sel_begin are offset to the first segment of the launch; blockIdx.x = segment within it
@@ -1154,7 +1148,11 @@ __global__ void __launch_bounds__(HASH_NT) k_kmer_hash(const uint64_t* __restric
 	const uint32_t n_sel = (uint32_t)(end - begin);
 	const uint64_t ob = seg_out_base[g];
 	const uint32_t cap = (uint32_t)(seg_out_base[g + 1] - ob);
-	const uint16_t* __restrict__ arr[2] = { codes + ob, rrc + ob };     // forward codes; reverse-complement codes (k-mer at pos starts at cap - k - pos)
+	// Two streams over the segment's slot of `cap` codes: forward R0[x] = code[x]; reverse R1[x] = complement(code[cap - 1 - x]), in which
+	// the reverse complement of the k-mer at pos starts at cap - k - pos and reads forwards.  R1 is made on the fly while staging (cap is
+	// a multiple of 64, tiles start on multiples of 8: eight entries of R1 are one aligned 128-bit load of the code array, read backwards
+	// and complemented through tab_comp) -- round 1 kept a second code array for it (2 bytes written + 2 read per code).
+	const uint16_t* __restrict__ fwd = codes + ob;
 	const uint32_t* __restrict__ gpos = inst_pos + begin;
 	uint64_t* __restrict__ out = inst_hash + 2 * begin;
 	const uint32_t half = (k + 1) / 2;
@@ -1179,7 +1177,16 @@ __global__ void __launch_bounds__(HASH_NT) k_kmer_hash(const uint64_t* __restric
 			const uint32_t d = i >= HASH_TILE / 8 + 1 ? 1 : 0, q = i - d * (HASH_TILE / 8 + 1);
 			const uint32_t o = T0[d] + 8 * q;
 			uint4 v = make_uint4(0, 0, 0, 0);
-			if (o < cap) v = __ldg((const uint4*)(arr[d] + o));
+			if (o < cap)
+			{
+				if (d == 0) v = __ldg((const uint4*)(fwd + o));
+				else
+				{
+					const uint4 x = __ldg((const uint4*)(fwd + (cap - 8 - o)));
+					v = make_uint4(complement_pair_swapped(x.w, tab_comp), complement_pair_swapped(x.z, tab_comp), complement_pair_swapped(x.y, tab_comp),
+						complement_pair_swapped(x.x, tab_comp));
+				}
+			}
 			*(uint4*)(s_c[d] + 8 * q) = v;
 		}
 		// ---- warp 0 meanwhile finds the k-mers of the tile: forward starts in [T0f - reach, T0f + TILE), reverse starts
@@ -1247,7 +1254,12 @@ __global__ void __launch_bounds__(HASH_NT) k_kmer_hash(const uint64_t* __restric
 				if (rem)
 				{
 					uint64_t wd = 0;
-					for (uint32_t j = 0; j < rem; j++) wd |= (uint64_t)arr[d][st + 4 * nb + j] << (16 * j);
+					for (uint32_t j = 0; j < rem; j++)
+					{
+						const uint32_t x = st + 4 * nb + j;
+						const uint32_t cd = d == 0 ? fwd[x] : (uint32_t)__ldg(tab_comp + min((uint32_t)fwd[cap - 1 - x], MAX_CODE - 1));
+						wd |= (uint64_t)cd << (16 * j);
+					}
 					mm.tail(wd);
 				}
 				hcur = mm.finish();
@@ -1255,109 +1267,6 @@ __global__ void __launch_bounds__(HASH_NT) k_kmer_hash(const uint64_t* __restric
 			out[2 * i + d] = hcur;
 		}
 		__syncthreads();
-	}
-}
-
-// K3b2, lane-per-k-mer form (alternative, selected with MBGFE_HASH_LANES=1; same results, same speed on the bench).
-// The chain h = (h ^ f(block)) * M is a serial dependency of (k+1)/8 steps per k-mer and direction; k_kmer_hash above
-// shares f between overlapping k-mers but keeps only the ~90 k-mers of a tile in flight while everybody else waits at its
-// barriers, so it runs at the latency of that chain.  Here every thread is a chain all the time: a CTA of two warps
-// stages the codes its k-mers span (both directions, as aligned 64-bit pairs) in shared memory, then each lane walks one
-// (k-mer, direction) after the other, computing f itself -- three 64-bit multiplications per block instead of one and a
-// shared two, no barrier inside.  Measured (chr20 bench, ncu): 5.16 ms, the same as the tiled kernel, and bound by the
-// integer-multiply half of the fma pipe (sm__pipe_fmaheavy_cycles_active 79 %): a 64-bit product is 3 IMAD + 1 add, the
-// kernel does 11.7 G of them.  A read whose span exceeds the staging capacity is done in groups of consecutive k-mers.
-// cap_codes = staged codes per direction (multiple of 8); dynamic shared memory = 4 * cap_codes bytes.
-constexpr int HASHL_NT = 64;
-
-__global__ void __launch_bounds__(HASHL_NT) k_kmer_hash_lanes(const uint64_t* __restrict__ seg_out_base, const uint16_t* __restrict__ codes, const uint16_t* __restrict__ rrc,
-	const uint32_t* __restrict__ inst_pos, const uint64_t* __restrict__ sel_begin, uint64_t inst_cap, uint64_t* __restrict__ inst_hash, uint32_t k, uint32_t cap_codes)
-{
-	MBGFE_DYN_SMEM(smem_raw);
-	const uint32_t g = blockIdx.x;
-	const uint64_t begin = sel_begin[g], end = sel_begin[g + 1];
-	if (end <= begin || end > inst_cap) return;
-	const uint32_t n_sel = (uint32_t)(end - begin);
-	const uint64_t ob = seg_out_base[g];
-	const uint32_t cap = (uint32_t)(seg_out_base[g + 1] - ob);
-	const uint32_t* __restrict__ pos = inst_pos + begin;
-	uint64_t* __restrict__ out = inst_hash + 2 * begin;
-	const uint32_t half = (k + 1) / 2;
-	const uint32_t nb = half / 4, rem = half & 3;
-	uint64_t h_init;
-	{ Murmur mm; mm.init((uint64_t)half * 2); h_init = mm.h; }
-	uint2* const s_fw = (uint2*)smem_raw;                 // 4 codes per pair
-	uint2* const s_rc = s_fw + cap_codes / 4;
-	// positions a group may span: what fits, evened out over the groups the read needs (no short last group)
-	const uint32_t room_max = cap_codes - half - 16;
-	const uint32_t reach_all = pos[n_sel - 1] - pos[0] + 1;
-	const uint32_t n_groups = (reach_all + room_max - 1) / room_max;
-	const uint32_t room = min(room_max, (reach_all + n_groups - 1) / n_groups + 64);
-	uint32_t i0 = 0;
-	while (i0 < n_sel)
-	{
-		// ---- group [i0, i1): consecutive k-mers whose codes fit the staging area (every thread finds the same i1)
-		const uint32_t p0 = pos[i0];
-		uint32_t i1 = n_sel;
-		if (pos[n_sel - 1] - p0 > room)
-		{
-			uint32_t lo = i0 + 1, hi = n_sel;                // first index whose position is out of reach
-			while (lo < hi) { const uint32_t mid = (lo + hi) >> 1; if (pos[mid] - p0 > room) hi = mid; else lo = mid + 1; }
-			i1 = lo;
-		}
-		const uint32_t p1 = pos[i1 - 1];
-		// staged ranges start on a multiple of 8 codes (16 bytes): forward from p0, reverse from the start of the LAST k-mer
-		const uint32_t a0f = p0 & ~7u, a0r = (cap - k - p1) & ~7u;
-		const uint32_t n_stage = ((p1 - p0) + half + 16 + 7) >> 3;       // uint4 per direction
-		for (uint32_t q = threadIdx.x; q < 2 * n_stage; q += HASHL_NT)
-		{
-			const uint32_t d = q >= n_stage ? 1 : 0, j = q - d * n_stage;
-			const uint32_t o = (d ? a0r : a0f) + 8 * j;
-			uint4 v = make_uint4(0, 0, 0, 0);
-			if (o < cap) v = __ldg((const uint4*)((d ? rrc : codes) + ob + o));
-			*(uint4*)((d ? s_rc : s_fw) + 2 * j) = v;
-		}
-		__syncthreads();
-		// ---- chains: 2 * (i1 - i0) of them, lanes take them round robin (a warp's lanes: neighbouring k-mers, one direction)
-		const uint32_t n_chain = 2 * (i1 - i0);
-		for (uint32_t c = threadIdx.x; c < n_chain; c += HASHL_NT)
-		{
-			const uint32_t d = c >= (i1 - i0) ? 1 : 0;
-			const uint32_t i = i0 + c - d * (i1 - i0);
-			const uint32_t st = d ? cap - k - pos[i] : pos[i];
-			const uint32_t rel = st - (d ? a0r : a0f);
-			const uint2* __restrict__ pp = (d ? s_rc : s_fw) + (rel >> 2);
-			const bool wodd = (rel & 2) != 0;
-			const uint32_t sh = (rel & 1) * 16;
-			uint64_t hcur = h_init;
-			uint2 pa = pp[0];
-#pragma unroll 4
-			for (uint32_t t = 0; t < nb; t++)
-			{
-				const uint2 pb = pp[t + 1];
-				const uint32_t x0 = wodd ? pa.y : pa.x, x1 = wodd ? pb.x : pa.y, x2 = wodd ? pb.y : pb.x;
-#ifdef MBGFE_EMU_BUILD
-				const uint32_t lo = sh ? ((x0 >> 16) | (x1 << 16)) : x0, hi = sh ? ((x1 >> 16) | (x2 << 16)) : x1;
-#else
-				const uint32_t lo = __funnelshift_r(x0, x1, sh), hi = __funnelshift_r(x1, x2, sh);
-#endif
-				uint64_t wd = u64_of(lo, hi);
-				wd *= Murmur::MUL; wd ^= wd >> 47; wd *= Murmur::MUL;
-				hcur ^= wd; hcur *= Murmur::MUL;
-				pa = pb;
-			}
-			Murmur mm; mm.h = hcur;
-			if (rem)
-			{
-				const uint16_t* __restrict__ arr = (d ? rrc : codes) + ob;
-				uint64_t wd = 0;
-				for (uint32_t j = 0; j < rem; j++) wd |= (uint64_t)arr[st + 4 * nb + j] << (16 * j);
-				mm.tail(wd);
-			}
-			out[2 * i + d] = mm.finish();
-		}
-		__syncthreads();
-		i0 = i1;
 	}
 }
 
@@ -1447,13 +1356,6 @@ __global__ void __launch_bounds__(256) k_apply_variants(uint64_t* __restrict__ i
 	}
 }
 
-
-// KAT helper: rrc for one stand-alone code array of n codes (cap == n)
-__global__ void k_revcomp_codes(const uint16_t* __restrict__ codes, uint32_t n, const uint16_t* __restrict__ tab_comp, uint16_t* __restrict__ rrc)
-{
-	const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-	if (i < n) rrc[n - 1 - i] = tab_comp[codes[i]];
-}
 
 // instances whose two halves hash alike: palindromes or (practically impossible) collisions
 __global__ void __launch_bounds__(256) k_find_palindromes(const uint64_t* __restrict__ inst_hash, const uint64_t* __restrict__ range_begin, const uint64_t* __restrict__ range_end,

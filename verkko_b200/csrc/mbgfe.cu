@@ -9,7 +9,11 @@
 #include <cstdarg>
 #include <cstdio>
 #include <cstring>
+#include <fcntl.h>
+#include <functional>
 #include <string>
+#include <sys/stat.h>
+#include <unistd.h>
 #include <vector>
 #include <zlib.h>
 
@@ -72,7 +76,6 @@ struct mbgfe
 	size_t max_smem = 0;
 	SelectPlan plan;
 	int select_nt = NT_SELECT_DEFAULT;                              // threads per CTA of k_select
-	uint32_t hash_cap_codes = 9216;                   // k_kmer_hash_lanes: codes staged per direction
 
 	// code tables
 	DevBuf tab_hash, tab_pair, tab_comp;
@@ -87,6 +90,12 @@ struct mbgfe
 	bool resident = false, processed = false, exported_parts = false, exported_table = false, exported_codes = false, have_table = false;
 	uint64_t n_reads = 0, n_bases = 0;
 	std::vector<uint64_t> read_off;                   // n_reads + 1
+	std::vector<uint64_t> read_end;                   // empty: read r ends where read r + 1 begins; else n_reads ends (file images: headers sit in between)
+	// plain FASTA files waiting for mbgfe_run's streaming loader (row a1); base = batch position of the file's first byte
+	struct DeferredFile { std::string path; int fd; uint64_t size, base; };
+	std::vector<DeferredFile> files;
+	std::vector<uint64_t> name_off; std::vector<uint32_t> name_len, name_file;   // names of file-image reads: fetched on demand
+	std::vector<DeferredFile> image_files;            // the files the resident image was made from (kept open for names / rare re-reads)
 	std::vector<uint64_t> seg_in, seg_out;            // per segment
 	std::vector<uint32_t> seg_len, seg_read, seg_rawoff, seg_nonacgt_before;
 	uint64_t total_out = 0;
@@ -95,7 +104,7 @@ struct mbgfe
 	// device buffers
 	DevBuf d_ascii, d_packed, d_nonacgt, d_counters;
 	DevBuf d_seg_in, d_seg_out, d_seg_len, d_seg_c1, d_seg_c2, d_seg_nsel, d_sel_begin;
-	DevBuf d_sym, d_codes, d_rrc, d_selmask, d_pos1, d_pos2;
+	DevBuf d_sym, d_codes, d_selmask, d_pos1, d_pos2;
 	DevBuf d_inst_pos, d_inst_seg, d_inst_flag, d_inst_hash, d_inst_slot, d_pal_list;
 	DevBuf d_nodes, d_edges, d_node_out, d_edge_out, d_records, d_recv;
 	DevBuf d_inst_packpos, d_ids_out, d_id_begin, d_edge_records, d_xbuf[4];   // sharded table: id replies and edge records
@@ -116,6 +125,10 @@ struct mbgfe
 	std::vector<uint32_t> h_th_unitig, h_th_upos, h_th_urest, h_thin_pos;
 	std::vector<uint8_t> h_thin;
 	bool have_thin = false;
+	// the list after reads.filter(kept) of filterKmersToUnitigKmers, its unitigs and the new sequence overlaps
+	DevBuf d_thin_scan, d_tpos, d_tu_nodes, d_tu_off, d_tu_unitig, d_tu_begin, d_t_newov;
+	uint64_t n_thin = 0, n_tedges = 0, n_tpos = 0;
+	std::vector<mbgfe_hash128> h_t_hash; std::vector<uint32_t> h_t_cov, h_tu_nodes; std::vector<uint8_t> h_t_tip; std::vector<mbgfe_edge> h_t_edges, h_t_newov; std::vector<uint64_t> h_tu_begin;
 	uint32_t unitig_min_cov = 1;
 	bool have_threads = false;
 	std::vector<mbgfe_hash128> h_f_hash;
@@ -185,6 +198,8 @@ void release_host(HostBuf& b) { if (b.p) cudaFreeHost(b.p); b.p = nullptr; b.cap
 // poses are kept on request, and whenever hpc variants are registered (the re-hash reads run lengths from them)
 bool want_poses_of(const mbgfe* h) { return (h->prm.flags & MBGFE_KEEP_POSES) != 0 || h->n_var != 0; }
 
+uint64_t read_end_of(const mbgfe* h, uint64_t r) { return h->read_end.empty() ? h->read_off[r + 1] : h->read_end[r]; }
+
 uint64_t next_pow2(uint64_t v) { uint64_t p = 1; while (p < v) p <<= 1; return p; }
 
 bool is_acgt(char c) { c &= (char)0xdf; return c == 'A' || c == 'C' || c == 'G' || c == 'T'; }
@@ -206,7 +221,7 @@ SegTable seg_table(const mbgfe* h)
 
 // Segments of the resident reads: reads shorter than 32 bases are ignored (MBG/ReadHelper.h:838); the others are cut
 // at every character outside ACGTacgt (positions found by k_pack_ascii, sorted ascending in `bad`).
-void build_segments(mbgfe* h, const std::vector<uint64_t>& bad, const std::vector<const char*>& read_ptr)
+void build_segments(mbgfe* h, const std::vector<uint64_t>& bad, const std::function<const char*(uint64_t)>& read_ptr)
 {
 	h->seg_in.clear(); h->seg_out.clear(); h->seg_len.clear(); h->seg_read.clear(); h->seg_rawoff.clear(); h->seg_nonacgt_before.clear();
 	uint64_t out = 0;
@@ -223,12 +238,12 @@ void build_segments(mbgfe* h, const std::vector<uint64_t>& bad, const std::vecto
 	};
 	for (uint64_t r = 0; r < h->n_reads; r++)
 	{
-		const uint64_t a = h->read_off[r], b = h->read_off[r + 1];
+		const uint64_t a = h->read_off[r], b = read_end_of(h, r);
 		while (bi < bad.size() && bad[bi] < a) bi++;
 		if (b - a < 32) { while (bi < bad.size() && bad[bi] < b) bi++; continue; }
 		if (bi >= bad.size() || bad[bi] >= b) { add(r, a, b - a, 0); continue; }
 		// read with other characters: walk its non-ACGT positions
-		const char* raw = read_ptr[r];
+		const char* raw = read_ptr(r);
 		uint64_t cur = a;
 		uint32_t collapsed_other = 0; // characters outside ACGT that survive the collapse step, so far
 		while (cur < b)
@@ -414,6 +429,9 @@ int load_file(mbgfe* h, const char* path)
 }
 
 namespace {
+int materialize_files(mbgfe* h);
+int run_files(mbgfe* h);
+void close_files(std::vector<mbgfe::DeferredFile>& v) { for (auto& f : v) if (f.fd >= 0) close(f.fd); v.clear(); }
 int prepare_process(mbgfe* h);
 uint32_t launch_front(mbgfe* h, uint32_t g0, uint32_t cnt, bool timed, cudaStream_t on = nullptr);
 int process_tail(mbgfe* h, uint32_t launches);
@@ -477,11 +495,6 @@ int mbgfe_create(const mbgfe_params* prm, mbgfe** out)
 	cudaFuncSetAttribute(k_select<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->plan.smem_bytes);
 	cudaFuncSetAttribute(k_select<256>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->plan.smem_bytes);
 	cudaFuncSetAttribute(k_select<512>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->plan.smem_bytes);
-	// staged codes per direction of k_kmer_hash_lanes (4096: best on the bench, 13 CTAs per SM); large k needs room for
-	// at least one k-mer
-	h->hash_cap_codes = std::max<uint32_t>(4096, (((prm->k + 1) / 2 + 16 + 1024) + 7) & ~7u);
-	if (const char* e = getenv("MBGFE_HASH_CAP")) h->hash_cap_codes = std::max<uint32_t>((uint32_t)atoi(e) & ~7u, (((prm->k + 1) / 2 + 16 + 64) + 7) & ~7u);
-	cudaFuncSetAttribute(k_kmer_hash_lanes, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(4 * h->hash_cap_codes));
 	if (cudaStreamSynchronize(h->stream) != cudaSuccess || cudaGetLastError() != cudaSuccess)
 		return bail(fail(h, MBGFE_E_CUDA, "table kernel failed: is this an sm_100 device?"));
 	*out = h;
@@ -492,13 +505,13 @@ void mbgfe_destroy(mbgfe* h)
 {
 	if (!h) return;
 	for (DevBuf* b : { &h->tab_hash, &h->tab_pair, &h->tab_comp, &h->d_ascii, &h->d_packed, &h->d_nonacgt, &h->d_counters, &h->d_seg_in, &h->d_seg_out,
-		&h->d_seg_len, &h->d_seg_c1, &h->d_seg_c2, &h->d_seg_nsel, &h->d_sel_begin, &h->d_sym, &h->d_codes, &h->d_rrc, &h->d_selmask, &h->d_pos1, &h->d_pos2,
+		&h->d_seg_len, &h->d_seg_c1, &h->d_seg_c2, &h->d_seg_nsel, &h->d_sel_begin, &h->d_sym, &h->d_codes, &h->d_selmask, &h->d_pos1, &h->d_pos2,
 		&h->d_inst_pos, &h->d_inst_seg, &h->d_inst_flag, &h->d_inst_hash, &h->d_inst_slot, &h->d_pal_list, &h->d_nodes, &h->d_edges, &h->d_node_out,
 		&h->d_edge_out, &h->d_records, &h->d_recv, &h->d_bucket_count, &h->d_bucket_begin, &h->d_scan_tot, &h->d_scan_off, &h->d_node_hash_sorted, &h->d_node_cov,
 		&h->d_node_tip, &h->d_edges_sorted, &h->d_inst_packpos, &h->d_ids_out, &h->d_id_begin, &h->d_edge_records, &h->d_xbuf[0], &h->d_xbuf[1], &h->d_xbuf[2],
 		&h->d_xbuf[3], &h->d_var_hash, &h->d_var_offset, &h->d_var_len_begin, &h->d_var_len, &h->d_g_deg, &h->d_g_nb, &h->d_g_link, &h->d_g_st[0], &h->d_g_st[1],
 		&h->d_g_kept, &h->d_g_newid, &h->d_g_flag, &h->d_g_at, &h->d_g_flag2, &h->d_g_at2, &h->d_g_flag_byte, &h->d_f_hash, &h->d_f_cov, &h->d_f_tip, &h->d_f_edges, &h->d_f_orig, &h->d_t_hash, &h->d_t_cov, &h->d_t_tip, &h->d_t_edges, &h->d_t_orig, &h->d_g_kept8, &h->d_u_pos, &h->d_th_final, &h->d_th_node, &h->d_th_unitig, &h->d_th_upos, &h->d_th_urest, &h->d_th_step, &h->d_thin, &h->d_thin_pos,
-		&h->d_u_begin, &h->d_u_nodes, &h->d_u_of_node, &h->d_u_fw, &h->d_u_edges }) release(*b);
+		&h->d_u_begin, &h->d_u_nodes, &h->d_u_of_node, &h->d_u_fw, &h->d_u_edges, &h->d_thin_scan, &h->d_tpos, &h->d_tu_nodes, &h->d_tu_off, &h->d_tu_unitig, &h->d_tu_begin, &h->d_t_newov }) release(*b);
 	for (HostBuf* b : { &h->p_node_hashes, &h->p_node_cov, &h->p_node_tip, &h->p_edges, &h->p_stage }) release_host(*b);
 	for (auto& e : h->ev) if (e) cudaEventDestroy(e);
 	for (auto& e : h->piece_events) cudaEventDestroy(e);
@@ -509,6 +522,7 @@ void mbgfe_destroy(mbgfe* h)
 	if (h->stream) cudaStreamDestroy(h->stream);
 	for (auto* v : h->owned_bases) delete v;
 	for (auto* v : h->owned_offsets) delete v;
+	close_files(h->files); close_files(h->image_files);
 	delete h;
 }
 
@@ -531,6 +545,7 @@ int mbgfe_add_reads(mbgfe* h, const char* bases, const uint64_t* offsets, uint64
 		if (offsets[r + 1] < offsets[r]) return fail(h, MBGFE_E_PARAM, "offsets must be non-decreasing (read %llu)", (unsigned long long)r);
 		if (offsets[r + 1] - offsets[r] >= (1ull << 29)) return fail(h, MBGFE_E_LIMIT, "read %llu is longer than 2^29-1 bases", (unsigned long long)r);
 	}
+	if (!h->files.empty()) if (int rc = materialize_files(h)) return rc;      // keep the order the caller added things in
 	HostChunk c = { bases, offsets, n_reads };
 	h->pending.push_back(c);
 	return 0;
@@ -539,6 +554,22 @@ int mbgfe_add_reads(mbgfe* h, const char* bases, const uint64_t* offsets, uint64
 int mbgfe_add_file(mbgfe* h, const char* path)
 {
 	if (!h || !path) return MBGFE_E_PARAM;
+	// a plain (uncompressed) FASTA file is not read here: mbgfe_run streams it -- read, scan and 2-bit packing in one pass on
+	// worker threads, overlapped with the copies and the kernels (run_files).  Everything else (.gz: zlib is the bound; FASTQ)
+	// is parsed now.
+	{
+		std::string base = path;
+		auto ends = [&](const char* suf) { size_t n = strlen(suf); return base.size() >= n && base.compare(base.size() - n, n, suf) == 0; };
+		struct stat sb;
+		if ((ends(".fasta") || ends(".fa")) && h->pending.empty() && !getenv("MBGFE_FILE_LEGACY") && stat(path, &sb) == 0 && S_ISREG(sb.st_mode) && sb.st_size > 0)
+		{
+			const int fd = open(path, O_RDONLY);
+			if (fd < 0) return fail(h, MBGFE_E_IO, "cannot read %s", path);
+			h->files.push_back({ path, fd, (uint64_t)sb.st_size, 0 });
+			return 0;
+		}
+	}
+	if (!h->files.empty()) if (int rc = materialize_files(h)) return rc;
 	// names are indexed by read; reads added without names before this file get empty names
 	uint64_t have = 0;
 	for (auto& c : h->pending) have += c.n_reads;
@@ -546,9 +577,25 @@ int mbgfe_add_file(mbgfe* h, const char* path)
 	return load_file(h, path);
 }
 
-const char* mbgfe_read_name(const mbgfe* h, uint64_t read_idx)
+const char* mbgfe_read_name(const mbgfe* h_, uint64_t read_idx)
 {
-	if (!h || read_idx >= h->names.size()) return "";
+	mbgfe* h = const_cast<mbgfe*>(h_);
+	if (!h) return "";
+	if (!h->files.empty()) materialize_files(h);      // names asked for before the run: parse now
+	if (read_idx < h->name_off.size() && h->names.size() <= read_idx)
+	{
+		// reads of a streamed file: the header text is fetched from the file the first time a name is wanted
+		h->names.resize(h->name_off.size());
+		for (uint64_t r = 0; r < h->name_off.size(); r++)
+		{
+			std::string& n = h->names[r];
+			n.resize(h->name_len[r]);
+			const mbgfe::DeferredFile& f = h->image_files[h->name_file[r]];
+			if (h->name_len[r] && pread(f.fd, &n[0], h->name_len[r], (off_t)(h->name_off[r] - f.base)) != (ssize_t)h->name_len[r]) n.clear();
+			if (!n.empty() && n.back() == '\r') n.pop_back();
+		}
+	}
+	if (read_idx >= h->names.size()) return "";
 	return h->names[read_idx].c_str();
 }
 
@@ -557,6 +604,8 @@ int mbgfe_reset(mbgfe* h)
 	if (!h) return MBGFE_E_PARAM;
 	h->pending.clear();
 	h->names.clear();
+	close_files(h->files); close_files(h->image_files);
+	h->name_off.clear(); h->name_len.clear(); h->name_file.clear(); h->read_end.clear();
 	for (auto* v : h->owned_bases) delete v;
 	for (auto* v : h->owned_offsets) delete v;
 	h->owned_bases.clear(); h->owned_offsets.clear();
@@ -569,6 +618,7 @@ int mbgfe_reset(mbgfe* h)
 int mbgfe_upload(mbgfe* h)
 {
 	if (!h) return MBGFE_E_PARAM;
+	if (!h->files.empty()) if (int rc = materialize_files(h)) return rc;
 	clear_results(h);
 	h->resident = false;
 	h->stats.h2d_bytes = 0; h->stats.d2h_bytes = 0;
@@ -577,6 +627,8 @@ int mbgfe_upload(mbgfe* h)
 	if (n_reads >= (1ull << 32)) return fail(h, MBGFE_E_LIMIT, "more than 2^32-1 reads in one batch");
 	h->n_reads = n_reads; h->n_bases = n_bases;
 	h->read_off.resize(n_reads + 1);
+	h->read_end.clear();
+	h->name_off.clear(); h->name_len.clear(); h->name_file.clear(); close_files(h->image_files);
 	std::vector<const char*> read_ptr(n_reads);
 	if (int rc = ensure(h, h->d_ascii, n_bases + 64)) return rc;
 	if (int rc = ensure(h, h->d_packed, n_bases / 4 + 64)) return rc;
@@ -610,7 +662,7 @@ int mbgfe_upload(mbgfe* h)
 	std::vector<uint64_t> bad;
 	if (n_bad) { if (int rc = download(h, bad, h->d_nonacgt, n_bad)) return rc; std::sort(bad.begin(), bad.end()); }
 	h->nonacgt_count = n_bad;
-	build_segments(h, bad, read_ptr);
+	build_segments(h, bad, [&](uint64_t r_) { return read_ptr[r_]; });
 	if (int rc = upload_segments(h)) return rc;
 	CU(h, cudaStreamSynchronize(h->stream));
 	h->stats.ms_upload = elapsed(h, 0, 1);
@@ -644,7 +696,6 @@ int prepare_process(mbgfe* h)
 	const uint64_t tot = h->total_out;
 	if (int rc = ensure(h, h->d_sym, tot / 4 + 64)) return rc;
 	if (int rc = ensure(h, h->d_codes, tot * 2 + 64)) return rc;
-	if (int rc = ensure(h, h->d_rrc, tot * 2 + 64)) return rc;
 	if (int rc = ensure(h, h->d_selmask, tot / 8 + 64)) return rc;
 	if (need_pos1) if (int rc = ensure(h, h->d_pos1, tot * 4 + 64)) return rc;
 	if (want_poses) if (int rc = ensure(h, h->d_pos2, tot * 4 + 64)) return rc;
@@ -675,11 +726,11 @@ uint32_t launch_front(mbgfe* h, uint32_t g0, uint32_t cnt, bool timed, cudaStrea
 		h->prm.error_masking == MBGFE_MASK_NO ? 1 : 0);
 	if (timed) tick(h, 4);
 	if (h->msat)
-		MBGFE_LAUNCH(k_msat, (cnt + MSAT_WARPS - 1) / MSAT_WARPS, MSAT_WARPS * 32, 0, on, st, h->d_sym.as<uint64_t>(), c1, h->d_codes.as<uint16_t>(), h->d_rrc.as<uint16_t>(),
+		MBGFE_LAUNCH(k_msat, (cnt + MSAT_WARPS - 1) / MSAT_WARPS, MSAT_WARPS * 32, 0, on, st, h->d_sym.as<uint64_t>(), c1, h->d_codes.as<uint16_t>(),
 			c2, (const uint32_t*)pos1, pos2, h->max_motif);
 	else
 		MBGFE_LAUNCH(k_unpack_symbols<NT_MSAT>, cnt, NT_MSAT, 0, on, st, h->d_sym.as<uint64_t>(), c1, h->d_codes.as<uint16_t>(),
-			h->d_rrc.as<uint16_t>(), c2, (const uint32_t*)pos1, pos2);
+			c2, (const uint32_t*)pos1, pos2);
 	if (timed) tick(h, 5);
 	if (h->select_nt == 64)
 		MBGFE_LAUNCH(k_select<64>, cnt, 64, h->plan.smem_bytes, on, st, h->d_codes.as<uint16_t>(), c2, h->tab_pair.as<uint4>(),
@@ -751,13 +802,8 @@ void launch_list_hash(mbgfe* h, uint32_t g0, uint32_t g1, uint64_t n_hint, uint3
 	const uint64_t* sb = h->d_sel_begin.as<uint64_t>();
 	MBGFE_LAUNCH(k_list_selected<NT_LIST>, g1 - g0, NT_LIST, 0, h->stream, st, g0, h->d_selmask.as<uint32_t>(), h->d_seg_c2.as<uint32_t>() + g0, h->d_seg_nsel.as<uint32_t>() + g0,
 		sb + g0, h->d_inst_pos.as<uint32_t>(), h->d_inst_seg.as<uint32_t>(), h->d_inst_flag.as<uint8_t>(), k, h->inst_cap, ctr + CTR_OVERFLOW);
-	const bool lanes_hash = getenv("MBGFE_HASH_LANES") != nullptr;          // the lane-per-k-mer kernel, kept for comparison
-	if (!lanes_hash)
-		MBGFE_LAUNCH(k_kmer_hash, g1 - g0, HASH_NT, 0, h->stream, h->d_seg_out.as<uint64_t>() + g0, h->d_codes.as<uint16_t>(), h->d_rrc.as<uint16_t>(), h->d_inst_pos.as<uint32_t>(),
-			sb + g0, h->inst_cap, h->d_inst_hash.as<uint64_t>(), k);
-	else
-		MBGFE_LAUNCH(k_kmer_hash_lanes, g1 - g0, HASHL_NT, 4 * h->hash_cap_codes, h->stream, h->d_seg_out.as<uint64_t>() + g0, h->d_codes.as<uint16_t>(), h->d_rrc.as<uint16_t>(),
-			h->d_inst_pos.as<uint32_t>(), sb + g0, h->inst_cap, h->d_inst_hash.as<uint64_t>(), k, h->hash_cap_codes);
+	MBGFE_LAUNCH(k_kmer_hash, g1 - g0, HASH_NT, 0, h->stream, h->d_seg_out.as<uint64_t>() + g0, h->d_codes.as<uint16_t>(), h->tab_comp.as<uint16_t>(), h->d_inst_pos.as<uint32_t>(),
+		sb + g0, h->inst_cap, h->d_inst_hash.as<uint64_t>(), k);
 	const unsigned pal_grid = n_hint ? (unsigned)((n_hint + 255) / 256) : (unsigned)h->sm_count * 4;
 	MBGFE_LAUNCH(k_find_palindromes, pal_grid, 256, 0, h->stream, h->d_inst_hash.as<uint64_t>(), sb + g0, sb + g1, h->inst_cap, ctr + CTR_PALINDROME, h->d_pal_list.as<uint64_t>(), PAL_CAP);
 	launches += 3;
@@ -897,6 +943,13 @@ int mbgfe_run(mbgfe* h)
 		if (int rc = mbgfe_upload(h)) return rc;
 		return mbgfe_process(h);
 	}
+	if (!h->files.empty())
+	{
+		const int rc = run_files(h);
+		if (rc != 1) return rc;
+		// 1: a file the streaming loader does not take (sequence split over several lines, too many short reads): parse it the plain way
+		if (int rc2 = materialize_files(h)) return rc2;
+	}
 	clear_results(h);
 	h->resident = false;
 	h->stats.h2d_bytes = 0; h->stats.d2h_bytes = 0;
@@ -905,6 +958,8 @@ int mbgfe_run(mbgfe* h)
 	if (n_reads >= (1ull << 32)) return fail(h, MBGFE_E_LIMIT, "more than 2^32-1 reads in one batch");
 	h->n_reads = n_reads; h->n_bases = n_bases;
 	h->read_off.resize(n_reads + 1);
+	h->read_end.clear();
+	h->name_off.clear(); h->name_len.clear(); h->name_file.clear(); close_files(h->image_files);
 	std::vector<const char*> read_ptr(n_reads);
 	{
 		uint64_t pos = 0, r = 0;
@@ -921,7 +976,7 @@ int mbgfe_run(mbgfe* h)
 	const uint64_t bad_cap = std::max<uint64_t>(1 << 20, n_bases / 16);
 	if (int rc = ensure(h, h->d_nonacgt, bad_cap * 8)) return rc;
 	const std::vector<uint64_t> none;
-	build_segments(h, none, read_ptr);
+	build_segments(h, none, [&](uint64_t r_) { return read_ptr[r_]; });
 	const uint32_t n_seg = (uint32_t)h->seg_len.size();
 	CU(h, cudaMemsetAsync(h->d_counters.p, 0, h->d_counters.cap, h->stream));
 	if (int rc = upload_segments(h)) return rc;
@@ -1047,7 +1102,7 @@ int mbgfe_run(mbgfe* h)
 		}
 		CU(h, cudaEventRecord(h->pack_events[piece], fs));
 		uint32_t g_end = g_done;
-		while (g_end < n_seg && h->read_off[h->seg_read[g_end] + 1] <= packed_upto) g_end++;
+		while (g_end < n_seg && read_end_of(h, h->seg_read[g_end]) <= packed_upto) g_end++;
 		if (g_end == g_done) { CU(h, cudaStreamWaitEvent(h->stream, h->pack_events[piece], 0)); continue; }
 		launches += launch_front(h, g_done, g_end - g_done, false, fs);
 		CU(h, cudaEventRecord(h->front_events[piece], fs));
@@ -1060,7 +1115,7 @@ int mbgfe_run(mbgfe* h)
 			CU(h, cudaMemcpyAsync(&n0, h->d_sel_begin.as<uint64_t>() + g_end, 8, cudaMemcpyDeviceToHost, h->stream));
 			CU(h, cudaStreamSynchronize(h->stream));
 			h->stats.d2h_bytes += 8;
-			const uint64_t bases0 = h->read_off[h->seg_read[g_end - 1] + 1];
+			const uint64_t bases0 = read_end_of(h, h->seg_read[g_end - 1]);
 			const double per_base = (double)n0 / (double)std::max<uint64_t>(bases0, 1);
 			const uint64_t est = (uint64_t)(per_base * (double)n_bases) + 1;
 			if (int rc = ensure_instances(h, std::max<uint64_t>(est + est / 4 + 4096, h->inst_cap))) return rc;
@@ -1102,7 +1157,7 @@ int mbgfe_run(mbgfe* h)
 		if (int rc = download(h, bad, h->d_nonacgt, n_bad_dev)) return rc;
 		bad.insert(bad.end(), pool.bad.begin(), pool.bad.end());      // found by the host packers
 		std::sort(bad.begin(), bad.end());
-		build_segments(h, bad, read_ptr);
+		build_segments(h, bad, [&](uint64_t r_) { return read_ptr[r_]; });
 		if (int rc = upload_segments(h)) return rc;
 		CU(h, cudaStreamSynchronize(h->stream));
 		h->stats.segments = h->seg_len.size();
@@ -1129,6 +1184,298 @@ int mbgfe_run(mbgfe* h)
 }
 
 namespace {
+
+// deferred files -> parsed into memory the plain way (mbgfe_upload, variants, mixed input, files the streaming loader refuses)
+int materialize_files(mbgfe* h)
+{
+	std::vector<mbgfe::DeferredFile> todo;
+	todo.swap(h->files);
+	for (auto& f : todo)
+	{
+		if (f.fd >= 0) close(f.fd);
+		uint64_t have = 0;
+		for (auto& c : h->pending) have += c.n_reads;
+		if (h->names.size() < have) h->names.resize(have);
+		if (int rc = load_file(h, f.path.c_str())) return rc;
+	}
+	return 0;
+}
+
+// Record structure of a FASTA file from the scan events of its tasks, in file order (MBG/fastqloader.h:38-80): a record is a
+// '>' line and the sequence lines up to the next one; lines before the first header are skipped; a trailing '\r' is dropped;
+// empty lines are skipped.  The streaming loader only takes records whose sequence sits on ONE line (a contiguous range of the
+// file image); `multiline` reports the others.
+struct FastaStitch
+{
+	uint64_t line_start = 0, seq_start = 0, seq_end = 0, name_start = 0, name_end = 0, pending_cr = ~0ull;
+	bool in_header = false, have_record = false, have_seq = false, multiline = false;
+	size_t bad_at_line = 0;
+	std::vector<uint64_t>* bad = nullptr;
+	std::function<void(uint64_t, uint64_t, uint64_t, uint64_t)> emit;      // seq_start, seq_end, name_start, name_end
+
+	void flush_cr() { if (pending_cr != ~0ull) { bad->push_back(pending_cr); pending_cr = ~0ull; } }
+	void finish_record() { if (have_record && !have_seq) emit(name_end, name_end, name_start, name_end); have_record = false; have_seq = false; }
+	void end_line(uint64_t pos)          // the current line is [line_start, pos)
+	{
+		if (in_header) { name_end = pos; in_header = false; have_record = true; have_seq = false; }
+		else
+		{
+			uint64_t end = pos;
+			if (pending_cr != ~0ull && pending_cr + 1 == pos) { end = pos - 1; pending_cr = ~0ull; }      // "\r\n"
+			flush_cr();
+			if (end > line_start)
+			{
+				if (!have_record) bad->resize(bad_at_line);            // text before the first header: not a read
+				else if (have_seq) multiline = true;
+				else { seq_start = line_start; seq_end = end; have_seq = true; emit(seq_start, seq_end, name_start, name_end); }
+			}
+		}
+		line_start = pos + 1;
+		bad_at_line = bad->size();
+	}
+	void event(uint64_t pos, unsigned char ch)
+	{
+		if (ch == '\n') { end_line(pos); return; }
+		if (in_header) return;
+		if (ch == '>' && pos == line_start) { flush_cr(); finish_record(); in_header = true; name_start = pos + 1; return; }
+		flush_cr();
+		if (ch == '\r') pending_cr = pos; else bad->push_back(pos);
+	}
+	void end_of_file(uint64_t pos) { if (pos > line_start || in_header) end_line(pos); flush_cr(); finish_record(); }
+};
+
+// mbgfe_run on plain FASTA files: the file never exists as a parsed copy in host memory.  Worker threads pread() it in tasks
+// of 1 MiB, pack EVERY byte to 2 bits in file order (hostpack.cpp: pack_scan_fasta) straight into pinned staging and report the
+// handful of bytes per read that are not ACGT; this thread stitches those into reads (FastaStitch), appends the segment table,
+// queues the H2D copy of the piece and launches K1 .. K4 on the segments the piece completed -- the same per-piece pipeline as
+// the in-memory path.  The device image keeps file coordinates (header bytes are junk entries nobody reads), so parse == pack
+// and the bus carries a quarter byte per file byte.  Returns 1 when a file needs the plain parser instead.
+int run_files(mbgfe* h)
+{
+	clear_results(h);
+	h->resident = false;
+	h->stats.h2d_bytes = 0; h->stats.d2h_bytes = 0;
+	close_files(h->image_files);
+	h->names.clear(); h->name_off.clear(); h->name_len.clear(); h->name_file.clear();
+	uint64_t total = 0;
+	for (auto& f : h->files) { f.base = total; total += (f.size + 31) & ~(uint64_t)31; }
+	const uint64_t n_image = total;
+	uint64_t PIECE = h->prm.piece_bytes ? std::max<uint64_t>((h->prm.piece_bytes + 31) & ~31u, 64) : (32ull << 20);
+	if (const char* e = getenv("MBGFE_PIECE_MB")) if (!h->prm.piece_bytes && atoi(e) > 0) PIECE = (uint64_t)atoi(e) << 20;
+	const uint64_t TASK = std::min<uint64_t>(PIECE, 1ull << 20);
+	// capacity of the segment table and of the per-symbol arrays: nobody knows the reads yet.  One segment per 256 file bytes
+	// is far more than HiFi reads need; a file of shorter reads goes to the plain parser.
+	const uint64_t seg_cap = std::max<uint64_t>(1 << 16, n_image / 256);
+	const uint64_t out_cap = n_image + 64 * seg_cap;
+	if (seg_cap >= (1ull << 32) - 2) return 1;
+	{
+		const size_t n = seg_cap;
+		if (int rc = ensure(h, h->d_seg_in, (n + 1) * 8)) return rc;
+		if (int rc = ensure(h, h->d_seg_out, (n + 1) * 8)) return rc;
+		if (int rc = ensure(h, h->d_seg_len, (n + 1) * 4)) return rc;
+		if (int rc = ensure(h, h->d_seg_c1, (n + 1) * 4)) return rc;
+		if (int rc = ensure(h, h->d_seg_c2, (n + 1) * 4)) return rc;
+		if (int rc = ensure(h, h->d_seg_nsel, (n + 1) * 4)) return rc;
+		if (int rc = ensure(h, h->d_sel_begin, (n + 2) * 8)) return rc;
+	}
+	if (int rc = ensure(h, h->d_packed, n_image / 4 + 64)) return rc;
+	if (int rc = ensure(h, h->d_nonacgt, 8 << 20)) return rc;
+	if (int rc = ensure_host(h, h->p_stage, n_image / 4 + 64)) return rc;
+	h->read_off.clear(); h->read_end.clear();
+	h->seg_in.clear(); h->seg_out.clear(); h->seg_len.clear(); h->seg_read.clear(); h->seg_rawoff.clear(); h->seg_nonacgt_before.clear();
+	h->total_out = out_cap;
+	CU(h, cudaMemsetAsync(h->d_counters.p, 0, h->d_counters.cap, h->stream));
+	if (int rc = prepare_process(h)) return rc;
+	h->total_out = 0;
+	tick(h, 0);
+	tick(h, 3);
+	CU(h, cudaStreamWaitEvent(h->copy_stream, h->ev[0], 0));
+	// ---- pieces and tasks
+	struct Piece { size_t file; uint64_t pos, len; size_t task0, task1; };
+	std::vector<Piece> pieces;
+	std::vector<mbgfe_host::FileTask> tasks;
+	for (size_t fi = 0; fi < h->files.size(); fi++)
+	{
+		const auto& f = h->files[fi];
+		for (uint64_t off = 0; off < f.size; off += PIECE)
+		{
+			Piece pc { fi, f.base + off, std::min(PIECE, f.size - off), tasks.size(), 0 };
+			for (uint64_t o = 0; o < pc.len; o += TASK)
+			{
+				mbgfe_host::FileTask t;
+				t.piece = pieces.size(); t.fd = f.fd; t.file_off = off + o; t.n = std::min(TASK, pc.len - o);
+				t.dst = (uint64_t*)h->p_stage.p + (pc.pos + o) / 32; t.pos = pc.pos + o;
+				tasks.push_back(std::move(t));
+			}
+			pc.task1 = tasks.size();
+			pieces.push_back(pc);
+		}
+	}
+	const unsigned hw = std::thread::hardware_concurrency();
+	const unsigned share = std::max(1u, h->prm.world);
+	unsigned n_workers = hw / share > 2 ? std::min(hw / share - 1, 63u) : 1;
+	if (const char* e = getenv("MBGFE_FILE_THREADS")) if (atoi(e) > 0) n_workers = (unsigned)atoi(e);
+	mbgfe_host::FilePool pool;
+	pool.start(std::move(tasks), pieces.size(), n_workers);
+	while (h->piece_events.size() < pieces.size())
+	{
+		cudaEvent_t e;
+		CU(h, cudaEventCreate(&e)); h->piece_events.push_back(e);
+		CU(h, cudaEventCreateWithFlags(&e, cudaEventDisableTiming)); h->front_events.push_back(e);
+		CU(h, cudaEventCreateWithFlags(&e, cudaEventDisableTiming)); h->pack_events.push_back(e);
+	}
+	// ---- the stitcher: reads and segments as the pieces come in
+	std::vector<uint64_t> bad;
+	uint64_t out = 0, raw_bases = 0;
+	bool refuse = false;
+	size_t cur_file = 0;
+	FastaStitch st;
+	st.bad = &bad;
+	const std::function<void(uint64_t, uint64_t, uint64_t, uint64_t)> emit_read = [&](uint64_t s0, uint64_t s1, uint64_t n0, uint64_t n1)
+	{
+		const uint64_t r = h->read_off.size();
+		h->read_off.push_back(s0); h->read_end.push_back(s1);
+		h->name_off.push_back(n0); h->name_len.push_back((uint32_t)(n1 - n0)); h->name_file.push_back((uint32_t)cur_file);
+		raw_bases += s1 - s0;
+		if (s1 - s0 >= (1ull << 29)) { refuse = true; return; }
+		if (s1 - s0 < 32) return;                                     // MBG/ReadHelper.h:838
+		if (h->seg_len.size() >= seg_cap) { refuse = true; return; }
+		h->seg_in.push_back(s0); h->seg_len.push_back((uint32_t)(s1 - s0)); h->seg_read.push_back((uint32_t)r); h->seg_rawoff.push_back(0);
+		h->seg_nonacgt_before.push_back(0); h->seg_out.push_back(out);
+		out += ((s1 - s0) + 1 + 63) & ~(uint64_t)63;
+	};
+	st.emit = emit_read;
+	const bool want_table = !(h->prm.flags & MBGFE_NO_TABLE);
+	unsigned long long* ctr = h->d_counters.as<unsigned long long>();
+	uint32_t g_done = 0, g_tail = 0, launches = 0;
+	uint64_t h2d_bytes = 0;
+	bool sized = false;
+	auto drain = [&]() { pool.finish(); cudaStreamSynchronize(h->copy_stream); cudaStreamSynchronize(h->front_stream[0]); cudaStreamSynchronize(h->front_stream[1]); cudaStreamSynchronize(h->stream); };
+	for (size_t piece = 0; piece < pieces.size(); piece++)
+	{
+		const Piece& pc = pieces[piece];
+		pool.wait_piece(piece);
+		if (pc.file != cur_file) { cur_file = pc.file; st = FastaStitch(); st.bad = &bad; st.emit = emit_read; st.line_start = pc.pos; }
+		if (piece == 0) st.line_start = pc.pos;
+		const size_t seg_before = h->seg_len.size();
+		for (size_t t = pc.task0; t < pc.task1; t++)
+		{
+			mbgfe_host::FileTask& k = pool.tasks[t];
+			if (k.error) { drain(); return fail(h, MBGFE_E_IO, "read error in %s", h->files[pc.file].path.c_str()); }
+			for (uint64_t ev : k.events) st.event(ev >> 8, (unsigned char)(ev & 0xff));
+			std::vector<uint64_t>().swap(k.events);
+		}
+		const bool file_ends = piece + 1 == pieces.size() || pieces[piece + 1].file != pc.file;
+		if (file_ends) st.end_of_file(h->files[pc.file].base + h->files[pc.file].size);
+		if (st.multiline || refuse || out > out_cap) { drain(); return 1; }
+		// ---- new rows of the segment table, then the piece itself, in order on the copy stream
+		const size_t seg_now = h->seg_len.size();
+		if (seg_now > seg_before)
+		{
+			const size_t n = seg_now - seg_before;
+			CU(h, cudaMemcpyAsync(h->d_seg_in.as<uint64_t>() + seg_before, h->seg_in.data() + seg_before, n * 8, cudaMemcpyHostToDevice, h->copy_stream));
+			CU(h, cudaMemcpyAsync(h->d_seg_out.as<uint64_t>() + seg_before, h->seg_out.data() + seg_before, n * 8, cudaMemcpyHostToDevice, h->copy_stream));
+			CU(h, cudaMemcpyAsync(h->d_seg_out.as<uint64_t>() + seg_now, &out, 8, cudaMemcpyHostToDevice, h->copy_stream));
+			CU(h, cudaMemcpyAsync(h->d_seg_len.as<uint32_t>() + seg_before, h->seg_len.data() + seg_before, n * 4, cudaMemcpyHostToDevice, h->copy_stream));
+			h2d_bytes += n * 20 + 8;
+		}
+		{
+			const uint64_t bytes = (pc.len + 31) / 32 * 8;
+			CU(h, cudaMemcpyAsync(h->d_packed.as<char>() + pc.pos / 4, (const char*)h->p_stage.p + pc.pos / 4, bytes, cudaMemcpyHostToDevice, h->copy_stream));
+			h2d_bytes += bytes;
+		}
+		CU(h, cudaEventRecord(h->piece_events[piece], h->copy_stream));
+		if (piece + 1 == pieces.size()) CU(h, cudaEventRecord(h->ev[1], h->copy_stream));
+		// ---- K1 .. K3a on the segments this piece completed (a read is only known once its line has ended: all of them)
+		const cudaStream_t fs = h->front_stream[piece & 1];
+		CU(h, cudaStreamWaitEvent(fs, h->piece_events[piece], 0));
+		const uint32_t g_end = (uint32_t)seg_now;
+		if (g_end == g_done) continue;
+		launches += launch_front(h, g_done, g_end - g_done, false, fs);
+		CU(h, cudaEventRecord(h->front_events[piece], fs));
+		CU(h, cudaStreamWaitEvent(h->stream, h->front_events[piece], 0));
+		launch_scan(h, g_done, g_end, launches);
+		g_done = g_end;
+		if (!sized)
+		{
+			uint64_t n0 = 0;
+			CU(h, cudaMemcpyAsync(&n0, h->d_sel_begin.as<uint64_t>() + g_end, 8, cudaMemcpyDeviceToHost, h->stream));
+			CU(h, cudaStreamSynchronize(h->stream));
+			h->stats.d2h_bytes += 8;
+			const double per_byte = (double)n0 / (double)std::max<uint64_t>(pc.pos + pc.len, 1);
+			const uint64_t est = (uint64_t)(per_byte * (double)n_image) + 1;
+			if (int rc = ensure_instances(h, std::max<uint64_t>(est + est / 4 + 4096, h->inst_cap))) return rc;
+			if (want_table)
+			{
+				const uint64_t slots = std::max<uint64_t>(next_pow2(std::max<uint64_t>(2 * est, 1024)), h->prm.table_slots ? next_pow2(h->prm.table_slots) : 0);
+				if (int rc = clear_tables(h, slots, launches)) return rc;
+				h->stats.table_slots = slots;
+			}
+			sized = true;
+		}
+		launch_list_hash(h, g_tail, g_end, 0, launches);
+		launch_tables(h, g_tail, g_end, 0, launches, false);
+		g_tail = g_end;
+	}
+	if (pieces.empty()) CU(h, cudaEventRecord(h->ev[1], h->copy_stream));
+	tick(h, 9);
+	pool.finish();
+	const uint32_t n_seg = (uint32_t)h->seg_len.size();
+	h->total_out = out;
+	h->n_reads = h->read_off.size(); h->n_bases = n_image;
+	h->image_files.swap(h->files);
+	h->files.clear();
+	// ---- one read-back decides whether the pipelined result stands
+	unsigned long long c8[8] = { 0 };
+	uint64_t n_inst = 0;
+	CU(h, cudaMemcpyAsync(c8, ctr, sizeof(c8), cudaMemcpyDeviceToHost, h->stream));
+	if (n_seg) CU(h, cudaMemcpyAsync(&n_inst, h->d_sel_begin.as<uint64_t>() + n_seg, 8, cudaMemcpyDeviceToHost, h->stream));
+	CU(h, cudaStreamSynchronize(h->stream));
+	CU(h, cudaStreamSynchronize(h->copy_stream));
+	CU(h, cudaGetLastError());
+	h->stats.d2h_bytes += sizeof(c8) + 8;
+	h->stats.h2d_bytes += h2d_bytes;
+	h->stats.ms_upload = elapsed(h, 0, 1);
+	h->stats.ms_pack = 0;
+	h->stats.reads = h->n_reads; h->stats.raw_bases = raw_bases; h->stats.nonacgt = bad.size();
+	h->nonacgt_count = bad.size();
+	h->pending.clear();
+	if (!bad.empty())
+	{
+		// rare: cut the reads at the characters outside ACGT and run the resident image again; the few reads that hold such
+		// characters are read back from the file (the collapse step needs their text, build_segments)
+		std::sort(bad.begin(), bad.end());
+		std::string text;
+		build_segments(h, bad, [&](uint64_t r) -> const char*
+		{
+			const auto& f = h->image_files[h->name_file[r]];
+			const uint64_t len = h->read_end[r] - h->read_off[r];
+			text.resize(len);
+			if (len && pread(f.fd, &text[0], len, (off_t)(h->read_off[r] - f.base)) != (ssize_t)len) std::fill(text.begin(), text.end(), 'N');
+			return text.data();
+		});
+		if (int rc = upload_segments(h)) return rc;
+		CU(h, cudaStreamSynchronize(h->stream));
+		h->stats.segments = h->seg_len.size();
+		h->resident = true;
+		return mbgfe_process(h);
+	}
+	h->stats.segments = n_seg;
+	h->resident = true;
+	if ((n_seg && !sized) || g_tail != n_seg || c8[CTR_PALINDROME] || c8[CTR_OVERFLOW] || n_inst > h->inst_cap)
+	{
+		tick(h, 4); tick(h, 5);
+		h->stats.table_grows += (c8[CTR_OVERFLOW] || n_inst > h->inst_cap) ? 1 : 0;
+		return process_tail(h, launches);
+	}
+	if (!n_seg) { if (int rc = ensure_instances(h, std::max<uint64_t>(4096, h->inst_cap))) return rc; if (want_table) { if (int rc = clear_tables(h, 1024, launches)) return rc; h->stats.table_slots = 1024; CU(h, cudaStreamSynchronize(h->stream)); } }
+	h->n_inst = n_inst;
+	h->stats.distinct = want_table ? c8[CTR_DISTINCT] : 0;
+	h->stats.distinct_edges = (want_table && h->edge_slots) ? c8[CTR_EDGES] : 0;
+	h->have_table = want_table;
+	finish_stats(h, n_inst, launches, false);
+	return 0;
+}
 
 // part table: per-segment results -> reference-shaped parts (MBG/ReadHelper.h:81-88, 838-862, 976-977, 1058-1059)
 int export_parts(mbgfe* h)
@@ -1157,7 +1504,7 @@ int export_parts(mbgfe* h)
 		mbgfe_part p;
 		p.read_idx = h->seg_read[g];
 		p.part_offset = offset;
-		p.raw_len = (uint32_t)(h->read_off[p.read_idx + 1] - h->read_off[p.read_idx]);
+		p.raw_len = (uint32_t)(read_end_of(h, p.read_idx) - h->read_off[p.read_idx]);
 		p.n_codes = c2;
 		p.code_begin = code_cursor;
 		p.pose_begin = pose_cursor;
@@ -1612,6 +1959,7 @@ int mbgfe_thin_unitigs(mbgfe* h)
 	if (!h->have_unitigs) return fail(h, MBGFE_E_STATE, "mbgfe_thin_unitigs needs mbgfe_build_unitigs first");
 	const uint64_t n_kept = h->n_kept, n_pos = h->n_unitig_nodes, n_fedges = h->n_fedges;
 	uint32_t launches = 0;
+	h->have_thin = false; h->have_threads = false;
 	tick(h, 12);
 	if (int rc = ensure(h, h->d_thin, n_kept + 64)) return rc;
 	if (int rc = ensure(h, h->d_thin_pos, (n_kept + 1) * 4)) return rc;
@@ -1649,9 +1997,48 @@ int mbgfe_thin_unitigs(mbgfe* h)
 		MBGFE_LAUNCH(k_thin_flags, grid_for(h, n_pos), 256, 0, h->stream, h->d_u_nodes.as<uint32_t>(), n_pos, mark, h->d_thin.as<uint8_t>());
 		launches += 2;
 	}
+	// ---- apply it (MBG/MBG.cpp:1166-1184): reads.filter(kept) into the other scratch set, the unitigs renumbered, the new overlaps
+	uint64_t n_thin = 0, n_tedges = 0, n_tpos = 0;
+	if (n_pos)
+	{
+		uint32_t* mark = h->d_g_deg.as<uint32_t>();
+		if (int rc = ensure(h, h->d_thin_scan, (n_pos + 2) * 8)) return rc;
+		if (int rc = ensure(h, h->d_tpos, (n_kept + 1) * 4)) return rc;
+		if (int rc = device_scan(h, mark, h->d_thin_scan.as<uint64_t>(), (uint32_t)n_pos)) return rc;
+		MBGFE_LAUNCH(k_thin_kept32, grid_for(h, n_kept), 256, 0, h->stream, h->d_thin.as<uint8_t>(), n_kept, h->d_g_kept.as<uint32_t>());
+		launches += 4;
+		if (int rc = ensure(h, h->d_g_newid, (n_kept + 2) * 8)) return rc;
+		if (int rc = scan_kept(h, n_kept, n_thin, launches)) return rc;
+		GList l { h->d_f_hash.as<uint4>(), h->d_f_cov.as<uint32_t>(), h->d_f_tip.as<uint8_t>(), h->d_f_edges.as<EdgeRec>(), h->d_f_orig.as<uint32_t>(), n_kept, n_fedges, 0 };
+		if (int rc = ensure(h, h->d_g_flag, (std::max(n_fedges, n_pos) + 1) * 4)) return rc;
+		if (int rc = ensure(h, h->d_g_at, (std::max(n_fedges, n_pos) + 2) * 8)) return rc;
+		if (int rc = filter_list(h, l, n_thin, launches)) return rc;        // -> the d_t_* set
+		n_tedges = l.m;
+		n_tpos = n_thin;               // every k-mer that stays sits in exactly one unitig position
+		if (int rc = ensure(h, h->d_tu_nodes, (n_tpos + 1) * 4)) return rc;
+		if (int rc = ensure(h, h->d_tu_off, (n_tpos + 1) * 4)) return rc;
+		if (int rc = ensure(h, h->d_tu_unitig, (n_tpos + 1) * 4)) return rc;
+		if (int rc = ensure(h, h->d_tu_begin, (h->n_unitigs + 2) * 8)) return rc;
+		if (int rc = ensure(h, h->d_t_newov, (n_tpos + 1) * sizeof(EdgeRec))) return rc;
+		MBGFE_LAUNCH(k_thin_compact, grid_for(h, n_pos), 256, 0, h->stream, h->d_u_nodes.as<uint32_t>(), n_pos, mark, h->d_thin_scan.as<uint64_t>(), h->d_u_of_node.as<uint32_t>(),
+			h->d_u_begin.as<uint64_t>(), h->d_g_newid.as<uint64_t>(), h->d_thin_pos.as<uint32_t>(), h->d_tpos.as<uint32_t>(), h->d_tu_nodes.as<uint32_t>(), h->d_tu_off.as<uint32_t>(),
+			h->d_tu_unitig.as<uint32_t>());
+		MBGFE_LAUNCH(k_thin_begins, grid_for(h, h->n_unitigs + 1), 256, 0, h->stream, h->d_u_begin.as<uint64_t>(), h->n_unitigs, h->d_thin_scan.as<uint64_t>(), h->d_tu_begin.as<uint64_t>());
+		MBGFE_LAUNCH(k_thin_overlaps, grid_for(h, n_tpos), 256, 0, h->stream, h->d_tu_nodes.as<uint32_t>(), h->d_tu_off.as<uint32_t>(), h->d_tu_unitig.as<uint32_t>(),
+			h->d_tu_begin.as<uint64_t>(), n_tpos, h->prm.k, h->d_t_newov.as<EdgeRec>());
+		launches += 3;
+	}
 	tick(h, 13);
 	fetch(h, h->h_thin, h->d_thin, n_kept);
 	fetch(h, h->h_thin_pos, h->d_thin_pos, n_kept);
+	fetch(h, h->h_t_hash, h->d_t_hash, n_thin);
+	fetch(h, h->h_t_cov, h->d_t_cov, n_thin);
+	fetch(h, h->h_t_tip, h->d_t_tip, n_thin);
+	fetch(h, h->h_t_edges, h->d_t_edges, n_tedges);
+	fetch(h, h->h_tu_nodes, h->d_tu_nodes, n_tpos);
+	if (n_pos) fetch(h, h->h_tu_begin, h->d_tu_begin, h->n_unitigs + 1); else h->h_tu_begin.assign(h->n_unitigs + 1, 0);
+	fetch(h, h->h_t_newov, h->d_t_newov, n_tpos - std::min<uint64_t>(n_tpos, h->n_unitigs));
+	h->n_thin = n_thin; h->n_tedges = n_tedges; h->n_tpos = n_tpos;
 	CU(h, cudaStreamSynchronize(h->stream));
 	CU(h, cudaGetLastError());
 	h->stats.ms_unitigs = elapsed(h, 12, 13);
@@ -1682,10 +2069,11 @@ int mbgfe_thread_reads(mbgfe* h)
 		if (n_kept) { MBGFE_LAUNCH(k_invert_orig, grid_for(h, n_kept), 256, 0, h->stream, h->d_f_orig.as<uint32_t>(), n_kept, h->d_th_final.as<uint32_t>()); launches++; }
 		MBGFE_LAUNCH(k_thread_locate, grid_for(h, n_inst), 256, 0, h->stream, h->d_inst_slot.as<uint32_t>(), h->d_inst_hash.as<uint64_t>(), n_inst, h->d_nodes.as<NodeSlot>(),
 			h->d_th_final.as<uint32_t>(), h->d_u_of_node.as<uint32_t>(), h->d_u_fw.as<uint32_t>(), h->d_u_pos.as<uint32_t>(), h->d_u_begin.as<uint64_t>(),
-			h->d_th_node.as<uint32_t>(), h->d_th_unitig.as<uint32_t>(), h->d_th_upos.as<uint32_t>(), h->d_th_urest.as<uint32_t>());
+			h->have_thin ? h->d_thin.as<uint8_t>() : (const uint8_t*)nullptr, h->have_thin ? h->d_tpos.as<uint32_t>() : (const uint32_t*)nullptr,
+			h->have_thin ? h->d_thin_scan.as<uint64_t>() : (const uint64_t*)nullptr, h->d_th_node.as<uint32_t>(), h->d_th_unitig.as<uint32_t>(), h->d_th_upos.as<uint32_t>(), h->d_th_urest.as<uint32_t>());
 		MBGFE_LAUNCH(k_thread_steps, grid_for(h, n_inst), 256, 0, h->stream, h->d_th_node.as<uint32_t>(), h->d_th_unitig.as<uint32_t>(), h->d_th_upos.as<uint32_t>(),
 			h->d_th_urest.as<uint32_t>(), h->d_inst_flag.as<uint8_t>(), h->d_inst_pos.as<uint32_t>(), h->d_inst_slot.as<uint32_t>(), h->d_inst_hash.as<uint64_t>(), n_inst,
-			h->d_edges.as<EdgeSlot>(), h->edge_slots - 1, h->prm.k, h->unitig_min_cov, h->d_th_step.as<uint8_t>());
+			h->d_edges.as<EdgeSlot>(), h->edge_slots - 1, h->prm.k, h->unitig_min_cov, h->have_thin ? h->d_thin_pos.as<uint32_t>() : (const uint32_t*)nullptr, h->d_th_step.as<uint8_t>());
 		launches += 2;
 	}
 	tick(h, 13);
@@ -1728,6 +2116,11 @@ uint64_t mbgfe_count(mbgfe* h, int what)
 		case MBGFE_UNITIG_EDGES: return h->have_unitigs ? h->n_uedges : 0;
 		case MBGFE_INST_UNITIG: case MBGFE_INST_UNITIG_POS: case MBGFE_INST_UNITIG_REST: case MBGFE_INST_STEP: return h->have_threads ? h->h_th_step.size() : 0;
 		case MBGFE_F_NODE_THIN: case MBGFE_F_NODE_UNITIG_OFFSET: return h->have_thin ? h->h_thin.size() : 0;
+		case MBGFE_T_NODE_HASHES: case MBGFE_T_NODE_COVERAGE: case MBGFE_T_NODE_TIP: return h->have_thin ? h->n_thin : 0;
+		case MBGFE_T_EDGES: return h->have_thin ? h->n_tedges : 0;
+		case MBGFE_T_UNITIG_BEGIN: return h->have_thin ? h->h_tu_begin.size() : 0;
+		case MBGFE_T_UNITIG_NODES: return h->have_thin ? h->n_tpos : 0;
+		case MBGFE_T_NEW_OVERLAPS: return h->have_thin ? h->h_t_newov.size() : 0;
 	}
 	return 0;
 }
@@ -1776,10 +2169,21 @@ const void* mbgfe_data(mbgfe* h, int what)
 				default: return h->h_th_step.data();
 			}
 	}
-	if (what == MBGFE_F_NODE_THIN || what == MBGFE_F_NODE_UNITIG_OFFSET)
+	if (what == MBGFE_F_NODE_THIN || what == MBGFE_F_NODE_UNITIG_OFFSET || (what >= MBGFE_T_NODE_HASHES && what <= MBGFE_T_NEW_OVERLAPS))
 	{
 		if (!h->have_thin) { fail(h, MBGFE_E_STATE, "thinning requested before mbgfe_thin_unitigs"); return nullptr; }
-		return what == MBGFE_F_NODE_THIN ? (const void*)h->h_thin.data() : (const void*)h->h_thin_pos.data();
+		switch (what)
+		{
+			case MBGFE_F_NODE_THIN: return h->h_thin.data();
+			case MBGFE_F_NODE_UNITIG_OFFSET: return h->h_thin_pos.data();
+			case MBGFE_T_NODE_HASHES: return h->h_t_hash.data();
+			case MBGFE_T_NODE_COVERAGE: return h->h_t_cov.data();
+			case MBGFE_T_NODE_TIP: return h->h_t_tip.data();
+			case MBGFE_T_EDGES: return h->h_t_edges.data();
+			case MBGFE_T_UNITIG_BEGIN: return h->h_tu_begin.data();
+			case MBGFE_T_UNITIG_NODES: return h->h_tu_nodes.data();
+			default: return h->h_t_newov.data();
+		}
 	}
 	fail(h, MBGFE_E_PARAM, "unknown result array %d", what);
 	return nullptr;
@@ -2042,29 +2446,25 @@ int mbgfe_kat_kmer_hash(mbgfe* h, const uint16_t* codes, uint32_t k, mbgfe_hash1
 {
 	if (!h || !codes || !out) return MBGFE_E_PARAM;
 	if (k == 0) return fail(h, MBGFE_E_PARAM, "k must be positive");
-	DevBuf d_codes, d_rrc, d_misc;
-	int rc = ensure(h, d_codes, (size_t)k * 2 + 64);
-	if (!rc) rc = ensure(h, d_rrc, (size_t)k * 2 + 64);
+	DevBuf d_codes, d_misc;
+	int rc = ensure(h, d_codes, (size_t)k * 2 + 256);
 	if (!rc) rc = ensure(h, d_misc, 128);
-	if (rc) { release(d_codes); release(d_rrc); release(d_misc); return rc; }
-	// one synthetic instance: a single segment whose slot is exactly the k codes, position 0
-	const uint64_t bases[2] = { 0, k };
+	if (rc) { release(d_codes); release(d_misc); return rc; }
+	// one synthetic instance: a single segment whose slot holds the k codes (slots are multiples of 64 codes), position 0
+	const uint64_t bases[2] = { 0, ((uint64_t)k + 1 + 63) & ~63ull };
 	const uint32_t zero32 = 0;
 	cudaMemsetAsync(d_codes.p, 0, d_codes.cap, h->stream);
-	cudaMemsetAsync(d_rrc.p, 0, d_rrc.cap, h->stream);
 	cudaMemcpyAsync(d_codes.p, codes, (size_t)k * 2, cudaMemcpyHostToDevice, h->stream);
 	cudaMemcpyAsync(d_misc.as<char>() + 0, bases, 16, cudaMemcpyHostToDevice, h->stream);   // seg_out_base[0..1]
 	cudaMemcpyAsync(d_misc.as<char>() + 16, &zero32, 4, cudaMemcpyHostToDevice, h->stream);  // inst_pos[0]
-	cudaMemcpyAsync(d_misc.as<char>() + 20, &zero32, 4, cudaMemcpyHostToDevice, h->stream);  // inst_seg[0]
 	const uint64_t range[2] = { 0, 1 };
 	cudaMemcpyAsync(d_misc.as<char>() + 64, range, 16, cudaMemcpyHostToDevice, h->stream);   // instance range [0, 1)
-	MBGFE_LAUNCH(k_revcomp_codes, (k + 255) / 256, 256, 0, h->stream, d_codes.as<uint16_t>(), k, h->tab_comp.as<uint16_t>(), d_rrc.as<uint16_t>());
-	MBGFE_LAUNCH(k_kmer_hash, 1, HASH_NT, 0, h->stream, (const uint64_t*)d_misc.p, d_codes.as<uint16_t>(), d_rrc.as<uint16_t>(), (const uint32_t*)(d_misc.as<char>() + 16),
+	MBGFE_LAUNCH(k_kmer_hash, 1, HASH_NT, 0, h->stream, (const uint64_t*)d_misc.p, d_codes.as<uint16_t>(), h->tab_comp.as<uint16_t>(), (const uint32_t*)(d_misc.as<char>() + 16),
 		(const uint64_t*)(d_misc.as<char>() + 64), (uint64_t)1, (uint64_t*)(d_misc.as<char>() + 32), k);
 	cudaStreamSynchronize(h->stream);
 	uint64_t res[2] = { 0, 0 };
 	cudaError_t e = cudaMemcpy(res, d_misc.as<char>() + 32, 16, cudaMemcpyDeviceToHost);
-	release(d_codes); release(d_rrc); release(d_misc);
+	release(d_codes); release(d_misc);
 	if (e != cudaSuccess) return fail(h, MBGFE_E_CUDA, "kat kernel failed: %s", cudaGetErrorString(e));
 	out->lo = res[0]; out->hi = res[1];
 	return 0;

@@ -17,6 +17,7 @@ PARTS, CODES, POSES, POSITIONS, HASHES, NODE_HASHES, NODE_COVERAGE, NODE_TIP, ED
 NODE_KEPT, F_NODE_HASHES, F_NODE_COVERAGE, F_NODE_TIP, F_EDGES, UNITIG_BEGIN, UNITIG_NODES, F_NODE_UNITIG, UNITIG_EDGES = range(9, 18)
 INST_UNITIG, INST_UNITIG_POS, INST_UNITIG_REST, INST_STEP = range(18, 22)
 F_NODE_THIN, F_NODE_UNITIG_OFFSET = 22, 23
+T_NODE_HASHES, T_NODE_COVERAGE, T_NODE_TIP, T_EDGES, T_UNITIG_BEGIN, T_UNITIG_NODES, T_NEW_OVERLAPS = range(24, 31)
 UNITIG_ONECOV_HEURISTIC = 1      # mbgfe_build_unitigs_ex flag (include/mbgfe.h)
 
 PART_DTYPE = np.dtype([
@@ -268,6 +269,12 @@ class MbgFrontEnd:
         unitig) per filtered node"""
         self._check(self.lib.mbgfe_thin_unitigs(self.handle))
         return self._data(F_NODE_THIN, "u1"), self._data(F_NODE_UNITIG_OFFSET, "<u4")
+
+    def thinned(self):
+        """the list, unitigs and new sequence overlaps after the thinning was applied (MBG/MBG.cpp:1166-1184); needs thin_unitigs()"""
+        return dict(node_hash=self._data(T_NODE_HASHES, "<u8", 2).reshape(-1, 2), node_cov=self._data(T_NODE_COVERAGE, "<u4"), node_tip=self._data(T_NODE_TIP, "u1"),
+                    edges=self._data(T_EDGES, "<u4", 6).reshape(-1, 6), unitig_begin=self._data(T_UNITIG_BEGIN, "<u8"), unitig_nodes=self._data(T_UNITIG_NODES, "<u4"),
+                    new_overlaps=self._data(T_NEW_OVERLAPS, "<u4", 6).reshape(-1, 6))
 
     def read_paths(self):
         """the ReadPath list of getReadPaths (MBG/MBG.cpp:1235-1251) put together from thread_reads() the way
