@@ -32,6 +32,20 @@ UnitigGraph getUnitigGraph(HashList& hashlist, const size_t minCoverage, const d
 UnitigGraph getUnitigs(const UnitigGraph& oldgraph); // MBG.cpp:782
 void filterKmersToUnitigKmers(UnitigGraph& unitigs, HashList& reads, const size_t kmerSize, const bool filterWithinUnitig); // MBG.cpp:1065
 void sortKmersByHashes(UnitigGraph& unitigs, HashList& reads); // MBG.cpp:1059
+#include "UnitigResolver.h"
+#include "HPCConsensus.h"
+#include "StringIndex.h"
+#include "DumbSelect.h"
+#include "CompressedSequence.h"
+struct AssemblyStats { size_t nodes, edges, size, N50, approxKmers; };     // MBG.cpp:34-42 (defined in the .cpp only)
+std::vector<ReadPath> getReadPaths(const UnitigGraph& graph, const HashList& hashlist, const size_t numThreads, const ReadpartIterator& partIterator, const size_t kmerSize); // MBG.cpp:1235
+void verifyEdgeConsistency(const UnitigGraph& unitigs, const HashList& hashlist, const StringIndex& stringIndex, const std::vector<CompressedSequenceType>& unitigSequences, const size_t kmerSize); // MBG.cpp:1220
+std::vector<double> getRawKmerCoverages(const UnitigGraph& unitigs, const std::vector<CompressedSequenceType>& unitigSequences, const HashList& reads, const size_t kmerSize); // MBG.cpp:1253
+AssemblyStats writeGraph(const UnitigGraph& unitigs, const std::string& filename, const HashList& hashlist, const std::vector<CompressedSequenceType>& unitigSequences, const StringIndex& stringIndex, const size_t kmerSize, const std::vector<double>& unitigRawKmerCoverages, const std::string& nodeNamePrefix); // MBG.cpp:941
+std::vector<DumbSelect> getUnitigExpandedPoses(const HashList& hashlist, const UnitigGraph& unitigs, const std::vector<CompressedSequenceType>& unitigSequences, const StringIndex& stringIndex); // MBG.cpp:1514
+void sortPaths(std::vector<ReadPath>& readPaths); // MBG.cpp:1398
+void writePaths(const HashList& hashlist, const UnitigGraph& unitigs, const std::vector<CompressedSequenceType>& unitigSequences, const StringIndex& stringIndex, const std::vector<DumbSelect>& unitigExpandedPoses, const std::vector<ReadPath>& readPaths, const size_t kmerSize, const std::string& outputSequencePaths, const std::string& nodeNamePrefix); // MBG.cpp:115
+void printUnitigKmerCount(const UnitigGraph& unitigs); // MBG.cpp:1049
 
 namespace {
 
@@ -483,6 +497,106 @@ double refshim_time_file_digest(int mode, uint64_t k, uint64_t w, const char* pa
 	auto t1 = std::chrono::steady_clock::now();
 	if (digest10) hashlist_digest(list, digest10);
 	return std::chrono::duration<double>(t1 - t0).count();
+}
+
+
+// ---------------------------------------------------------------------------------------------------------------------------
+// T4: the tables of libmbgfe handed to the reference's OWN back end -- the binding INTEGRATION.md 1 describes,
+// compiled.  The reference's containers are filled through their public members only (HashList::addNode / coverage.set /
+// setTipKmer / setEdgeCoverage / addSequenceOverlap, MBG/HashList.h:15-48; UnitigGraph's public vectors and setters,
+// MBG/UnitigGraph.h:13-38) and the rest of runMBG (MBG/MBG.cpp:1573-1628) runs unchanged, function by function, writing the GFA
+// and the GAF.  Nodes arrive in ascending canonical-hash order (MBGFE_NODE_* / MBGFE_T_*), i.e. already as sortByHash leaves them.
+//
+//   stage 0  replaces loadReadsAsHashesMultithread (MBG.cpp:1570): HashList <- node table + edge table; the reference continues
+//            from getUnitigGraph (MBG.cpp:1573)
+//   stage 1  replaces everything up to sortKmersByHashes (MBG.cpp:1570-1581): HashList <- thinned list (+ new overlaps),
+//            UnitigGraph <- thinned unitigs + unitig edges; the reference continues from getReadPaths (MBG.cpp:1586)
+// Passes 4 and 5 (read paths, unitig sequences) read the FASTA through the reference's own iterator.
+static void fill_hashlist(HashList& reads, const uint64_t* node_hash, const uint32_t* node_cov, const uint8_t* node_tip, uint64_t n_nodes, const uint32_t* edges6, uint64_t n_edges)
+{
+	for (uint64_t i = 0; i < n_nodes; i++)
+	{
+		const HashType hsh = ((HashType)node_hash[2 * i + 1] << 64) + (HashType)node_hash[2 * i];      // canonical: smaller than its swapped form
+		const std::pair<size_t, bool> node = reads.addNode(hsh);
+		if (node.first != i || !node.second) abort();
+		reads.coverage.set(i, node_cov[i]);
+		if (node_tip[i]) reads.setTipKmer(i);
+	}
+	for (uint64_t e = 0; e < n_edges; e++)
+	{
+		const uint32_t* r = edges6 + 6 * e;
+		const std::pair<size_t, bool> from { r[0], r[1] != 0 }, to { r[2], r[3] != 0 };
+		reads.addSequenceOverlap(from, to, r[5]);
+		reads.setEdgeCoverage(from, to, r[4]);
+	}
+}
+
+int refshim_backend(int stage, int mode, uint64_t k, uint64_t w, const char* fasta, uint64_t min_cov, double min_unitig_cov, uint64_t max_resolve, uint64_t max_uncond_resolve,
+	int guesswork, int copycount_heuristic, int only_local_resolve, int do_cleaning,
+	const uint64_t* node_hash, const uint32_t* node_cov, const uint8_t* node_tip, uint64_t n_nodes, const uint32_t* edges6, uint64_t n_edges,
+	const uint32_t* new_overlaps6, uint64_t n_new_overlaps, const uint64_t* unitig_begin, const uint32_t* unitig_nodes, uint64_t n_unitigs, const uint32_t* unitig_edges6, uint64_t n_unitig_edges,
+	const char* out_gfa, const char* out_gaf)
+{
+	std::vector<std::string> files { std::string(fasta) };
+	ReadpartIterator partIterator { (size_t)k, (size_t)w, (ErrorMasking)mode, 1, files, false, "" };
+	HashList reads { (size_t)k };
+	std::ostringstream log;
+	fill_hashlist(reads, node_hash, node_cov, node_tip, n_nodes, edges6, n_edges);
+	UnitigGraph unitigs;
+	if (stage == 0)
+	{
+		unitigs = getUnitigGraph(reads, min_cov, min_unitig_cov, false, (min_unitig_cov >= 2) && (max_resolve > 0) && guesswork);      // MBG.cpp:1573
+		if (min_unitig_cov > (double)min_cov) unitigs = getUnitigs(unitigs.filterUnitigsByCoverage(min_unitig_cov, false));
+		filterKmersToUnitigKmers(unitigs, reads, k, true);
+		sortKmersByHashes(unitigs, reads);
+	}
+	else
+	{
+		for (uint64_t e = 0; e < n_new_overlaps; e++)      // MBG.cpp:1178-1183
+		{
+			const uint32_t* r = new_overlaps6 + 6 * e;
+			reads.addSequenceOverlap(std::make_pair((size_t)r[0], r[1] != 0), std::make_pair((size_t)r[2], r[3] != 0), r[5]);
+		}
+		unitigs.unitigs.resize(n_unitigs);
+		unitigs.unitigCoverage.resize(n_unitigs);
+		unitigs.edges.resize(n_unitigs);
+		unitigs.edgeCov.resize(n_unitigs);
+		unitigs.edgeOvlp.resize(n_unitigs);
+		unitigs.leftClip.resize(n_unitigs, 0);       // as startUnitig leaves them (MBG.cpp:356-357)
+		unitigs.rightClip.resize(n_unitigs, 0);
+		for (uint64_t u = 0; u < n_unitigs; u++)
+			for (uint64_t j = unitig_begin[u]; j < unitig_begin[u + 1]; j++)
+			{
+				unitigs.unitigs[u].emplace_back(unitig_nodes[j] >> 1, (unitig_nodes[j] & 1) != 0);
+				unitigs.unitigCoverage[u].push_back(node_cov[unitig_nodes[j] >> 1]);
+			}
+		for (uint64_t e = 0; e < n_unitig_edges; e++)      // as the last loop of getUnitigGraph leaves them (MBG.cpp:764-779)
+		{
+			const uint32_t* r = unitig_edges6 + 6 * e;
+			const std::pair<size_t, bool> from { r[0], r[1] != 0 }, to { r[2], r[3] != 0 };
+			unitigs.edges.addEdge(from, to);
+			unitigs.edges.addEdge(reverse(to), reverse(from));
+			unitigs.setEdgeCoverage(from, to, r[4]);
+			unitigs.setEdgeOverlap(from, to, 0);
+		}
+	}
+	std::vector<ReadPath> readPaths = getReadPaths(unitigs, reads, 1, partIterator, k);      // MBG.cpp:1586
+	if (max_resolve > 0)
+		std::tie(unitigs, readPaths) = resolveUnitigs(unitigs, reads, readPaths, partIterator, min_unitig_cov, k, max_resolve, max_uncond_resolve, false, guesswork != 0,
+			copycount_heuristic != 0, only_local_resolve != 0, do_cleaning != 0, log);
+	std::vector<CompressedSequenceType> unitigSequences;
+	StringIndex stringIndex;
+	std::tie(unitigSequences, stringIndex) = getHPCUnitigSequences(reads, unitigs, readPaths, k, partIterator, 1);
+	verifyEdgeConsistency(unitigs, reads, stringIndex, unitigSequences, k);
+	std::vector<double> rawCov = getRawKmerCoverages(unitigs, unitigSequences, reads, k);
+	writeGraph(unitigs, out_gfa, reads, unitigSequences, stringIndex, k, rawCov, "");
+	if (out_gaf && out_gaf[0])
+	{
+		std::vector<DumbSelect> expandedPoses = getUnitigExpandedPoses(reads, unitigs, unitigSequences, stringIndex);
+		sortPaths(readPaths);
+		writePaths(reads, unitigs, unitigSequences, stringIndex, expandedPoses, readPaths, k, out_gaf, "");
+	}
+	return 0;
 }
 
 // Known-answer helpers (SURVEY.md 8c "tables", "FastHasher", "hash(vector)", "msat" rows).

@@ -71,3 +71,39 @@ def check_thinning(fe_result_unitigs, thin, offsets, want, k, what=""):
             assert ov.get((f, ffw, t, tfw)) == k - (int(offsets[y >> 1]) - int(offsets[x >> 1])), f"{what}: overlap of neighbours {x}, {y} in unitig {i}"
             checked += 1
     return checked
+
+
+def run_thinned_pass(mode, k, w, reads, min_cov, min_unitig_cov, oracle, library=None, one_cov=True, what=""):
+    """runMBG's pass 3 + 4 under MBG's defaults on the device: table, getUnitigGraph, filterKmersToUnitigKmers APPLIED
+    (MBGFE_T_*: reads.filter(kept), renumbered unitigs, new sequence overlaps, MBG/MBG.cpp:1065-1185) and getReadPaths on the
+    thinned list (MBG/MBG.cpp:1586) -- against the oracle's sequential restatement of the same sequence (pinned on the
+    reference in tests/test_oracle.py::test_unitig_kmer_thinning_equals_reference).  Returns the number of read paths compared."""
+    import numpy as np
+    from oracle_lib import ReadPaths, UnitigResult, compare_paths, compare_unitigs, sorted_edges
+    fe = MbgFrontEnd(k, w, mode, library=library)
+    try:
+        if isinstance(reads, tuple):
+            fe.add_reads(*reads)
+        else:
+            fe.add_read_list(reads)
+        fe.run()
+        fe.build_unitigs(min_cov, min_unitig_cov, one_cov_heuristic=one_cov)
+        fe.thin_unitigs()
+        th = fe.thinned()
+        rp = fe.read_paths()
+    finally:
+        fe.close()
+    _, want = oracle.run_unitigs(mode, k, w, reads, min_cov, min_unitig_cov, one_cov=one_cov, thin=True, paths=True)
+    assert np.array_equal(th["node_hash"], want.node_hash) and np.array_equal(th["node_cov"], want.node_cov) and np.array_equal(th["node_tip"], want.node_tip), f"{what}: thinned list"
+    assert np.array_equal(sorted_edges(th["edges"]), sorted_edges(want.edges)), f"{what}: edges of the thinned list"
+    got = UnitigResult(kept=None, node_hash=th["node_hash"], node_cov=th["node_cov"], node_tip=th["node_tip"], edges=th["edges"],
+                       unitig_begin=th["unitig_begin"], unitig_nodes=th["unitig_nodes"])
+    compare_unitigs(got, UnitigResult({f: want[f] for f in ("kept", "node_hash", "node_cov", "node_tip", "edges", "unitig_begin", "unitig_nodes")}), what)
+    # sequence overlaps: what the edges hold, then the new ones on top (HashList::addSequenceOverlap replaces)
+    ov = {(int(r[0]), int(r[1]), int(r[2]), int(r[3])): int(r[5]) for r in th["edges"]}
+    for r in th["new_overlaps"]:
+        ov[(int(r[0]), int(r[1]), int(r[2]), int(r[3]))] = int(r[5])
+    assert ov == {(int(r[0]), int(r[1]), int(r[2]), int(r[3])): int(r[4]) for r in want.overlaps}, f"{what}: sequence overlaps after the thinning"
+    paths = ReadPaths(heads=rp["heads"], path=rp["path"], poses=rp["poses"])
+    compare_paths(paths, got, want.paths, want, what)
+    return len(want.paths.heads), int(len(th["new_overlaps"]))

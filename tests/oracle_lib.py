@@ -536,3 +536,50 @@ def write_fasta(path, bases, offsets, line=0):
                     f.write(seq[j:j + line] + b"\n")
             else:
                 f.write(seq + b"\n")
+
+
+REF_MBG = os.path.join(ROOT, "oracle", "_ref", "MBG")
+
+
+def reference_cli(fasta, out_gfa, out_gaf, mode, k, w, a, u, r=0, big_r=0, guesswork=False, threads=1, extra=()):
+    """the reference's own executable (oracle/_ref/MBG, built by oracle/Makefile) -> (gfa bytes, gaf bytes)"""
+    cmd = [REF_MBG, "-i", str(fasta), "-o", str(out_gfa), "-k", str(k), "-w", str(w), "-a", str(a), "-u", str(u), "-t", str(threads),
+           "--error-masking=" + mode, "--output-sequence-paths", str(out_gaf), "-r", str(r), "-R", str(big_r)]
+    if guesswork:
+        cmd.append("--do-unsafe-guesswork-resolutions")
+    cmd += list(extra)
+    subprocess.run(cmd, check=True, stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL)
+    return open(out_gfa, "rb").read(), open(out_gaf, "rb").read()
+
+
+def reference_backend(stage, fasta, out_gfa, out_gaf, mode, k, w, a, u, r=0, big_r=0, guesswork=False, *, node_hash, node_cov, node_tip, edges,
+                      new_overlaps=None, unitig_begin=None, unitig_nodes=None, unitig_edges=None):
+    """T4: tables (stage 0) or the thinned list + unitigs (stage 1) handed to the reference's own back end
+    (oracle/ref_shim.cpp:refshim_backend) -> (gfa bytes, gaf bytes)"""
+    lib = C.CDLL(REF_SO)
+    f = lib.refshim_backend
+    f.restype = C.c_int
+    f.argtypes = [C.c_int, C.c_int, C.c_uint64, C.c_uint64, C.c_char_p, C.c_uint64, C.c_double, C.c_uint64, C.c_uint64, C.c_int, C.c_int, C.c_int, C.c_int,
+                  C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p, C.c_uint64,
+                  C.c_void_p, C.c_uint64, C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p, C.c_uint64, C.c_char_p, C.c_char_p]
+    nh = np.ascontiguousarray(node_hash, dtype=np.uint64)
+    nc = np.ascontiguousarray(node_cov, dtype=np.uint32)
+    nt = np.ascontiguousarray(node_tip, dtype=np.uint8)
+    ed = np.ascontiguousarray(edges, dtype=np.uint32).reshape(-1, 6)
+    no = np.ascontiguousarray(new_overlaps if new_overlaps is not None else np.zeros((0, 6)), dtype=np.uint32).reshape(-1, 6)
+    ub = np.ascontiguousarray(unitig_begin if unitig_begin is not None else np.zeros(1), dtype=np.uint64)
+    un = np.ascontiguousarray(unitig_nodes if unitig_nodes is not None else np.zeros(0), dtype=np.uint32)
+    ue = np.ascontiguousarray(unitig_edges if unitig_edges is not None else np.zeros((0, 6)), dtype=np.uint32).reshape(-1, 6)
+    saved = os.dup(2)
+    devnull = os.open(os.devnull, os.O_WRONLY)
+    os.dup2(devnull, 2)
+    try:
+        rc = f(stage, MODES[mode], k, w, str(fasta).encode(), a, float(u), r, big_r, 1 if guesswork else 0, 0, 0, 1,
+               nh.ctypes.data, nc.ctypes.data, nt.ctypes.data, len(nc), ed.ctypes.data, len(ed),
+               no.ctypes.data, len(no), ub.ctypes.data, un.ctypes.data, len(ub) - 1, ue.ctypes.data, len(ue), str(out_gfa).encode(), str(out_gaf).encode())
+    finally:
+        os.dup2(saved, 2)
+        os.close(saved)
+        os.close(devnull)
+    assert rc == 0
+    return open(out_gfa, "rb").read(), open(out_gaf, "rb").read()

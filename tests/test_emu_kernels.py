@@ -187,6 +187,14 @@ def test_emulated_unitig_kmer_thinning(oracle, emu_library):
     assert check_thinning(ug, thin, off, want, 301, "emu thinning") > 10 and thin.sum() < len(thin)
 
 
+def test_emulated_thinning_applied_and_read_paths_on_the_thinned_list(oracle, emu_library):
+    """row f2 as runMBG takes it by default: read threading AFTER filterKmersToUnitigKmers, on the emulator build"""
+    from fe_helpers import run_thinned_pass
+    reads = workloads.coverage_reads(n_reads=16, error_ppm=4000)
+    n_paths, n_new = run_thinned_pass("collapse-msat", 301, 30, reads, 1, 2, oracle, library=emu_library, what="emu thinned pass")
+    assert n_paths > 5 and n_new > 5
+
+
 @pytest.mark.parametrize("pct,mode,k,w", [("100", "hpc", 63, 33), ("50", "collapse-msat", 301, 30)])
 def test_emulated_host_packed_pieces(oracle, emu_library, monkeypatch, pct, mode, k, w):
     """the two upload routes of mbgfe_run (ASCII + K0 on the device, 2-bit packing on host threads) mixed piece by piece,

@@ -234,3 +234,33 @@ def test_table_digest_equals_reference_hashlist_digest(oracle, reference, tmp_pa
     assert table_digest(run.node_hash, cov, run.node_tip, run.edges)["node_xor"] != mine["node_xor"]
     e = run.edges.copy(); e[0, 1] ^= 1
     assert table_digest(run.node_hash, run.node_cov, run.node_tip, e)["edge_sum"] != mine["edge_sum"]
+
+
+@pytest.mark.parametrize("r,big_r,guesswork", [(0, 0, False), (1500, 400, True)])
+def test_t4_backend_from_tables_gives_the_reference_gfa(oracle, reference, tmp_path, r, big_r, guesswork):
+    """T4 on the checker's side: tables in the library's result layout -- here the oracle's, the GPU test hands
+    over the device's -- put into the reference's own HashList / UnitigGraph (oracle/ref_shim.cpp:refshim_backend) and the rest
+    of runMBG run unchanged give the GFA and GAF of `MBG -t 1` byte for byte.  Stage 0 replaces loadReadsAsHashesMultithread,
+    stage 1 everything up to sortKmersByHashes."""
+    import hashlib
+    from oracle_lib import reference_backend, reference_cli, write_fasta
+    bases, offsets = workloads.as_pair(workloads.coverage_reads(genome_len=40000, n_reads=60, len_min=6000, len_max=10000, error_ppm=2000))
+    fa = tmp_path / "reads.fa"
+    write_fasta(fa, bases, offsets)
+    mode, k, w, a, u = "collapse-msat", 301, 30, 1, 2
+    want_gfa, want_gaf = reference_cli(fa, tmp_path / "ref.gfa", tmp_path / "ref.gaf", mode, k, w, a, u, r, big_r, guesswork)
+    assert want_gfa.count(b"\nS\t") + want_gfa.startswith(b"S\t") > 0 and len(want_gaf) > 0
+    table = oracle.run(mode, k, w, (bases, offsets))
+    gfa0, gaf0 = reference_backend(0, fa, tmp_path / "s0.gfa", tmp_path / "s0.gaf", mode, k, w, a, u, r, big_r, guesswork,
+                                   node_hash=table.node_hash, node_cov=table.node_cov, node_tip=table.node_tip, edges=table.edges)
+    assert hashlib.md5(gfa0).hexdigest() == hashlib.md5(want_gfa).hexdigest(), "stage 0 GFA"
+    assert hashlib.md5(gaf0).hexdigest() == hashlib.md5(want_gaf).hexdigest(), "stage 0 GAF"
+    one_cov = u >= 2 and r > 0 and guesswork
+    _, th = oracle.run_unitigs(mode, k, w, (bases, offsets), a, u, one_cov=one_cov, thin=True)
+    ov = np.zeros((len(th.overlaps), 6), np.uint32)
+    ov[:, :4], ov[:, 5] = th.overlaps[:, :4], th.overlaps[:, 4]
+    gfa1, gaf1 = reference_backend(1, fa, tmp_path / "s1.gfa", tmp_path / "s1.gaf", mode, k, w, a, u, r, big_r, guesswork,
+                                   node_hash=th.node_hash, node_cov=th.node_cov, node_tip=th.node_tip, edges=th.edges, new_overlaps=ov,
+                                   unitig_begin=th.unitig_begin, unitig_nodes=th.unitig_nodes, unitig_edges=th.unitig_edges)
+    assert hashlib.md5(gfa1).hexdigest() == hashlib.md5(want_gfa).hexdigest(), "stage 1 GFA"
+    assert hashlib.md5(gaf1).hexdigest() == hashlib.md5(want_gaf).hexdigest(), "stage 1 GAF"
