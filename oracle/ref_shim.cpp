@@ -18,7 +18,18 @@
 #include <sstream>
 #include <string>
 #include <vector>
+#include <fstream>
+#include <thread>
+#include <unordered_map>
+#include <unordered_set>
+#include <algorithm>
+#include <phmap.h>
+#include <zstr.hpp>
+// the hpc-variant table of ReadpartIterator (ReadHelper.h:250) is private and has no getter; the T4 test has to read it back
+// after the reference's own passes 1 and 2 (refshim_hpc_variants), so this translation unit -- test infrastructure -- opens it
+#define private public
 #include "ReadHelper.h"
+#undef private
 #include "HashList.h"
 #include "FastHasher.h"
 #include "ErrorMaskHelper.h"
@@ -531,14 +542,73 @@ static void fill_hashlist(HashList& reads, const uint64_t* node_hash, const uint
 	}
 }
 
+// Passes 1 and 2 of runMBG under --hpc-variant-onecopy-coverage (MBG.cpp:1554-1567), run by the reference itself: the variant table
+// it leaves in its iterator, flattened the way mbgfe_set_variants takes it (entry e: hash, offset, lengths[len_begin[e] .. len_begin[e+1])).
+// Row f3 (consensus + variant discovery) is not built, so this table is an INPUT of the CUDA path in the T4 test.
+static std::vector<uint64_t> g_var_hash; static std::vector<uint32_t> g_var_offset, g_var_len; static std::vector<uint64_t> g_var_begin;
+uint64_t refshim_hpc_variants(int mode, uint64_t k, uint64_t w, const char* fasta, uint64_t min_cov, double min_unitig_cov, double onecopy_coverage)
+{
+	std::vector<std::string> files { std::string(fasta) };
+	ReadpartIterator partIterator { (size_t)k, (size_t)w, (ErrorMasking)mode, 1, files, false, "" };
+	HashList reads { (size_t)k };
+	std::ostringstream log;
+	loadReadsAsHashesMultithread(reads, k, partIterator, 1, log);
+	auto unitigs = getUnitigGraph(reads, min_cov, min_unitig_cov, false, false);
+	if (min_unitig_cov > (double)min_cov) unitigs = getUnitigs(unitigs.filterUnitigsByCoverage(min_unitig_cov, false));
+	sortKmersByHashes(unitigs, reads);
+	getHpcVariantsAndReadPaths(reads, unitigs, k, partIterator, 1, onecopy_coverage * 1.5, onecopy_coverage * 0.5);
+	g_var_hash.clear(); g_var_offset.clear(); g_var_len.clear(); g_var_begin.assign(1, 0);
+	for (const auto& pair : partIterator.hpcVariants)
+		for (const auto& entry : pair.second)
+		{
+			g_var_hash.push_back((uint64_t)pair.first); g_var_hash.push_back((uint64_t)(pair.first >> 64));
+			g_var_offset.push_back((uint32_t)entry.first);
+			for (size_t len : entry.second) g_var_len.push_back((uint32_t)len);
+			g_var_begin.push_back(g_var_len.size());
+		}
+	return g_var_offset.size();
+}
+const void* refshim_hpc_variants_data(int what)
+{
+	switch (what) { case 0: return g_var_hash.data(); case 1: return g_var_offset.data(); case 2: return g_var_begin.data(); case 3: return g_var_len.data(); }
+	return nullptr;
+}
+uint64_t refshim_hpc_variants_lengths() { return g_var_len.size(); }
+
+int refshim_backend_variants(int stage, int mode, uint64_t k, uint64_t w, const char* fasta, uint64_t min_cov, double min_unitig_cov, uint64_t max_resolve, uint64_t max_uncond_resolve,
+	int guesswork, int copycount_heuristic, int only_local_resolve, int do_cleaning,
+	const uint64_t* node_hash, const uint32_t* node_cov, const uint8_t* node_tip, uint64_t n_nodes, const uint32_t* edges6, uint64_t n_edges,
+	const uint32_t* new_overlaps6, uint64_t n_new_overlaps, const uint64_t* unitig_begin, const uint32_t* unitig_nodes, uint64_t n_unitigs, const uint32_t* unitig_edges6, uint64_t n_unitig_edges,
+	const char* out_gfa, const char* out_gaf,
+	const uint64_t* var_hash, const uint32_t* var_offset, const uint64_t* var_len_begin, const uint32_t* var_len, uint64_t n_var);
+
 int refshim_backend(int stage, int mode, uint64_t k, uint64_t w, const char* fasta, uint64_t min_cov, double min_unitig_cov, uint64_t max_resolve, uint64_t max_uncond_resolve,
 	int guesswork, int copycount_heuristic, int only_local_resolve, int do_cleaning,
 	const uint64_t* node_hash, const uint32_t* node_cov, const uint8_t* node_tip, uint64_t n_nodes, const uint32_t* edges6, uint64_t n_edges,
 	const uint32_t* new_overlaps6, uint64_t n_new_overlaps, const uint64_t* unitig_begin, const uint32_t* unitig_nodes, uint64_t n_unitigs, const uint32_t* unitig_edges6, uint64_t n_unitig_edges,
 	const char* out_gfa, const char* out_gaf)
 {
+	return refshim_backend_variants(stage, mode, k, w, fasta, min_cov, min_unitig_cov, max_resolve, max_uncond_resolve, guesswork, copycount_heuristic, only_local_resolve, do_cleaning,
+		node_hash, node_cov, node_tip, n_nodes, edges6, n_edges, new_overlaps6, n_new_overlaps, unitig_begin, unitig_nodes, n_unitigs, unitig_edges6, n_unitig_edges, out_gfa, out_gaf,
+		nullptr, nullptr, nullptr, nullptr, 0);
+}
+
+// var_*: the hpc-variant table of pass 2 (what runMBG's iterator holds from MBG.cpp:1564 on); passes 4 and 5 need it too
+int refshim_backend_variants(int stage, int mode, uint64_t k, uint64_t w, const char* fasta, uint64_t min_cov, double min_unitig_cov, uint64_t max_resolve, uint64_t max_uncond_resolve,
+	int guesswork, int copycount_heuristic, int only_local_resolve, int do_cleaning,
+	const uint64_t* node_hash, const uint32_t* node_cov, const uint8_t* node_tip, uint64_t n_nodes, const uint32_t* edges6, uint64_t n_edges,
+	const uint32_t* new_overlaps6, uint64_t n_new_overlaps, const uint64_t* unitig_begin, const uint32_t* unitig_nodes, uint64_t n_unitigs, const uint32_t* unitig_edges6, uint64_t n_unitig_edges,
+	const char* out_gfa, const char* out_gaf,
+	const uint64_t* var_hash, const uint32_t* var_offset, const uint64_t* var_len_begin, const uint32_t* var_len, uint64_t n_var)
+{
 	std::vector<std::string> files { std::string(fasta) };
 	ReadpartIterator partIterator { (size_t)k, (size_t)w, (ErrorMasking)mode, 1, files, false, "" };
+	for (uint64_t e = 0; e < n_var; e++)
+	{
+		const HashType hsh = ((HashType)var_hash[2 * e + 1] << 64) + (HashType)var_hash[2 * e];
+		std::vector<size_t> lens { var_len + var_len_begin[e], var_len + var_len_begin[e + 1] };
+		partIterator.addHpcVariants(hsh, var_offset[e], lens);
+	}
 	HashList reads { (size_t)k };
 	std::ostringstream log;
 	fill_hashlist(reads, node_hash, node_cov, node_tip, n_nodes, edges6, n_edges);
@@ -579,6 +649,24 @@ int refshim_backend(int stage, int mode, uint64_t k, uint64_t w, const char* fas
 			unitigs.setEdgeCoverage(from, to, r[4]);
 			unitigs.setEdgeOverlap(from, to, 0);
 		}
+	}
+	if (const char* dump = getenv("REFSHIM_DUMP_UNITIGS"))
+	{
+		FILE* f = fopen(dump, "w");
+		for (size_t u = 0; u < unitigs.unitigs.size(); u++)
+		{
+			fprintf(f, "U %zu n=%zu:", u, unitigs.unitigs[u].size());
+			for (auto nd : unitigs.unitigs[u]) fprintf(f, " %zu%c", (size_t)nd.first, nd.second ? '+' : '-');
+			fprintf(f, "\n");
+			for (int fw = 1; fw >= 0; fw--) for (auto to : unitigs.edges[std::make_pair(u, fw == 1)]) fprintf(f, "  E %zu%c -> %zu%c cov %zu\n", u, fw ? '+' : '-', (size_t)to.first, to.second ? '+' : '-', unitigs.edgeCoverage(std::make_pair(u, fw == 1), to));
+		}
+		for (size_t i = 0; i < reads.size(); i++)
+		{
+			fprintf(f, "N %zu cov %zu tip %d\n", i, (size_t)reads.coverage.get(i), reads.isTipKmer(i) ? 1 : 0);
+			for (int fw = 1; fw >= 0; fw--) for (auto pr : reads.getSequenceOverlaps(std::make_pair(i, fw == 1))) fprintf(f, "  O %zu%c -> %zu%c ov %zu\n", i, fw ? '+' : '-', (size_t)pr.first.first, pr.first.second ? '+' : '-', (size_t)pr.second);
+			for (int fw = 1; fw >= 0; fw--) for (auto pr : reads.getEdgeCoverages(std::make_pair(i, fw == 1))) fprintf(f, "  C %zu%c -> %zu%c cov %zu\n", i, fw ? '+' : '-', (size_t)pr.first.first, pr.first.second ? '+' : '-', (size_t)pr.second);
+		}
+		fclose(f);
 	}
 	std::vector<ReadPath> readPaths = getReadPaths(unitigs, reads, 1, partIterator, k);      // MBG.cpp:1586
 	if (max_resolve > 0)

@@ -552,16 +552,39 @@ def reference_cli(fasta, out_gfa, out_gaf, mode, k, w, a, u, r=0, big_r=0, guess
     return open(out_gfa, "rb").read(), open(out_gaf, "rb").read()
 
 
+def reference_hpc_variants(fasta, mode, k, w, a, u, onecopy_coverage):
+    """passes 1 and 2 of runMBG under --hpc-variant-onecopy-coverage, run by the reference -> Variants (row f3 is not built)"""
+    lib = C.CDLL(REF_SO)
+    lib.refshim_hpc_variants.restype = C.c_uint64
+    lib.refshim_hpc_variants.argtypes = [C.c_int, C.c_uint64, C.c_uint64, C.c_char_p, C.c_uint64, C.c_double, C.c_double]
+    lib.refshim_hpc_variants_data.restype = C.c_void_p
+    lib.refshim_hpc_variants_data.argtypes = [C.c_int]
+    lib.refshim_hpc_variants_lengths.restype = C.c_uint64
+    saved = os.dup(2)
+    devnull = os.open(os.devnull, os.O_WRONLY)
+    os.dup2(devnull, 2)
+    try:
+        n = lib.refshim_hpc_variants(MODES[mode], k, w, str(fasta).encode(), a, float(u), float(onecopy_coverage))
+    finally:
+        os.dup2(saved, 2)
+        os.close(saved)
+        os.close(devnull)
+    return Variants(_arr(lib.refshim_hpc_variants_data(0), 2 * n, "<u8").reshape(-1, 2), _arr(lib.refshim_hpc_variants_data(1), n, "<u4"),
+                    _arr(lib.refshim_hpc_variants_data(2), n + 1, "<u8"), _arr(lib.refshim_hpc_variants_data(3), lib.refshim_hpc_variants_lengths(), "<u4"))
+
+
 def reference_backend(stage, fasta, out_gfa, out_gaf, mode, k, w, a, u, r=0, big_r=0, guesswork=False, *, node_hash, node_cov, node_tip, edges,
-                      new_overlaps=None, unitig_begin=None, unitig_nodes=None, unitig_edges=None):
+                      new_overlaps=None, unitig_begin=None, unitig_nodes=None, unitig_edges=None, variants=None):
     """T4: tables (stage 0) or the thinned list + unitigs (stage 1) handed to the reference's own back end
     (oracle/ref_shim.cpp:refshim_backend) -> (gfa bytes, gaf bytes)"""
     lib = C.CDLL(REF_SO)
-    f = lib.refshim_backend
+    f = lib.refshim_backend_variants
     f.restype = C.c_int
     f.argtypes = [C.c_int, C.c_int, C.c_uint64, C.c_uint64, C.c_char_p, C.c_uint64, C.c_double, C.c_uint64, C.c_uint64, C.c_int, C.c_int, C.c_int, C.c_int,
                   C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p, C.c_uint64,
-                  C.c_void_p, C.c_uint64, C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p, C.c_uint64, C.c_char_p, C.c_char_p]
+                  C.c_void_p, C.c_uint64, C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p, C.c_uint64, C.c_char_p, C.c_char_p,
+                  C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint64]
+    v = variants if variants is not None else Variants(np.zeros((0, 2)), [], [0], [])
     nh = np.ascontiguousarray(node_hash, dtype=np.uint64)
     nc = np.ascontiguousarray(node_cov, dtype=np.uint32)
     nt = np.ascontiguousarray(node_tip, dtype=np.uint8)
@@ -576,10 +599,42 @@ def reference_backend(stage, fasta, out_gfa, out_gaf, mode, k, w, a, u, r=0, big
     try:
         rc = f(stage, MODES[mode], k, w, str(fasta).encode(), a, float(u), r, big_r, 1 if guesswork else 0, 0, 0, 1,
                nh.ctypes.data, nc.ctypes.data, nt.ctypes.data, len(nc), ed.ctypes.data, len(ed),
-               no.ctypes.data, len(no), ub.ctypes.data, un.ctypes.data, len(ub) - 1, ue.ctypes.data, len(ue), str(out_gfa).encode(), str(out_gaf).encode())
+               no.ctypes.data, len(no), ub.ctypes.data, un.ctypes.data, len(ub) - 1, ue.ctypes.data, len(ue), str(out_gfa).encode(), str(out_gaf).encode(),
+               v.hashes.ctypes.data, v.offsets.ctypes.data, v.len_begin.ctypes.data, v.lengths.ctypes.data, len(v.offsets))
     finally:
         os.dup2(saved, 2)
         os.close(saved)
         os.close(devnull)
     assert rc == 0
     return open(out_gfa, "rb").read(), open(out_gaf, "rb").read()
+
+
+def sort_unitigs(u):
+    """UnitigGraph::sort (MBG/UnitigGraph.cpp:278-438) on a UnitigResult whose node ids are in hash order: every unitig oriented so
+    that its first node id is below its last one (a single k-mer: forward), unitigs ordered by that first id, unitig edges
+    renumbered and put back into canon() form.  The device numbers its unitigs this way already; the oracle's come in walk order."""
+    b = u.unitig_begin.astype(np.int64)
+    n = len(b) - 1
+    seqs, flip = [], []
+    for i in range(n):
+        s = u.unitig_nodes[b[i]:b[i + 1]].astype(np.int64)
+        f = (s[-1] >> 1) < (s[0] >> 1) if len(s) > 1 else not (s[0] & 1)
+        seqs.append((s[::-1] ^ 1) if f else s)
+        flip.append(bool(f))
+    order = sorted(range(n), key=lambda i: int(seqs[i][0] >> 1))
+    new_id = np.empty(n, np.int64)
+    new_id[order] = np.arange(n)
+    nodes = np.concatenate([seqs[i] for i in order]).astype(np.uint32) if n else np.zeros(0, np.uint32)
+    begin = np.zeros(n + 1, np.uint64)
+    begin[1:] = np.cumsum([len(seqs[i]) for i in order])
+    e = u.unitig_edges.astype(np.int64).copy()
+    for r in e:
+        f, ffw, t, tfw = int(r[0]), int(r[1]), int(r[2]), int(r[3])
+        ffw, tfw = ffw ^ flip[f], tfw ^ flip[t]
+        f, t = int(new_id[f]), int(new_id[t])
+        if t < f or (t == f and not tfw and not ffw):
+            f, ffw, t, tfw = t, 1 - tfw, f, 1 - ffw
+        r[0], r[1], r[2], r[3] = f, ffw, t, tfw
+    out = UnitigResult(u)
+    out["unitig_begin"], out["unitig_nodes"], out["unitig_edges"] = begin, nodes, e.astype(np.uint32)
+    return out

@@ -256,7 +256,9 @@ def test_t4_backend_from_tables_gives_the_reference_gfa(oracle, reference, tmp_p
     assert hashlib.md5(gfa0).hexdigest() == hashlib.md5(want_gfa).hexdigest(), "stage 0 GFA"
     assert hashlib.md5(gaf0).hexdigest() == hashlib.md5(want_gaf).hexdigest(), "stage 0 GAF"
     one_cov = u >= 2 and r > 0 and guesswork
+    from oracle_lib import sort_unitigs
     _, th = oracle.run_unitigs(mode, k, w, (bases, offsets), a, u, one_cov=one_cov, thin=True)
+    th = sort_unitigs(th)                   # the oracle numbers unitigs in walk order, the library like UnitigGraph::sort
     ov = np.zeros((len(th.overlaps), 6), np.uint32)
     ov[:, :4], ov[:, 5] = th.overlaps[:, :4], th.overlaps[:, 4]
     gfa1, gaf1 = reference_backend(1, fa, tmp_path / "s1.gfa", tmp_path / "s1.gaf", mode, k, w, a, u, r, big_r, guesswork,
@@ -264,3 +266,33 @@ def test_t4_backend_from_tables_gives_the_reference_gfa(oracle, reference, tmp_p
                                    unitig_begin=th.unitig_begin, unitig_nodes=th.unitig_nodes, unitig_edges=th.unitig_edges)
     assert hashlib.md5(gfa1).hexdigest() == hashlib.md5(want_gfa).hexdigest(), "stage 1 GFA"
     assert hashlib.md5(gaf1).hexdigest() == hashlib.md5(want_gaf).hexdigest(), "stage 1 GAF"
+
+
+def test_t4_backend_with_hpc_variants_verkko_flags(oracle, reference, tmp_path):
+    """T4 under Verkko's flag SET (--hpc-variant-onecopy-coverage on, resolution on, guesswork, -a 1 -u 2, collapse-msat): the
+    variant table comes from the reference's own passes 1-2 (row f3 is not built), pass 3 tables with the variants applied -- here
+    the oracle's, the GPU test hands over the device's -- go through the reference's back end: GFA and GAF of MBG -t 1"""
+    import hashlib
+    from oracle_lib import reference_backend, reference_cli, reference_hpc_variants, write_fasta
+    bases, offsets = workloads.diploid_msat_reads()
+    fa = tmp_path / "reads.fa"
+    write_fasta(fa, bases, offsets)
+    mode, k, w, a, u, r, big_r, onecopy = "collapse-msat", 301, 30, 1, 2, 4000, 1000, 8
+    want_gfa, want_gaf = reference_cli(fa, tmp_path / "ref.gfa", tmp_path / "ref.gaf", mode, k, w, a, u, r, big_r, True, extra=("--hpc-variant-onecopy-coverage", str(onecopy)))
+    variants = reference_hpc_variants(fa, mode, k, w, a, u, onecopy)
+    assert len(variants.offsets) > 10, "the workload must produce hpc variants"
+    table = oracle.run(mode, k, w, (bases, offsets), variants=variants)
+    plain = oracle.run(mode, k, w, (bases, offsets))
+    assert not np.array_equal(table.node_hash, plain.node_hash), "the variants must change hashes"
+    gfa0, gaf0 = reference_backend(0, fa, tmp_path / "s0.gfa", tmp_path / "s0.gaf", mode, k, w, a, u, r, big_r, True, variants=variants,
+                                   node_hash=table.node_hash, node_cov=table.node_cov, node_tip=table.node_tip, edges=table.edges)
+    assert hashlib.md5(gfa0).hexdigest() == hashlib.md5(want_gfa).hexdigest() and hashlib.md5(gaf0).hexdigest() == hashlib.md5(want_gaf).hexdigest(), "stage 0"
+    from oracle_lib import sort_unitigs
+    _, th = oracle.run_unitigs(mode, k, w, (bases, offsets), a, u, variants=variants, one_cov=True, thin=True)
+    th = sort_unitigs(th)
+    ov = np.zeros((len(th.overlaps), 6), np.uint32)
+    ov[:, :4], ov[:, 5] = th.overlaps[:, :4], th.overlaps[:, 4]
+    gfa1, gaf1 = reference_backend(1, fa, tmp_path / "s1.gfa", tmp_path / "s1.gaf", mode, k, w, a, u, r, big_r, True, variants=variants,
+                                   node_hash=th.node_hash, node_cov=th.node_cov, node_tip=th.node_tip, edges=th.edges, new_overlaps=ov,
+                                   unitig_begin=th.unitig_begin, unitig_nodes=th.unitig_nodes, unitig_edges=th.unitig_edges)
+    assert hashlib.md5(gfa1).hexdigest() == hashlib.md5(want_gfa).hexdigest() and hashlib.md5(gaf1).hexdigest() == hashlib.md5(want_gaf).hexdigest(), "stage 1"

@@ -53,3 +53,38 @@ def test_t4_device_tables_through_the_reference_back_end(tmp_path, genome, n_rea
                                    unitig_begin=th["unitig_begin"], unitig_nodes=th["unitig_nodes"], unitig_edges=th["unitig_edges"])
     assert hashlib.md5(gfa1).hexdigest() == hashlib.md5(want_gfa).hexdigest(), "stage 1 (thinned list + unitigs) GFA differs from MBG -t 1"
     assert hashlib.md5(gaf1).hexdigest() == hashlib.md5(want_gaf).hexdigest(), "stage 1 (thinned list + unitigs) GAF differs from MBG -t 1"
+
+
+@pytest.mark.skipif(not have_reference(), reason="oracle/_ref not built")
+@pytest.mark.parametrize("k,w,r,big_r", [(301, 30, 4000, 1000), (1001, 100, 15000, 4000)])
+def test_t4_verkko_flag_set_with_hpc_variants(tmp_path, k, w, r, big_r):
+    """Verkko's flag set (Snakefiles/1-buildGraph.sm:88-100): --hpc-variant-onecopy-coverage on, resolution on, guesswork, -a 1
+    -u 2, collapse-msat.  The variant table is the reference's own (passes 1-2; row f3 is not built) and goes in through
+    mbgfe_set_variants; pass 3 on the device (rows a1-a14, f1) through the reference's back end = MBG -t 1, byte for byte."""
+    import workloads
+    from oracle_lib import reference_hpc_variants
+    bases, offsets = workloads.diploid_msat_reads(len_min=6000 if k < 1001 else 11000, len_max=10000 if k < 1001 else 19000)
+    fa = tmp_path / "reads.fa"
+    write_fasta(fa, bases, offsets)
+    mode, a, u, onecopy = "collapse-msat", 1, 2, 8
+    want_gfa, want_gaf = reference_cli(fa, tmp_path / "ref.gfa", tmp_path / "ref.gaf", mode, k, w, a, u, r, big_r, True, extra=("--hpc-variant-onecopy-coverage", str(onecopy)))
+    variants = reference_hpc_variants(fa, mode, k, w, a, u, onecopy)
+    assert len(variants.offsets) > 10
+    fe = MbgFrontEnd(k, w, mode)
+    try:
+        fe.add_file(str(fa))
+        fe.set_variants(variants.hashes, variants.offsets, variants.len_begin, variants.lengths)
+        fe.run()
+        table = dict(node_hash=fe.node_hashes(), node_cov=fe.node_coverage(), node_tip=fe.node_tip(), edges=fe.edges())
+        ug = fe.build_unitigs(a, u, one_cov_heuristic=True)
+        unitig_edges = ug["unitig_edges"].copy()
+        fe.thin_unitigs()
+        th = fe.thinned()
+    finally:
+        fe.close()
+    gfa0, gaf0 = reference_backend(0, fa, tmp_path / "s0.gfa", tmp_path / "s0.gaf", mode, k, w, a, u, r, big_r, True, variants=variants, **table)
+    assert hashlib.md5(gfa0).hexdigest() == hashlib.md5(want_gfa).hexdigest() and hashlib.md5(gaf0).hexdigest() == hashlib.md5(want_gaf).hexdigest(), "stage 0"
+    gfa1, gaf1 = reference_backend(1, fa, tmp_path / "s1.gfa", tmp_path / "s1.gaf", mode, k, w, a, u, r, big_r, True, variants=variants,
+                                   node_hash=th["node_hash"], node_cov=th["node_cov"], node_tip=th["node_tip"], edges=th["edges"], new_overlaps=th["new_overlaps"],
+                                   unitig_begin=th["unitig_begin"], unitig_nodes=th["unitig_nodes"], unitig_edges=unitig_edges)
+    assert hashlib.md5(gfa1).hexdigest() == hashlib.md5(want_gfa).hexdigest() and hashlib.md5(gaf1).hexdigest() == hashlib.md5(want_gaf).hexdigest(), "stage 1"

@@ -90,3 +90,28 @@ def circular_reads(seed=9, genome_len=3000, read_len=2500, step=300, both_strand
             r = bytes(comp[c] for c in reversed(r))
         reads.append(r)
     return reads
+
+
+def diploid_msat_reads(seed=3, genome_len=150000, n_loci=60, coverage_each=15, len_min=6000, len_max=10000, error_ppm=500):
+    """reads from two haplotypes that differ in the copy number of inserted microsatellites (motif 2-4, 5-8 copies vs +2): what
+    --hpc-variant-onecopy-coverage looks for (run-length clusters with support on both alleles, MBG/ConsensusMaker.cpp:482-537)"""
+    from verkko_b200 import synth
+    rng = np.random.default_rng(seed)
+    base = synth.genome(7, genome_len).tobytes()
+    loci = sorted(rng.choice(np.arange(2000, genome_len - 2000), n_loci, replace=False).tolist())
+    acgt = b"ACGT"
+    h1, h2, last = [], [], 0
+    for p in loci:
+        m = int(rng.integers(2, 5))
+        motif = bytes(acgt[i] for i in rng.permutation(4)[:m])
+        c = int(rng.integers(5, 9))
+        h1 += [base[last:p], motif * c]
+        h2 += [base[last:p], motif * (c + 2)]
+        last = p
+    h1.append(base[last:]); h2.append(base[last:])
+    haps = [np.frombuffer(b"".join(h), dtype=np.uint8).copy() for h in (h1, h2)]
+    n = int(genome_len * coverage_each / ((len_min + len_max) / 2))
+    parts = [synth.reads(11 + i, haps[i], n, len_min, len_max, error_ppm) for i in range(2)]
+    bases = np.concatenate([parts[0][0], parts[1][0]])
+    offsets = np.concatenate([parts[0][1], parts[1][1][1:] + parts[0][1][-1]])
+    return bases, offsets
