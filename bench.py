@@ -299,19 +299,38 @@ def main():
     if world > 1 or force_exchange:
         if os.environ.get("NCCL_DEBUG", "VERSION").upper() == "VERSION":
             os.environ["NCCL_DEBUG"] = "WARN"       # keep NCCL's version banner off stdout: rank 0 prints ONE JSON line
-        if force_exchange:
-            dist.init_process_group("nccl", init_method="tcp://127.0.0.1:29577", rank=0, world_size=1, device_id=torch.device("cuda", local_rank))
-        else:
-            dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    if world > 1:
+        # torch.distributed is host plumbing only (gloo: the NCCL id hand-out, barriers, max / sum of a few scalars); the data path
+        # collectives run inside libmbgfe on its own NCCL communicator (mbgfe_comm_init_nccl / mbgfe_exchange)
+        dist.init_process_group("gloo")
     from verkko_b200 import MbgFrontEnd
-    from verkko_b200.distributed import DistributedCounter
     from verkko_b200.frontend import NO_TABLE
 
     sharded = world > 1 or force_exchange
     fe = MbgFrontEnd(wl["k"], wl["w"], "collapse-msat", device=local_rank, rank=rank, world=world, flags=NO_TABLE if sharded else 0)
     bases, offsets, pinned = make_reads(wl, world, rank, args.scale, pinned_alloc=fe.pinned)
     n_bases = int(offsets[-1])
-    counter = DistributedCounter(fe, world, rank) if sharded else None
+
+    class Exchange:
+        """mbgfe_exchange: counts, node records, id replies, edge records -- all inside the library, over NCCL"""
+        launches, last_exchange_ms, sent_bytes = 0, 0.0, 0
+
+        def exchange_and_count(self):
+            fe.exchange()
+            st_x = fe.stats()
+            self.launches, self.last_exchange_ms, self.sent_bytes = st_x["exchange_launches"], st_x["ms_exchange"], st_x["exchange_bytes"]
+
+        def download_counts(self):
+            cov = fe.node_coverage(copy=False)
+            fe.node_hashes(copy=False)
+            return int(cov.sum(dtype=np.uint64)) + len(fe.edges(copy=False))
+    counter = None
+    if sharded:
+        uid = [fe.unique_id() if rank == 0 else None]
+        if world > 1:
+            dist.broadcast_object_list(uid, src=0)
+        fe.comm_init_nccl(uid[0])
+        counter = Exchange()
 
     def barrier():
         torch.cuda.synchronize()
@@ -342,15 +361,13 @@ def main():
             stage_ms[kname] = stage_ms.get(kname, 0.0) + st[kname]
         if counter:
             stage_ms["ms_exchange"] = stage_ms.get("ms_exchange", 0.0) + counter.last_exchange_ms
-            for name, v in counter.wall_ms.items():
-                stage_ms["wall_" + name] = stage_ms.get("wall_" + name, 0.0) + v
     device_ms = fe.timer_stop()
     barrier()
     wall_ms = (time.time() - t0) * 1e3
     clocks = sampler.stop()
     st = fe.stats()
     launches = st["launches"] * args.steps + (counter.launches * args.steps if counter else 0)
-    t = torch.tensor([device_ms, wall_ms, float(n_bases), float(st["selected"])], dtype=torch.float64, device="cuda")
+    t = torch.tensor([device_ms, wall_ms, float(n_bases), float(st["selected"])], dtype=torch.float64)
     if world > 1:
         mx = t.clone()
         dist.all_reduce(mx, op=dist.ReduceOp.MAX)
@@ -472,7 +489,7 @@ def main():
         steps = np.bincount(th["step"], minlength=6)
         unitig_info["thread_reads"] = {"ms": st_t["ms_unitigs"], "instances": int(len(th["step"])), "launches": st_t["launches"],
                                        "located": int(steps[2:].sum()), "paths": int(steps[2] + steps[3]), "unitig_crossings": int(steps[5])}
-    e2e_t = torch.tensor([float(np.mean(e2e_ms))], dtype=torch.float64, device="cuda")
+    e2e_t = torch.tensor([float(np.mean(e2e_ms))], dtype=torch.float64)
     if world > 1:
         dist.all_reduce(e2e_t, op=dist.ReduceOp.MAX)
     e2e_value = total_bases / (float(e2e_t[0]) * 1e-3)
@@ -533,7 +550,8 @@ def main():
         emit(json.dumps(line))
     if world > 1:
         dist.barrier()
-    if sharded:
+    fe.close()
+    if world > 1:
         dist.destroy_process_group()
 
 

@@ -19,7 +19,7 @@
 extern "C" {
 #endif
 
-#define MBGFE_ABI_VERSION 1
+#define MBGFE_ABI_VERSION 2
 
 /* --error-masking, numbered like the reference enum ErrorMasking (MBG/ReadHelper.h:20-29) */
 enum {
@@ -143,6 +143,9 @@ typedef struct {
 	float ms_upload, ms_pack, ms_collapse, ms_msat, ms_select, ms_hash, ms_nodes, ms_edges, ms_process, ms_export;
 	uint32_t launches;                   /* kernels launched by the last mbgfe_process() / mbgfe_build_unitigs() */
 	float ms_unitigs;                    /* device time of the last mbgfe_build_unitigs() */
+	float ms_exchange;                   /* device time of the last mbgfe_exchange(), first kernel to last */
+	uint32_t exchange_launches;          /* kernels it launched */
+	uint64_t exchange_bytes;             /* bytes this rank sent (node records + id replies + edge records) */
 } mbgfe_stats;
 
 typedef struct mbgfe mbgfe;
@@ -245,36 +248,29 @@ int mbgfe_timer_start(mbgfe* h);
 int mbgfe_timer_stop(mbgfe* h, float* ms);
 
 /* Multi-GPU sharding by k-mer owner (the reference has no multi-device path -- its HashList is one
- * process-wide map behind a mutex, MBG/HashList.h:15-48).  One process and one handle per GPU, reads sharded by rank in
- * contiguous blocks, canonical hashes range-partitioned in equal shares (owner = floor(world * F(hash.hi)); F(x) = x + x (1 - x) is the
- * distribution of the canonical high word, the smaller of two uniform words), so that concatenating
- * the ranks' sorted partitions IS the global sortByHash order.  After mbgfe_process() with MBGFE_NO_TABLE on every rank:
- *
- *   nodes   mbgfe_exchange_counts   send_counts[world] = records this rank holds for each owner
- *           mbgfe_exchange_pack     writes the 32-byte records {canonical hash lo, hi, flags (bit 0 tip), reserved},
- *                                   grouped by owner, into a device buffer and returns its address
- *           (the caller moves them with an NCCL all-to-all-v between device buffers)
- *           mbgfe_exchange_insert   counts n_records received records (device pointer) into this rank's partition
- *   ids     mbgfe_exchange_node_ids global node id (id_base = nodes owned by lower ranks, + rank in the partition) of
- *                                   every received record, uint32 each, in the order received; the caller sends them
- *                                   back with the reverse all-to-all-v, so every rank learns the ids of its own k-mers
- *   edges   mbgfe_exchange_edge_counts / _pack   16-byte records {canonical (from, to) key, (global instance index
- *                                   << 24) | overlap} for every consecutive selected pair, grouped by the rank that owns
- *                                   `from` (id_begin[world + 1] = first node id of every rank); device_ids = the ids
- *                                   received for this rank's packed records; inst_base = selected k-mers on lower
- *                                   ranks (keeps "last observation in input order" global, MBG/HashList.cpp:67-72)
- *           mbgfe_exchange_insert_edges          counts received edge records into this rank's edge partition
- *   mbgfe_exchange_scratch  device scratch buffer `which` (0..3) of at least `bytes` bytes for the caller's receives.
- * Afterwards MBGFE_NODE_* / MBGFE_EDGES return this rank's partition with GLOBAL node ids (limit 2^31-1 nodes). */
-int mbgfe_exchange_counts(mbgfe* h, uint64_t* send_counts);
-int mbgfe_exchange_pack(mbgfe* h, void** device_records);
-int mbgfe_exchange_reserve(mbgfe* h, uint64_t n_records, void** device_recv);
-int mbgfe_exchange_insert(mbgfe* h, const void* device_records, uint64_t n_records);
-int mbgfe_exchange_scratch(mbgfe* h, uint32_t which, uint64_t bytes, void** device_ptr);
-int mbgfe_exchange_node_ids(mbgfe* h, uint64_t id_base, const void* device_records, uint64_t n_records, void** device_ids);
-int mbgfe_exchange_edge_counts(mbgfe* h, const void* device_ids, const uint64_t* id_begin, uint64_t inst_base, uint64_t* send_counts);
-int mbgfe_exchange_edge_pack(mbgfe* h, const uint64_t* send_counts, void** device_records);
-int mbgfe_exchange_insert_edges(mbgfe* h, const void* device_records, uint64_t n_records);
+ * process-wide map behind a mutex, MBG/HashList.h:15-48).  One handle per GPU, reads sharded by rank in contiguous blocks,
+ * canonical hashes range-partitioned in equal shares (owner = floor(world * F(hash.hi)); F(x) = x + x (1 - x) is the distribution of
+ * the canonical high word, the smaller of two uniform words), so that concatenating the ranks' sorted partitions IS the global
+ * sortByHash order.  After mbgfe_process() / mbgfe_run() with MBGFE_NO_TABLE on every rank, ONE collective call does the rest inside
+ * the library:
+ *   1. one kernel counts, per owner, the node records AND the edge records this rank holds (the owner of an edge is the owner of its
+ *      canonical `from` node: decided from the hashes alone); one all-gather gives every rank the whole count matrix
+ *   2. node records {canonical hash lo, hi, tip, reserved} (32 bytes) go to their owners (all-to-all-v); owners count them into their
+ *      partition and remember the slot of every record
+ *   3. partition sizes are all-gathered; global node id = nodes owned by lower ranks + rank inside the sorted partition, read from the
+ *      slot (no second probe); ids go back to the senders (reverse all-to-all-v, 4 bytes each)
+ *   4. edge records {canonical (from id, to id), (global instance index << 24) | overlap} (16 bytes) go to the owner of `from`
+ *      (keeps "last observation in input order" global, MBG/HashList.cpp:67-72); owners build their edge partition
+ * Afterwards MBGFE_NODE_* / MBGFE_EDGES return this rank's partition with GLOBAL node ids (limit 2^31-1 nodes).
+ * Transports: NCCL between processes (grouped ncclSend / ncclRecv; libnccl.so.2 is loaded on first use), peer copies between the
+ * handles of one process (mbgfe_exchange_group), or the caller's own collectives on the library's device buffers (callbacks). */
+typedef int (*mbgfe_allgather_fn)(void* ctx, const void* device_send, void* device_recv, uint64_t bytes_per_rank);
+typedef int (*mbgfe_alltoallv_fn)(void* ctx, const void* device_send, const uint64_t* send_bytes, void* device_recv, const uint64_t* recv_bytes);
+int mbgfe_comm_unique_id(void* id128);                              /* ncclGetUniqueId: rank 0 makes it, the caller hands it to every rank */
+int mbgfe_comm_init_nccl(mbgfe* h, const void* id128);              /* ncclCommInitRank(world, rank) on the handle's device (collective) */
+int mbgfe_comm_init_callbacks(mbgfe* h, mbgfe_alltoallv_fn alltoallv, mbgfe_allgather_fn allgather, void* ctx);
+int mbgfe_exchange(mbgfe* h);                                       /* collective over the ranks of the communicator */
+int mbgfe_exchange_group(mbgfe** handles, uint32_t n);              /* handles[r] = rank r of world n, all in this process */
 
 /* Known-answer access to the device primitives (each runs a tiny kernel): per-code hash of the rolling hasher
  * (MBG/FastHasher.cpp:33-43), code complement (MBG/ErrorMaskHelper.cpp:43-100), k-mer hash (MBG/MBGCommon.cpp:25-35). */

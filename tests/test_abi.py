@@ -17,7 +17,7 @@ def declared_symbols():
 def test_header_declares_the_path():
     syms = declared_symbols()
     for needed in ("mbgfe_create", "mbgfe_add_reads", "mbgfe_add_file", "mbgfe_upload", "mbgfe_process", "mbgfe_run", "mbgfe_data",
-                   "mbgfe_count", "mbgfe_exchange_pack", "mbgfe_exchange_insert", "mbgfe_destroy"):
+                   "mbgfe_count", "mbgfe_exchange", "mbgfe_exchange_group", "mbgfe_comm_init_nccl", "mbgfe_destroy"):
         assert needed in syms
 
 
@@ -57,3 +57,12 @@ def test_product_does_not_touch_the_oracle():
                 if f.endswith((".py", ".cu", ".cuh", ".cpp", ".h")):
                     text = open(os.path.join(dirpath, f)).read()
                     assert "libmbg_oracle" not in text and "oracle_lib" not in text and "libmbgref" not in text, os.path.join(dirpath, f)
+
+
+def test_product_does_not_import_torch():
+    """the product path is C++ / CUDA behind a ctypes mirror: torch (and torch.distributed) is test and bench plumbing only"""
+    for dirpath, _, files in os.walk(os.path.join(ROOT, "verkko_b200")):
+        for f in files:
+            if f.endswith(".py"):
+                text = open(os.path.join(dirpath, f)).read()
+                assert "import torch" not in text and "from torch" not in text, os.path.join(dirpath, f)

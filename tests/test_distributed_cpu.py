@@ -1,54 +1,27 @@
-"""world_size-2 test of the sharded k-mer counting path on CPU: gloo backend, the GPU-less emulator build as the
-per-rank engine ("device" pointers are host pointers there).  Checks that the union of the two rank partitions equals
-the single-rank table of the oracle and that every k-mer landed on its owner."""
+"""The sharded k-mer counting path (mbgfe_exchange) on CPU: the GPU-less emulator build as the per-rank engine.
+* world_size 2 and 3 over torch.distributed / gloo: one process per rank, the library's exchange driven through the
+  callback transport (the same exchange_run the NCCL transport drives on GPUs);
+* the same through mbgfe_exchange_group (all ranks in one process, copies between their buffers).
+Checks that the union of the rank partitions equals the single-rank table of the oracle and that every k-mer and edge
+landed on its owner."""
 import os
 import sys
 
 import numpy as np
 import pytest
-import torch
-import torch.distributed as dist
-import torch.multiprocessing as mp
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
 
-def _worker(rank, world, port, emu, out_dir):
-    sys.path.insert(0, ROOT)
-    sys.path.insert(0, os.path.join(ROOT, "tests"))
-    os.environ["MASTER_ADDR"] = "127.0.0.1"
-    os.environ["MASTER_PORT"] = str(port)
-    dist.init_process_group("gloo", rank=rank, world_size=world)
-    import workloads
-    from verkko_b200.distributed import DistributedCounter
-    from verkko_b200.frontend import NO_TABLE, MbgFrontEnd
-    bases, offsets = workloads.coverage_reads(n_reads=8)
+def shard(bases, offsets, rank, world):
     n = len(offsets) - 1
     lo, hi = rank * n // world, (rank + 1) * n // world
-    fe = MbgFrontEnd(501, 50, "collapse-msat", flags=NO_TABLE, rank=rank, world=world, library=emu)
-    fe.add_reads(bases[int(offsets[lo]):int(offsets[hi])], offsets[lo:hi + 1] - offsets[lo])
-    fe.run()
-    counter = DistributedCounter(fe, world, rank, on_gpu=False)
-    counter.exchange_and_count()
-    np.savez(os.path.join(out_dir, f"rank{rank}.npz"), node_hash=fe.node_hashes(), node_cov=fe.node_coverage(), node_tip=fe.node_tip(), edges=fe.edges(),
-             id_begin=counter.id_begin)
-    fe.close()
-    dist.barrier()
-    dist.destroy_process_group()
+    return bases[int(offsets[lo]):int(offsets[hi])], offsets[lo:hi + 1] - offsets[lo]
 
 
-@pytest.mark.parametrize("world", [2, 3])
-def test_partitioned_counting(oracle, emu_library, tmp_path, world):
-    import socket
-    import workloads
-    from verkko_b200.distributed import owner_of
-    s = socket.socket()
-    s.bind(("127.0.0.1", 0))
-    port = s.getsockname()[1]
-    s.close()
-    mp.spawn(_worker, args=(world, port, emu_library, str(tmp_path)), nprocs=world, join=True)
-    want = oracle.run("collapse-msat", 501, 50, workloads.coverage_reads(n_reads=8))
-    parts = [np.load(tmp_path / f"rank{r}.npz") for r in range(world)]
+def check_partitions(parts, want, world):
+    from dist_helpers import owner_of
+    from oracle_lib import sorted_edges
     for r, p in enumerate(parts):
         assert all(int(o) == r for o in owner_of(p["node_hash"][:, 1], world)), "k-mer on the wrong owner"
     # owner ranges are ordered, so concatenating the sorted partitions is the global sortByHash order
@@ -56,12 +29,66 @@ def test_partitioned_counting(oracle, emu_library, tmp_path, world):
     cov = np.concatenate([p["node_cov"] for p in parts])
     tip = np.concatenate([p["node_tip"] for p in parts])
     assert np.array_equal(nh, want.node_hash) and np.array_equal(cov, want.node_cov) and np.array_equal(tip, want.node_tip)
-    # edges: every rank holds the edges whose `from` node it owns, with global ids, each partition sorted like the
-    # single-GPU export; concatenated they are the oracle's edge table
-    id_begin = parts[0]["id_begin"]
+    # edges: every rank holds the edges whose `from` node it owns, with global ids; concatenated they are the oracle's edge table
+    begin = np.concatenate([[0], np.cumsum([len(p["node_cov"]) for p in parts])])
     for r, p in enumerate(parts):
         e = p["edges"]
-        assert np.all((e[:, 0] >= id_begin[r]) & (e[:, 0] < id_begin[r + 1])), "edge on the wrong owner"
-    from oracle_lib import sorted_edges
+        assert np.all((e[:, 0] >= begin[r]) & (e[:, 0] < begin[r + 1])), "edge on the wrong owner"
     edges = np.concatenate([p["edges"] for p in parts])
     assert np.array_equal(sorted_edges(edges), sorted_edges(want.edges))
+
+
+def _worker(rank, world, port, emu, out_dir):
+    sys.path.insert(0, ROOT)
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import torch.distributed as dist
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    import workloads
+    from dist_helpers import gloo_callbacks
+    from verkko_b200.frontend import NO_TABLE, MbgFrontEnd
+    bases, offsets = workloads.coverage_reads(n_reads=8)
+    fe = MbgFrontEnd(501, 50, "collapse-msat", flags=NO_TABLE, rank=rank, world=world, library=emu)
+    fe.add_reads(*shard(bases, offsets, rank, world))
+    fe.run()
+    fe.comm_init_callbacks(*gloo_callbacks(world))
+    fe.exchange()
+    fe.exchange()          # a second exchange over the same instances gives the same partition
+    np.savez(os.path.join(out_dir, f"rank{rank}.npz"), node_hash=fe.node_hashes(), node_cov=fe.node_coverage(), node_tip=fe.node_tip(), edges=fe.edges())
+    fe.close()
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("world", [2, 3])
+def test_partitioned_counting_over_gloo(oracle, emu_library, tmp_path, world):
+    import socket
+    import torch.multiprocessing as mp
+    import workloads
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    port = s.getsockname()[1]
+    s.close()
+    mp.spawn(_worker, args=(world, port, emu_library, str(tmp_path)), nprocs=world, join=True)
+    want = oracle.run("collapse-msat", 501, 50, workloads.coverage_reads(n_reads=8))
+    check_partitions([np.load(tmp_path / f"rank{r}.npz") for r in range(world)], want, world)
+
+
+@pytest.mark.parametrize("world", [2, 4])
+def test_partitioned_counting_in_one_process(oracle, emu_library, world):
+    """mbgfe_exchange_group: all ranks are handles of this process"""
+    import workloads
+    from verkko_b200.frontend import NO_TABLE, MbgFrontEnd
+    bases, offsets = workloads.coverage_reads(n_reads=8)
+    fes = [MbgFrontEnd(501, 50, "collapse-msat", flags=NO_TABLE, rank=r, world=world, library=emu_library) for r in range(world)]
+    try:
+        for r, fe in enumerate(fes):
+            fe.add_reads(*shard(bases, offsets, r, world))
+            fe.run()
+        MbgFrontEnd.exchange_group(fes)
+        parts = [dict(node_hash=fe.node_hashes(), node_cov=fe.node_coverage(), node_tip=fe.node_tip(), edges=fe.edges()) for fe in fes]
+    finally:
+        for fe in fes:
+            fe.close()
+    check_partitions(parts, oracle.run("collapse-msat", 501, 50, (bases, offsets)), world)

@@ -8,7 +8,6 @@ import os
 import sys
 
 import numpy as np
-import torch
 import torch.distributed as dist
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
@@ -18,11 +17,10 @@ sys.path.insert(0, os.path.join(ROOT, "tests"))
 
 def main():
     rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
-    torch.cuda.set_device(local)
-    dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    dist.init_process_group("gloo")          # host plumbing (NCCL id hand-out, gathering the results); the data path is mbgfe_exchange over NCCL
     import workloads
+    from dist_helpers import owner_of
     from oracle_lib import Oracle, sorted_edges
-    from verkko_b200.distributed import DistributedCounter, owner_of
     from verkko_b200.frontend import NO_TABLE, MbgFrontEnd
     ok = True
     for mode, k, w, n_reads in (("collapse-msat", 1001, 100, 64), ("hpc", 501, 50, 24)):
@@ -32,17 +30,20 @@ def main():
         fe = MbgFrontEnd(k, w, mode, device=local, flags=NO_TABLE, rank=rank, world=world)
         fe.add_reads(bases[int(offsets[lo]):int(offsets[hi])], offsets[lo:hi + 1] - offsets[lo])
         fe.run()
-        counter = DistributedCounter(fe, world, rank)
-        counter.exchange_and_count()
-        mine = dict(node_hash=fe.node_hashes(), node_cov=fe.node_coverage(), node_tip=fe.node_tip(), edges=fe.edges(), id_begin=counter.id_begin)
+        uid = [fe.unique_id() if rank == 0 else None]
+        dist.broadcast_object_list(uid, src=0)
+        fe.comm_init_nccl(uid[0])
+        fe.exchange()
+        mine = dict(node_hash=fe.node_hashes(), node_cov=fe.node_coverage(), node_tip=fe.node_tip(), edges=fe.edges())
         gathered = [None] * world
         dist.all_gather_object(gathered, mine)
         if rank == 0:
             want = Oracle().run(mode, k, w, (bases, offsets))
+            begin = np.concatenate([[0], np.cumsum([len(p["node_cov"]) for p in gathered])])
             for r, p in enumerate(gathered):
                 assert all(int(o) == r for o in owner_of(p["node_hash"][:, 1], world)), "k-mer on the wrong owner"
                 e = p["edges"]
-                assert np.all((e[:, 0] >= p["id_begin"][r]) & (e[:, 0] < p["id_begin"][r + 1])), "edge on the wrong owner"
+                assert np.all((e[:, 0] >= begin[r]) & (e[:, 0] < begin[r + 1])), "edge on the wrong owner"
             nh = np.concatenate([p["node_hash"] for p in gathered])
             good = (np.array_equal(nh, want.node_hash) and np.array_equal(np.concatenate([p["node_cov"] for p in gathered]), want.node_cov)
                     and np.array_equal(np.concatenate([p["node_tip"] for p in gathered]), want.node_tip)

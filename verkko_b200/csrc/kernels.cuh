@@ -1968,6 +1968,82 @@ __global__ void __launch_bounds__(256) k_insert_edge_records(const unsigned long
 	warp_count(distinct, is_new);
 }
 
+// ---- the exchange as libmbgfe runs it itself (mbgfe_exchange): counts of BOTH collectives from the hashes alone, one pass
+
+// the rank that will own the edge observation (i - 1, i): the owner of its canonical `from` node (canonical_edge_key's choice)
+__device__ __forceinline__ uint32_t edge_owner_of(uint64_t a_lo, uint64_t a_hi, uint64_t b_lo, uint64_t b_hi, uint32_t world)
+{
+	uint64_t ak_lo, ak_hi, bk_lo, bk_hi; uint32_t afw, bfw;
+	canonical_key(a_lo, a_hi, ak_lo, ak_hi, afw);
+	canonical_key(b_lo, b_hi, bk_lo, bk_hi, bfw);
+	const bool to_smaller = bk_hi < ak_hi || (bk_hi == ak_hi && bk_lo < ak_lo);
+	const bool same = bk_hi == ak_hi && bk_lo == ak_lo;
+	return owner_of((to_smaller || (same && !bfw && !afw)) ? bk_hi : ak_hi, world);
+}
+
+__device__ __forceinline__ bool has_edge_observation(uint64_t i, uint64_t n_inst, const uint64_t* __restrict__ inst_hash, const uint8_t* __restrict__ inst_flag)
+{
+	if (i >= n_inst || i == 0 || (inst_flag[i] & 1)) return false;
+	return inst_hash[2 * i] != inst_hash[2 * i + 1] && inst_hash[2 * (i - 1)] != inst_hash[2 * (i - 1) + 1];      // neither is a palindrome
+}
+
+// counts[0 .. world) = node records per owner, counts[world .. 2 world) = edge records per owner
+__global__ void __launch_bounds__(256) k_owner_count2(const uint64_t* __restrict__ inst_hash, const uint8_t* __restrict__ inst_flag, uint64_t n_inst, uint32_t world,
+	unsigned long long* __restrict__ counts)
+{
+	const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+	uint32_t owner = NO_OWNER, eowner = NO_OWNER;
+	if (i < n_inst)
+	{
+		const uint64_t lo = inst_hash[2 * i], hi = inst_hash[2 * i + 1];
+		if (lo != hi) { uint64_t key_lo, key_hi; uint32_t fw; canonical_key(lo, hi, key_lo, key_hi, fw); owner = owner_of(key_hi, world); }
+		if (has_edge_observation(i, n_inst, inst_hash, inst_flag)) eowner = edge_owner_of(inst_hash[2 * (i - 1)], inst_hash[2 * (i - 1) + 1], lo, hi, world);
+	}
+	block_owner_alloc(owner, counts, world);
+	block_owner_alloc(eowner, counts + world, world);
+}
+
+// received node records into this rank's partition; the slot each one landed in is kept (ids are answered from it, no second probe)
+__global__ void __launch_bounds__(256) k_insert_records2(const uint64_t* __restrict__ rec, uint64_t n_rec, NodeSlot* __restrict__ table, uint64_t mask,
+	uint32_t* __restrict__ rec_slot, unsigned long long* __restrict__ distinct, unsigned long long* __restrict__ overflow)
+{
+	const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+	bool is_new = false;
+	if (i < n_rec)
+	{
+		const uint64_t slot = node_insert(table, mask, rec[4 * i], rec[4 * i + 1], 1, (uint32_t)rec[4 * i + 2] & 1u, is_new);
+		if (slot == ~0ull) atomicAdd(overflow, 1ull);
+		rec_slot[i] = (uint32_t)slot;
+	}
+	warp_count(distinct, is_new);
+}
+
+__global__ void __launch_bounds__(256) k_slot_ids(const uint32_t* __restrict__ rec_slot, uint64_t n_rec, const NodeSlot* __restrict__ table, uint32_t id_base, uint32_t* __restrict__ ids)
+{
+	const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+	if (i < n_rec) ids[i] = id_base + (uint32_t)table[rec_slot[i]].rank;
+}
+
+// edge records {canonical (from id, to id) key, (global instance index << 24) | overlap} grouped by the owner of `from` (same
+// rule as k_owner_count2 counted with)
+__global__ void __launch_bounds__(256) k_edge_owner_pack2(const uint64_t* __restrict__ inst_hash, const uint32_t* __restrict__ inst_pos, const uint8_t* __restrict__ inst_flag,
+	const uint32_t* __restrict__ inst_packpos, const uint32_t* __restrict__ packed_ids, uint64_t n_inst, uint64_t inst_base, uint32_t k, uint32_t world,
+	unsigned long long* __restrict__ cursors, unsigned long long* __restrict__ records)
+{
+	const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+	const bool have = has_edge_observation(i, n_inst, inst_hash, inst_flag);
+	uint32_t owner = NO_OWNER;
+	if (have) owner = edge_owner_of(inst_hash[2 * (i - 1)], inst_hash[2 * (i - 1) + 1], inst_hash[2 * i], inst_hash[2 * i + 1], world);
+	const unsigned long long o = block_owner_alloc(owner, cursors, world);
+	if (have)
+	{
+		ulonglong2 r;
+		r.x = canonical_edge_key(inst_hash[2 * (i - 1)], inst_hash[2 * (i - 1) + 1], inst_hash[2 * i], inst_hash[2 * i + 1], packed_ids[inst_packpos[i - 1]], packed_ids[inst_packpos[i]]);
+		r.y = ((unsigned long long)(inst_base + i) << 24) | (inst_pos[i - 1] + k - inst_pos[i]);
+		*(ulonglong2*)(records + 2 * o) = r;
+	}
+}
+
 // KAT helper: complement table and per-code hash are read back directly; the k-mer hash runs k_kmer_hash on one
 // synthetic instance.
 

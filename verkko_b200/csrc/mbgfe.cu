@@ -21,6 +21,10 @@
 #include "graph.cuh"
 #include "hostpack.h"
 #include "../../include/mbgfe.h"
+#ifndef MBGFE_EMU_BUILD
+#include <dlfcn.h>
+#include <nccl.h>
+#endif
 
 static_assert(sizeof(mbgfe_dev::EdgeRec) == sizeof(mbgfe_edge), "device edge record is the ABI edge record");
 
@@ -108,6 +112,11 @@ struct mbgfe
 	DevBuf d_inst_pos, d_inst_seg, d_inst_flag, d_inst_hash, d_inst_slot, d_pal_list;
 	DevBuf d_nodes, d_edges, d_node_out, d_edge_out, d_records, d_recv;
 	DevBuf d_inst_packpos, d_ids_out, d_id_begin, d_edge_records, d_xbuf[4];   // sharded table: id replies and edge records
+	DevBuf d_xrow, d_xmatrix, d_rec_slot;                                    // exchange: this rank's counts, everybody's, slot of every received record
+	int comm_kind = 0;                                                       // 0 none, 1 NCCL, 2 group (one process), 3 caller's callbacks
+	void* nccl_comm = nullptr;
+	mbgfe_alltoallv_fn cb_alltoallv = nullptr; mbgfe_allgather_fn cb_allgather = nullptr; void* cb_ctx = nullptr;
+	std::vector<uint64_t> id_begin;                                          // first global node id of every rank (world + 1)
 	const void* x_packed_ids = nullptr;                                      // ids of this rank's packed records, as received
 	uint64_t x_inst_base = 0;
 	std::vector<uint64_t> x_counts;                                          // per-owner record counts of the last mbgfe_exchange_counts
@@ -429,6 +438,7 @@ int load_file(mbgfe* h, const char* path)
 }
 
 namespace {
+void destroy_comm(mbgfe* h);
 int materialize_files(mbgfe* h);
 int run_files(mbgfe* h);
 void close_files(std::vector<mbgfe::DeferredFile>& v) { for (auto& f : v) if (f.fd >= 0) close(f.fd); v.clear(); }
@@ -511,7 +521,7 @@ void mbgfe_destroy(mbgfe* h)
 		&h->d_node_tip, &h->d_edges_sorted, &h->d_inst_packpos, &h->d_ids_out, &h->d_id_begin, &h->d_edge_records, &h->d_xbuf[0], &h->d_xbuf[1], &h->d_xbuf[2],
 		&h->d_xbuf[3], &h->d_var_hash, &h->d_var_offset, &h->d_var_len_begin, &h->d_var_len, &h->d_g_deg, &h->d_g_nb, &h->d_g_link, &h->d_g_st[0], &h->d_g_st[1],
 		&h->d_g_kept, &h->d_g_newid, &h->d_g_flag, &h->d_g_at, &h->d_g_flag2, &h->d_g_at2, &h->d_g_flag_byte, &h->d_f_hash, &h->d_f_cov, &h->d_f_tip, &h->d_f_edges, &h->d_f_orig, &h->d_t_hash, &h->d_t_cov, &h->d_t_tip, &h->d_t_edges, &h->d_t_orig, &h->d_g_kept8, &h->d_u_pos, &h->d_th_final, &h->d_th_node, &h->d_th_unitig, &h->d_th_upos, &h->d_th_urest, &h->d_th_step, &h->d_thin, &h->d_thin_pos,
-		&h->d_u_begin, &h->d_u_nodes, &h->d_u_of_node, &h->d_u_fw, &h->d_u_edges, &h->d_thin_scan, &h->d_tpos, &h->d_tu_nodes, &h->d_tu_off, &h->d_tu_unitig, &h->d_tu_begin, &h->d_t_newov }) release(*b);
+		&h->d_u_begin, &h->d_u_nodes, &h->d_u_of_node, &h->d_u_fw, &h->d_u_edges, &h->d_xrow, &h->d_xmatrix, &h->d_rec_slot, &h->d_thin_scan, &h->d_tpos, &h->d_tu_nodes, &h->d_tu_off, &h->d_tu_unitig, &h->d_tu_begin, &h->d_t_newov }) release(*b);
 	for (HostBuf* b : { &h->p_node_hashes, &h->p_node_cov, &h->p_node_tip, &h->p_edges, &h->p_stage }) release_host(*b);
 	for (auto& e : h->ev) if (e) cudaEventDestroy(e);
 	for (auto& e : h->piece_events) cudaEventDestroy(e);
@@ -523,6 +533,7 @@ void mbgfe_destroy(mbgfe* h)
 	for (auto* v : h->owned_bases) delete v;
 	for (auto* v : h->owned_offsets) delete v;
 	close_files(h->files); close_files(h->image_files);
+	destroy_comm(h);
 	delete h;
 }
 
@@ -2212,180 +2223,366 @@ int mbgfe_timer_stop(mbgfe* h, float* ms)
 	return 0;
 }
 
-int mbgfe_exchange_counts(mbgfe* h, uint64_t* send_counts)
+// ====================================================================================== multi-GPU exchange
+// The whole exchange runs inside the library: counts of both collectives from one kernel and one all-gather, node records to
+// their owners, ids answered from the slot each record landed in, edge records to the owner of their `from` node.  Three
+// transports move the bytes: NCCL (one process per GPU; grouped ncclSend / ncclRecv over NVLink), peer copies between the
+// handles of ONE process (mbgfe_exchange_group), or the caller's own collectives (callbacks; the CPU tests use gloo).
+// Host synchronisations per exchange: the count matrix, the partition sizes, the final counters.
+
+}
+
+namespace {
+
+#ifndef MBGFE_EMU_BUILD
+struct NcclApi
 {
-	if (!h || !send_counts) return MBGFE_E_PARAM;
-	if (!h->processed) return fail(h, MBGFE_E_STATE, "exchange before mbgfe_process");
-	unsigned long long* ctr = h->d_counters.as<unsigned long long>();
-	const uint32_t world = h->prm.world;
-	CU(h, cudaMemsetAsync(ctr + CTR_OWNER, 0, world * 8, h->stream));
-	if (h->n_inst) MBGFE_LAUNCH(k_owner_count, (unsigned)((h->n_inst + 255) / 256), 256, 0, h->stream, h->d_inst_hash.as<uint64_t>(), h->n_inst, world, ctr + CTR_OWNER);
-	std::vector<unsigned long long> c(world);
-	CU(h, cudaMemcpyAsync(c.data(), ctr + CTR_OWNER, world * 8, cudaMemcpyDeviceToHost, h->stream));
-	CU(h, cudaStreamSynchronize(h->stream));
-	for (uint32_t i = 0; i < world; i++) send_counts[i] = c[i];
-	h->x_counts.assign(send_counts, send_counts + world);
+	void* lib = nullptr;
+	ncclResult_t (*GetUniqueId)(ncclUniqueId*) = nullptr;
+	ncclResult_t (*CommInitRank)(ncclComm_t*, int, ncclUniqueId, int) = nullptr;
+	ncclResult_t (*CommDestroy)(ncclComm_t) = nullptr;
+	ncclResult_t (*AllGather)(const void*, void*, size_t, ncclDataType_t, ncclComm_t, cudaStream_t) = nullptr;
+	ncclResult_t (*Send)(const void*, size_t, ncclDataType_t, int, ncclComm_t, cudaStream_t) = nullptr;
+	ncclResult_t (*Recv)(void*, size_t, ncclDataType_t, int, ncclComm_t, cudaStream_t) = nullptr;
+	ncclResult_t (*GroupStart)() = nullptr;
+	ncclResult_t (*GroupEnd)() = nullptr;
+	const char* (*GetErrorString)(ncclResult_t) = nullptr;
+};
+NcclApi* nccl_api()
+{
+	static NcclApi api;
+	static bool tried = false;
+	if (!tried)
+	{
+		tried = true;
+		// the process may already hold a libnccl.so.2 (torch's); dlopen then hands back that one
+		void* lib = dlopen("libnccl.so.2", RTLD_NOW | RTLD_GLOBAL);
+		if (!lib) lib = dlopen("libnccl.so", RTLD_NOW | RTLD_GLOBAL);
+		if (lib)
+		{
+			api.lib = lib;
+			*(void**)&api.GetUniqueId = dlsym(lib, "ncclGetUniqueId");
+			*(void**)&api.CommInitRank = dlsym(lib, "ncclCommInitRank");
+			*(void**)&api.CommDestroy = dlsym(lib, "ncclCommDestroy");
+			*(void**)&api.AllGather = dlsym(lib, "ncclAllGather");
+			*(void**)&api.Send = dlsym(lib, "ncclSend");
+			*(void**)&api.Recv = dlsym(lib, "ncclRecv");
+			*(void**)&api.GroupStart = dlsym(lib, "ncclGroupStart");
+			*(void**)&api.GroupEnd = dlsym(lib, "ncclGroupEnd");
+			*(void**)&api.GetErrorString = dlsym(lib, "ncclGetErrorString");
+			if (!api.GetUniqueId || !api.CommInitRank || !api.AllGather || !api.Send || !api.Recv || !api.GroupStart || !api.GroupEnd) api.lib = nullptr;
+		}
+	}
+	return api.lib ? &api : nullptr;
+}
+#define NCCLCHK(h, call) do { ncclResult_t r_ = (call); if (r_ != ncclSuccess) return fail(h, MBGFE_E_CUDA, "%s failed: %s", #call, nccl_api()->GetErrorString ? nccl_api()->GetErrorString(r_) : "nccl error"); } while (0)
+#endif
+
+void destroy_comm(mbgfe* h)
+{
+#ifndef MBGFE_EMU_BUILD
+	if (h->nccl_comm && nccl_api() && nccl_api()->CommDestroy) nccl_api()->CommDestroy((ncclComm_t)h->nccl_comm);
+#endif
+	h->nccl_comm = nullptr; h->comm_kind = 0;
+}
+
+// ---- transport: all-gather of `bytes` per rank and all-to-all-v between device buffers.  hs = the handles taking part IN THIS
+// PROCESS: one (NCCL, callbacks: the other ranks are other processes) or all `world` of them (group).
+int x_allgather(std::vector<mbgfe*>& hs, std::vector<const void*>& send, std::vector<void*>& recv, size_t bytes)
+{
+	mbgfe* h0 = hs[0];
+	if (h0->comm_kind == 2)
+	{
+		for (mbgfe* h : hs) { CU(h, cudaSetDevice(h->prm.device)); CU(h, cudaStreamSynchronize(h->stream)); }
+		for (size_t j = 0; j < hs.size(); j++)
+			for (size_t i = 0; i < hs.size(); i++)
+				CU(hs[j], cudaMemcpyPeerAsync((char*)recv[j] + i * bytes, hs[j]->prm.device, send[i], hs[i]->prm.device, bytes, hs[j]->stream));
+		return 0;
+	}
+	if (h0->comm_kind == 3)
+	{
+		CU(h0, cudaStreamSynchronize(h0->stream));
+		if (h0->cb_allgather(h0->cb_ctx, send[0], recv[0], bytes)) return fail(h0, MBGFE_E_CUDA, "all-gather callback failed");
+		return 0;
+	}
+#ifndef MBGFE_EMU_BUILD
+	if (h0->comm_kind == 1) { NCCLCHK(h0, nccl_api()->AllGather(send[0], recv[0], bytes, ncclUint8, (ncclComm_t)h0->nccl_comm, h0->stream)); return 0; }
+#endif
+	return fail(h0, MBGFE_E_STATE, "no communicator: call mbgfe_comm_init_nccl / mbgfe_comm_init_callbacks, or use mbgfe_exchange_group");
+}
+
+// counts in elements of elem bytes; per handle: send[p] elements for rank p from send_buf (grouped by rank), recv likewise
+int x_alltoallv(std::vector<mbgfe*>& hs, std::vector<const void*>& send_buf, std::vector<std::vector<uint64_t>>& send_cnt, std::vector<void*>& recv_buf,
+	std::vector<std::vector<uint64_t>>& recv_cnt, size_t elem)
+{
+	mbgfe* h0 = hs[0];
+	const uint32_t world = h0->prm.world;
+	if (h0->comm_kind == 2)
+	{
+		for (mbgfe* h : hs) { CU(h, cudaSetDevice(h->prm.device)); CU(h, cudaStreamSynchronize(h->stream)); }
+		for (size_t j = 0; j < hs.size(); j++)      // receiver j pulls what every sender i packed for it
+		{
+			uint64_t roff = 0;
+			for (size_t i = 0; i < hs.size(); i++)
+			{
+				uint64_t soff = 0;
+				for (size_t q = 0; q < j; q++) soff += send_cnt[i][q];
+				const uint64_t n = send_cnt[i][j];
+				if (n) CU(hs[j], cudaMemcpyPeerAsync((char*)recv_buf[j] + roff * elem, hs[j]->prm.device, (const char*)send_buf[i] + soff * elem, hs[i]->prm.device, n * elem, hs[j]->stream));
+				roff += n;
+			}
+		}
+		return 0;
+	}
+	if (h0->comm_kind == 3)
+	{
+		CU(h0, cudaStreamSynchronize(h0->stream));
+		std::vector<uint64_t> sb(world), rb(world);
+		for (uint32_t p = 0; p < world; p++) { sb[p] = send_cnt[0][p] * elem; rb[p] = recv_cnt[0][p] * elem; }
+		if (h0->cb_alltoallv(h0->cb_ctx, send_buf[0], sb.data(), recv_buf[0], rb.data())) return fail(h0, MBGFE_E_CUDA, "all-to-all callback failed");
+		return 0;
+	}
+#ifndef MBGFE_EMU_BUILD
+	if (h0->comm_kind == 1)
+	{
+		NcclApi* n = nccl_api();
+		NCCLCHK(h0, n->GroupStart());
+		uint64_t soff = 0, roff = 0;
+		for (uint32_t p = 0; p < world; p++)
+		{
+			if (send_cnt[0][p]) NCCLCHK(h0, n->Send((const char*)send_buf[0] + soff * elem, send_cnt[0][p] * elem, ncclUint8, (int)p, (ncclComm_t)h0->nccl_comm, h0->stream));
+			if (recv_cnt[0][p]) NCCLCHK(h0, n->Recv((char*)recv_buf[0] + roff * elem, recv_cnt[0][p] * elem, ncclUint8, (int)p, (ncclComm_t)h0->nccl_comm, h0->stream));
+			soff += send_cnt[0][p]; roff += recv_cnt[0][p];
+		}
+		NCCLCHK(h0, n->GroupEnd());
+		return 0;
+	}
+#endif
+	return fail(h0, MBGFE_E_STATE, "no communicator");
+}
+
+int exchange_run(std::vector<mbgfe*>& hs)
+{
+	const size_t nh = hs.size();
+	const uint32_t world = hs[0]->prm.world;
+	const size_t row = 2 * world + 1;                       // node counts, edge counts, instances
+	std::vector<const void*> sp(nh); std::vector<void*> rp(nh);
+	auto on = [&](mbgfe* h) { return cudaSetDevice(h->prm.device); };
+	// ---- S1: counts of both collectives
+	for (size_t x = 0; x < nh; x++)
+	{
+		mbgfe* h = hs[x];
+		CU(h, on(h));
+		if (!h->processed) return fail(h, MBGFE_E_STATE, "exchange before mbgfe_process / mbgfe_run");
+		if (int rc = ensure(h, h->d_xrow, row * 8)) return rc;
+		if (int rc = ensure(h, h->d_xmatrix, row * world * 8)) return rc;
+		tick(h, 12);
+		CU(h, cudaMemsetAsync(h->d_xrow.p, 0, row * 8, h->stream));
+		if (h->n_inst) MBGFE_LAUNCH(k_owner_count2, (unsigned)((h->n_inst + 255) / 256), 256, 0, h->stream, h->d_inst_hash.as<uint64_t>(), h->d_inst_flag.as<uint8_t>(), h->n_inst, world,
+			h->d_xrow.as<unsigned long long>());
+		CU(h, cudaMemcpyAsync(h->d_xrow.as<uint64_t>() + 2 * world, &h->n_inst, 8, cudaMemcpyHostToDevice, h->stream));
+		sp[x] = h->d_xrow.p; rp[x] = h->d_xmatrix.p;
+	}
+	if (int rc = x_allgather(hs, sp, rp, row * 8)) return rc;
+	std::vector<std::vector<uint64_t>> M(nh, std::vector<uint64_t>(row * world));
+	for (size_t x = 0; x < nh; x++) { mbgfe* h = hs[x]; CU(h, on(h)); CU(h, cudaMemcpyAsync(M[x].data(), h->d_xmatrix.p, row * world * 8, cudaMemcpyDeviceToHost, h->stream)); }
+	for (size_t x = 0; x < nh; x++) { mbgfe* h = hs[x]; CU(h, on(h)); CU(h, cudaStreamSynchronize(h->stream)); }
+	// ---- S2: node records, grouped by owner
+	std::vector<std::vector<uint64_t>> nsend(nh, std::vector<uint64_t>(world)), nrecv(nh, std::vector<uint64_t>(world)), esend(nh, std::vector<uint64_t>(world)), erecv(nh, std::vector<uint64_t>(world));
+	std::vector<uint64_t> n_send(nh), n_recv(nh), e_send(nh), e_recv(nh), inst_base(nh);
+	for (size_t x = 0; x < nh; x++)
+	{
+		mbgfe* h = hs[x];
+		CU(h, on(h));
+		const uint32_t me = h->prm.rank;
+		const uint64_t* m = M[x].data();
+		n_send[x] = n_recv[x] = e_send[x] = e_recv[x] = inst_base[x] = 0;
+		for (uint32_t p = 0; p < world; p++)
+		{
+			nsend[x][p] = m[me * row + p]; nrecv[x][p] = m[p * row + me]; esend[x][p] = m[me * row + world + p]; erecv[x][p] = m[p * row + world + me];
+			n_send[x] += nsend[x][p]; n_recv[x] += nrecv[x][p]; e_send[x] += esend[x][p]; e_recv[x] += erecv[x][p];
+			if (p < me) inst_base[x] += m[p * row + 2 * world];
+		}
+		if (int rc = ensure(h, h->d_records, (n_send[x] + 1) * 32)) return rc;
+		if (int rc = ensure(h, h->d_recv, (n_recv[x] + 1) * 32)) return rc;
+		if (int rc = ensure(h, h->d_inst_packpos, (h->n_inst + 1) * 4)) return rc;
+		std::vector<unsigned long long> cursors(world);
+		uint64_t at = 0;
+		for (uint32_t p = 0; p < world; p++) { cursors[p] = at; at += nsend[x][p]; }
+		unsigned long long* ctr = h->d_counters.as<unsigned long long>();
+		CU(h, cudaMemcpyAsync(ctr + CTR_OWNER, cursors.data(), world * 8, cudaMemcpyHostToDevice, h->stream));
+		if (h->n_inst) MBGFE_LAUNCH(k_owner_pack, (unsigned)((h->n_inst + 255) / 256), 256, 0, h->stream, h->d_inst_hash.as<uint64_t>(), h->d_inst_flag.as<uint8_t>(), h->n_inst, world,
+			ctr + CTR_OWNER, h->d_records.as<uint64_t>(), h->d_inst_packpos.as<uint32_t>());
+		CU(h, cudaStreamSynchronize(h->stream));      // `cursors` is a host temporary of this iteration
+		sp[x] = h->d_records.p; rp[x] = h->d_recv.p;
+	}
+	if (int rc = x_alltoallv(hs, sp, nsend, rp, nrecv, 32)) return rc;
+	// ---- S3: this rank's partition of the node table
+	for (size_t x = 0; x < nh; x++)
+	{
+		mbgfe* h = hs[x];
+		CU(h, on(h));
+		unsigned long long* ctr = h->d_counters.as<unsigned long long>();
+		const uint64_t slots = std::max<uint64_t>(next_pow2(std::max<uint64_t>(2 * n_recv[x], 1024)), h->prm.table_slots ? next_pow2(h->prm.table_slots) : 0);
+		if (slots >= (1ull << 31)) return fail(h, MBGFE_E_LIMIT, "node table would need %llu slots (limit 2^31 per GPU)", (unsigned long long)slots);
+		if (int rc = ensure(h, h->d_nodes, slots * sizeof(NodeSlot))) return rc;
+		if (int rc = ensure(h, h->d_rec_slot, (n_recv[x] + 1) * 4)) return rc;
+		h->node_slots = slots; h->edge_slots = 0;
+		CU(h, cudaMemsetAsync(ctr + CTR_DISTINCT, 0, 16, h->stream));
+		CU(h, cudaMemsetAsync(ctr + CTR_OVERFLOW, 0, 8, h->stream));
+		const unsigned clear_grid = (unsigned)std::min<uint64_t>((slots + 255) / 256, (uint64_t)h->sm_count * 8);
+		MBGFE_LAUNCH(k_table_clear, clear_grid, 256, 0, h->stream, h->d_nodes.as<NodeSlot>(), slots);
+		if (n_recv[x]) MBGFE_LAUNCH(k_insert_records2, (unsigned)((n_recv[x] + 255) / 256), 256, 0, h->stream, h->d_recv.as<uint64_t>(), n_recv[x], h->d_nodes.as<NodeSlot>(), slots - 1,
+			h->d_rec_slot.as<uint32_t>(), ctr + CTR_DISTINCT, ctr + CTR_OVERFLOW);
+		h->stats.table_slots = slots;
+		sp[x] = ctr + CTR_DISTINCT; rp[x] = h->d_xmatrix.p;
+	}
+	if (int rc = x_allgather(hs, sp, rp, 8)) return rc;
+	std::vector<std::vector<uint64_t>> sizes(nh, std::vector<uint64_t>(world));
+	for (size_t x = 0; x < nh; x++) { mbgfe* h = hs[x]; CU(h, on(h)); CU(h, cudaMemcpyAsync(sizes[x].data(), h->d_xmatrix.p, world * 8, cudaMemcpyDeviceToHost, h->stream)); }
+	for (size_t x = 0; x < nh; x++) { mbgfe* h = hs[x]; CU(h, on(h)); CU(h, cudaStreamSynchronize(h->stream)); }
+	// ---- S4: global node ids of the received records, back to their senders
+	for (size_t x = 0; x < nh; x++)
+	{
+		mbgfe* h = hs[x];
+		CU(h, on(h));
+		const uint32_t me = h->prm.rank;
+		uint64_t base = 0, all = 0;
+		h->id_begin.assign(world + 1, 0);
+		for (uint32_t p = 0; p < world; p++) { if (p < me) base += sizes[x][p]; all += sizes[x][p]; h->id_begin[p + 1] = all; }
+		if (all >= (1ull << 31)) return fail(h, MBGFE_E_LIMIT, "more than 2^31-1 nodes in the sharded table");
+		h->stats.distinct = sizes[x][me]; h->stats.distinct_edges = 0;
+		h->id_base = (uint32_t)base;
+		h->exported_table = false; h->nodes_ranked = false; h->edges_global = false; h->table_sharded = true; h->have_table = true;
+		h->stats.selected = h->n_inst;
+		if (h->prm.flags & MBGFE_NO_EDGES) { sp[x] = nullptr; continue; }
+		if (int rc = rank_nodes(h)) return rc;
+		if (int rc = ensure(h, h->d_ids_out, (n_recv[x] + 1) * 4)) return rc;
+		if (int rc = ensure(h, h->d_xbuf[0], (n_send[x] + 1) * 4)) return rc;
+		if (n_recv[x]) MBGFE_LAUNCH(k_slot_ids, (unsigned)((n_recv[x] + 255) / 256), 256, 0, h->stream, h->d_rec_slot.as<uint32_t>(), n_recv[x], h->d_nodes.as<NodeSlot>(), h->id_base,
+			h->d_ids_out.as<uint32_t>());
+		sp[x] = h->d_ids_out.p; rp[x] = h->d_xbuf[0].p;
+	}
+	if (!(hs[0]->prm.flags & MBGFE_NO_EDGES))
+	{
+		if (int rc = x_alltoallv(hs, sp, nrecv, rp, nsend, 4)) return rc;
+		// ---- S5: edge observations to the owner of their `from` node
+		for (size_t x = 0; x < nh; x++)
+		{
+			mbgfe* h = hs[x];
+			CU(h, on(h));
+			if (int rc = ensure(h, h->d_edge_records, (e_send[x] + 1) * 16)) return rc;
+			if (int rc = ensure(h, h->d_xbuf[1], (e_recv[x] + 1) * 16)) return rc;
+			std::vector<unsigned long long> cursors(world);
+			uint64_t at = 0;
+			for (uint32_t p = 0; p < world; p++) { cursors[p] = at; at += esend[x][p]; }
+			unsigned long long* ctr = h->d_counters.as<unsigned long long>();
+			CU(h, cudaMemcpyAsync(ctr + CTR_OWNER, cursors.data(), world * 8, cudaMemcpyHostToDevice, h->stream));
+			if (h->n_inst) MBGFE_LAUNCH(k_edge_owner_pack2, (unsigned)((h->n_inst + 255) / 256), 256, 0, h->stream, h->d_inst_hash.as<uint64_t>(), h->d_inst_pos.as<uint32_t>(),
+				h->d_inst_flag.as<uint8_t>(), h->d_inst_packpos.as<uint32_t>(), h->d_xbuf[0].as<uint32_t>(), h->n_inst, inst_base[x], h->prm.k, world, ctr + CTR_OWNER,
+				h->d_edge_records.as<unsigned long long>());
+			CU(h, cudaStreamSynchronize(h->stream));
+			sp[x] = h->d_edge_records.p; rp[x] = h->d_xbuf[1].p;
+		}
+		if (int rc = x_alltoallv(hs, sp, esend, rp, erecv, 16)) return rc;
+		for (size_t x = 0; x < nh; x++)
+		{
+			mbgfe* h = hs[x];
+			CU(h, on(h));
+			unsigned long long* ctr = h->d_counters.as<unsigned long long>();
+			const uint64_t slots = next_pow2(std::max<uint64_t>(2 * e_recv[x], 1024));
+			if (slots >= (1ull << 31)) return fail(h, MBGFE_E_LIMIT, "edge table would need %llu slots (limit 2^31 per GPU)", (unsigned long long)slots);
+			if (int rc = ensure(h, h->d_edges, slots * sizeof(EdgeSlot))) return rc;
+			h->edge_slots = slots;
+			const unsigned clear_grid = (unsigned)std::min<uint64_t>((slots + 255) / 256, (uint64_t)h->sm_count * 8);
+			MBGFE_LAUNCH(k_edge_clear, clear_grid, 256, 0, h->stream, h->d_edges.as<EdgeSlot>(), slots);
+			if (e_recv[x]) MBGFE_LAUNCH(k_insert_edge_records, (unsigned)((e_recv[x] + 255) / 256), 256, 0, h->stream, h->d_xbuf[1].as<unsigned long long>(), e_recv[x],
+				h->d_edges.as<EdgeSlot>(), slots - 1, ctr + CTR_EDGES);
+			h->edges_global = true;
+		}
+	}
+	// ---- the final counters
+	for (size_t x = 0; x < nh; x++)
+	{
+		mbgfe* h = hs[x];
+		CU(h, on(h));
+		unsigned long long* ctr = h->d_counters.as<unsigned long long>();
+		tick(h, 13);
+		unsigned long long five[5] = { 0, 0, 0, 0, 0 };
+		CU(h, cudaMemcpyAsync(five, ctr + CTR_DISTINCT, sizeof(five), cudaMemcpyDeviceToHost, h->stream));
+		CU(h, cudaStreamSynchronize(h->stream));
+		CU(h, cudaGetLastError());
+		if (five[CTR_OVERFLOW - CTR_DISTINCT]) return fail(h, MBGFE_E_LIMIT, "the sharded k-mer table overflowed (%llu inserts gave up)", five[CTR_OVERFLOW - CTR_DISTINCT]);
+		h->stats.distinct_edges = five[1];
+		h->stats.ms_exchange = elapsed(h, 12, 13);
+		h->stats.exchange_bytes = n_send[x] * 32 + n_recv[x] * 4 + e_send[x] * 16;
+		h->stats.exchange_launches = 3 + (h->edge_slots ? 11 : 0);
+	}
 	return 0;
 }
 
-int mbgfe_exchange_pack(mbgfe* h, void** device_records)
+}
+
+extern "C" {
+
+int mbgfe_comm_unique_id(void* id128)
 {
-	if (!h || !device_records) return MBGFE_E_PARAM;
-	if (!h->processed) return fail(h, MBGFE_E_STATE, "exchange before mbgfe_process");
-	const uint32_t world = h->prm.world;
-	std::vector<uint64_t> counts(world);
-	if (h->x_counts.size() == world) counts = h->x_counts;        // counted by the caller a moment ago
-	else if (int rc = mbgfe_exchange_counts(h, counts.data())) return rc;
-	std::vector<unsigned long long> cursors(world);
-	uint64_t total = 0;
-	for (uint32_t i = 0; i < world; i++) { cursors[i] = total; total += counts[i]; }
-	if (int rc = ensure(h, h->d_records, (total + 1) * 32)) return rc;
-	if (int rc = ensure(h, h->d_inst_packpos, (h->n_inst + 1) * 4)) return rc;
-	unsigned long long* ctr = h->d_counters.as<unsigned long long>();
-	CU(h, cudaMemcpyAsync(ctr + CTR_OWNER, cursors.data(), world * 8, cudaMemcpyHostToDevice, h->stream));
-	if (h->n_inst) MBGFE_LAUNCH(k_owner_pack, (unsigned)((h->n_inst + 255) / 256), 256, 0, h->stream, h->d_inst_hash.as<uint64_t>(), h->d_inst_flag.as<uint8_t>(), h->n_inst, world,
-		ctr + CTR_OWNER, h->d_records.as<uint64_t>(), h->d_inst_packpos.as<uint32_t>());
-	CU(h, cudaStreamSynchronize(h->stream));
-	CU(h, cudaGetLastError());
-	*device_records = h->d_records.p;
+#ifndef MBGFE_EMU_BUILD
+	NcclApi* n = nccl_api();
+	if (!n || !id128) return MBGFE_E_CUDA;
+	static_assert(sizeof(ncclUniqueId) == 128, "ncclUniqueId is 128 bytes");
+	return n->GetUniqueId((ncclUniqueId*)id128) == ncclSuccess ? 0 : MBGFE_E_CUDA;
+#else
+	(void)id128; return MBGFE_E_CUDA;
+#endif
+}
+
+int mbgfe_comm_init_nccl(mbgfe* h, const void* id128)
+{
+	if (!h || !id128) return MBGFE_E_PARAM;
+#ifndef MBGFE_EMU_BUILD
+	NcclApi* n = nccl_api();
+	if (!n) return fail(h, MBGFE_E_CUDA, "libnccl.so.2 cannot be loaded");
+	CU(h, cudaSetDevice(h->prm.device));
+	ncclUniqueId id;
+	memcpy(&id, id128, sizeof(id));
+	ncclComm_t comm = nullptr;
+	NCCLCHK(h, n->CommInitRank(&comm, (int)h->prm.world, id, (int)h->prm.rank));
+	h->nccl_comm = comm;
+	h->comm_kind = 1;
+	return 0;
+#else
+	return fail(h, MBGFE_E_CUDA, "the emulator build has no NCCL");
+#endif
+}
+
+int mbgfe_comm_init_callbacks(mbgfe* h, mbgfe_alltoallv_fn alltoallv, mbgfe_allgather_fn allgather, void* ctx)
+{
+	if (!h || !alltoallv || !allgather) return MBGFE_E_PARAM;
+	h->cb_alltoallv = alltoallv; h->cb_allgather = allgather; h->cb_ctx = ctx;
+	h->comm_kind = 3;
 	return 0;
 }
 
-int mbgfe_exchange_reserve(mbgfe* h, uint64_t n_records, void** device_recv)
-{
-	if (!h || !device_recv) return MBGFE_E_PARAM;
-	if (int rc = ensure(h, h->d_recv, (n_records + 1) * 32)) return rc;
-	*device_recv = h->d_recv.p;
-	return 0;
-}
-
-int mbgfe_exchange_insert(mbgfe* h, const void* device_records, uint64_t n_records)
+int mbgfe_exchange(mbgfe* h)
 {
 	if (!h) return MBGFE_E_PARAM;
-	unsigned long long* ctr = h->d_counters.as<unsigned long long>();
-	const uint64_t slots = next_pow2(std::max<uint64_t>(2 * n_records, 1024));
-	if (slots >= (1ull << 31)) return fail(h, MBGFE_E_LIMIT, "node table would need %llu slots (limit 2^31 per GPU)", (unsigned long long)slots);
-	if (int rc = ensure(h, h->d_nodes, slots * sizeof(NodeSlot))) return rc;
-	h->node_slots = slots; h->edge_slots = 0;
-	CU(h, cudaMemsetAsync(ctr + CTR_DISTINCT, 0, 16, h->stream));
-	tick(h, 12);
-	const unsigned clear_grid = (unsigned)std::min<uint64_t>((slots + 255) / 256, (uint64_t)h->sm_count * 8);
-	MBGFE_LAUNCH(k_table_clear, clear_grid, 256, 0, h->stream, h->d_nodes.as<NodeSlot>(), slots);
-	if (n_records) MBGFE_LAUNCH(k_insert_records, (unsigned)((n_records + 255) / 256), 256, 0, h->stream, (const uint64_t*)device_records, n_records, h->d_nodes.as<NodeSlot>(), slots - 1,
-		ctr + CTR_DISTINCT);
-	tick(h, 13);
-	uint64_t d = 0;
-	if (int rc = read_counter(h, CTR_DISTINCT, &d)) return rc;
-	CU(h, cudaGetLastError());
-	h->stats.distinct = d; h->stats.distinct_edges = 0; h->stats.table_slots = slots;
-	h->stats.ms_nodes = elapsed(h, 12, 13);
-	h->exported_table = false; h->nodes_ranked = false; h->edges_global = false;
-	h->table_sharded = true;
-	h->have_table = true;
-	return 0;
+	if (h->comm_kind != 1 && h->comm_kind != 3) return fail(h, MBGFE_E_STATE, "mbgfe_exchange needs mbgfe_comm_init_nccl or mbgfe_comm_init_callbacks first");
+	std::vector<mbgfe*> hs { h };
+	return exchange_run(hs);
 }
 
-int mbgfe_exchange_scratch(mbgfe* h, uint32_t which, uint64_t bytes, void** device_ptr)
+int mbgfe_exchange_group(mbgfe** handles, uint32_t n)
 {
-	if (!h || !device_ptr || which >= 4) return MBGFE_E_PARAM;
-	if (int rc = ensure(h, h->d_xbuf[which], bytes + 64)) return rc;
-	*device_ptr = h->d_xbuf[which].p;
-	return 0;
-}
-
-int mbgfe_exchange_node_ids(mbgfe* h, uint64_t id_base, const void* device_records, uint64_t n_records, void** device_ids)
-{
-	if (!h || !device_ids) return MBGFE_E_PARAM;
-	if (!h->have_table) return fail(h, MBGFE_E_STATE, "node ids requested before mbgfe_exchange_insert");
-	if (id_base + h->stats.distinct >= (1ull << 31)) return fail(h, MBGFE_E_LIMIT, "more than 2^31-1 nodes in the sharded table");
-	h->id_base = (uint32_t)id_base;
-	if (int rc = rank_nodes(h)) return rc;
-	if (int rc = ensure(h, h->d_ids_out, (n_records + 1) * 4)) return rc;
-	if (n_records) MBGFE_LAUNCH(k_record_ids, (unsigned)((n_records + 255) / 256), 256, 0, h->stream, (const uint64_t*)device_records, n_records, h->d_nodes.as<NodeSlot>(),
-		h->node_slots - 1, h->id_base, h->d_ids_out.as<uint32_t>());
-	CU(h, cudaStreamSynchronize(h->stream));
-	CU(h, cudaGetLastError());
-	*device_ids = h->d_ids_out.p;
-	return 0;
-}
-
-static int edge_exchange_launch(mbgfe* h, bool pack)
-{
-	unsigned long long* ctr = h->d_counters.as<unsigned long long>();
-	if (!h->n_inst) return 0;
-	const unsigned grid = (unsigned)((h->n_inst + 255) / 256);
-	if (!pack)
-		MBGFE_LAUNCH(k_edge_owner_count, grid, 256, 0, h->stream, h->d_inst_hash.as<uint64_t>(), h->d_inst_pos.as<uint32_t>(), h->d_inst_flag.as<uint8_t>(),
-			h->d_inst_packpos.as<uint32_t>(), (const uint32_t*)h->x_packed_ids, h->n_inst, h->x_inst_base, h->prm.k, h->d_id_begin.as<uint64_t>(), h->prm.world, ctr + CTR_OWNER);
-	else
-		MBGFE_LAUNCH(k_edge_owner_pack, grid, 256, 0, h->stream, h->d_inst_hash.as<uint64_t>(), h->d_inst_pos.as<uint32_t>(), h->d_inst_flag.as<uint8_t>(),
-			h->d_inst_packpos.as<uint32_t>(), (const uint32_t*)h->x_packed_ids, h->n_inst, h->x_inst_base, h->prm.k, h->d_id_begin.as<uint64_t>(), h->prm.world, ctr + CTR_OWNER,
-			h->d_edge_records.as<unsigned long long>());
-	return 0;
-}
-
-int mbgfe_exchange_edge_counts(mbgfe* h, const void* device_ids, const uint64_t* id_begin, uint64_t inst_base, uint64_t* send_counts)
-{
-	if (!h || !id_begin || !send_counts) return MBGFE_E_PARAM;
-	if (!h->processed || !h->d_inst_packpos.p) return fail(h, MBGFE_E_STATE, "edge exchange before mbgfe_exchange_pack");
-	if (h->n_inst && !device_ids) return fail(h, MBGFE_E_PARAM, "null id array");
-	const uint32_t world = h->prm.world;
-	h->x_packed_ids = device_ids; h->x_inst_base = inst_base;
-	if (int rc = ensure(h, h->d_id_begin, (world + 1) * 8)) return rc;
-	unsigned long long* ctr = h->d_counters.as<unsigned long long>();
-	CU(h, cudaMemcpyAsync(h->d_id_begin.p, id_begin, (world + 1) * 8, cudaMemcpyHostToDevice, h->stream));
-	CU(h, cudaMemsetAsync(ctr + CTR_OWNER, 0, world * 8, h->stream));
-	if (int rc = edge_exchange_launch(h, false)) return rc;
-	std::vector<unsigned long long> c(world);
-	CU(h, cudaMemcpyAsync(c.data(), ctr + CTR_OWNER, world * 8, cudaMemcpyDeviceToHost, h->stream));
-	CU(h, cudaStreamSynchronize(h->stream));
-	CU(h, cudaGetLastError());
-	for (uint32_t i = 0; i < world; i++) send_counts[i] = c[i];
-	return 0;
-}
-
-int mbgfe_exchange_edge_pack(mbgfe* h, const uint64_t* send_counts, void** device_records)
-{
-	if (!h || !send_counts || !device_records) return MBGFE_E_PARAM;
-	if (!h->d_id_begin.p) return fail(h, MBGFE_E_STATE, "mbgfe_exchange_edge_pack before mbgfe_exchange_edge_counts");
-	const uint32_t world = h->prm.world;
-	std::vector<unsigned long long> cursors(world);
-	uint64_t total = 0;
-	for (uint32_t i = 0; i < world; i++) { cursors[i] = total; total += send_counts[i]; }
-	if (int rc = ensure(h, h->d_edge_records, (total + 1) * 16)) return rc;
-	unsigned long long* ctr = h->d_counters.as<unsigned long long>();
-	CU(h, cudaMemcpyAsync(ctr + CTR_OWNER, cursors.data(), world * 8, cudaMemcpyHostToDevice, h->stream));
-	if (int rc = edge_exchange_launch(h, true)) return rc;
-	CU(h, cudaStreamSynchronize(h->stream));
-	CU(h, cudaGetLastError());
-	*device_records = h->d_edge_records.p;
-	return 0;
-}
-
-int mbgfe_exchange_insert_edges(mbgfe* h, const void* device_records, uint64_t n_records)
-{
-	if (!h) return MBGFE_E_PARAM;
-	if (!h->have_table) return fail(h, MBGFE_E_STATE, "edges before nodes: call mbgfe_exchange_insert first");
-	unsigned long long* ctr = h->d_counters.as<unsigned long long>();
-	const uint64_t slots = next_pow2(std::max<uint64_t>(2 * n_records, 1024));
-	if (slots >= (1ull << 31)) return fail(h, MBGFE_E_LIMIT, "edge table would need %llu slots (limit 2^31 per GPU)", (unsigned long long)slots);
-	if (int rc = ensure(h, h->d_edges, slots * sizeof(EdgeSlot))) return rc;
-	h->edge_slots = slots;
-	CU(h, cudaMemsetAsync(ctr + CTR_EDGES, 0, 8, h->stream));
-	tick(h, 12);
-	const unsigned clear_grid = (unsigned)std::min<uint64_t>((slots + 255) / 256, (uint64_t)h->sm_count * 8);
-	MBGFE_LAUNCH(k_edge_clear, clear_grid, 256, 0, h->stream, h->d_edges.as<EdgeSlot>(), slots);
-	if (n_records) MBGFE_LAUNCH(k_insert_edge_records, (unsigned)((n_records + 255) / 256), 256, 0, h->stream, (const unsigned long long*)device_records, n_records,
-		h->d_edges.as<EdgeSlot>(), slots - 1, ctr + CTR_EDGES);
-	tick(h, 13);
-	uint64_t d = 0;
-	if (int rc = read_counter(h, CTR_EDGES, &d)) return rc;
-	CU(h, cudaGetLastError());
-	h->stats.distinct_edges = d;
-	h->stats.ms_edges = elapsed(h, 12, 13);
-	h->edges_global = true;
-	h->exported_table = false;
-	return 0;
+	if (!handles || n == 0) return MBGFE_E_PARAM;
+	std::vector<mbgfe*> hs(handles, handles + n);
+	for (uint32_t i = 0; i < n; i++)
+	{
+		if (!hs[i]) return MBGFE_E_PARAM;
+		if (hs[i]->prm.world != n || hs[i]->prm.rank != i) return fail(hs[i], MBGFE_E_PARAM, "mbgfe_exchange_group: handle %u must be rank %u of %u", i, i, n);
+		hs[i]->comm_kind = 2;
+	}
+	return exchange_run(hs);
 }
 
 int mbgfe_set_variants(mbgfe* h, const mbgfe_hash128* hashes, const uint32_t* offsets, const uint64_t* len_begin, const uint32_t* lengths, uint64_t n_entries)

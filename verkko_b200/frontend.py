@@ -36,7 +36,8 @@ class Stats(C.Structure):
         "reads", "raw_bases", "segments", "collapsed_symbols", "codes", "parts", "hashed_parts", "selected", "distinct",
         "distinct_edges", "table_slots", "table_grows", "nonacgt", "h2d_bytes", "d2h_bytes")] + [(n, C.c_float) for n in (
         "ms_upload", "ms_pack", "ms_collapse", "ms_msat", "ms_select", "ms_hash", "ms_nodes", "ms_edges", "ms_process",
-        "ms_export")] + [("launches", C.c_uint32), ("ms_unitigs", C.c_float)]
+        "ms_export")] + [("launches", C.c_uint32), ("ms_unitigs", C.c_float), ("ms_exchange", C.c_float), ("exchange_launches", C.c_uint32),
+                         ("exchange_bytes", C.c_uint64)]
 
 
 class MbgfeError(RuntimeError):
@@ -82,15 +83,11 @@ def load_library(path=None):
     L.mbgfe_get_stats.argtypes = [C.c_void_p, C.POINTER(Stats)]
     L.mbgfe_timer_start.argtypes = [C.c_void_p]
     L.mbgfe_timer_stop.argtypes = [C.c_void_p, C.POINTER(C.c_float)]
-    L.mbgfe_exchange_counts.argtypes = [C.c_void_p, C.c_void_p]
-    L.mbgfe_exchange_pack.argtypes = [C.c_void_p, C.POINTER(C.c_void_p)]
-    L.mbgfe_exchange_reserve.argtypes = [C.c_void_p, C.c_uint64, C.POINTER(C.c_void_p)]
-    L.mbgfe_exchange_insert.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64]
-    L.mbgfe_exchange_scratch.argtypes = [C.c_void_p, C.c_uint32, C.c_uint64, C.POINTER(C.c_void_p)]
-    L.mbgfe_exchange_node_ids.argtypes = [C.c_void_p, C.c_uint64, C.c_void_p, C.c_uint64, C.POINTER(C.c_void_p)]
-    L.mbgfe_exchange_edge_counts.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p]
-    L.mbgfe_exchange_edge_pack.argtypes = [C.c_void_p, C.c_void_p, C.POINTER(C.c_void_p)]
-    L.mbgfe_exchange_insert_edges.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64]
+    L.mbgfe_comm_unique_id.argtypes = [C.c_void_p]
+    L.mbgfe_comm_init_nccl.argtypes = [C.c_void_p, C.c_void_p]
+    L.mbgfe_comm_init_callbacks.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
+    L.mbgfe_exchange.argtypes = [C.c_void_p]
+    L.mbgfe_exchange_group.argtypes = [C.c_void_p, C.c_uint32]
     L.mbgfe_build_unitigs.argtypes = [C.c_void_p, C.c_uint32, C.c_double]
     L.mbgfe_build_unitigs_ex.argtypes = [C.c_void_p, C.c_uint32, C.c_double, C.c_uint32]
     L.mbgfe_thread_reads.argtypes = [C.c_void_p]
@@ -137,7 +134,7 @@ class MbgFrontEnd:
                  table_slots=0, library=None, piece_bytes=0):
         self.lib = load_library(library)
         mode = MODES[error_masking] if isinstance(error_masking, str) else int(error_masking)
-        self.params = Params(1, k, w, mode, kmer_abundance, flags, device, rank, world, piece_bytes, table_slots)
+        self.params = Params(2, k, w, mode, kmer_abundance, flags, device, rank, world, piece_bytes, table_slots)
         self.handle = C.c_void_p()
         rc = self.lib.mbgfe_create(C.byref(self.params), C.byref(self.handle))
         if rc != 0:
@@ -332,49 +329,39 @@ class MbgFrontEnd:
     def pinned(self, nbytes):
         return PinnedBuffer(self.lib, nbytes)
 
-    # ---- multi-GPU exchange (device pointers as integers)
-    def exchange_counts(self):
-        out = np.zeros(self.params.world, dtype=np.uint64)
-        self._check(self.lib.mbgfe_exchange_counts(self.handle, out.ctypes.data))
-        return out
+    # ---- multi-GPU exchange (include/mbgfe.h): the whole thing runs inside the library
+    def unique_id(self):
+        """ncclGetUniqueId (rank 0), as 128 bytes to hand to every rank"""
+        buf = (C.c_char * 128)()
+        self._check(self.lib.mbgfe_comm_unique_id(buf))
+        return bytes(buf)
 
-    def exchange_pack(self):
-        p = C.c_void_p()
-        self._check(self.lib.mbgfe_exchange_pack(self.handle, C.byref(p)))
-        return p.value or 0
+    def comm_init_nccl(self, unique_id):
+        buf = (C.c_char * 128).from_buffer_copy(unique_id)
+        self._check(self.lib.mbgfe_comm_init_nccl(self.handle, buf))
 
-    def exchange_reserve(self, n_records):
-        p = C.c_void_p()
-        self._check(self.lib.mbgfe_exchange_reserve(self.handle, n_records, C.byref(p)))
-        return p.value or 0
+    def comm_init_callbacks(self, alltoallv, allgather):
+        """the caller's collectives on the library's device buffers: alltoallv(send_ptr, send_bytes[world], recv_ptr, recv_bytes[world]),
+        allgather(send_ptr, recv_ptr, bytes_per_rank); both return 0 on success"""
+        world = self.params.world
+        A2A = C.CFUNCTYPE(C.c_int, C.c_void_p, C.c_void_p, C.POINTER(C.c_uint64), C.c_void_p, C.POINTER(C.c_uint64))
+        AG = C.CFUNCTYPE(C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint64)
+        self._cb = (A2A(lambda ctx, s, sb, r, rb: int(alltoallv(s or 0, [sb[i] for i in range(world)], r or 0, [rb[i] for i in range(world)]) or 0)),
+                    AG(lambda ctx, s, r, n: int(allgather(s or 0, r or 0, n) or 0)))
+        self._check(self.lib.mbgfe_comm_init_callbacks(self.handle, self._cb[0], self._cb[1], None))
 
-    def exchange_insert(self, device_ptr, n_records):
-        self._check(self.lib.mbgfe_exchange_insert(self.handle, device_ptr, n_records))
+    def exchange(self):
+        self._check(self.lib.mbgfe_exchange(self.handle))
 
-    def exchange_scratch(self, which, nbytes):
-        p = C.c_void_p()
-        self._check(self.lib.mbgfe_exchange_scratch(self.handle, which, nbytes, C.byref(p)))
-        return p.value or 0
-
-    def exchange_node_ids(self, id_base, device_ptr, n_records):
-        p = C.c_void_p()
-        self._check(self.lib.mbgfe_exchange_node_ids(self.handle, id_base, device_ptr, n_records, C.byref(p)))
-        return p.value or 0
-
-    def exchange_edge_counts(self, device_ids, id_begin, inst_base):
-        id_begin = np.ascontiguousarray(id_begin, dtype=np.uint64)
-        out = np.zeros(self.params.world, dtype=np.uint64)
-        self._check(self.lib.mbgfe_exchange_edge_counts(self.handle, device_ids, id_begin.ctypes.data, inst_base, out.ctypes.data))
-        return out
-
-    def exchange_edge_pack(self, send_counts):
-        send_counts = np.ascontiguousarray(send_counts, dtype=np.uint64)
-        p = C.c_void_p()
-        self._check(self.lib.mbgfe_exchange_edge_pack(self.handle, send_counts.ctypes.data, C.byref(p)))
-        return p.value or 0
-
-    def exchange_insert_edges(self, device_ptr, n_records):
-        self._check(self.lib.mbgfe_exchange_insert_edges(self.handle, device_ptr, n_records))
+    @staticmethod
+    def exchange_group(handles):
+        """all ranks in this process (one handle per GPU, or several on one GPU): peer copies instead of a communicator"""
+        arr = (C.c_void_p * len(handles))(*[h.handle for h in handles])
+        rc = handles[0].lib.mbgfe_exchange_group(arr, len(handles))
+        if rc:
+            for h in handles:
+                h._check(rc) if h.lib.mbgfe_last_error(h.handle) else None
+            handles[0]._check(rc)
 
     # ---- known-answer access
     def kat_tables(self):
