@@ -190,6 +190,14 @@ int mbgfe_upload(mbgfe* h);
 int mbgfe_process(mbgfe* h);
 int mbgfe_run(mbgfe* h);
 
+/* Input larger than one resident batch (the reference streams any volume through its queue into ONE HashList,
+ * MBG/ReadHelper.h:102-160): mbgfe_run_append() = mbgfe_run() on the pending reads, but the selected k-mers of the batches before
+ * it stay in the instance lists (25 bytes each on the device; MBGFE_POSITIONS / MBGFE_HASHES then cover all batches, MBGFE_PARTS /
+ * MBGFE_CODES the last one) and no table is built.  When every batch is in: mbgfe_build_table() counts all of them into one node /
+ * edge table (single GPU), or mbgfe_exchange() into the sharded one.  mbgfe_reset() / mbgfe_run() start over. */
+int mbgfe_run_append(mbgfe* h);
+int mbgfe_build_table(mbgfe* h);
+
 /* Results (downloaded and, for the tables, ordered on first request). */
 uint64_t mbgfe_count(mbgfe* h, int what);
 const void* mbgfe_data(mbgfe* h, int what);

@@ -150,6 +150,10 @@ struct mbgfe
 	uint64_t node_slots = 0, edge_slots = 0;
 	uint64_t n_inst = 0;
 	uint64_t inst_cap = 0;                            // capacity of the instance lists (entries)
+	// mbgfe_run_append: the selected k-mers of earlier batches stay in the instance lists, this batch's follow them
+	bool appending = false;
+	uint64_t append_base = 0;                         // instances of earlier batches
+	DevBuf d_append_base, d_range;
 
 	// host results
 	std::vector<mbgfe_part> parts;
@@ -521,7 +525,7 @@ void mbgfe_destroy(mbgfe* h)
 		&h->d_node_tip, &h->d_edges_sorted, &h->d_inst_packpos, &h->d_ids_out, &h->d_id_begin, &h->d_edge_records, &h->d_xbuf[0], &h->d_xbuf[1], &h->d_xbuf[2],
 		&h->d_xbuf[3], &h->d_var_hash, &h->d_var_offset, &h->d_var_len_begin, &h->d_var_len, &h->d_g_deg, &h->d_g_nb, &h->d_g_link, &h->d_g_st[0], &h->d_g_st[1],
 		&h->d_g_kept, &h->d_g_newid, &h->d_g_flag, &h->d_g_at, &h->d_g_flag2, &h->d_g_at2, &h->d_g_flag_byte, &h->d_f_hash, &h->d_f_cov, &h->d_f_tip, &h->d_f_edges, &h->d_f_orig, &h->d_t_hash, &h->d_t_cov, &h->d_t_tip, &h->d_t_edges, &h->d_t_orig, &h->d_g_kept8, &h->d_u_pos, &h->d_th_final, &h->d_th_node, &h->d_th_unitig, &h->d_th_upos, &h->d_th_urest, &h->d_th_step, &h->d_thin, &h->d_thin_pos,
-		&h->d_u_begin, &h->d_u_nodes, &h->d_u_of_node, &h->d_u_fw, &h->d_u_edges, &h->d_xrow, &h->d_xmatrix, &h->d_rec_slot, &h->d_thin_scan, &h->d_tpos, &h->d_tu_nodes, &h->d_tu_off, &h->d_tu_unitig, &h->d_tu_begin, &h->d_t_newov }) release(*b);
+		&h->d_u_begin, &h->d_u_nodes, &h->d_u_of_node, &h->d_u_fw, &h->d_u_edges, &h->d_append_base, &h->d_range, &h->d_xrow, &h->d_xmatrix, &h->d_rec_slot, &h->d_thin_scan, &h->d_tpos, &h->d_tu_nodes, &h->d_tu_off, &h->d_tu_unitig, &h->d_tu_begin, &h->d_t_newov }) release(*b);
 	for (HostBuf* b : { &h->p_node_hashes, &h->p_node_cov, &h->p_node_tip, &h->p_edges, &h->p_stage }) release_host(*b);
 	for (auto& e : h->ev) if (e) cudaEventDestroy(e);
 	for (auto& e : h->piece_events) cudaEventDestroy(e);
@@ -622,6 +626,7 @@ int mbgfe_reset(mbgfe* h)
 	h->owned_bases.clear(); h->owned_offsets.clear();
 	h->resident = false;
 	h->n_reads = 0; h->n_bases = 0;
+	h->append_base = 0; h->appending = false;
 	clear_results(h);
 	return 0;
 }
@@ -762,12 +767,29 @@ uint32_t launch_front(mbgfe* h, uint32_t g0, uint32_t cnt, bool timed, cudaStrea
 // All of it is driven by instance ranges read from device memory (entries of sel_begin), so the same launches serve the
 // whole batch (mbgfe_process: exact sizes known) and one piece of it (mbgfe_run: sizes estimated, checked afterwards).
 
+// grows a buffer and keeps its first `keep` bytes (the instances of earlier batches)
+int ensure_keep(mbgfe* h, DevBuf& b, size_t bytes, size_t keep)
+{
+	bytes = (bytes + 255) & ~(size_t)255;
+	if (b.cap >= bytes) return 0;
+	if (!keep || !b.p) return ensure(h, b, bytes);
+	void* np = nullptr;
+	CU(h, cudaMalloc(&np, bytes));
+	CU(h, cudaMemcpyAsync(np, b.p, std::min(keep, b.cap), cudaMemcpyDeviceToDevice, h->stream));
+	CU(h, cudaStreamSynchronize(h->stream));
+	CU(h, cudaFree(b.p));
+	b.p = np; b.cap = bytes;
+	return 0;
+}
+
 int ensure_instances(mbgfe* h, uint64_t cap)
 {
-	if (int rc = ensure(h, h->d_inst_pos, cap * 4 + 64)) return rc;
-	if (int rc = ensure(h, h->d_inst_seg, cap * 4 + 64)) return rc;
-	if (int rc = ensure(h, h->d_inst_flag, cap + 64)) return rc;
-	if (int rc = ensure(h, h->d_inst_hash, cap * 16 + 64)) return rc;
+	const uint64_t keep = h->appending ? h->append_base : 0;
+	cap += keep > cap ? keep : 0;
+	if (int rc = ensure_keep(h, h->d_inst_pos, cap * 4 + 64, keep * 4)) return rc;
+	if (int rc = ensure_keep(h, h->d_inst_seg, cap * 4 + 64, keep * 4)) return rc;
+	if (int rc = ensure_keep(h, h->d_inst_flag, cap + 64, keep)) return rc;
+	if (int rc = ensure_keep(h, h->d_inst_hash, cap * 16 + 64, keep * 16)) return rc;
 	if (int rc = ensure(h, h->d_inst_slot, cap * 4 + 64)) return rc;
 	if (int rc = ensure(h, h->d_pal_list, PAL_CAP * 8)) return rc;
 	h->inst_cap = cap;
@@ -798,7 +820,9 @@ int clear_tables(mbgfe* h, uint64_t slots, uint32_t& launches)
 void launch_scan(mbgfe* h, uint32_t g0, uint32_t g1, uint32_t& launches)
 {
 	uint64_t* sb = h->d_sel_begin.as<uint64_t>();
-	MBGFE_LAUNCH(k_scan_u32<1024>, 1, 1024, 0, h->stream, h->d_seg_nsel.as<uint32_t>() + g0, sb + g0, g1 - g0, g0 ? (const uint64_t*)(sb + g0) : (const uint64_t*)nullptr);
+	// the scan of the first segments starts from the instances earlier batches left (mbgfe_run_append), else from 0
+	const uint64_t* first_carry = (h->appending && h->append_base) ? h->d_append_base.as<uint64_t>() : (const uint64_t*)nullptr;
+	MBGFE_LAUNCH(k_scan_u32<1024>, 1, 1024, 0, h->stream, h->d_seg_nsel.as<uint32_t>() + g0, sb + g0, g1 - g0, g0 ? (const uint64_t*)(sb + g0) : first_carry);
 	launches++;
 }
 
@@ -823,7 +847,7 @@ void launch_list_hash(mbgfe* h, uint32_t g0, uint32_t g1, uint64_t n_hint, uint3
 // K4a + K4b for the instances of segments [g0, g1)
 void launch_tables(mbgfe* h, uint32_t g0, uint32_t g1, uint64_t n_hint, uint32_t& launches, bool timed)
 {
-	if (h->prm.flags & MBGFE_NO_TABLE) { if (timed) { tick(h, 8); tick(h, 9); } return; }
+	if ((h->prm.flags & MBGFE_NO_TABLE) || h->appending) { if (timed) { tick(h, 8); tick(h, 9); } return; }
 	unsigned long long* ctr = h->d_counters.as<unsigned long long>();
 	const uint64_t* sb = h->d_sel_begin.as<uint64_t>();
 	const unsigned grid = n_hint ? (unsigned)((n_hint + 255) / 256) : (unsigned)h->sm_count * 8;
@@ -914,7 +938,7 @@ int process_tail(mbgfe* h, uint32_t launches)
 			h->d_inst_pos.as<uint32_t>(), h->d_inst_seg.as<uint32_t>(), n_inst, h->d_seg_out.as<uint64_t>(), h->d_pos2.as<uint32_t>(), vt, k);
 		launches++;
 	}
-	if (!(h->prm.flags & MBGFE_NO_TABLE))
+	if (!(h->prm.flags & MBGFE_NO_TABLE) && !h->appending)
 	{
 		const uint64_t slots = std::max<uint64_t>(next_pow2(std::max<uint64_t>(2 * n_inst, 1024)), h->prm.table_slots ? next_pow2(h->prm.table_slots) : 0);
 		if (int rc = clear_tables(h, slots, launches)) return rc;
@@ -1082,7 +1106,7 @@ int mbgfe_run(mbgfe* h)
 	// ---- phase B: behind each piece, K0 on its bytes and K1 .. K4 on the segments it completes.  The instance lists and
 	// the tables are sized from the first piece that completes segments (selected k-mers per base, extrapolated); the
 	// kernels refuse to write past those sizes and count what they refused, and the exact path reruns the tail then.
-	const bool want_table = !(h->prm.flags & MBGFE_NO_TABLE);
+	const bool want_table = !(h->prm.flags & MBGFE_NO_TABLE) && !h->appending;
 	unsigned long long* ctr = h->d_counters.as<unsigned long long>();
 	uint64_t packed_upto = 0;
 	uint32_t g_done = 0, g_tail = 0, launches = 0;
@@ -1128,8 +1152,11 @@ int mbgfe_run(mbgfe* h)
 			h->stats.d2h_bytes += 8;
 			const uint64_t bases0 = read_end_of(h, h->seg_read[g_end - 1]);
 			const double per_base = (double)n0 / (double)std::max<uint64_t>(bases0, 1);
-			const uint64_t est = (uint64_t)(per_base * (double)n_bases) + 1;
-			if (int rc = ensure_instances(h, std::max<uint64_t>(est + est / 4 + 4096, h->inst_cap))) return rc;
+			n0 -= std::min<uint64_t>(n0, h->appending ? h->append_base : 0);
+			const double per_base2 = (double)n0 / (double)std::max<uint64_t>(bases0, 1);
+			const uint64_t est = (uint64_t)(per_base2 * (double)n_bases) + 1;
+			(void)per_base;
+			if (int rc = ensure_instances(h, std::max<uint64_t>(est + est / 4 + 4096 + (h->appending ? h->append_base : 0), h->inst_cap))) return rc;
 			if (want_table)
 			{
 				const uint64_t slots = std::max<uint64_t>(next_pow2(std::max<uint64_t>(2 * est, 1024)), h->prm.table_slots ? next_pow2(h->prm.table_slots) : 0);
@@ -1356,7 +1383,7 @@ int run_files(mbgfe* h)
 		out += ((s1 - s0) + 1 + 63) & ~(uint64_t)63;
 	};
 	st.emit = emit_read;
-	const bool want_table = !(h->prm.flags & MBGFE_NO_TABLE);
+	const bool want_table = !(h->prm.flags & MBGFE_NO_TABLE) && !h->appending;
 	unsigned long long* ctr = h->d_counters.as<unsigned long long>();
 	uint32_t g_done = 0, g_tail = 0, launches = 0;
 	uint64_t h2d_bytes = 0;
@@ -1413,9 +1440,10 @@ int run_files(mbgfe* h)
 			CU(h, cudaMemcpyAsync(&n0, h->d_sel_begin.as<uint64_t>() + g_end, 8, cudaMemcpyDeviceToHost, h->stream));
 			CU(h, cudaStreamSynchronize(h->stream));
 			h->stats.d2h_bytes += 8;
+			n0 -= std::min<uint64_t>(n0, h->appending ? h->append_base : 0);
 			const double per_byte = (double)n0 / (double)std::max<uint64_t>(pc.pos + pc.len, 1);
 			const uint64_t est = (uint64_t)(per_byte * (double)n_image) + 1;
-			if (int rc = ensure_instances(h, std::max<uint64_t>(est + est / 4 + 4096, h->inst_cap))) return rc;
+			if (int rc = ensure_instances(h, std::max<uint64_t>(est + est / 4 + 4096 + (h->appending ? h->append_base : 0), h->inst_cap))) return rc;
 			if (want_table)
 			{
 				const uint64_t slots = std::max<uint64_t>(next_pow2(std::max<uint64_t>(2 * est, 1024)), h->prm.table_slots ? next_pow2(h->prm.table_slots) : 0);
@@ -2583,6 +2611,69 @@ int mbgfe_exchange_group(mbgfe** handles, uint32_t n)
 		hs[i]->comm_kind = 2;
 	}
 	return exchange_run(hs);
+}
+
+// Input larger than one resident batch (the reference streams any volume through its queue into one HashList,
+// MBG/ReadHelper.h:102-160): the front end runs batch by batch, the selected k-mers (position, flags, 128-bit hash: 25 bytes each,
+// a few per thousand bases) of every batch stay on the device, and the tables are built once over all of them.
+int mbgfe_run_append(mbgfe* h)
+{
+	if (!h) return MBGFE_E_PARAM;
+	if (h->n_var) return fail(h, MBGFE_E_STATE, "mbgfe_run_append with hpc variants registered: not supported");
+	h->append_base = h->processed ? h->n_inst : 0;
+	h->appending = true;
+	if (int rc = ensure(h, h->d_append_base, 64)) { h->appending = false; return rc; }
+	cudaMemcpyAsync(h->d_append_base.p, &h->append_base, 8, cudaMemcpyHostToDevice, h->stream);
+	cudaStreamSynchronize(h->stream);
+	const int rc = mbgfe_run(h);
+	h->appending = false;
+	return rc;
+}
+
+int mbgfe_build_table(mbgfe* h)
+{
+	if (!h) return MBGFE_E_PARAM;
+	if (!h->processed) return fail(h, MBGFE_E_STATE, "mbgfe_build_table before a run");
+	if (h->prm.flags & MBGFE_NO_TABLE) return fail(h, MBGFE_E_STATE, "mbgfe_build_table on a handle created with MBGFE_NO_TABLE (sharded tables are built by mbgfe_exchange)");
+	uint32_t launches = 0;
+	unsigned long long* ctr = h->d_counters.as<unsigned long long>();
+	const uint64_t n_inst = h->n_inst;
+	const uint64_t slots = std::max<uint64_t>(next_pow2(std::max<uint64_t>(2 * n_inst, 1024)), h->prm.table_slots ? next_pow2(h->prm.table_slots) : 0);
+	if (int rc = ensure(h, h->d_range, 64)) return rc;
+	const uint64_t range[2] = { 0, n_inst };
+	CU(h, cudaMemcpyAsync(h->d_range.p, range, 16, cudaMemcpyHostToDevice, h->stream));
+	CU(h, cudaMemsetAsync(ctr + CTR_DISTINCT, 0, 16, h->stream));
+	CU(h, cudaMemsetAsync(ctr + CTR_OVERFLOW, 0, 8, h->stream));
+	if (int rc = ensure(h, h->d_inst_slot, (n_inst + 1) * 4 + 64)) return rc;
+	tick(h, 7);
+	if (int rc = clear_tables(h, slots, launches)) return rc;
+	const unsigned grid = (unsigned)std::max<uint64_t>(1, (n_inst + 255) / 256);
+	const uint64_t* rg = h->d_range.as<uint64_t>();
+	if (n_inst)
+	{
+		MBGFE_LAUNCH(k_insert_nodes, grid, 256, 0, h->stream, h->d_inst_hash.as<uint64_t>(), h->d_inst_flag.as<uint8_t>(), rg, rg + 1, h->inst_cap, h->d_nodes.as<NodeSlot>(),
+			h->node_slots - 1, h->d_inst_slot.as<uint32_t>(), ctr + CTR_DISTINCT, ctr + CTR_OVERFLOW);
+		launches++;
+	}
+	tick(h, 8);
+	if (n_inst && !(h->prm.flags & MBGFE_NO_EDGES))
+	{
+		MBGFE_LAUNCH(k_insert_edges, grid, 256, 0, h->stream, h->d_inst_hash.as<uint64_t>(), h->d_inst_pos.as<uint32_t>(), h->d_inst_flag.as<uint8_t>(), h->d_inst_slot.as<uint32_t>(),
+			rg, rg + 1, h->inst_cap, h->d_edges.as<EdgeSlot>(), h->edge_slots - 1, ctr + CTR_EDGES, ctr + CTR_OVERFLOW, h->prm.k);
+		launches++;
+	}
+	tick(h, 9);
+	unsigned long long five[5] = { 0, 0, 0, 0, 0 };
+	CU(h, cudaMemcpyAsync(five, ctr + CTR_DISTINCT, sizeof(five), cudaMemcpyDeviceToHost, h->stream));
+	CU(h, cudaStreamSynchronize(h->stream));
+	CU(h, cudaGetLastError());
+	if (five[CTR_OVERFLOW - CTR_DISTINCT]) return fail(h, MBGFE_E_LIMIT, "k-mer table of %llu slots overflowed", (unsigned long long)slots);
+	h->stats.distinct = five[0]; h->stats.distinct_edges = five[1]; h->stats.table_slots = slots;
+	h->stats.ms_nodes = elapsed(h, 7, 8); h->stats.ms_edges = elapsed(h, 8, 9);
+	h->stats.launches = launches;
+	h->have_table = true; h->exported_table = false; h->nodes_ranked = false; h->edges_global = false; h->table_sharded = false; h->id_base = 0;
+	h->have_unitigs = false; h->have_thin = false; h->have_threads = false;
+	return 0;
 }
 
 int mbgfe_set_variants(mbgfe* h, const mbgfe_hash128* hashes, const uint32_t* offsets, const uint64_t* len_begin, const uint32_t* lengths, uint64_t n_entries)

@@ -74,7 +74,7 @@ def load_library(path=None):
     L.mbgfe_add_file.argtypes = [C.c_void_p, C.c_char_p]
     L.mbgfe_read_name.argtypes = [C.c_void_p, C.c_uint64]
     L.mbgfe_read_name.restype = C.c_char_p
-    for f in (L.mbgfe_reset, L.mbgfe_upload, L.mbgfe_process, L.mbgfe_run):
+    for f in (L.mbgfe_reset, L.mbgfe_upload, L.mbgfe_process, L.mbgfe_run, L.mbgfe_run_append, L.mbgfe_build_table):
         f.argtypes = [C.c_void_p]
     L.mbgfe_count.argtypes = [C.c_void_p, C.c_int]
     L.mbgfe_count.restype = C.c_uint64
@@ -201,6 +201,14 @@ class MbgFrontEnd:
     def run(self):
         self._check(self.lib.mbgfe_run(self.handle))
         self._keep = []
+
+    def run_append(self):
+        """mbgfe_run on the pending reads, keeping the selected k-mers of earlier batches; tables come from build_table() / exchange()"""
+        self._check(self.lib.mbgfe_run_append(self.handle))
+        self._keep = []
+
+    def build_table(self):
+        self._check(self.lib.mbgfe_build_table(self.handle))
 
     # ---- results
     def count(self, what):
