@@ -39,6 +39,8 @@ WORKLOADS = {
     "herro": dict(genome=64_000_000, coverage=30, len_min=30000, len_max=50000, error_ppm=7500, k=1001, w=100,
                   desc="HERRO/ONT-duplex-shaped synthetic reads 30x (64 Mbp per GPU, 30-50 kb reads, 0.75% errors), MBG k=1001 w=100 collapse-msat"),
 }
+HG002 = dict(genome=3_100_000_000, coverage=30, len_min=15000, len_max=20000, error_ppm=1000, k=1001, w=100, batch_reads=110_000,
+             desc="HG002-shaped synthetic diploid HiFi (3.1 Gbp x 2 haplotypes, 0.1% SNPs, 15-20 kb reads, 0.1% errors), MBG k=1001 w=100 collapse-msat")
 METRIC = "raw HiFi bases/s through the MBG graph-build front end (HPC+microsatellite compression, syncmer selection k=1001 w=100, 128-bit k-mer hashing, k-mer counting)"
 SEED_GENOME, SEED_READS = 7, 11
 
@@ -253,6 +255,116 @@ def cpu_baseline(wl, scale, device=0):
     return out, {f: mine[f] for f in DETERMINISTIC}, bad
 
 
+def run_hg002(args, rank, world, local_rank, dist, torch, emit):
+    """BASELINE.json configs[2]: the HG002-shaped diploid set sharded over the GPUs of one box.  TOTAL work is fixed (strong
+    scaling): 2 x 3.1 Gbp x 30x x --scale bases, rank r takes every world-th block of reads, in batches of 110 000 reads (one
+    chr20-sized resident batch each) through mbgfe_run_append; ONE exchange (or mbgfe_build_table at N = 1) counts the selected
+    k-mers of all batches.  --scale < 1 lowers the coverage (host memory: every batch sits in pinned memory before the clock starts)."""
+    from verkko_b200 import MbgFrontEnd, synth
+    from verkko_b200.frontend import NO_TABLE
+    wl = HG002
+    hap_len = int(wl["genome"] * args.genome_scale)
+    hap1 = synth.genome(SEED_GENOME, hap_len)
+    rng = np.random.default_rng(5)
+    hap2 = hap1.copy()
+    idx = rng.integers(0, hap_len, hap_len // 1000)
+    hap2[idx] = np.frombuffer(b"ACGT", dtype=np.uint8)[rng.integers(0, 4, len(idx))]
+    genome = np.concatenate([hap1, hap2])
+    del hap1, hap2
+    mean_len = (wl["len_min"] + wl["len_max"]) / 2
+    total_reads = int(2 * hap_len * wl["coverage"] * args.scale / mean_len)
+    per_rank = total_reads // world
+    sharded = world > 1
+    fe = MbgFrontEnd(wl["k"], wl["w"], "collapse-msat", device=local_rank, rank=rank, world=world, flags=NO_TABLE if sharded else 0)
+    if sharded:
+        uid = [fe.unique_id() if rank == 0 else None]
+        dist.broadcast_object_list(uid, src=0)
+        fe.comm_init_nccl(uid[0])
+    batches, keep = [], []
+    first = rank * per_rank
+    for b0 in range(0, per_rank, wl["batch_reads"]):
+        n = min(wl["batch_reads"], per_rank - b0)
+        offsets = synth.read_offsets(SEED_READS, genome, n, wl["len_min"], wl["len_max"], wl["error_ppm"], first_read=first + b0)
+        buf = fe.pinned(int(offsets[-1]) + 64)
+        synth.fill_reads(SEED_READS, genome, n, wl["len_min"], wl["len_max"], offsets, buf.array[:int(offsets[-1])], wl["error_ppm"], first_read=first + b0)
+        batches.append((buf.array[:int(offsets[-1])], offsets))
+        keep.append(buf)
+    del genome
+    n_bases = sum(int(o[-1]) for _, o in batches)
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+
+    def finish():
+        if sharded:
+            fe.exchange()
+        else:
+            fe.build_table()
+    # ---- resident per batch: upload untimed, front end timed on the device, then the table / exchange
+    def resident_step():
+        fe.reset()
+        ms = 0.0
+        for b, o in batches:
+            fe.add_reads(b, o)
+            fe.upload_append()
+            fe.timer_start()
+            fe.process_append()
+            ms += fe.timer_stop()
+        fe.timer_start()
+        finish()
+        return ms + fe.timer_stop()
+    for _ in range(args.warmup):
+        resident_step()
+    sampler = ClockSampler(local_rank)
+    barrier()
+    sampler.start()
+    dev_ms = [resident_step() for _ in range(args.steps)]
+    barrier()
+    clocks = sampler.stop()
+    st = fe.stats()
+    # ---- end to end: every batch from pinned host memory, the table (partition) read back
+    e2e_ms, checksum = [], 0
+    for it in range(1 + args.e2e_steps):
+        barrier()
+        t0 = time.time()
+        fe.reset()
+        for b, o in batches:
+            fe.add_reads(b, o)
+            fe.run_append()
+        finish()
+        cov = fe.node_coverage(copy=False)
+        checksum = int(cov[::1024].sum(dtype=np.uint64)) + len(fe.node_hashes(copy=False)) + len(fe.edges(copy=False))
+        barrier()
+        if it > 0:
+            e2e_ms.append((time.time() - t0) * 1e3)
+    st_e = fe.stats()
+    t = torch.tensor([float(np.mean(dev_ms)), float(np.mean(e2e_ms))], dtype=torch.float64)
+    sm = torch.tensor([float(n_bases), float(st_e["selected"]), float(st_e["distinct"]), float(st_e["distinct_edges"])], dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        dist.all_reduce(sm, op=dist.ReduceOp.SUM)
+    if rank == 0:
+        peak, peak_src = measured_peak()
+        line = {"metric": METRIC, "value": float(sm[0]) / (float(t[0]) * 1e-3), "unit": "bases/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+                "ms_per_step": float(t[0]), "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "u16 codes / u64 hashes (integer)", "data": "synthetic",
+                "config": {"workload": wl["desc"] + f", {wl['coverage'] * args.scale:g}x" + (f", genome x{args.genome_scale}" if args.genome_scale != 1 else ""), "k": wl["k"], "w": wl["w"],
+                           "error_masking": "collapse-msat", "batches_per_gpu": len(batches), "bases_per_gpu": n_bases, "total_bases": float(sm[0]),
+                           "parallelism": f"reads sharded over {world} GPU(s) in batches (mbgfe_run_append), k-mers owned by hash range, one mbgfe_exchange over NCCL",
+                           "l2": "every batch (>= 0.48 GB packed) is larger than the 126 MB L2"},
+                "kmers_per_s": float(sm[1]) / (float(t[0]) * 1e-3), "counts": {"selected_kmers": float(sm[1]), "distinct_kmers": float(sm[2]), "distinct_edges": float(sm[3])},
+                "exchange": {"ms": st["ms_exchange"], "bytes_sent_rank0": st["exchange_bytes"], "launches": st["exchange_launches"],
+                             "nvlink_GBps_rank0": (st["exchange_bytes"] / (st["ms_exchange"] * 1e-3) / 1e9) if st["ms_exchange"] > 0 else None, "nvlink_peak_GBps": 900.0},
+                "clocks": clocks, "gpu_launches": int((st["launches"] * len(batches) + st["exchange_launches"]) * args.steps),
+                "e2e": {"value": float(sm[0]) / (float(t[1]) * 1e-3), "unit": "bases/s", "ms_per_step": float(t[1]), "h2d_bytes_per_step": int(st_e["h2d_bytes"] * len(batches)),
+                        "d2h_bytes_per_step": int(st_e["d2h_bytes"]), "checksum": checksum}}
+        emit(json.dumps(line))
+    if world > 1:
+        dist.barrier()
+    fe.close()
+
+
 def main():
     # stdout carries exactly ONE JSON line (rank 0).  Libraries chat on fd 1 (NCCL prints its version banner there when the
     # first communicator is made), so fd 1 is pointed at stderr for the whole run and the line goes to the saved descriptor.
@@ -267,7 +379,8 @@ def main():
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--workload", default="chr20", choices=list(WORKLOADS))
+    ap.add_argument("--workload", default="chr20", choices=list(WORKLOADS) + ["hg002"])
+    ap.add_argument("--genome-scale", type=float, default=1.0, help="hg002: shrink the genome (quick runs)")
     ap.add_argument("--scale", type=float, default=1.0, help="shrink the genome (and read count) for quick runs")
     ap.add_argument("--e2e-steps", type=int, default=0, help="timed end-to-end steps (0 = --steps)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
@@ -275,7 +388,7 @@ def main():
     ap.add_argument("--k", type=int, default=0, help="k-mer size override (BASELINE.json configs[4]: the k/w sweep)")
     ap.add_argument("--w", type=int, default=0, help="window size override")
     args = ap.parse_args()
-    wl = dict(WORKLOADS[args.workload])
+    wl = dict(WORKLOADS[args.workload if args.workload != "hg002" else "chr20"])
     if args.k or args.w:
         wl["k"], wl["w"] = args.k or wl["k"], args.w or wl["w"]
         wl["desc"] = wl["desc"].replace("k=1001 w=100", f"k={wl['k']} w={wl['w']}")
@@ -299,6 +412,14 @@ def main():
     if world > 1 or force_exchange:
         if os.environ.get("NCCL_DEBUG", "VERSION").upper() == "VERSION":
             os.environ["NCCL_DEBUG"] = "WARN"       # keep NCCL's version banner off stdout: rank 0 prints ONE JSON line
+    if args.workload == "hg002":
+        if world > 1:
+            os.environ.setdefault("NCCL_DEBUG", "WARN")
+            dist.init_process_group("gloo")
+        run_hg002(args, rank, world, local_rank, dist, torch, emit)
+        if world > 1:
+            dist.destroy_process_group()
+        return
     if world > 1:
         # torch.distributed is host plumbing only (gloo: the NCCL id hand-out, barriers, max / sum of a few scalars); the data path
         # collectives run inside libmbgfe on its own NCCL communicator (mbgfe_comm_init_nccl / mbgfe_exchange)

@@ -196,6 +196,8 @@ int mbgfe_run(mbgfe* h);
  * MBGFE_CODES the last one) and no table is built.  When every batch is in: mbgfe_build_table() counts all of them into one node /
  * edge table (single GPU), or mbgfe_exchange() into the sharded one.  mbgfe_reset() / mbgfe_run() start over. */
 int mbgfe_run_append(mbgfe* h);
+int mbgfe_upload_append(mbgfe* h);     /* the same in two steps: upload the next batch ...                              */
+int mbgfe_process_append(mbgfe* h);    /* ... and run the front end on it (repeatable: replaces this batch's instances) */
 int mbgfe_build_table(mbgfe* h);
 
 /* Results (downloaded and, for the tables, ordered on first request). */

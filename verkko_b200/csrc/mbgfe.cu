@@ -2616,19 +2616,33 @@ int mbgfe_exchange_group(mbgfe** handles, uint32_t n)
 // Input larger than one resident batch (the reference streams any volume through its queue into one HashList,
 // MBG/ReadHelper.h:102-160): the front end runs batch by batch, the selected k-mers (position, flags, 128-bit hash: 25 bytes each,
 // a few per thousand bases) of every batch stay on the device, and the tables are built once over all of them.
-int mbgfe_run_append(mbgfe* h)
+static int append_call(mbgfe* h, int (*what)(mbgfe*), bool fresh_batch)
 {
 	if (!h) return MBGFE_E_PARAM;
-	if (h->n_var) return fail(h, MBGFE_E_STATE, "mbgfe_run_append with hpc variants registered: not supported");
-	h->append_base = h->processed ? h->n_inst : 0;
+	if (h->n_var) return fail(h, MBGFE_E_STATE, "append runs with hpc variants registered: not supported");
+	// mbgfe_process_append after mbgfe_upload: the upload cleared the results of the batch before but not its instances
+	if (fresh_batch) h->append_base = h->processed ? h->n_inst : 0;
 	h->appending = true;
 	if (int rc = ensure(h, h->d_append_base, 64)) { h->appending = false; return rc; }
 	cudaMemcpyAsync(h->d_append_base.p, &h->append_base, 8, cudaMemcpyHostToDevice, h->stream);
 	cudaStreamSynchronize(h->stream);
-	const int rc = mbgfe_run(h);
+	const int rc = what(h);
 	h->appending = false;
 	return rc;
 }
+int mbgfe_run_append(mbgfe* h) { return append_call(h, mbgfe_run, true); }
+// resident form: mbgfe_upload_append() brings the next batch in (the instances of the batches before it stay), mbgfe_process_append()
+// runs the front end on it and may be repeated (each repetition replaces this batch's instances, not the earlier ones)
+int mbgfe_upload_append(mbgfe* h)
+{
+	if (!h) return MBGFE_E_PARAM;
+	h->append_base = h->processed ? h->n_inst : 0;
+	const uint64_t keep = h->append_base;
+	const int rc = mbgfe_upload(h);
+	h->append_base = keep;
+	return rc;
+}
+int mbgfe_process_append(mbgfe* h) { return append_call(h, mbgfe_process, false); }
 
 int mbgfe_build_table(mbgfe* h)
 {

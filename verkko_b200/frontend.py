@@ -74,7 +74,7 @@ def load_library(path=None):
     L.mbgfe_add_file.argtypes = [C.c_void_p, C.c_char_p]
     L.mbgfe_read_name.argtypes = [C.c_void_p, C.c_uint64]
     L.mbgfe_read_name.restype = C.c_char_p
-    for f in (L.mbgfe_reset, L.mbgfe_upload, L.mbgfe_process, L.mbgfe_run, L.mbgfe_run_append, L.mbgfe_build_table):
+    for f in (L.mbgfe_reset, L.mbgfe_upload, L.mbgfe_process, L.mbgfe_run, L.mbgfe_run_append, L.mbgfe_upload_append, L.mbgfe_process_append, L.mbgfe_build_table):
         f.argtypes = [C.c_void_p]
     L.mbgfe_count.argtypes = [C.c_void_p, C.c_int]
     L.mbgfe_count.restype = C.c_uint64
@@ -206,6 +206,13 @@ class MbgFrontEnd:
         """mbgfe_run on the pending reads, keeping the selected k-mers of earlier batches; tables come from build_table() / exchange()"""
         self._check(self.lib.mbgfe_run_append(self.handle))
         self._keep = []
+
+    def upload_append(self):
+        self._check(self.lib.mbgfe_upload_append(self.handle))
+        self._keep = []
+
+    def process_append(self):
+        self._check(self.lib.mbgfe_process_append(self.handle))
 
     def build_table(self):
         self._check(self.lib.mbgfe_build_table(self.handle))
