@@ -2396,6 +2396,18 @@ int exchange_run(std::vector<mbgfe*>& hs)
 	const size_t row = 2 * world + 1;                       // node counts, edge counts, instances
 	std::vector<const void*> sp(nh); std::vector<void*> rp(nh);
 	auto on = [&](mbgfe* h) { return cudaSetDevice(h->prm.device); };
+	// MBGFE_EXCHANGE_TRACE=1: device time of every phase of rank hs[0] on stderr (synchronises after each phase: for diagnosis only)
+	const bool trace = getenv("MBGFE_EXCHANGE_TRACE") != nullptr;
+	cudaEvent_t tr0 = nullptr, tr1 = nullptr;
+	if (trace) { cudaEventCreate(&tr0); cudaEventCreate(&tr1); cudaEventRecord(tr0, hs[0]->stream); }
+	auto mark = [&](const char* name)
+	{
+		if (!trace) return;
+		cudaEventRecord(tr1, hs[0]->stream); cudaEventSynchronize(tr1);
+		float ms = 0; cudaEventElapsedTime(&ms, tr0, tr1);
+		fprintf(stderr, "[exchange rank %u] %-22s %8.3f ms\n", hs[0]->prm.rank, name, ms);
+		cudaEventRecord(tr0, hs[0]->stream);
+	};
 	// ---- S1: counts of both collectives
 	for (size_t x = 0; x < nh; x++)
 	{
@@ -2411,7 +2423,9 @@ int exchange_run(std::vector<mbgfe*>& hs)
 		CU(h, cudaMemcpyAsync(h->d_xrow.as<uint64_t>() + 2 * world, &h->n_inst, 8, cudaMemcpyHostToDevice, h->stream));
 		sp[x] = h->d_xrow.p; rp[x] = h->d_xmatrix.p;
 	}
+	mark("count kernel");
 	if (int rc = x_allgather(hs, sp, rp, row * 8)) return rc;
+	mark("count all-gather");
 	std::vector<std::vector<uint64_t>> M(nh, std::vector<uint64_t>(row * world));
 	for (size_t x = 0; x < nh; x++) { mbgfe* h = hs[x]; CU(h, on(h)); CU(h, cudaMemcpyAsync(M[x].data(), h->d_xmatrix.p, row * world * 8, cudaMemcpyDeviceToHost, h->stream)); }
 	for (size_t x = 0; x < nh; x++) { mbgfe* h = hs[x]; CU(h, on(h)); CU(h, cudaStreamSynchronize(h->stream)); }
@@ -2444,7 +2458,9 @@ int exchange_run(std::vector<mbgfe*>& hs)
 		CU(h, cudaStreamSynchronize(h->stream));      // `cursors` is a host temporary of this iteration
 		sp[x] = h->d_records.p; rp[x] = h->d_recv.p;
 	}
+	mark("node pack");
 	if (int rc = x_alltoallv(hs, sp, nsend, rp, nrecv, 32)) return rc;
+	mark("node all-to-all");
 	// ---- S3: this rank's partition of the node table
 	for (size_t x = 0; x < nh; x++)
 	{
@@ -2465,7 +2481,9 @@ int exchange_run(std::vector<mbgfe*>& hs)
 		h->stats.table_slots = slots;
 		sp[x] = ctr + CTR_DISTINCT; rp[x] = h->d_xmatrix.p;
 	}
+	mark("table clear + insert");
 	if (int rc = x_allgather(hs, sp, rp, 8)) return rc;
+	mark("sizes all-gather");
 	std::vector<std::vector<uint64_t>> sizes(nh, std::vector<uint64_t>(world));
 	for (size_t x = 0; x < nh; x++) { mbgfe* h = hs[x]; CU(h, on(h)); CU(h, cudaMemcpyAsync(sizes[x].data(), h->d_xmatrix.p, world * 8, cudaMemcpyDeviceToHost, h->stream)); }
 	for (size_t x = 0; x < nh; x++) { mbgfe* h = hs[x]; CU(h, on(h)); CU(h, cudaStreamSynchronize(h->stream)); }
@@ -2493,7 +2511,9 @@ int exchange_run(std::vector<mbgfe*>& hs)
 	}
 	if (!(hs[0]->prm.flags & MBGFE_NO_EDGES))
 	{
+		mark("rank nodes + ids");
 		if (int rc = x_alltoallv(hs, sp, nrecv, rp, nsend, 4)) return rc;
+		mark("id all-to-all");
 		// ---- S5: edge observations to the owner of their `from` node
 		for (size_t x = 0; x < nh; x++)
 		{
@@ -2512,7 +2532,9 @@ int exchange_run(std::vector<mbgfe*>& hs)
 			CU(h, cudaStreamSynchronize(h->stream));
 			sp[x] = h->d_edge_records.p; rp[x] = h->d_xbuf[1].p;
 		}
+		mark("edge pack");
 		if (int rc = x_alltoallv(hs, sp, esend, rp, erecv, 16)) return rc;
+		mark("edge all-to-all");
 		for (size_t x = 0; x < nh; x++)
 		{
 			mbgfe* h = hs[x];
@@ -2529,6 +2551,8 @@ int exchange_run(std::vector<mbgfe*>& hs)
 			h->edges_global = true;
 		}
 	}
+	mark("edge clear + insert");
+	if (trace) { cudaEventDestroy(tr0); cudaEventDestroy(tr1); }
 	// ---- the final counters
 	for (size_t x = 0; x < nh; x++)
 	{
