@@ -296,3 +296,28 @@ def test_t4_backend_with_hpc_variants_verkko_flags(oracle, reference, tmp_path):
                                    node_hash=th.node_hash, node_cov=th.node_cov, node_tip=th.node_tip, edges=th.edges, new_overlaps=ov,
                                    unitig_begin=th.unitig_begin, unitig_nodes=th.unitig_nodes, unitig_edges=th.unitig_edges)
     assert hashlib.md5(gfa1).hexdigest() == hashlib.md5(want_gfa).hexdigest() and hashlib.md5(gaf1).hexdigest() == hashlib.md5(want_gaf).hexdigest(), "stage 1"
+
+
+def test_dropin_executable_argv_and_failure_modes(reference, tmp_path):
+    """oracle/_ref/MBG_b200 (integration build: MBG's main.cpp + back end around libmbgfe, oracle/mbg_b200.cpp) without a GPU: options
+    outside the B200 front end run the reference's own runMBG (renamed, not removed) and give MBG's files; the B200 path itself fails
+    loudly instead of falling back; MBG's own argument validation is untouched (main.cpp:158-198)."""
+    import subprocess
+    import torch
+    from oracle_lib import REF_MBG, write_fasta
+    exe = os.path.join(os.path.dirname(REF_MBG), "MBG_b200")
+    if not os.path.exists(exe):
+        pytest.skip("oracle/_ref/MBG_b200 not built (make -C oracle ref dropin)")
+    bases, offsets = workloads.as_pair(workloads.coverage_reads(genome_len=40000, n_reads=60, len_min=6000, len_max=10000, error_ppm=2000))
+    fa = tmp_path / "reads.fa"
+    write_fasta(fa, bases, offsets)
+    args = ["-i", str(fa), "-k", "301", "-w", "30", "-a", "1", "-u", "2", "-t", "1", "--error-masking=collapse-msat", "-r", "1500", "-R", "400", "--do-unsafe-guesswork-resolutions", "--keep-gaps"]
+    subprocess.run([REF_MBG] + args + ["-o", str(tmp_path / "a.gfa"), "--output-sequence-paths", str(tmp_path / "a.gaf")], check=True, stderr=subprocess.DEVNULL)
+    r = subprocess.run([exe] + args + ["-o", str(tmp_path / "b.gfa"), "--output-sequence-paths", str(tmp_path / "b.gaf")], stderr=subprocess.PIPE)
+    assert r.returncode == 0 and b"reference path" in r.stderr
+    assert (tmp_path / "a.gfa").read_bytes() == (tmp_path / "b.gfa").read_bytes() and (tmp_path / "a.gaf").read_bytes() == (tmp_path / "b.gaf").read_bytes()
+    r = subprocess.run([exe, "-i", str(fa), "-o", str(tmp_path / "c.gfa"), "-k", "300", "-w", "30"], stderr=subprocess.PIPE)      # even k: MBG's own check
+    assert r.returncode != 0
+    if not torch.cuda.is_available():
+        r = subprocess.run([exe] + args[:-1] + ["-o", str(tmp_path / "d.gfa")], stderr=subprocess.PIPE)
+        assert r.returncode != 0 and b"no CPU path" in r.stderr
