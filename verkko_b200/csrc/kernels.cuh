@@ -987,126 +987,6 @@ __global__ void __launch_bounds__(NT) k_select(SegTable seg, const uint16_t* __r
 	if (threadIdx.x == 0) seg_nsel[g] = total_sel;
 }
 
-// K3a, lane-sequential form (the default when 8 <= w <= 128; k_select above serves the other window sizes).
-// k_select is bound by the ALU pipe at ~150 thread instructions per code: prefix scan (37), two ring reads and two variable
-// rotations per hash (28), suffix / block / running minima per decision (36), rings and barriers.  Here every LANE does what one
-// CPU thread of the reference does -- it rolls the hash through its own chunk of a read (MBG/FastHasher.h:16-27: two table entries,
-// two rotations by one, four XORs per position) and slides the window minimum along -- so nothing is scanned, shuffled or
-// synchronised: ~65 instructions per code.  A chunk is L k-mer positions of one segment; its first hash costs s add steps (the
-// s-mer before the chunk is not available), which is why L is a few times s.
-// Window minimum without a deque (van Herk / Gil-Werman blocks of w hashes): the lane keeps the last w hashes in its own column of a
-// shared-memory ring; when a block is complete it is swept backwards into suffix minima (+ one flag per entry: "not above anything
-// after it in the block"); the window of k-mer p = suffix of the previous block from p + running prefix of the current block.
-//   left end selected   <=> flag(p) and suffix(p) <= prefix      (h[p] is the window minimum; ties kept as the reference keeps them)
-//   right end selected  <=> h[p+w-1] == prefix and prefix <= suffix(p)
-// add4/rem4 and tab_add/tab_rem: per-code table entries with the rotations by s and s-1 of FastHasher::precalcRots folded in
-// (k_build_roll_tables), plain bases from shared memory.
-// dynamic shared memory = warps per CTA * w * (256 + 32) bytes.
-__global__ void __launch_bounds__(256) k_build_roll_tables(const uint4* __restrict__ tab_pair, uint32_t s, uint4* __restrict__ tab_add, uint4* __restrict__ tab_rem)
-{
-	const uint32_t c = blockIdx.x * blockDim.x + threadIdx.x;
-	if (c >= MAX_CODE) return;
-	const uint4 v = tab_pair[c];
-	const uint64_t hf = u64_of(v.x, v.y), hb = u64_of(v.z, v.w);
-	const uint64_t ba = rotl64(hb, (s + 63) & 63), fr = rotl64(hf, s & 63), br = rotr64(hb, 1);      // bwAdd, fwRemove, bwRemove (MBG/FastHasher.cpp:58-72)
-	tab_add[c] = make_uint4((uint32_t)hf, (uint32_t)(hf >> 32), (uint32_t)ba, (uint32_t)(ba >> 32));
-	tab_rem[c] = make_uint4((uint32_t)fr, (uint32_t)(fr >> 32), (uint32_t)br, (uint32_t)(br >> 32));
-}
-
-// chunks per segment (and the selected count, which the lanes add to, reset)
-__global__ void __launch_bounds__(256) k_select_chunks(const uint32_t* __restrict__ seg_c2, uint32_t n_seg, uint32_t k, uint32_t L, uint32_t* __restrict__ n_chunks, uint32_t* __restrict__ seg_nsel)
-{
-	const uint32_t g = blockIdx.x * blockDim.x + threadIdx.x;
-	if (g >= n_seg) return;
-	const uint32_t n = seg_c2[g];
-	n_chunks[g] = n >= k ? (n - k + 1 + L - 1) / L : 0u;
-	seg_nsel[g] = 0;
-}
-
-__global__ void __launch_bounds__(32) k_select_seq(SegTable seg, const uint16_t* __restrict__ codes, const uint32_t* __restrict__ seg_c2, const uint64_t* __restrict__ chunk_begin,
-	const uint4* __restrict__ tab_add, const uint4* __restrict__ tab_rem, uint32_t* __restrict__ selmask32, uint32_t* __restrict__ seg_nsel, uint32_t k, uint32_t w, uint32_t L)
-{
-	MBGFE_DYN_SMEM(smem_raw);
-	__shared__ uint4 add4[4], rem4[4];
-	const uint32_t lane = threadIdx.x & 31;
-	if (threadIdx.x < 4) add4[threadIdx.x] = __ldg(tab_add + threadIdx.x);
-	else if (threadIdx.x < 8) rem4[threadIdx.x - 4] = __ldg(tab_rem + threadIdx.x - 4);
-	__syncthreads();
-	uint64_t* __restrict__ ring = (uint64_t*)smem_raw + lane;                 // entry j of this lane's column: ring[32 * j]
-	uint8_t* __restrict__ flag = (uint8_t*)((uint64_t*)smem_raw + 32 * (size_t)w) + lane;
-	const uint64_t t_id = (uint64_t)blockIdx.x * 32 + lane;
-	if (t_id >= chunk_begin[seg.n]) return;
-	// the segment this chunk belongs to: the last one whose first chunk is not after t_id
-	uint32_t g;
-	{
-		uint32_t lo = 0, hi = seg.n;
-		while (hi - lo > 1) { const uint32_t mid = (lo + hi) >> 1; if (chunk_begin[mid] <= t_id) lo = mid; else hi = mid; }
-		g = lo;
-	}
-	const uint32_t n = seg_c2[g];
-	const uint32_t s = k - w + 1;
-	const uint32_t n_kmers = n - k + 1;
-	const uint32_t x0 = (uint32_t)(t_id - chunk_begin[g]) * L;
-	const uint32_t n_dec = min(L, n_kmers - x0), n_h = n_dec + w - 1;
-	const uint64_t out0 = seg.out_base[g];
-	const uint16_t* __restrict__ cp = codes + out0 + x0;
-	uint32_t* __restrict__ mask_out = selmask32 + ((out0 + x0) >> 5);
-	auto entry = [&](const uint4* small, const uint4* __restrict__ big, uint32_t code) -> uint4
-	{
-		uint4 v = small[code & 3];
-		if (code >= 4) v = __ldg(big + code);
-		return v;
-	};
-	// ---- the first s-mer of the chunk: s add steps
-	uint64_t fw = 0, bw = 0;
-	for (uint32_t i = 0; i < s; i++)
-	{
-		const uint4 a = entry(add4, tab_add, __ldg(cp + i));
-		fw = rotl_c(fw, 1) ^ u64_of(a.x, a.y);
-		bw = rotr_c(bw, 1) ^ u64_of(a.z, a.w);
-	}
-	uint64_t pm = 0;
-	uint32_t slot = 0, word = 0, count = 0;
-	for (uint32_t t = 0; t < n_h; t++)
-	{
-		if (t)
-		{
-			const uint4 a = entry(add4, tab_add, __ldg(cp + s + t - 1)), r = entry(rem4, tab_rem, __ldg(cp + t - 1));
-			fw = rotl_c(fw, 1) ^ u64_of(a.x, a.y) ^ u64_of(r.x, r.y);
-			bw = rotr_c(bw, 1) ^ u64_of(a.z, a.w) ^ u64_of(r.z, r.w);
-		}
-		const uint64_t hv = fw < bw ? fw : bw;
-		pm = (slot == 0 || hv < pm) ? hv : pm;
-		ring[32 * slot] = hv;
-		if (slot == w - 1)
-		{
-			// the block is complete: suffix minima in place, and which entries are not above anything after them
-			uint64_t run = hv;
-			flag[32 * (w - 1)] = 1;
-			for (uint32_t j = w - 1; j-- > 0; )
-			{
-				const uint64_t v = ring[32 * j];
-				const bool f = v <= run;
-				run = f ? v : run;
-				ring[32 * j] = run;
-				flag[32 * j] = f ? 1 : 0;
-			}
-		}
-		const uint32_t next = slot + 1 == w ? 0 : slot + 1;
-		if (t + 1 >= w)
-		{
-			const uint32_t p = t + 1 - w;                       // the k-mer whose window ends here
-			const uint64_t suf = ring[32 * next];
-			const bool lt = suf < pm, le = suf <= pm;
-			const bool sel = (flag[32 * next] && le) || (hv == pm && !lt);
-			word |= (sel ? 1u : 0u) << (p & 31);
-			if ((p & 31) == 31 || p + 1 == n_dec) { mask_out[p >> 5] = word; count += __popc(word); word = 0; }
-		}
-		slot = next;
-	}
-	if (count) atomicAdd(seg_nsel + g, count);
-}
-
 // --------------------------------------------------------------------------- K3b: positions and k-mer hashes
 
 // exclusive prefix sum of a small uint32 array into uint64 (one CTA; segment tables are small).  carry_in: the sum

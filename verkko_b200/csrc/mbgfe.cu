@@ -80,9 +80,6 @@ struct mbgfe
 	size_t max_smem = 0;
 	SelectPlan plan;
 	int select_nt = NT_SELECT_DEFAULT;                              // threads per CTA of k_select
-	bool select_seq = false;                          // K3a runs as k_select_seq (8 <= w <= 128)
-	uint32_t select_L = 2048;                         // k-mer positions per lane chunk of k_select_seq
-	DevBuf tab_add, tab_rem, d_sel_nch, d_sel_cbegin;
 
 	// code tables
 	DevBuf tab_hash, tab_pair, tab_comp;
@@ -295,8 +292,6 @@ int upload_segments(mbgfe* h)
 	if (int rc = ensure(h, h->d_seg_c2, (n + 1) * 4)) return rc;
 	if (int rc = ensure(h, h->d_seg_nsel, (n + 1) * 4)) return rc;
 	if (int rc = ensure(h, h->d_sel_begin, (n + 2) * 8)) return rc;
-	if (int rc = ensure(h, h->d_sel_nch, (n + 1) * 4)) return rc;
-	if (int rc = ensure(h, h->d_sel_cbegin, (2 * n + 4) * 8)) return rc;
 	if (n)
 	{
 		CU(h, cudaMemcpyAsync(h->d_seg_in.p, h->seg_in.data(), n * 8, cudaMemcpyHostToDevice, h->stream));
@@ -510,19 +505,6 @@ int mbgfe_create(const mbgfe_params* prm, mbgfe** out)
 		bool ok2 = false;
 		if (nt == 64 || nt == 256 || nt == 512) { SelectPlan p2 = make_plan(prm->k, prm->w, h->max_smem, ok2, (uint32_t)nt); if (ok2) { h->plan = p2; h->select_nt = nt; } }
 	}
-	// the lane-sequential K3a: window ring of w entries per lane in shared memory
-	{
-		const uint32_t s_mer = prm->k - prm->w + 1;
-		h->select_seq = prm->w >= 8 && prm->w <= 128 && !getenv("MBGFE_SELECT_TILED");
-		h->select_L = std::max<uint32_t>(2048, ((2 * s_mer + 63) / 64) * 64);
-		if (const char* e = getenv("MBGFE_SELECT_L")) if (atoi(e) >= 64) h->select_L = std::max<uint32_t>(((uint32_t)atoi(e) + 63) / 64 * 64, 64);
-		if (h->select_seq)
-		{
-			if (ensure(h, h->tab_add, MAX_CODE * 16) || ensure(h, h->tab_rem, MAX_CODE * 16)) return bail(MBGFE_E_CUDA);
-			MBGFE_LAUNCH(k_build_roll_tables, (MAX_CODE + 255) / 256, 256, 0, h->stream, h->tab_pair.as<uint4>(), s_mer, h->tab_add.as<uint4>(), h->tab_rem.as<uint4>());
-			cudaFuncSetAttribute(k_select_seq, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(prm->w * 288));
-		}
-	}
 	cudaFuncSetAttribute(k_select<NT_SELECT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->plan.smem_bytes);
 	cudaFuncSetAttribute(k_select<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->plan.smem_bytes);
 	cudaFuncSetAttribute(k_select<256>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->plan.smem_bytes);
@@ -543,7 +525,7 @@ void mbgfe_destroy(mbgfe* h)
 		&h->d_node_tip, &h->d_edges_sorted, &h->d_inst_packpos, &h->d_ids_out, &h->d_id_begin, &h->d_edge_records, &h->d_xbuf[0], &h->d_xbuf[1], &h->d_xbuf[2],
 		&h->d_xbuf[3], &h->d_var_hash, &h->d_var_offset, &h->d_var_len_begin, &h->d_var_len, &h->d_g_deg, &h->d_g_nb, &h->d_g_link, &h->d_g_st[0], &h->d_g_st[1],
 		&h->d_g_kept, &h->d_g_newid, &h->d_g_flag, &h->d_g_at, &h->d_g_flag2, &h->d_g_at2, &h->d_g_flag_byte, &h->d_f_hash, &h->d_f_cov, &h->d_f_tip, &h->d_f_edges, &h->d_f_orig, &h->d_t_hash, &h->d_t_cov, &h->d_t_tip, &h->d_t_edges, &h->d_t_orig, &h->d_g_kept8, &h->d_u_pos, &h->d_th_final, &h->d_th_node, &h->d_th_unitig, &h->d_th_upos, &h->d_th_urest, &h->d_th_step, &h->d_thin, &h->d_thin_pos,
-		&h->d_u_begin, &h->d_u_nodes, &h->d_u_of_node, &h->d_u_fw, &h->d_u_edges, &h->tab_add, &h->tab_rem, &h->d_sel_nch, &h->d_sel_cbegin, &h->d_append_base, &h->d_range, &h->d_xrow, &h->d_xmatrix, &h->d_rec_slot, &h->d_thin_scan, &h->d_tpos, &h->d_tu_nodes, &h->d_tu_off, &h->d_tu_unitig, &h->d_tu_begin, &h->d_t_newov }) release(*b);
+		&h->d_u_begin, &h->d_u_nodes, &h->d_u_of_node, &h->d_u_fw, &h->d_u_edges, &h->d_append_base, &h->d_range, &h->d_xrow, &h->d_xmatrix, &h->d_rec_slot, &h->d_thin_scan, &h->d_tpos, &h->d_tu_nodes, &h->d_tu_off, &h->d_tu_unitig, &h->d_tu_begin, &h->d_t_newov }) release(*b);
 	for (HostBuf* b : { &h->p_node_hashes, &h->p_node_cov, &h->p_node_tip, &h->p_edges, &h->p_stage }) release_host(*b);
 	for (auto& e : h->ev) if (e) cudaEventDestroy(e);
 	for (auto& e : h->piece_events) cudaEventDestroy(e);
@@ -766,20 +748,6 @@ uint32_t launch_front(mbgfe* h, uint32_t g0, uint32_t cnt, bool timed, cudaStrea
 		MBGFE_LAUNCH(k_unpack_symbols<NT_MSAT>, cnt, NT_MSAT, 0, on, st, h->d_sym.as<uint64_t>(), c1, h->d_codes.as<uint16_t>(),
 			c2, (const uint32_t*)pos1, pos2);
 	if (timed) tick(h, 5);
-	if (h->select_seq)
-	{
-		// chunks per segment -> scan -> one lane per chunk.  The grid is sized from what the host knows (raw lengths bound the number of
-		// k-mers); lanes beyond the real chunk count leave at once.
-		uint64_t ub = 0;
-		for (uint32_t g = g0; g < g0 + cnt; g++) ub += h->seg_len[g] / h->select_L + 1;
-		uint32_t* nch = h->d_sel_nch.as<uint32_t>() + g0;
-		uint64_t* cb = h->d_sel_cbegin.as<uint64_t>() + 2 * (size_t)g0;      // cnt + 1 entries; pieces on the two front streams must not share any
-		MBGFE_LAUNCH(k_select_chunks, (cnt + 255) / 256, 256, 0, on, c2, cnt, k, h->select_L, nch, h->d_seg_nsel.as<uint32_t>() + g0);
-		MBGFE_LAUNCH(k_scan_u32<1024>, 1, 1024, 0, on, nch, cb, cnt, (const uint64_t*)nullptr);
-		MBGFE_LAUNCH(k_select_seq, (unsigned)((ub + 31) / 32), 32, (size_t)w * 288, on, st, h->d_codes.as<uint16_t>(), c2, cb, h->tab_add.as<uint4>(), h->tab_rem.as<uint4>(),
-			h->d_selmask.as<uint32_t>(), h->d_seg_nsel.as<uint32_t>() + g0, k, w, h->select_L);
-		return 5;
-	}
 	if (h->select_nt == 64)
 		MBGFE_LAUNCH(k_select<64>, cnt, 64, h->plan.smem_bytes, on, st, h->d_codes.as<uint16_t>(), c2, h->tab_pair.as<uint4>(),
 			h->d_selmask.as<uint8_t>(), h->d_seg_nsel.as<uint32_t>() + g0, k, w, h->plan);
@@ -1347,8 +1315,6 @@ int run_files(mbgfe* h)
 		if (int rc = ensure(h, h->d_seg_c2, (n + 1) * 4)) return rc;
 		if (int rc = ensure(h, h->d_seg_nsel, (n + 1) * 4)) return rc;
 		if (int rc = ensure(h, h->d_sel_begin, (n + 2) * 8)) return rc;
-		if (int rc = ensure(h, h->d_sel_nch, (n + 1) * 4)) return rc;
-		if (int rc = ensure(h, h->d_sel_cbegin, (2 * n + 4) * 8)) return rc;
 	}
 	if (int rc = ensure(h, h->d_packed, n_image / 4 + 64)) return rc;
 	if (int rc = ensure(h, h->d_nonacgt, 8 << 20)) return rc;
