@@ -204,3 +204,17 @@ def test_emulated_host_packed_pieces(oracle, emu_library, monkeypatch, pct, mode
     reads += [workloads.lcg_bases(5, 9000).replace(b"ACGTA", b"ACNNA", 3), workloads.lcg_bases(6, 7000).lower(), workloads.lcg_bases(8, 4097)]
     got = run_frontend(mode, k, w, reads, library=emu_library, piece_bytes=3200)      # (0 %: every other emulator test)
     compare_runs(got, oracle.run(mode, k, w, reads), what=f"host pack {pct}% {mode}")
+
+
+@pytest.mark.parametrize("mode,k,w", [("hpc", 63, 33), ("no", 101, 20), ("dinuc", 63, 33), ("collapse", 31, 1)])
+def test_emulated_collapse_by_table_without_positions(oracle, emu_library, mode, k, w):
+    """k_collapse_lut (the K1 that runs when per-base positions are not wanted: flags = 0) in every run-length mode, ragged lengths
+    around the 4 096-base tile and the 128-base lane share"""
+    a = workloads.read_a()
+    reads = [a, a[:4096], a[:4097], a[:4095 + 128], a[:129], a[:127], a[:33], workloads.read_with_other_characters(), workloads.repeat_rich(7, 9000), b"A" * 5000 + a[:300]]
+    got = run_frontend(mode, k, w, reads, library=emu_library, flags=0)
+    want = oracle.run(mode, k, w, reads)
+    assert np.array_equal(got.positions, want.positions) and np.array_equal(got.hashes, want.hashes)
+    assert np.array_equal(got.node_hash, want.node_hash) and np.array_equal(got.node_cov, want.node_cov)
+    for f in ("read_idx", "part_offset", "raw_len", "n_codes", "n_sel"):
+        assert np.array_equal(got.parts[f], want.parts[f]), f

@@ -383,6 +383,139 @@ __global__ void __launch_bounds__(COLLAPSE_WARPS * 32) k_collapse(SegTable seg, 
 	}
 }
 
+// K1, byte-table form (the one that runs unless per-base positions are wanted; k_collapse above serves those runs).
+// ncu on k_collapse (r01): ALU pipe, ~290 instructions per 32 bases, of which the 5-round bit-compress of the two planes is ~110 and
+// the per-tile overheads (unaligned window, warp scan, staging, barriers) most of the rest -- 20 % of the HBM copy peak for a kernel
+// that moves 0.44 bytes per base.  Two changes: (1) compaction by table: PEXT8[mask][value] = the bits of `value` selected by `mask`,
+// gathered at the low end -- 64 KB, copied into shared memory once per CTA (CTAs are persistent: warps stride over the segments), two
+// byte lookups per 8 bases and plane; (2) a lane takes FOUR words (128 bases) per tile of 4 096, so the warp scan, the staging and
+// the synchronisation are paid once per 128 bases.  ~90 instructions per 32 bases.
+// dynamic shared memory = 65 536 + warps * 2 * COLLAPSE_STAGE * 4 bytes.
+#ifdef MBGFE_EMU_BUILD
+constexpr int COLLAPSE_LUT_WARPS = 1;      // the emulator's warp primitives are CTA-wide barriers
+#else
+constexpr int COLLAPSE_LUT_WARPS = 8;
+#endif
+constexpr uint32_t COLLAPSE_STAGE = 132;   // staging words per plane and warp: a tile's 128 output words + the carried word + spill
+
+__global__ void __launch_bounds__(256) k_build_pext8(uint8_t* __restrict__ lut)
+{
+	const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+	if (i >= 65536) return;
+	const uint32_t m = i >> 8, v = i & 0xff;
+	uint32_t out = 0, n = 0;
+	for (uint32_t b = 0; b < 8; b++) if ((m >> b) & 1) { out |= ((v >> b) & 1) << n; n++; }
+	lut[i] = (uint8_t)out;
+}
+
+// both planes of one word through the table: the kept bits of lo / hi gathered at the low end (popc(keep) of them)
+__device__ __forceinline__ void compress_planes_lut(const uint8_t* __restrict__ lut, uint32_t& lo, uint32_t& hi, uint32_t keep)
+{
+	uint32_t out_lo = 0, out_hi = 0, off = 0;
+#pragma unroll
+	for (int b = 0; b < 4; b++)
+	{
+		const uint32_t m = (keep >> (8 * b)) & 0xff;
+		const uint8_t* __restrict__ row = lut + (m << 8);
+		out_lo |= (uint32_t)row[(lo >> (8 * b)) & 0xff] << off;
+		out_hi |= (uint32_t)row[(hi >> (8 * b)) & 0xff] << off;
+		off += __popc(m);
+	}
+	lo = out_lo; hi = out_hi;
+}
+
+__global__ void __launch_bounds__(COLLAPSE_LUT_WARPS * 32) k_collapse_lut(SegTable seg, const uint64_t* __restrict__ packed, uint64_t* __restrict__ sym,
+	uint32_t* __restrict__ seg_c1, const uint8_t* __restrict__ pext8, int keep_all)
+{
+	MBGFE_DYN_SMEM(smem_raw);
+	uint8_t* lut = smem_raw;
+	const uint32_t lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+	uint32_t* st_lo = (uint32_t*)(smem_raw + 65536) + (size_t)wid * 2 * COLLAPSE_STAGE;
+	uint32_t* st_hi = st_lo + COLLAPSE_STAGE;
+	for (uint32_t i = threadIdx.x; i < 4096; i += blockDim.x) ((uint4*)lut)[i] = __ldg((const uint4*)pext8 + i);
+	__syncthreads();
+	for (uint32_t g = blockIdx.x * COLLAPSE_LUT_WARPS + wid; g < seg.n; g += gridDim.x * COLLAPSE_LUT_WARPS)
+	{
+		const uint64_t in0 = seg.in_start[g];
+		const uint32_t len = seg.len[g];
+		uint64_t* __restrict__ out = sym + (seg.out_base[g] >> 5);
+		const uint64_t* __restrict__ src = packed + (in0 >> 5);
+		const uint32_t sh = (uint32_t)(in0 & 31);
+		uint32_t carry = 0, part_lo = 0, part_hi = 0, prev_lo = 0, prev_hi = 0;
+		// the lane's 128 bases of a tile: five source words, realigned to four
+		uint64_t raw[5];
+		auto fetch = [&](uint32_t base0)
+		{
+#pragma unroll
+			for (int j = 0; j < 5; j++) raw[j] = 0;
+			if (base0 < len)
+			{
+				const uint64_t* q = src + (base0 >> 5);
+#pragma unroll
+				for (int j = 0; j < 5; j++) raw[j] = __ldg(q + j);      // the packed array is padded past the batch
+			}
+		};
+		fetch(lane * 128);
+		for (uint32_t tile = 0; tile < len; tile += 4096)
+		{
+			const uint32_t base0 = tile + lane * 128;
+			Planes wd[4];
+#pragma unroll
+			for (int j = 0; j < 4; j++) wd[j] = sh ? shift_in(planes_of(raw[j]), planes_of(raw[j + 1]), sh) : planes_of(raw[j]);
+			fetch(base0 + 4096);
+			const uint32_t nvalid = base0 < len ? min(128u, len - base0) : 0u;
+			uint32_t below_lo = __shfl_up_sync(FULL, wd[3].lo >> 31, 1), below_hi = __shfl_up_sync(FULL, wd[3].hi >> 31, 1);
+			if (lane == 0) { below_lo = prev_lo; below_hi = prev_hi; }
+			prev_lo = __shfl_sync(FULL, wd[3].lo >> 31, 31); prev_hi = __shfl_sync(FULL, wd[3].hi >> 31, 31);
+			uint32_t keep[4], cnt[4], lane_total = 0;
+#pragma unroll
+			for (int j = 0; j < 4; j++)
+			{
+				uint32_t kp = (wd[j].lo ^ ((wd[j].lo << 1) | below_lo)) | (wd[j].hi ^ ((wd[j].hi << 1) | below_hi));
+				if (base0 + 32 * j == 0) kp |= 1u;
+				if (keep_all) kp = 0xffffffffu;
+				kp &= low_bits(nvalid > 32u * j ? min(32u, nvalid - 32u * j) : 0u);
+				keep[j] = kp; cnt[j] = __popc(kp); lane_total += cnt[j];
+				below_lo = wd[j].lo >> 31; below_hi = wd[j].hi >> 31;
+			}
+			uint32_t inc = lane_total;
+#pragma unroll
+			for (int d = 1; d < 32; d <<= 1) { const uint32_t t = __shfl_up_sync(FULL, inc, d); if (lane >= (uint32_t)d) inc += t; }
+			const uint32_t tile_total = __shfl_sync(FULL, inc, 31);
+			// the staging strip holds symbols [carry & ~31, ...): word 0 is the unfinished word of the previous tile
+			for (uint32_t i = 1 + lane; i < COLLAPSE_STAGE; i += 32) { st_lo[i] = 0; st_hi[i] = 0; }
+			if (lane == 0) { st_lo[0] = part_lo; st_hi[0] = part_hi; }
+			__syncwarp();
+			uint32_t o = (carry & 31) + inc - lane_total;
+#pragma unroll
+			for (int j = 0; j < 4; j++)
+			{
+				if (cnt[j])
+				{
+					uint32_t lo = wd[j].lo, hi = wd[j].hi;
+					compress_planes_lut(lut, lo, hi, keep[j]);
+					const uint32_t bs = o & 31;
+					atomicOr(&st_lo[o >> 5], lo << bs);
+					atomicOr(&st_hi[o >> 5], hi << bs);
+					if (bs && cnt[j] + bs > 32) { atomicOr(&st_lo[(o >> 5) + 1], lo >> (32 - bs)); atomicOr(&st_hi[(o >> 5) + 1], hi >> (32 - bs)); }
+					o += cnt[j];
+				}
+			}
+			__syncwarp();
+			const uint32_t filled = (carry & 31) + tile_total;
+			const bool last = tile + 4096 >= len;
+			const uint32_t n_words = last ? (filled + 31) / 32 : filled / 32;
+			const uint32_t w0 = carry >> 5;
+			for (uint32_t i = lane; i < n_words; i += 32) out[w0 + i] = word_of(st_lo[i], st_hi[i]);
+			part_lo = (filled & 31) ? st_lo[filled >> 5] : 0u;
+			part_hi = (filled & 31) ? st_hi[filled >> 5] : 0u;
+			carry += tile_total;
+			__syncwarp();
+		}
+		if (lane == 0) seg_c1[g] = carry;
+	}
+}
+
 // ------------------------------------------------------------------------------- K2: microsatellite coding
 
 // 1 bit per position p of word a where sym[p] == sym[p+m]; b = the 32 symbols that follow a

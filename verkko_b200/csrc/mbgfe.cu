@@ -82,7 +82,7 @@ struct mbgfe
 	int select_nt = NT_SELECT_DEFAULT;                              // threads per CTA of k_select
 
 	// code tables
-	DevBuf tab_hash, tab_pair, tab_comp;
+	DevBuf tab_hash, tab_pair, tab_comp, tab_pext8;
 
 	// pending input
 	std::vector<HostChunk> pending;
@@ -498,6 +498,9 @@ int mbgfe_create(const mbgfe_params* prm, mbgfe** out)
 	if (ensure(h, h->tab_hash, MAX_CODE * 8) || ensure(h, h->tab_pair, MAX_CODE * 16) || ensure(h, h->tab_comp, MAX_CODE * 2) ||
 		ensure(h, h->d_counters, (CTR_OWNER + prm->world + 8) * 8)) return bail(MBGFE_E_CUDA);
 	MBGFE_LAUNCH(k_build_tables, (MAX_CODE + 255) / 256, 256, 0, h->stream, h->tab_hash.as<uint64_t>(), h->tab_pair.as<uint4>(), h->tab_comp.as<uint16_t>());
+	if (ensure(h, h->tab_pext8, 65536)) return bail(MBGFE_E_CUDA);
+	MBGFE_LAUNCH(k_build_pext8, 256, 256, 0, h->stream, h->tab_pext8.as<uint8_t>());
+	cudaFuncSetAttribute(k_collapse_lut, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(65536 + COLLAPSE_LUT_WARPS * 2 * COLLAPSE_STAGE * 4));
 	if (const char* e = getenv("MBGFE_SELECT_NT"))
 	{
 		// experiment knob: threads per CTA of k_select (64 / 256 / 512 instead of 128); the tile is 8 codes per thread
@@ -518,7 +521,7 @@ int mbgfe_create(const mbgfe_params* prm, mbgfe** out)
 void mbgfe_destroy(mbgfe* h)
 {
 	if (!h) return;
-	for (DevBuf* b : { &h->tab_hash, &h->tab_pair, &h->tab_comp, &h->d_ascii, &h->d_packed, &h->d_nonacgt, &h->d_counters, &h->d_seg_in, &h->d_seg_out,
+	for (DevBuf* b : { &h->tab_hash, &h->tab_pair, &h->tab_comp, &h->tab_pext8, &h->d_ascii, &h->d_packed, &h->d_nonacgt, &h->d_counters, &h->d_seg_in, &h->d_seg_out,
 		&h->d_seg_len, &h->d_seg_c1, &h->d_seg_c2, &h->d_seg_nsel, &h->d_sel_begin, &h->d_sym, &h->d_codes, &h->d_selmask, &h->d_pos1, &h->d_pos2,
 		&h->d_inst_pos, &h->d_inst_seg, &h->d_inst_flag, &h->d_inst_hash, &h->d_inst_slot, &h->d_pal_list, &h->d_nodes, &h->d_edges, &h->d_node_out,
 		&h->d_edge_out, &h->d_records, &h->d_recv, &h->d_bucket_count, &h->d_bucket_begin, &h->d_scan_tot, &h->d_scan_off, &h->d_node_hash_sorted, &h->d_node_cov,
@@ -738,8 +741,19 @@ uint32_t launch_front(mbgfe* h, uint32_t g0, uint32_t cnt, bool timed, cudaStrea
 	uint32_t* pos2 = want_poses ? h->d_pos2.as<uint32_t>() : nullptr;
 	uint32_t* c1 = h->d_seg_c1.as<uint32_t>() + g0;
 	uint32_t* c2 = h->d_seg_c2.as<uint32_t>() + g0;
-	MBGFE_LAUNCH(k_collapse, (cnt + COLLAPSE_WARPS - 1) / COLLAPSE_WARPS, COLLAPSE_WARPS * 32, 0, on, st, h->d_packed.as<uint64_t>(), h->d_sym.as<uint64_t>(), c1, pos1,
-		h->prm.error_masking == MBGFE_MASK_NO ? 1 : 0);
+	if (!pos1 && !getenv("MBGFE_COLLAPSE_BITWISE"))
+	{
+#ifdef MBGFE_EMU_BUILD
+		const unsigned grid1 = cnt;
+#else
+		const unsigned grid1 = std::min<unsigned>((cnt + COLLAPSE_LUT_WARPS - 1) / COLLAPSE_LUT_WARPS, (unsigned)h->sm_count * 3);      // persistent: 3 CTAs of 72 KB per SM
+#endif
+		MBGFE_LAUNCH(k_collapse_lut, grid1, COLLAPSE_LUT_WARPS * 32, 65536 + COLLAPSE_LUT_WARPS * 2 * COLLAPSE_STAGE * 4, on, st, h->d_packed.as<uint64_t>(), h->d_sym.as<uint64_t>(), c1,
+			h->tab_pext8.as<uint8_t>(), h->prm.error_masking == MBGFE_MASK_NO ? 1 : 0);
+	}
+	else
+		MBGFE_LAUNCH(k_collapse, (cnt + COLLAPSE_WARPS - 1) / COLLAPSE_WARPS, COLLAPSE_WARPS * 32, 0, on, st, h->d_packed.as<uint64_t>(), h->d_sym.as<uint64_t>(), c1, pos1,
+			h->prm.error_masking == MBGFE_MASK_NO ? 1 : 0);
 	if (timed) tick(h, 4);
 	if (h->msat)
 		MBGFE_LAUNCH(k_msat, (cnt + MSAT_WARPS - 1) / MSAT_WARPS, MSAT_WARPS * 32, 0, on, st, h->d_sym.as<uint64_t>(), c1, h->d_codes.as<uint16_t>(),
