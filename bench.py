@@ -584,6 +584,37 @@ def main():
             fe.reset()
             fe.add_reads(bases, offsets)          # back to the full in-memory batch for the stages below (untimed)
             fe.run()
+    # ---- pass 3 of runMBG: the same reads with hpc variants registered (row a11); the re-hash runs per piece inside the
+    # pipelined run, so the leg costs one more small kernel per piece and the run-length positions K1 has to write
+    e2e_variants = None
+    if world == 1 and not args.no_file:
+        nh = fe.node_hashes(copy=True)
+        pick = nh[:: max(1, len(nh) // 6600)]
+        k_ = wl["k"]
+        v_hash = np.repeat(pick, 3, axis=0)
+        v_off = np.tile(np.array([k_ // 4, k_ // 2, (3 * k_) // 4], dtype=np.uint32), len(pick))
+        v_len = np.tile(np.array([2, 4, 1000], dtype=np.uint32), len(v_off))
+        v_begin = np.arange(len(v_off) + 1, dtype=np.uint64) * 3
+        ms_var = []
+        for it in range(1 + args.e2e_steps):
+            barrier()
+            t0 = time.time()
+            fe.reset()
+            fe.add_reads(bases, offsets)
+            fe.set_variants(v_hash, v_off, v_begin, v_len)
+            fe.run()
+            cov = fe.node_coverage(copy=False)
+            hashes = fe.node_hashes(copy=False)
+            edges = fe.edges(copy=False)
+            _ = int(cov[::1024].sum(dtype=np.uint64)) + len(hashes) + len(edges)
+            barrier()
+            if it > 0:
+                ms_var.append((time.time() - t0) * 1e3)
+        e2e_variants = {"value": n_bases / (float(np.mean(ms_var)) * 1e-3), "unit": "bases/s", "ms_per_step": float(np.mean(ms_var)), "variant_entries": int(len(v_off)),
+                        "vs_pass1": float(np.mean(ms_var)) / float(np.mean(e2e_ms))}
+        fe.reset()
+        fe.add_reads(bases, offsets)          # back to the plain batch for the stages below (untimed)
+        fe.run()
     # ---- the step after the table (rows a14 / f1), outside the timed regions: abundance filter + unitig chains on the device
     unitig_info = None
     if world == 1 and not sharded:
@@ -656,6 +687,8 @@ def main():
         }
         if e2e_file:
             line["e2e_file"] = e2e_file
+        if e2e_variants:
+            line["e2e_pass3_variants"] = e2e_variants
         if unitig_info:
             line["unitig_stage"] = unitig_info
         traffic_file = os.path.join(ROOT, "profiles", "ncu_traffic.json")

@@ -70,6 +70,32 @@ def test_emulated_hpc_variant_rehash(oracle, emu_library, mode, k, w, flags):
         assert np.array_equal(got.hashes, want.hashes) and np.array_equal(got.node_hash, want.node_hash) and np.array_equal(got.node_cov, want.node_cov)
 
 
+def test_emulated_hpc_variants_keep_the_pipelined_run(oracle, emu_library, tmp_path):
+    """pass 3 of runMBG (reads + registered hpc variants) goes through mbgfe_run's pipelined upload, from memory and from a
+    FASTA file: the re-hash runs per piece between K3b and the table inserts"""
+    from oracle_lib import make_variants, write_fasta
+    from verkko_b200.frontend import MbgFrontEnd
+    mode, k, w = "collapse-msat", 301, 30
+    reads = workloads.coverage_reads(n_reads=12)
+    variants = make_variants(oracle.run(mode, k, w, reads), k, 150)
+    want = oracle.run(mode, k, w, reads, variants=variants)
+    got = run_frontend(mode, k, w, reads, library=emu_library, variants=variants)
+    compare_runs(got, want, what="emu variants, pipelined from memory")
+    fa = str(tmp_path / "reads.fa")
+    bases, offsets = workloads.as_pair(reads)
+    write_fasta(fa, bases, offsets)
+    fe = MbgFrontEnd(k, w, mode, library=emu_library)
+    try:
+        fe.add_file(fa)
+        fe.set_variants(variants.hashes, variants.offsets, variants.len_begin, variants.lengths)
+        fe.run()
+        assert np.array_equal(fe.node_hashes(), want.node_hash) and np.array_equal(fe.node_coverage(), want.node_cov)
+        assert np.array_equal(fe.edges(), want.edges)
+        assert fe.stats()["h2d_bytes"] < len(bases) // 3, "the file route ships 2-bit reads"
+    finally:
+        fe.close()
+
+
 def check_unitigs(got, want, what):
     from oracle_lib import compare_unitigs
     assert np.array_equal(got.kept, want.kept), f"{what}: kept flags differ"

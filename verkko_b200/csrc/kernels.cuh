@@ -1444,9 +1444,12 @@ __device__ __forceinline__ uint64_t variant_fold(uint64_t h, uint64_t x) { h ^= 
 // XOR the hash of the clustered run lengths at the recorded offsets into the two halves (MBG/ReadHelper.h:684-730).
 // pos2 = per-code positions (poses) of every segment slot; only differences of neighbours are used.
 __global__ void __launch_bounds__(256) k_apply_variants(uint64_t* __restrict__ inst_hash, const uint32_t* __restrict__ inst_pos, const uint32_t* __restrict__ inst_seg,
-	uint64_t n_inst, const uint64_t* __restrict__ seg_out_base, const uint32_t* __restrict__ pos2, VariantTable vt, uint32_t k)
+	const uint64_t* __restrict__ range_begin, const uint64_t* __restrict__ range_end, uint64_t inst_cap, const uint64_t* __restrict__ seg_out_base,
+	const uint32_t* __restrict__ pos2, VariantTable vt, uint32_t k)
 {
-	for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n_inst; i += (uint64_t)gridDim.x * blockDim.x)
+	// the instance range is read from device memory (entries of sel_begin), like the other kernels after selection
+	const uint64_t i0 = *range_begin, i1 = min(*range_end, inst_cap);
+	for (uint64_t i = i0 + (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < i1; i += (uint64_t)gridDim.x * blockDim.x)
 	{
 		const uint64_t lo = inst_hash[2 * i], hi = inst_hash[2 * i + 1];
 		const uint32_t* __restrict__ poses = pos2 + seg_out_base[inst_seg[i]] + inst_pos[i];

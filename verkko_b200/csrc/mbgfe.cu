@@ -858,6 +858,22 @@ void launch_list_hash(mbgfe* h, uint32_t g0, uint32_t g1, uint64_t n_hint, uint3
 	launches += 3;
 }
 
+// Pass 3 of runMBG: hashes of k-mers with registered hpc variants are perturbed after the palindrome rule
+// (MBG/ReadHelper.h:672-737) and before anything is counted.  Runs per piece between K3b and K4, so pass 3 keeps the
+// pipelined upload; a palindrome in the batch sends the run through process_tail, which re-hashes and re-applies.
+void launch_variants(mbgfe* h, uint32_t g0, uint32_t g1, uint64_t n_hint, uint32_t& launches)
+{
+	if (!h->n_var || g1 == g0) return;
+	VariantTable vt;
+	vt.hash = h->d_var_hash.as<uint64_t>(); vt.offset = h->d_var_offset.as<uint32_t>();
+	vt.len_begin = h->d_var_len_begin.as<uint64_t>(); vt.len = h->d_var_len.as<uint32_t>(); vt.n = h->n_var;
+	const uint64_t* sb = h->d_sel_begin.as<uint64_t>();
+	const unsigned grid = n_hint ? (unsigned)std::min<uint64_t>((n_hint + 255) / 256, (uint64_t)h->sm_count * 16) : (unsigned)h->sm_count * 8;
+	MBGFE_LAUNCH(k_apply_variants, grid, 256, 0, h->stream, h->d_inst_hash.as<uint64_t>(), h->d_inst_pos.as<uint32_t>(), h->d_inst_seg.as<uint32_t>(), sb + g0, sb + g1, h->inst_cap,
+		h->d_seg_out.as<uint64_t>(), h->d_pos2.as<uint32_t>(), vt, h->prm.k);
+	launches++;
+}
+
 // K4a + K4b for the instances of segments [g0, g1)
 void launch_tables(mbgfe* h, uint32_t g0, uint32_t g1, uint64_t n_hint, uint32_t& launches, bool timed)
 {
@@ -941,17 +957,7 @@ int process_tail(mbgfe* h, uint32_t launches)
 		launches++;
 	}
 	h->stats.distinct = 0; h->stats.distinct_edges = 0;
-	if (h->n_var && n_inst)
-	{
-		// pass 3 of runMBG: hashes of k-mers with registered hpc variants are perturbed after the palindrome rule
-		// (MBG/ReadHelper.h:672-737) and before anything is counted
-		VariantTable vt;
-		vt.hash = h->d_var_hash.as<uint64_t>(); vt.offset = h->d_var_offset.as<uint32_t>();
-		vt.len_begin = h->d_var_len_begin.as<uint64_t>(); vt.len = h->d_var_len.as<uint32_t>(); vt.n = h->n_var;
-		MBGFE_LAUNCH(k_apply_variants, (unsigned)std::min<uint64_t>((n_inst + 255) / 256, (uint64_t)h->sm_count * 16), 256, 0, h->stream, h->d_inst_hash.as<uint64_t>(),
-			h->d_inst_pos.as<uint32_t>(), h->d_inst_seg.as<uint32_t>(), n_inst, h->d_seg_out.as<uint64_t>(), h->d_pos2.as<uint32_t>(), vt, k);
-		launches++;
-	}
+	if (n_inst) launch_variants(h, 0, n_seg, n_inst, launches);
 	if (!(h->prm.flags & MBGFE_NO_TABLE) && !h->appending)
 	{
 		const uint64_t slots = std::max<uint64_t>(next_pow2(std::max<uint64_t>(2 * n_inst, 1024)), h->prm.table_slots ? next_pow2(h->prm.table_slots) : 0);
@@ -986,12 +992,6 @@ extern "C" {
 int mbgfe_run(mbgfe* h)
 {
 	if (!h) return MBGFE_E_PARAM;
-	if (h->n_var)
-	{
-		// the variant re-hash sits between hashing and counting: take the unpipelined path
-		if (int rc = mbgfe_upload(h)) return rc;
-		return mbgfe_process(h);
-	}
 	if (!h->files.empty())
 	{
 		const int rc = run_files(h);
@@ -1180,6 +1180,7 @@ int mbgfe_run(mbgfe* h)
 			sized = true;
 		}
 		launch_list_hash(h, g_tail, g_end, 0, launches);
+		launch_variants(h, g_tail, g_end, 0, launches);      // pass 3 keeps the pipelined upload
 		launch_tables(h, g_tail, g_end, 0, launches, false);
 		g_tail = g_end;
 	}
@@ -1467,6 +1468,7 @@ int run_files(mbgfe* h)
 			sized = true;
 		}
 		launch_list_hash(h, g_tail, g_end, 0, launches);
+		launch_variants(h, g_tail, g_end, 0, launches);      // pass 3 keeps the pipelined upload
 		launch_tables(h, g_tail, g_end, 0, launches, false);
 		g_tail = g_end;
 	}
