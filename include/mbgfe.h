@@ -287,6 +287,16 @@ int mbgfe_exchange_group(mbgfe** handles, uint32_t n);              /* handles[r
 int mbgfe_kat_tables(mbgfe* h, uint64_t* char_hash_30948, uint16_t* complement_30948);
 int mbgfe_kat_kmer_hash(mbgfe* h, const uint16_t* codes, uint32_t k, mbgfe_hash128* out);
 
+/* mbgfe_kat_kmer_hash without any allocation.  No counterpart in the reference: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).
+ * Same inputs, same result.  Its device scratch (the code slot, the one-instance tables and the result) is a static
+ * __device__ array of about 2 * MBGFE_NOALLOC_MAX_K + 512 bytes that every GPU loading the library holds until exit; the
+ * call makes no cudaMalloc / cudaFree / allocating library call.  k > MBGFE_NOALLOC_MAX_K is rejected with MBGFE_E_LIMIT.
+ * Every call on a device shares that one array: calls that overlap on the GPU (two handles on one device, two threads) race;
+ * serialise them.  The call clears what it needs zeroed, so results do not depend on the previous call. */
+#define MBGFE_NOALLOC_MAX_K 16384u
+int mbgfe_kat_kmer_hash_noalloc(mbgfe* h, const uint16_t* codes, uint32_t k, mbgfe_hash128* out);
+
 #ifdef __cplusplus
 }
 #endif

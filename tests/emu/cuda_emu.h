@@ -31,7 +31,7 @@
 #define __launch_bounds__(...)
 #define __shared__ static
 #define __constant__ static const
-#define __align__(n) alignas(n)
+#define __align__(n) __attribute__((aligned(n)))
 
 struct uint3 { unsigned x, y, z; };
 struct uint4 { unsigned x, y, z, w; };
@@ -152,6 +152,7 @@ inline const char* cudaGetErrorString(cudaError_t) { return "emulator"; }
 inline cudaError_t cudaGetLastError() { return 0; }
 inline cudaError_t cudaGetDeviceCount(int* n) { *n = 1; return 0; }
 inline cudaError_t cudaSetDevice(int) { return 0; }
+template <class T> inline cudaError_t cudaGetSymbolAddress(void** p, const T& symbol) { *p = (void*)&symbol; return 0; }
 inline cudaError_t cudaGetDeviceProperties(cudaDeviceProp* p, int) { memset(p, 0, sizeof(*p)); strcpy(p->name, "emulated"); p->major = 10; p->minor = 0; p->multiProcessorCount = 4; p->sharedMemPerBlockOptin = 227 * 1024; return 0; }
 inline cudaError_t cudaStreamCreate(cudaStream_t* s) { *s = nullptr; return 0; }
 inline cudaError_t cudaStreamDestroy(cudaStream_t) { return 0; }

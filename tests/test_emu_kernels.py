@@ -70,6 +70,22 @@ def test_emulated_hpc_variant_rehash(oracle, emu_library, mode, k, w, flags):
         assert np.array_equal(got.hashes, want.hashes) and np.array_equal(got.node_hash, want.node_hash) and np.array_equal(got.node_cov, want.node_cov)
 
 
+def test_emulated_noalloc_kmer_hash(oracle, emu_library):
+    """mbgfe_kat_kmer_hash_noalloc on the emulator build: host logic (limit, clearing of the shared scratch between calls);
+    the GPU version is tests/test_zz_no_alloc.py"""
+    from verkko_b200.frontend import MbgFrontEnd, MbgfeError
+    fe = MbgFrontEnd(1001, 100, library=emu_library)
+    try:
+        rng = np.random.default_rng(2)
+        for k in (2001, 31, 16384, 33):
+            codes = rng.integers(0, 30948, k).astype(np.uint16)
+            assert fe.kat_kmer_hash_noalloc(codes) == fe.kat_kmer_hash(codes) == oracle.kmer_hash(codes), k
+        with pytest.raises(MbgfeError, match="MBGFE_NOALLOC_MAX_K"):
+            fe.kat_kmer_hash_noalloc(np.zeros(16385, dtype=np.uint16))
+    finally:
+        fe.close()
+
+
 def test_emulated_hpc_variants_keep_the_pipelined_run(oracle, emu_library, tmp_path):
     """pass 3 of runMBG (reads + registered hpc variants) goes through mbgfe_run's pipelined upload, from memory and from a
     FASTA file: the re-hash runs per piece between K3b and the table inserts"""

@@ -11,6 +11,7 @@
 #include <cstring>
 #include <fcntl.h>
 #include <functional>
+#include <mutex>
 #include <string>
 #include <sys/stat.h>
 #include <unistd.h>
@@ -2808,6 +2809,63 @@ int mbgfe_kat_kmer_hash(mbgfe* h, const uint16_t* codes, uint32_t k, mbgfe_hash1
 	cudaError_t e = cudaMemcpy(res, d_misc.as<char>() + 32, 16, cudaMemcpyDeviceToHost);
 	release(d_codes); release(d_misc);
 	if (e != cudaSuccess) return fail(h, MBGFE_E_CUDA, "kat kernel failed: %s", cudaGetErrorString(e));
+	out->lo = res[0]; out->hi = res[1];
+	return 0;
+}
+
+// ---- mbgfe_kat_kmer_hash_noalloc: the same k-mer hash with no allocation of any kind (no counterpart in the reference;
+// added for callers that cannot call cudaMalloc: CUDA graph capture, tight serving
+// loops, harnesses that forbid it).  The staging that mbgfe_kat_kmer_hash allocates per call -- the code slot, the
+// one-segment table, the instance and the result -- lives in this file-scope array instead: NOALLOC_SCRATCH_BYTES on every
+// GPU that loads the library, until the process exits.  In host code `noalloc_scratch` is only a stand-in for the symbol:
+// the device address comes from cudaGetSymbolAddress, asked once per device with that device current.
+constexpr uint32_t NOALLOC_MISC_BYTES = 256;              // seg_out_base[2] @0, inst_pos @16, result @32, instance range @64
+constexpr size_t NOALLOC_SCRATCH_BYTES = NOALLOC_MISC_BYTES + (((size_t)MBGFE_NOALLOC_MAX_K + 1 + 63) & ~(size_t)63) * 2;
+static __device__ __align__(256) unsigned char noalloc_scratch[NOALLOC_SCRATCH_BYTES];
+
+constexpr int NOALLOC_MAX_DEVICES = 64;
+static std::mutex noalloc_lock;
+static unsigned char* noalloc_address[NOALLOC_MAX_DEVICES];      // per device, filled on first use
+
+int mbgfe_kat_kmer_hash_noalloc(mbgfe* h, const uint16_t* codes, uint32_t k, mbgfe_hash128* out)
+{
+	if (!h || !codes || !out) return MBGFE_E_PARAM;
+	if (k == 0) return fail(h, MBGFE_E_PARAM, "k must be positive");
+	if (k > MBGFE_NOALLOC_MAX_K) return fail(h, MBGFE_E_LIMIT, "mbgfe_kat_kmer_hash_noalloc: k = %u exceeds MBGFE_NOALLOC_MAX_K = %u (the static scratch holds no more); use mbgfe_kat_kmer_hash",
+		k, (unsigned)MBGFE_NOALLOC_MAX_K);
+	const int dev = h->prm.device;
+	if (dev < 0 || dev >= NOALLOC_MAX_DEVICES) return fail(h, MBGFE_E_LIMIT, "mbgfe_kat_kmer_hash_noalloc: device %d outside 0..%d", dev, NOALLOC_MAX_DEVICES - 1);
+	CU(h, cudaSetDevice(dev));
+	unsigned char* scratch = nullptr;
+	{
+		std::lock_guard<std::mutex> guard(noalloc_lock);
+		if (!noalloc_address[dev])
+		{
+			void* p_ = nullptr;
+			const cudaError_t e = cudaGetSymbolAddress((void**)&p_, noalloc_scratch);
+			if (e != cudaSuccess || !p_) return fail(h, MBGFE_E_CUDA, "cudaGetSymbolAddress(noalloc_scratch) on device %d: %s", dev, cudaGetErrorString(e));
+			noalloc_address[dev] = (unsigned char*)p_;
+		}
+		scratch = noalloc_address[dev];
+	}
+	// the same synthetic instance as above: one segment whose slot holds the k codes, position 0.  The array keeps what the
+	// last call left, and K3b reads whole aligned 16-byte words of the slot: clear the slot (and the result) first.
+	const size_t slot_codes = ((size_t)k + 1 + 63) & ~(size_t)63;
+	uint16_t* d_codes = (uint16_t*)(scratch + NOALLOC_MISC_BYTES);
+	const uint64_t bases[2] = { 0, slot_codes };
+	const uint32_t zero32 = 0;
+	const uint64_t range[2] = { 0, 1 };
+	CU(h, cudaMemsetAsync(scratch, 0, NOALLOC_MISC_BYTES + slot_codes * 2, h->stream));
+	CU(h, cudaMemcpyAsync(d_codes, codes, (size_t)k * 2, cudaMemcpyHostToDevice, h->stream));
+	CU(h, cudaMemcpyAsync(scratch + 0, bases, 16, cudaMemcpyHostToDevice, h->stream));    // seg_out_base[0..1]
+	CU(h, cudaMemcpyAsync(scratch + 16, &zero32, 4, cudaMemcpyHostToDevice, h->stream));  // inst_pos[0]
+	CU(h, cudaMemcpyAsync(scratch + 64, range, 16, cudaMemcpyHostToDevice, h->stream));   // instance range [0, 1)
+	MBGFE_LAUNCH(k_kmer_hash, 1, HASH_NT, 0, h->stream, (const uint64_t*)scratch, (const uint16_t*)d_codes, h->tab_comp.as<uint16_t>(), (const uint32_t*)(scratch + 16),
+		(const uint64_t*)(scratch + 64), (uint64_t)1, (uint64_t*)(scratch + 32), k);
+	CU(h, cudaGetLastError());
+	uint64_t res[2] = { 0, 0 };
+	CU(h, cudaMemcpyAsync(res, scratch + 32, 16, cudaMemcpyDeviceToHost, h->stream));
+	CU(h, cudaStreamSynchronize(h->stream));
 	out->lo = res[0]; out->hi = res[1];
 	return 0;
 }

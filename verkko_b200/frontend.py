@@ -95,6 +95,7 @@ def load_library(path=None):
     L.mbgfe_set_variants.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint64]
     L.mbgfe_kat_tables.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
     L.mbgfe_kat_kmer_hash.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p]
+    L.mbgfe_kat_kmer_hash_noalloc.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p]
     if path == library_path():
         _lib = L
     return L
@@ -389,4 +390,11 @@ class MbgFrontEnd:
         codes = np.ascontiguousarray(codes, dtype=np.uint16)
         out = np.zeros(2, dtype=np.uint64)
         self._check(self.lib.mbgfe_kat_kmer_hash(self.handle, codes.ctypes.data, len(codes), out.ctypes.data))
+        return int(out[0]), int(out[1])
+
+    def kat_kmer_hash_noalloc(self, codes):
+        """the same through mbgfe_kat_kmer_hash_noalloc: static device scratch, no allocation; len(codes) <= NOALLOC_MAX_K"""
+        codes = np.ascontiguousarray(codes, dtype=np.uint16)
+        out = np.zeros(2, dtype=np.uint64)
+        self._check(self.lib.mbgfe_kat_kmer_hash_noalloc(self.handle, codes.ctypes.data, len(codes), out.ctypes.data))
         return int(out[0]), int(out[1])
