@@ -22,6 +22,8 @@ def main():
     ap.add_argument("--mode", default="collapse-msat")
     ap.add_argument("--k", type=int, default=0)
     ap.add_argument("--w", type=int, default=0)
+    ap.add_argument("--library", default=None, help="an experimental build of libmbgfe.so (tools/build_variant.sh)")
+    ap.add_argument("--digest", action="store_true", help="also print an order-free digest of the finished table (to compare builds)")
     args = ap.parse_args()
     wl = dict(bench.WORKLOADS[args.workload])
     if args.k:
@@ -29,7 +31,7 @@ def main():
     if args.w:
         wl["w"] = args.w
     from verkko_b200 import MbgFrontEnd
-    fe = MbgFrontEnd(wl["k"], wl["w"], args.mode)
+    fe = MbgFrontEnd(wl["k"], wl["w"], args.mode, library=args.library)
     bases, offsets, pinned = bench.make_reads(wl, 1, 0, args.scale, pinned_alloc=fe.pinned)
     fe.add_reads(bases, offsets)
     fe.upload()
@@ -39,6 +41,11 @@ def main():
     fe.parts()
     st2 = fe.stats()
     st.update({k: st2[k] for k in ("collapsed_symbols", "codes", "parts", "hashed_parts")})
+    if args.digest:
+        import numpy as np
+        nh, cov, ed = fe.node_hashes(), fe.node_coverage(), fe.edges()
+        st["digest"] = {"nodes": int(len(nh)), "hash_xor": int(np.bitwise_xor.reduce(nh.reshape(-1))), "cov_sum": int(cov.sum(dtype=np.uint64)),
+                        "edges": int(len(ed)), "edge_sum": int(ed.astype(np.uint64).sum(dtype=np.uint64))}
     print(json.dumps(st))
 
 

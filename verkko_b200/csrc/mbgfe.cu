@@ -841,6 +841,13 @@ void launch_scan(mbgfe* h, uint32_t g0, uint32_t g1, uint32_t& launches)
 	launches++;
 }
 
+// K3b2, one CTA per segment (also behind the two known-answer entry points)
+void launch_kmer_hash(cudaStream_t stream, uint32_t n_seg, const uint64_t* seg_out_base, const uint16_t* codes, const uint16_t* tab_comp, const uint32_t* inst_pos,
+	const uint64_t* sel_begin, uint64_t inst_cap, uint64_t* inst_hash, uint32_t k)
+{
+	MBGFE_LAUNCH(k_kmer_hash, n_seg, HASH_NT, 0, stream, seg_out_base, codes, tab_comp, inst_pos, sel_begin, inst_cap, inst_hash, k);
+}
+
 // K3b for the instances of segments [g0, g1).  n_hint: instance count when the host knows it (exact grids), else 0.
 void launch_list_hash(mbgfe* h, uint32_t g0, uint32_t g1, uint64_t n_hint, uint32_t& launches)
 {
@@ -852,7 +859,7 @@ void launch_list_hash(mbgfe* h, uint32_t g0, uint32_t g1, uint64_t n_hint, uint3
 	const uint64_t* sb = h->d_sel_begin.as<uint64_t>();
 	MBGFE_LAUNCH(k_list_selected<NT_LIST>, g1 - g0, NT_LIST, 0, h->stream, st, g0, h->d_selmask.as<uint32_t>(), h->d_seg_c2.as<uint32_t>() + g0, h->d_seg_nsel.as<uint32_t>() + g0,
 		sb + g0, h->d_inst_pos.as<uint32_t>(), h->d_inst_seg.as<uint32_t>(), h->d_inst_flag.as<uint8_t>(), k, h->inst_cap, ctr + CTR_OVERFLOW);
-	MBGFE_LAUNCH(k_kmer_hash, g1 - g0, HASH_NT, 0, h->stream, h->d_seg_out.as<uint64_t>() + g0, h->d_codes.as<uint16_t>(), h->tab_comp.as<uint16_t>(), h->d_inst_pos.as<uint32_t>(),
+	launch_kmer_hash(h->stream, g1 - g0, h->d_seg_out.as<uint64_t>() + g0, h->d_codes.as<uint16_t>(), h->tab_comp.as<uint16_t>(), h->d_inst_pos.as<uint32_t>(),
 		sb + g0, h->inst_cap, h->d_inst_hash.as<uint64_t>(), k);
 	const unsigned pal_grid = n_hint ? (unsigned)((n_hint + 255) / 256) : (unsigned)h->sm_count * 4;
 	MBGFE_LAUNCH(k_find_palindromes, pal_grid, 256, 0, h->stream, h->d_inst_hash.as<uint64_t>(), sb + g0, sb + g1, h->inst_cap, ctr + CTR_PALINDROME, h->d_pal_list.as<uint64_t>(), PAL_CAP);
@@ -2802,7 +2809,7 @@ int mbgfe_kat_kmer_hash(mbgfe* h, const uint16_t* codes, uint32_t k, mbgfe_hash1
 	cudaMemcpyAsync(d_misc.as<char>() + 16, &zero32, 4, cudaMemcpyHostToDevice, h->stream);  // inst_pos[0]
 	const uint64_t range[2] = { 0, 1 };
 	cudaMemcpyAsync(d_misc.as<char>() + 64, range, 16, cudaMemcpyHostToDevice, h->stream);   // instance range [0, 1)
-	MBGFE_LAUNCH(k_kmer_hash, 1, HASH_NT, 0, h->stream, (const uint64_t*)d_misc.p, d_codes.as<uint16_t>(), h->tab_comp.as<uint16_t>(), (const uint32_t*)(d_misc.as<char>() + 16),
+	launch_kmer_hash(h->stream, 1, (const uint64_t*)d_misc.p, d_codes.as<uint16_t>(), h->tab_comp.as<uint16_t>(), (const uint32_t*)(d_misc.as<char>() + 16),
 		(const uint64_t*)(d_misc.as<char>() + 64), (uint64_t)1, (uint64_t*)(d_misc.as<char>() + 32), k);
 	cudaStreamSynchronize(h->stream);
 	uint64_t res[2] = { 0, 0 };
@@ -2860,7 +2867,7 @@ int mbgfe_kat_kmer_hash_noalloc(mbgfe* h, const uint16_t* codes, uint32_t k, mbg
 	CU(h, cudaMemcpyAsync(scratch + 0, bases, 16, cudaMemcpyHostToDevice, h->stream));    // seg_out_base[0..1]
 	CU(h, cudaMemcpyAsync(scratch + 16, &zero32, 4, cudaMemcpyHostToDevice, h->stream));  // inst_pos[0]
 	CU(h, cudaMemcpyAsync(scratch + 64, range, 16, cudaMemcpyHostToDevice, h->stream));   // instance range [0, 1)
-	MBGFE_LAUNCH(k_kmer_hash, 1, HASH_NT, 0, h->stream, (const uint64_t*)scratch, (const uint16_t*)d_codes, h->tab_comp.as<uint16_t>(), (const uint32_t*)(scratch + 16),
+	launch_kmer_hash(h->stream, 1, (const uint64_t*)scratch, (const uint16_t*)d_codes, h->tab_comp.as<uint16_t>(), (const uint32_t*)(scratch + 16),
 		(const uint64_t*)(scratch + 64), (uint64_t)1, (uint64_t*)(scratch + 32), k);
 	CU(h, cudaGetLastError());
 	uint64_t res[2] = { 0, 0 };
