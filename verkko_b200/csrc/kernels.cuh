@@ -768,6 +768,20 @@ __global__ void __launch_bounds__(MSAT_WARPS * 32) k_msat(SegTable seg, const ui
 		{
 			// ---- single-symbol codes: every code start outside cover == 1
 			uint32_t sb = flags & ~cover1;
+			if (!pos2)
+			{
+				// without positions: one predicated store per symbol, the output slot counted along -- no find-first-set / popcount per
+				// code and no divergence between lanes (the loop below ran as long as the fullest word of the warp: 24 % of K2's
+				// instructions at 18 of 32 lanes)
+				uint32_t o = idx - base8;
+#pragma unroll
+				for (uint32_t b = 0; b < 32; b++)
+				{
+					if ((sb >> b) & 1) st_c[o] = (uint16_t)(((a0.lo >> b) & 1) | (((a0.hi >> b) & 1) << 1));
+					o += (flags >> b) & 1;
+				}
+				sb = 0;
+			}
 			while (sb)
 			{
 				const uint32_t b = __ffs(sb) - 1; sb &= sb - 1;
@@ -883,16 +897,6 @@ __device__ __forceinline__ uint64_t rotl_v(uint64_t v, uint32_t r)
 }
 __device__ __forceinline__ uint64_t rotr_v(uint64_t v, uint32_t r) { return rotl_v(v, (64 - r) & 63); }
 
-// Shared-memory plan of k_select<NT>.  A tile is T = 8 NT codes: every thread owns 8 consecutive codes / s-mer hashes /
-// k-mer decisions per tile, kept in registers.  Three stages run per tile with fixed lags (all multiples of 8):
-//   A  prefix values for codes [t0, t0+T)          -> pq ring   (16 B per prefix index: P', Q')
-//   B  s-mer hashes for [t0-LH, t0-LH+T)           -> h ring    (8 B per s-mer) + per-block minimum + minimum of the
-//                                                                first r hashes of each block of 8
-//   C  k-mer decisions for [t0-LH-LW, t0-LH-LW+T)  -> 1 bit per position
-// Ring layouts are padded per block of 8 entries (pq: 9 x 16 B, h: 10 x 8 B) so that threads that own consecutive blocks
-// hit distinct banks with 128-bit accesses.
-struct SelectPlan { uint32_t LH, LW, NBP, NBH, smem_bytes; };
-
 // K3a: FastHasher + findSyncmerPositions (MBG/FastHasher.h:16-32, MBG/ReadHelper.h:31-79) without the sequential
 // dependence.  The reference rolls fw = rotl(fw,1)^H[c] with the outgoing character removed; with the "moving frame"
 // prefixes  P'[n+1] = rotl(P'[n] ^ H[c_n], 1)  and  Q'[n+1] = rotr(Q'[n] ^ H[comp c_n], 1)  (P'[0] = Q'[0] = 0) the hash
@@ -905,27 +909,60 @@ struct SelectPlan { uint32_t LH, LW, NBP, NBH, smem_bytes; };
 // w-1 = 8a + r the window of p = 8b+j is: the suffix of block b from j, blocks b+1..b+a-1 (block minima), and the
 // first r+j+1 hashes counted from the start of block b+a (a running minimum over the 8 "last" hashes, seeded with the
 // minimum of the first r hashes of that block).
-// One CTA per segment.  Output: 1 bit per code position + selected count per segment.
-// Algorithmic bytes: 2 read per code + 1/8 written per code.
+// One CTA per segment, a tile is T = 8 NT codes: every thread owns 8 consecutive codes / s-mer hashes / k-mer decisions
+// per tile, kept in registers.  Three stages run per tile with fixed lags (multiples of 8):
+//   A  codes [t0, t0+T) -> code ring, prefixes at the block starts -> pq ring
+//   B  s-mer hashes for [t0-LH, t0-LH+T)           -> h ring (8 B per s-mer) + per-block minimum + minimum of the
+//                                                                first r hashes of each block of 8
+//   C  k-mer decisions for [t0-LH-LW, t0-LH-LW+T)  -> 1 bit per position
+// Output: 1 bit per code position + selected count per segment.  Algorithmic bytes: 2 read per code + 1/8 written per code.
+//
+// Rolling form.  Round 1's k_select kept P' and Q' of EVERY position in shared memory (16 bytes per position, two passes over
+// the thread's 8 codes to produce them, two 128-bit loads and three run-time rotations per s-mer to consume them).  Here the
+// ring holds the prefixes of one position in 8 -- those a thread needs for its FIRST s-mer, P'/Q' at 8j and at 8j + (s mod 8) --
+// and the other seven hashes of the thread roll from it as the reference's FastHasher does, with the outgoing and incoming
+// characters taken from a 2-byte-per-position code ring and their hashes from tables rotated in advance:
+//     fw(i+1) = rotl(fw(i), 1) ^ H[c(i+s)] ^ rotl(H[c(i)], s)               tab_in  = { H[c],          rotl(H[comp c], s-1) }
+//     bw(i+1) = rotr(bw(i), 1) ^ rotl(Hc[c(i+s)], s-1) ^ rotr(Hc[c(i)], 1)   tab_out = { rotl(H[c], s), rotr(H[comp c], 1)   }
+// (both follow from fw(i) = rotr(P'[i+s],1) ^ rotl(P'[i],s-1), bw(i) = rotl(Q'[i+s],s) ^ Q'[i] and the prefix recurrences).
+// Stage A loses its second pass and seven of its eight stores; shared memory per CTA falls from 50 KB to 25 KB (k=1001, w=100,
+// 128 threads); with 64 threads per CTA 6.71 -> 5.75 ms on the bench (profiles/r02_select_experiments.md).
+struct SelectPlan { uint32_t LH, LW, NBP, NBH, smem_bytes; };
+constexpr uint32_t BM_MIRROR = 16;      // windows up to w = 128 read their block minima without wrapping
+
+__global__ void k_build_roll_tables(const uint4* __restrict__ tab_pair, uint4* __restrict__ tab_in, uint4* __restrict__ tab_out, uint32_t s)
+{
+	const uint32_t c = blockIdx.x * blockDim.x + threadIdx.x;
+	if (c >= MAX_CODE) return;
+	const uint4 v = tab_pair[c];
+	const uint64_t hf = ((uint64_t)v.y << 32) | v.x, hb = ((uint64_t)v.w << 32) | v.z;
+	const uint64_t in_b = rotl64(hb, s - 1), out_f = rotl64(hf, s), out_b = rotr64(hb, 1);
+	tab_in[c] = make_uint4(v.x, v.y, (uint32_t)in_b, (uint32_t)(in_b >> 32));
+	tab_out[c] = make_uint4((uint32_t)out_f, (uint32_t)(out_f >> 32), (uint32_t)out_b, (uint32_t)(out_b >> 32));
+}
+
 template <int NT>
 __global__ void __launch_bounds__(NT) k_select(SegTable seg, const uint16_t* __restrict__ codes, const uint32_t* __restrict__ seg_c2,
-	const uint4* __restrict__ tab_pair, uint8_t* __restrict__ selmask, uint32_t* __restrict__ seg_nsel, uint32_t k, uint32_t w, SelectPlan plan)
+	const uint4* __restrict__ tab_pair, const uint4* __restrict__ tab_in, const uint4* __restrict__ tab_out, uint8_t* __restrict__ selmask,
+	uint32_t* __restrict__ seg_nsel, uint32_t k, uint32_t w, SelectPlan plan)
 {
 	constexpr uint32_t T = NT * 8;
 	constexpr uint64_t INF = ~0ull;
 	MBGFE_DYN_SMEM(smem_raw);
-	__shared__ uint4 small_tab[4];
+	__shared__ uint4 small_tab[4], small_in[4], small_out[4];
 	__shared__ Xor2 warp_tot[NT / 32];
+	__shared__ Xor2 s_carry[2];                                      // P', Q' at the start of the tile (by tile parity)
 	__shared__ uint32_t warp_tmp[NT / 32];
 	const uint32_t g = blockIdx.x;
 	if (g >= seg.n) return;
 	const uint32_t n = seg_c2[g];
 	if (n < k) { if (threadIdx.x == 0) seg_nsel[g] = 0; return; }
 	const uint32_t NBP = plan.NBP, NBH = plan.NBH, LH = plan.LH, LW = plan.LW;
-	uint4* pq = (uint4*)smem_raw;                                  // NBP blocks x 9 entries
-	uint64_t* hr = (uint64_t*)(pq + (size_t)NBP * 9);              // NBH blocks x 10 entries
-	uint64_t* bm = hr + (size_t)NBH * 10;                          // NBH block minima
-	uint64_t* pre = bm + NBH;                                      // NBH minima of the first r hashes of a block
+	uint4* pq = (uint4*)smem_raw;                                  // NBP blocks x { (P',Q')[8j], (P',Q')[8j + sr] }
+	uint4* cr = pq + (size_t)NBP * 2;                              // NBP + 1 blocks of 8 codes; block NBP mirrors block 0
+	uint64_t* hr = (uint64_t*)(cr + NBP + 1);                      // NBH blocks x 10 entries
+	uint64_t* bm = hr + (size_t)NBH * 10;                          // NBH block minima + BM_MIRROR entries that repeat the first ones
+	uint64_t* pre = bm + NBH + BM_MIRROR;                          // NBH minima of the first r hashes of a block
 	const uint64_t out0 = seg.out_base[g];
 	const uint16_t* __restrict__ c = codes + out0;
 	uint8_t* __restrict__ mask_out = selmask + (out0 >> 3);
@@ -935,70 +972,75 @@ __global__ void __launch_bounds__(NT) k_select(SegTable seg, const uint16_t* __r
 	const uint32_t sa = s >> 3, sr = s & 7;
 	const uint32_t rot_s1 = (s - 1) & 63, rot_s = s & 63;
 	const uint32_t lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
-	if (threadIdx.x < 4) small_tab[threadIdx.x] = __ldg(tab_pair + threadIdx.x);
-	if (threadIdx.x == 0) pq[0] = make_uint4(0, 0, 0, 0);          // P'[0] = Q'[0] = 0
-	// ring cursors (in blocks) of the first block each stage touches in the current tile
-	uint32_t curA = 0;                                             // pq block of prefix index t0
-	uint32_t curBp = (NBP - (LH >> 3) % NBP) % NBP;                // pq block of prefix index t0 - LH
+	if (threadIdx.x < 4) { small_tab[threadIdx.x] = __ldg(tab_pair + threadIdx.x); small_in[threadIdx.x] = __ldg(tab_in + threadIdx.x); small_out[threadIdx.x] = __ldg(tab_out + threadIdx.x); }
+	if (threadIdx.x == 0) { Xor2 z; z.a = 0; z.b = 0; s_carry[0] = z; s_carry[1] = z; }      // P'[0] = Q'[0] = 0
+	uint32_t curA = 0;                                             // pq / code block of position t0
+	uint32_t curBp = (NBP - (LH >> 3) % NBP) % NBP;                // pq / code block of position t0 - LH
 	uint32_t curBh = (NBH - (LH >> 3) % NBH) % NBH;                // h block of s-mer t0 - LH
 	uint32_t curC = (NBH - ((LH + LW) >> 3) % NBH) % NBH;          // h block of k-mer t0 - LH - LW
-	uint32_t my_sel = 0;
-	// the codes of the next tile are requested one tile ahead, so that their latency hides behind stages B and C
+	uint32_t my_sel = 0, parity = 0;
 	uint4 cw_next = make_uint4(0, 0, 0, 0);
 	if (8 * threadIdx.x < n) cw_next = __ldg((const uint4*)(c + 8 * threadIdx.x));
 	__syncthreads();
 	for (uint32_t t0 = 0; t0 < n + LH + LW; t0 += T)
 	{
-		// ------------------------------------------------------------------ stage A: prefixes of the new codes
-		if (t0 < n)
+		// ------------------------------------------------------------------ stage A: codes and block prefixes of the new tile
 		{
-			const uint32_t j0 = t0 + 8 * threadIdx.x;
-			const uint4 cw = cw_next;
-			cw_next = make_uint4(0, 0, 0, 0);
-			if (j0 + T < n) cw_next = __ldg((const uint4*)(c + j0 + T));
-			const uint32_t cws[4] = { cw.x, cw.y, cw.z, cw.w };
-			uint64_t hf[8], hb[8];
-#pragma unroll
-			for (int e = 0; e < 8; e++)
-			{
-				uint32_t code = (cws[e >> 1] >> ((e & 1) * 16)) & 0xffff;
-				if (j0 + e >= n) code = 0;
-				uint4 v = small_tab[code & 3];
-				if (code >= 4) v = __ldg(tab_pair + code);
-				hf[e] = u64_of(v.x, v.y); hb[e] = u64_of(v.z, v.w);
-			}
-			uint64_t ip = 0, iq = 0;
-#pragma unroll
-			for (int e = 0; e < 8; e++) { ip = rotl_c(ip ^ hf[e], 1); iq = rotr_c(iq ^ hb[e], 1); }
-			// inclusive warp scan; the value coming from d lanes below is advanced over the 8d codes gathered so far
-#pragma unroll
-			for (int d = 1; d < 32; d <<= 1)
-			{
-				const uint64_t tp = __shfl_up_sync(FULL, ip, d), tq = __shfl_up_sync(FULL, iq, d);
-				if (lane >= (uint32_t)d) { ip ^= rotl_c(tp, (8 * d) & 63); iq ^= rotr_c(tq, (8 * d) & 63); }
-			}
-			if (lane == 31) { Xor2 t; t.a = ip; t.b = iq; warp_tot[wid] = t; }
-			uint64_t ep = __shfl_up_sync(FULL, ip, 1), eq = __shfl_up_sync(FULL, iq, 1);
-			if (lane == 0) { ep = 0; eq = 0; }
-			__syncthreads();
-			// prefix at the start of the tile: index t0 sits at offset 0 of the block stage A writes first (left there by
-			// the previous tile; P'[0] = Q'[0] = 0 before the first).  A tile spans a multiple of 64 positions, so it
-			// enters every warp's base as it is.
-			Xor2 wbase;
-			{ const uint4 v = pq[(size_t)curA * 9]; wbase.a = u64_of(v.x, v.y); wbase.b = u64_of(v.z, v.w); }
-#pragma unroll
-			for (int i = 0; i < NT / 32 - 1; i++) { const Xor2 t = warp_tot[i]; if (i < (int)wid) { wbase.a ^= t.a; wbase.b ^= t.b; } }
-			uint64_t pv = rotl_c(wbase.a, (8 * lane) & 63) ^ ep, qv = rotr_c(wbase.b, (8 * lane) & 63) ^ eq;
-			// prefix index j0+e+1 lives in block curA + thread (offsets 1..7) and the next block (offset 0)
 			uint32_t blk = curA + threadIdx.x; if (blk >= NBP) blk -= NBP;
-			uint32_t blk2 = blk + 1; if (blk2 >= NBP) blk2 -= NBP;
-			uint4* dst = pq + (size_t)blk * 9;
-#pragma unroll
-			for (int e = 0; e < 8; e++)
+			if (t0 <= n)
 			{
-				pv = rotl_c(pv ^ hf[e], 1); qv = rotr_c(qv ^ hb[e], 1);
-				const uint4 v = make_uint4((uint32_t)pv, (uint32_t)(pv >> 32), (uint32_t)qv, (uint32_t)(qv >> 32));
-				if (e < 7) dst[e + 1] = v; else pq[(size_t)blk2 * 9] = v;
+				const uint32_t j0 = t0 + 8 * threadIdx.x;
+				uint4 cw = cw_next;
+				cw_next = make_uint4(0, 0, 0, 0);
+				if (j0 + T < n) cw_next = __ldg((const uint4*)(c + j0 + T));
+				// codes at and beyond n read as 0 (the slot holds whatever an earlier batch left there)
+				const uint32_t nv = j0 < n ? min(8u, n - j0) : 0u;
+				uint32_t cws[4] = { cw.x, cw.y, cw.z, cw.w };
+				if (nv < 8)
+				{
+#pragma unroll
+					for (int q = 0; q < 4; q++) { if (nv <= 2u * q) cws[q] = 0; else if (nv == 2u * q + 1) cws[q] &= 0xffffu; }
+				}
+				const uint4 cwm = make_uint4(cws[0], cws[1], cws[2], cws[3]);
+				cr[blk] = cwm;
+				if (blk == 0) cr[NBP] = cwm;
+				uint64_t ip = 0, iq = 0, cap_p = 0, cap_q = 0;
+#pragma unroll
+				for (int e = 0; e < 8; e++)
+				{
+					const uint32_t code = (cws[e >> 1] >> ((e & 1) * 16)) & 0xffff;
+					uint4 v = small_tab[code & 3];
+					if (code >= 4) v = __ldg(tab_pair + code);
+					ip = rotl_c(ip ^ u64_of(v.x, v.y), 1); iq = rotr_c(iq ^ u64_of(v.z, v.w), 1);
+					if ((uint32_t)e + 1 == sr) { cap_p = ip; cap_q = iq; }          // local prefix after sr codes
+				}
+				const uint64_t lp = ip, lq = iq;                                        // this block alone
+				// inclusive warp scan; the value coming from d lanes below is advanced over the 8d codes gathered so far
+#pragma unroll
+				for (int d = 1; d < 32; d <<= 1)
+				{
+					const uint64_t tp = __shfl_up_sync(FULL, ip, d), tq = __shfl_up_sync(FULL, iq, d);
+					if (lane >= (uint32_t)d) { ip ^= rotl_c(tp, (8 * d) & 63); iq ^= rotr_c(tq, (8 * d) & 63); }
+				}
+				if (lane == 31) { Xor2 t; t.a = ip; t.b = iq; warp_tot[wid] = t; }
+				uint64_t ep = __shfl_up_sync(FULL, ip, 1), eq = __shfl_up_sync(FULL, iq, 1);
+				if (lane == 0) { ep = 0; eq = 0; }
+				__syncthreads();
+				// a warp spans 256 positions and a tile a multiple of that: the tile's and the lower warps' totals enter as they are
+				Xor2 wbase = s_carry[parity];
+#pragma unroll
+				for (int i = 0; i < NT / 32 - 1; i++) { const Xor2 t = warp_tot[i]; if (i < (int)wid) { wbase.a ^= t.a; wbase.b ^= t.b; } }
+				const uint64_t pv = rotl_c(wbase.a, (8 * lane) & 63) ^ ep, qv = rotr_c(wbase.b, (8 * lane) & 63) ^ eq;      // P'[j0], Q'[j0]
+				const uint64_t ps = rotl_v(pv, sr) ^ cap_p, qs = rotr_v(qv, sr) ^ cap_q;                                  // P'[j0 + sr], Q'[j0 + sr]
+				pq[2 * blk] = make_uint4((uint32_t)pv, (uint32_t)(pv >> 32), (uint32_t)qv, (uint32_t)(qv >> 32));
+				pq[2 * blk + 1] = make_uint4((uint32_t)ps, (uint32_t)(ps >> 32), (uint32_t)qs, (uint32_t)(qs >> 32));
+				if (threadIdx.x == NT - 1) { Xor2 t; t.a = rotl_c(pv, 8) ^ lp; t.b = rotr_c(qv, 8) ^ lq; s_carry[parity ^ 1] = t; }      // P'[t0 + T]
+			}
+			else
+			{
+				const uint4 z = make_uint4(0, 0, 0, 0);
+				cr[blk] = z;
+				if (blk == 0) cr[NBP] = z;
 			}
 		}
 		__syncthreads();
@@ -1009,29 +1051,65 @@ __global__ void __launch_bounds__(NT) k_select(SegTable seg, const uint16_t* __r
 			{
 				uint32_t b0 = curBp + threadIdx.x; if (b0 >= NBP) b0 -= NBP;
 				uint32_t b1 = b0 + sa; if (b1 >= NBP) b1 -= NBP;
-				uint32_t b2 = b1 + 1; if (b2 >= NBP) b2 -= NBP;
-				const uint4* x0 = pq + (size_t)b0 * 9;
-				const uint4* y1 = pq + (size_t)b1 * 9;
-				const uint4* y2 = pq + (size_t)b2 * 9;
-				uint64_t hv[8];
-				uint64_t m = INF, mpre = INF;
 				const uint32_t i0u = (uint32_t)i0;
 				const uint32_t n_ok = i0u < n_smers ? min(8u, n_smers - i0u) : 0u;    // valid s-mers of this block
+				uint64_t fw, bw;
+				{
+					const uint4 x = pq[2 * b0], y = pq[2 * b1 + 1];
+					fw = rotr_c(u64_of(y.x, y.y), 1) ^ rotl_v(u64_of(x.x, x.y), rot_s1);
+					bw = rotl_v(u64_of(y.z, y.w), rot_s) ^ u64_of(x.z, x.w);
+				}
+				// outgoing codes c[i0 .. i0+7]: this block; incoming codes c[i0+s .. i0+s+7]: from offset sr of block b1 on
+				const uint4 oc = cr[b0];
+				uint32_t iw[4];
+				{
+					const uint4 A = cr[b1], B = cr[b1 + 1];
+					uint32_t w5[5];
+					switch (sr >> 1)
+					{
+						case 0: w5[0] = A.x; w5[1] = A.y; w5[2] = A.z; w5[3] = A.w; w5[4] = B.x; break;
+						case 1: w5[0] = A.y; w5[1] = A.z; w5[2] = A.w; w5[3] = B.x; w5[4] = B.y; break;
+						case 2: w5[0] = A.z; w5[1] = A.w; w5[2] = B.x; w5[3] = B.y; w5[4] = B.z; break;
+						default: w5[0] = A.w; w5[1] = B.x; w5[2] = B.y; w5[3] = B.z; w5[4] = B.w; break;
+					}
+					if (sr & 1)
+					{
+#pragma unroll
+						for (int q = 0; q < 4; q++) iw[q] = (w5[q] >> 16) | (w5[q + 1] << 16);
+					}
+					else
+					{
+#pragma unroll
+						for (int q = 0; q < 4; q++) iw[q] = w5[q];
+					}
+				}
+				const uint32_t ow[4] = { oc.x, oc.y, oc.z, oc.w };
+				uint64_t hv[8];
+				uint64_t m = INF, mpre = INF;
 #pragma unroll
 				for (int e = 0; e < 8; e++)
 				{
-					uint64_t v = INF;
-					if ((uint32_t)e < n_ok)
+					hv[e] = fw < bw ? fw : bw;
+					if (e < 7)
 					{
-						const uint4 x = x0[e];
-						const uint4 y = (e + sr < 8) ? y1[e + sr] : y2[e + sr - 8];
-						const uint64_t fw = rotr_c(u64_of(y.x, y.y), 1) ^ rotl_v(u64_of(x.x, x.y), rot_s1);
-						const uint64_t bw = rotl_v(u64_of(y.z, y.w), rot_s) ^ u64_of(x.z, x.w);
-						v = fw < bw ? fw : bw;
+						const uint32_t co = (ow[e >> 1] >> ((e & 1) * 16)) & 0xffff, ci = (iw[e >> 1] >> ((e & 1) * 16)) & 0xffff;
+						uint4 vo = small_out[co & 3], vi = small_in[ci & 3];
+						if (co >= 4) vo = __ldg(tab_out + co);
+						if (ci >= 4) vi = __ldg(tab_in + ci);
+						fw = rotl_c(fw, 1) ^ u64_of(vi.x, vi.y) ^ u64_of(vo.x, vo.y);
+						bw = rotr_c(bw, 1) ^ u64_of(vi.z, vi.w) ^ u64_of(vo.z, vo.w);
 					}
-					hv[e] = v;
+				}
+				if (n_ok < 8)      // only where the segment ends
+				{
+#pragma unroll
+					for (int e = 0; e < 8; e++) if ((uint32_t)e >= n_ok) hv[e] = INF;
+				}
+#pragma unroll
+				for (int e = 0; e < 8; e++)
+				{
 					if ((uint32_t)e == r) mpre = m;      // minimum of the first r hashes of the block
-					m = v < m ? v : m;
+					m = hv[e] < m ? hv[e] : m;
 				}
 				uint32_t hbk = curBh + threadIdx.x; if (hbk >= NBH) hbk -= NBH;
 				uint4* dst = (uint4*)(hr + (size_t)hbk * 10);
@@ -1039,6 +1117,7 @@ __global__ void __launch_bounds__(NT) k_select(SegTable seg, const uint16_t* __r
 				for (int e = 0; e < 4; e++)
 					dst[e] = make_uint4((uint32_t)hv[2 * e], (uint32_t)(hv[2 * e] >> 32), (uint32_t)hv[2 * e + 1], (uint32_t)(hv[2 * e + 1] >> 32));
 				bm[hbk] = m;
+				if (hbk < BM_MIRROR) bm[NBH + hbk] = m;
 				pre[hbk] = mpre;
 			}
 		}
@@ -1080,13 +1159,22 @@ __global__ void __launch_bounds__(NT) k_select(SegTable seg, const uint16_t* __r
 					for (int t = 6; t >= 0; t--) suf[t] = own[t] < suf[t + 1] ? own[t] : suf[t + 1];
 					uint64_t core = INF;                                 // blocks b+1 .. b+a-1
 					{
-						// blocks d0+1 .. d0+a-1 of the ring: at most one wrap, so two plain runs
+						// blocks d0+1 .. d0+a-1 of the ring, read through its mirrored head when a <= BM_MIRROR (no wrap), else in two runs
 						const uint32_t first = d0 + 1, cnt = a - 1;
-						const uint32_t run1 = first >= NBH ? 0 : min(cnt, NBH - first);
-						const uint64_t* q1 = bm + first;
-						for (uint32_t t = 0; t < run1; t++) { const uint64_t v = q1[t]; core = v < core ? v : core; }
-						const uint64_t* q2 = bm + (first >= NBH ? first - NBH : 0);
-						for (uint32_t t = 0; t < cnt - run1; t++) { const uint64_t v = q2[t]; core = v < core ? v : core; }
+						if (a <= BM_MIRROR)
+						{
+							const uint64_t* q1 = bm + first;
+#pragma unroll 4
+							for (uint32_t t = 0; t < cnt; t++) { const uint64_t v = q1[t]; core = v < core ? v : core; }
+						}
+						else
+						{
+							const uint32_t run1 = first >= NBH ? 0 : min(cnt, NBH - first);
+							const uint64_t* q1 = bm + first;
+							for (uint32_t t = 0; t < run1; t++) { const uint64_t v = q1[t]; core = v < core ? v : core; }
+							const uint64_t* q2 = bm + (first >= NBH ? first - NBH : 0);
+							for (uint32_t t = 0; t < cnt - run1; t++) { const uint64_t v = q2[t]; core = v < core ? v : core; }
+						}
 					}
 					uint32_t e0 = d0 + a; if (e0 >= NBH) e0 -= NBH;      // block that holds the window ends
 					uint32_t e1 = e0 + 1; if (e1 >= NBH) e1 -= NBH;
@@ -1110,6 +1198,7 @@ __global__ void __launch_bounds__(NT) k_select(SegTable seg, const uint16_t* __r
 			}
 		}
 		__syncthreads();
+		parity ^= 1;
 		curA += NT; if (curA >= NBP) curA -= NBP;
 		curBp += NT; if (curBp >= NBP) curBp -= NBP;
 		curBh += NT; if (curBh >= NBH) curBh -= NBH;

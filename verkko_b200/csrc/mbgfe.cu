@@ -65,7 +65,6 @@ struct Timer
 
 }
 
-constexpr int NT_SELECT_DEFAULT = 128;
 
 struct mbgfe
 {
@@ -80,10 +79,9 @@ struct mbgfe
 	int sm_count = 148;
 	size_t max_smem = 0;
 	SelectPlan plan;
-	int select_nt = NT_SELECT_DEFAULT;                              // threads per CTA of k_select
 
 	// code tables
-	DevBuf tab_hash, tab_pair, tab_comp, tab_pext8;
+	DevBuf tab_hash, tab_pair, tab_comp, tab_pext8, tab_in, tab_out;
 
 	// pending input
 	std::vector<HostChunk> pending;
@@ -221,7 +219,10 @@ bool is_acgt(char c) { c &= (char)0xdf; return c == 'A' || c == 'C' || c == 'G' 
 enum { CTR_NONACGT = 0, CTR_PALINDROME = 1, CTR_DISTINCT = 2, CTR_EDGES = 3, CTR_CURSOR = 4 /* and 5 */, CTR_OVERFLOW = 6, CTR_OWNER = 8 /* .. 8+world */ };
 constexpr uint64_t PAL_CAP = 1 << 20;
 
-constexpr int NT_MSAT = 128, NT_SELECT = 128, NT_LIST = 128;   // k_select: 128 beats 64 / 256 / 512 on the bench (7.1 / 7.6 / 8.1 / 10.8 ms)
+#ifndef MBGFE_NT_SELECT
+#define MBGFE_NT_SELECT 64
+#endif
+constexpr int NT_MSAT = 128, NT_SELECT = MBGFE_NT_SELECT, NT_LIST = 128;   // k_select: 64 / 128 / 256 threads = 5.75 / 6.03 / 7.24 ms on the bench
 
 SegTable seg_table(const mbgfe* h)
 {
@@ -312,7 +313,7 @@ SelectPlan make_plan(uint32_t k, uint32_t w, size_t max_smem, bool& ok, uint32_t
 	p.LW = 8 * (a + 1);
 	p.NBP = (p.LH + T) / 8 + 2;
 	p.NBH = nt + p.LW / 8 + 2;
-	const size_t bytes = (size_t)p.NBP * 9 * 16 + (size_t)p.NBH * 10 * 8 + (size_t)p.NBH * 16 + 64;
+	const size_t bytes = (size_t)p.NBP * 32 + (size_t)(p.NBP + 1) * 16 + (size_t)p.NBH * 10 * 8 + (size_t)p.NBH * 16 + BM_MIRROR * 8 + 64;
 	p.smem_bytes = (uint32_t)bytes;
 	ok = bytes + 2048 <= max_smem;
 	return p;
@@ -502,17 +503,9 @@ int mbgfe_create(const mbgfe_params* prm, mbgfe** out)
 	if (ensure(h, h->tab_pext8, 65536)) return bail(MBGFE_E_CUDA);
 	MBGFE_LAUNCH(k_build_pext8, 256, 256, 0, h->stream, h->tab_pext8.as<uint8_t>());
 	cudaFuncSetAttribute(k_collapse_lut, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(65536 + COLLAPSE_LUT_WARPS * 2 * COLLAPSE_STAGE * 4));
-	if (const char* e = getenv("MBGFE_SELECT_NT"))
-	{
-		// experiment knob: threads per CTA of k_select (64 / 256 / 512 instead of 128); the tile is 8 codes per thread
-		const int nt = atoi(e);
-		bool ok2 = false;
-		if (nt == 64 || nt == 256 || nt == 512) { SelectPlan p2 = make_plan(prm->k, prm->w, h->max_smem, ok2, (uint32_t)nt); if (ok2) { h->plan = p2; h->select_nt = nt; } }
-	}
+	if (ensure(h, h->tab_in, MAX_CODE * 16) || ensure(h, h->tab_out, MAX_CODE * 16)) return bail(MBGFE_E_CUDA);
+	MBGFE_LAUNCH(k_build_roll_tables, (MAX_CODE + 255) / 256, 256, 0, h->stream, h->tab_pair.as<uint4>(), h->tab_in.as<uint4>(), h->tab_out.as<uint4>(), prm->k - prm->w + 1);
 	cudaFuncSetAttribute(k_select<NT_SELECT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->plan.smem_bytes);
-	cudaFuncSetAttribute(k_select<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->plan.smem_bytes);
-	cudaFuncSetAttribute(k_select<256>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->plan.smem_bytes);
-	cudaFuncSetAttribute(k_select<512>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->plan.smem_bytes);
 	if (cudaStreamSynchronize(h->stream) != cudaSuccess || cudaGetLastError() != cudaSuccess)
 		return bail(fail(h, MBGFE_E_CUDA, "table kernel failed: is this an sm_100 device?"));
 	*out = h;
@@ -522,7 +515,7 @@ int mbgfe_create(const mbgfe_params* prm, mbgfe** out)
 void mbgfe_destroy(mbgfe* h)
 {
 	if (!h) return;
-	for (DevBuf* b : { &h->tab_hash, &h->tab_pair, &h->tab_comp, &h->tab_pext8, &h->d_ascii, &h->d_packed, &h->d_nonacgt, &h->d_counters, &h->d_seg_in, &h->d_seg_out,
+	for (DevBuf* b : { &h->tab_hash, &h->tab_pair, &h->tab_comp, &h->tab_pext8, &h->tab_in, &h->tab_out, &h->d_ascii, &h->d_packed, &h->d_nonacgt, &h->d_counters, &h->d_seg_in, &h->d_seg_out,
 		&h->d_seg_len, &h->d_seg_c1, &h->d_seg_c2, &h->d_seg_nsel, &h->d_sel_begin, &h->d_sym, &h->d_codes, &h->d_selmask, &h->d_pos1, &h->d_pos2,
 		&h->d_inst_pos, &h->d_inst_seg, &h->d_inst_flag, &h->d_inst_hash, &h->d_inst_slot, &h->d_pal_list, &h->d_nodes, &h->d_edges, &h->d_node_out,
 		&h->d_edge_out, &h->d_records, &h->d_recv, &h->d_bucket_count, &h->d_bucket_begin, &h->d_scan_tot, &h->d_scan_off, &h->d_node_hash_sorted, &h->d_node_cov,
@@ -763,18 +756,8 @@ uint32_t launch_front(mbgfe* h, uint32_t g0, uint32_t cnt, bool timed, cudaStrea
 		MBGFE_LAUNCH(k_unpack_symbols<NT_MSAT>, cnt, NT_MSAT, 0, on, st, h->d_sym.as<uint64_t>(), c1, h->d_codes.as<uint16_t>(),
 			c2, (const uint32_t*)pos1, pos2);
 	if (timed) tick(h, 5);
-	if (h->select_nt == 64)
-		MBGFE_LAUNCH(k_select<64>, cnt, 64, h->plan.smem_bytes, on, st, h->d_codes.as<uint16_t>(), c2, h->tab_pair.as<uint4>(),
-			h->d_selmask.as<uint8_t>(), h->d_seg_nsel.as<uint32_t>() + g0, k, w, h->plan);
-	else if (h->select_nt == 256)
-		MBGFE_LAUNCH(k_select<256>, cnt, 256, h->plan.smem_bytes, on, st, h->d_codes.as<uint16_t>(), c2, h->tab_pair.as<uint4>(),
-			h->d_selmask.as<uint8_t>(), h->d_seg_nsel.as<uint32_t>() + g0, k, w, h->plan);
-	else if (h->select_nt == 512)
-		MBGFE_LAUNCH(k_select<512>, cnt, 512, h->plan.smem_bytes, on, st, h->d_codes.as<uint16_t>(), c2, h->tab_pair.as<uint4>(),
-			h->d_selmask.as<uint8_t>(), h->d_seg_nsel.as<uint32_t>() + g0, k, w, h->plan);
-	else
-		MBGFE_LAUNCH(k_select<NT_SELECT>, cnt, NT_SELECT, h->plan.smem_bytes, on, st, h->d_codes.as<uint16_t>(), c2, h->tab_pair.as<uint4>(),
-			h->d_selmask.as<uint8_t>(), h->d_seg_nsel.as<uint32_t>() + g0, k, w, h->plan);
+	MBGFE_LAUNCH(k_select<NT_SELECT>, cnt, NT_SELECT, h->plan.smem_bytes, on, st, h->d_codes.as<uint16_t>(), c2, h->tab_pair.as<uint4>(), h->tab_in.as<uint4>(),
+		h->tab_out.as<uint4>(), h->d_selmask.as<uint8_t>(), h->d_seg_nsel.as<uint32_t>() + g0, k, w, h->plan);
 	return 3;
 }
 
