@@ -248,12 +248,15 @@ def test_emulated_host_packed_pieces(oracle, emu_library, monkeypatch, pct, mode
     compare_runs(got, oracle.run(mode, k, w, reads), what=f"host pack {pct}% {mode}")
 
 
-@pytest.mark.parametrize("mode,k,w", [("hpc", 63, 33), ("no", 101, 20), ("dinuc", 63, 33), ("collapse", 31, 1)])
+@pytest.mark.parametrize("mode,k,w", [("hpc", 63, 33), ("no", 101, 20), ("dinuc", 63, 33), ("collapse", 31, 1), ("msat", 63, 33), ("collapse-msat", 101, 20)])
 def test_emulated_collapse_by_table_without_positions(oracle, emu_library, mode, k, w):
     """k_collapse_lut (the K1 that runs when per-base positions are not wanted: flags = 0) in every run-length mode, ragged lengths
-    around the 4 096-base tile and the 128-base lane share"""
+    around the 4 096-base tile and the 128-base lane share; in the msat modes also K2's store-per-symbol emission of single codes
+    (the path without positions), with tandem repeats longer than a tile"""
     a = workloads.read_a()
     reads = [a, a[:4096], a[:4097], a[:4095 + 128], a[:129], a[:127], a[:33], workloads.read_with_other_characters(), workloads.repeat_rich(7, 9000), b"A" * 5000 + a[:300]]
+    if "msat" in mode:
+        reads += workloads.long_tandem_reads()[:2] + [workloads.repeat_rich(22, 5000)]
     got = run_frontend(mode, k, w, reads, library=emu_library, flags=0)
     want = oracle.run(mode, k, w, reads)
     assert np.array_equal(got.positions, want.positions) and np.array_equal(got.hashes, want.hashes)
