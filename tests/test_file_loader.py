@@ -132,6 +132,9 @@ def test_streaming_fasta_on_gpu(oracle, tmp_path, piece):
     fb.write_bytes(data)
     got = run_file([fa, fb], "collapse-msat", 1001, 100, piece_bytes=piece)
     check_against_oracle(oracle, got, [fa.read_bytes(), data], "collapse-msat", 1001, 100, f"gpu streaming piece={piece}")
+    # characters outside ACGT are cut by the stitcher as the pieces come in: the run never goes back over the image (a second,
+    # staged pass would report per-kernel times)
+    assert got["stats"]["nonacgt"] > 0 and got["stats"]["ms_collapse"] == 0 and got["stats"]["ms_select"] == 0
     # the same through the plain parser (MBGFE_FILE_LEGACY): identical arrays
     os.environ["MBGFE_FILE_LEGACY"] = "1"
     try:

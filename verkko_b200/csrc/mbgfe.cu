@@ -1254,10 +1254,11 @@ struct FastaStitch
 	uint64_t line_start = 0, seq_start = 0, seq_end = 0, name_start = 0, name_end = 0, pending_cr = ~0ull;
 	bool in_header = false, have_record = false, have_seq = false, multiline = false;
 	size_t bad_at_line = 0;
-	std::vector<uint64_t>* bad = nullptr;
+	std::vector<uint64_t>* bad = nullptr;                                  // positions of the characters outside ACGT, ascending ...
+	std::vector<unsigned char>* bad_ch = nullptr;                          // ... and the characters themselves
 	std::function<void(uint64_t, uint64_t, uint64_t, uint64_t)> emit;      // seq_start, seq_end, name_start, name_end
 
-	void flush_cr() { if (pending_cr != ~0ull) { bad->push_back(pending_cr); pending_cr = ~0ull; } }
+	void flush_cr() { if (pending_cr != ~0ull) { bad->push_back(pending_cr); bad_ch->push_back('\r'); pending_cr = ~0ull; } }
 	void finish_record() { if (have_record && !have_seq) emit(name_end, name_end, name_start, name_end); have_record = false; have_seq = false; }
 	void end_line(uint64_t pos)          // the current line is [line_start, pos)
 	{
@@ -1269,7 +1270,7 @@ struct FastaStitch
 			flush_cr();
 			if (end > line_start)
 			{
-				if (!have_record) bad->resize(bad_at_line);            // text before the first header: not a read
+				if (!have_record) { bad->resize(bad_at_line); bad_ch->resize(bad_at_line); }      // text before the first header: not a read
 				else if (have_seq) multiline = true;
 				else { seq_start = line_start; seq_end = end; have_seq = true; emit(seq_start, seq_end, name_start, name_end); }
 			}
@@ -1283,7 +1284,7 @@ struct FastaStitch
 		if (in_header) return;
 		if (ch == '>' && pos == line_start) { flush_cr(); finish_record(); in_header = true; name_start = pos + 1; return; }
 		flush_cr();
-		if (ch == '\r') pending_cr = pos; else bad->push_back(pos);
+		if (ch == '\r') pending_cr = pos; else { bad->push_back(pos); bad_ch->push_back(ch); }
 	}
 	void end_of_file(uint64_t pos) { if (pos > line_start || in_header) end_line(pos); flush_cr(); finish_record(); }
 };
@@ -1370,11 +1371,12 @@ int run_files(mbgfe* h)
 	}
 	// ---- the stitcher: reads and segments as the pieces come in
 	std::vector<uint64_t> bad;
+	std::vector<unsigned char> bad_ch;
 	uint64_t out = 0, raw_bases = 0;
 	bool refuse = false;
 	size_t cur_file = 0;
 	FastaStitch st;
-	st.bad = &bad;
+	st.bad = &bad; st.bad_ch = &bad_ch;
 	const std::function<void(uint64_t, uint64_t, uint64_t, uint64_t)> emit_read = [&](uint64_t s0, uint64_t s1, uint64_t n0, uint64_t n1)
 	{
 		const uint64_t r = h->read_off.size();
@@ -1383,10 +1385,38 @@ int run_files(mbgfe* h)
 		raw_bases += s1 - s0;
 		if (s1 - s0 >= (1ull << 29)) { refuse = true; return; }
 		if (s1 - s0 < 32) return;                                     // MBG/ReadHelper.h:838
-		if (h->seg_len.size() >= seg_cap) { refuse = true; return; }
-		h->seg_in.push_back(s0); h->seg_len.push_back((uint32_t)(s1 - s0)); h->seg_read.push_back((uint32_t)r); h->seg_rawoff.push_back(0);
-		h->seg_nonacgt_before.push_back(0); h->seg_out.push_back(out);
-		out += ((s1 - s0) + 1 + 63) & ~(uint64_t)63;
+		auto add = [&](uint64_t start, uint64_t len, uint32_t nonacgt_before)
+		{
+			if (h->seg_len.size() >= seg_cap) { refuse = true; return; }
+			h->seg_in.push_back(start); h->seg_len.push_back((uint32_t)len); h->seg_read.push_back((uint32_t)r); h->seg_rawoff.push_back((uint32_t)(start - s0));
+			h->seg_nonacgt_before.push_back(nonacgt_before); h->seg_out.push_back(out);
+			out += (len + 1 + 63) & ~(uint64_t)63;
+		};
+		// the characters outside ACGT of this line are the last entries of `bad` (the scan reported them before the line's end)
+		size_t bi = st.bad_at_line;
+		while (bi < bad.size() && bad[bi] < s0) bi++;
+		if (bi >= bad.size() || bad[bi] >= s1) { add(s0, s1 - s0, 0); return; }
+		// a read with such characters is cut at them right here, as build_segments does for a resident batch (MBG/ReadHelper.h:864-897):
+		// the run never has to go back over the image.  A character next to an ACGT base always differs from it; inside a run of
+		// other characters the scan's own bytes decide what the collapse step keeps.
+		uint64_t cur = s0;
+		uint32_t collapsed_other = 0;
+		while (cur < s1)
+		{
+			const uint64_t stop = (bi < bad.size() && bad[bi] < s1) ? bad[bi] : s1;
+			if (stop > cur) add(cur, stop - cur, collapsed_other);
+			if (stop >= s1) break;
+			uint64_t e = stop;
+			while (bi < bad.size() && bad[bi] == e && e < s1)
+			{
+				unsigned char c = bad_ch[bi], pch = (e > stop) ? bad_ch[bi - 1] : 0;
+				if (c >= 'a' && c <= 'z') c = (unsigned char)(c - 32);
+				if (pch >= 'a' && pch <= 'z') pch = (unsigned char)(pch - 32);
+				if (e == stop || c != pch) collapsed_other++;
+				e++; bi++;
+			}
+			cur = e;
+		}
 	};
 	st.emit = emit_read;
 	const bool want_table = !(h->prm.flags & MBGFE_NO_TABLE) && !h->appending;
@@ -1399,7 +1429,7 @@ int run_files(mbgfe* h)
 	{
 		const Piece& pc = pieces[piece];
 		pool.wait_piece(piece);
-		if (pc.file != cur_file) { cur_file = pc.file; st = FastaStitch(); st.bad = &bad; st.emit = emit_read; st.line_start = pc.pos; }
+		if (pc.file != cur_file) { cur_file = pc.file; st = FastaStitch(); st.bad = &bad; st.bad_ch = &bad_ch; st.bad_at_line = bad.size(); st.emit = emit_read; st.line_start = pc.pos; }
 		if (piece == 0) st.line_start = pc.pos;
 		const size_t seg_before = h->seg_len.size();
 		for (size_t t = pc.task0; t < pc.task1; t++)
@@ -1486,26 +1516,6 @@ int run_files(mbgfe* h)
 	h->stats.reads = h->n_reads; h->stats.raw_bases = raw_bases; h->stats.nonacgt = bad.size();
 	h->nonacgt_count = bad.size();
 	h->pending.clear();
-	if (!bad.empty())
-	{
-		// rare: cut the reads at the characters outside ACGT and run the resident image again; the few reads that hold such
-		// characters are read back from the file (the collapse step needs their text, build_segments)
-		std::sort(bad.begin(), bad.end());
-		std::string text;
-		build_segments(h, bad, [&](uint64_t r) -> const char*
-		{
-			const auto& f = h->image_files[h->name_file[r]];
-			const uint64_t len = h->read_end[r] - h->read_off[r];
-			text.resize(len);
-			if (len && pread(f.fd, &text[0], len, (off_t)(h->read_off[r] - f.base)) != (ssize_t)len) std::fill(text.begin(), text.end(), 'N');
-			return text.data();
-		});
-		if (int rc = upload_segments(h)) return rc;
-		CU(h, cudaStreamSynchronize(h->stream));
-		h->stats.segments = h->seg_len.size();
-		h->resident = true;
-		return mbgfe_process(h);
-	}
 	h->stats.segments = n_seg;
 	h->resident = true;
 	if ((n_seg && !sized) || g_tail != n_seg || c8[CTR_PALINDROME] || c8[CTR_OVERFLOW] || n_inst > h->inst_cap)
