@@ -263,14 +263,16 @@ int mbgfe_timer_stop(mbgfe* h, float* ms);
  * the canonical high word, the smaller of two uniform words), so that concatenating the ranks' sorted partitions IS the global
  * sortByHash order.  After mbgfe_process() / mbgfe_run() with MBGFE_NO_TABLE on every rank, ONE collective call does the rest inside
  * the library:
- *   1. one kernel counts, per owner, the node records AND the edge records this rank holds (the owner of an edge is the owner of its
- *      canonical `from` node: decided from the hashes alone); one all-gather gives every rank the whole count matrix
+ *   1. one kernel counts, per owner, the node records AND the edge records this rank holds (the owner of an edge is the owner of one
+ *      of its two nodes -- the canonical `from` when the low bits of the two canonical hashes agree, else `to`: decided from the hashes
+ *      alone, the same for both strands, and uniform over the ranks); one all-gather gives every rank the whole count matrix
  *   2. node records {canonical hash lo, hi, tip, reserved} (32 bytes) go to their owners (all-to-all-v); owners count them into their
  *      partition and remember the slot of every record
  *   3. partition sizes are all-gathered; global node id = nodes owned by lower ranks + rank inside the sorted partition, read from the
  *      slot (no second probe); ids go back to the senders (reverse all-to-all-v, 4 bytes each)
- *   4. edge records {canonical (from id, to id), (global instance index << 24) | overlap} (16 bytes) go to the owner of `from`
- *      (keeps "last observation in input order" global, MBG/HashList.cpp:67-72); owners build their edge partition
+ *   4. edge records {canonical (from id, to id), (global instance index << 24) | overlap} (16 bytes) go to the edge's owner
+ *      (keeps "last observation in input order" global, MBG/HashList.cpp:67-72); owners build their edge partition.  The partitions
+ *      are each sorted; together (not concatenated) they are the edge table
  * Afterwards MBGFE_NODE_* / MBGFE_EDGES return this rank's partition with GLOBAL node ids (limit 2^31-1 nodes).
  * Transports: NCCL between processes (grouped ncclSend / ncclRecv; libnccl.so.2 is loaded on first use), peer copies between the
  * handles of one process (mbgfe_exchange_group), or the caller's own collectives on the library's device buffers (callbacks). */

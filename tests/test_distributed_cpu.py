@@ -29,11 +29,18 @@ def check_partitions(parts, want, world):
     cov = np.concatenate([p["node_cov"] for p in parts])
     tip = np.concatenate([p["node_tip"] for p in parts])
     assert np.array_equal(nh, want.node_hash) and np.array_equal(cov, want.node_cov) and np.array_equal(tip, want.node_tip)
-    # edges: every rank holds the edges whose `from` node it owns, with global ids; concatenated they are the oracle's edge table
+    # edges: global ids; a rank holds the edges of which it owns `from` when the low bits of the two canonical hashes agree, else those
+    # of which it owns `to` (balanced over the ranks: always `from`, the smaller hash, would load the low ranks); together they are
+    # the oracle's edge table
     begin = np.concatenate([[0], np.cumsum([len(p["node_cov"]) for p in parts])])
+    n_edges = [len(p["edges"]) for p in parts]
     for r, p in enumerate(parts):
         e = p["edges"]
-        assert np.all((e[:, 0] >= begin[r]) & (e[:, 0] < begin[r + 1])), "edge on the wrong owner"
+        take_from = ((nh[e[:, 0], 0] ^ nh[e[:, 2], 0]) & np.uint64(1)) == 0      # columns: from, from_fw, to, to_fw, coverage, overlap
+        holder = np.where(take_from, np.minimum(e[:, 0], e[:, 2]), np.maximum(e[:, 0], e[:, 2]))
+        assert np.all((holder >= begin[r]) & (holder < begin[r + 1])), "edge on the wrong owner"
+    if sum(n_edges) > 2000:
+        assert max(n_edges) < 1.25 * sum(n_edges) / world + 50, f"edges not balanced over the ranks: {n_edges}"
     edges = np.concatenate([p["edges"] for p in parts])
     assert np.array_equal(sorted_edges(edges), sorted_edges(want.edges))
 

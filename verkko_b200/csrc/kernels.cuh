@@ -2209,7 +2209,12 @@ __global__ void __launch_bounds__(256) k_insert_edge_records(const unsigned long
 
 // ---- the exchange as libmbgfe runs it itself (mbgfe_exchange): counts of BOTH collectives from the hashes alone, one pass
 
-// the rank that will own the edge observation (i - 1, i): the owner of its canonical `from` node (canonical_edge_key's choice)
+// The rank that will own the edge observation (i - 1, i): the owner of one of its two nodes, `from` (canonical_edge_key's choice, the
+// smaller canonical hash) when the low bits of the two canonical hashes agree, else `to`.  Always `from` was round 1's rule, and
+// with k-mers owned by hash RANGE it sent the edges to the low ranks (the smaller of two hashes is in the lowest 1/world of the range
+// with probability 1 - (1 - 1/world)^2: 75 % of the edges on rank 0 of 2, 23 % instead of 12.5 % on rank 0 of 8 -- the "inserts of
+// received records run 1.5-1.9x slower" of profiles/r02_exchange_trace_n2.txt).  The bit is symmetric in the two nodes and the same for
+// both strands of an observation, and min and max together are uniform over the ranks.
 __device__ __forceinline__ uint32_t edge_owner_of(uint64_t a_lo, uint64_t a_hi, uint64_t b_lo, uint64_t b_hi, uint32_t world)
 {
 	uint64_t ak_lo, ak_hi, bk_lo, bk_hi; uint32_t afw, bfw;
@@ -2217,7 +2222,9 @@ __device__ __forceinline__ uint32_t edge_owner_of(uint64_t a_lo, uint64_t a_hi, 
 	canonical_key(b_lo, b_hi, bk_lo, bk_hi, bfw);
 	const bool to_smaller = bk_hi < ak_hi || (bk_hi == ak_hi && bk_lo < ak_lo);
 	const bool same = bk_hi == ak_hi && bk_lo == ak_lo;
-	return owner_of((to_smaller || (same && !bfw && !afw)) ? bk_hi : ak_hi, world);
+	const bool from_is_b = to_smaller || (same && !bfw && !afw);
+	const bool take_from = ((ak_lo ^ bk_lo) & 1) == 0;
+	return owner_of((from_is_b == take_from) ? bk_hi : ak_hi, world);
 }
 
 __device__ __forceinline__ bool has_edge_observation(uint64_t i, uint64_t n_inst, const uint64_t* __restrict__ inst_hash, const uint8_t* __restrict__ inst_flag)
@@ -2263,8 +2270,8 @@ __global__ void __launch_bounds__(256) k_slot_ids(const uint32_t* __restrict__ r
 	if (i < n_rec) ids[i] = id_base + (uint32_t)table[rec_slot[i]].rank;
 }
 
-// edge records {canonical (from id, to id) key, (global instance index << 24) | overlap} grouped by the owner of `from` (same
-// rule as k_owner_count2 counted with)
+// edge records {canonical (from id, to id) key, (global instance index << 24) | overlap} grouped by edge_owner_of (the rule
+// k_owner_count2 counted with)
 __global__ void __launch_bounds__(256) k_edge_owner_pack2(const uint64_t* __restrict__ inst_hash, const uint32_t* __restrict__ inst_pos, const uint8_t* __restrict__ inst_flag,
 	const uint32_t* __restrict__ inst_packpos, const uint32_t* __restrict__ packed_ids, uint64_t n_inst, uint64_t inst_base, uint32_t k, uint32_t world,
 	unsigned long long* __restrict__ cursors, unsigned long long* __restrict__ records)

@@ -1691,9 +1691,12 @@ int export_table(mbgfe* h)
 	// ---- edges: node slots -> node ids, buckets of ~32 edges on `from`
 	if (n_edges)
 	{
+		// (a sharded partition holds edges whose `from` may belong to another rank: its buckets span the global id range)
+		const uint64_t id_span = h->edges_global && !h->id_begin.empty() ? h->id_begin.back() : n_nodes;
+		const uint32_t id_first = h->edges_global ? 0u : h->id_base;
 		uint32_t eshift = 0;
-		while (eshift < 31 && (n_nodes >> eshift) > std::max<uint64_t>(1, n_edges / 32)) eshift++;
-		const uint32_t n_eb = (uint32_t)(n_nodes >> eshift) + 1;
+		while (eshift < 31 && (id_span >> eshift) > std::max<uint64_t>(1, n_edges / 32)) eshift++;
+		const uint32_t n_eb = (uint32_t)(id_span >> eshift) + 1;
 		if (int rc = ensure(h, h->d_bucket_count, (size_t)n_eb * 4 + 64)) return rc;
 		if (int rc = ensure(h, h->d_bucket_begin, (size_t)(n_eb + 2) * 8)) return rc;
 		if (int rc = ensure(h, h->d_edge_out, (n_edges + 1) * sizeof(EdgeRec))) return rc;
@@ -1703,10 +1706,10 @@ int export_table(mbgfe* h)
 		const unsigned erank_grid = (unsigned)std::min<uint64_t>(((uint64_t)n_eb * 32 + 255) / 256, (uint64_t)h->sm_count * 32);
 		CU(h, cudaMemsetAsync(h->d_bucket_count.p, 0, (size_t)n_eb * 4, h->stream));
 		const NodeSlot* slot_names = h->edges_global ? nullptr : h->d_nodes.as<NodeSlot>();     // sharded table: edge keys already hold global ids
-		MBGFE_LAUNCH(k_edge_bucket_count, egrid, 256, 0, h->stream, h->d_edges.as<EdgeSlot>(), h->edge_slots, slot_names, eshift, h->id_base, h->d_bucket_count.as<uint32_t>());
+		MBGFE_LAUNCH(k_edge_bucket_count, egrid, 256, 0, h->stream, h->d_edges.as<EdgeSlot>(), h->edge_slots, slot_names, eshift, id_first, h->d_bucket_count.as<uint32_t>());
 		if (int rc = device_scan(h, h->d_bucket_count.as<uint32_t>(), h->d_bucket_begin.as<uint64_t>(), n_eb)) return rc;
 		CU(h, cudaMemsetAsync(h->d_bucket_count.p, 0, (size_t)n_eb * 4, h->stream));
-		MBGFE_LAUNCH(k_edge_bucket_scatter, egrid, 256, 0, h->stream, h->d_edges.as<EdgeSlot>(), h->edge_slots, slot_names, eshift, h->id_base,
+		MBGFE_LAUNCH(k_edge_bucket_scatter, egrid, 256, 0, h->stream, h->d_edges.as<EdgeSlot>(), h->edge_slots, slot_names, eshift, id_first,
 			h->d_bucket_begin.as<uint64_t>(), h->d_bucket_count.as<uint32_t>(), h->d_edge_out.as<EdgeRec>());
 		MBGFE_LAUNCH(k_edge_bucket_rank, erank_grid, 256, 0, h->stream, h->d_edge_out.as<EdgeRec>(), h->d_bucket_begin.as<uint64_t>(), n_eb, h->d_edges_sorted.as<EdgeRec>());
 		CU(h, cudaMemcpyAsync(h->p_edges.p, h->d_edges_sorted.p, n_edges * sizeof(mbgfe_edge), cudaMemcpyDeviceToHost, h->stream));
