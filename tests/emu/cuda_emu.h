@@ -6,10 +6,12 @@
 // it is built into tests/emu/libmbgfe_emu.so by tests/emu/Makefile, is never installed next to the product
 // library, and nothing in verkko_b200/ loads it.  The product library has no CPU path.
 //
-// Model: one CTA at a time; every CUDA thread of the CTA is an OS thread; __syncthreads() is a barrier; warp
-// collectives (__shfl_up_sync / __ballot_sync with the full mask) are implemented with CTA-wide barriers, so every
-// thread of the CTA must reach each collective -- which the kernels guarantee.  `__shared__` variables become
-// function-level statics (valid because CTAs run one after another).
+// Model: one CTA at a time; every CUDA thread of the CTA is a FIBER (ucontext) of the launching OS thread, run round-robin and
+// switched only at barriers: __syncthreads() waits for the CTA, warp collectives (__shfl_*_sync / __ballot_sync / __syncwarp
+// with the full mask) for the 32 threads of the warp.  (OS threads with futex barriers, the first form, spent most of the
+// CPU suite in the kernel: a barrier over 256 threads on 8 cores is hundreds of context switches.)  Nothing here may spin on
+// another thread's progress without reaching a barrier -- the kernels do not.  `__shared__` variables become function-level
+// statics (valid because CTAs run one after another).
 #pragma once
 #include <algorithm>
 #include <atomic>
@@ -19,6 +21,9 @@
 #include <cstring>
 #include <functional>
 #include <mutex>
+#include <atomic>
+#include <memory>
+#include <ucontext.h>
 #include <thread>
 #include <vector>
 
@@ -43,20 +48,25 @@ struct dim3 { unsigned x, y, z; dim3(unsigned a = 1, unsigned b = 1, unsigned c 
 
 namespace emu {
 
+void yield();      // to the scheduler: the next fiber of the CTA runs
+
+// generation barrier between fibers of one OS thread: the last arriver opens it, the others yield until it has
 struct Barrier
 {
-	std::mutex m; std::condition_variable cv; unsigned n = 0, waiting = 0; unsigned long gen = 0;
-	void reset(unsigned count) { n = count; waiting = 0; }
+	unsigned count = 0, gen = 0, n = 0;
+	void reset(unsigned c) { n = c; count = 0; }
 	void wait()
 	{
-		std::unique_lock<std::mutex> lk(m);
-		unsigned long g = gen;
-		if (++waiting == n) { waiting = 0; gen++; cv.notify_all(); return; }
-		cv.wait(lk, [&] { return gen != g; });
+		const unsigned g = gen;
+		if (++count == n) { count = 0; gen++; return; }
+		while (gen == g) yield();
 	}
 };
 
 inline Barrier& barrier() { static Barrier b; return b; }
+// one barrier per warp of the CTA: warp collectives synchronise the 32 threads of a warp only (as the hardware does), which is also
+// what keeps the emulator usable -- a barrier over all the OS threads of a 256-thread CTA costs a few hundred context switches
+inline Barrier* warp_barriers() { static Barrier b[32]; return b; }
 inline uint64_t* xchg() { static uint64_t buf[2048]; return buf; }
 inline unsigned char*& dyn_smem() { static unsigned char* p = nullptr; return p; }
 inline std::mutex& big_lock() { static std::mutex m; return m; }
@@ -76,10 +86,10 @@ inline T __shfl_up_sync(unsigned, T v, unsigned d)
 	static_assert(sizeof(T) <= 8, "shuffle of <= 8 bytes");
 	uint64_t raw = 0; memcpy(&raw, &v, sizeof(T));
 	emu::xchg()[threadIdx.x] = raw;
-	emu::barrier().wait();
+	emu::warp_barriers()[threadIdx.x >> 5].wait();
 	unsigned lane = threadIdx.x & 31;
 	uint64_t got = lane >= d ? emu::xchg()[threadIdx.x - d] : raw;
-	emu::barrier().wait();
+	emu::warp_barriers()[threadIdx.x >> 5].wait();
 	T out; memcpy(&out, &got, sizeof(T));
 	return out;
 }
@@ -90,23 +100,23 @@ inline T __shfl_sync(unsigned, T v, unsigned src)
 	static_assert(sizeof(T) <= 8, "shuffle of <= 8 bytes");
 	uint64_t raw = 0; memcpy(&raw, &v, sizeof(T));
 	emu::xchg()[threadIdx.x] = raw;
-	emu::barrier().wait();
+	emu::warp_barriers()[threadIdx.x >> 5].wait();
 	uint64_t got = emu::xchg()[(threadIdx.x & ~31u) + (src & 31)];
-	emu::barrier().wait();
+	emu::warp_barriers()[threadIdx.x >> 5].wait();
 	T out; memcpy(&out, &got, sizeof(T));
 	return out;
 }
 
-inline void __syncwarp(unsigned = 0xffffffffu) { emu::barrier().wait(); }
+inline void __syncwarp(unsigned = 0xffffffffu) { emu::warp_barriers()[threadIdx.x >> 5].wait(); }
 inline unsigned long long __umul64hi(unsigned long long a, unsigned long long b) { return (unsigned long long)(((unsigned __int128)a * b) >> 64); }
 
 inline unsigned __ballot_sync(unsigned, int pred)
 {
 	emu::xchg()[threadIdx.x] = pred ? 1 : 0;
-	emu::barrier().wait();
+	emu::warp_barriers()[threadIdx.x >> 5].wait();
 	unsigned base = threadIdx.x & ~31u, r = 0;
 	for (unsigned i = 0; i < 32 && base + i < blockDim.x; i++) if (emu::xchg()[base + i]) r |= 1u << i;
-	emu::barrier().wait();
+	emu::warp_barriers()[threadIdx.x >> 5].wait();
 	return r;
 }
 
@@ -179,27 +189,60 @@ template <typename F> inline cudaError_t cudaFuncSetAttribute(F, cudaFuncAttribu
 
 namespace emu {
 
+struct Fiber { ucontext_t ctx; bool done = false; };
+struct Sched
+{
+	ucontext_t main_ctx;
+	std::vector<Fiber> fibers;
+	std::function<void()> body;
+	unsigned cur = 0, alive = 0;
+};
+inline Sched*& sched() { static thread_local Sched* s = nullptr; return s; }
+inline std::vector<std::unique_ptr<char[]>>& stacks() { static thread_local std::vector<std::unique_ptr<char[]>> v; return v; }
+constexpr size_t FIBER_STACK = 256 * 1024;
+inline void yield() { Sched* s = sched(); swapcontext(&s->fibers[s->cur].ctx, &s->main_ctx); }
+inline void fiber_entry() { Sched* s = sched(); s->body(); s->fibers[s->cur].done = true; s->alive--; }      // returns to main_ctx (uc_link)
+
 template <typename K, typename... Args>
 void launch(K kernel, dim3 grid, dim3 block, size_t smem_bytes, Args... args)
 {
 	std::vector<unsigned char> smem(smem_bytes + 64);
 	dyn_smem() = smem.data();
-	barrier().reset(block.x);
-	std::vector<std::thread> pool;
-	for (unsigned t = 0; t < block.x; t++)
+	Sched s;
+	Sched* outer = sched();
+	sched() = &s;
+	s.body = [&]() { kernel(args...); };
+	s.fibers.resize(block.x);
+	while (stacks().size() < block.x) stacks().emplace_back(new char[FIBER_STACK]);
+	ucontext_t proto;
+	getcontext(&proto);
+	for (unsigned b = 0; b < grid.x; b++)
 	{
-		pool.emplace_back([=]()
+		barrier().reset(block.x);
+		for (unsigned w = 0; w * 32 < block.x; w++) warp_barriers()[w].reset(std::min(32u, block.x - 32 * w));
+		for (unsigned t = 0; t < block.x; t++)
 		{
-			blockDim = block; gridDim = grid; threadIdx = { t, 0, 0 };
-			for (unsigned b = 0; b < grid.x; b++)
+			Fiber& f = s.fibers[t];
+			f.ctx = proto;
+			f.ctx.uc_stack.ss_sp = stacks()[t].get();
+			f.ctx.uc_stack.ss_size = FIBER_STACK;
+			f.ctx.uc_link = &s.main_ctx;
+			makecontext(&f.ctx, (void (*)())fiber_entry, 0);
+			f.done = false;
+		}
+		s.alive = block.x;
+		while (s.alive)
+		{
+			for (unsigned t = 0; t < block.x; t++)
 			{
-				blockIdx = { b, 0, 0 };
-				kernel(args...);
-				barrier().wait(); // CTAs run one after another: statics standing in for __shared__ are reused
+				if (s.fibers[t].done) continue;
+				s.cur = t;
+				blockDim = block; gridDim = grid; threadIdx = { t, 0, 0 }; blockIdx = { b, 0, 0 };
+				swapcontext(&s.main_ctx, &s.fibers[t].ctx);
 			}
-		});
+		}
 	}
-	for (auto& th : pool) th.join();
+	sched() = outer;
 }
 
 }
