@@ -15,6 +15,23 @@ def test_emulated_kernels_match_oracle(oracle, emu_library, mode, k, w):
     compare_runs(run_frontend(mode, k, w, reads, library=emu_library), oracle.run(mode, k, w, reads), what=f"{mode} k={k} w={w}")
 
 
+# (k, w): every residue of s = k - w + 1 mod 8 (where the incoming characters of K3a's rolled hashes sit inside their 16-code window,
+# odd residues through the 16-bit funnel), windows inside one block of 8 (w <= 8), spanning 2, 3, .. blocks, every r = (w - 1) mod 8
+SELECT_SHAPES = [(31, 1), (33, 2), (35, 3), (37, 4), (39, 5), (41, 6), (43, 7), (45, 8), (63, 9), (65, 10), (67, 12), (99, 16), (101, 17), (127, 24), (201, 31),
+                 (255, 40), (301, 57), (401, 64), (501, 95), (1001, 100), (1001, 128), (1001, 256)]
+
+
+@pytest.mark.parametrize("k,w", SELECT_SHAPES)
+def test_emulated_select_shapes(oracle, emu_library, k, w):
+    """K3a in rolling form over the shapes its index arithmetic distinguishes (s mod 8, a = (w-1) div 8 incl. 0, r = (w-1) mod 8),
+    on reads that end 0..9 codes past a block, with tandem repeats (equal hashes inside a window: ties are kept)"""
+    a = workloads.read_a()
+    reads = [a[:3000 + 7 * i] for i in range(10)] + [workloads.repeat_rich(k + w, 4000), workloads.long_tandem_reads()[0][:6000], a[:k + 40], a[:k], a[:k - 1]]
+    for mode in ("hpc", "collapse-msat"):
+        got = run_frontend(mode, k, w, reads, library=emu_library)
+        compare_runs(got, oracle.run(mode, k, w, reads), what=f"select shape {mode} k={k} w={w} s%8={(k - w + 1) % 8}")
+
+
 def test_emulated_kernels_table_with_coverage(oracle, emu_library):
     reads = workloads.coverage_reads(n_reads=6)
     compare_runs(run_frontend("collapse-msat", 501, 50, reads, library=emu_library), oracle.run("collapse-msat", 501, 50, reads), what="coverage")

@@ -390,3 +390,17 @@ def test_host_packed_upload_pieces(oracle, monkeypatch, pct):
         compare_runs(got, oracle.run(mode, k, w, reads), what=f"host pack {pct}% {mode}")
     big = workloads.coverage_reads(genome_len=400000, n_reads=600, len_min=12000, len_max=20000)
     compare_runs(run_frontend("collapse-msat", 1001, 100, big, piece_bytes=1 << 20), oracle.run("collapse-msat", 1001, 100, big), what=f"host pack {pct}% big")
+
+
+def test_select_shapes_on_gpu(oracle):
+    """K3a (rolling form) over every residue of s mod 8, windows of 1 .. 32 blocks and every r -- the shapes of
+    tests/test_emu_kernels.py::test_emulated_select_shapes on the real library"""
+    from test_emu_kernels import SELECT_SHAPES
+    from fe_helpers import run_frontend
+    from oracle_lib import compare_runs
+    import workloads
+    a = workloads.read_a()
+    for k, w in SELECT_SHAPES:
+        reads = [a[:3000 + 7 * i] for i in range(10)] + [workloads.repeat_rich(k + w, 4000), workloads.long_tandem_reads()[0][:6000], a[:k + 40], a[:k], a[:k - 1]]
+        compare_runs(run_frontend("collapse-msat", k, w, reads), oracle.run("collapse-msat", k, w, reads), what=f"select shape k={k} w={w}")
+
