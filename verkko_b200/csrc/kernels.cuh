@@ -1810,47 +1810,6 @@ __global__ void __launch_bounds__(256) k_insert_nodes(const uint64_t* __restrict
 	}
 }
 
-// records received from other ranks: {key_lo, key_hi, flags, reserved}
-__global__ void __launch_bounds__(256) k_insert_records(const uint64_t* __restrict__ rec, uint64_t n_rec, NodeSlot* __restrict__ table, uint64_t mask,
-	unsigned long long* __restrict__ distinct)
-{
-	const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
-	bool is_new = false;
-	if (i < n_rec) node_insert(table, mask, rec[4 * i], rec[4 * i + 1], 1, (uint32_t)rec[4 * i + 2] & 1u, is_new);
-	warp_count(distinct, is_new);
-}
-
-// re-insert every entry of an old table into a larger one (growth)
-__global__ void __launch_bounds__(256) k_table_rehash(const NodeSlot* __restrict__ old_table, uint64_t old_slots, NodeSlot* __restrict__ table, uint64_t mask)
-{
-	for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < old_slots; i += (uint64_t)gridDim.x * blockDim.x)
-	{
-		NodeSlot s = old_table[i];
-		if (s.key_lo == ~0ull && s.key_hi == ~0ull) continue;
-		bool is_new;
-		node_insert(table, mask, s.key_lo, s.key_hi, s.count, s.flags, is_new);
-	}
-}
-
-__global__ void __launch_bounds__(256) k_lookup_nodes(const uint64_t* __restrict__ inst_hash, uint64_t n_inst, const NodeSlot* __restrict__ table, uint64_t mask,
-	uint32_t* __restrict__ inst_slot)
-{
-	const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
-	if (i >= n_inst) return;
-	uint64_t lo = inst_hash[2 * i], hi = inst_hash[2 * i + 1];
-	uint64_t key_lo, key_hi; uint32_t fw;
-	canonical_key(lo, hi, key_lo, key_hi, fw);
-	uint64_t slot = slot_hash(key_lo, key_hi) & mask;
-	while (true)
-	{
-		const NodeSlot* sp = table + slot;
-		uint64_t cl = sp->key_lo, ch = sp->key_hi;
-		if (cl == key_lo && ch == key_hi) { inst_slot[i] = (uint32_t)slot; return; }
-		if (cl == ~0ull && ch == ~0ull) { inst_slot[i] = 0xffffffffu; return; }
-		slot = (slot + 1) & mask;
-	}
-}
-
 // Edge table: 32-byte slots keyed by the canonical (from, to) pair of (node slot << 1 | fw).
 //   key      : from << 32 | to ; all-ones = empty
 //   ordered  : (global instance index of the later k-mer << 24) | overlap ; atomicMax keeps the LAST observation
@@ -2107,18 +2066,6 @@ __device__ __forceinline__ unsigned long long block_owner_alloc(uint32_t owner, 
 	return owner != NO_OWNER ? base[owner] + local : 0ull;
 }
 
-__global__ void __launch_bounds__(256) k_owner_count(const uint64_t* __restrict__ inst_hash, uint64_t n_inst, uint32_t world, unsigned long long* __restrict__ counts)
-{
-	const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
-	uint32_t owner = NO_OWNER;
-	if (i < n_inst)
-	{
-		const uint64_t lo = inst_hash[2 * i], hi = inst_hash[2 * i + 1];
-		if (lo != hi) { uint64_t key_lo, key_hi; uint32_t fw; canonical_key(lo, hi, key_lo, key_hi, fw); owner = owner_of(key_hi, world); }
-	}
-	block_owner_alloc(owner, counts, world);
-}
-
 __global__ void __launch_bounds__(256) k_owner_pack(const uint64_t* __restrict__ inst_hash, const uint8_t* __restrict__ inst_flag, uint64_t n_inst, uint32_t world,
 	unsigned long long* __restrict__ cursors, uint64_t* __restrict__ records, uint32_t* __restrict__ inst_packpos)
 {
@@ -2138,66 +2085,7 @@ __global__ void __launch_bounds__(256) k_owner_pack(const uint64_t* __restrict__
 	inst_packpos[i] = (uint32_t)o;     // where the owner's answer (the global node id) will come back
 }
 
-// owner side: global node id of every received record, in the order received.  Needs the ranks left in the table by
-// the node export (k_node_bucket_rank); id = id_base (number of nodes owned by lower ranks) + rank.
-__global__ void __launch_bounds__(256) k_record_ids(const uint64_t* __restrict__ rec, uint64_t n_rec, const NodeSlot* __restrict__ table, uint64_t mask, uint32_t id_base,
-	uint32_t* __restrict__ ids)
-{
-	const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
-	if (i >= n_rec) return;
-	const uint64_t key_lo = rec[4 * i], key_hi = rec[4 * i + 1];
-	uint64_t slot = slot_hash(key_lo, key_hi) & mask;
-	while (true)
-	{
-		const NodeSlot* sp = table + slot;
-		if (sp->key_lo == key_lo && sp->key_hi == key_hi) { ids[i] = id_base + (uint32_t)sp->rank; return; }
-		slot = (slot + 1) & mask;      // every received record was inserted, so the probe always ends on its key
-	}
-}
-
-// sender side: edge observations as 16-byte records {canonical (from id, to id) key, (global instance index << 24) |
-// overlap}, sent to the rank that owns `from` (node ids are dealt to ranks in contiguous ranges: id_begin[r] ..
-// id_begin[r+1]), so each rank's sorted edge partition continues the previous one.
-__device__ __forceinline__ bool edge_observation(uint64_t i, uint64_t n_inst, const uint64_t* __restrict__ inst_hash, const uint32_t* __restrict__ inst_pos,
-	const uint8_t* __restrict__ inst_flag, const uint32_t* __restrict__ inst_packpos, const uint32_t* __restrict__ packed_ids, uint64_t inst_base, uint32_t k,
-	unsigned long long& key, unsigned long long& ordered)
-{
-	if (i >= n_inst || i == 0 || (inst_flag[i] & 1)) return false;
-	const uint32_t pa = inst_packpos[i - 1], pb = inst_packpos[i];
-	if (pa == 0xffffffffu || pb == 0xffffffffu) return false;
-	key = canonical_edge_key(inst_hash[2 * (i - 1)], inst_hash[2 * (i - 1) + 1], inst_hash[2 * i], inst_hash[2 * i + 1], packed_ids[pa], packed_ids[pb]);
-	ordered = ((unsigned long long)(inst_base + i) << 24) | (inst_pos[i - 1] + k - inst_pos[i]);
-	return true;
-}
-
-__device__ __forceinline__ uint32_t id_owner(uint32_t id, const uint64_t* __restrict__ id_begin, uint32_t world)
-{
-	uint32_t r = 0;
-	while (r + 1 < world && (uint64_t)id >= id_begin[r + 1]) r++;
-	return r;
-}
-
-__global__ void __launch_bounds__(256) k_edge_owner_count(const uint64_t* __restrict__ inst_hash, const uint32_t* __restrict__ inst_pos, const uint8_t* __restrict__ inst_flag,
-	const uint32_t* __restrict__ inst_packpos, const uint32_t* __restrict__ packed_ids, uint64_t n_inst, uint64_t inst_base, uint32_t k, const uint64_t* __restrict__ id_begin,
-	uint32_t world, unsigned long long* __restrict__ counts)
-{
-	const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
-	unsigned long long key, ordered;
-	const bool have = edge_observation(i, n_inst, inst_hash, inst_pos, inst_flag, inst_packpos, packed_ids, inst_base, k, key, ordered);
-	block_owner_alloc(have ? id_owner((uint32_t)(key >> 33), id_begin, world) : NO_OWNER, counts, world);
-}
-
-__global__ void __launch_bounds__(256) k_edge_owner_pack(const uint64_t* __restrict__ inst_hash, const uint32_t* __restrict__ inst_pos, const uint8_t* __restrict__ inst_flag,
-	const uint32_t* __restrict__ inst_packpos, const uint32_t* __restrict__ packed_ids, uint64_t n_inst, uint64_t inst_base, uint32_t k, const uint64_t* __restrict__ id_begin,
-	uint32_t world, unsigned long long* __restrict__ cursors, unsigned long long* __restrict__ records)
-{
-	const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
-	unsigned long long key, ordered;
-	const bool have = edge_observation(i, n_inst, inst_hash, inst_pos, inst_flag, inst_packpos, packed_ids, inst_base, k, key, ordered);
-	const unsigned long long o = block_owner_alloc(have ? id_owner((uint32_t)(key >> 33), id_begin, world) : NO_OWNER, cursors, world);
-	if (have) { ulonglong2 r; r.x = key; r.y = ordered; *(ulonglong2*)(records + 2 * o) = r; }
-}
-
+// owner side: edge records {canonical (from id, to id) key, (global instance index << 24) | overlap} into this rank's edge partition
 __global__ void __launch_bounds__(256) k_insert_edge_records(const unsigned long long* __restrict__ rec, uint64_t n_rec, EdgeSlot* __restrict__ table, uint64_t mask,
 	unsigned long long* __restrict__ distinct)
 {
