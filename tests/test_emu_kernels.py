@@ -37,6 +37,40 @@ def test_emulated_kernels_table_with_coverage(oracle, emu_library):
     compare_runs(run_frontend("collapse-msat", 501, 50, reads, library=emu_library), oracle.run("collapse-msat", 501, 50, reads), what="coverage")
 
 
+def test_emulated_tables_sized_from_a_sketch(oracle, emu_library, monkeypatch):
+    """the exact tail sizes the node and edge tables from a distinct-count sketch of the hashes (two slots per expected distinct
+    key instead of two per instance); an estimate that comes out far too low is mended by doubling the overflowed tables"""
+    reads = workloads.coverage_reads(n_reads=30, genome_len=20000)          # ~15x coverage: far fewer distinct k-mers than instances
+    want = oracle.run("collapse-msat", 301, 30, reads)
+    from verkko_b200.frontend import MbgFrontEnd
+
+    def run():      # upload + process: the exact tail (mbgfe_run sizes its tables from the first piece, before it can know)
+        fe = MbgFrontEnd(301, 30, "collapse-msat", library=emu_library)
+        try:
+            fe.add_reads(*workloads.as_pair(reads))
+            fe.upload()
+            fe.process()
+            return dict(node_hash=fe.node_hashes(), node_cov=fe.node_coverage(), node_tip=fe.node_tip(), edges=fe.edges(), stats=fe.stats())
+        finally:
+            fe.close()
+
+    def same(got):
+        return all(np.array_equal(got[f], want[f]) for f in ("node_hash", "node_cov", "node_tip", "edges"))
+
+    monkeypatch.setenv("MBGFE_NO_SKETCH", "1")
+    plain = run()
+    monkeypatch.delenv("MBGFE_NO_SKETCH")
+    monkeypatch.setenv("MBGFE_SKETCH_MIN", "0")
+    got = run()
+    assert same(plain) and same(got)
+    assert got["stats"]["table_slots"] < plain["stats"]["table_slots"], (got["stats"]["table_slots"], plain["stats"]["table_slots"])
+    assert got["stats"]["table_slots"] >= 2 * len(want.node_hash)
+    monkeypatch.setenv("MBGFE_SKETCH_DIV", "16")
+    low = run()
+    assert same(low)
+    assert low["stats"]["table_grows"] >= 1 and low["stats"]["table_slots"] >= len(want.node_hash)
+
+
 def test_emulated_palindrome_rule(oracle, emu_library):
     """droppable palindromes vanish like in the reference; a non-droppable one is an error in both"""
     from verkko_b200 import MbgfeError

@@ -1781,6 +1781,54 @@ __global__ void __launch_bounds__(256) k_table_clear(NodeSlot* __restrict__ tabl
 	}
 }
 
+// How many DISTINCT k-mers and edges are about to be inserted, before the tables are sized (linear counting: every key sets one bit of
+// a bitmap with at least as many bits as there are keys; distinct ~ -M ln(1 - ones / M)).  Sizing the tables from the number of
+// INSTANCES gives a table 2 x coverage too large, and every slot of it is filled, scanned twice by the ranking and twice by the
+// export: at 30x coverage that is most of the memory traffic of the step after K3b.
+__device__ __forceinline__ void sketch_set(uint32_t* __restrict__ bitmap, uint64_t mask, uint64_t h)
+{
+	const uint64_t bit = (h ^ (h >> 29)) & mask;
+	atomicOr(bitmap + (bit >> 5), 1u << (bit & 31));
+}
+
+// instances [0, n): nodes into bitmap, edge observations (unordered pair of the two canonical k-mers) into edge_bitmap
+__global__ void __launch_bounds__(256) k_sketch_instances(const uint64_t* __restrict__ inst_hash, const uint8_t* __restrict__ inst_flag, uint64_t n_inst,
+	uint32_t* __restrict__ bitmap, uint32_t* __restrict__ edge_bitmap, uint64_t mask)
+{
+	for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n_inst; i += (uint64_t)gridDim.x * blockDim.x)
+	{
+		const uint64_t lo = inst_hash[2 * i], hi = inst_hash[2 * i + 1];
+		uint64_t k_lo, k_hi; uint32_t fw;
+		canonical_key(lo, hi, k_lo, k_hi, fw);
+		const uint64_t a = slot_hash(k_lo, k_hi);
+		sketch_set(bitmap, mask, a);
+		if (edge_bitmap && i > 0 && !(inst_flag[i] & 1))
+		{
+			uint64_t p_lo, p_hi;
+			canonical_key(inst_hash[2 * (i - 1)], inst_hash[2 * (i - 1) + 1], p_lo, p_hi, fw);
+			const uint64_t b = slot_hash(p_lo, p_hi);
+			sketch_set(edge_bitmap, mask, (a + b) * 0x9e3779b97f4a7c15ull ^ (a ^ b));      // symmetric in the two k-mers
+		}
+	}
+}
+
+// records of `stride` 64-bit words whose first one (narrow) or two (wide) words are the key
+__global__ void __launch_bounds__(256) k_sketch_records(const uint64_t* __restrict__ rec, uint64_t n_rec, uint32_t stride, uint32_t wide, uint32_t* __restrict__ bitmap, uint64_t mask)
+{
+	for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n_rec; i += (uint64_t)gridDim.x * blockDim.x)
+	{
+		const uint64_t a = rec[(uint64_t)stride * i], b = wide ? rec[(uint64_t)stride * i + 1] : (a >> 17);
+		sketch_set(bitmap, mask, slot_hash(a, b));
+	}
+}
+
+__global__ void __launch_bounds__(256) k_sketch_count(const uint32_t* __restrict__ bitmap, uint64_t n_words, unsigned long long* __restrict__ ones)
+{
+	uint32_t c = 0;
+	for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n_words; i += (uint64_t)gridDim.x * blockDim.x) c += __popc(bitmap[i]);
+	if (c) atomicAdd(ones, (unsigned long long)c);
+}
+
 // K4a: count k-mers.  One thread per instance of [*range_begin, *range_end): canonical key, probe, 128-bit CAS claim,
 // atomic add / or (HashList::addNode + setTipKmer, MBG/HashList.cpp:120-149,23-26).
 // Algorithmic bytes: 16 read per instance + one 32-byte slot read and written (random access: sector-bound).

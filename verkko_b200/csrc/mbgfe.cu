@@ -6,6 +6,7 @@
 // The compute path is CUDA only (kernels.cuh).  There is no host implementation of any stage in this file: the host
 // parses files, builds the (tiny) segment table, sequences kernels and orders the exported table.
 #include <algorithm>
+#include <cmath>
 #include <cstdarg>
 #include <cstdio>
 #include <cstring>
@@ -82,6 +83,7 @@ struct mbgfe
 
 	// code tables
 	DevBuf tab_hash, tab_pair, tab_comp, tab_pext8, tab_in, tab_out;
+	DevBuf d_sketch;                                                // distinct-count bitmaps (size_tables)
 
 	// pending input
 	std::vector<HostChunk> pending;
@@ -515,7 +517,7 @@ int mbgfe_create(const mbgfe_params* prm, mbgfe** out)
 void mbgfe_destroy(mbgfe* h)
 {
 	if (!h) return;
-	for (DevBuf* b : { &h->tab_hash, &h->tab_pair, &h->tab_comp, &h->tab_pext8, &h->tab_in, &h->tab_out, &h->d_ascii, &h->d_packed, &h->d_nonacgt, &h->d_counters, &h->d_seg_in, &h->d_seg_out,
+	for (DevBuf* b : { &h->tab_hash, &h->tab_pair, &h->tab_comp, &h->tab_pext8, &h->tab_in, &h->tab_out, &h->d_sketch, &h->d_ascii, &h->d_packed, &h->d_nonacgt, &h->d_counters, &h->d_seg_in, &h->d_seg_out,
 		&h->d_seg_len, &h->d_seg_c1, &h->d_seg_c2, &h->d_seg_nsel, &h->d_sel_begin, &h->d_sym, &h->d_codes, &h->d_selmask, &h->d_pos1, &h->d_pos2,
 		&h->d_inst_pos, &h->d_inst_seg, &h->d_inst_flag, &h->d_inst_hash, &h->d_inst_slot, &h->d_pal_list, &h->d_nodes, &h->d_edges, &h->d_node_out,
 		&h->d_edge_out, &h->d_records, &h->d_recv, &h->d_bucket_count, &h->d_bucket_begin, &h->d_scan_tot, &h->d_scan_off, &h->d_node_hash_sorted, &h->d_node_cov,
@@ -794,23 +796,84 @@ int ensure_instances(mbgfe* h, uint64_t cap)
 	return 0;
 }
 
-// empty node (and edge) tables of `slots` slots
-int clear_tables(mbgfe* h, uint64_t slots, uint32_t& launches)
+// empty node and edge tables of that many slots (powers of two)
+int clear_tables(mbgfe* h, uint64_t node_slots, uint64_t edge_slots, uint32_t& launches)
 {
-	if (slots >= (1ull << 31)) return fail(h, MBGFE_E_LIMIT, "node table would need %llu slots (limit 2^31 per GPU)", (unsigned long long)slots);
-	if (int rc = ensure(h, h->d_nodes, slots * sizeof(NodeSlot))) return rc;
-	h->node_slots = slots;
-	const unsigned clear_grid = (unsigned)std::min<uint64_t>((slots + 255) / 256, (uint64_t)h->sm_count * 8);
-	MBGFE_LAUNCH(k_table_clear, clear_grid, 256, 0, h->stream, h->d_nodes.as<NodeSlot>(), slots);
+	if (node_slots >= (1ull << 31) || edge_slots >= (1ull << 31))
+		return fail(h, MBGFE_E_LIMIT, "the tables would need %llu / %llu slots (limit 2^31 per GPU)", (unsigned long long)node_slots, (unsigned long long)edge_slots);
+	if (int rc = ensure(h, h->d_nodes, node_slots * sizeof(NodeSlot))) return rc;
+	h->node_slots = node_slots;
+	MBGFE_LAUNCH(k_table_clear, (unsigned)std::min<uint64_t>((node_slots + 255) / 256, (uint64_t)h->sm_count * 8), 256, 0, h->stream, h->d_nodes.as<NodeSlot>(), node_slots);
 	launches++;
 	if (!(h->prm.flags & MBGFE_NO_EDGES))
 	{
-		if (int rc = ensure(h, h->d_edges, slots * sizeof(EdgeSlot))) return rc;
-		h->edge_slots = slots;
-		MBGFE_LAUNCH(k_edge_clear, clear_grid, 256, 0, h->stream, h->d_edges.as<EdgeSlot>(), slots);
+		if (int rc = ensure(h, h->d_edges, edge_slots * sizeof(EdgeSlot))) return rc;
+		h->edge_slots = edge_slots;
+		MBGFE_LAUNCH(k_edge_clear, (unsigned)std::min<uint64_t>((edge_slots + 255) / 256, (uint64_t)h->sm_count * 8), 256, 0, h->stream, h->d_edges.as<EdgeSlot>(), edge_slots);
 		launches++;
 	}
 	else h->edge_slots = 0;
+	return 0;
+}
+
+// distinct keys behind `ones` set bits of an M-bit linear-counting bitmap, with a little head room
+uint64_t sketch_estimate(uint64_t ones, uint64_t M)
+{
+	if (ones >= M) return 8 * M;
+	return (uint64_t)(-(double)M * std::log(1.0 - (double)ones / (double)M) * 1.03) + 256;
+}
+
+// runs a sketch launch `fill` (or two: nodes and edges) over a fresh bitmap pair of M bits each and returns the two estimates
+template <typename Fill>
+int run_sketch(mbgfe* h, uint64_t n_keys, bool second, uint64_t est[2], uint32_t& launches, Fill fill)
+{
+	const uint64_t M = std::max<uint64_t>(next_pow2(n_keys), 1 << 16), words = M / 32;
+	if (int rc = ensure(h, h->d_sketch, 256 + 2 * words * 4)) return rc;
+	CU(h, cudaMemsetAsync(h->d_sketch.p, 0, 256 + (second ? 2 : 1) * words * 4, h->stream));
+	uint32_t* bm0 = (uint32_t*)(h->d_sketch.as<char>() + 256);
+	uint32_t* bm1 = second ? bm0 + words : (uint32_t*)nullptr;
+	fill(bm0, bm1, M - 1);
+	unsigned long long* ones = h->d_sketch.as<unsigned long long>();
+	const unsigned grid = (unsigned)std::min<uint64_t>((words + 255) / 256, (uint64_t)h->sm_count * 8);
+	MBGFE_LAUNCH(k_sketch_count, grid, 256, 0, h->stream, bm0, words, ones);
+	if (second) MBGFE_LAUNCH(k_sketch_count, grid, 256, 0, h->stream, bm1, words, ones + 1);
+	launches += second ? 3 : 2;
+	unsigned long long got[2] = { 0, 0 };
+	CU(h, cudaMemcpyAsync(got, ones, 16, cudaMemcpyDeviceToHost, h->stream));
+	CU(h, cudaStreamSynchronize(h->stream));
+	h->stats.d2h_bytes += 16;
+	est[0] = sketch_estimate(got[0], M); est[1] = second ? sketch_estimate(got[1], M) : 0;
+	return 0;
+}
+
+// (experiments and tests: MBGFE_NO_SKETCH = size from the instances as round 1 did; MBGFE_SKETCH_MIN = smallest input that is sketched)
+bool sketch_wanted(uint64_t n_keys)
+{
+	// Default: only inputs whose tables would be a matter of capacity.  Measured on the chr20 bench (15.6 M instances, 7.6 M distinct k-mers,
+	// coverage 2): the sketch halves both tables but costs 0.5 ms itself and the fuller node table probes longer -- 17.2 -> 17.8 ms.  At 30x
+	// coverage the tables shrink 8x or more, and two slots per instance stop fitting next to the instances of a whole genome.
+	const char* min_env = getenv("MBGFE_SKETCH_MIN");
+	return n_keys > 0 && !getenv("MBGFE_NO_SKETCH") && n_keys >= (min_env ? (uint64_t)atoll(min_env) : (1ull << 26));
+}
+
+// Table sizes for the resident instances: two slots per DISTINCT k-mer / edge expected (a sketch of the hashes, k_sketch_instances),
+// never more than two per instance, never less than the caller asked for.  full = what the number of instances alone would give.
+int size_tables(mbgfe* h, uint64_t n_inst, uint64_t* node_slots, uint64_t* edge_slots, uint64_t* full_out, uint32_t& launches)
+{
+	const uint64_t floor_slots = h->prm.table_slots ? next_pow2(h->prm.table_slots) : 0;
+	const uint64_t full = std::max<uint64_t>(next_pow2(std::max<uint64_t>(2 * n_inst, 1024)), floor_slots);
+	*node_slots = full; *edge_slots = full; *full_out = full;
+	if (!sketch_wanted(n_inst)) return 0;
+	const bool edges = !(h->prm.flags & MBGFE_NO_EDGES);
+	uint64_t est[2];
+	if (int rc = run_sketch(h, n_inst, edges, est, launches, [&](uint32_t* bm0, uint32_t* bm1, uint64_t mask)
+	{
+		MBGFE_LAUNCH(k_sketch_instances, (unsigned)std::min<uint64_t>((n_inst + 255) / 256, (uint64_t)h->sm_count * 16), 256, 0, h->stream, h->d_inst_hash.as<uint64_t>(),
+			h->d_inst_flag.as<uint8_t>(), n_inst, bm0, bm1, mask);
+	})) return rc;
+	if (const char* d = getenv("MBGFE_SKETCH_DIV")) { const uint64_t by = std::max(1, atoi(d)); est[0] /= by; est[1] /= by; }      // tests: an estimate that is too low
+	*node_slots = std::min(full, std::max<uint64_t>(next_pow2(std::max<uint64_t>(2 * est[0], 1024)), floor_slots));
+	if (edges) *edge_slots = std::min(full, std::max<uint64_t>(next_pow2(std::max<uint64_t>(2 * est[1], 1024)), floor_slots));
 	return 0;
 }
 
@@ -951,18 +1014,27 @@ int process_tail(mbgfe* h, uint32_t launches)
 	if (n_inst) launch_variants(h, 0, n_seg, n_inst, launches);
 	if (!(h->prm.flags & MBGFE_NO_TABLE) && !h->appending)
 	{
-		const uint64_t slots = std::max<uint64_t>(next_pow2(std::max<uint64_t>(2 * n_inst, 1024)), h->prm.table_slots ? next_pow2(h->prm.table_slots) : 0);
-		if (int rc = clear_tables(h, slots, launches)) return rc;
-		launch_tables(h, 0, n_seg, n_inst, launches, true);
-		unsigned long long five[5] = { 0, 0, 0, 0, 0 };      // CTR_DISTINCT, CTR_EDGES, cursor x2, CTR_OVERFLOW
-		CU(h, cudaMemcpyAsync(five, ctr + CTR_DISTINCT, sizeof(five), cudaMemcpyDeviceToHost, h->stream));
-		CU(h, cudaStreamSynchronize(h->stream));
-		h->stats.d2h_bytes += sizeof(five);
-		// the probe limit (MAX_PROBES) gave up on some k-mer or edge: the result would silently miss it
-		if (five[CTR_OVERFLOW - CTR_DISTINCT]) return fail(h, MBGFE_E_LIMIT, "k-mer table of %llu slots overflowed (%llu inserts gave up); pass a larger mbgfe_params.table_slots",
-			(unsigned long long)slots, five[CTR_OVERFLOW - CTR_DISTINCT]);
-		h->stats.distinct = five[0]; h->stats.distinct_edges = five[1];
-		h->stats.table_slots = slots;
+		uint64_t node_slots, edge_slots, full;
+		if (int rc = size_tables(h, n_inst, &node_slots, &edge_slots, &full, launches)) return rc;
+		for (int attempt = 0; ; attempt++)
+		{
+			if (int rc = clear_tables(h, node_slots, edge_slots, launches)) return rc;
+			launch_tables(h, 0, n_seg, n_inst, launches, true);
+			unsigned long long five[5] = { 0, 0, 0, 0, 0 };      // CTR_DISTINCT, CTR_EDGES, cursor x2, CTR_OVERFLOW
+			CU(h, cudaMemcpyAsync(five, ctr + CTR_DISTINCT, sizeof(five), cudaMemcpyDeviceToHost, h->stream));
+			CU(h, cudaStreamSynchronize(h->stream));
+			h->stats.d2h_bytes += sizeof(five);
+			h->stats.distinct = five[0]; h->stats.distinct_edges = five[1];
+			if (!five[CTR_OVERFLOW - CTR_DISTINCT]) break;
+			// the probe limit (MAX_PROBES) gave up on some k-mer or edge: the result would silently miss it.  A sketch that came out low is
+			// mended by doubling; tables already at their full size cannot be.
+			if ((node_slots >= full && edge_slots >= full) || attempt == 4) return fail(h, MBGFE_E_LIMIT, "k-mer table of %llu slots overflowed (%llu inserts gave up); pass a larger mbgfe_params.table_slots",
+				(unsigned long long)node_slots, five[CTR_OVERFLOW - CTR_DISTINCT]);
+			node_slots = std::min(full, 2 * node_slots); edge_slots = std::min(full, 2 * edge_slots);
+			h->stats.table_grows++;
+			CU(h, cudaMemsetAsync(ctr + CTR_DISTINCT, 0, (CTR_OVERFLOW - CTR_DISTINCT + 1) * 8, h->stream));
+		}
+		h->stats.table_slots = node_slots;
 		h->have_table = true;
 	}
 	else { tick(h, 8); tick(h, 9); CU(h, cudaStreamSynchronize(h->stream)); }
@@ -1165,7 +1237,7 @@ int mbgfe_run(mbgfe* h)
 			if (want_table)
 			{
 				const uint64_t slots = std::max<uint64_t>(next_pow2(std::max<uint64_t>(2 * est, 1024)), h->prm.table_slots ? next_pow2(h->prm.table_slots) : 0);
-				if (int rc = clear_tables(h, slots, launches)) return rc;
+				if (int rc = clear_tables(h, slots, slots, launches)) return rc;
 				h->stats.table_slots = slots;
 			}
 			sized = true;
@@ -1483,7 +1555,7 @@ int run_files(mbgfe* h)
 			if (want_table)
 			{
 				const uint64_t slots = std::max<uint64_t>(next_pow2(std::max<uint64_t>(2 * est, 1024)), h->prm.table_slots ? next_pow2(h->prm.table_slots) : 0);
-				if (int rc = clear_tables(h, slots, launches)) return rc;
+				if (int rc = clear_tables(h, slots, slots, launches)) return rc;
 				h->stats.table_slots = slots;
 			}
 			sized = true;
@@ -1524,7 +1596,7 @@ int run_files(mbgfe* h)
 		h->stats.table_grows += (c8[CTR_OVERFLOW] || n_inst > h->inst_cap) ? 1 : 0;
 		return process_tail(h, launches);
 	}
-	if (!n_seg) { if (int rc = ensure_instances(h, std::max<uint64_t>(4096, h->inst_cap))) return rc; if (want_table) { if (int rc = clear_tables(h, 1024, launches)) return rc; h->stats.table_slots = 1024; CU(h, cudaStreamSynchronize(h->stream)); } }
+	if (!n_seg) { if (int rc = ensure_instances(h, std::max<uint64_t>(4096, h->inst_cap))) return rc; if (want_table) { if (int rc = clear_tables(h, 1024, 1024, launches)) return rc; h->stats.table_slots = 1024; CU(h, cudaStreamSynchronize(h->stream)); } }
 	h->n_inst = n_inst;
 	h->stats.distinct = want_table ? c8[CTR_DISTINCT] : 0;
 	h->stats.distinct_edges = (want_table && h->edge_slots) ? c8[CTR_EDGES] : 0;
@@ -2487,7 +2559,18 @@ int exchange_run(std::vector<mbgfe*>& hs)
 		mbgfe* h = hs[x];
 		CU(h, on(h));
 		unsigned long long* ctr = h->d_counters.as<unsigned long long>();
-		const uint64_t slots = std::max<uint64_t>(next_pow2(std::max<uint64_t>(2 * n_recv[x], 1024)), h->prm.table_slots ? next_pow2(h->prm.table_slots) : 0);
+		const uint64_t floor_slots = h->prm.table_slots ? next_pow2(h->prm.table_slots) : 0;
+		uint64_t slots = std::max<uint64_t>(next_pow2(std::max<uint64_t>(2 * n_recv[x], 1024)), floor_slots);
+		if (sketch_wanted(n_recv[x]))
+		{
+			// two slots per DISTINCT k-mer this rank received, not two per record (size_tables)
+			uint64_t est[2]; uint32_t dummy = 0;
+			if (int rc = run_sketch(h, n_recv[x], false, est, dummy, [&](uint32_t* bm0, uint32_t*, uint64_t mask)
+			{
+				MBGFE_LAUNCH(k_sketch_records, (unsigned)std::min<uint64_t>((n_recv[x] + 255) / 256, (uint64_t)h->sm_count * 16), 256, 0, h->stream, h->d_recv.as<uint64_t>(), n_recv[x], 4u, 1u, bm0, mask);
+			})) return rc;
+			slots = std::min(slots, std::max<uint64_t>(next_pow2(std::max<uint64_t>(2 * est[0], 1024)), floor_slots));
+		}
 		if (slots >= (1ull << 31)) return fail(h, MBGFE_E_LIMIT, "node table would need %llu slots (limit 2^31 per GPU)", (unsigned long long)slots);
 		if (int rc = ensure(h, h->d_nodes, slots * sizeof(NodeSlot))) return rc;
 		if (int rc = ensure(h, h->d_rec_slot, (n_recv[x] + 1) * 4)) return rc;
@@ -2560,7 +2643,16 @@ int exchange_run(std::vector<mbgfe*>& hs)
 			mbgfe* h = hs[x];
 			CU(h, on(h));
 			unsigned long long* ctr = h->d_counters.as<unsigned long long>();
-			const uint64_t slots = next_pow2(std::max<uint64_t>(2 * e_recv[x], 1024));
+			uint64_t slots = next_pow2(std::max<uint64_t>(2 * e_recv[x], 1024));
+			if (sketch_wanted(e_recv[x]))
+			{
+				uint64_t est[2]; uint32_t dummy = 0;
+				if (int rc = run_sketch(h, e_recv[x], false, est, dummy, [&](uint32_t* bm0, uint32_t*, uint64_t mask)
+				{
+					MBGFE_LAUNCH(k_sketch_records, (unsigned)std::min<uint64_t>((e_recv[x] + 255) / 256, (uint64_t)h->sm_count * 16), 256, 0, h->stream, h->d_xbuf[1].as<uint64_t>(), e_recv[x], 2u, 0u, bm0, mask);
+				})) return rc;
+				slots = std::min(slots, next_pow2(std::max<uint64_t>(2 * est[0], 1024)));
+			}
 			if (slots >= (1ull << 31)) return fail(h, MBGFE_E_LIMIT, "edge table would need %llu slots (limit 2^31 per GPU)", (unsigned long long)slots);
 			if (int rc = ensure(h, h->d_edges, slots * sizeof(EdgeSlot))) return rc;
 			h->edge_slots = slots;
@@ -2696,37 +2788,44 @@ int mbgfe_build_table(mbgfe* h)
 	uint32_t launches = 0;
 	unsigned long long* ctr = h->d_counters.as<unsigned long long>();
 	const uint64_t n_inst = h->n_inst;
-	const uint64_t slots = std::max<uint64_t>(next_pow2(std::max<uint64_t>(2 * n_inst, 1024)), h->prm.table_slots ? next_pow2(h->prm.table_slots) : 0);
 	if (int rc = ensure(h, h->d_range, 64)) return rc;
 	const uint64_t range[2] = { 0, n_inst };
 	CU(h, cudaMemcpyAsync(h->d_range.p, range, 16, cudaMemcpyHostToDevice, h->stream));
-	CU(h, cudaMemsetAsync(ctr + CTR_DISTINCT, 0, 16, h->stream));
-	CU(h, cudaMemsetAsync(ctr + CTR_OVERFLOW, 0, 8, h->stream));
 	if (int rc = ensure(h, h->d_inst_slot, (n_inst + 1) * 4 + 64)) return rc;
 	tick(h, 7);
-	if (int rc = clear_tables(h, slots, launches)) return rc;
+	uint64_t node_slots, edge_slots, full;
+	if (int rc = size_tables(h, n_inst, &node_slots, &edge_slots, &full, launches)) return rc;
 	const unsigned grid = (unsigned)std::max<uint64_t>(1, (n_inst + 255) / 256);
 	const uint64_t* rg = h->d_range.as<uint64_t>();
-	if (n_inst)
+	for (int attempt = 0; ; attempt++)
 	{
-		MBGFE_LAUNCH(k_insert_nodes, grid, 256, 0, h->stream, h->d_inst_hash.as<uint64_t>(), h->d_inst_flag.as<uint8_t>(), rg, rg + 1, h->inst_cap, h->d_nodes.as<NodeSlot>(),
-			h->node_slots - 1, h->d_inst_slot.as<uint32_t>(), ctr + CTR_DISTINCT, ctr + CTR_OVERFLOW);
-		launches++;
+		CU(h, cudaMemsetAsync(ctr + CTR_DISTINCT, 0, (CTR_OVERFLOW - CTR_DISTINCT + 1) * 8, h->stream));
+		if (int rc = clear_tables(h, node_slots, edge_slots, launches)) return rc;
+		if (n_inst)
+		{
+			MBGFE_LAUNCH(k_insert_nodes, grid, 256, 0, h->stream, h->d_inst_hash.as<uint64_t>(), h->d_inst_flag.as<uint8_t>(), rg, rg + 1, h->inst_cap, h->d_nodes.as<NodeSlot>(),
+				h->node_slots - 1, h->d_inst_slot.as<uint32_t>(), ctr + CTR_DISTINCT, ctr + CTR_OVERFLOW);
+			launches++;
+		}
+		tick(h, 8);
+		if (n_inst && !(h->prm.flags & MBGFE_NO_EDGES))
+		{
+			MBGFE_LAUNCH(k_insert_edges, grid, 256, 0, h->stream, h->d_inst_hash.as<uint64_t>(), h->d_inst_pos.as<uint32_t>(), h->d_inst_flag.as<uint8_t>(), h->d_inst_slot.as<uint32_t>(),
+				rg, rg + 1, h->inst_cap, h->d_edges.as<EdgeSlot>(), h->edge_slots - 1, ctr + CTR_EDGES, ctr + CTR_OVERFLOW, h->prm.k);
+			launches++;
+		}
+		tick(h, 9);
+		unsigned long long five[5] = { 0, 0, 0, 0, 0 };
+		CU(h, cudaMemcpyAsync(five, ctr + CTR_DISTINCT, sizeof(five), cudaMemcpyDeviceToHost, h->stream));
+		CU(h, cudaStreamSynchronize(h->stream));
+		CU(h, cudaGetLastError());
+		h->stats.distinct = five[0]; h->stats.distinct_edges = five[1];
+		if (!five[CTR_OVERFLOW - CTR_DISTINCT]) break;
+		if ((node_slots >= full && edge_slots >= full) || attempt == 4) return fail(h, MBGFE_E_LIMIT, "k-mer table of %llu slots overflowed", (unsigned long long)node_slots);
+		node_slots = std::min(full, 2 * node_slots); edge_slots = std::min(full, 2 * edge_slots);
+		h->stats.table_grows++;
 	}
-	tick(h, 8);
-	if (n_inst && !(h->prm.flags & MBGFE_NO_EDGES))
-	{
-		MBGFE_LAUNCH(k_insert_edges, grid, 256, 0, h->stream, h->d_inst_hash.as<uint64_t>(), h->d_inst_pos.as<uint32_t>(), h->d_inst_flag.as<uint8_t>(), h->d_inst_slot.as<uint32_t>(),
-			rg, rg + 1, h->inst_cap, h->d_edges.as<EdgeSlot>(), h->edge_slots - 1, ctr + CTR_EDGES, ctr + CTR_OVERFLOW, h->prm.k);
-		launches++;
-	}
-	tick(h, 9);
-	unsigned long long five[5] = { 0, 0, 0, 0, 0 };
-	CU(h, cudaMemcpyAsync(five, ctr + CTR_DISTINCT, sizeof(five), cudaMemcpyDeviceToHost, h->stream));
-	CU(h, cudaStreamSynchronize(h->stream));
-	CU(h, cudaGetLastError());
-	if (five[CTR_OVERFLOW - CTR_DISTINCT]) return fail(h, MBGFE_E_LIMIT, "k-mer table of %llu slots overflowed", (unsigned long long)slots);
-	h->stats.distinct = five[0]; h->stats.distinct_edges = five[1]; h->stats.table_slots = slots;
+	h->stats.table_slots = node_slots;
 	h->stats.ms_nodes = elapsed(h, 7, 8); h->stats.ms_edges = elapsed(h, 8, 9);
 	h->stats.launches = launches;
 	h->have_table = true; h->exported_table = false; h->nodes_ranked = false; h->edges_global = false; h->table_sharded = false; h->id_base = 0;
