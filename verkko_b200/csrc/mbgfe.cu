@@ -849,11 +849,13 @@ int run_sketch(mbgfe* h, uint64_t n_keys, bool second, uint64_t est[2], uint32_t
 // (experiments and tests: MBGFE_NO_SKETCH = size from the instances as round 1 did; MBGFE_SKETCH_MIN = smallest input that is sketched)
 bool sketch_wanted(uint64_t n_keys)
 {
-	// Default: only inputs whose tables would be a matter of capacity.  Measured on the chr20 bench (15.6 M instances, 7.6 M distinct k-mers,
-	// coverage 2): the sketch halves both tables but costs 0.5 ms itself and the fuller node table probes longer -- 17.2 -> 17.8 ms.  At 30x
-	// coverage the tables shrink 8x or more, and two slots per instance stop fitting next to the instances of a whole genome.
+	// Off unless MBGFE_SKETCH_MIN says from how many keys on.  Measured: chr20 bench (15.6 M instances, 7.6 M distinct k-mers) -- the sketch
+	// halves both tables but costs 0.5 ms itself and the fuller node table probes longer, 17.2 -> 17.8 ms; HG002-shaped quarter genome on 2
+	// GPUs (189 M records per GPU, 92 M distinct: at k = 1001 most k-mers of reads with 0.1 % errors hold an error and are unique) --
+	// exchange 84.1 -> 85.7 ms.  It pays in memory only (the two tables of a rank of the full HG002 run: 34 GB -> 17 GB), and in time only
+	// where k-mers repeat 4x or more.
 	const char* min_env = getenv("MBGFE_SKETCH_MIN");
-	return n_keys > 0 && !getenv("MBGFE_NO_SKETCH") && n_keys >= (min_env ? (uint64_t)atoll(min_env) : (1ull << 26));
+	return n_keys > 0 && min_env && !getenv("MBGFE_NO_SKETCH") && n_keys >= (uint64_t)atoll(min_env);
 }
 
 // Table sizes for the resident instances: two slots per DISTINCT k-mer / edge expected (a sketch of the hashes, k_sketch_instances),
