@@ -582,7 +582,7 @@ __global__ void __launch_bounds__(MSAT_WARPS * 32) k_msat(SegTable seg, const ui
 	uint32_t* __restrict__ pos2, uint32_t max_motif)
 {
 	__shared__ uint64_t s_words[MSAT_WARPS][36];                       // planar words tile_word0 - 1 .. tile_word0 + 34
-	__shared__ uint32_t s_cand[MSAT_WARPS][32 * 33];                   // per lane: (run end << 3) | (7 - motif) of its candidates, in position order
+	__shared__ uint32_t s_cand[MSAT_WARPS][32 * 33];                   // per lane: (run end << 3) | (7 - motif) of the candidate at each of its 32 positions, then of its emitted runs
 	__align__(16) __shared__ uint16_t s_codes[MSAT_WARPS][MSAT_STAGE];
 	const uint32_t lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
 	const uint32_t g = blockIdx.x * MSAT_WARPS + wid;
@@ -646,46 +646,47 @@ __global__ void __launch_bounds__(MSAT_WARPS * 32) k_msat(SegTable seg, const ui
 				cand_any |= run;
 			}
 		}
-		// ---- pass 1: every candidate position in order -> largest end (then smallest motif) among the runs starting there
+		// ---- pass 1: per candidate position the largest end (then smallest motif) among the runs starting there, kept in my_cand[position].
+		// One loop per motif length over the bits of its own candidate mask: a lane's e0 / e1 / cm of that length are registers, and the
+		// body runs once per round (the loop over positions with five predicated motif branches inside it ran every branch for a handful
+		// of lanes: 17 % of the kernel's instructions at 6 of 32 lanes)
 		uint32_t local_max = 0;
 		{
-			uint32_t cb = cand_any, j = 0;
-			while (cb)
-			{
-				const uint32_t b = __ffs(cb) - 1;
-				cb &= cb - 1;
-				uint32_t best = 0;
+			uint32_t seen = 0;
 #pragma unroll
-				for (uint32_t m = 2; m <= 6; m++)
+			for (uint32_t m = 2; m <= 6; m++)
+			{
+				uint32_t cbm = cm[m];
+				while (cbm)
 				{
-					if ((cm[m] >> b) & 1)
+					const uint32_t b = __ffs(cbm) - 1;
+					cbm &= cbm - 1;
+					// eq_m holds from b to the first zero above it; beyond the 64 positions this lane sees, walk on
+					const uint32_t stop_lo = ~funnel_r(e0[m], e1[m], b), stop_hi = ~(e1[m] >> b);
+					uint32_t q = p0 + 64;
+					if (stop_lo) q = p0 + b + (__ffs(stop_lo) - 1);
+					else if (stop_hi) q = p0 + b + 32 + (__ffs(stop_hi) - 1);      // (the shifted-in zeros stop it at p0 + 64 at the latest)
+					if (q >= p0 + 64)
 					{
-						// eq_m holds from b to the first zero above it; beyond the 64 positions this lane sees, walk on
-						const uint32_t stop_lo = ~funnel_r(e0[m], e1[m], b), stop_hi = ~(e1[m] >> b);
-						uint32_t q = p0 + 64;
-						if (stop_lo) q = p0 + b + (__ffs(stop_lo) - 1);
-						else if (stop_hi) q = p0 + b + 32 + (__ffs(stop_hi) - 1);      // (the shifted-in zeros stop it at p0 + 64 at the latest)
-						if (q >= p0 + 64)
+						const uint32_t lim = n - m;
+						q = p0 + 64;
+						while (q < lim)
 						{
-							const uint32_t lim = n - m;
-							q = p0 + 64;
-							while (q < lim)
-							{
-								const Planes x = win(q), y = win(q + m);
-								uint32_t ne = (x.lo ^ y.lo) | (x.hi ^ y.hi);
-								const uint32_t room = lim - q;
-								if (room < 32) ne |= ~low_bits(room);
-								if (ne) { q += __ffs(ne) - 1; break; }
-								q += 32;
-							}
-							if (q > lim) q = lim;
+							const Planes x = win(q), y = win(q + m);
+							uint32_t ne = (x.lo ^ y.lo) | (x.hi ^ y.hi);
+							const uint32_t room = lim - q;
+							if (room < 32) ne |= ~low_bits(room);
+							if (ne) { q += __ffs(ne) - 1; break; }
+							q += 32;
 						}
-						const uint32_t val = ((q + m) << 3) | (7 - m);   // larger end wins, then smaller motif
-						best = max(best, val);
+						if (q > lim) q = lim;
 					}
+					uint32_t val = ((q + m) << 3) | (7 - m);   // larger end wins, then smaller motif
+					if ((seen >> b) & 1) val = max(val, my_cand[b]);
+					my_cand[b] = val;
+					local_max = max(local_max, val >> 3);
 				}
-				my_cand[j++] = best;
-				local_max = max(local_max, best >> 3);
+				seen |= cm[m];
 			}
 		}
 		// ---- scan 1: exclusive prefix maximum of candidate ends
@@ -706,12 +707,12 @@ __global__ void __launch_bounds__(MSAT_WARPS * 32) k_msat(SegTable seg, const ui
 		uint32_t emit_bits = 0, n_emit = 0, ge1 = 0, ge2_own = 0;
 		uint32_t my_sm = 0, my_pe = 0;     // latest emitted run of this word: start | m << 29, end of the run emitted before it
 		{
-			uint32_t running = pm_in, cb = cand_any, j = 0;
+			uint32_t running = pm_in, cb = cand_any;
 			while (cb)
 			{
 				const uint32_t b = __ffs(cb) - 1;
 				cb &= cb - 1;
-				const uint32_t val = my_cand[j++];
+				const uint32_t val = my_cand[b];      // (the emitted ones are packed to the front below: never past the entry just read)
 				const uint32_t end = val >> 3;
 				if (end > running)
 				{
