@@ -942,7 +942,10 @@ __global__ void k_build_roll_tables(const uint4* __restrict__ tab_pair, uint4* _
 	tab_out[c] = make_uint4((uint32_t)out_f, (uint32_t)(out_f >> 32), (uint32_t)out_b, (uint32_t)(out_b >> 32));
 }
 
-template <int NT>
+// SR = s mod 8 is a template parameter: where the second prefix of a block sits, which words of the 16-code window hold the incoming
+// characters and whether they need the 16-bit funnel are then decided at compile time (as run-time values they cost 32 predicated
+// moves per thread and tile for the capture alone).
+template <int NT, int SR>
 __global__ void __launch_bounds__(NT) k_select(SegTable seg, const uint16_t* __restrict__ codes, const uint32_t* __restrict__ seg_c2,
 	const uint4* __restrict__ tab_pair, const uint4* __restrict__ tab_in, const uint4* __restrict__ tab_out, uint8_t* __restrict__ selmask,
 	uint32_t* __restrict__ seg_nsel, uint32_t k, uint32_t w, SelectPlan plan)
@@ -970,7 +973,8 @@ __global__ void __launch_bounds__(NT) k_select(SegTable seg, const uint16_t* __r
 	const uint32_t s = k - w + 1;
 	const uint32_t n_kmers = n - k + 1, n_smers = n - s + 1;
 	const uint32_t a = (w - 1) >> 3, r = (w - 1) & 7;
-	const uint32_t sa = s >> 3, sr = s & 7;
+	const uint32_t sa = s >> 3;
+	constexpr uint32_t sr = SR;      // == s & 7 (the host picks the instantiation)
 	const uint32_t rot_s1 = (s - 1) & 63, rot_s = s & 63;
 	const uint32_t lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
 	if (threadIdx.x < 4) { small_tab[threadIdx.x] = __ldg(tab_pair + threadIdx.x); small_in[threadIdx.x] = __ldg(tab_in + threadIdx.x); small_out[threadIdx.x] = __ldg(tab_out + threadIdx.x); }
@@ -1032,7 +1036,7 @@ __global__ void __launch_bounds__(NT) k_select(SegTable seg, const uint16_t* __r
 #pragma unroll
 				for (int i = 0; i < NT / 32 - 1; i++) { const Xor2 t = warp_tot[i]; if (i < (int)wid) { wbase.a ^= t.a; wbase.b ^= t.b; } }
 				const uint64_t pv = rotl_c(wbase.a, (8 * lane) & 63) ^ ep, qv = rotr_c(wbase.b, (8 * lane) & 63) ^ eq;      // P'[j0], Q'[j0]
-				const uint64_t ps = rotl_v(pv, sr) ^ cap_p, qs = rotr_v(qv, sr) ^ cap_q;                                  // P'[j0 + sr], Q'[j0 + sr]
+				const uint64_t ps = rotl_c(pv, sr) ^ cap_p, qs = rotr_c(qv, sr) ^ cap_q;                                  // P'[j0 + sr], Q'[j0 + sr]
 				pq[2 * blk] = make_uint4((uint32_t)pv, (uint32_t)(pv >> 32), (uint32_t)qv, (uint32_t)(qv >> 32));
 				pq[2 * blk + 1] = make_uint4((uint32_t)ps, (uint32_t)(ps >> 32), (uint32_t)qs, (uint32_t)(qs >> 32));
 				if (threadIdx.x == NT - 1) { Xor2 t; t.a = rotl_c(pv, 8) ^ lp; t.b = rotr_c(qv, 8) ^ lq; s_carry[parity ^ 1] = t; }      // P'[t0 + T]

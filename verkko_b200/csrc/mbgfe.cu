@@ -507,7 +507,14 @@ int mbgfe_create(const mbgfe_params* prm, mbgfe** out)
 	cudaFuncSetAttribute(k_collapse_lut, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(65536 + COLLAPSE_LUT_WARPS * 2 * COLLAPSE_STAGE * 4));
 	if (ensure(h, h->tab_in, MAX_CODE * 16) || ensure(h, h->tab_out, MAX_CODE * 16)) return bail(MBGFE_E_CUDA);
 	MBGFE_LAUNCH(k_build_roll_tables, (MAX_CODE + 255) / 256, 256, 0, h->stream, h->tab_pair.as<uint4>(), h->tab_in.as<uint4>(), h->tab_out.as<uint4>(), prm->k - prm->w + 1);
-	cudaFuncSetAttribute(k_select<NT_SELECT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->plan.smem_bytes);
+	cudaFuncSetAttribute(k_select<NT_SELECT, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->plan.smem_bytes);
+	cudaFuncSetAttribute(k_select<NT_SELECT, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->plan.smem_bytes);
+	cudaFuncSetAttribute(k_select<NT_SELECT, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->plan.smem_bytes);
+	cudaFuncSetAttribute(k_select<NT_SELECT, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->plan.smem_bytes);
+	cudaFuncSetAttribute(k_select<NT_SELECT, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->plan.smem_bytes);
+	cudaFuncSetAttribute(k_select<NT_SELECT, 5>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->plan.smem_bytes);
+	cudaFuncSetAttribute(k_select<NT_SELECT, 6>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->plan.smem_bytes);
+	cudaFuncSetAttribute(k_select<NT_SELECT, 7>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->plan.smem_bytes);
 	if (cudaStreamSynchronize(h->stream) != cudaSuccess || cudaGetLastError() != cudaSuccess)
 		return bail(fail(h, MBGFE_E_CUDA, "table kernel failed: is this an sm_100 device?"));
 	*out = h;
@@ -758,8 +765,13 @@ uint32_t launch_front(mbgfe* h, uint32_t g0, uint32_t cnt, bool timed, cudaStrea
 		MBGFE_LAUNCH(k_unpack_symbols<NT_MSAT>, cnt, NT_MSAT, 0, on, st, h->d_sym.as<uint64_t>(), c1, h->d_codes.as<uint16_t>(),
 			c2, (const uint32_t*)pos1, pos2);
 	if (timed) tick(h, 5);
-	MBGFE_LAUNCH(k_select<NT_SELECT>, cnt, NT_SELECT, h->plan.smem_bytes, on, st, h->d_codes.as<uint16_t>(), c2, h->tab_pair.as<uint4>(), h->tab_in.as<uint4>(),
-		h->tab_out.as<uint4>(), h->d_selmask.as<uint8_t>(), h->d_seg_nsel.as<uint32_t>() + g0, k, w, h->plan);
+#define MBGFE_SELECT_CASE(SR) case SR: MBGFE_LAUNCH((k_select<NT_SELECT, SR>), cnt, NT_SELECT, h->plan.smem_bytes, on, st, h->d_codes.as<uint16_t>(), c2, h->tab_pair.as<uint4>(), \
+		h->tab_in.as<uint4>(), h->tab_out.as<uint4>(), h->d_selmask.as<uint8_t>(), h->d_seg_nsel.as<uint32_t>() + g0, k, w, h->plan); break;
+	switch ((k - w + 1) & 7)      // s mod 8
+	{
+		MBGFE_SELECT_CASE(0) MBGFE_SELECT_CASE(1) MBGFE_SELECT_CASE(2) MBGFE_SELECT_CASE(3) MBGFE_SELECT_CASE(4) MBGFE_SELECT_CASE(5) MBGFE_SELECT_CASE(6) MBGFE_SELECT_CASE(7)
+	}
+#undef MBGFE_SELECT_CASE
 	return 3;
 }
 
