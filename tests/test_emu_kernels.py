@@ -32,6 +32,14 @@ def test_emulated_select_shapes(oracle, emu_library, k, w):
         compare_runs(got, oracle.run(mode, k, w, reads), what=f"select shape {mode} k={k} w={w} s%8={(k - w + 1) % 8}")
 
 
+@pytest.mark.parametrize("seed", range(24))
+def test_emulated_random_inputs(oracle, emu_library, seed):
+    """seeded random configurations against the oracle (workloads.random_case): any mode, odd k from 31, any legal w, reads of
+    repeats and plain sequence, lengths around k and around the tile boundaries, stray characters, lower case, duplicates"""
+    mode, k, w, reads = workloads.random_case(seed)
+    compare_runs(run_frontend(mode, k, w, reads, library=emu_library), oracle.run(mode, k, w, reads), what=f"random seed={seed} {mode} k={k} w={w}")
+
+
 def test_emulated_kernels_table_with_coverage(oracle, emu_library):
     reads = workloads.coverage_reads(n_reads=6)
     compare_runs(run_frontend("collapse-msat", 501, 50, reads, library=emu_library), oracle.run("collapse-msat", 501, 50, reads), what="coverage")

@@ -404,3 +404,10 @@ def test_select_shapes_on_gpu(oracle):
         reads = [a[:3000 + 7 * i] for i in range(10)] + [workloads.repeat_rich(k + w, 4000), workloads.long_tandem_reads()[0][:6000], a[:k + 40], a[:k], a[:k - 1]]
         compare_runs(run_frontend("collapse-msat", k, w, reads), oracle.run("collapse-msat", k, w, reads), what=f"select shape k={k} w={w}")
 
+
+def test_random_inputs_on_gpu(oracle):
+    """the seeded random configurations of tests/test_emu_kernels.py::test_emulated_random_inputs, and more of them, on the real library"""
+    for seed in range(48):
+        mode, k, w, reads = workloads.random_case(seed)
+        compare_runs(run_frontend(mode, k, w, reads), oracle.run(mode, k, w, reads), what=f"random seed={seed} {mode} k={k} w={w}")
+

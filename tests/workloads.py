@@ -115,3 +115,28 @@ def diploid_msat_reads(seed=3, genome_len=150000, n_loci=60, coverage_each=15, l
     bases = np.concatenate([parts[0][0], parts[1][0]])
     offsets = np.concatenate([parts[0][1], parts[1][1][1:] + parts[0][1][-1]])
     return bases, offsets
+
+
+def random_case(seed):
+    """(mode, k, w, reads) of a seeded random configuration: any mode, odd k from 31, any legal w, reads of repeats and plain
+    sequence, lengths around k and around the 32-base / 1 024-symbol tile boundaries, stray characters, lower case, and the
+    first two reads once more (coverage 2 on their k-mers, their edges seen twice)"""
+    from oracle_lib import MODES
+    rng = np.random.default_rng(1000 + seed)
+    mode = list(MODES)[int(rng.integers(0, len(MODES)))]
+    k = 31 + 2 * int(rng.integers(0, 120))
+    w = int(rng.integers(1, k - 30 + 1))
+    reads = []
+    for _ in range(int(rng.integers(3, 9))):
+        n = int(rng.choice([k - 1, k, k + 1, k + 33, 1024, 1025, 2048 + 31, int(rng.integers(40, 6000))]))
+        body = repeat_rich(int(rng.integers(1, 1 << 30)), n) if rng.random() < 0.5 else lcg_bases(int(rng.integers(1, 1 << 20)), n)
+        body = bytearray(body)
+        if rng.random() < 0.3 and n > 10:
+            for _ in range(int(rng.integers(1, 4))):
+                at = int(rng.integers(0, n - 3))
+                body[at:at + int(rng.integers(1, 4))] = b"NRN"[:int(rng.integers(1, 4))]
+        if rng.random() < 0.2:
+            body = bytearray(bytes(body).lower())
+        reads.append(bytes(body[:n]))
+    return mode, k, w, reads + reads[:2]
+
