@@ -679,9 +679,9 @@ def main():
             "roofline": {"bound": "hbm", "kernel": dominant, "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": None,
                          "peak_source": peak_src,
                          # what ncu says limits each kernel (profiles/r02_ncu_full_front_scale1.txt); none of them is DRAM-bound
-                         "limiter": {"k_select": "ALU pipe: 64-bit min / compare / xor / rotate are 2-4 32-bit ALU instructions each (ISETP+SEL 37 % of the instructions), issue 62 %",
-                                     "k_kmer_hash": "a chain of latencies: issue 52 %, LSU data pipe 75 % (shared-memory f loads), fmaheavy 59 % (Murmur64A multiplies), barrier stall 9.7 per issue",
-                                     "k_msat": "instruction issue 82 % with 17.5 of 32 lanes active (per-lane candidate and stretch loops)",
+                         "limiter": {"k_select": "ALU pipe 83 % and LSU data pipe 83 %: 64-bit min / compare / xor / rotate are 2-4 32-bit ALU instructions each, table and ring reads; issue 64 %",
+                                     "k_kmer_hash": "a chain of latencies: issue 50 %, LSU data pipe 79 % (shared-memory f loads), fmaheavy 53 % (Murmur64A multiplies), barrier stall 9.9 per issue",
+                                     "k_msat": "instruction issue 80 %, ALU pipe 77 %, divergence in the per-lane candidate and stretch loops",
                                      "k_collapse": "LSU data pipe 91 % (byte-table lookups in shared memory), issue 59 %",
                                      "k_insert_nodes": "DRAM sectors + atomics (random 32-byte slots)", "k_insert_edges": "DRAM sectors + atomics (random 32-byte slots)"},
                          "all_kernels_GBps": {n: (b / (m * 1e-3) / 1e9 if m > 0 else None) for n, (b, m) in alg.items()}},
