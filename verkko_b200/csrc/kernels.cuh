@@ -1158,10 +1158,6 @@ __global__ void __launch_bounds__(NT) k_select(SegTable seg, const uint16_t* __r
 				}
 				else
 				{
-					uint64_t suf[8];
-					suf[7] = own[7];
-#pragma unroll
-					for (int t = 6; t >= 0; t--) suf[t] = own[t] < suf[t + 1] ? own[t] : suf[t + 1];
 					uint64_t core = INF;                                 // blocks b+1 .. b+a-1
 					{
 						// blocks d0+1 .. d0+a-1 of the ring, read through its mirrored head when a <= BM_MIRROR (no wrap), else in two runs
@@ -1183,6 +1179,10 @@ __global__ void __launch_bounds__(NT) k_select(SegTable seg, const uint16_t* __r
 					}
 					uint32_t e0 = d0 + a; if (e0 >= NBH) e0 -= NBH;      // block that holds the window ends
 					uint32_t e1 = e0 + 1; if (e1 >= NBH) e1 -= NBH;
+					uint64_t suf[8];                                     // suf[j] = min(own[j..7], inner blocks)
+					suf[7] = own[7] < core ? own[7] : core;
+#pragma unroll
+					for (int t = 6; t >= 0; t--) suf[t] = own[t] < suf[t + 1] ? own[t] : suf[t + 1];
 					uint64_t run = pre[e0];
 					const uint64_t* l0 = hr + (size_t)e0 * 10;
 					const uint64_t* l1 = hr + (size_t)e1 * 10;
@@ -1191,8 +1191,7 @@ __global__ void __launch_bounds__(NT) k_select(SegTable seg, const uint16_t* __r
 					{
 						const uint64_t last = (j + r < 8) ? l0[j + r] : l1[j + r - 8];
 						run = last < run ? last : run;
-						uint64_t wmin = suf[j] < core ? suf[j] : core;
-						wmin = run < wmin ? run : wmin;
+						const uint64_t wmin = run < suf[j] ? run : suf[j];
 						if (own[j] == wmin || last == wmin) bits |= 1u << j;
 					}
 				}
