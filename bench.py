@@ -303,15 +303,27 @@ def run_hg002(args, rank, world, local_rank, dist, torch, emit):
         else:
             fe.build_table()
     # ---- resident per batch: upload untimed, front end timed on the device, then the table / exchange
+    stage_sum = {}
+
     def resident_step():
         fe.reset()
         ms = 0.0
+        for kname in list(stage_sum):
+            stage_sum[kname] = 0.0
         for b, o in batches:
             fe.add_reads(b, o)
             fe.upload_append()
             fe.timer_start()
             fe.process_append()
             ms += fe.timer_stop()
+            stb = fe.stats()
+            for kname in ("ms_collapse", "ms_msat", "ms_select", "ms_hash", "ms_process"):      # per kernel stage, by events around the launches
+                stage_sum[kname] = stage_sum.get(kname, 0.0) + stb[kname]
+        stage_sum["ms_batches_timer"] = ms      # the same batches by one timer around each call (adds what the host leaves idle between launches)
+        # every rank enters the collective together: the uploads between the timed regions are untimed, and without this a rank whose
+        # uploads are quicker (the GPUs on the other socket of the box) waits inside its timed exchange for the ranks still uploading
+        # -- measured at N = 8: 66 ms on four ranks, 150 ms on the other four for the same work
+        barrier()
         fe.timer_start()
         finish()
         return ms + fe.timer_stop()
@@ -342,9 +354,13 @@ def run_hg002(args, rank, world, local_rank, dist, torch, emit):
     st_e = fe.stats()
     t = torch.tensor([float(np.mean(dev_ms)), float(np.mean(e2e_ms))], dtype=torch.float64)
     sm = torch.tensor([float(n_bases), float(st_e["selected"]), float(st_e["distinct"]), float(st_e["distinct_edges"])], dtype=torch.float64)
+    per_rank_ms = [float(np.mean(dev_ms))]
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         dist.all_reduce(sm, op=dist.ReduceOp.SUM)
+        gathered = [None] * world
+        dist.all_gather_object(gathered, float(np.mean(dev_ms)))
+        per_rank_ms = gathered
     if rank == 0:
         peak, peak_src = measured_peak()
         line = {"metric": METRIC, "value": float(sm[0]) / (float(t[0]) * 1e-3), "unit": "bases/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
@@ -357,6 +373,7 @@ def run_hg002(args, rank, world, local_rank, dist, torch, emit):
                 "exchange": {"ms": st["ms_exchange"], "bytes_sent_rank0": st["exchange_bytes"], "launches": st["exchange_launches"],
                              "nvlink_GBps_rank0": (st["exchange_bytes"] / (st["ms_exchange"] * 1e-3) / 1e9) if st["ms_exchange"] > 0 else None, "nvlink_peak_GBps": 900.0},
                 "clocks": clocks, "gpu_launches": int((st["launches"] * len(batches) + st["exchange_launches"]) * args.steps),
+                "stage_ms_per_step_rank0": dict(stage_sum), "ms_per_step_by_rank": per_rank_ms,
                 "e2e": {"value": float(sm[0]) / (float(t[1]) * 1e-3), "unit": "bases/s", "ms_per_step": float(t[1]), "h2d_bytes_per_step": int(st_e["h2d_bytes"] * len(batches)),
                         "d2h_bytes_per_step": int(st_e["d2h_bytes"]), "checksum": checksum}}
         emit(json.dumps(line))
