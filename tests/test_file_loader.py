@@ -109,6 +109,48 @@ def test_emulated_streaming_fasta(oracle, emu_library, tmp_path, piece):
         assert got["stats"]["h2d_bytes"] < (len(data) + len(second)) // 3, "the bus must carry packed bases, not the file"
 
 
+def random_fasta(seed):
+    """single-line records with runs of characters outside ACGT of every kind the collapse rule distinguishes: the same character
+    repeated, different ones in a row, lower and upper case mixed inside a run, at the start and at the end of a read, next to a
+    base, a lone \\r in the middle, \\r\\n line ends, empty records and empty lines"""
+    rng = np.random.default_rng(seed)
+    out = b""
+    for r in range(int(rng.integers(3, 9))):
+        n = int(rng.integers(20, 5000))
+        seq = bytearray(workloads.repeat_rich(int(rng.integers(1, 1 << 30)), n) if rng.random() < 0.5 else lcg_bases(int(rng.integers(1, 1 << 20)), n))
+        for _ in range(int(rng.integers(0, 6))):
+            at = int(rng.integers(0, n))
+            run = bytes(rng.choice(list(b"NNNRYnrK\r-*"), size=int(rng.integers(1, 7))).astype(np.uint8))
+            seq[at:at + len(run)] = run
+        seq = bytes(seq[:n])
+        if rng.random() < 0.2:
+            seq = b"N" * int(rng.integers(1, 4)) + seq
+        if rng.random() < 0.2:
+            seq = seq + b"n" * int(rng.integers(1, 4))
+        if rng.random() < 0.15:
+            seq = seq.lower()
+        end = b"\r\n" if rng.random() < 0.3 else b"\n"
+        out += b">read %d of seed %d" % (r, seed) + end
+        if rng.random() < 0.9:
+            out += seq + end
+        if rng.random() < 0.3:
+            out += b"\n"
+    return out
+
+
+@pytest.mark.parametrize("seed", range(16))
+def test_emulated_streaming_fasta_random(oracle, emu_library, tmp_path, seed):
+    """the stitcher cuts reads at characters outside ACGT itself (no second pass over the image): random files against the oracle fed
+    what the reference's parser would hand over, in the modes where the collapse step looks at those characters"""
+    data = random_fasta(seed)
+    fa = tmp_path / "random.fa"
+    fa.write_bytes(data)
+    mode, k, w = [("collapse-msat", 101, 20), ("collapse", 31, 1), ("hpc", 63, 33), ("collapse-dinuc", 63, 9)][seed % 4]
+    got = run_file([fa], mode, k, w, library=emu_library, piece_bytes=[0, 256, 4096, 96][(seed // 4) % 4])
+    check_against_oracle(oracle, got, [data], mode, k, w, f"random fasta seed={seed} {mode}")
+    assert got["stats"]["h2d_bytes"] < len(data) // 3 + 4096, "the streaming loader ran (packed bases on the bus), not the plain parser"
+
+
 def test_emulated_streaming_fasta_falls_back_on_multiline(oracle, emu_library, tmp_path):
     a = workloads.read_a()
     data = b">one\n" + a[:5000] + b"\n>two\n" + b"\n".join(a[5000 + i:5000 + i + 70] for i in range(0, 4000, 70)) + b"\n>three\n" + a[9000:15000] + b"\n"
