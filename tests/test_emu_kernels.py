@@ -228,6 +228,33 @@ def test_emulated_read_threading(oracle, emu_library, mode, k, w, a, u, one_cov,
     assert len(want.paths.heads) > 0
 
 
+@pytest.mark.parametrize("seed", range(12))
+def test_emulated_graph_stage_random(oracle, emu_library, seed):
+    """rows a14 / f1 / f2 on seeded random read sets against the oracle: a genome with repeats read at 6 .. 14x with 0.2 .. 1.5 %
+    errors (tips, bubbles and coverage-1 k-mers for the filters), random mode / k / w / -a / -u, with and without the one-coverage
+    heuristic: kept flags, unitigs, unitig edges and the read paths"""
+    from fe_helpers import run_frontend_unitigs
+    from oracle_lib import compare_paths
+    from verkko_b200 import synth
+    rng = np.random.default_rng(500 + seed)
+    mode = ["collapse-msat", "hpc", "no", "msat"][seed % 4]
+    k = 31 + 2 * int(rng.integers(10, 140))
+    w = int(rng.integers(3, min(60, k - 30) + 1))
+    glen = int(rng.integers(6000, 20000))
+    g = synth.genome(int(rng.integers(1, 1 << 20)), glen)
+    if seed % 3 == 0:          # a repeat of a few hundred bases: branching unitigs
+        g = np.concatenate([g, g[1000:1600], synth.genome(int(rng.integers(1, 1 << 20)), 3000)])
+    cov = int(rng.integers(6, 15))
+    lmin = max(2 * k + 100, 1500)
+    reads = synth.reads(int(rng.integers(1, 1 << 20)), g, cov * len(g) // (lmin + 1000), lmin, lmin + 2000, int(rng.integers(2000, 15000)))
+    a, u = int(rng.integers(1, 3)), int(rng.integers(1, 4))
+    one_cov = bool(seed & 1)
+    _, got = run_frontend_unitigs(mode, k, w, reads, a, u, library=emu_library, one_cov=one_cov, paths=True)
+    _, want = oracle.run_unitigs(mode, k, w, reads, a, u, one_cov=one_cov, paths=True)
+    check_unitigs(got, want, f"random graph stage seed={seed} {mode} k={k} w={w} a={a} u={u}")
+    compare_paths(got.paths, got, want.paths, want, f"random read paths seed={seed}")
+
+
 def test_emulated_graph_stage_on_empty_and_tiny_tables(oracle, emu_library):
     """edge cases of rows a14 / f1 / f2: no k-mer at all, a single read whose k-mers all have coverage 1 (everything is
     filtered), reads shorter than 32 bases"""
@@ -294,6 +321,23 @@ def test_emulated_thinning_applied_and_read_paths_on_the_thinned_list(oracle, em
     reads = workloads.coverage_reads(n_reads=16, error_ppm=4000)
     n_paths, n_new = run_thinned_pass("collapse-msat", 301, 30, reads, 1, 2, oracle, library=emu_library, what="emu thinned pass")
     assert n_paths > 5 and n_new > 5
+
+
+@pytest.mark.parametrize("seed", range(8))
+def test_emulated_thinned_pass_random(oracle, emu_library, seed):
+    """MBG's default order on seeded random read sets: unitigs -> filterKmersToUnitigKmers applied -> read threading on the thinned
+    list (fe_helpers.run_thinned_pass checks the thinned tables, the new overlaps and the read paths against the oracle)"""
+    from fe_helpers import run_thinned_pass
+    from verkko_b200 import synth
+    rng = np.random.default_rng(900 + seed)
+    mode = ["collapse-msat", "hpc", "no", "collapse-dinuc"][seed % 4]
+    k = 31 + 2 * int(rng.integers(10, 140))
+    w = int(rng.integers(3, min(40, k - 30) + 1))
+    g = synth.genome(int(rng.integers(1, 1 << 20)), int(rng.integers(8000, 20000)))
+    lmin = max(2 * k + 100, 1500)
+    cov = int(rng.integers(8, 15))
+    reads = synth.reads(int(rng.integers(1, 1 << 20)), g, cov * len(g) // (lmin + 1000), lmin, lmin + 2000, int(rng.integers(1000, 8000)))
+    run_thinned_pass(mode, k, w, reads, 1, int(rng.integers(1, 3)), oracle, library=emu_library, what=f"random thinned pass seed={seed} {mode} k={k} w={w}")
 
 
 @pytest.mark.parametrize("pct,mode,k,w", [("100", "hpc", 63, 33), ("50", "collapse-msat", 301, 30)])
