@@ -235,20 +235,7 @@ def test_emulated_graph_stage_random(oracle, emu_library, seed):
     heuristic: kept flags, unitigs, unitig edges and the read paths"""
     from fe_helpers import run_frontend_unitigs
     from oracle_lib import compare_paths
-    from verkko_b200 import synth
-    rng = np.random.default_rng(500 + seed)
-    mode = ["collapse-msat", "hpc", "no", "msat"][seed % 4]
-    k = 31 + 2 * int(rng.integers(10, 140))
-    w = int(rng.integers(3, min(60, k - 30) + 1))
-    glen = int(rng.integers(6000, 20000))
-    g = synth.genome(int(rng.integers(1, 1 << 20)), glen)
-    if seed % 3 == 0:          # a repeat of a few hundred bases: branching unitigs
-        g = np.concatenate([g, g[1000:1600], synth.genome(int(rng.integers(1, 1 << 20)), 3000)])
-    cov = int(rng.integers(6, 15))
-    lmin = max(2 * k + 100, 1500)
-    reads = synth.reads(int(rng.integers(1, 1 << 20)), g, cov * len(g) // (lmin + 1000), lmin, lmin + 2000, int(rng.integers(2000, 15000)))
-    a, u = int(rng.integers(1, 3)), int(rng.integers(1, 4))
-    one_cov = bool(seed & 1)
+    mode, k, w, reads, a, u, one_cov = workloads.random_graph_case(seed)
     _, got = run_frontend_unitigs(mode, k, w, reads, a, u, library=emu_library, one_cov=one_cov, paths=True)
     _, want = oracle.run_unitigs(mode, k, w, reads, a, u, one_cov=one_cov, paths=True)
     check_unitigs(got, want, f"random graph stage seed={seed} {mode} k={k} w={w} a={a} u={u}")

@@ -411,3 +411,17 @@ def test_random_inputs_on_gpu(oracle):
         mode, k, w, reads = workloads.random_case(seed)
         compare_runs(run_frontend(mode, k, w, reads), oracle.run(mode, k, w, reads), what=f"random seed={seed} {mode} k={k} w={w}")
 
+
+def test_graph_stage_random_on_gpu(oracle):
+    """rows a14 / f1 / f2 on the seeded random read sets of tests/test_emu_kernels.py::test_emulated_graph_stage_random (and as many
+    again), on the real library: kept flags, unitigs, unitig edges, read paths"""
+    from fe_helpers import run_frontend_unitigs
+    from oracle_lib import compare_paths, compare_unitigs
+    for seed in range(24):
+        mode, k, w, reads, a, u, one_cov = workloads.random_graph_case(seed)
+        _, got = run_frontend_unitigs(mode, k, w, reads, a, u, one_cov=one_cov, paths=True)
+        _, want = oracle.run_unitigs(mode, k, w, reads, a, u, one_cov=one_cov, paths=True)
+        assert np.array_equal(got.kept, want.kept), f"seed {seed}: kept flags differ"
+        compare_unitigs(got, want, f"random graph stage seed={seed} {mode} k={k} w={w} a={a} u={u}")
+        compare_paths(got.paths, got, want.paths, want, f"random read paths seed={seed}")
+

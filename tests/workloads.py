@@ -140,3 +140,21 @@ def random_case(seed):
         reads.append(bytes(body[:n]))
     return mode, k, w, reads + reads[:2]
 
+
+def random_graph_case(seed):
+    """(mode, k, w, reads, a, u, one_cov) of a seeded random read set for the graph stage: a genome (every third one with a repeat of
+    a few hundred bases) read at 6 .. 14x with 0.2 .. 1.5 % errors -- tips, bubbles and coverage-1 k-mers for the filters"""
+    from verkko_b200 import synth
+    rng = np.random.default_rng(500 + seed)
+    mode = ["collapse-msat", "hpc", "no", "msat"][seed % 4]
+    k = 31 + 2 * int(rng.integers(10, 140))
+    w = int(rng.integers(3, min(60, k - 30) + 1))
+    glen = int(rng.integers(6000, 20000))
+    g = synth.genome(int(rng.integers(1, 1 << 20)), glen)
+    if seed % 3 == 0:
+        g = np.concatenate([g, g[1000:1600], synth.genome(int(rng.integers(1, 1 << 20)), 3000)])
+    cov = int(rng.integers(6, 15))
+    lmin = max(2 * k + 100, 1500)
+    reads = synth.reads(int(rng.integers(1, 1 << 20)), g, cov * len(g) // (lmin + 1000), lmin, lmin + 2000, int(rng.integers(2000, 15000)))
+    return mode, k, w, reads, int(rng.integers(1, 3)), int(rng.integers(1, 4)), bool(seed & 1)
+
