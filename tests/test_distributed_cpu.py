@@ -99,3 +99,47 @@ def test_partitioned_counting_in_one_process(oracle, emu_library, world):
         for fe in fes:
             fe.close()
     check_partitions(parts, oracle.run("collapse-msat", 501, 50, (bases, offsets)), world)
+
+
+@pytest.mark.parametrize("seed", range(8))
+def test_partitioned_counting_random(oracle, emu_library, seed):
+    """seeded random sharded runs in one process: world 2 .. 8 (also more ranks than reads), any mode, reads appended in one or two
+    batches per rank, an empty rank, the sketch-sized tables on odd seeds -- the partitions together are the oracle's single table,
+    and the edges are balanced over the ranks"""
+    import workloads
+    from verkko_b200 import synth
+    from verkko_b200.frontend import NO_TABLE, MbgFrontEnd
+    rng = np.random.default_rng(300 + seed)
+    world = [2, 3, 5, 8, 4, 7, 6, 2][seed]
+    mode = ["collapse-msat", "hpc", "no", "msat", "collapse-dinuc", "dinuc", "collapse", "collapse-msat"][seed]
+    k = 31 + 2 * int(rng.integers(10, 120))
+    w = int(rng.integers(3, min(50, k - 30) + 1))
+    g = synth.genome(int(rng.integers(1, 1 << 20)), int(rng.integers(8000, 16000)))
+    lmin = max(2 * k + 100, 1200)
+    bases, offsets = synth.reads(int(rng.integers(1, 1 << 20)), g, int(rng.integers(6, 40)), lmin, lmin + 1500, int(rng.integers(500, 6000)))
+    if seed & 1:
+        os.environ["MBGFE_SKETCH_MIN"] = "0"
+    try:
+        fes = [MbgFrontEnd(k, w, mode, flags=NO_TABLE, rank=r, world=world, library=emu_library) for r in range(world)]
+        try:
+            for r, fe in enumerate(fes):
+                b, o = shard(bases, offsets, r, world)
+                n = len(o) - 1
+                if seed % 3 == 0 and n >= 2:          # the rank's reads in two appended batches
+                    cut = n // 2
+                    fe.add_reads(b[:int(o[cut])], o[:cut + 1])
+                    fe.run_append()
+                    fe.add_reads(b[int(o[cut]):], o[cut:] - o[cut])
+                    fe.run_append()
+                else:
+                    fe.add_reads(b, o)
+                    fe.run()
+            MbgFrontEnd.exchange_group(fes)
+            parts = [dict(node_hash=fe.node_hashes(), node_cov=fe.node_coverage(), node_tip=fe.node_tip(), edges=fe.edges()) for fe in fes]
+        finally:
+            for fe in fes:
+                fe.close()
+    finally:
+        os.environ.pop("MBGFE_SKETCH_MIN", None)
+    check_partitions(parts, oracle.run(mode, k, w, (bases, offsets)), world)
+
