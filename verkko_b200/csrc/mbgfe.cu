@@ -216,8 +216,6 @@ uint64_t read_end_of(const mbgfe* h, uint64_t r) { return h->read_end.empty() ? 
 
 uint64_t next_pow2(uint64_t v) { uint64_t p = 1; while (p < v) p <<= 1; return p; }
 
-bool is_acgt(char c) { c &= (char)0xdf; return c == 'A' || c == 'C' || c == 'G' || c == 'T'; }
-
 enum { CTR_NONACGT = 0, CTR_PALINDROME = 1, CTR_DISTINCT = 2, CTR_EDGES = 3, CTR_CURSOR = 4 /* and 5 */, CTR_OVERFLOW = 6, CTR_OWNER = 8 /* .. 8+world */ };
 constexpr uint64_t PAL_CAP = 1 << 20;
 
